@@ -1,0 +1,1231 @@
+// cb_celt_entropy.h -- kernel A body: everything in a CELT frame that hangs off the range decoder.
+//
+// One warp per stream.  The warp walks the symbol stream in uniform control flow (header flags,
+// coarse/fine energy, tf, bit allocation, per-band theta/PVQ indices) and fans out over its 32
+// lanes for the per-band vector work (residual normalisation, spreading rotation chains,
+// Hadamard/Haar reordering, folding, stereo merge, renormalisation).  Output: the normalised
+// spectrum X, the band log-energies and the post-filter parameters for kernel B, plus the updated
+// small state.  Bit-exact with celt_decode_with_ec() up to (not including) celt_synthesis()
+// (opus-fix/celt/celt_decoder.c:713-1062) and with the decode half of celt/bands.c, celt/vq.c,
+// celt/cwrs.c, celt/rate.c, celt/quant_bands.c, celt/laplace.c.
+#pragma once
+#include "cb_common.h"
+#include "cb_rangedec.h"
+#include "cb_state.h"
+#include "celt_tables.h"
+
+// ---- small constant tables (uniform index) ------------------------------------------------
+CB_UTABLE i8 ct_tf_select[4][8] = {   // celt.c:247-252
+    {0, -1, 0, -1, 0, -1, 0, -1}, {0, -1, 0, -2, 1, 0, 1, -1},
+    {0, -2, 0, -3, 2, 0, 1, -1},  {0, -2, 0, -3, 3, 0, 1, -1}};
+CB_UTABLE u8 ct_trim_icdf[11] = {126, 124, 119, 109, 87, 41, 19, 9, 4, 2, 0};   // celt.h:150
+CB_UTABLE u8 ct_spread_icdf[4] = {25, 23, 2, 0};                               // celt.h:152
+CB_UTABLE u8 ct_tapset_icdf[3] = {2, 1, 0};                                     // celt.h:154
+CB_UTABLE u8 ct_small_energy_icdf[3] = {2, 1, 0};                               // quant_bands.c:142
+CB_UTABLE i16 ct_pred_coef[4] = {29440, 26112, 21248, 16384};                   // quant_bands.c:66
+CB_UTABLE i16 ct_beta_coef[4] = {30147, 22282, 12124, 6554};                    // quant_bands.c:67
+CB_UTABLE u8 ct_ordery[30] = {1, 0, 3, 0, 2, 1, 7, 0, 4, 3, 6, 1, 5, 2,          // bands.c:525-530
+                              15, 0, 8, 7, 12, 3, 11, 4, 14, 1, 9, 6, 13, 2, 10, 5};
+CB_UTABLE i16 ct_exp2_table8[8] = {16384, 17866, 19483, 21247, 23170, 25267, 27554, 30048};
+CB_UTABLE u8 ct_bit_interleave[16] = {0, 1, 1, 1, 2, 3, 3, 3, 2, 3, 3, 3, 2, 3, 3, 3};
+CB_UTABLE u8 ct_bit_deinterleave[16] = {0x00, 0x03, 0x0C, 0x0F, 0x30, 0x33, 0x3C, 0x3F,
+                                        0xC0, 0xC3, 0xCC, 0xCF, 0xF0, 0xF3, 0xFC, 0xFF};
+
+#define CB_SPREAD_NONE 0
+#define CB_SPREAD_NORMAL 2
+#define CB_SPREAD_AGGRESSIVE 3
+#define CB_MAX_FINE_BITS 8
+#define CB_FINE_OFFSET 21
+#define CB_ALLOC_STEPS 6
+
+// One level of the split recursion (quant_partition), kept in shared memory.
+struct PartFrame {
+  i16* X; i16* lowband;
+  i32 N, b, B, LM, gain, fill;
+  i32 stage, mbits, sbits, itheta, rebal0, B0, cm, gmid, gside;
+};
+
+// Per-warp shared-memory workspace of kernel A.
+struct alignas(16) EntWork {
+  i16 X[2 * CB_MAXN];
+  i16 norm[2 * CB_NORM_STRIDE];
+  i32 tmp32[88];                 // iy[176] / Hadamard temp (as i16) or allocation scratch (4x21 i32)
+  i32 pulses[CB_NBANDS];
+  i16 bandE[2 * CB_NBANDS];
+  i16 cap[CB_NBANDS];
+  i16 offsets[CB_NBANDS];
+  i8 fine_quant[CB_NBANDS];
+  i8 fine_prio[CB_NBANDS];
+  i8 tf_res[CB_NBANDS];
+  u8 collapse[2 * CB_NBANDS];
+  PartFrame stack[5];
+};
+
+struct BandCtx {
+  int i, intensity, spread, tf_change;
+  i32 remaining_bits;
+  u32 seed;
+};
+
+CB_FN int ebands(int i) { return ct_eband5ms[i]; }
+
+// ---- rate.h helpers (rate.h:48-87) --------------------------------------------------------
+CB_FN int get_pulses(int i) { return i < 8 ? i : (8 + (i & 7)) << ((i >> 3) - 1); }
+CB_FN const u8* pulse_cache(int band, int LM) { return ct_cache_bits50 + ct_cache_index50[(LM + 1) * CB_NBANDS + band]; }
+CB_FN int bits2pulses(int band, int LM, int bits) {
+  const u8* cache = pulse_cache(band, LM);
+  int lo = 0, hi = cache[0];
+  bits--;
+  for (int it = 0; it < 6; it++) {   // LOG_MAX_PSEUDO
+    int mid = (lo + hi + 1) >> 1;
+    if ((int)cache[mid] >= bits) hi = mid; else lo = mid;
+  }
+  if (bits - (lo == 0 ? -1 : (int)cache[lo]) <= (int)cache[hi] - bits) return lo;
+  return hi;
+}
+CB_FN int pulses2bits(int band, int LM, int pulses) {
+  return pulses == 0 ? 0 : pulse_cache(band, LM)[pulses] + 1;
+}
+CB_FN u32 pvq_u(int n, int k) {   // CELT_PVQ_U (cwrs.c:196)
+  int lo = n < k ? n : k, hi = n < k ? k : n;
+  return ct_pvq_u_data[ct_pvq_u_row[lo] + hi];
+}
+
+// ---- lane-parallel vector helpers -----------------------------------------------------------
+// haar1 (bands.c:581-594): independent butterflies
+CB_FN void v_haar1(i16* X, int N0, int stride) {
+  N0 >>= 1;
+  CB_WSYNC();
+  CB_LANE_LOOP(p, N0 * stride) {
+    int i = p % stride, j = p / stride;
+    int a = stride * 2 * j + i, b = stride * (2 * j + 1) + i;
+    i32 t1 = mult16_16(23170, X[a]);
+    i32 t2 = mult16_16(23170, X[b]);
+    X[a] = ext16(pshr32(add32(t1, t2), 15));
+    X[b] = ext16(pshr32(sub32(t1, t2), 15));
+  }
+  CB_WSYNC();
+}
+// deinterleave_hadamard / interleave_hadamard (bands.c:532-579), via the i16 temp
+CB_FN void v_deinterleave(i16* X, i16* tmp, int N0, int stride, int hadamard) {
+  int N = N0 * stride;
+  CB_WSYNC();
+  CB_LANE_LOOP(p, N) {
+    int i = p % stride, j = p / stride;        // source index p = j*stride+i
+    int row = hadamard ? ct_ordery[stride - 2 + i] : i;
+    tmp[row * N0 + j] = X[p];
+  }
+  CB_WSYNC();
+  CB_LANE_LOOP(p, N) X[p] = tmp[p];
+  CB_WSYNC();
+}
+CB_FN void v_interleave(i16* X, i16* tmp, int N0, int stride, int hadamard) {
+  int N = N0 * stride;
+  CB_WSYNC();
+  CB_LANE_LOOP(p, N) {
+    int i = p % stride, j = p / stride;        // destination index p = j*stride+i
+    int row = hadamard ? ct_ordery[stride - 2 + i] : i;
+    tmp[p] = X[row * N0 + j];
+  }
+  CB_WSYNC();
+  CB_LANE_LOOP(p, N) X[p] = tmp[p];
+  CB_WSYNC();
+}
+// renormalise_vector (vq.c:349-374)
+CB_FN void v_renormalise(i16* X, int N, i32 gain) {
+  CB_WSYNC();
+  i32 acc = 0;
+  CB_LANE_LOOP(j, N) acc = mac16_16(acc, X[j], X[j]);
+  i32 E = add32(1, cb_wsum(acc));
+  int k = cb_ilog2(E) >> 1;
+  i32 t = vshr32(E, 2 * (k - 7));
+  i16 g = (i16)mult16_16_p15(cb_rsqrt_norm(t), gain);
+  CB_LANE_LOOP(j, N) X[j] = ext16(pshr32(mult16_16(g, X[j]), k + 1));
+  CB_WSYNC();
+}
+// one pass of exp_rotation1 (vq.c:43-67) over `nblocks` blocks of `len` samples; the `st`
+// residue classes of a block are independent recurrences, so each lane owns whole chains.
+CB_FN void v_rot_pass(i16* X, int nblocks, int len, int st, i32 c, i32 s) {
+  i32 ms = (i16)(-s);
+  CB_WSYNC();
+  CB_LANE_LOOP(ch, nblocks * st) {
+    i16* x = X + (ch / st) * len;
+    int r = ch % st;
+    for (int i = r; i < len - st; i += st) {
+      i32 x1 = x[i], x2 = x[i + st];
+      x[i + st] = ext16(pshr32(mac16_16(mult16_16(c, x2), s, x1), 15));
+      x[i] = ext16(pshr32(mac16_16(mult16_16(c, x1), ms, x2), 15));
+    }
+    int last = len - 2 * st - 1;
+    if (last >= r) {
+      int i0 = last - ((last - r) % st);
+      for (int i = i0; i >= 0; i -= st) {
+        i32 x1 = x[i], x2 = x[i + st];
+        x[i + st] = ext16(pshr32(mac16_16(mult16_16(c, x2), s, x1), 15));
+        x[i] = ext16(pshr32(mac16_16(mult16_16(c, x1), ms, x2), 15));
+      }
+    }
+  }
+  CB_WSYNC();
+}
+// exp_rotation, decoder direction (vq.c:70-115 with dir=-1)
+CB_FN void v_exp_rotation_dec(i16* X, int len, int stride, int K, int spread) {
+  if (2 * K >= len || spread == CB_SPREAD_NONE) return;
+  int factor = spread == 1 ? 15 : spread == 2 ? 10 : 5;   // SPREAD_FACTOR[spread-1]
+  i16 gain = (i16)cb_div(mult16_16(CB_Q15ONE, len), len + factor * K);
+  i16 theta = (i16)(mult16_16_q15(gain, gain) >> 1);
+  i16 c = cb_cos_norm(theta);
+  i16 s = cb_cos_norm(sub16(CB_Q15ONE, theta));
+  int stride2 = 0;
+  if (len >= 8 * stride) {
+    stride2 = 1;
+    while ((stride2 * stride2 + stride2) * stride + (stride >> 2) < len) stride2++;
+  }
+  len = len / stride;
+  if (stride2) v_rot_pass(X, stride, len, stride2, s, c);
+  v_rot_pass(X, stride, len, 1, c, s);
+}
+
+// ---- PVQ index -> pulse vector (cwrs.c:463-541), uniform; every lane stores the same values ---
+CB_FN i32 pvq_decode(i16* y, int n, int k, u32 i) {
+  i32 yy = 0;
+  u32 p, q;
+  int s, k0;
+  i16 val;
+  while (n > 2) {
+    if (k >= n) {
+      int rowoff = ct_pvq_u_row[n];
+      p = ct_pvq_u_data[rowoff + k + 1];
+      s = -(int)(i >= p);
+      i -= p & (u32)s;
+      k0 = k;
+      q = ct_pvq_u_data[rowoff + n];
+      if (q > i) {
+        k = n;
+        do p = ct_pvq_u_data[ct_pvq_u_row[--k] + n]; while (p > i);
+      } else {
+        for (p = ct_pvq_u_data[rowoff + k]; p > i; p = ct_pvq_u_data[rowoff + k]) k--;
+      }
+      i -= p;
+      val = (i16)((k0 - k + s) ^ s);
+      *y++ = val;
+      yy = mac16_16(yy, val, val);
+    } else {
+      p = ct_pvq_u_data[ct_pvq_u_row[k] + n];
+      q = ct_pvq_u_data[ct_pvq_u_row[k + 1] + n];
+      if (p <= i && i < q) {
+        i -= p;
+        *y++ = 0;
+      } else {
+        s = -(int)(i >= q);
+        i -= q & (u32)s;
+        k0 = k;
+        do p = ct_pvq_u_data[ct_pvq_u_row[--k] + n]; while (p > i);
+        i -= p;
+        val = (i16)((k0 - k + s) ^ s);
+        *y++ = val;
+        yy = mac16_16(yy, val, val);
+      }
+    }
+    n--;
+  }
+  p = 2 * (u32)k + 1;
+  s = -(int)(i >= p);
+  i -= p & (u32)s;
+  k0 = k;
+  k = (int)((i + 1) >> 1);
+  if (k) i -= 2 * (u32)k - 1;
+  val = (i16)((k0 - k + s) ^ s);
+  *y++ = val;
+  yy = mac16_16(yy, val, val);
+  s = -(int)i;
+  val = (i16)((k + s) ^ s);
+  *y = val;
+  yy = mac16_16(yy, val, val);
+  return yy;
+}
+
+// alg_unquant (vq.c:329-347)
+CB_FN u32 alg_unquant(EntWork& w, RangeDec& rd, i16* X, int N, int K, int spread, int B, i32 gain) {
+  i16* iy = (i16*)w.tmp32;
+  u32 idx = rd_uint(rd, pvq_u(N, K) + pvq_u(N, K + 1));
+  CB_WSYNC();
+  i32 Ryy = pvq_decode(iy, N, K, idx);
+  CB_WSYNC();
+  // normalise_residual (vq.c:117-137)
+  int k = cb_ilog2(Ryy) >> 1;
+  i32 t = vshr32(Ryy, 2 * (k - 7));
+  i16 g = (i16)mult16_16_p15(cb_rsqrt_norm(t), gain);
+  u32 mask = 0;
+  int N0 = N / B;
+  CB_LANE_LOOP(j, N) {
+    i32 v = iy[j];
+    X[j] = ext16(pshr32(mult16_16(g, v), k + 1));
+    if (v != 0) mask |= 1u << (j / N0);       // extract_collapse_mask (vq.c:139-159)
+  }
+  mask = B <= 1 ? 1u : cb_wor(mask);
+  v_exp_rotation_dec(X, N, B, K, spread);
+  return mask;
+}
+
+// ---- theta (bands.c:596-818, decoder side) --------------------------------------------------
+CB_FN int compute_qn(int N, int b, int offset, int pulse_cap, int stereo) {
+  int N2 = 2 * N - 1;
+  if (stereo && N == 2) N2--;
+  int qb = (b + N2 * offset) / N2;            // celt_sudiv
+  qb = cb_imin(b - pulse_cap - (4 << CB_BITRES), qb);
+  qb = cb_imin(8 << CB_BITRES, qb);
+  int qn;
+  if (qb < (1 << CB_BITRES >> 1)) qn = 1;
+  else {
+    qn = ct_exp2_table8[qb & 0x7] >> (14 - (qb >> CB_BITRES));
+    qn = (qn + 1) >> 1 << 1;
+  }
+  return qn;
+}
+CB_FN i16 bitexact_cos(i16 x) {              // bands.c:70-80
+  i32 tmp = (4096 + (i32)x * x) >> 13;
+  i16 x2 = (i16)tmp;
+  x2 = (i16)((32767 - x2) + frac_mul16(x2, (-7651 + frac_mul16(x2, (8277 + frac_mul16(-626, x2))))));
+  return (i16)(1 + x2);
+}
+CB_FN int bitexact_log2tan(int isin, int icos) {   // bands.c:82-93
+  int lc = cb_ilog((u32)icos), ls = cb_ilog((u32)isin);
+  icos <<= 15 - lc;
+  isin <<= 15 - ls;
+  return (ls - lc) * (1 << 11) + frac_mul16(isin, frac_mul16(isin, -2597) + 7932)
+         - frac_mul16(icos, frac_mul16(icos, -2597) + 7932);
+}
+struct Split { int inv, imid, iside, delta, itheta, qalloc; };
+
+CB_FN void dec_theta(BandCtx& cx, RangeDec& rd, Split& sp, int N, int& b, int B, int B0, int LM,
+                     int stereo, int& fill) {
+  int itheta = 0, inv = 0;
+  int pulse_cap = ct_logN400[cx.i] + LM * (1 << CB_BITRES);
+  int offset = (pulse_cap >> 1) - (stereo && N == 2 ? 16 : 4);
+  int qn = compute_qn(N, b, offset, pulse_cap, stereo);
+  if (stereo && cx.i >= cx.intensity) qn = 1;
+  i32 tell = (i32)rd_tell_frac(rd);
+  if (qn != 1) {
+    if (stereo && N > 2) {                    // step pdf
+      int p0 = 3, x0 = qn / 2;
+      u32 ft = (u32)(p0 * (x0 + 1) + x0);
+      int fs = (int)rd_decode(rd, ft);
+      int x;
+      if (fs < (x0 + 1) * p0) x = fs / p0;
+      else x = x0 + 1 + (fs - (x0 + 1) * p0);
+      u32 fl = (u32)(x <= x0 ? p0 * x : (x - 1 - x0) + (x0 + 1) * p0);
+      u32 fh = (u32)(x <= x0 ? p0 * (x + 1) : (x - x0) + (x0 + 1) * p0);
+      rd_update(rd, fl, fh, ft);
+      itheta = x;
+    } else if (B0 > 1 || stereo) {            // uniform pdf
+      itheta = (int)rd_uint(rd, (u32)qn + 1);
+    } else {                                  // triangular pdf
+      int half = qn >> 1;
+      int ft = (half + 1) * (half + 1);
+      int fm = (int)rd_decode(rd, (u32)ft);
+      int fs, fl;
+      if (fm < (half * (half + 1) >> 1)) {
+        itheta = (int)((cb_isqrt32(8 * (u32)fm + 1) - 1) >> 1);
+        fs = itheta + 1;
+        fl = itheta * (itheta + 1) >> 1;
+      } else {
+        itheta = (int)((2 * (u32)(qn + 1) - cb_isqrt32(8 * (u32)(ft - fm - 1) + 1)) >> 1);
+        fs = qn + 1 - itheta;
+        fl = ft - ((qn + 1 - itheta) * (qn + 2 - itheta) >> 1);
+      }
+      rd_update(rd, (u32)fl, (u32)(fl + fs), (u32)ft);
+    }
+    itheta = (int)((u32)(itheta * 16384) / (u32)qn);
+  } else if (stereo) {
+    if (b > 2 << CB_BITRES && cx.remaining_bits > 2 << CB_BITRES) inv = rd_bit_logp(rd, 2);
+    else inv = 0;
+    itheta = 0;
+  }
+  int qalloc = (i32)rd_tell_frac(rd) - tell;
+  b -= qalloc;
+  int imid, iside, delta;
+  if (itheta == 0) {
+    imid = 32767; iside = 0;
+    fill &= (1 << B) - 1;
+    delta = -16384;
+  } else if (itheta == 16384) {
+    imid = 0; iside = 32767;
+    fill &= ((1 << B) - 1) << B;
+    delta = 16384;
+  } else {
+    imid = bitexact_cos((i16)itheta);
+    iside = bitexact_cos((i16)(16384 - itheta));
+    delta = frac_mul16((N - 1) << 7, bitexact_log2tan(iside, imid));
+  }
+  sp.inv = inv; sp.imid = imid; sp.iside = iside; sp.delta = delta; sp.itheta = itheta; sp.qalloc = qalloc;
+}
+
+// ---- leaf of the split recursion (bands.c:966-1038, decoder side) ---------------------------
+CB_FN u32 part_leaf(EntWork& w, BandCtx& cx, RangeDec& rd, i16* X, int N, int b, int B,
+                    const i16* lowband, int LM, i32 gain, int fill) {
+  u32 cm = 0;
+  int q = bits2pulses(cx.i, LM, b);
+  int curr_bits = pulses2bits(cx.i, LM, q);
+  cx.remaining_bits -= curr_bits;
+  while (cx.remaining_bits < 0 && q > 0) {
+    cx.remaining_bits += curr_bits;
+    q--;
+    curr_bits = pulses2bits(cx.i, LM, q);
+    cx.remaining_bits -= curr_bits;
+  }
+  if (q != 0) {
+    cm = alg_unquant(w, rd, X, N, get_pulses(q), cx.spread, B, gain);
+  } else {
+    u32 cm_mask = (u32)((1ull << B) - 1);
+    fill &= (int)cm_mask;
+    CB_WSYNC();
+    if (!fill) {
+      CB_LANE_LOOP(j, N) X[j] = 0;
+      CB_WSYNC();
+    } else {
+      u32 seed0 = cx.seed;
+      if (lowband == nullptr) {               // noise
+        CB_LANE_LOOP(j, N) X[j] = (i16)((i32)cb_lcg_skip(seed0, (u32)j + 1) >> 20);
+        cm = cm_mask;
+      } else {                                // folded spectrum, +-1/256 dither
+        CB_LANE_LOOP(j, N) {
+          u32 sd = cb_lcg_skip(seed0, (u32)j + 1);
+          i32 t = (sd & 0x8000u) ? 4 : -4;
+          X[j] = (i16)(lowband[j] + t);
+        }
+        cm = (u32)fill;
+      }
+      cx.seed = cb_lcg_skip(seed0, (u32)N);
+      v_renormalise(X, N, gain);
+    }
+  }
+  return cm;
+}
+
+// ---- quant_partition (bands.c:864-1040) as an explicit stack ---------------------------------
+CB_FN u32 dec_partition(EntWork& w, BandCtx& cx, RangeDec& rd, i16* X0, int N0, int b0, int B_0,
+                        i16* lowband0, int LM0, i32 gain0, int fill0) {
+  PartFrame* st = w.stack;
+  int sp = 0;
+  st[0].X = X0; st[0].lowband = lowband0; st[0].N = N0; st[0].b = b0; st[0].B = B_0;
+  st[0].LM = LM0; st[0].gain = gain0; st[0].fill = fill0; st[0].stage = 0;
+  u32 ret = 0;
+  while (sp >= 0) {
+    PartFrame& f = st[sp];
+    if (f.stage == 0) {
+      int N = f.N, b = f.b, B = f.B, LM = f.LM, fill = f.fill;
+      const u8* cache = pulse_cache(cx.i, LM);
+      if (LM != -1 && b > cache[cache[0]] + 12 && N > 2) {
+        int B0 = B;
+        N >>= 1;
+        LM -= 1;
+        if (B == 1) fill = (fill & 1) | (fill << 1);
+        B = (B + 1) >> 1;
+        Split s;
+        dec_theta(cx, rd, s, N, b, B, B0, LM, 0, fill);
+        int delta = s.delta, itheta = s.itheta;
+        if (B0 > 1 && (itheta & 0x3fff)) {
+          if (itheta > 8192) delta -= delta >> (4 - LM);
+          else delta = cb_imin(0, delta + (N << CB_BITRES >> (5 - LM)));
+        }
+        int mbits = cb_imax(0, cb_imin(b, (b - delta) / 2));
+        int sbits = b - mbits;
+        cx.remaining_bits -= s.qalloc;
+        f.N = N; f.B = B; f.LM = LM; f.fill = fill; f.B0 = B0;
+        f.mbits = mbits; f.sbits = sbits; f.itheta = itheta;
+        f.rebal0 = cx.remaining_bits;
+        f.gmid = mult16_16_p15(f.gain, s.imid);
+        f.gside = mult16_16_p15(f.gain, s.iside);
+        f.stage = (mbits >= sbits) ? 1 : 3;    // 1: mid first, 3: side first
+        PartFrame& c = st[sp + 1];
+        c.N = N; c.B = B; c.LM = LM; c.stage = 0;
+        if (mbits >= sbits) {
+          c.X = f.X; c.lowband = f.lowband; c.b = mbits; c.gain = (i16)f.gmid; c.fill = fill;
+        } else {
+          c.X = f.X + N; c.lowband = f.lowband ? f.lowband + N : nullptr; c.b = sbits;
+          c.gain = (i16)f.gside; c.fill = fill >> B;
+        }
+        sp++;
+      } else {
+        ret = part_leaf(w, cx, rd, f.X, N, b, B, f.lowband, LM, f.gain, fill);
+        sp--;
+      }
+    } else if (f.stage == 1) {                 // mid done, now side
+      f.cm = (i32)ret;
+      i32 rebalance = f.mbits - (f.rebal0 - cx.remaining_bits);
+      if (rebalance > 3 << CB_BITRES && f.itheta != 0) f.sbits += rebalance - (3 << CB_BITRES);
+      PartFrame& c = st[sp + 1];
+      c.N = f.N; c.B = f.B; c.LM = f.LM; c.stage = 0;
+      c.X = f.X + f.N; c.lowband = f.lowband ? f.lowband + f.N : nullptr; c.b = f.sbits;
+      c.gain = (i16)f.gside; c.fill = f.fill >> f.B;
+      f.stage = 2;
+      sp++;
+    } else if (f.stage == 2) {
+      ret = (u32)f.cm | (ret << (f.B0 >> 1));
+      sp--;
+    } else if (f.stage == 3) {                 // side done, now mid
+      f.cm = (i32)(ret << (f.B0 >> 1));
+      i32 rebalance = f.sbits - (f.rebal0 - cx.remaining_bits);
+      if (rebalance > 3 << CB_BITRES && f.itheta != 16384) f.mbits += rebalance - (3 << CB_BITRES);
+      PartFrame& c = st[sp + 1];
+      c.N = f.N; c.B = f.B; c.LM = f.LM; c.stage = 0;
+      c.X = f.X; c.lowband = f.lowband; c.b = f.mbits; c.gain = (i16)f.gmid; c.fill = f.fill;
+      f.stage = 4;
+      sp++;
+    } else {
+      ret = (u32)f.cm | ret;
+      sp--;
+    }
+  }
+  return ret;
+}
+
+// quant_band_n1 (bands.c:819-858)
+CB_FN u32 dec_band_n1(BandCtx& cx, RangeDec& rd, i16* X, i16* Y, i16* lowband_out) {
+  i16* x = X;
+  int nch = Y ? 2 : 1;
+  for (int c = 0; c < nch; c++) {
+    int sign = 0;
+    if (cx.remaining_bits >= 1 << CB_BITRES) {
+      sign = (int)rd_bits(rd, 1);
+      cx.remaining_bits -= 1 << CB_BITRES;
+    }
+    x[0] = sign ? -CB_NORM_SCALING : CB_NORM_SCALING;
+    x = Y;
+  }
+  if (lowband_out) lowband_out[0] = (i16)(X[0] >> 4);
+  return 1;
+}
+
+// quant_band (bands.c:1044-1172), decoder side
+CB_FN u32 dec_band(EntWork& w, BandCtx& cx, RangeDec& rd, i16* X, int N, int b, int B, i16* lowband,
+                   int LM, i16* lowband_out, i32 gain, i16* lowband_scratch, int fill) {
+  int N0 = N, N_B = N / B, B0 = B;
+  int time_divide = 0, recombine = 0;
+  int longBlocks = B0 == 1;
+  int tf_change = cx.tf_change;
+  i16* tmp = (i16*)w.tmp32;
+  if (N == 1) return dec_band_n1(cx, rd, X, nullptr, lowband_out);
+  if (tf_change > 0) recombine = tf_change;
+  if (lowband_scratch && lowband && (recombine || ((N_B & 1) == 0 && tf_change < 0) || B0 > 1)) {
+    CB_WSYNC();
+    CB_LANE_LOOP(j, N) lowband_scratch[j] = lowband[j];
+    CB_WSYNC();
+    lowband = lowband_scratch;
+  }
+  for (int k = 0; k < recombine; k++) {
+    if (lowband) v_haar1(lowband, N >> k, 1 << k);
+    fill = ct_bit_interleave[fill & 0xF] | ct_bit_interleave[fill >> 4] << 2;
+  }
+  B >>= recombine;
+  N_B <<= recombine;
+  while ((N_B & 1) == 0 && tf_change < 0) {
+    if (lowband) v_haar1(lowband, N_B, B);
+    fill |= fill << B;
+    B <<= 1;
+    N_B >>= 1;
+    time_divide++;
+    tf_change++;
+  }
+  B0 = B;
+  int N_B0 = N_B;
+  if (B0 > 1 && lowband) v_deinterleave(lowband, tmp, N_B >> recombine, B0 << recombine, longBlocks);
+
+  u32 cm = dec_partition(w, cx, rd, X, N, b, B, lowband, LM, gain, fill);
+
+  if (B0 > 1) v_interleave(X, tmp, N_B >> recombine, B0 << recombine, longBlocks);
+  N_B = N_B0;
+  B = B0;
+  for (int k = 0; k < time_divide; k++) {
+    B >>= 1;
+    N_B <<= 1;
+    cm |= cm >> B;
+    v_haar1(X, N_B, B);
+  }
+  for (int k = 0; k < recombine; k++) {
+    cm = ct_bit_deinterleave[cm];
+    v_haar1(X, N0 >> k, 1 << k);
+  }
+  B <<= recombine;
+  if (lowband_out) {
+    i16 n = (i16)cb_sqrt(shl32(N0, 22));
+    CB_WSYNC();
+    CB_LANE_LOOP(j, N0) lowband_out[j] = (i16)mult16_16_q15(n, X[j]);
+    CB_WSYNC();
+  }
+  cm &= (u32)((1 << B) - 1);
+  return cm;
+}
+
+// stereo_merge (bands.c:375-425)
+CB_FN void v_stereo_merge(i16* X, i16* Y, i32 mid, int N) {
+  CB_WSYNC();
+  i32 axp = 0, aside = 0;
+  CB_LANE_LOOP(j, N) {
+    axp = mac16_16(axp, Y[j], X[j]);
+    aside = mac16_16(aside, Y[j], Y[j]);
+  }
+  i32 xp = cb_wsum(axp), side = cb_wsum(aside);
+  xp = mult16_32_q15(mid, xp);
+  i16 mid2 = (i16)(mid >> 1);
+  i32 m2 = mult16_16(mid2, mid2);
+  i32 El = sub32(add32(m2, side), shl32(xp, 1));
+  i32 Er = add32(add32(m2, side), shl32(xp, 1));
+  if (Er < 161061 || El < 161061) {           // QCONST32(6e-4f, 28)
+    CB_LANE_LOOP(j, N) Y[j] = X[j];
+    CB_WSYNC();
+    return;
+  }
+  int kl = cb_ilog2(El) >> 1, kr = cb_ilog2(Er) >> 1;
+  i32 lgain = cb_rsqrt_norm(vshr32(El, (kl - 7) << 1));
+  i32 rgain = cb_rsqrt_norm(vshr32(Er, (kr - 7) << 1));
+  if (kl < 7) kl = 7;
+  if (kr < 7) kr = 7;
+  CB_LANE_LOOP(j, N) {
+    i16 l = (i16)mult16_16_p15(mid, X[j]);
+    i16 r = Y[j];
+    X[j] = ext16(pshr32(mult16_16(lgain, sub16(l, r)), kl + 1));
+    Y[j] = ext16(pshr32(mult16_16(rgain, add16(l, r)), kr + 1));
+  }
+  CB_WSYNC();
+}
+
+// quant_band_stereo (bands.c:1176-1334), decoder side
+CB_FN u32 dec_band_stereo(EntWork& w, BandCtx& cx, RangeDec& rd, i16* X, i16* Y, int N, int b, int B,
+                          i16* lowband, int LM, i16* lowband_out, i16* lowband_scratch, int fill) {
+  if (N == 1) return dec_band_n1(cx, rd, X, Y, lowband_out);
+  int orig_fill = fill;
+  Split s;
+  dec_theta(cx, rd, s, N, b, B, B, LM, 1, fill);
+  i32 mid = s.imid, side = s.iside;
+  int itheta = s.itheta, delta = s.delta;
+  u32 cm;
+  if (N == 2) {
+    int mbits = b, sbits = 0;
+    if (itheta != 0 && itheta != 16384) sbits = 1 << CB_BITRES;
+    mbits -= sbits;
+    int c = itheta > 8192;
+    cx.remaining_bits -= s.qalloc + sbits;
+    i16* x2 = c ? Y : X;
+    i16* y2 = c ? X : Y;
+    int sign = 0;
+    if (sbits) sign = (int)rd_bits(rd, 1);
+    sign = 1 - 2 * sign;
+    cm = dec_band(w, cx, rd, x2, N, mbits, B, lowband, LM, lowband_out, CB_Q15ONE, lowband_scratch, orig_fill);
+    CB_WSYNC();
+    y2[0] = (i16)(-sign * x2[1]);
+    y2[1] = (i16)(sign * x2[0]);
+    i16 X0 = (i16)mult16_16_q15(mid, X[0]);
+    i16 X1 = (i16)mult16_16_q15(mid, X[1]);
+    i16 Y0 = (i16)mult16_16_q15(side, Y[0]);
+    i16 Y1 = (i16)mult16_16_q15(side, Y[1]);
+    CB_WSYNC();
+    X[0] = (i16)sub16(X0, Y0);
+    Y[0] = add16(X0, Y0);
+    X[1] = (i16)sub16(X1, Y1);
+    Y[1] = add16(X1, Y1);
+    CB_WSYNC();
+  } else {
+    int mbits = cb_imax(0, cb_imin(b, (b - delta) / 2));
+    int sbits = b - mbits;
+    cx.remaining_bits -= s.qalloc;
+    i32 rebalance = cx.remaining_bits;
+    if (mbits >= sbits) {
+      cm = dec_band(w, cx, rd, X, N, mbits, B, lowband, LM, lowband_out, CB_Q15ONE, lowband_scratch, fill);
+      rebalance = mbits - (rebalance - cx.remaining_bits);
+      if (rebalance > 3 << CB_BITRES && itheta != 0) sbits += rebalance - (3 << CB_BITRES);
+      cm |= dec_band(w, cx, rd, Y, N, sbits, B, nullptr, LM, nullptr, side, nullptr, fill >> B);
+    } else {
+      cm = dec_band(w, cx, rd, Y, N, sbits, B, nullptr, LM, nullptr, side, nullptr, fill >> B);
+      rebalance = sbits - (rebalance - cx.remaining_bits);
+      if (rebalance > 3 << CB_BITRES && itheta != 16384) mbits += rebalance - (3 << CB_BITRES);
+      cm |= dec_band(w, cx, rd, X, N, mbits, B, lowband, LM, lowband_out, CB_Q15ONE, lowband_scratch, fill);
+    }
+  }
+  if (N != 2) v_stereo_merge(X, Y, mid, N);
+  if (s.inv) {
+    CB_WSYNC();
+    CB_LANE_LOOP(j, N) Y[j] = (i16)(-Y[j]);
+    CB_WSYNC();
+  }
+  return cm;
+}
+
+// quant_all_bands (bands.c:1337-1502), decoder side.  Xc = channel-0 spectrum, channel stride = N.
+CB_FN void dec_all_bands(EntWork& w, RangeDec& rd, int start, int end, int C, int Nfrm, int shortBlocks,
+                         int spread, int dual_stereo, int intensity, i32 total_bits, i32 balance,
+                         int LM, int codedBands, u32& seed) {
+  const int M = 1 << LM;
+  const int B = shortBlocks ? M : 1;
+  i16* X_ = w.X;
+  i16* Y_ = C == 2 ? w.X + Nfrm : nullptr;
+  const int norm_offset = M * ebands(start);
+  i16* norm = w.norm;
+  i16* norm2 = w.norm + CB_NORM_STRIDE;
+  i16* lowband_scratch = X_ + M * ebands(CB_NBANDS - 1);
+  int lowband_offset = 0;
+  int update_lowband = 1;
+  BandCtx cx;
+  cx.intensity = intensity;
+  cx.seed = seed;
+  cx.spread = spread;
+  for (int i = start; i < end; i++) {
+    cx.i = i;
+    int last = (i == end - 1);
+    i16* X = X_ + M * ebands(i);
+    i16* Y = Y_ ? Y_ + M * ebands(i) : nullptr;
+    int N = M * ebands(i + 1) - M * ebands(i);
+    i32 tell = (i32)rd_tell_frac(rd);
+    if (i != start) balance -= tell;
+    i32 remaining_bits = total_bits - tell - 1;
+    cx.remaining_bits = remaining_bits;
+    int b;
+    if (i <= codedBands - 1) {
+      i32 curr_balance = balance / cb_imin(3, codedBands - i);     // celt_sudiv
+      b = cb_imax(0, cb_imin(16383, cb_imin(remaining_bits + 1, w.pulses[i] + curr_balance)));
+    } else {
+      b = 0;
+    }
+    if (M * ebands(i) - N >= M * ebands(start) && (update_lowband || lowband_offset == 0)) lowband_offset = i;
+    int tf_change = w.tf_res[i];
+    cx.tf_change = tf_change;
+    if (last) lowband_scratch = nullptr;
+    int effective_lowband = -1;
+    u32 x_cm, y_cm;
+    if (lowband_offset != 0 && (spread != CB_SPREAD_AGGRESSIVE || B > 1 || tf_change < 0)) {
+      effective_lowband = cb_imax(0, M * ebands(lowband_offset) - norm_offset - N);
+      int fold_start = lowband_offset;
+      while (M * ebands(--fold_start) > effective_lowband + norm_offset) {}
+      int fold_end = lowband_offset - 1;
+      while (M * ebands(++fold_end) < effective_lowband + norm_offset + N) {}
+      x_cm = y_cm = 0;
+      int fold_i = fold_start;
+      do {
+        x_cm |= w.collapse[fold_i * C + 0];
+        y_cm |= w.collapse[fold_i * C + C - 1];
+      } while (++fold_i < fold_end);
+    } else {
+      x_cm = y_cm = (u32)((1 << B) - 1);
+    }
+    if (dual_stereo && i == intensity) {
+      dual_stereo = 0;
+      int cnt = M * ebands(i) - norm_offset;
+      CB_WSYNC();
+      CB_LANE_LOOP(j, cnt) norm[j] = (i16)(((i32)norm[j] + (i32)norm2[j]) >> 1);
+      CB_WSYNC();
+    }
+    i16* lb = effective_lowband != -1 ? norm + effective_lowband : nullptr;
+    i16* lb2 = effective_lowband != -1 ? norm2 + effective_lowband : nullptr;
+    i16* lout = last ? nullptr : norm + M * ebands(i) - norm_offset;
+    i16* lout2 = last ? nullptr : norm2 + M * ebands(i) - norm_offset;
+    if (dual_stereo) {
+      x_cm = dec_band(w, cx, rd, X, N, b / 2, B, lb, LM, lout, CB_Q15ONE, lowband_scratch, (int)x_cm);
+      y_cm = dec_band(w, cx, rd, Y, N, b / 2, B, lb2, LM, lout2, CB_Q15ONE, lowband_scratch, (int)y_cm);
+    } else {
+      if (Y != nullptr)
+        x_cm = dec_band_stereo(w, cx, rd, X, Y, N, b, B, lb, LM, lout, lowband_scratch, (int)(x_cm | y_cm));
+      else
+        x_cm = dec_band(w, cx, rd, X, N, b, B, lb, LM, lout, CB_Q15ONE, lowband_scratch, (int)(x_cm | y_cm));
+      y_cm = x_cm;
+    }
+    w.collapse[i * C + 0] = (u8)x_cm;
+    w.collapse[i * C + C - 1] = (u8)y_cm;
+    balance += w.pulses[i] + tell;
+    update_lowband = b > (N << CB_BITRES);
+  }
+  seed = cx.seed;
+}
+
+// anti_collapse (bands.c:241-335)
+CB_FN void v_anti_collapse(EntWork& w, int LM, int C, int Nfrm, int start, int end, const i16* logE,
+                           const i16* prev1logE, const i16* prev2logE, u32 seed) {
+  for (int i = start; i < end; i++) {
+    int N0 = ebands(i + 1) - ebands(i);
+    int depth = (int)((u32)(1 + w.pulses[i]) / (u32)N0) >> LM;
+    i32 thresh32 = cb_exp2(-(i32)shl16(depth, 10 - CB_BITRES)) >> 1;
+    i16 thresh = (i16)mult16_32_q15(16384, min32(32767, thresh32));
+    i32 t = N0 << LM;
+    int shift = cb_ilog2(t) >> 1;
+    t = shl32(t, (7 - shift) << 1);
+    i16 sqrt_1 = cb_rsqrt_norm(t);
+    for (int c = 0; c < C; c++) {
+      i32 prev1 = prev1logE[c * CB_NBANDS + i];
+      i32 prev2 = prev2logE[c * CB_NBANDS + i];
+      if (C == 1) {
+        prev1 = cb_imax(prev1, prev1logE[CB_NBANDS + i]);
+        prev2 = cb_imax(prev2, prev2logE[CB_NBANDS + i]);
+      }
+      i32 Ediff = (i32)logE[c * CB_NBANDS + i] - cb_imin(prev1, prev2);
+      Ediff = max32(0, Ediff);
+      i16 r;
+      if (Ediff < 16384) {
+        i32 r32 = cb_exp2(-(i32)(i16)Ediff) >> 1;
+        r = (i16)(2 * cb_imin(16383, r32));
+      } else {
+        r = 0;
+      }
+      if (LM == 3) r = (i16)mult16_16_q14(23170, min32(23169, r));
+      r = (i16)(cb_imin(thresh, r) >> 1);
+      r = (i16)(mult16_16_q15(sqrt_1, r) >> shift);
+      i16* X = w.X + c * Nfrm + (ebands(i) << LM);
+      int renormalize = 0;
+      for (int k = 0; k < (1 << LM); k++) {
+        if (!(w.collapse[i * C + c] & (1 << k))) {
+          u32 seed0 = seed;
+          CB_WSYNC();
+          CB_LANE_LOOP(j, N0) {
+            u32 sd = cb_lcg_skip(seed0, (u32)j + 1);
+            X[(j << LM) + k] = (sd & 0x8000u) ? r : (i16)(-r);
+          }
+          seed = cb_lcg_skip(seed0, (u32)N0);
+          renormalize = 1;
+        }
+      }
+      if (renormalize) v_renormalise(X, N0 << LM, CB_Q15ONE);
+    }
+  }
+}
+
+// ---- energy decoding (quant_bands.c:435-549) -------------------------------------------------
+CB_FN void dec_coarse_energy(EntWork& w, RangeDec& rd, int start, int end, int intra, int C, int LM) {
+  const u8* prob = ct_e_prob_model + (LM * 2 + intra) * 42;
+  i32 prev[2] = {0, 0};
+  i32 coef, beta;
+  if (intra) { coef = 0; beta = 4915; }
+  else { beta = ct_beta_coef[LM]; coef = ct_pred_coef[LM]; }
+  i32 budget = (i32)rd.storage * 8;
+  for (int i = start; i < end; i++) {
+    for (int c = 0; c < C; c++) {
+      int qi;
+      i32 tell = rd_tell(rd);
+      if (budget - tell >= 15) {
+        int pi = 2 * cb_imin(i, 20);
+        qi = rd_laplace(rd, (u32)prob[pi] << 7, (int)prob[pi + 1] << 6);
+      } else if (budget - tell >= 2) {
+        qi = rd_icdf(rd, ct_small_energy_icdf, 2);
+        qi = (qi >> 1) ^ -(qi & 1);
+      } else if (budget - tell >= 1) {
+        qi = -rd_bit_logp(rd, 1);
+      } else {
+        qi = -1;
+      }
+      i32 q = shl32(qi, CB_DB_SHIFT);
+      i16& e = w.bandE[i + c * CB_NBANDS];
+      e = (i16)cb_imax(-9216, e);              // -QCONST16(9.f, DB_SHIFT)
+      i32 tmp = add32(add32(pshr32(mult16_16(coef, e), 8), prev[c]), shl32(q, 7));
+      tmp = max32(-3670016, tmp);              // -QCONST32(28.f, DB_SHIFT+7)
+      e = (i16)pshr32(tmp, 7);
+      prev[c] = sub32(add32(prev[c], shl32(q, 7)), mult16_16(beta, pshr32(q, 8)));
+    }
+  }
+}
+CB_FN void dec_fine_energy(EntWork& w, RangeDec& rd, int start, int end, int C) {
+  for (int i = start; i < end; i++) {
+    int fq = w.fine_quant[i];
+    if (fq <= 0) continue;
+    for (int c = 0; c < C; c++) {
+      i32 q2 = (i32)rd_bits(rd, (u32)fq);
+      i32 offset = sub16((add32(shl32(q2, CB_DB_SHIFT), 512)) >> fq, 512);
+      w.bandE[i + c * CB_NBANDS] = (i16)(w.bandE[i + c * CB_NBANDS] + (i16)offset);
+    }
+  }
+}
+CB_FN void dec_energy_finalise(EntWork& w, RangeDec& rd, int start, int end, int bits_left, int C) {
+  for (int prio = 0; prio < 2; prio++) {
+    for (int i = start; i < end && bits_left >= C; i++) {
+      if (w.fine_quant[i] >= CB_MAX_FINE_BITS || w.fine_prio[i] != prio) continue;
+      for (int c = 0; c < C; c++) {
+        i32 q2 = (i32)rd_bits(rd, 1);
+        i32 offset = ((i32)shl16(q2, CB_DB_SHIFT) - 512) >> (w.fine_quant[i] + 1);
+        w.bandE[i + c * CB_NBANDS] = (i16)(w.bandE[i + c * CB_NBANDS] + (i16)offset);
+        bits_left--;
+      }
+    }
+  }
+}
+
+// tf_decode (celt_decoder.c:352-389)
+CB_FN void dec_tf(EntWork& w, RangeDec& rd, int start, int end, int isTransient, int LM) {
+  u32 budget = rd.storage * 8;
+  u32 tell = (u32)rd_tell(rd);
+  int logp = isTransient ? 2 : 4;
+  int tf_select_rsv = LM > 0 && tell + logp + 1 <= budget;
+  budget -= tf_select_rsv;
+  int tf_changed = 0, curr = 0;
+  for (int i = start; i < end; i++) {
+    if (tell + logp <= budget) {
+      curr ^= rd_bit_logp(rd, (u32)logp);
+      tell = (u32)rd_tell(rd);
+      tf_changed |= curr;
+    }
+    w.tf_res[i] = (i8)curr;
+    logp = isTransient ? 4 : 5;
+  }
+  int tf_select = 0;
+  if (tf_select_rsv && ct_tf_select[LM][4 * isTransient + 0 + tf_changed] != ct_tf_select[LM][4 * isTransient + 2 + tf_changed])
+    tf_select = rd_bit_logp(rd, 1);
+  for (int i = start; i < end; i++)
+    w.tf_res[i] = ct_tf_select[LM][4 * isTransient + 2 * tf_select + w.tf_res[i]];
+}
+
+// ---- bit allocation (rate.c:248-638), decoder side -------------------------------------------
+CB_FN int dec_allocation(EntWork& w, RangeDec& rd, int start, int end, int alloc_trim, int& intensity,
+                         int& dual_stereo, i32 total, i32& balance_out, int C, int LM) {
+  i32* bits1 = w.tmp32;
+  i32* bits2 = w.tmp32 + CB_NBANDS;
+  i32* thresh = w.tmp32 + 2 * CB_NBANDS;
+  i32* trim_offset = w.tmp32 + 3 * CB_NBANDS;
+  i32* bits = w.pulses;
+  total = max32(total, 0);
+  int skip_start = start;
+  int skip_rsv = total >= 1 << CB_BITRES ? 1 << CB_BITRES : 0;
+  total -= skip_rsv;
+  int intensity_rsv = 0, dual_stereo_rsv = 0;
+  if (C == 2) {
+    intensity_rsv = ct_log2_frac_table[end - start];
+    if (intensity_rsv > total) intensity_rsv = 0;
+    else {
+      total -= intensity_rsv;
+      dual_stereo_rsv = total >= 1 << CB_BITRES ? 1 << CB_BITRES : 0;
+      total -= dual_stereo_rsv;
+    }
+  }
+  for (int j = start; j < end; j++) {
+    int wdt = ebands(j + 1) - ebands(j);
+    thresh[j] = cb_imax(C << CB_BITRES, (3 * wdt << LM << CB_BITRES) >> 4);
+    trim_offset[j] = C * wdt * (alloc_trim - 5 - LM) * (end - j - 1) * (1 << (LM + CB_BITRES)) >> 6;
+    if (wdt << LM == 1) trim_offset[j] -= C << CB_BITRES;
+  }
+  int lo = 1, hi = 11 - 1;                    // nbAllocVectors = 11
+  do {
+    int done = 0, psum = 0;
+    int mid = (lo + hi) >> 1;
+    for (int j = end; j-- > start;) {
+      int wdt = ebands(j + 1) - ebands(j);
+      int bitsj = C * wdt * ct_band_alloc[mid * CB_NBANDS + j] << LM >> 2;
+      if (bitsj > 0) bitsj = cb_imax(0, bitsj + trim_offset[j]);
+      bitsj += w.offsets[j];
+      if (bitsj >= thresh[j] || done) {
+        done = 1;
+        psum += cb_imin(bitsj, w.cap[j]);
+      } else if (bitsj >= C << CB_BITRES) {
+        psum += C << CB_BITRES;
+      }
+    }
+    if (psum > total) hi = mid - 1; else lo = mid + 1;
+  } while (lo <= hi);
+  hi = lo--;
+  for (int j = start; j < end; j++) {
+    int wdt = ebands(j + 1) - ebands(j);
+    int bits1j = C * wdt * ct_band_alloc[lo * CB_NBANDS + j] << LM >> 2;
+    int bits2j = hi >= 11 ? w.cap[j] : C * wdt * ct_band_alloc[hi * CB_NBANDS + j] << LM >> 2;
+    if (bits1j > 0) bits1j = cb_imax(0, bits1j + trim_offset[j]);
+    if (bits2j > 0) bits2j = cb_imax(0, bits2j + trim_offset[j]);
+    if (lo > 0) bits1j += w.offsets[j];
+    bits2j += w.offsets[j];
+    if (w.offsets[j] > 0) skip_start = j;
+    bits2j = cb_imax(0, bits2j - bits1j);
+    bits1[j] = bits1j;
+    bits2[j] = bits2j;
+  }
+  // interp_bits2pulses (rate.c:248-525)
+  const int alloc_floor = C << CB_BITRES;
+  const int stereo = C > 1;
+  const int logM = LM << CB_BITRES;
+  i32 psum;
+  lo = 0;
+  hi = 1 << CB_ALLOC_STEPS;
+  for (int it = 0; it < CB_ALLOC_STEPS; it++) {
+    int mid = (lo + hi) >> 1;
+    psum = 0;
+    int done = 0;
+    for (int j = end; j-- > start;) {
+      int tmp = bits1[j] + (int)((i32)mid * bits2[j] >> CB_ALLOC_STEPS);
+      if (tmp >= thresh[j] || done) {
+        done = 1;
+        psum += cb_imin(tmp, w.cap[j]);
+      } else if (tmp >= alloc_floor) {
+        psum += alloc_floor;
+      }
+    }
+    if (psum > total) hi = mid; else lo = mid;
+  }
+  psum = 0;
+  {
+    int done = 0;
+    for (int j = end; j-- > start;) {
+      int tmp = bits1[j] + (lo * bits2[j] >> CB_ALLOC_STEPS);
+      if (tmp < thresh[j] && !done) {
+        if (tmp >= alloc_floor) tmp = alloc_floor; else tmp = 0;
+      } else {
+        done = 1;
+      }
+      tmp = cb_imin(tmp, w.cap[j]);
+      bits[j] = tmp;
+      psum += tmp;
+    }
+  }
+  int codedBands;
+  for (codedBands = end;; codedBands--) {
+    int j = codedBands - 1;
+    if (j <= skip_start) {
+      total += skip_rsv;
+      break;
+    }
+    i32 left = total - psum;
+    int span = ebands(codedBands) - ebands(start);
+    i32 percoeff = (i32)((u32)left / (u32)span);
+    left -= span * percoeff;
+    int rem = cb_imax(left - (ebands(j) - ebands(start)), 0);
+    int band_width = ebands(codedBands) - ebands(j);
+    int band_bits = (int)(bits[j] + percoeff * band_width + rem);
+    if (band_bits >= cb_imax(thresh[j], alloc_floor + (1 << CB_BITRES))) {
+      if (rd_bit_logp(rd, 1)) break;
+      psum += 1 << CB_BITRES;
+      band_bits -= 1 << CB_BITRES;
+    }
+    psum -= bits[j] + intensity_rsv;
+    if (intensity_rsv > 0) intensity_rsv = ct_log2_frac_table[j - start];
+    psum += intensity_rsv;
+    if (band_bits >= alloc_floor) {
+      psum += alloc_floor;
+      bits[j] = alloc_floor;
+    } else {
+      bits[j] = 0;
+    }
+  }
+  if (intensity_rsv > 0) intensity = start + (int)rd_uint(rd, (u32)(codedBands + 1 - start));
+  else intensity = 0;
+  if (intensity <= start) {
+    total += dual_stereo_rsv;
+    dual_stereo_rsv = 0;
+  }
+  if (dual_stereo_rsv > 0) dual_stereo = rd_bit_logp(rd, 1);
+  else dual_stereo = 0;
+
+  i32 left = total - psum;
+  {
+    int span = ebands(codedBands) - ebands(start);
+    i32 percoeff = (i32)((u32)left / (u32)span);
+    left -= span * percoeff;
+    for (int j = start; j < codedBands; j++) bits[j] += (int)percoeff * (ebands(j + 1) - ebands(j));
+    for (int j = start; j < codedBands; j++) {
+      int tmp = (int)min32(left, ebands(j + 1) - ebands(j));
+      bits[j] += tmp;
+      left -= tmp;
+    }
+  }
+  i32 balance = 0;
+  int j;
+  for (j = start; j < codedBands; j++) {
+    int N0 = ebands(j + 1) - ebands(j);
+    int N = N0 << LM;
+    i32 bit = bits[j] + balance;
+    i32 excess;
+    int eb;
+    if (N > 1) {
+      excess = max32(bit - w.cap[j], 0);
+      bits[j] = bit - excess;
+      int den = C * N + ((C == 2 && N > 2 && !dual_stereo && j < intensity) ? 1 : 0);
+      int NClogN = den * (ct_logN400[j] + logM);
+      int offset = (NClogN >> 1) - den * CB_FINE_OFFSET;
+      if (N == 2) offset += den << CB_BITRES >> 2;
+      if (bits[j] + offset < den * 2 << CB_BITRES) offset += NClogN >> 2;
+      else if (bits[j] + offset < den * 3 << CB_BITRES) offset += NClogN >> 3;
+      eb = cb_imax(0, (bits[j] + offset + (den << (CB_BITRES - 1))));
+      eb = (int)((u32)eb / (u32)den) >> CB_BITRES;
+      if (C * eb > (bits[j] >> CB_BITRES)) eb = bits[j] >> stereo >> CB_BITRES;
+      eb = cb_imin(eb, CB_MAX_FINE_BITS);
+      w.fine_prio[j] = (i8)(eb * (den << CB_BITRES) >= bits[j] + offset);
+      bits[j] -= C * eb << CB_BITRES;
+    } else {
+      excess = max32(0, bit - (C << CB_BITRES));
+      bits[j] = bit - excess;
+      eb = 0;
+      w.fine_prio[j] = 1;
+    }
+    if (excess > 0) {
+      int extra_fine = cb_imin(excess >> (stereo + CB_BITRES), CB_MAX_FINE_BITS - eb);
+      eb += extra_fine;
+      int extra_bits = extra_fine * C << CB_BITRES;
+      w.fine_prio[j] = (i8)(extra_bits >= excess - balance);
+      excess -= extra_bits;
+    }
+    balance = excess;
+    w.fine_quant[j] = (i8)eb;
+  }
+  balance_out = balance;
+  for (; j < end; j++) {
+    int eb = bits[j] >> stereo >> CB_BITRES;
+    w.fine_quant[j] = (i8)eb;
+    bits[j] = 0;
+    w.fine_prio[j] = (i8)(eb < 1);
+  }
+  return codedBands;
+}
+
+// ---- one CELT frame, entropy half (celt_decoder.c:713-1062 minus synthesis/deemphasis) -------
+// `pkt`/`len`: CELT payload staged in shared memory.  Returns 0 or a negative OPUS_* code.
+struct EntFrameCfg { int LM, C, start, end, accum; };
+
+CB_FN int celt_entropy_decode(EntWork& w, CeltDecState* stg, FrameSide* side, const u8* pkt, int len,
+                              const EntFrameCfg& cfg, u32* final_range) {
+  const int LM = cfg.LM, C = cfg.C, start = cfg.start, end = cfg.end;
+  const int M = 1 << LM, N = M * 120;
+  const int CC = stg->channels;
+  const int lane = CB_LANE();
+  (void)lane;
+  // load the small state
+  CB_LANE_LOOP(j, 2 * CB_NBANDS) w.bandE[j] = stg->oldBandE[j];
+  CB_WSYNC();
+  int effEnd = end > CB_NBANDS ? CB_NBANDS : end;
+
+  RangeDec rd;
+  rd_init(rd, pkt, (u32)len);
+
+  if (C == 1) {
+    CB_WSYNC();
+    CB_LANE_LOOP(i, CB_NBANDS) w.bandE[i] = (i16)cb_imax(w.bandE[i], w.bandE[CB_NBANDS + i]);
+    CB_WSYNC();
+  }
+  i32 total_bits = len * 8;
+  i32 tell = rd_tell(rd);
+  int silence;
+  if (tell >= total_bits) silence = 1;
+  else if (tell == 1) silence = rd_bit_logp(rd, 15);
+  else silence = 0;
+  if (silence) {
+    tell = len * 8;
+    rd.nbits_total += tell - rd_tell(rd);
+  }
+  i32 postfilter_gain = 0;
+  int postfilter_pitch = 0, postfilter_tapset = 0;
+  if (start == 0 && tell + 16 <= total_bits) {
+    if (rd_bit_logp(rd, 1)) {
+      int octave = (int)rd_uint(rd, 6);
+      postfilter_pitch = (16 << octave) + (int)rd_bits(rd, 4 + (u32)octave) - 1;
+      int qg = (int)rd_bits(rd, 3);
+      if (rd_tell(rd) + 2 <= total_bits) postfilter_tapset = rd_icdf(rd, ct_tapset_icdf, 2);
+      postfilter_gain = 3072 * (qg + 1);       // QCONST16(.09375f,15)
+    }
+    tell = rd_tell(rd);
+  }
+  int isTransient = 0;
+  if (LM > 0 && tell + 3 <= total_bits) {
+    isTransient = rd_bit_logp(rd, 3);
+    tell = rd_tell(rd);
+  }
+  int shortBlocks = isTransient ? M : 0;
+  int intra_ener = tell + 3 <= total_bits ? rd_bit_logp(rd, 3) : 0;
+  dec_coarse_energy(w, rd, start, end, intra_ener, C, LM);
+  dec_tf(w, rd, start, end, isTransient, LM);
+  tell = rd_tell(rd);
+  int spread_decision = CB_SPREAD_NORMAL;
+  if (tell + 4 <= total_bits) spread_decision = rd_icdf(rd, ct_spread_icdf, 5);
+  // init_caps (celt.c:255-264)
+  for (int i = 0; i < CB_NBANDS; i++) {
+    int Nb = (ebands(i + 1) - ebands(i)) << LM;
+    w.cap[i] = (i16)((ct_cache_caps50[CB_NBANDS * (2 * LM + C - 1) + i] + 64) * C * Nb >> 2);
+  }
+  int dynalloc_logp = 6;
+  total_bits <<= CB_BITRES;
+  tell = (i32)rd_tell_frac(rd);
+  for (int i = start; i < end; i++) {
+    int width = C * (ebands(i + 1) - ebands(i)) << LM;
+    int quanta = cb_imin(width << CB_BITRES, cb_imax(6 << CB_BITRES, width));
+    int loop_logp = dynalloc_logp;
+    int boost = 0;
+    while (tell + (loop_logp << CB_BITRES) < total_bits && boost < w.cap[i]) {
+      int flag = rd_bit_logp(rd, (u32)loop_logp);
+      tell = (i32)rd_tell_frac(rd);
+      if (!flag) break;
+      boost += quanta;
+      total_bits -= quanta;
+      loop_logp = 1;
+    }
+    w.offsets[i] = (i16)boost;
+    if (boost > 0) dynalloc_logp = cb_imax(2, dynalloc_logp - 1);
+  }
+  int alloc_trim = tell + (6 << CB_BITRES) <= total_bits ? rd_icdf(rd, ct_trim_icdf, 7) : 5;
+  i32 bits = (((i32)len * 8) << CB_BITRES) - (i32)rd_tell_frac(rd) - 1;
+  int anti_collapse_rsv = isTransient && LM >= 2 && bits >= ((LM + 2) << CB_BITRES) ? (1 << CB_BITRES) : 0;
+  bits -= anti_collapse_rsv;
+  int intensity = 0, dual_stereo = 0;
+  i32 balance = 0;
+  int codedBands = dec_allocation(w, rd, start, end, alloc_trim, intensity, dual_stereo, bits, balance, C, LM);
+  dec_fine_energy(w, rd, start, end, C);
+
+  u32 seed = stg->rng;
+  dec_all_bands(w, rd, start, end, C, N, shortBlocks, spread_decision, dual_stereo, intensity,
+                len * (8 << CB_BITRES) - anti_collapse_rsv, balance, LM, codedBands, seed);
+  int anti_collapse_on = 0;
+  if (anti_collapse_rsv > 0) anti_collapse_on = (int)rd_bits(rd, 1);
+  dec_energy_finalise(w, rd, start, end, len * 8 - rd_tell(rd), C);
+  if (anti_collapse_on)
+    v_anti_collapse(w, LM, C, N, start, end, w.bandE, stg->oldLogE, stg->oldLogE2, seed);
+  CB_WSYNC();
+  if (silence) {
+    CB_LANE_LOOP(i, C * CB_NBANDS) w.bandE[i] = -28672;     // -QCONST16(28.f, DB_SHIFT)
+    CB_WSYNC();
+  }
+
+  // ---- hand-off to the synthesis kernel ----
+  int pf_period = cb_imax(stg->pf_period, 15);               // COMBFILTER_MINPERIOD
+  int pf_period_old = cb_imax(stg->pf_period_old, 15);
+  CB_LANE_LOOP(j, 2 * CB_NBANDS) side->bandE[j] = w.bandE[j];
+  {
+    // X as 32-bit words, coalesced
+    const u32* src = (const u32*)w.X;
+    u32* dst = (u32*)side->X;
+    CB_LANE_LOOP(j, C * N / 2) dst[j] = src[j];
+  }
+  side->accum = cfg.accum;
+  side->kind = 1; side->LM = LM; side->C = C; side->transient = isTransient; side->silence = silence;
+  side->start = start; side->effEnd = effEnd;
+  side->T0 = pf_period_old; side->T1 = pf_period; side->T2 = postfilter_pitch;
+  side->g0 = stg->pf_gain_old; side->g1 = stg->pf_gain; side->g2 = postfilter_gain;
+  side->tap0 = stg->pf_tapset_old; side->tap1 = stg->pf_tapset; side->tap2 = postfilter_tapset;
+
+  // ---- small-state update (celt_decoder.c:1014-1062) ----
+  int npo = pf_period, ngo = stg->pf_gain, nto = stg->pf_tapset;          // *_old <- current
+  int np = postfilter_pitch, ng = postfilter_gain, nt = postfilter_tapset;
+  if (LM != 0) { npo = np; ngo = ng; nto = nt; }
+  CB_WSYNC();
+  if (C == 1) {
+    CB_LANE_LOOP(i, CB_NBANDS) w.bandE[CB_NBANDS + i] = w.bandE[i];
+    CB_WSYNC();
+  }
+  const int loss_count = stg->loss_count;
+  CB_LANE_LOOP(i, 2 * CB_NBANDS) {
+    i16 e = w.bandE[i];
+    i16 l1 = stg->oldLogE[i], l2 = stg->oldLogE2[i], bg = stg->backgroundLogE[i];
+    if (!isTransient) {
+      l2 = l1;
+      l1 = e;
+      i32 inc = loss_count < 10 ? M * 1 : 1024;   // M*QCONST16(0.001f,DB_SHIFT) : QCONST16(1.f,DB_SHIFT)
+      bg = (i16)cb_imin(bg + inc, e);
+    } else {
+      l1 = (i16)cb_imin(l1, e);
+    }
+    int band = i % CB_NBANDS;
+    if (band < start || band >= end) {
+      e = 0;
+      l1 = l2 = -28672;
+    }
+    stg->oldBandE[i] = e;
+    stg->oldLogE[i] = l1;
+    stg->oldLogE2[i] = l2;
+    stg->backgroundLogE[i] = bg;
+  }
+  CB_WSYNC();
+  stg->pf_period = np; stg->pf_gain = ng; stg->pf_tapset = nt;
+  stg->pf_period_old = npo; stg->pf_gain_old = ngo; stg->pf_tapset_old = nto;
+  stg->rng = rd.rng;
+  stg->loss_count = 0;
+  if (rd.error) stg->error = 1;
+  *final_range = rd.rng;
+  (void)CC;
+  if (rd_tell(rd) > 8 * len) return -3;        // OPUS_INTERNAL_ERROR
+  return 0;
+}

@@ -1,0 +1,74 @@
+// cb_state.h -- per-stream decoder state as laid out in HBM, and the per-frame hand-off record
+// between the entropy kernel (A) and the synthesis kernel (B).
+//
+// Counterpart of struct OpusCustomDecoder (opus-fix/celt/celt_decoder.c:67-100), re-laid-out:
+//   * the "small" state (coder seed, post-filter parameters, band energies) is owned by kernel A;
+//   * the "signal" state (output history, overlap tail, de-emphasis memory) is owned by kernel B.
+// The reference keeps a linear 2048+120 sample buffer per channel and memmoves it by N every
+// frame (celt_decoder.c:963).  Here the history is a 2048-sample ring (hist_pos = index of the
+// oldest sample) plus a 60-sample overlap tail, so a frame costs N stores instead of ~2048.
+#pragma once
+#include "cb_common.h"
+#include <stddef.h>
+
+#define CB_NBANDS 21
+#define CB_MAXN 960          // samples per channel per frame at LM=3
+#define CB_OVERLAP 120
+#define CB_HIST 2048         // DECODE_BUFFER_SIZE
+#define CB_LPC_ORDER 24
+#define CB_NORM_STRIDE 624   // 8*eBands[20]
+
+struct alignas(16) CeltDecState {
+  // ---- small state (kernel A) ----
+  u32 rng;                   // celt_decoder.c:81
+  i32 error;
+  i32 last_pitch_index;
+  i32 loss_count;
+  i32 pf_period, pf_period_old;
+  i32 pf_gain, pf_gain_old;          // opus_val16 values
+  i32 pf_tapset, pf_tapset_old;
+  i32 channels;              // CC (output channels), fixed at create
+  i32 downsample;            // 48000/Fs
+  i16 oldBandE[2 * CB_NBANDS];
+  i16 oldLogE[2 * CB_NBANDS];
+  i16 oldLogE2[2 * CB_NBANDS];
+  i16 backgroundLogE[2 * CB_NBANDS];
+  i16 lpc[2 * CB_LPC_ORDER];
+  // ---- signal state (kernel B) ----
+  i32 preemph_mem[2];
+  i32 hist_pos[2];           // ring index of the oldest sample, per channel (each channel warp owns one)
+  i32 tail[2][CB_OVERLAP / 2];        // un-windowed IMDCT overlap, decode_mem[2048..2048+60)
+  i32 hist[2][CB_HIST];               // decode_mem[0..2048), ring
+};
+
+// What kernel A tells kernel B about one frame (lives in the scratch arena, one per stream).
+struct alignas(16) FrameSide {
+  i32 kind;                  // 0 = nothing to synthesise, 1 = normal frame
+  i32 LM, C, transient, silence, start, effEnd;
+  i32 T0, T1, T2;            // post-filter periods: old, current, new (celt_decoder.c:1003-1011)
+  i32 g0, g1, g2;
+  i32 tap0, tap1, tap2;
+  i32 accum;                 // hybrid: add into pcm (celt_decoder.c:236-245)
+  i32 pad[3];
+  i16 bandE[2 * CB_NBANDS];  // log energies used by denormalise_bands
+  i16 pad2[6];
+  i16 X[2 * CB_MAXN];        // normalised spectrum, channel-major
+};
+
+// Frame descriptor built by the host (or implied by a raw packet).
+// celt_decoder_init + OPUS_RESET_STATE (celt_decoder.c:134-172,1196-1204): all-zero except the
+// two log-energy memories, which start at -28 dB.  Host-side helper (the blob is then copied to HBM).
+static inline void celt_state_reset(CeltDecState* s, int channels, int downsample) {
+  unsigned char* p = (unsigned char*)s;
+  for (size_t i = 0; i < sizeof(CeltDecState); i++) p[i] = 0;
+  s->channels = channels;
+  s->downsample = downsample;
+  for (int i = 0; i < 2 * CB_NBANDS; i++) s->oldLogE[i] = s->oldLogE2[i] = -28672;
+}
+
+struct FrameDesc {
+  i32 offset;                // byte offset of the CELT payload in the packet arena
+  i32 len;                   // payload bytes (after TOC / framing)
+  i32 toc;                   // Opus TOC byte (frame size, bandwidth, stereo flag), -1 = skip stream
+  i32 pcm_offset;            // sample-frame offset inside this stream's PCM row
+};
