@@ -1,0 +1,239 @@
+"""concentus_b200 -- Python face of libopus_b200.so (the B200-native batched Opus engine).
+
+The classes mirror the reference's native plugin wrappers so that tests read like the
+reference's own (CSharp/Concentus/Native/NativeOpusDecoder.cs:74-214):
+
+    OpusDecoder(Fs, channels).decode(packet_bytes_or_None, frame_size, fec=False) -> int16 ndarray
+    OpusDecoder.final_range / bandwidth / last_packet_duration / reset_state()
+    OpusBatchDecoder(Fs, channels, n).decode(...)      # n independent streams per call
+
+Everything is computed by the CUDA library; there is no Python or CPU fallback.  Importing this
+package does not need a GPU, creating a decoder does.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libopus_b200.so")
+
+OPUS_OK = 0
+OPUS_BAD_ARG = -1
+OPUS_BUFFER_TOO_SMALL = -2
+OPUS_INTERNAL_ERROR = -3
+OPUS_INVALID_PACKET = -4
+OPUS_UNIMPLEMENTED = -5
+OPUS_INVALID_STATE = -6
+OPUS_ALLOC_FAIL = -7
+
+OPUS_GET_BANDWIDTH_REQUEST = 4009
+OPUS_RESET_STATE = 4028
+OPUS_GET_SAMPLE_RATE_REQUEST = 4029
+OPUS_GET_FINAL_RANGE_REQUEST = 4031
+OPUS_GET_PITCH_REQUEST = 4033
+OPUS_SET_GAIN_REQUEST = 4034
+OPUS_GET_LAST_PACKET_DURATION_REQUEST = 4039
+OPUS_GET_GAIN_REQUEST = 4045
+
+# every symbol include/opus_b200.h declares
+EXPORTS = [
+    "opus_get_version_string", "opus_strerror", "opus_decoder_get_size", "opus_decoder_create",
+    "opus_decode", "opus_decode_float", "opus_decoder_ctl", "opus_decoder_destroy",
+    "opus_packet_get_bandwidth", "opus_packet_get_nb_channels", "opus_packet_get_nb_frames",
+    "opus_packet_get_samples_per_frame", "opus_packet_get_nb_samples", "opus_decoder_get_nb_samples",
+    "opus_packet_parse", "opus_decode_batch", "opus_decode_batch_flat", "opus_decoder_group_create",
+    "opus_decoder_group_destroy", "opus_decode_group_flat", "opus_decode_group_device",
+    "opus_decoder_get_final_range_batch", "opus_b200_synchronize", "opus_b200_launch_count",
+    "opus_b200_profile_begin", "opus_b200_profile_end",
+]
+
+_lib = None
+
+
+class OpusError(RuntimeError):
+    def __init__(self, code, what=""):
+        self.code = code
+        msg = load().opus_strerror(code).decode() if _lib is not None else str(code)
+        super().__init__("%s: %s (%d)" % (what, msg, code))
+
+
+def load():
+    """dlopen libopus_b200.so and declare prototypes.  Raises if the library was not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            "libopus_b200.so is missing (%s). Build it with `python -m concentus_b200.build`; "
+            "there is no CPU fallback." % LIB_PATH)
+    lib = ctypes.CDLL(LIB_PATH)
+    c_int_p = ctypes.POINTER(ctypes.c_int)
+    vp = ctypes.c_void_p
+    lib.opus_get_version_string.restype = ctypes.c_char_p
+    lib.opus_strerror.restype = ctypes.c_char_p
+    lib.opus_strerror.argtypes = [ctypes.c_int]
+    lib.opus_decoder_create.restype = vp
+    lib.opus_decoder_create.argtypes = [ctypes.c_int32, ctypes.c_int, c_int_p]
+    lib.opus_decoder_destroy.argtypes = [vp]
+    lib.opus_decoder_destroy.restype = None
+    lib.opus_decode.argtypes = [vp, vp, ctypes.c_int32, vp, ctypes.c_int, ctypes.c_int]
+    lib.opus_decode_float.argtypes = [vp, vp, ctypes.c_int32, vp, ctypes.c_int, ctypes.c_int]
+    lib.opus_decode_batch.argtypes = [vp, vp, vp, vp, ctypes.c_int, vp, ctypes.c_int, vp]
+    lib.opus_decode_batch_flat.argtypes = [vp, ctypes.c_int, vp, ctypes.c_int32, vp, vp, vp, ctypes.c_int32,
+                                           ctypes.c_int, vp, vp]
+    lib.opus_decoder_group_create.restype = vp
+    lib.opus_decoder_group_create.argtypes = [vp, ctypes.c_int, c_int_p]
+    lib.opus_decoder_group_destroy.argtypes = [vp]
+    lib.opus_decoder_group_destroy.restype = None
+    lib.opus_decode_group_flat.argtypes = [vp, vp, ctypes.c_int32, vp, vp, vp, ctypes.c_int32, ctypes.c_int, vp, vp]
+    lib.opus_decode_group_device.argtypes = [vp, vp, vp, vp, vp, ctypes.c_int32, ctypes.c_int, vp, vp,
+                                             ctypes.c_int, ctypes.c_int, vp]
+    lib.opus_decoder_get_final_range_batch.argtypes = [vp, ctypes.c_int, vp]
+    lib.opus_b200_launch_count.restype = ctypes.c_longlong
+    lib.opus_packet_get_nb_samples.argtypes = [vp, ctypes.c_int32, ctypes.c_int32]
+    lib.opus_packet_get_nb_frames.argtypes = [vp, ctypes.c_int32]
+    lib.opus_packet_get_samples_per_frame.argtypes = [vp, ctypes.c_int32]
+    lib.opus_packet_get_bandwidth.argtypes = [vp]
+    lib.opus_packet_get_nb_channels.argtypes = [vp]
+    _lib = lib
+    return lib
+
+
+def _ptr(a):
+    return a.ctypes.data if a is not None else None
+
+
+class OpusDecoder(object):
+    """One stream.  Mirrors NativeOpusDecoder (reference Native/NativeOpusDecoder.cs)."""
+
+    def __init__(self, sample_rate, channels):
+        lib = load()
+        err = ctypes.c_int(0)
+        self._h = lib.opus_decoder_create(sample_rate, channels, ctypes.byref(err))
+        if not self._h:
+            raise OpusError(err.value, "opus_decoder_create")
+        self.sample_rate = sample_rate
+        self.channels = channels
+
+    def close(self):
+        if getattr(self, "_h", None):
+            load().opus_decoder_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def decode_raw(self, data, frame_size, fec=False):
+        """Returns (ret, pcm[frame_size, channels]); ret is what opus_decode returned."""
+        pcm = np.zeros((frame_size if frame_size > 0 else 1, self.channels), dtype=np.int16)
+        if data is None:
+            ret = load().opus_decode(self._h, None, 0, pcm.ctypes.data, frame_size, int(fec))
+        else:
+            buf = ctypes.create_string_buffer(bytes(data), len(data))
+            ret = load().opus_decode(self._h, ctypes.cast(buf, ctypes.c_void_p), len(data), pcm.ctypes.data,
+                                     frame_size, int(fec))
+        return ret, pcm
+
+    def decode(self, data, frame_size, fec=False):
+        ret, pcm = self.decode_raw(data, frame_size, fec)
+        if ret < 0:
+            raise OpusError(ret, "opus_decode")
+        return pcm[:ret]
+
+    def _get(self, request):
+        v = ctypes.c_int32(0)
+        rc = load().opus_decoder_ctl(self._h, request, ctypes.byref(v))
+        if rc != OPUS_OK:
+            raise OpusError(rc, "opus_decoder_ctl(%d)" % request)
+        return v.value
+
+    @property
+    def final_range(self):
+        return self._get(OPUS_GET_FINAL_RANGE_REQUEST) & 0xFFFFFFFF
+
+    @property
+    def bandwidth(self):
+        return self._get(OPUS_GET_BANDWIDTH_REQUEST)
+
+    @property
+    def last_packet_duration(self):
+        return self._get(OPUS_GET_LAST_PACKET_DURATION_REQUEST)
+
+    @property
+    def pitch(self):
+        return self._get(OPUS_GET_PITCH_REQUEST)
+
+    @property
+    def gain(self):
+        return self._get(OPUS_GET_GAIN_REQUEST)
+
+    @gain.setter
+    def gain(self, value):
+        rc = load().opus_decoder_ctl(self._h, OPUS_SET_GAIN_REQUEST, ctypes.c_int32(int(value)))
+        if rc != OPUS_OK:
+            raise OpusError(rc, "OPUS_SET_GAIN")
+
+    def reset_state(self):
+        rc = load().opus_decoder_ctl(self._h, OPUS_RESET_STATE)
+        if rc != OPUS_OK:
+            raise OpusError(rc, "OPUS_RESET_STATE")
+
+
+class OpusBatchDecoder(object):
+    """n independent streams of the same format, decoded by one call (opus_decode_group_flat)."""
+
+    def __init__(self, sample_rate, channels, n):
+        lib = load()
+        self.n = n
+        self.sample_rate = sample_rate
+        self.channels = channels
+        self.decoders = [OpusDecoder(sample_rate, channels) for _ in range(n)]
+        self._handles = (ctypes.c_void_p * n)(*[d._h for d in self.decoders])
+        err = ctypes.c_int(0)
+        self._g = lib.opus_decoder_group_create(self._handles, n, ctypes.byref(err))
+        if not self._g:
+            raise OpusError(err.value, "opus_decoder_group_create")
+
+    def close(self):
+        if getattr(self, "_g", None):
+            load().opus_decoder_group_destroy(self._g)
+            self._g = None
+        for d in getattr(self, "decoders", []):
+            d.close()
+        self.decoders = []
+
+    __del__ = close
+
+    def decode(self, packets, frame_size, fec=None):
+        """packets: list of n bytes objects (None/b'' = lost).  Returns (ret[n], pcm[n, frame_size, ch])."""
+        assert len(packets) == self.n
+        lens = np.array([len(p) if p else 0 for p in packets], dtype=np.int32)
+        offs = np.zeros(self.n, dtype=np.int32)
+        o = 0
+        for i, p in enumerate(packets):
+            if p:
+                offs[i] = o
+                o += len(p)
+            else:
+                offs[i] = -1
+        arena = np.frombuffer(b"".join(p for p in packets if p) + b"\0", dtype=np.uint8).copy()
+        return self.decode_flat(arena, o, offs, lens, frame_size, fec)
+
+    def decode_flat(self, arena, nbytes, offs, lens, frame_size, fec=None, pcm=None):
+        stride = frame_size * self.channels
+        if pcm is None:
+            pcm = np.zeros((self.n, frame_size, self.channels), dtype=np.int16)
+        ret = np.zeros(self.n, dtype=np.int32)
+        fec_a = None if fec is None else np.ascontiguousarray(fec, dtype=np.int32)
+        rc = load().opus_decode_group_flat(self._g, _ptr(arena), nbytes, _ptr(offs), _ptr(lens), _ptr(pcm), stride,
+                                           frame_size, _ptr(fec_a), _ptr(ret))
+        if rc != OPUS_OK:
+            raise OpusError(rc, "opus_decode_group_flat")
+        return ret, pcm
+
+    def final_ranges(self):
+        out = np.zeros(self.n, dtype=np.uint32)
+        rc = load().opus_decoder_get_final_range_batch(self._handles, self.n, _ptr(out))
+        if rc != OPUS_OK:
+            raise OpusError(rc, "opus_decoder_get_final_range_batch")
+        return out

@@ -25,6 +25,7 @@ typedef int8_t i8;
 #if defined(__CUDACC__) && !defined(CB_HOST_EMU)
 #define CB_DEVICE_BUILD 1
 #define CB_FN __device__ __forceinline__
+#define CB_HD __host__ __device__ __forceinline__
 #define CB_FN_NOINLINE __device__ __noinline__
 #define CB_UTABLE static __constant__ const
 #define CB_GTABLE static __device__ const
@@ -40,6 +41,7 @@ template <typename T> CB_FN T cb_ldg(const T* p) { return __ldg(p); }
 #else
 #define CB_DEVICE_BUILD 0
 #define CB_FN static inline
+#define CB_HD static inline
 #define CB_FN_NOINLINE static
 #define CB_UTABLE static const
 #define CB_GTABLE static const
@@ -55,8 +57,8 @@ template <typename T> CB_FN T cb_ldg(const T* p) { return *p; }
 #endif
 
 // ---- integer helpers -------------------------------------------------------------------
-CB_FN int cb_imin(int a, int b) { return a < b ? a : b; }
-CB_FN int cb_imax(int a, int b) { return a > b ? a : b; }
+CB_HD int cb_imin(int a, int b) { return a < b ? a : b; }
+CB_HD int cb_imax(int a, int b) { return a > b ? a : b; }
 // EC_ILOG (celt/ecintrin.h:69-82): position of the highest set bit, 1-based; 0 for 0.
 CB_FN int cb_ilog(u32 v) { return 32 - cb_clz(v); }
 // celt_ilog2 / celt_zlog2 (celt/mathops.h:148-160)

@@ -1,0 +1,64 @@
+// cb_decode_pass.h -- per-stream bodies of the two decode kernels (shared by the __global__
+// wrappers in cb_kernels.cu and by the test-only lane-loop emulation).
+#pragma once
+#include "cb_celt_entropy.h"
+#include "cb_celt_synth.h"
+#include "cb_opus_plan.h"
+
+// Kernel A, one stream, one pass.  `pkt` = per-warp staging area for the payload bytes.
+CB_FN void decode_entropy_pass(EntWork& w, u8* pkt, OpusDecState* st, StreamPlan* pl, FrameSide* side,
+                               const u8* data, i32* ret_slot, int pass) {
+  const int kind = pl->kind;
+  if (pl->ret < 0 || pass >= pl->nframes || kind == CB_PLAN_NONE) {
+    side->kind = 0;
+    return;
+  }
+  if (kind == CB_PLAN_ZERO) {
+    side->kind = 3;
+    return;
+  }
+  const int len = pl->len[pass];
+  const int nsamp = pl->nsamp[pass];
+  if (kind == CB_PLAN_PLC || len <= 1) {
+    // concealment (celt_decode_lost) is not built yet: flag it, never fake it
+    side->kind = 0;
+    pl->ret = CB_UNIMPLEMENTED;
+    *ret_slot = CB_UNIMPLEMENTED;
+    return;
+  }
+  const i32 off = pl->off[pass];
+  CB_LANE_LOOP(i, len) pkt[i] = data[off + i];
+  CB_WSYNC();
+  int LM = 0;
+  {
+    int fs48 = nsamp * st->celt.downsample;
+    while ((120 << LM) < fs48) LM++;
+  }
+  EntFrameCfg cfg;
+  cfg.LM = LM;
+  cfg.C = st->stream_channels;
+  cfg.start = 0;
+  cfg.end = opus_bandwidth_endband(st->bandwidth);
+  cfg.accum = 0;
+  u32 fr = 0;
+  int rc = celt_entropy_decode(w, &st->celt, side, pkt, len, cfg, &fr);
+  st->rangeFinal = fr;
+  st->prev_mode = CB_MODE_CELT_ONLY;
+  st->prev_redundancy = 0;
+  if (rc < 0) {
+    pl->ret = rc;
+    *ret_slot = rc;
+  }
+}
+
+// Kernel B, one (stream, channel), one pass.  `row` = this stream's PCM row.
+CB_FN void decode_synth_pass(SynWork& w, OpusDecState* st, const StreamPlan* pl, const FrameSide* side,
+                             i16* row, int c, int pass) {
+  const int CC = st->channels;
+  if (side->kind == 1) {
+    celt_synth_channel(w, &st->celt, side, c, row + (size_t)pl->pcm_off[pass] * CC);
+  } else if (side->kind == 3 && pass == 0) {
+    const int total = pl->total_samples;
+    CB_LANE_LOOP(j, total) row[j * CC + c] = 0;
+  }
+}

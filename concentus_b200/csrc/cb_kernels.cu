@@ -1,0 +1,120 @@
+// cb_kernels.cu -- sm_100a kernels of the batched Opus decoder and their launchers.
+//
+//   opus_plan_kernel    : 1 thread / stream  -- TOC + framing parse, argument checks, StreamPlan
+//   celt_entropy_kernel : 1 warp   / stream  -- range decoder + PVQ/band reconstruction (kernel A)
+//   celt_synth_kernel   : 1 warp   / (stream, channel) -- IMDCT, post-filter, de-emphasis (kernel B)
+//
+// A and B are launched once per frame index ("pass") of the packets in the batch; single-frame
+// packets (the normal case) need one pass.  All kernels are integer / latency bound (no tensor
+// cores): the design levers are warps resident per SM (7 CTAs x 4 warps = 28 warps, sized from the
+// 227 KB shared memory) and keeping every per-stream array in shared memory.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "cb_decode_pass.h"
+#include "cb_kernels.h"
+
+#define A_WARPS 4
+#define B_WARPS 4
+
+__global__ void opus_plan_kernel(OpusDecState* const* states, const u8* data, const i32* offs,
+                                 const i32* lens, const i32* fec, int frame_size, StreamPlan* plans,
+                                 i32* ret, int n) {
+  int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n) return;
+  OpusDecState* st = states[s];
+  StreamPlan* pl = &plans[s];
+  opus_plan_stream(st, pl, data, offs[s], lens[s], frame_size, fec ? fec[s] : 0, 0, nullptr);
+  ret[s] = pl->ret;
+}
+
+__global__ void __launch_bounds__(A_WARPS * 32, 7)
+celt_entropy_kernel(OpusDecState* const* states, const u8* data, StreamPlan* plans, FrameSide* sides,
+                    i32* ret, int n, int pass, int per_warp_bytes) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int warp = threadIdx.x >> 5;
+  const int s = blockIdx.x * A_WARPS + warp;
+  if (s >= n) return;
+  EntWork& w = *reinterpret_cast<EntWork*>(smem + (size_t)warp * per_warp_bytes);
+  u8* pkt = reinterpret_cast<u8*>(&w) + sizeof(EntWork);
+  OpusDecState* st = states[s];
+  StreamPlan* pl = &plans[s];
+  FrameSide* side = &sides[s];
+  decode_entropy_pass(w, pkt, st, pl, side, data, &ret[s], pass);
+}
+
+__global__ void __launch_bounds__(B_WARPS * 32, 7)
+celt_synth_kernel(OpusDecState* const* states, const StreamPlan* plans, const FrameSide* sides, i16* pcm,
+                  i32 pcm_stride, int n, int pass) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int warp = threadIdx.x >> 5;
+  const int gw = blockIdx.x * B_WARPS + warp;
+  const int s = gw >> 1, c = gw & 1;
+  if (s >= n) return;
+  OpusDecState* st = states[s];
+  const int CC = st->channels;
+  if (c >= CC) return;
+  const FrameSide* side = &sides[s];
+  const StreamPlan* pl = &plans[s];
+  SynWork& w = *reinterpret_cast<SynWork*>(smem + (size_t)warp * sizeof(SynWork));
+  i16* row = pcm + (size_t)s * pcm_stride;
+  decode_synth_pass(w, st, pl, side, row, c, pass);
+}
+
+// ---- launchers (host) ------------------------------------------------------------------------
+static int g_attr_done[64];
+
+extern "C" size_t cbk_entropy_smem_per_warp(int max_payload) {
+  size_t b = sizeof(EntWork) + (size_t)((max_payload + 15) & ~15);
+  return (b + 15) & ~(size_t)15;
+}
+
+extern "C" int cbk_launch_plan(OpusDecState* const* d_states, const u8* d_data, const i32* d_off,
+                               const i32* d_len, const i32* d_fec, int frame_size, StreamPlan* d_plans,
+                               i32* d_ret, int n, cudaStream_t stream) {
+  if (n <= 0) return 0;
+  opus_plan_kernel<<<(n + 127) / 128, 128, 0, stream>>>(d_states, d_data, d_off, d_len, d_fec, frame_size,
+                                                        d_plans, d_ret, n);
+  return (int)cudaGetLastError();
+}
+
+static int ensure_attrs() {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 64 && g_attr_done[dev]) return 0;
+  e = cudaFuncSetAttribute(celt_entropy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  if (e != cudaSuccess) return (int)e;
+  e = cudaFuncSetAttribute(celt_synth_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 64) g_attr_done[dev] = 1;
+  return 0;
+}
+
+extern "C" int cbk_launch_entropy(OpusDecState* const* d_states, const u8* d_data, StreamPlan* d_plans,
+                                  FrameSide* d_sides, i32* d_ret, int n, int pass, int max_payload,
+                                  cudaStream_t stream) {
+  if (n <= 0) return 0;
+  int rc = ensure_attrs();
+  if (rc) return rc;
+  const int per_warp = (int)cbk_entropy_smem_per_warp(max_payload);
+  const size_t smemA = (size_t)per_warp * A_WARPS;
+  celt_entropy_kernel<<<(n + A_WARPS - 1) / A_WARPS, A_WARPS * 32, smemA, stream>>>(
+      d_states, d_data, d_plans, d_sides, d_ret, n, pass, per_warp);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int cbk_launch_synth(OpusDecState* const* d_states, const StreamPlan* d_plans, const FrameSide* d_sides,
+                                i16* d_pcm, i32 pcm_stride, int n, int pass, cudaStream_t stream) {
+  if (n <= 0) return 0;
+  int rc = ensure_attrs();
+  if (rc) return rc;
+  const size_t smemB = sizeof(SynWork) * B_WARPS;
+  const int warpsB = n * 2;
+  celt_synth_kernel<<<(warpsB + B_WARPS - 1) / B_WARPS, B_WARPS * 32, smemB, stream>>>(
+      d_states, d_plans, d_sides, d_pcm, pcm_stride, n, pass);
+  return (int)cudaGetLastError();
+}
+
+extern "C" size_t cbk_sizeof_state(void) { return sizeof(OpusDecState); }
+extern "C" size_t cbk_sizeof_plan(void) { return sizeof(StreamPlan); }
+extern "C" size_t cbk_sizeof_side(void) { return sizeof(FrameSide); }

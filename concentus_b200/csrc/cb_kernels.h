@@ -1,0 +1,19 @@
+// cb_kernels.h -- launch interface between the host API (opus_api.cu) and the kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include "cb_state.h"
+
+extern "C" {
+size_t cbk_entropy_smem_per_warp(int max_payload);
+int cbk_launch_plan(OpusDecState* const* d_states, const u8* d_data, const i32* d_off, const i32* d_len,
+                    const i32* d_fec, int frame_size, StreamPlan* d_plans, i32* d_ret, int n,
+                    cudaStream_t stream);
+int cbk_launch_entropy(OpusDecState* const* d_states, const u8* d_data, StreamPlan* d_plans, FrameSide* d_sides,
+                       i32* d_ret, int n, int pass, int max_payload, cudaStream_t stream);
+int cbk_launch_synth(OpusDecState* const* d_states, const StreamPlan* d_plans, const FrameSide* d_sides,
+                     i16* d_pcm, i32 pcm_stride, int n, int pass, cudaStream_t stream);
+size_t cbk_sizeof_state(void);
+size_t cbk_sizeof_plan(void);
+size_t cbk_sizeof_side(void);
+}

@@ -55,7 +55,6 @@ struct alignas(16) FrameSide {
   i16 X[2 * CB_MAXN];        // normalised spectrum, channel-major
 };
 
-// Frame descriptor built by the host (or implied by a raw packet).
 // celt_decoder_init + OPUS_RESET_STATE (celt_decoder.c:134-172,1196-1204): all-zero except the
 // two log-energy memories, which start at -28 dB.  Host-side helper (the blob is then copied to HBM).
 static inline void celt_state_reset(CeltDecState* s, int channels, int downsample) {
@@ -66,9 +65,66 @@ static inline void celt_state_reset(CeltDecState* s, int channels, int downsampl
   for (int i = 0; i < 2 * CB_NBANDS; i++) s->oldLogE[i] = s->oldLogE2[i] = -28672;
 }
 
-struct FrameDesc {
-  i32 offset;                // byte offset of the CELT payload in the packet arena
-  i32 len;                   // payload bytes (after TOC / framing)
-  i32 toc;                   // Opus TOC byte (frame size, bandwidth, stereo flag), -1 = skip stream
-  i32 pcm_offset;            // sample-frame offset inside this stream's PCM row
+// ---- Opus layer ---------------------------------------------------------------------------
+#define CB_MODE_SILK_ONLY 1000
+#define CB_MODE_HYBRID 1001
+#define CB_MODE_CELT_ONLY 1002
+#define CB_BW_NARROWBAND 1101
+#define CB_BW_MEDIUMBAND 1102
+#define CB_BW_WIDEBAND 1103
+#define CB_BW_SUPERWIDEBAND 1104
+#define CB_BW_FULLBAND 1105
+#define CB_OK 0
+#define CB_BAD_ARG -1
+#define CB_BUFFER_TOO_SMALL -2
+#define CB_INTERNAL_ERROR -3
+#define CB_INVALID_PACKET -4
+#define CB_UNIMPLEMENTED -5
+#define CB_INVALID_STATE -6
+#define CB_ALLOC_FAIL -7
+
+// Per-stream decoder blob in HBM: struct OpusDecoder (opus-fix/src/opus_decoder.c:55-79) followed
+// by the CELT state.  The Opus-layer fields live on the device so that a batch call needs no
+// per-packet work on the host (TOC/framing is parsed by the plan kernel).
+struct alignas(16) OpusDecState {
+  i32 Fs, channels, decode_gain;
+  i32 stream_channels, bandwidth, mode, prev_mode, frame_size, prev_redundancy, last_packet_duration;
+  u32 rangeFinal;
+  i32 pad;
+  CeltDecState celt;
+};
+// opus_decoder_init + OPUS_RESET_STATE (opus_decoder.c:96-137,833-843)
+static inline void opus_state_reset(OpusDecState* s, int Fs, int channels, int keep_gain) {
+  int gain = keep_gain ? s->decode_gain : 0;
+  celt_state_reset(&s->celt, channels, 48000 / Fs);
+  s->Fs = Fs;
+  s->channels = channels;
+  s->decode_gain = gain;
+  s->stream_channels = channels;
+  s->bandwidth = 0;
+  s->mode = 0;
+  s->prev_mode = 0;
+  s->frame_size = Fs / 400;
+  s->prev_redundancy = 0;
+  s->last_packet_duration = 0;
+  s->rangeFinal = 0;
+  s->pad = 0;
+}
+
+// What the plan kernel decides for one stream of a batch call: which frames each later pass
+// decodes (offset/length in the packet arena), or which concealment chunks it synthesises.
+#define CB_MAX_FRAMES 48
+#define CB_PLAN_NONE 0      // error / nothing to do
+#define CB_PLAN_DECODE 1    // frames of a packet
+#define CB_PLAN_PLC 2       // concealment chunks (packet loss / DTX / FEC request on CELT)
+#define CB_PLAN_ZERO 3      // loss before any packet was seen: zeros (opus_decoder.c:261-268)
+struct alignas(16) StreamPlan {
+  i32 ret;                  // value opus_decode() returns for this stream
+  i32 nframes;
+  i32 kind;
+  i32 total_samples;        // samples per channel covered by the plan
+  i32 off[CB_MAX_FRAMES];   // payload offset in the arena
+  i16 len[CB_MAX_FRAMES];   // payload bytes (<=1 means "conceal this frame")
+  i16 nsamp[CB_MAX_FRAMES]; // samples per channel produced (API rate)
+  i16 pcm_off[CB_MAX_FRAMES];
 };

@@ -1,0 +1,653 @@
+// opus_api.cu -- host side of libopus_b200.so: the libopus decoder ABI + the batch entry points.
+//
+// Mirrors the reference's Opus API layer (opus-fix/src/opus_decoder.c, src/opus.c) in names,
+// argument meaning and error behaviour, but holds no codec arithmetic: every sample is produced
+// by the CUDA kernels in cb_kernels.cu.  There is NO CPU decode path -- if CUDA is unusable the
+// calls fail with OPUS_INTERNAL_ERROR / OPUS_ALLOC_FAIL and say why on stderr.
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <mutex>
+#include <vector>
+#include "../../include/opus_b200.h"
+#include "cb_kernels.h"
+#include "cb_state.h"
+#include "cb_opus_plan.h"
+
+#define CUDA_OK(call)                                                                            \
+  do {                                                                                           \
+    cudaError_t e_ = (call);                                                                     \
+    if (e_ != cudaSuccess) {                                                                     \
+      fprintf(stderr, "[opus_b200] CUDA error %s at %s:%d: %s\n", cudaGetErrorName(e_), __FILE__, \
+              __LINE__, cudaGetErrorString(e_));                                                 \
+      return OPUS_INTERNAL_ERROR;                                                                \
+    }                                                                                            \
+  } while (0)
+
+namespace {
+
+const int kMagic = 0x4f423230;   // "OB20"
+const int kSlab = 256;           // decoder states per cudaMalloc
+
+struct GrowBuf {                 // grow-only buffer (device or pinned host)
+  void* p = nullptr;
+  size_t cap = 0;
+  bool pinned = false;
+  int reserve(size_t bytes) {
+    if (bytes <= cap) return 0;
+    size_t want = bytes + bytes / 4 + 256;
+    if (p) { if (pinned) cudaFreeHost(p); else cudaFree(p); p = nullptr; cap = 0; }
+    cudaError_t e = pinned ? cudaMallocHost(&p, want) : cudaMalloc(&p, want);
+    if (e != cudaSuccess) {
+      fprintf(stderr, "[opus_b200] allocation of %zu bytes failed: %s\n", want, cudaGetErrorString(e));
+      p = nullptr;
+      return OPUS_ALLOC_FAIL;
+    }
+    cap = want;
+    return 0;
+  }
+};
+
+struct DevCtx {
+  int device = -1;
+  cudaStream_t stream = nullptr;
+  std::vector<OpusDecState*> slabs;
+  std::vector<OpusDecState*> free_slots;
+  // staging for the pointer-array / flat entry points
+  GrowBuf d_pkt, d_i32, d_pcm, d_states, d_plans, d_sides;
+  GrowBuf h_pkt, h_i32, h_pcm, h_states;
+  DevCtx() { h_pkt.pinned = h_i32.pinned = h_pcm.pinned = h_states.pinned = true; }
+};
+
+std::mutex g_mu;
+DevCtx g_ctx[16];
+long long g_launches = 0;
+
+// optional per-kernel timing (CUDA events on the launching stream), for bench.py's roofline line
+struct ProfRec { int kind; cudaEvent_t a, b; };
+bool g_prof_on = false;
+std::vector<ProfRec> g_prof;
+struct ProfScope {
+  cudaStream_t s; int kind; cudaEvent_t a = nullptr, b = nullptr; bool on;
+  ProfScope(cudaStream_t s_, int k) : s(s_), kind(k), on(g_prof_on) {
+    if (on) { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, s); }
+  }
+  ~ProfScope() {
+    if (on) { cudaEventRecord(b, s); g_prof.push_back({kind, a, b}); }
+  }
+};
+
+DevCtx* ctx_for_current_device(int* err) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= 16) {
+    fprintf(stderr, "[opus_b200] no usable CUDA device: %s\n", cudaGetErrorString(e));
+    if (err) *err = OPUS_INTERNAL_ERROR;
+    return nullptr;
+  }
+  DevCtx* c = &g_ctx[dev];
+  if (c->device < 0) {
+    e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+      fprintf(stderr, "[opus_b200] cudaStreamCreate failed: %s\n", cudaGetErrorString(e));
+      if (err) *err = OPUS_INTERNAL_ERROR;
+      return nullptr;
+    }
+    c->device = dev;
+  }
+  return c;
+}
+
+}  // namespace
+
+struct OpusDecoderGroup;
+struct OpusDecoder {
+  int magic;
+  int Fs, channels;
+  int device;
+  int decode_gain;
+  OpusDecState* d_state;
+  OpusDecoderGroup* self_group;   // group of one, created on first opus_decode()
+};
+
+struct OpusDecoderGroup {
+  int magic;
+  int n, device;
+  int Fs, channels;            // common values (or -1 when mixed)
+  OpusDecoder** members;
+  OpusDecState** d_states;     // device array of n state pointers
+  StreamPlan* d_plans;
+  FrameSide* d_sides;
+  i32* d_ret;                  // n
+  i32* d_maxframes;            // scratch for plan read-back (unused for now)
+};
+
+extern "C" {
+
+const char* opus_get_version_string(void) { return "libopus 1.1.2-fixed (opus_b200 sm_100a)"; }
+
+const char* opus_strerror(int error) {
+  static const char* const s[8] = {"success", "invalid argument", "buffer too small", "internal error",
+                                   "corrupted stream", "request not implemented", "invalid state",
+                                   "memory allocation failed"};
+  if (error > 0 || error < -7) return "unknown error";
+  return s[-error];
+}
+
+int opus_decoder_get_size(int channels) {
+  if (channels < 1 || channels > 2) return 0;
+  return (int)sizeof(OpusDecoder);
+}
+
+static int upload_fresh_state(OpusDecoder* st, int keep_gain) {
+  OpusDecState* h = (OpusDecState*)malloc(sizeof(OpusDecState));
+  if (!h) return OPUS_ALLOC_FAIL;
+  h->decode_gain = st->decode_gain;
+  opus_state_reset(h, st->Fs, st->channels, keep_gain);
+  cudaError_t e = cudaMemcpy(st->d_state, h, sizeof(OpusDecState), cudaMemcpyHostToDevice);
+  free(h);
+  if (e != cudaSuccess) {
+    fprintf(stderr, "[opus_b200] state upload failed: %s\n", cudaGetErrorString(e));
+    return OPUS_INTERNAL_ERROR;
+  }
+  return OPUS_OK;
+}
+
+OpusDecoder* opus_decoder_create(opus_int32 Fs, int channels, int* error) {
+  if ((Fs != 48000 && Fs != 24000 && Fs != 16000 && Fs != 12000 && Fs != 8000) || (channels != 1 && channels != 2)) {
+    if (error) *error = OPUS_BAD_ARG;
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> lk(g_mu);
+  int err = OPUS_OK;
+  DevCtx* c = ctx_for_current_device(&err);
+  if (!c) { if (error) *error = err; return nullptr; }
+  if (c->free_slots.empty()) {
+    OpusDecState* slab = nullptr;
+    cudaError_t e = cudaMalloc((void**)&slab, sizeof(OpusDecState) * kSlab);
+    if (e != cudaSuccess) {
+      fprintf(stderr, "[opus_b200] cudaMalloc of a decoder slab failed: %s\n", cudaGetErrorString(e));
+      if (error) *error = OPUS_ALLOC_FAIL;
+      return nullptr;
+    }
+    c->slabs.push_back(slab);
+    for (int i = kSlab - 1; i >= 0; i--) c->free_slots.push_back(slab + i);
+  }
+  OpusDecoder* st = (OpusDecoder*)calloc(1, sizeof(OpusDecoder));
+  if (!st) { if (error) *error = OPUS_ALLOC_FAIL; return nullptr; }
+  st->magic = kMagic;
+  st->Fs = Fs;
+  st->channels = channels;
+  st->device = c->device;
+  st->decode_gain = 0;
+  st->d_state = c->free_slots.back();
+  c->free_slots.pop_back();
+  int rc = upload_fresh_state(st, 0);
+  if (rc != OPUS_OK) {
+    c->free_slots.push_back(st->d_state);
+    free(st);
+    if (error) *error = rc;
+    return nullptr;
+  }
+  if (error) *error = OPUS_OK;
+  return st;
+}
+
+void opus_decoder_group_destroy(OpusDecoderGroup* g);
+
+void opus_decoder_destroy(OpusDecoder* st) {
+  if (!st || st->magic != kMagic) return;
+  if (st->self_group) { opus_decoder_group_destroy(st->self_group); st->self_group = nullptr; }
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (st->device >= 0 && st->device < 16) {
+    DevCtx* c = &g_ctx[st->device];
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    c->free_slots.push_back(st->d_state);
+  }
+  st->magic = 0;
+  free(st);
+}
+
+// ---- packet helpers (host restatement of src/opus.c:169-188 and src/opus_decoder.c:921-981) ----
+int opus_packet_get_samples_per_frame(const unsigned char* data, opus_int32 Fs) {
+  int audiosize;
+  if (data[0] & 0x80) {
+    audiosize = (data[0] >> 3) & 0x3;
+    audiosize = (Fs << audiosize) / 400;
+  } else if ((data[0] & 0x60) == 0x60) {
+    audiosize = (data[0] & 0x08) ? Fs / 50 : Fs / 100;
+  } else {
+    audiosize = (data[0] >> 3) & 0x3;
+    audiosize = audiosize == 3 ? Fs * 60 / 1000 : (Fs << audiosize) / 100;
+  }
+  return audiosize;
+}
+int opus_packet_get_bandwidth(const unsigned char* data) {
+  int bw;
+  if (data[0] & 0x80) {
+    bw = CB_BW_MEDIUMBAND + ((data[0] >> 5) & 0x3);
+    if (bw == CB_BW_MEDIUMBAND) bw = CB_BW_NARROWBAND;
+  } else if ((data[0] & 0x60) == 0x60) {
+    bw = (data[0] & 0x10) ? CB_BW_FULLBAND : CB_BW_SUPERWIDEBAND;
+  } else {
+    bw = CB_BW_NARROWBAND + ((data[0] >> 5) & 0x3);
+  }
+  return bw;
+}
+int opus_packet_get_nb_channels(const unsigned char* data) { return (data[0] & 0x4) ? 2 : 1; }
+int opus_packet_get_nb_frames(const unsigned char packet[], opus_int32 len) {
+  if (len < 1) return OPUS_BAD_ARG;
+  int count = packet[0] & 0x3;
+  if (count == 0) return 1;
+  if (count != 3) return 2;
+  if (len < 2) return OPUS_INVALID_PACKET;
+  return packet[1] & 0x3F;
+}
+int opus_packet_get_nb_samples(const unsigned char packet[], opus_int32 len, opus_int32 Fs) {
+  int count = opus_packet_get_nb_frames(packet, len);
+  if (count < 0) return count;
+  int samples = count * opus_packet_get_samples_per_frame(packet, Fs);
+  if (samples * 25 > Fs * 3) return OPUS_INVALID_PACKET;
+  return samples;
+}
+int opus_decoder_get_nb_samples(const OpusDecoder* dec, const unsigned char packet[], opus_int32 len) {
+  return opus_packet_get_nb_samples(packet, len, dec->Fs);
+}
+
+int opus_packet_parse(const unsigned char* data, opus_int32 len, unsigned char* out_toc,
+                      const unsigned char* frames[48], opus_int16 size[48], int* payload_offset) {
+  if (!size || !data) return OPUS_BAD_ARG;
+  int toc = 0, poff = 0;
+  int count = opus_parse_packet(data, len, 0, &toc, size, &poff, nullptr);
+  if (count < 0) return count;
+  if (out_toc) *out_toc = (unsigned char)toc;
+  if (payload_offset) *payload_offset = poff;
+  if (frames) {
+    const unsigned char* p = data + poff;
+    for (int i = 0; i < count; i++) { frames[i] = p; p += size[i]; }
+  }
+  return count;
+}
+
+// ---- groups --------------------------------------------------------------------------------
+static void group_free(OpusDecoderGroup* g) {
+  if (!g) return;
+  if (g->d_states) cudaFree(g->d_states);
+  if (g->d_plans) cudaFree(g->d_plans);
+  if (g->d_sides) cudaFree(g->d_sides);
+  if (g->d_ret) cudaFree(g->d_ret);
+  free(g->members);
+  g->magic = 0;
+  free(g);
+}
+
+OpusDecoderGroup* opus_decoder_group_create(OpusDecoder* const* st, int n, int* error) {
+  if (!st || n <= 0) { if (error) *error = OPUS_BAD_ARG; return nullptr; }
+  for (int i = 0; i < n; i++) {
+    if (!st[i] || st[i]->magic != kMagic || st[i]->device != st[0]->device) {
+      if (error) *error = OPUS_BAD_ARG;
+      return nullptr;
+    }
+  }
+  std::lock_guard<std::mutex> lk(g_mu);
+  int prev = -1;
+  cudaGetDevice(&prev);
+  if (cudaSetDevice(st[0]->device) != cudaSuccess) { if (error) *error = OPUS_INTERNAL_ERROR; return nullptr; }
+  OpusDecoderGroup* g = (OpusDecoderGroup*)calloc(1, sizeof(OpusDecoderGroup));
+  std::vector<OpusDecState*> ptrs(n);
+  g->magic = kMagic;
+  g->n = n;
+  g->device = st[0]->device;
+  g->Fs = st[0]->Fs;
+  g->channels = st[0]->channels;
+  g->members = (OpusDecoder**)malloc(sizeof(OpusDecoder*) * n);
+  for (int i = 0; i < n; i++) {
+    g->members[i] = st[i];
+    ptrs[i] = st[i]->d_state;
+    if (st[i]->Fs != g->Fs) g->Fs = -1;
+    if (st[i]->channels != g->channels) g->channels = -1;
+  }
+  bool ok = cudaMalloc((void**)&g->d_states, sizeof(OpusDecState*) * n) == cudaSuccess &&
+            cudaMalloc((void**)&g->d_plans, sizeof(StreamPlan) * n) == cudaSuccess &&
+            cudaMalloc((void**)&g->d_sides, sizeof(FrameSide) * n) == cudaSuccess &&
+            cudaMalloc((void**)&g->d_ret, sizeof(i32) * n) == cudaSuccess &&
+            cudaMemcpy(g->d_states, ptrs.data(), sizeof(OpusDecState*) * n, cudaMemcpyHostToDevice) == cudaSuccess;
+  if (prev >= 0) cudaSetDevice(prev);
+  if (!ok) {
+    fprintf(stderr, "[opus_b200] group allocation failed: %s\n", cudaGetErrorString(cudaGetLastError()));
+    group_free(g);
+    if (error) *error = OPUS_ALLOC_FAIL;
+    return nullptr;
+  }
+  if (error) *error = OPUS_OK;
+  return g;
+}
+
+void opus_decoder_group_destroy(OpusDecoderGroup* g) {
+  if (!g || g->magic != kMagic) return;
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (g->device >= 0 && g->device < 16 && g_ctx[g->device].stream) cudaStreamSynchronize(g_ctx[g->device].stream);
+  group_free(g);
+}
+
+// Queue plan + passes for a group; everything device resident.  No synchronisation.
+static int group_enqueue(OpusDecoderGroup* g, const u8* d_data, const i32* d_off, const i32* d_len, i16* d_pcm,
+                         i32 pcm_stride, int frame_size, const i32* d_fec, i32* d_ret, int passes,
+                         int max_packet_bytes, cudaStream_t stream) {
+  int rc;
+  {
+    ProfScope ps(stream, 0);
+    rc = cbk_launch_plan(g->d_states, d_data, d_off, d_len, d_fec, frame_size, g->d_plans, d_ret, g->n, stream);
+  }
+  g_launches += 1;
+  if (rc) { fprintf(stderr, "[opus_b200] plan launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
+  for (int p = 0; p < passes; p++) {
+    {
+      ProfScope ps(stream, 1);
+      rc = cbk_launch_entropy(g->d_states, d_data, g->d_plans, g->d_sides, d_ret, g->n, p, max_packet_bytes, stream);
+    }
+    if (!rc) {
+      ProfScope ps(stream, 2);
+      rc = cbk_launch_synth(g->d_states, g->d_plans, g->d_sides, d_pcm, pcm_stride, g->n, p, stream);
+    }
+    g_launches += 2;
+    if (rc) { fprintf(stderr, "[opus_b200] pass launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
+  }
+  return OPUS_OK;
+}
+
+int opus_decode_group_device(OpusDecoderGroup* g, const unsigned char* d_data, const opus_int32* d_offsets,
+                             const opus_int32* d_len, opus_int16* d_pcm, opus_int32 pcm_stride, int frame_size,
+                             const int* d_decode_fec, int* d_ret, int max_frames, int max_packet_bytes,
+                             void* cuda_stream) {
+  if (!g || g->magic != kMagic || !d_data || !d_offsets || !d_len || !d_pcm || !d_ret) return OPUS_BAD_ARG;
+  if (frame_size <= 0 || max_frames < 1 || max_frames > CB_MAX_FRAMES || max_packet_bytes < 0) return OPUS_BAD_ARG;
+  std::lock_guard<std::mutex> lk(g_mu);
+  CUDA_OK(cudaSetDevice(g->device));
+  int err = 0;
+  DevCtx* c = ctx_for_current_device(&err);
+  if (!c) return err;
+  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+  return group_enqueue(g, d_data, d_offsets, d_len, d_pcm, pcm_stride, frame_size, d_decode_fec, d_ret,
+                       max_frames, max_packet_bytes, s);
+}
+
+// Upper bound on the passes a batch needs, from the packets themselves (host side, O(n) byte reads).
+static int scan_passes(const unsigned char* data, const i32* off, const i32* len, int n, int frame_size, int Fs_hint,
+                       int* max_len) {
+  int passes = 1, mlen = 0, any_lost = 0;
+  for (int i = 0; i < n; i++) {
+    if (off[i] < 0 || len[i] <= 0) { any_lost = 1; continue; }
+    if (len[i] > mlen) mlen = len[i];
+    int nf = opus_packet_get_nb_frames(data + off[i], len[i]);
+    if (nf > passes) passes = nf;
+  }
+  if (any_lost) {
+    // concealment is cut into chunks of at least 2.5 ms (opus_decoder.c:239-292)
+    int F2_5 = (Fs_hint > 0 ? Fs_hint : 8000) / 400;
+    int chunks = (frame_size + F2_5 - 1) / F2_5;
+    if (chunks > passes) passes = chunks;
+  }
+  if (passes > CB_MAX_FRAMES) passes = CB_MAX_FRAMES;
+  *max_len = mlen;
+  return passes;
+}
+
+int opus_decode_group_flat(OpusDecoderGroup* g, const unsigned char* data, opus_int32 data_bytes,
+                           const opus_int32* offsets, const opus_int32* len, opus_int16* pcm,
+                           opus_int32 pcm_stride, int frame_size, const int* decode_fec, int* ret) {
+  if (!g || g->magic != kMagic || !offsets || !len || !pcm || !ret) return OPUS_BAD_ARG;
+  if (data_bytes < 0 || (data_bytes > 0 && !data)) return OPUS_BAD_ARG;
+  const int n = g->n;
+  if (frame_size <= 0) {
+    for (int i = 0; i < n; i++) ret[i] = OPUS_BAD_ARG;
+    return OPUS_OK;
+  }
+  int maxch = 1;
+  for (int i = 0; i < n; i++) {
+    if (g->members[i]->channels > maxch) maxch = g->members[i]->channels;
+    if (offsets[i] >= 0 && len[i] > 0 && (offsets[i] + (long long)len[i] > data_bytes)) return OPUS_BAD_ARG;
+  }
+  if (pcm_stride < frame_size * maxch) return OPUS_BAD_ARG;
+  std::lock_guard<std::mutex> lk(g_mu);
+  CUDA_OK(cudaSetDevice(g->device));
+  int err = 0;
+  DevCtx* c = ctx_for_current_device(&err);
+  if (!c) return err;
+  int max_len = 0;
+  int passes = scan_passes(data, offsets, len, n, frame_size, g->Fs, &max_len);
+  const size_t pkt_bytes = (size_t)data_bytes + 16;
+  const size_t pcm_bytes = (size_t)n * pcm_stride * sizeof(i16);
+  const size_t i32_bytes = (size_t)n * 3 * sizeof(i32);
+  if (c->d_pkt.reserve(pkt_bytes) || c->d_pcm.reserve(pcm_bytes) || c->d_i32.reserve(i32_bytes) ||
+      c->h_i32.reserve(i32_bytes))
+    return OPUS_ALLOC_FAIL;
+  i32* h_i = (i32*)c->h_i32.p;
+  memcpy(h_i, offsets, n * sizeof(i32));
+  memcpy(h_i + n, len, n * sizeof(i32));
+  if (decode_fec) memcpy(h_i + 2 * n, decode_fec, n * sizeof(i32));
+  else memset(h_i + 2 * n, 0, n * sizeof(i32));
+  i32* d_i = (i32*)c->d_i32.p;
+  cudaStream_t s = c->stream;
+  if (data_bytes > 0) CUDA_OK(cudaMemcpyAsync(c->d_pkt.p, data, data_bytes, cudaMemcpyHostToDevice, s));
+  CUDA_OK(cudaMemcpyAsync(d_i, h_i, i32_bytes, cudaMemcpyHostToDevice, s));
+  int rc = group_enqueue(g, (const u8*)c->d_pkt.p, d_i, d_i + n, (i16*)c->d_pcm.p, pcm_stride, frame_size,
+                         d_i + 2 * n, g->d_ret, passes, max_len, s);
+  if (rc != OPUS_OK) return rc;
+  CUDA_OK(cudaMemcpyAsync(pcm, c->d_pcm.p, pcm_bytes, cudaMemcpyDeviceToHost, s));
+  CUDA_OK(cudaMemcpyAsync(ret, g->d_ret, n * sizeof(i32), cudaMemcpyDeviceToHost, s));
+  CUDA_OK(cudaStreamSynchronize(s));
+  return OPUS_OK;
+}
+
+int opus_decode_batch_flat(OpusDecoder* const* st, int n, const unsigned char* data, opus_int32 data_bytes,
+                           const opus_int32* offsets, const opus_int32* len, opus_int16* pcm,
+                           opus_int32 pcm_stride, int frame_size, const int* decode_fec, int* ret) {
+  int err = 0;
+  OpusDecoderGroup* g = opus_decoder_group_create(st, n, &err);
+  if (!g) return err;
+  int rc = opus_decode_group_flat(g, data, data_bytes, offsets, len, pcm, pcm_stride, frame_size, decode_fec, ret);
+  opus_decoder_group_destroy(g);
+  return rc;
+}
+
+int opus_decode_batch(OpusDecoder* const* st, const unsigned char* const* data, const opus_int32* len,
+                      opus_int16* const* pcm, int frame_size, const int* decode_fec, int n, int* ret) {
+  if (!st || !len || !pcm || !ret || n <= 0) return OPUS_BAD_ARG;
+  if (frame_size <= 0) {
+    for (int i = 0; i < n; i++) ret[i] = OPUS_BAD_ARG;
+    return OPUS_OK;
+  }
+  // gather packets into one arena, run the flat path into a temporary PCM arena, scatter back
+  size_t total = 0;
+  int maxch = 1;
+  for (int i = 0; i < n; i++) {
+    if (!st[i] || st[i]->magic != kMagic || !pcm[i]) return OPUS_BAD_ARG;
+    if (data && data[i] && len[i] > 0) total += (size_t)len[i];
+    if (st[i]->channels > maxch) maxch = st[i]->channels;
+  }
+  if (total > 0x7fffffff) return OPUS_BAD_ARG;
+  std::vector<unsigned char> arena(total + 1);
+  std::vector<i32> off(n), ln(n);
+  size_t o = 0;
+  for (int i = 0; i < n; i++) {
+    ln[i] = len[i];
+    if (data && data[i] && len[i] > 0) {
+      memcpy(arena.data() + o, data[i], (size_t)len[i]);
+      off[i] = (i32)o;
+      o += (size_t)len[i];
+    } else {
+      off[i] = -1;
+      if (len[i] > 0) ln[i] = 0;     // data==NULL => lost, whatever len says (opus_decoder.c:613)
+    }
+  }
+  const i32 stride = frame_size * maxch;
+  std::vector<i16> out((size_t)n * stride);
+  int rc = opus_decode_batch_flat(st, n, arena.data(), (i32)total, off.data(), ln.data(), out.data(), stride,
+                                  frame_size, decode_fec, ret);
+  if (rc != OPUS_OK) return rc;
+  for (int i = 0; i < n; i++)
+    if (ret[i] > 0) memcpy(pcm[i], out.data() + (size_t)i * stride, (size_t)ret[i] * st[i]->channels * sizeof(i16));
+  return OPUS_OK;
+}
+
+int opus_decode(OpusDecoder* st, const unsigned char* data, opus_int32 len, opus_int16* pcm, int frame_size,
+                int decode_fec) {
+  if (!st || st->magic != kMagic) return OPUS_BAD_ARG;
+  if (frame_size <= 0) return OPUS_BAD_ARG;
+  if (!pcm) return OPUS_BAD_ARG;
+  if (!st->self_group) {
+    int err = 0;
+    st->self_group = opus_decoder_group_create(&st, 1, &err);
+    if (!st->self_group) return err;
+  }
+  int ret = OPUS_INTERNAL_ERROR;
+  const bool lost = (data == nullptr || len == 0);
+  i32 off = lost ? -1 : 0;
+  i32 ln = lost ? 0 : len;
+  if (ln < 0) return OPUS_BAD_ARG;
+  // decode into a scratch row first: only `ret` samples belong to the caller's buffer
+  std::vector<i16> row((size_t)frame_size * st->channels);
+  int rc = opus_decode_group_flat(st->self_group, lost ? nullptr : data, lost ? 0 : ln, &off, &ln, row.data(),
+                                  frame_size * st->channels, frame_size, &decode_fec, &ret);
+  if (rc != OPUS_OK) return rc;
+  if (ret > 0) memcpy(pcm, row.data(), (size_t)ret * st->channels * sizeof(i16));
+  return ret;
+}
+
+int opus_decode_float(OpusDecoder* st, const unsigned char* data, opus_int32 len, float* pcm, int frame_size,
+                      int decode_fec) {
+  if (!st || st->magic != kMagic || !pcm) return OPUS_BAD_ARG;
+  if (frame_size <= 0) return OPUS_BAD_ARG;
+  if (data != nullptr && len > 0 && !decode_fec) {
+    int nb = opus_decoder_get_nb_samples(st, data, len);
+    if (nb > 0) frame_size = frame_size < nb ? frame_size : nb;
+    else return OPUS_INVALID_PACKET;
+  }
+  std::vector<i16> tmp((size_t)frame_size * st->channels);
+  int ret = opus_decode(st, data, len, tmp.data(), frame_size, decode_fec);
+  if (ret > 0)
+    for (int i = 0; i < ret * st->channels; i++) pcm[i] = (1.f / 32768.f) * tmp[i];
+  return ret;
+}
+
+static int read_state_header(OpusDecoder* st, OpusDecState* hdr_out) {
+  DevCtx* c = &g_ctx[st->device];
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  cudaError_t e = cudaMemcpy(hdr_out, st->d_state, offsetof(OpusDecState, celt) + offsetof(CeltDecState, oldBandE),
+                             cudaMemcpyDeviceToHost);
+  if (e != cudaSuccess) {
+    fprintf(stderr, "[opus_b200] state read failed: %s\n", cudaGetErrorString(e));
+    return OPUS_INTERNAL_ERROR;
+  }
+  return OPUS_OK;
+}
+
+int opus_decoder_ctl(OpusDecoder* st, int request, ...) {
+  if (!st || st->magic != kMagic) return OPUS_BAD_ARG;
+  va_list ap;
+  va_start(ap, request);
+  int ret = OPUS_OK;
+  std::lock_guard<std::mutex> lk(g_mu);
+  static OpusDecState hdr;   // only the leading fields are filled (guarded by g_mu)
+  switch (request) {
+    case OPUS_GET_BANDWIDTH_REQUEST:
+    case OPUS_GET_FINAL_RANGE_REQUEST:
+    case OPUS_GET_PITCH_REQUEST:
+    case OPUS_GET_LAST_PACKET_DURATION_REQUEST: {
+      opus_int32* value = va_arg(ap, opus_int32*);
+      if (!value) { ret = OPUS_BAD_ARG; break; }
+      ret = read_state_header(st, &hdr);
+      if (ret != OPUS_OK) break;
+      if (request == OPUS_GET_BANDWIDTH_REQUEST) *value = hdr.bandwidth;
+      else if (request == OPUS_GET_FINAL_RANGE_REQUEST) *(opus_uint32*)value = hdr.rangeFinal;
+      else if (request == OPUS_GET_LAST_PACKET_DURATION_REQUEST) *value = hdr.last_packet_duration;
+      else *value = hdr.prev_mode == CB_MODE_CELT_ONLY ? hdr.celt.pf_period : 0;
+      break;
+    }
+    case OPUS_GET_SAMPLE_RATE_REQUEST: {
+      opus_int32* value = va_arg(ap, opus_int32*);
+      if (!value) { ret = OPUS_BAD_ARG; break; }
+      *value = st->Fs;
+      break;
+    }
+    case OPUS_GET_GAIN_REQUEST: {
+      opus_int32* value = va_arg(ap, opus_int32*);
+      if (!value) { ret = OPUS_BAD_ARG; break; }
+      *value = st->decode_gain;
+      break;
+    }
+    case OPUS_SET_GAIN_REQUEST: {
+      opus_int32 value = va_arg(ap, opus_int32);
+      if (value < -32768 || value > 32767) { ret = OPUS_BAD_ARG; break; }
+      st->decode_gain = value;
+      DevCtx* c = &g_ctx[st->device];
+      if (c->stream) cudaStreamSynchronize(c->stream);
+      if (cudaMemcpy(&st->d_state->decode_gain, &value, sizeof(i32), cudaMemcpyHostToDevice) != cudaSuccess)
+        ret = OPUS_INTERNAL_ERROR;
+      break;
+    }
+    case OPUS_RESET_STATE: {
+      DevCtx* c = &g_ctx[st->device];
+      if (c->stream) cudaStreamSynchronize(c->stream);
+      ret = upload_fresh_state(st, 1);
+      break;
+    }
+    default:
+      ret = OPUS_UNIMPLEMENTED;
+      break;
+  }
+  va_end(ap);
+  return ret;
+}
+
+int opus_decoder_get_final_range_batch(OpusDecoder* const* st, int n, opus_uint32* out) {
+  if (!st || !out || n <= 0) return OPUS_BAD_ARG;
+  std::lock_guard<std::mutex> lk(g_mu);
+  for (int i = 0; i < n; i++) {
+    if (!st[i] || st[i]->magic != kMagic) return OPUS_BAD_ARG;
+    DevCtx* c = &g_ctx[st[i]->device];
+    if (i == 0 && c->stream) cudaStreamSynchronize(c->stream);
+    CUDA_OK(cudaMemcpy(&out[i], &st[i]->d_state->rangeFinal, sizeof(u32), cudaMemcpyDeviceToHost));
+  }
+  return OPUS_OK;
+}
+
+int opus_b200_synchronize(void) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  int err = 0;
+  DevCtx* c = ctx_for_current_device(&err);
+  if (!c) return err;
+  CUDA_OK(cudaStreamSynchronize(c->stream));
+  return OPUS_OK;
+}
+
+long long opus_b200_launch_count(void) { return g_launches; }
+
+int opus_b200_profile_begin(void) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  g_prof_on = true;
+  return OPUS_OK;
+}
+
+int opus_b200_profile_end(double* ms, long long* counts) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  g_prof_on = false;
+  for (int k = 0; k < 3; k++) { if (ms) ms[k] = 0; if (counts) counts[k] = 0; }
+  cudaDeviceSynchronize();
+  for (auto& r : g_prof) {
+    float t = 0;
+    if (cudaEventElapsedTime(&t, r.a, r.b) == cudaSuccess && r.kind >= 0 && r.kind < 3) {
+      if (ms) ms[r.kind] += t;
+      if (counts) counts[r.kind] += 1;
+    }
+    cudaEventDestroy(r.a);
+    cudaEventDestroy(r.b);
+  }
+  g_prof.clear();
+  return OPUS_OK;
+}
+
+}  // extern "C"

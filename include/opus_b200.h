@@ -1,0 +1,143 @@
+/* opus_b200.h -- C ABI of libopus_b200.so, the B200-native batched Opus engine.
+ *
+ * Two groups of entry points:
+ *
+ *  1. The libopus decoder ABI that Concentus binds by P/Invoke
+ *     (reference: CSharp/Concentus/Native/NativeOpus.cs:85-159; C prototypes
+ *     opus-fix/include/opus.h:208-328,423-512).  Same names, argument meaning, return values and
+ *     error codes, so the shared library can be dropped in as "opus".  A decoder handle owns a
+ *     state slot in GPU memory; opus_decode() is a batch of one.
+ *
+ *  2. Batch entry points (new; SURVEY section 8b "New exports"): n independent streams decoded by
+ *     one call -- semantics are those of n opus_decode() calls, results are bit-identical to the
+ *     reference's fixed-point decoder, and every stream gets its own return code.
+ *
+ * All decoders taking part in one batch call must live on the same CUDA device (the device that
+ * was current when they were created).  Calls on the same decoders must not overlap in time
+ * (same rule as libopus: one state object, one caller).
+ */
+#ifndef OPUS_B200_H
+#define OPUS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef int32_t opus_int32;
+typedef uint32_t opus_uint32;
+typedef int16_t opus_int16;
+
+/* Error codes (opus-fix/include/opus_defines.h:46-60) */
+#define OPUS_OK 0
+#define OPUS_BAD_ARG -1
+#define OPUS_BUFFER_TOO_SMALL -2
+#define OPUS_INTERNAL_ERROR -3
+#define OPUS_INVALID_PACKET -4
+#define OPUS_UNIMPLEMENTED -5
+#define OPUS_INVALID_STATE -6
+#define OPUS_ALLOC_FAIL -7
+
+/* ctl requests understood by opus_decoder_ctl (opus_defines.h:130-167; opus_decoder.c:802-912) */
+#define OPUS_GET_BANDWIDTH_REQUEST 4009
+#define OPUS_RESET_STATE 4028
+#define OPUS_GET_SAMPLE_RATE_REQUEST 4029
+#define OPUS_GET_FINAL_RANGE_REQUEST 4031
+#define OPUS_GET_PITCH_REQUEST 4033
+#define OPUS_SET_GAIN_REQUEST 4034
+#define OPUS_GET_LAST_PACKET_DURATION_REQUEST 4039
+#define OPUS_GET_GAIN_REQUEST 4045
+
+typedef struct OpusDecoder OpusDecoder;
+
+/* ---- libopus ABI ------------------------------------------------------------------------ */
+
+/* replaces opus_get_version_string (celt/celt.c:286-299; NativeOpus.cs:157).  Contains "-fixed". */
+const char *opus_get_version_string(void);
+/* replaces opus_strerror (celt/celt.c:268-284) */
+const char *opus_strerror(int error);
+
+/* replaces opus_decoder_get_size (src/opus_decoder.c:82-94): size of the HOST handle. */
+int opus_decoder_get_size(int channels);
+/* replaces opus_decoder_create (src/opus_decoder.c:139-166; NativeOpus.cs:88). */
+OpusDecoder *opus_decoder_create(opus_int32 Fs, int channels, int *error);
+/* replaces opus_decode (src/opus_decoder.c:713-719; NativeOpus.cs:94): data==NULL or len==0
+ * requests packet-loss concealment. Returns samples per channel or a negative error code. */
+int opus_decode(OpusDecoder *st, const unsigned char *data, opus_int32 len, opus_int16 *pcm,
+                int frame_size, int decode_fec);
+/* replaces opus_decode_float (src/opus_decoder.c:722-753; NativeOpus.cs:97): int16 result / 32768. */
+int opus_decode_float(OpusDecoder *st, const unsigned char *data, opus_int32 len, float *pcm,
+                      int frame_size, int decode_fec);
+/* replaces opus_decoder_ctl (src/opus_decoder.c:789-912; NativeOpus.cs:100-106): one int or int*. */
+int opus_decoder_ctl(OpusDecoder *st, int request, ...);
+/* replaces opus_decoder_destroy (src/opus_decoder.c:914-917; NativeOpus.cs:91). */
+void opus_decoder_destroy(OpusDecoder *st);
+
+/* packet inspection helpers, host side (src/opus_decoder.c:921-981, src/opus.c:169-188,345-352) */
+int opus_packet_get_bandwidth(const unsigned char *data);
+int opus_packet_get_nb_channels(const unsigned char *data);
+int opus_packet_get_nb_frames(const unsigned char packet[], opus_int32 len);
+int opus_packet_get_samples_per_frame(const unsigned char *data, opus_int32 Fs);
+int opus_packet_get_nb_samples(const unsigned char packet[], opus_int32 len, opus_int32 Fs);
+int opus_decoder_get_nb_samples(const OpusDecoder *dec, const unsigned char packet[], opus_int32 len);
+int opus_packet_parse(const unsigned char *data, opus_int32 len, unsigned char *out_toc,
+                      const unsigned char *frames[48], opus_int16 size[48], int *payload_offset);
+
+/* ---- batch ABI (no counterpart in libopus; semantics = n x opus_decode) -------------------- */
+
+/* Pointer-array form.  data[i]==NULL or len[i]==0 => concealment for stream i.
+ * pcm[i] must hold frame_size*channels samples.  decode_fec may be NULL (all 0).
+ * ret[i] receives what opus_decode() would have returned for stream i.
+ * Return value: OPUS_OK if the batch ran (look at ret[] for per-stream results), else an error
+ * that prevented the whole batch (bad arguments, mixed devices, CUDA failure). */
+int opus_decode_batch(OpusDecoder *const *st, const unsigned char *const *data, const opus_int32 *len,
+                      opus_int16 *const *pcm, int frame_size, const int *decode_fec, int n, int *ret);
+
+/* Flat host form: one packet arena in, one PCM arena out (no per-stream host copies).
+ * Packet i occupies data[offsets[i] .. offsets[i]+len[i]); offsets[i] < 0 means "lost".
+ * Stream i's PCM goes to pcm + i*pcm_stride (pcm_stride in int16 units, >= frame_size*channels).
+ * Pinned host buffers make both copies asynchronous DMA. */
+int opus_decode_batch_flat(OpusDecoder *const *st, int n, const unsigned char *data, opus_int32 data_bytes,
+                           const opus_int32 *offsets, const opus_int32 *len, opus_int16 *pcm,
+                           opus_int32 pcm_stride, int frame_size, const int *decode_fec, int *ret);
+
+/* A decoder group pins down a fixed set of decoders (their GPU state pointers are uploaded once and
+ * the per-stream scratch is allocated once), so that repeated batch calls cost no set-up. */
+typedef struct OpusDecoderGroup OpusDecoderGroup;
+OpusDecoderGroup *opus_decoder_group_create(OpusDecoder *const *st, int n, int *error);
+void opus_decoder_group_destroy(OpusDecoderGroup *grp);
+
+/* Flat host form on a group (same meaning as opus_decode_batch_flat). */
+int opus_decode_group_flat(OpusDecoderGroup *grp, const unsigned char *data, opus_int32 data_bytes,
+                           const opus_int32 *offsets, const opus_int32 *len, opus_int16 *pcm,
+                           opus_int32 pcm_stride, int frame_size, const int *decode_fec, int *ret);
+
+/* Device-resident form: every data pointer is a DEVICE pointer on the group's device; nothing is
+ * copied and nothing is synchronised -- the work is queued on `cuda_stream` (a cudaStream_t,
+ * NULL = the library's own stream).  max_frames = upper bound on frames per packet in this batch
+ * (1 for ordinary one-frame packets), max_packet_bytes = upper bound on len[i]. */
+int opus_decode_group_device(OpusDecoderGroup *grp, const unsigned char *d_data,
+                             const opus_int32 *d_offsets, const opus_int32 *d_len, opus_int16 *d_pcm,
+                             opus_int32 pcm_stride, int frame_size, const int *d_decode_fec, int *d_ret,
+                             int max_frames, int max_packet_bytes, void *cuda_stream);
+
+/* Batched OPUS_GET_FINAL_RANGE: out[i] = final range of the last packet decoded by st[i]. */
+int opus_decoder_get_final_range_batch(OpusDecoder *const *st, int n, opus_uint32 *out);
+
+/* Blocks until all work queued by this library on the current device has finished. */
+int opus_b200_synchronize(void);
+/* Number of kernel launches issued by this library so far (process-wide counter). */
+long long opus_b200_launch_count(void);
+
+/* Per-kernel device timing with CUDA events on the launching stream (used by bench.py for the
+ * roofline line).  Between begin and end every kernel launch is bracketed by an event pair;
+ * end synchronises and returns summed milliseconds and launch counts for
+ * [0] plan kernel, [1] entropy kernel, [2] synthesis kernel. */
+int opus_b200_profile_begin(void);
+int opus_b200_profile_end(double ms[3], long long counts[3]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OPUS_B200_H */

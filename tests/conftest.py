@@ -1,0 +1,122 @@
+import ctypes
+import json
+import os
+import struct
+import subprocess
+import sys
+import zlib
+
+import numpy as np
+import pytest
+
+ROOT = os.path.normpath(os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+REF_SO = os.path.join(ROOT, "oracle", "_ref", "libopus_ref.so")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA GPU (run on the B200 box)")
+
+
+def read_bit(path):
+    """opus_demo .bit container: BE32 length, BE32 encoder final range, payload."""
+    d = open(path, "rb").read()
+    o, out = 0, []
+    while o < len(d):
+        ln, rng = struct.unpack(">II", d[o:o + 8])
+        o += 8
+        out.append((d[o:o + ln], rng))
+        o += ln
+    return out
+
+
+def golden_index():
+    return json.load(open(os.path.join(GOLDEN, "index.json")))
+
+
+def golden_case(name):
+    meta = golden_index()[name]
+    return meta, read_bit(os.path.join(GOLDEN, name + ".bit"))
+
+
+def crc32(a):
+    return zlib.crc32(np.ascontiguousarray(a).tobytes()) & 0xFFFFFFFF
+
+
+class RefDecoder(object):
+    """The UNMODIFIED reference decoder (oracle/_ref/libopus_ref.so, built from /root/reference)."""
+
+    _lib = None
+
+    @classmethod
+    def lib(cls):
+        if cls._lib is None:
+            lib = ctypes.CDLL(REF_SO)
+            lib.opus_decoder_create.restype = ctypes.c_void_p
+            lib.opus_decoder_create.argtypes = [ctypes.c_int32, ctypes.c_int, ctypes.POINTER(ctypes.c_int)]
+            lib.opus_decode.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int32, ctypes.c_void_p,
+                                        ctypes.c_int, ctypes.c_int]
+            lib.opus_decoder_destroy.argtypes = [ctypes.c_void_p]
+            lib.opus_decoder_destroy.restype = None
+            cls._lib = lib
+        return cls._lib
+
+    def __init__(self, fs, ch):
+        err = ctypes.c_int(0)
+        self.h = self.lib().opus_decoder_create(fs, ch, ctypes.byref(err))
+        assert self.h and err.value == 0
+        self.ch = ch
+
+    def decode_raw(self, data, frame_size, fec=0):
+        pcm = np.zeros((max(frame_size, 1), self.ch), dtype=np.int16)
+        ret = self.lib().opus_decode(self.h, data, len(data) if data else 0, pcm.ctypes.data, frame_size, fec)
+        return ret, pcm
+
+    @property
+    def final_range(self):
+        v = ctypes.c_uint32(0)
+        self.lib().opus_decoder_ctl(ctypes.c_void_p(self.h), 4031, ctypes.byref(v))
+        return v.value
+
+    def close(self):
+        if self.h:
+            self.lib().opus_decoder_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+
+def have_ref():
+    return os.path.exists(REF_SO)
+
+
+needs_ref = pytest.mark.skipif(not have_ref(), reason="oracle/_ref not built (needs /root/reference; run make -C oracle ref)")
+
+
+@pytest.fixture(scope="session")
+def emu_lib():
+    """Lane-loop emulation of the kernel sources (tests/emu), compiled with g++ on demand."""
+    src = os.path.join(ROOT, "tests", "emu", "emu_celt.cpp")
+    so = os.path.join(ROOT, "tests", "emu", "libemu_celt.so")
+    csrc = os.path.join(ROOT, "concentus_b200", "csrc")
+    newest = max([os.path.getmtime(src)] + [os.path.getmtime(os.path.join(csrc, f)) for f in os.listdir(csrc)])
+    if not os.path.exists(so) or os.path.getmtime(so) < newest:
+        subprocess.run(["g++", "-O2", "-fPIC", "-shared", "-Wall", "-Wno-unused-function", "-o", so, src],
+                       check=True)
+    lib = ctypes.CDLL(so)
+    lib.emu_celt_create.restype = ctypes.c_void_p
+    lib.emu_celt_create.argtypes = [ctypes.c_int, ctypes.c_int]
+    lib.emu_celt_destroy.argtypes = [ctypes.c_void_p]
+    lib.emu_celt_decode.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                    ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+    return lib
+
+
+def cuda_available():
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False

@@ -5,11 +5,11 @@
 #define CB_HOST_EMU 1
 #include <stdlib.h>
 #include <string.h>
-#include "../../concentus_b200/csrc/cb_celt_entropy.h"
-#include "../../concentus_b200/csrc/cb_celt_synth.h"
+#include "../../concentus_b200/csrc/cb_decode_pass.h"
 
 extern "C" {
 
+// ---- CELT layer only (payload without TOC) ----
 void* emu_celt_create(int channels, int downsample) {
   CeltDecState* s = (CeltDecState*)malloc(sizeof(CeltDecState));
   celt_state_reset(s, channels, downsample);
@@ -17,7 +17,6 @@ void* emu_celt_create(int channels, int downsample) {
 }
 void emu_celt_destroy(void* s) { free(s); }
 
-// Decode one CELT frame (payload without TOC).  Returns samples per channel or <0.
 int emu_celt_decode(void* state, const unsigned char* payload, int len, int LM, int C, int start, int end,
                     short* pcm, unsigned* final_range) {
   CeltDecState* st = (CeltDecState*)state;
@@ -29,6 +28,34 @@ int emu_celt_decode(void* state, const unsigned char* payload, int len, int LM, 
   if (rc < 0) return rc;
   for (int c = 0; c < st->channels; c++) celt_synth_channel(sw, st, &side, c, pcm);
   return (120 << LM) / st->downsample;
+}
+
+// ---- Opus layer: the same plan/pass sequence the CUDA launchers run, for one stream ----
+void* emu_opus_create(int Fs, int channels) {
+  OpusDecState* s = (OpusDecState*)malloc(sizeof(OpusDecState));
+  s->decode_gain = 0;
+  opus_state_reset(s, Fs, channels, 0);
+  return s;
+}
+void emu_opus_destroy(void* s) { free(s); }
+unsigned emu_opus_final_range(void* s) { return ((OpusDecState*)s)->rangeFinal; }
+int emu_opus_last_packet_duration(void* s) { return ((OpusDecState*)s)->last_packet_duration; }
+
+int emu_opus_decode(void* state, const unsigned char* data, int len, short* pcm, int frame_size, int fec) {
+  OpusDecState* st = (OpusDecState*)state;
+  static EntWork ew;
+  static SynWork sw;
+  static FrameSide side;
+  static unsigned char pkt[1600];
+  StreamPlan pl;
+  i32 ret = 0;
+  opus_plan_stream(st, &pl, data, data ? 0 : -1, data ? len : 0, frame_size, fec, 0, nullptr);
+  ret = pl.ret;
+  for (int pass = 0; pass < pl.nframes; pass++) {
+    decode_entropy_pass(ew, pkt, st, &pl, &side, data, &ret, pass);
+    for (int c = 0; c < st->channels; c++) decode_synth_pass(sw, st, &pl, &side, pcm, c, pass);
+  }
+  return ret;
 }
 
 }  // extern "C"
