@@ -59,6 +59,7 @@ struct alignas(16) EntWork {
   i8 tf_res[CB_NBANDS];
   u8 collapse[2 * CB_NBANDS];
   PartFrame stack[5];
+  RangeDec rd;                   // coder registers; in shared memory so the rd_* routines can be real calls
 };
 
 struct BandCtx {
@@ -76,7 +77,7 @@ CB_FN int bits2pulses(int band, int LM, int bits) {
   const u8* cache = pulse_cache(band, LM);
   int lo = 0, hi = cache[0];
   bits--;
-  for (int it = 0; it < 6; it++) {   // LOG_MAX_PSEUDO
+  CB_NOUNROLL for (int it = 0; it < 6; it++) {   // LOG_MAX_PSEUDO
     int mid = (lo + hi + 1) >> 1;
     if ((int)cache[mid] >= bits) hi = mid; else lo = mid;
   }
@@ -93,11 +94,12 @@ CB_FN u32 pvq_u(int n, int k) {   // CELT_PVQ_U (cwrs.c:196)
 
 // ---- lane-parallel vector helpers -----------------------------------------------------------
 // haar1 (bands.c:581-594): independent butterflies
-CB_FN void v_haar1(i16* X, int N0, int stride) {
+CB_FN_NOINLINE void v_haar1(i16* X, int N0, int stride) {
   N0 >>= 1;
+  const int sh = 31 - cb_clz((u32)stride);   // stride is a power of two
   CB_WSYNC();
   CB_LANE_LOOP(p, N0 * stride) {
-    int i = p % stride, j = p / stride;
+    int i = p & (stride - 1), j = p >> sh;
     int a = stride * 2 * j + i, b = stride * (2 * j + 1) + i;
     i32 t1 = mult16_16(23170, X[a]);
     i32 t2 = mult16_16(23170, X[b]);
@@ -109,9 +111,10 @@ CB_FN void v_haar1(i16* X, int N0, int stride) {
 // deinterleave_hadamard / interleave_hadamard (bands.c:532-579), via the i16 temp
 CB_FN void v_deinterleave(i16* X, i16* tmp, int N0, int stride, int hadamard) {
   int N = N0 * stride;
+  const int sh = 31 - cb_clz((u32)stride);     // stride is a power of two
   CB_WSYNC();
   CB_LANE_LOOP(p, N) {
-    int i = p % stride, j = p / stride;        // source index p = j*stride+i
+    int i = p & (stride - 1), j = p >> sh;     // source index p = j*stride+i
     int row = hadamard ? ct_ordery[stride - 2 + i] : i;
     tmp[row * N0 + j] = X[p];
   }
@@ -121,9 +124,10 @@ CB_FN void v_deinterleave(i16* X, i16* tmp, int N0, int stride, int hadamard) {
 }
 CB_FN void v_interleave(i16* X, i16* tmp, int N0, int stride, int hadamard) {
   int N = N0 * stride;
+  const int sh = 31 - cb_clz((u32)stride);     // stride is a power of two
   CB_WSYNC();
   CB_LANE_LOOP(p, N) {
-    int i = p % stride, j = p / stride;        // destination index p = j*stride+i
+    int i = p & (stride - 1), j = p >> sh;     // destination index p = j*stride+i
     int row = hadamard ? ct_ordery[stride - 2 + i] : i;
     tmp[p] = X[row * N0 + j];
   }
@@ -132,7 +136,7 @@ CB_FN void v_interleave(i16* X, i16* tmp, int N0, int stride, int hadamard) {
   CB_WSYNC();
 }
 // renormalise_vector (vq.c:349-374)
-CB_FN void v_renormalise(i16* X, int N, i32 gain) {
+CB_FN_NOINLINE void v_renormalise(i16* X, int N, i32 gain) {
   CB_WSYNC();
   i32 acc = 0;
   CB_LANE_LOOP(j, N) acc = mac16_16(acc, X[j], X[j]);
@@ -145,13 +149,13 @@ CB_FN void v_renormalise(i16* X, int N, i32 gain) {
 }
 // one pass of exp_rotation1 (vq.c:43-67) over `nblocks` blocks of `len` samples; the `st`
 // residue classes of a block are independent recurrences, so each lane owns whole chains.
-CB_FN void v_rot_pass(i16* X, int nblocks, int len, int st, i32 c, i32 s) {
+CB_FN_NOINLINE void v_rot_pass(i16* X, int nblocks, int len, int st, i32 c, i32 s) {
   i32 ms = (i16)(-s);
   CB_WSYNC();
   CB_LANE_LOOP(ch, nblocks * st) {
     i16* x = X + (ch / st) * len;
     int r = ch % st;
-    for (int i = r; i < len - st; i += st) {
+    CB_NOUNROLL for (int i = r; i < len - st; i += st) {
       i32 x1 = x[i], x2 = x[i + st];
       x[i + st] = ext16(pshr32(mac16_16(mult16_16(c, x2), s, x1), 15));
       x[i] = ext16(pshr32(mac16_16(mult16_16(c, x1), ms, x2), 15));
@@ -159,7 +163,7 @@ CB_FN void v_rot_pass(i16* X, int nblocks, int len, int st, i32 c, i32 s) {
     int last = len - 2 * st - 1;
     if (last >= r) {
       int i0 = last - ((last - r) % st);
-      for (int i = i0; i >= 0; i -= st) {
+      CB_NOUNROLL for (int i = i0; i >= 0; i -= st) {
         i32 x1 = x[i], x2 = x[i + st];
         x[i + st] = ext16(pshr32(mac16_16(mult16_16(c, x2), s, x1), 15));
         x[i] = ext16(pshr32(mac16_16(mult16_16(c, x1), ms, x2), 15));
@@ -179,7 +183,7 @@ CB_FN void v_exp_rotation_dec(i16* X, int len, int stride, int K, int spread) {
   int stride2 = 0;
   if (len >= 8 * stride) {
     stride2 = 1;
-    while ((stride2 * stride2 + stride2) * stride + (stride >> 2) < len) stride2++;
+    CB_NOUNROLL while ((stride2 * stride2 + stride2) * stride + (stride >> 2) < len) stride2++;
   }
   len = len / stride;
   if (stride2) v_rot_pass(X, stride, len, stride2, s, c);
@@ -192,7 +196,7 @@ CB_FN i32 pvq_decode(i16* y, int n, int k, u32 i) {
   u32 p, q;
   int s, k0;
   i16 val;
-  while (n > 2) {
+  CB_NOUNROLL while (n > 2) {
     if (k >= n) {
       int rowoff = ct_pvq_u_row[n];
       p = ct_pvq_u_data[rowoff + k + 1];
@@ -202,9 +206,9 @@ CB_FN i32 pvq_decode(i16* y, int n, int k, u32 i) {
       q = ct_pvq_u_data[rowoff + n];
       if (q > i) {
         k = n;
-        do p = ct_pvq_u_data[ct_pvq_u_row[--k] + n]; while (p > i);
+        CB_NOUNROLL do p = ct_pvq_u_data[ct_pvq_u_row[--k] + n]; while (p > i);
       } else {
-        for (p = ct_pvq_u_data[rowoff + k]; p > i; p = ct_pvq_u_data[rowoff + k]) k--;
+        CB_NOUNROLL for (p = ct_pvq_u_data[rowoff + k]; p > i; p = ct_pvq_u_data[rowoff + k]) k--;
       }
       i -= p;
       val = (i16)((k0 - k + s) ^ s);
@@ -220,7 +224,7 @@ CB_FN i32 pvq_decode(i16* y, int n, int k, u32 i) {
         s = -(int)(i >= q);
         i -= q & (u32)s;
         k0 = k;
-        do p = ct_pvq_u_data[ct_pvq_u_row[--k] + n]; while (p > i);
+        CB_NOUNROLL do p = ct_pvq_u_data[ct_pvq_u_row[--k] + n]; while (p > i);
         i -= p;
         val = (i16)((k0 - k + s) ^ s);
         *y++ = val;
@@ -368,7 +372,7 @@ CB_FN u32 part_leaf(EntWork& w, BandCtx& cx, RangeDec& rd, i16* X, int N, int b,
   int q = bits2pulses(cx.i, LM, b);
   int curr_bits = pulses2bits(cx.i, LM, q);
   cx.remaining_bits -= curr_bits;
-  while (cx.remaining_bits < 0 && q > 0) {
+  CB_NOUNROLL while (cx.remaining_bits < 0 && q > 0) {
     cx.remaining_bits += curr_bits;
     q--;
     curr_bits = pulses2bits(cx.i, LM, q);
@@ -411,7 +415,7 @@ CB_FN u32 dec_partition(EntWork& w, BandCtx& cx, RangeDec& rd, i16* X0, int N0, 
   st[0].X = X0; st[0].lowband = lowband0; st[0].N = N0; st[0].b = b0; st[0].B = B_0;
   st[0].LM = LM0; st[0].gain = gain0; st[0].fill = fill0; st[0].stage = 0;
   u32 ret = 0;
-  while (sp >= 0) {
+  CB_NOUNROLL while (sp >= 0) {
     PartFrame& f = st[sp];
     if (f.stage == 0) {
       int N = f.N, b = f.b, B = f.B, LM = f.LM, fill = f.fill;
@@ -485,7 +489,7 @@ CB_FN u32 dec_partition(EntWork& w, BandCtx& cx, RangeDec& rd, i16* X0, int N0, 
 CB_FN u32 dec_band_n1(BandCtx& cx, RangeDec& rd, i16* X, i16* Y, i16* lowband_out) {
   i16* x = X;
   int nch = Y ? 2 : 1;
-  for (int c = 0; c < nch; c++) {
+  CB_NOUNROLL for (int c = 0; c < nch; c++) {
     int sign = 0;
     if (cx.remaining_bits >= 1 << CB_BITRES) {
       sign = (int)rd_bits(rd, 1);
@@ -514,13 +518,13 @@ CB_FN u32 dec_band(EntWork& w, BandCtx& cx, RangeDec& rd, i16* X, int N, int b, 
     CB_WSYNC();
     lowband = lowband_scratch;
   }
-  for (int k = 0; k < recombine; k++) {
+  CB_NOUNROLL for (int k = 0; k < recombine; k++) {
     if (lowband) v_haar1(lowband, N >> k, 1 << k);
     fill = ct_bit_interleave[fill & 0xF] | ct_bit_interleave[fill >> 4] << 2;
   }
   B >>= recombine;
   N_B <<= recombine;
-  while ((N_B & 1) == 0 && tf_change < 0) {
+  CB_NOUNROLL while ((N_B & 1) == 0 && tf_change < 0) {
     if (lowband) v_haar1(lowband, N_B, B);
     fill |= fill << B;
     B <<= 1;
@@ -537,13 +541,13 @@ CB_FN u32 dec_band(EntWork& w, BandCtx& cx, RangeDec& rd, i16* X, int N, int b, 
   if (B0 > 1) v_interleave(X, tmp, N_B >> recombine, B0 << recombine, longBlocks);
   N_B = N_B0;
   B = B0;
-  for (int k = 0; k < time_divide; k++) {
+  CB_NOUNROLL for (int k = 0; k < time_divide; k++) {
     B >>= 1;
     N_B <<= 1;
     cm |= cm >> B;
     v_haar1(X, N_B, B);
   }
-  for (int k = 0; k < recombine; k++) {
+  CB_NOUNROLL for (int k = 0; k < recombine; k++) {
     cm = ct_bit_deinterleave[cm];
     v_haar1(X, N0 >> k, 1 << k);
   }
@@ -591,68 +595,12 @@ CB_FN void v_stereo_merge(i16* X, i16* Y, i32 mid, int N) {
   CB_WSYNC();
 }
 
-// quant_band_stereo (bands.c:1176-1334), decoder side
-CB_FN u32 dec_band_stereo(EntWork& w, BandCtx& cx, RangeDec& rd, i16* X, i16* Y, int N, int b, int B,
-                          i16* lowband, int LM, i16* lowband_out, i16* lowband_scratch, int fill) {
-  if (N == 1) return dec_band_n1(cx, rd, X, Y, lowband_out);
-  int orig_fill = fill;
-  Split s;
-  dec_theta(cx, rd, s, N, b, B, B, LM, 1, fill);
-  i32 mid = s.imid, side = s.iside;
-  int itheta = s.itheta, delta = s.delta;
-  u32 cm;
-  if (N == 2) {
-    int mbits = b, sbits = 0;
-    if (itheta != 0 && itheta != 16384) sbits = 1 << CB_BITRES;
-    mbits -= sbits;
-    int c = itheta > 8192;
-    cx.remaining_bits -= s.qalloc + sbits;
-    i16* x2 = c ? Y : X;
-    i16* y2 = c ? X : Y;
-    int sign = 0;
-    if (sbits) sign = (int)rd_bits(rd, 1);
-    sign = 1 - 2 * sign;
-    cm = dec_band(w, cx, rd, x2, N, mbits, B, lowband, LM, lowband_out, CB_Q15ONE, lowband_scratch, orig_fill);
-    CB_WSYNC();
-    y2[0] = (i16)(-sign * x2[1]);
-    y2[1] = (i16)(sign * x2[0]);
-    i16 X0 = (i16)mult16_16_q15(mid, X[0]);
-    i16 X1 = (i16)mult16_16_q15(mid, X[1]);
-    i16 Y0 = (i16)mult16_16_q15(side, Y[0]);
-    i16 Y1 = (i16)mult16_16_q15(side, Y[1]);
-    CB_WSYNC();
-    X[0] = (i16)sub16(X0, Y0);
-    Y[0] = add16(X0, Y0);
-    X[1] = (i16)sub16(X1, Y1);
-    Y[1] = add16(X1, Y1);
-    CB_WSYNC();
-  } else {
-    int mbits = cb_imax(0, cb_imin(b, (b - delta) / 2));
-    int sbits = b - mbits;
-    cx.remaining_bits -= s.qalloc;
-    i32 rebalance = cx.remaining_bits;
-    if (mbits >= sbits) {
-      cm = dec_band(w, cx, rd, X, N, mbits, B, lowband, LM, lowband_out, CB_Q15ONE, lowband_scratch, fill);
-      rebalance = mbits - (rebalance - cx.remaining_bits);
-      if (rebalance > 3 << CB_BITRES && itheta != 0) sbits += rebalance - (3 << CB_BITRES);
-      cm |= dec_band(w, cx, rd, Y, N, sbits, B, nullptr, LM, nullptr, side, nullptr, fill >> B);
-    } else {
-      cm = dec_band(w, cx, rd, Y, N, sbits, B, nullptr, LM, nullptr, side, nullptr, fill >> B);
-      rebalance = sbits - (rebalance - cx.remaining_bits);
-      if (rebalance > 3 << CB_BITRES && itheta != 16384) mbits += rebalance - (3 << CB_BITRES);
-      cm |= dec_band(w, cx, rd, X, N, mbits, B, lowband, LM, lowband_out, CB_Q15ONE, lowband_scratch, fill);
-    }
-  }
-  if (N != 2) v_stereo_merge(X, Y, mid, N);
-  if (s.inv) {
-    CB_WSYNC();
-    CB_LANE_LOOP(j, N) Y[j] = (i16)(-Y[j]);
-    CB_WSYNC();
-  }
-  return cm;
-}
+// One call of quant_band() as data, so that the (large) band decoder is instantiated at exactly
+// one call site: instruction-cache footprint is what bounds this kernel (see profiles/).
+struct BandJob { i16* X; i16* lowband; i16* lowband_out; i16* scratch; i32 b, gain, fill; };
 
-// quant_all_bands (bands.c:1337-1502), decoder side.  Xc = channel-0 spectrum, channel stride = N.
+// quant_all_bands (bands.c:1337-1502) with quant_band_stereo (bands.c:1176-1334) folded in as a
+// small job list per band.  Decoder side.  Xc = channel-0 spectrum, channel stride = N.
 CB_FN void dec_all_bands(EntWork& w, RangeDec& rd, int start, int end, int C, int Nfrm, int shortBlocks,
                          int spread, int dual_stereo, int intensity, i32 total_bits, i32 balance,
                          int LM, int codedBands, u32& seed) {
@@ -670,7 +618,7 @@ CB_FN void dec_all_bands(EntWork& w, RangeDec& rd, int start, int end, int C, in
   cx.intensity = intensity;
   cx.seed = seed;
   cx.spread = spread;
-  for (int i = start; i < end; i++) {
+  CB_NOUNROLL for (int i = start; i < end; i++) {
     cx.i = i;
     int last = (i == end - 1);
     i16* X = X_ + M * ebands(i);
@@ -696,12 +644,12 @@ CB_FN void dec_all_bands(EntWork& w, RangeDec& rd, int start, int end, int C, in
     if (lowband_offset != 0 && (spread != CB_SPREAD_AGGRESSIVE || B > 1 || tf_change < 0)) {
       effective_lowband = cb_imax(0, M * ebands(lowband_offset) - norm_offset - N);
       int fold_start = lowband_offset;
-      while (M * ebands(--fold_start) > effective_lowband + norm_offset) {}
+      CB_NOUNROLL while (M * ebands(--fold_start) > effective_lowband + norm_offset) {}
       int fold_end = lowband_offset - 1;
-      while (M * ebands(++fold_end) < effective_lowband + norm_offset + N) {}
+      CB_NOUNROLL while (M * ebands(++fold_end) < effective_lowband + norm_offset + N) {}
       x_cm = y_cm = 0;
       int fold_i = fold_start;
-      do {
+      CB_NOUNROLL do {
         x_cm |= w.collapse[fold_i * C + 0];
         y_cm |= w.collapse[fold_i * C + C - 1];
       } while (++fold_i < fold_end);
@@ -719,15 +667,114 @@ CB_FN void dec_all_bands(EntWork& w, RangeDec& rd, int start, int end, int C, in
     i16* lb2 = effective_lowband != -1 ? norm2 + effective_lowband : nullptr;
     i16* lout = last ? nullptr : norm + M * ebands(i) - norm_offset;
     i16* lout2 = last ? nullptr : norm2 + M * ebands(i) - norm_offset;
+
+    // ---- build the job list for this band ----
+    BandJob J0, J1;
+    int njobs = 0;
+    int mode;                       // 0 mono, 1 dual stereo, 2 joint stereo N>2, 3 joint stereo N==2, 4 done
+    Split s;
+    s.inv = 0; s.itheta = 0; s.imid = 0; s.iside = 0; s.delta = 0; s.qalloc = 0;
+    int mbits = 0, sbits = 0, mid_first = 1, n2_swap = 0, n2_sign = 1;
+    i32 rebalance0 = 0;
+    u32 cm = 0;
     if (dual_stereo) {
-      x_cm = dec_band(w, cx, rd, X, N, b / 2, B, lb, LM, lout, CB_Q15ONE, lowband_scratch, (int)x_cm);
-      y_cm = dec_band(w, cx, rd, Y, N, b / 2, B, lb2, LM, lout2, CB_Q15ONE, lowband_scratch, (int)y_cm);
+      mode = 1;
+      J0.X = X; J0.lowband = lb; J0.lowband_out = lout; J0.scratch = lowband_scratch; J0.b = b / 2; J0.gain = CB_Q15ONE; J0.fill = (i32)x_cm;
+      J1.X = Y; J1.lowband = lb2; J1.lowband_out = lout2; J1.scratch = lowband_scratch; J1.b = b / 2; J1.gain = CB_Q15ONE; J1.fill = (i32)y_cm;
+      njobs = 2;
+    } else if (Y == nullptr) {
+      mode = 0;
+      J0.X = X; J0.lowband = lb; J0.lowband_out = lout; J0.scratch = lowband_scratch; J0.b = b; J0.gain = CB_Q15ONE; J0.fill = (i32)(x_cm | y_cm);
+      J1 = J0;
+      njobs = 1;
+    } else if (N == 1) {
+      mode = 4;
+      cm = dec_band_n1(cx, rd, X, Y, lout);
+      J0.X = X; J0.lowband = nullptr; J0.lowband_out = nullptr; J0.scratch = nullptr; J0.b = 0; J0.gain = 0; J0.fill = 0;
+      J1 = J0;
     } else {
-      if (Y != nullptr)
-        x_cm = dec_band_stereo(w, cx, rd, X, Y, N, b, B, lb, LM, lout, lowband_scratch, (int)(x_cm | y_cm));
-      else
-        x_cm = dec_band(w, cx, rd, X, N, b, B, lb, LM, lout, CB_Q15ONE, lowband_scratch, (int)(x_cm | y_cm));
-      y_cm = x_cm;
+      int fill = (int)(x_cm | y_cm);
+      const int orig_fill = fill;
+      int bb = b;
+      dec_theta(cx, rd, s, N, bb, B, B, LM, 1, fill);
+      if (N == 2) {
+        mode = 3;
+        mbits = bb;
+        sbits = 0;
+        if (s.itheta != 0 && s.itheta != 16384) sbits = 1 << CB_BITRES;
+        mbits -= sbits;
+        n2_swap = s.itheta > 8192;
+        cx.remaining_bits -= s.qalloc + sbits;
+        int sign = 0;
+        if (sbits) sign = (int)rd_bits(rd, 1);
+        n2_sign = 1 - 2 * sign;
+        J0.X = n2_swap ? Y : X; J0.lowband = lb; J0.lowband_out = lout; J0.scratch = lowband_scratch;
+        J0.b = mbits; J0.gain = CB_Q15ONE; J0.fill = orig_fill;
+        J1 = J0;
+        njobs = 1;
+      } else {
+        mode = 2;
+        mbits = cb_imax(0, cb_imin(bb, (bb - s.delta) / 2));
+        sbits = bb - mbits;
+        cx.remaining_bits -= s.qalloc;
+        rebalance0 = cx.remaining_bits;
+        mid_first = mbits >= sbits;
+        BandJob Jm, Js;
+        Jm.X = X; Jm.lowband = lb; Jm.lowband_out = lout; Jm.scratch = lowband_scratch; Jm.b = mbits; Jm.gain = CB_Q15ONE; Jm.fill = fill;
+        Js.X = Y; Js.lowband = nullptr; Js.lowband_out = nullptr; Js.scratch = nullptr; Js.b = sbits; Js.gain = s.iside; Js.fill = fill >> B;
+        if (mid_first) { J0 = Jm; J1 = Js; } else { J0 = Js; J1 = Jm; }
+        njobs = 2;
+      }
+    }
+    // ---- run the jobs: the one and only call site of dec_band ----
+    u32 cm0 = 0, cm1 = 0;
+    CB_NOUNROLL for (int jn = 0; jn < njobs; jn++) {
+      BandJob J = jn == 0 ? J0 : J1;
+      if (mode == 2 && jn == 1) {
+        i32 first_bits = mid_first ? mbits : sbits;
+        i32 rebalance = first_bits - (rebalance0 - cx.remaining_bits);
+        int blocked = mid_first ? (s.itheta == 0) : (s.itheta == 16384);
+        if (rebalance > 3 << CB_BITRES && !blocked) J.b += rebalance - (3 << CB_BITRES);
+      }
+      u32 r = dec_band(w, cx, rd, J.X, N, J.b, B, J.lowband, LM, J.lowband_out, J.gain, J.scratch, J.fill);
+      if (jn == 0) cm0 = r; else cm1 = r;
+    }
+    // ---- per-mode epilogue ----
+    if (mode == 0) {
+      x_cm = y_cm = cm0;
+    } else if (mode == 1) {
+      x_cm = cm0;
+      y_cm = cm1;
+    } else if (mode == 4) {
+      x_cm = y_cm = cm;
+    } else {
+      if (mode == 3) {
+        i16* x2 = n2_swap ? Y : X;
+        i16* y2 = n2_swap ? X : Y;
+        CB_WSYNC();
+        y2[0] = (i16)(-n2_sign * x2[1]);
+        y2[1] = (i16)(n2_sign * x2[0]);
+        i16 X0 = (i16)mult16_16_q15(s.imid, X[0]);
+        i16 X1 = (i16)mult16_16_q15(s.imid, X[1]);
+        i16 Y0 = (i16)mult16_16_q15(s.iside, Y[0]);
+        i16 Y1 = (i16)mult16_16_q15(s.iside, Y[1]);
+        CB_WSYNC();
+        X[0] = (i16)sub16(X0, Y0);
+        Y[0] = add16(X0, Y0);
+        X[1] = (i16)sub16(X1, Y1);
+        Y[1] = add16(X1, Y1);
+        CB_WSYNC();
+        cm = cm0;
+      } else {
+        cm = cm0 | cm1;
+        v_stereo_merge(X, Y, s.imid, N);
+      }
+      if (s.inv) {
+        CB_WSYNC();
+        CB_LANE_LOOP(j, N) Y[j] = (i16)(-Y[j]);
+        CB_WSYNC();
+      }
+      x_cm = y_cm = cm;
     }
     w.collapse[i * C + 0] = (u8)x_cm;
     w.collapse[i * C + C - 1] = (u8)y_cm;
@@ -740,7 +787,7 @@ CB_FN void dec_all_bands(EntWork& w, RangeDec& rd, int start, int end, int C, in
 // anti_collapse (bands.c:241-335)
 CB_FN void v_anti_collapse(EntWork& w, int LM, int C, int Nfrm, int start, int end, const i16* logE,
                            const i16* prev1logE, const i16* prev2logE, u32 seed) {
-  for (int i = start; i < end; i++) {
+  CB_NOUNROLL for (int i = start; i < end; i++) {
     int N0 = ebands(i + 1) - ebands(i);
     int depth = (int)((u32)(1 + w.pulses[i]) / (u32)N0) >> LM;
     i32 thresh32 = cb_exp2(-(i32)shl16(depth, 10 - CB_BITRES)) >> 1;
@@ -749,7 +796,7 @@ CB_FN void v_anti_collapse(EntWork& w, int LM, int C, int Nfrm, int start, int e
     int shift = cb_ilog2(t) >> 1;
     t = shl32(t, (7 - shift) << 1);
     i16 sqrt_1 = cb_rsqrt_norm(t);
-    for (int c = 0; c < C; c++) {
+    CB_NOUNROLL for (int c = 0; c < C; c++) {
       i32 prev1 = prev1logE[c * CB_NBANDS + i];
       i32 prev2 = prev2logE[c * CB_NBANDS + i];
       if (C == 1) {
@@ -770,7 +817,7 @@ CB_FN void v_anti_collapse(EntWork& w, int LM, int C, int Nfrm, int start, int e
       r = (i16)(mult16_16_q15(sqrt_1, r) >> shift);
       i16* X = w.X + c * Nfrm + (ebands(i) << LM);
       int renormalize = 0;
-      for (int k = 0; k < (1 << LM); k++) {
+      CB_NOUNROLL for (int k = 0; k < (1 << LM); k++) {
         if (!(w.collapse[i * C + c] & (1 << k))) {
           u32 seed0 = seed;
           CB_WSYNC();
@@ -795,8 +842,8 @@ CB_FN void dec_coarse_energy(EntWork& w, RangeDec& rd, int start, int end, int i
   if (intra) { coef = 0; beta = 4915; }
   else { beta = ct_beta_coef[LM]; coef = ct_pred_coef[LM]; }
   i32 budget = (i32)rd.storage * 8;
-  for (int i = start; i < end; i++) {
-    for (int c = 0; c < C; c++) {
+  CB_NOUNROLL for (int i = start; i < end; i++) {
+    CB_NOUNROLL for (int c = 0; c < C; c++) {
       int qi;
       i32 tell = rd_tell(rd);
       if (budget - tell >= 15) {
@@ -821,10 +868,10 @@ CB_FN void dec_coarse_energy(EntWork& w, RangeDec& rd, int start, int end, int i
   }
 }
 CB_FN void dec_fine_energy(EntWork& w, RangeDec& rd, int start, int end, int C) {
-  for (int i = start; i < end; i++) {
+  CB_NOUNROLL for (int i = start; i < end; i++) {
     int fq = w.fine_quant[i];
     if (fq <= 0) continue;
-    for (int c = 0; c < C; c++) {
+    CB_NOUNROLL for (int c = 0; c < C; c++) {
       i32 q2 = (i32)rd_bits(rd, (u32)fq);
       i32 offset = sub16((add32(shl32(q2, CB_DB_SHIFT), 512)) >> fq, 512);
       w.bandE[i + c * CB_NBANDS] = (i16)(w.bandE[i + c * CB_NBANDS] + (i16)offset);
@@ -832,10 +879,10 @@ CB_FN void dec_fine_energy(EntWork& w, RangeDec& rd, int start, int end, int C) 
   }
 }
 CB_FN void dec_energy_finalise(EntWork& w, RangeDec& rd, int start, int end, int bits_left, int C) {
-  for (int prio = 0; prio < 2; prio++) {
-    for (int i = start; i < end && bits_left >= C; i++) {
+  CB_NOUNROLL for (int prio = 0; prio < 2; prio++) {
+    CB_NOUNROLL for (int i = start; i < end && bits_left >= C; i++) {
       if (w.fine_quant[i] >= CB_MAX_FINE_BITS || w.fine_prio[i] != prio) continue;
-      for (int c = 0; c < C; c++) {
+      CB_NOUNROLL for (int c = 0; c < C; c++) {
         i32 q2 = (i32)rd_bits(rd, 1);
         i32 offset = ((i32)shl16(q2, CB_DB_SHIFT) - 512) >> (w.fine_quant[i] + 1);
         w.bandE[i + c * CB_NBANDS] = (i16)(w.bandE[i + c * CB_NBANDS] + (i16)offset);
@@ -853,7 +900,7 @@ CB_FN void dec_tf(EntWork& w, RangeDec& rd, int start, int end, int isTransient,
   int tf_select_rsv = LM > 0 && tell + logp + 1 <= budget;
   budget -= tf_select_rsv;
   int tf_changed = 0, curr = 0;
-  for (int i = start; i < end; i++) {
+  CB_NOUNROLL for (int i = start; i < end; i++) {
     if (tell + logp <= budget) {
       curr ^= rd_bit_logp(rd, (u32)logp);
       tell = (u32)rd_tell(rd);
@@ -865,7 +912,7 @@ CB_FN void dec_tf(EntWork& w, RangeDec& rd, int start, int end, int isTransient,
   int tf_select = 0;
   if (tf_select_rsv && ct_tf_select[LM][4 * isTransient + 0 + tf_changed] != ct_tf_select[LM][4 * isTransient + 2 + tf_changed])
     tf_select = rd_bit_logp(rd, 1);
-  for (int i = start; i < end; i++)
+  CB_NOUNROLL for (int i = start; i < end; i++)
     w.tf_res[i] = ct_tf_select[LM][4 * isTransient + 2 * tf_select + w.tf_res[i]];
 }
 
@@ -891,17 +938,17 @@ CB_FN int dec_allocation(EntWork& w, RangeDec& rd, int start, int end, int alloc
       total -= dual_stereo_rsv;
     }
   }
-  for (int j = start; j < end; j++) {
+  CB_NOUNROLL for (int j = start; j < end; j++) {
     int wdt = ebands(j + 1) - ebands(j);
     thresh[j] = cb_imax(C << CB_BITRES, (3 * wdt << LM << CB_BITRES) >> 4);
     trim_offset[j] = C * wdt * (alloc_trim - 5 - LM) * (end - j - 1) * (1 << (LM + CB_BITRES)) >> 6;
     if (wdt << LM == 1) trim_offset[j] -= C << CB_BITRES;
   }
   int lo = 1, hi = 11 - 1;                    // nbAllocVectors = 11
-  do {
+  CB_NOUNROLL do {
     int done = 0, psum = 0;
     int mid = (lo + hi) >> 1;
-    for (int j = end; j-- > start;) {
+    CB_NOUNROLL for (int j = end; j-- > start;) {
       int wdt = ebands(j + 1) - ebands(j);
       int bitsj = C * wdt * ct_band_alloc[mid * CB_NBANDS + j] << LM >> 2;
       if (bitsj > 0) bitsj = cb_imax(0, bitsj + trim_offset[j]);
@@ -916,7 +963,7 @@ CB_FN int dec_allocation(EntWork& w, RangeDec& rd, int start, int end, int alloc
     if (psum > total) hi = mid - 1; else lo = mid + 1;
   } while (lo <= hi);
   hi = lo--;
-  for (int j = start; j < end; j++) {
+  CB_NOUNROLL for (int j = start; j < end; j++) {
     int wdt = ebands(j + 1) - ebands(j);
     int bits1j = C * wdt * ct_band_alloc[lo * CB_NBANDS + j] << LM >> 2;
     int bits2j = hi >= 11 ? w.cap[j] : C * wdt * ct_band_alloc[hi * CB_NBANDS + j] << LM >> 2;
@@ -936,11 +983,11 @@ CB_FN int dec_allocation(EntWork& w, RangeDec& rd, int start, int end, int alloc
   i32 psum;
   lo = 0;
   hi = 1 << CB_ALLOC_STEPS;
-  for (int it = 0; it < CB_ALLOC_STEPS; it++) {
+  CB_NOUNROLL for (int it = 0; it < CB_ALLOC_STEPS; it++) {
     int mid = (lo + hi) >> 1;
     psum = 0;
     int done = 0;
-    for (int j = end; j-- > start;) {
+    CB_NOUNROLL for (int j = end; j-- > start;) {
       int tmp = bits1[j] + (int)((i32)mid * bits2[j] >> CB_ALLOC_STEPS);
       if (tmp >= thresh[j] || done) {
         done = 1;
@@ -954,7 +1001,7 @@ CB_FN int dec_allocation(EntWork& w, RangeDec& rd, int start, int end, int alloc
   psum = 0;
   {
     int done = 0;
-    for (int j = end; j-- > start;) {
+    CB_NOUNROLL for (int j = end; j-- > start;) {
       int tmp = bits1[j] + (lo * bits2[j] >> CB_ALLOC_STEPS);
       if (tmp < thresh[j] && !done) {
         if (tmp >= alloc_floor) tmp = alloc_floor; else tmp = 0;
@@ -967,7 +1014,7 @@ CB_FN int dec_allocation(EntWork& w, RangeDec& rd, int start, int end, int alloc
     }
   }
   int codedBands;
-  for (codedBands = end;; codedBands--) {
+  CB_NOUNROLL for (codedBands = end;; codedBands--) {
     int j = codedBands - 1;
     if (j <= skip_start) {
       total += skip_rsv;
@@ -1009,8 +1056,8 @@ CB_FN int dec_allocation(EntWork& w, RangeDec& rd, int start, int end, int alloc
     int span = ebands(codedBands) - ebands(start);
     i32 percoeff = (i32)((u32)left / (u32)span);
     left -= span * percoeff;
-    for (int j = start; j < codedBands; j++) bits[j] += (int)percoeff * (ebands(j + 1) - ebands(j));
-    for (int j = start; j < codedBands; j++) {
+    CB_NOUNROLL for (int j = start; j < codedBands; j++) bits[j] += (int)percoeff * (ebands(j + 1) - ebands(j));
+    CB_NOUNROLL for (int j = start; j < codedBands; j++) {
       int tmp = (int)min32(left, ebands(j + 1) - ebands(j));
       bits[j] += tmp;
       left -= tmp;
@@ -1018,7 +1065,7 @@ CB_FN int dec_allocation(EntWork& w, RangeDec& rd, int start, int end, int alloc
   }
   i32 balance = 0;
   int j;
-  for (j = start; j < codedBands; j++) {
+  CB_NOUNROLL for (j = start; j < codedBands; j++) {
     int N0 = ebands(j + 1) - ebands(j);
     int N = N0 << LM;
     i32 bit = bits[j] + balance;
@@ -1056,7 +1103,7 @@ CB_FN int dec_allocation(EntWork& w, RangeDec& rd, int start, int end, int alloc
     w.fine_quant[j] = (i8)eb;
   }
   balance_out = balance;
-  for (; j < end; j++) {
+  CB_NOUNROLL for (; j < end; j++) {
     int eb = bits[j] >> stereo >> CB_BITRES;
     w.fine_quant[j] = (i8)eb;
     bits[j] = 0;
@@ -1081,7 +1128,7 @@ CB_FN int celt_entropy_decode(EntWork& w, CeltDecState* stg, FrameSide* side, co
   CB_WSYNC();
   int effEnd = end > CB_NBANDS ? CB_NBANDS : end;
 
-  RangeDec rd;
+  RangeDec& rd = w.rd;
   rd_init(rd, pkt, (u32)len);
 
   if (C == 1) {
@@ -1124,19 +1171,19 @@ CB_FN int celt_entropy_decode(EntWork& w, CeltDecState* stg, FrameSide* side, co
   int spread_decision = CB_SPREAD_NORMAL;
   if (tell + 4 <= total_bits) spread_decision = rd_icdf(rd, ct_spread_icdf, 5);
   // init_caps (celt.c:255-264)
-  for (int i = 0; i < CB_NBANDS; i++) {
+  CB_NOUNROLL for (int i = 0; i < CB_NBANDS; i++) {
     int Nb = (ebands(i + 1) - ebands(i)) << LM;
     w.cap[i] = (i16)((ct_cache_caps50[CB_NBANDS * (2 * LM + C - 1) + i] + 64) * C * Nb >> 2);
   }
   int dynalloc_logp = 6;
   total_bits <<= CB_BITRES;
   tell = (i32)rd_tell_frac(rd);
-  for (int i = start; i < end; i++) {
+  CB_NOUNROLL for (int i = start; i < end; i++) {
     int width = C * (ebands(i + 1) - ebands(i)) << LM;
     int quanta = cb_imin(width << CB_BITRES, cb_imax(6 << CB_BITRES, width));
     int loop_logp = dynalloc_logp;
     int boost = 0;
-    while (tell + (loop_logp << CB_BITRES) < total_bits && boost < w.cap[i]) {
+    CB_NOUNROLL while (tell + (loop_logp << CB_BITRES) < total_bits && boost < w.cap[i]) {
       int flag = rd_bit_logp(rd, (u32)loop_logp);
       tell = (i32)rd_tell_frac(rd);
       if (!flag) break;

@@ -37,7 +37,7 @@ CB_FN void v_denormalise(const i16* X, i32* dst, const i16* bandLogE, int start,
   if (downsample != 1) bound = cb_imin(bound, N / downsample);
   if (silence) { bound = 0; start = end = 0; }
   CB_WSYNC();
-  CB_LANE_LOOP(j, M * ct_eband5ms[start]) dst[j] = 0;
+  CB_LANE_LOOPU(j, M * ct_eband5ms[start]) dst[j] = 0;
   for (int i = start; i < end; i++) {
     int j0 = M * ct_eband5ms[i], j1 = M * ct_eband5ms[i + 1];
     i16 lg = add16(bandLogE[i], shl16((i16)ct_eMeans[i], 6));
@@ -47,13 +47,13 @@ CB_FN void v_denormalise(const i16* X, i32* dst, const i16* bandLogE, int start,
     else g = (i16)cb_exp2_frac(lg & ((1 << CB_DB_SHIFT) - 1));
     if (shift < 0) {
       if (shift < -2) { g = 32767; shift = -2; }
-      CB_LANE_LOOP(t, j1 - j0) dst[j0 + t] = shl32(mult16_16(X[j0 + t], g), -shift);
+      CB_LANE_LOOPU(t, j1 - j0) dst[j0 + t] = shl32(mult16_16(X[j0 + t], g), -shift);
     } else {
-      CB_LANE_LOOP(t, j1 - j0) dst[j0 + t] = mult16_16(X[j0 + t], g) >> shift;
+      CB_LANE_LOOPU(t, j1 - j0) dst[j0 + t] = mult16_16(X[j0 + t], g) >> shift;
     }
   }
   CB_WSYNC();
-  CB_LANE_LOOP(t, N - bound) dst[bound + t] = 0;
+  CB_LANE_LOOPU(t, N - bound) dst[bound + t] = 0;
   CB_WSYNC();
 }
 
@@ -62,7 +62,7 @@ CB_FN void v_denormalise(const i16* X, i32* dst, const i16* bandLogE, int start,
 CB_FN void fft_radix4(i32* base, int nb, int bstride, int G, int m, int mm, int fs) {
   const int per = G * m;
   CB_WSYNC();
-  CB_LANE_LOOP(u, nb * per) {
+  CB_LANE_LOOPU(u, nb * per) {
     int blk = u / per, r = u % per;
     int g = r / m, j = r % m;
     i32* F0 = base + blk * bstride + 2 * (g * mm + j);
@@ -93,7 +93,7 @@ CB_FN void fft_radix4(i32* base, int nb, int bstride, int G, int m, int mm, int 
 // kf_bfly2 (kiss_fft.c:51-108): only ever follows a radix-4 with m==1, so m==4, group stride 8
 CB_FN void fft_radix2_m4(i32* base, int nb, int bstride, int G) {
   CB_WSYNC();
-  CB_LANE_LOOP(u, nb * G * 4) {
+  CB_LANE_LOOPU(u, nb * G * 4) {
     int blk = u / (G * 4), r = u % (G * 4);
     int g = r >> 2, j = r & 3;
     i32* F = base + blk * bstride + 2 * (g * 8 + j);
@@ -113,7 +113,7 @@ CB_FN void fft_radix2_m4(i32* base, int nb, int bstride, int G) {
 CB_FN void fft_radix3(i32* base, int nb, int bstride, int G, int m, int mm, int fs) {
   const int per = G * m;
   CB_WSYNC();
-  CB_LANE_LOOP(u, nb * per) {
+  CB_LANE_LOOPU(u, nb * per) {
     int blk = u / per, r = u % per;
     int g = r / m, j = r % m;
     i32* F0 = base + blk * bstride + 2 * (g * mm + j);
@@ -137,7 +137,7 @@ CB_FN void fft_radix5(i32* base, int nb, int bstride, int G, int m, int mm, int 
   const int per = G * m;
   const i32 yar = 10126, yai = -31164, ybr = -26510, ybi = -19261;
   CB_WSYNC();
-  CB_LANE_LOOP(u, nb * per) {
+  CB_LANE_LOOPU(u, nb * per) {
     int blk = u / per, r = u % per;
     int g = r / m, j = r % m;
     i32* F0 = base + blk * bstride + 2 * (g * mm + j);
@@ -207,7 +207,7 @@ CB_FN void v_imdct(const i32* freq, i32* out, int B, int NB, int sh) {
   const i16* bitrev = sh == 0 ? ct_fft_bitrev480 : sh == 1 ? ct_fft_bitrev240 : sh == 2 ? ct_fft_bitrev120 : ct_fft_bitrev60;
   i32* ybase = out + (CB_OVERLAP >> 1);
   CB_WSYNC();
-  CB_LANE_LOOP(u, B * N4) {           // pre-rotation, scattered into bit-reversed order
+  CB_LANE_LOOPU(u, B * N4) {           // pre-rotation, scattered into bit-reversed order
     int b = u / N4, i = u % N4;
     const i32* in = freq + b;
     i32 x1 = in[2 * B * i];
@@ -221,7 +221,7 @@ CB_FN void v_imdct(const i32* freq, i32* out, int B, int NB, int sh) {
     yp[2 * rev] = yi;
   }
   fft_run(ybase, B, NB, sh);
-  CB_LANE_LOOP(u, B * (N4 >> 1)) {    // post-rotation from both ends
+  CB_LANE_LOOPU(u, B * (N4 >> 1)) {    // post-rotation from both ends
     int b = u / (N4 >> 1), i = u % (N4 >> 1);
     i32* yp0 = ybase + NB * b + 2 * i;
     i32* yp1 = ybase + NB * b + N2 - 2 - 2 * i;
@@ -239,7 +239,7 @@ CB_FN void v_imdct(const i32* freq, i32* out, int B, int NB, int sh) {
     yp0[1] = yi;
   }
   CB_WSYNC();
-  CB_LANE_LOOP(u, B * (CB_OVERLAP / 2)) {   // TDAC mirror
+  CB_LANE_LOOPU(u, B * (CB_OVERLAP / 2)) {   // TDAC mirror
     int b = u / (CB_OVERLAP / 2), i = u % (CB_OVERLAP / 2);
     i32* o = out + NB * b;
     i32 x1 = o[CB_OVERLAP - 1 - i], x2 = o[i];
@@ -273,7 +273,7 @@ CB_FN void v_comb_filter(i32* buf, int off, int n, const i32* hist, int pos, int
   for (int base = 0; base < overlap; base += wave) {
     int cnt = cb_imin(wave, overlap - base);
     CB_WSYNC();
-    CB_LANE_LOOP(t, cnt) {
+    CB_LANE_LOOPU(t, cnt) {
       int i = off + base + t;
       i32 w = cb_ldg(&ct_window120[base + t]);
       i32 f = (i16)mult16_16_q15(w, w);
@@ -297,7 +297,7 @@ CB_FN void v_comb_filter(i32* buf, int off, int n, const i32* hist, int pos, int
   for (int base = overlap; base < n; base += wave1) {
     int cnt = cb_imin(wave1, n - base);
     CB_WSYNC();
-    CB_LANE_LOOP(t, cnt) {
+    CB_LANE_LOOPU(t, cnt) {
       int i = off + base + t;
       i32 y = buf[i];
       y = add32(y, mult16_32_q15(g10, comb_at(buf, hist, pos, i - T1)));
@@ -327,7 +327,7 @@ CB_FN void celt_synth_channel(SynWork& w, CeltDecState* st, const FrameSide* sid
     i32* f2 = w.buf + (CB_OVERLAP >> 1);
     v_denormalise(side->X, w.freq, side->bandE, side->start, side->effEnd, M, downsample, side->silence);
     v_denormalise(side->X + N, f2, side->bandE + CB_NBANDS, side->start, side->effEnd, M, downsample, side->silence);
-    CB_LANE_LOOP(i, N) w.freq[i] = half32(add32(w.freq[i], f2[i]));
+    CB_LANE_LOOPU(i, N) w.freq[i] = half32(add32(w.freq[i], f2[i]));
     CB_WSYNC();
   } else {
     int sc = (C == 1) ? 0 : c;
@@ -335,18 +335,18 @@ CB_FN void celt_synth_channel(SynWork& w, CeltDecState* st, const FrameSide* sid
                   downsample, side->silence);
   }
   // 2. overlap tail of the previous frame becomes out_syn[0..60)
-  CB_LANE_LOOP(i, CB_OVERLAP / 2) w.buf[i] = st->tail[c][i];
+  CB_LANE_LOOPU(i, CB_OVERLAP / 2) w.buf[i] = st->tail[c][i];
   // 3. inverse MDCT(s)
   v_imdct(w.freq, w.buf, B, NB, sh);
   // 4. new overlap tail
-  CB_LANE_LOOP(i, CB_OVERLAP / 2) st->tail[c][i] = w.buf[N + i];
+  CB_LANE_LOOPU(i, CB_OVERLAP / 2) st->tail[c][i] = w.buf[N + i];
   // 5. pitch post-filter (celt_decoder.c:1002-1013)
   v_comb_filter(w.buf, 0, 120, hist, pos, side->T0, side->T1, side->g0, side->g1, side->tap0, side->tap1, CB_OVERLAP);
   if (LM != 0)
     v_comb_filter(w.buf, 120, N - 120, hist, pos, side->T1, side->T2, side->g1, side->g2, side->tap1, side->tap2, CB_OVERLAP);
   CB_WSYNC();
   // 6. history ring: the frame overwrites the N oldest samples
-  CB_LANE_LOOP(j, N) hist[(pos + j) & (CB_HIST - 1)] = w.buf[j];
+  CB_LANE_LOOPU(j, N) hist[(pos + j) & (CB_HIST - 1)] = w.buf[j];
   // 7. de-emphasis (celt_decoder.c:185-275): serial one-pole IIR, one lane
   CB_WSYNC();
   CB_IF_LANE0 {
@@ -362,9 +362,9 @@ CB_FN void celt_synth_channel(SynWork& w, CeltDecState* st, const FrameSide* sid
   CB_WSYNC();
   const int Nd = N / downsample;
   if (side->accum) {
-    CB_LANE_LOOP(j, Nd) pcm[j * CC + c] = sat16((i32)pcm[j * CC + c] + (i32)sig2word16(w.buf[j * downsample]));
+    CB_LANE_LOOPU(j, Nd) pcm[j * CC + c] = sat16((i32)pcm[j * CC + c] + (i32)sig2word16(w.buf[j * downsample]));
   } else {
-    CB_LANE_LOOP(j, Nd) pcm[j * CC + c] = sig2word16(w.buf[j * downsample]);
+    CB_LANE_LOOPU(j, Nd) pcm[j * CC + c] = sig2word16(w.buf[j * downsample]);
   }
   CB_WSYNC();
 }

@@ -26,12 +26,14 @@ typedef int8_t i8;
 #define CB_DEVICE_BUILD 1
 #define CB_FN __device__ __forceinline__
 #define CB_HD __host__ __device__ __forceinline__
-#define CB_FN_NOINLINE __device__ __noinline__
+#define CB_FN_NOINLINE static __device__ __noinline__
 #define CB_UTABLE static __constant__ const
 #define CB_GTABLE static __device__ const
 #define CB_LANE() ((int)(threadIdx.x & 31))
-#define CB_LANE_LOOP(i, n) for (int i = CB_LANE(); i < (n); i += 32)
+#define CB_LANE_LOOP(i, n) _Pragma("unroll 1") for (int i = CB_LANE(); i < (n); i += 32)
+#define CB_LANE_LOOPU(i, n) for (int i = CB_LANE(); i < (n); i += 32)   /* compiler may unroll */
 #define CB_WSYNC() __syncwarp()
+#define CB_NOUNROLL _Pragma("unroll 1")
 CB_FN i32 cb_wsum(i32 v) { return (i32)__reduce_add_sync(0xffffffffu, (unsigned)v); }
 CB_FN u32 cb_wor(u32 v) { return __reduce_or_sync(0xffffffffu, v); }
 CB_FN i32 cb_wmax(i32 v) { return __reduce_max_sync(0xffffffffu, v); }
@@ -47,7 +49,9 @@ template <typename T> CB_FN T cb_ldg(const T* p) { return __ldg(p); }
 #define CB_GTABLE static const
 #define CB_LANE() 0
 #define CB_LANE_LOOP(i, n) for (int i = 0; i < (n); ++i)
+#define CB_LANE_LOOPU(i, n) for (int i = 0; i < (n); ++i)
 #define CB_WSYNC() ((void)0)
+#define CB_NOUNROLL
 CB_FN i32 cb_wsum(i32 v) { return v; }
 CB_FN u32 cb_wor(u32 v) { return v; }
 CB_FN i32 cb_wmax(i32 v) { return v; }
@@ -126,11 +130,11 @@ CB_FN i32 frac_mul16(i32 a, i32 b) { return (16384 + (i32)(i16)a * (i32)(i16)b) 
 
 // ---- celt/mathops.c ---------------------------------------------------------------------
 // isqrt32 (mathops.c:42-63): exact floor(sqrt(v))
-CB_FN u32 cb_isqrt32(u32 v) {
+CB_FN_NOINLINE u32 cb_isqrt32(u32 v) {
   u32 g = 0;
   int bshift = (cb_ilog(v) - 1) >> 1;
   u32 b = 1u << bshift;
-  do {
+  CB_NOUNROLL do {
     u32 t = ((g << 1) + b) << bshift;
     if (t <= v) { g += b; v -= t; }
     b >>= 1;
@@ -224,10 +228,10 @@ CB_FN i16 cb_log2(i32 x) {
 }
 // celt_lcg_rand (bands.c:63) and an O(log j) skip-ahead so lanes can draw element j directly.
 CB_FN u32 cb_lcg(u32 s) { return 1664525u * s + 1013904223u; }
-CB_FN u32 cb_lcg_skip(u32 s, u32 steps) {
+CB_FN_NOINLINE u32 cb_lcg_skip(u32 s, u32 steps) {
   u32 a = 1664525u, c = 1013904223u;   // x -> a*x + c, composed by repeated squaring
   u32 A = 1u, C = 0u;
-  while (steps) {
+  CB_NOUNROLL while (steps) {
     if (steps & 1u) { A = A * a; C = C * a + c; }
     c = (a + 1u) * c;
     a = a * a;

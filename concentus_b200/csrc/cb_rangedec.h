@@ -25,7 +25,7 @@ CB_FN int rd_byte_end(RangeDec& d) { return d.end_offs < d.storage ? d.buf[d.sto
 
 // ec_dec_normalize (entdec.c:104-131): EC_SYM_BITS=8, EC_CODE_BOT=2^23, EC_CODE_EXTRA=7
 CB_FN void rd_normalize(RangeDec& d) {
-  while (d.rng <= 0x800000u) {
+  CB_NOUNROLL while (d.rng <= 0x800000u) {
     d.nbits_total += 8;
     d.rng <<= 8;
     int sym = d.rem;
@@ -54,7 +54,7 @@ CB_FN void rd_init(RangeDec& d, const u8* buf, u32 storage) {
 CB_FN int rd_tell(const RangeDec& d) { return d.nbits_total - cb_ilog(d.rng); }
 // ec_tell_frac (entcode.c:69-97), 1/8-bit resolution
 CB_UTABLE u32 rd_tell_correction[8] = {35733, 38967, 42495, 46340, 50535, 55109, 60097, 65535};
-CB_FN u32 rd_tell_frac(const RangeDec& d) {
+CB_FN_NOINLINE u32 rd_tell_frac(const RangeDec& d) {
   u32 nbits = (u32)d.nbits_total << 3;
   int l = cb_ilog(d.rng);
   u32 r = d.rng >> (l - 16);
@@ -63,27 +63,27 @@ CB_FN u32 rd_tell_frac(const RangeDec& d) {
   return nbits - (u32)((l << 3) + (int)b);
 }
 // ec_decode (entdec.c:155-172): two unsigned divides
-CB_FN u32 rd_decode(RangeDec& d, u32 ft) {
+CB_FN_NOINLINE u32 rd_decode(RangeDec& d, u32 ft) {
   d.ext = d.rng / ft;
   u32 s = d.val / d.ext;
   return ft - (s + 1 < ft ? s + 1 : ft);
 }
 // ec_decode_bin (entdec.c:174-179)
-CB_FN u32 rd_decode_bin(RangeDec& d, u32 bits) {
+CB_FN_NOINLINE u32 rd_decode_bin(RangeDec& d, u32 bits) {
   d.ext = d.rng >> bits;
   u32 s = d.val / d.ext;
   u32 top = 1u << bits;
   return top - (s + 1u < top ? s + 1u : top);
 }
 // ec_dec_update (entdec.c:181-200)
-CB_FN void rd_update(RangeDec& d, u32 fl, u32 fh, u32 ft) {
+CB_FN_NOINLINE void rd_update(RangeDec& d, u32 fl, u32 fh, u32 ft) {
   u32 s = d.ext * (ft - fh);
   d.val -= s;
   d.rng = fl > 0 ? d.ext * (fh - fl) : d.rng - s;
   rd_normalize(d);
 }
 // ec_dec_bit_logp (entdec.c:203-216)
-CB_FN int rd_bit_logp(RangeDec& d, u32 logp) {
+CB_FN_NOINLINE int rd_bit_logp(RangeDec& d, u32 logp) {
   u32 r = d.rng, v = d.val;
   u32 s = r >> logp;
   int ret = v < s;
@@ -93,11 +93,11 @@ CB_FN int rd_bit_logp(RangeDec& d, u32 logp) {
   return ret;
 }
 // ec_dec_icdf (entdec.c:218-236); icdf lives in constant memory (uniform index)
-CB_FN int rd_icdf(RangeDec& d, const u8* icdf, u32 ftb) {
+CB_FN_NOINLINE int rd_icdf(RangeDec& d, const u8* icdf, u32 ftb) {
   u32 s = d.rng, v = d.val, t;
   u32 r = s >> ftb;
   int ret = -1;
-  do {
+  CB_NOUNROLL do {
     t = s;
     s = r * icdf[++ret];
   } while (v < s);
@@ -107,11 +107,11 @@ CB_FN int rd_icdf(RangeDec& d, const u8* icdf, u32 ftb) {
   return ret;
 }
 // ec_dec_bits (entdec.c:284-319): raw bits from the tail of the packet
-CB_FN u32 rd_bits(RangeDec& d, u32 bits) {
+CB_FN_NOINLINE u32 rd_bits(RangeDec& d, u32 bits) {
   u32 window = d.end_window;
   int available = d.nend_bits;
   if ((u32)available < bits) {
-    do {
+    CB_NOUNROLL do {
       window |= (u32)rd_byte_end(d) << available;
       available += 8;
     } while (available <= 32 - 8);
@@ -125,7 +125,7 @@ CB_FN u32 rd_bits(RangeDec& d, u32 bits) {
   return ret;
 }
 // ec_dec_uint (entdec.c:238-282), EC_UINT_BITS=8
-CB_FN u32 rd_uint(RangeDec& d, u32 ft_in) {
+CB_FN_NOINLINE u32 rd_uint(RangeDec& d, u32 ft_in) {
   u32 ft = ft_in - 1;
   int ftb = cb_ilog(ft);
   if (ftb > 8) {
@@ -144,7 +144,7 @@ CB_FN u32 rd_uint(RangeDec& d, u32 ft_in) {
   return s;
 }
 // ec_laplace_decode (laplace.c:94-134), LAPLACE_MINP=1, LAPLACE_NMIN=16
-CB_FN int rd_laplace(RangeDec& d, u32 fs, int decay) {
+CB_FN_NOINLINE int rd_laplace(RangeDec& d, u32 fs, int decay) {
   int val = 0;
   u32 fm = rd_decode_bin(d, 15);
   u32 fl = 0;
@@ -153,7 +153,7 @@ CB_FN int rd_laplace(RangeDec& d, u32 fs, int decay) {
     fl = fs;
     // ec_laplace_get_freq1 (laplace.c:44-49)
     fs = (((32768u - 32u - fs) * (u32)(16384 - decay)) >> 15) + 1;
-    while (fs > 1 && fm >= fl + 2 * fs) {
+    CB_NOUNROLL while (fs > 1 && fm >= fl + 2 * fs) {
       fs *= 2;
       fl += fs;
       fs = (u32)(((i32)(fs - 2) * (i32)decay) >> 15);
