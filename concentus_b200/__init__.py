@@ -45,7 +45,7 @@ EXPORTS = [
     "opus_packet_parse", "opus_decode_batch", "opus_decode_batch_flat", "opus_decoder_group_create",
     "opus_decoder_group_destroy", "opus_decode_group_flat", "opus_decode_group_device",
     "opus_decoder_get_final_range_batch", "opus_b200_synchronize", "opus_b200_launch_count",
-    "opus_b200_profile_begin", "opus_b200_profile_end",
+    "opus_b200_profile_begin", "opus_b200_profile_end", "opus_decode_batch_device_static",
 ]
 
 _lib = None
@@ -89,6 +89,8 @@ def load():
     lib.opus_decode_group_flat.argtypes = [vp, vp, ctypes.c_int32, vp, vp, vp, ctypes.c_int32, ctypes.c_int, vp, vp]
     lib.opus_decode_group_device.argtypes = [vp, vp, vp, vp, vp, ctypes.c_int32, ctypes.c_int, vp, vp,
                                              ctypes.c_int, ctypes.c_int, vp]
+    lib.opus_decode_batch_device_static.argtypes = [vp, ctypes.c_int, vp, vp, vp, vp, ctypes.c_int32, ctypes.c_int,
+                                                    vp, ctypes.c_int, ctypes.c_int, vp]
     lib.opus_decoder_get_final_range_batch.argtypes = [vp, ctypes.c_int, vp]
     lib.opus_b200_launch_count.restype = ctypes.c_longlong
     lib.opus_packet_get_nb_samples.argtypes = [vp, ctypes.c_int32, ctypes.c_int32]

@@ -626,6 +626,13 @@ int opus_b200_synchronize(void) {
 
 long long opus_b200_launch_count(void) { return g_launches; }
 
+// internal (used by cb_noalloc.cu): device address of a decoder's state blob and its GPU index
+OpusDecState* opusb_internal_device_state(const OpusDecoder* st, int* device) {
+  if (!st || st->magic != kMagic) return nullptr;
+  if (device) *device = st->device;
+  return st->d_state;
+}
+
 int opus_b200_profile_begin(void) {
   std::lock_guard<std::mutex> lk(g_mu);
   g_prof_on = true;

@@ -122,6 +122,26 @@ int opus_decode_group_device(OpusDecoderGroup *grp, const unsigned char *d_data,
                              opus_int32 pcm_stride, int frame_size, const int *d_decode_fec, int *d_ret,
                              int max_frames, int max_packet_bytes, void *cuda_stream);
 
+/* No counterpart in the reference (libopus keeps all scratch on the caller's stack).
+ * Device-resident batch decode that allocates nothing: for callers that must not call cudaMalloc --
+ * a real-time decode thread (allocation takes driver-wide locks, cudaFree synchronises the whole
+ * GPU and stalls every other stream's audio) or a host with a fixed, pre-carved GPU memory budget.
+ * It takes the decoders directly (no OpusDecoderGroup, whose creation
+ * allocates); the per-stream scratch is a fixed array inside the library image, about 1.1 MB, held
+ * by every GPU that loads the library until the process exits.  Limit: n <= 256
+ * (OPUS_B200_STATIC_MAX_STREAMS); more is rejected with OPUS_BAD_ARG and a message on stderr.
+ * All pointers except `st` are device pointers; the decoding is bit-identical to
+ * opus_decode_group_device().  The array is shared by every call on that GPU and still holds the
+ * previous call's records, which this call overwrites: calls that could run concurrently on one GPU
+ * (different streams or threads) race and must be ordered by the caller.  The first call on a GPU
+ * looks up the array's device address (cudaGetSymbolAddress); make it at start-up, before any
+ * stream capture.  decode_fec is not offered here (treated as 0). */
+#define OPUS_B200_STATIC_MAX_STREAMS 256
+int opus_decode_batch_device_static(OpusDecoder *const *st, int n, const unsigned char *d_data,
+                                    const opus_int32 *d_offsets, const opus_int32 *d_len, opus_int16 *d_pcm,
+                                    opus_int32 pcm_stride, int frame_size, int *d_ret, int max_frames,
+                                    int max_packet_bytes, void *cuda_stream);
+
 /* Batched OPUS_GET_FINAL_RANGE: out[i] = final range of the last packet decoded by st[i]. */
 int opus_decoder_get_final_range_batch(OpusDecoder *const *st, int n, opus_uint32 *out);
 
