@@ -1,0 +1,501 @@
+// cb_celt_plc.h -- packet-loss concealment for CELT frames (kernel C body + the noise branch used
+// by kernel A).  Bit-exact with celt_decode_lost() (opus-fix/celt/celt_decoder.c:415-711),
+// celt_plc_pitch_search (:399-413), pitch_downsample / pitch_search / find_best_pitch / celt_fir5
+// (celt/pitch.c:45-370), _celt_autocorr / _celt_lpc / celt_fir / celt_iir (celt/celt_lpc.c:37-328).
+//
+// One warp per stream.  Concealment is rare (it runs only for lost or DTX frames), so the layout
+// favours clarity: channels are processed one after the other, inner products are lane loops folded
+// with redux, and the two truly serial recurrences (Levinson-Durbin, the order-24 IIR) keep their
+// order -- the IIR spreads its 24 taps over lanes and folds once per sample.
+#pragma once
+#include "cb_common.h"
+#include "cb_state.h"
+#include "cb_celt_synth.h"
+#include "cb_celt_entropy.h"
+
+#define CB_MAX_PERIOD 1024
+#define CB_PLC_PITCH_LAG_MAX 720
+#define CB_PLC_PITCH_LAG_MIN 100
+
+struct alignas(16) PlcWork {
+  i32 nb[CB_MAXN + CB_OVERLAP];      // D_new[2048-N .. 2048+overlap): the frame being concealed
+  i32 etmp[CB_OVERLAP];
+  i32 xcorr[(CB_PLC_PITCH_LAG_MAX - CB_PLC_PITCH_LAG_MIN) >> 1];
+  i32 ac[CB_LPC_ORDER + 1];
+  i32 lpc32[CB_LPC_ORDER];
+  i16 exc[CB_MAX_PERIOD + 32];       // excitation; [CB_MAX_PERIOD..) is IIR history scratch
+  i16 xx[CB_MAX_PERIOD];             // windowed / scaled copy (autocorr), FIR output staging
+  i16 xlp[CB_HIST >> 1];             // 2x decimated pitch buffer
+  i16 xlp4[(CB_HIST - CB_PLC_PITCH_LAG_MAX) >> 2];
+  i16 ylp4[CB_HIST >> 2];
+  i16 lpcmem[CB_LPC_ORDER];
+  i16 yhist[CB_MAXN + CB_OVERLAP + CB_LPC_ORDER];   // rounded IIR outputs (filter memory)
+};
+
+CB_FN i32 hist_at(const i32* hist, int pos, int i) { return hist[(pos + i) & (CB_HIST - 1)]; }
+
+// _celt_autocorr (celt_lpc.c:232-328) without the SIMD split: ac[k] = sum_{i>=k} x[i]x[i-k], then
+// the fixed-point normalisation.  x: n samples; xx: scratch of n samples.
+CB_FN int plc_autocorr(const i16* x, i32* ac, i16* xx, int use_window, int lag, int n) {
+  const i16* xptr = x;
+  CB_WSYNC();
+  if (use_window) {
+    CB_LANE_LOOP(i, n) xx[i] = x[i];
+    CB_WSYNC();
+    CB_LANE_LOOP(i, CB_OVERLAP) {
+      i32 w = cb_ldg(&ct_window120[i]);
+      xx[i] = (i16)mult16_16_q15(x[i], w);
+      xx[n - i - 1] = (i16)mult16_16_q15(x[n - i - 1], w);
+    }
+    CB_WSYNC();
+    xptr = xx;
+  }
+  i32 part = 0;
+  CB_LANE_LOOP(i, n) part = add32(part, mult16_16(xptr[i], xptr[i]) >> 9);
+  i32 ac0 = add32(1 + (n << 7), cb_wsum(part));
+  int shift = cb_ilog2(ac0) - 30 + 10;
+  shift = shift / 2;
+  if (shift > 0) {
+    CB_WSYNC();
+    CB_LANE_LOOP(i, n) {
+      i32 v = xptr[i];
+      xx[i] = (i16)pshr32(v, shift);
+    }
+    CB_WSYNC();
+    xptr = xx;
+  } else {
+    shift = 0;
+  }
+  CB_NOUNROLL for (int k = 0; k <= lag; k++) {
+    i32 d = 0;
+    CB_LANE_LOOP(t, n - k) d = mac16_16(d, xptr[t + k], xptr[t]);
+    ac[k] = cb_wsum(d);
+  }
+  CB_WSYNC();
+  shift = 2 * shift;
+  i32 a0 = ac[0];
+  if (shift <= 0) a0 = add32(a0, shl32(1, -shift));
+  CB_WSYNC();
+  ac[0] = a0;
+  CB_WSYNC();
+  if (a0 < 268435456) {
+    int shift2 = 29 - cb_ilog((u32)a0);
+    CB_LANE_LOOP(i, lag + 1) ac[i] = shl32(ac[i], shift2);
+    shift -= shift2;
+  } else if (a0 >= 536870912) {
+    int shift2 = 1;
+    if (a0 >= 1073741824) shift2++;
+    CB_LANE_LOOP(i, lag + 1) ac[i] = ac[i] >> shift2;
+    shift += shift2;
+  }
+  CB_WSYNC();
+  return shift;
+}
+
+// _celt_lpc (celt_lpc.c:37-93): Levinson-Durbin, uniform (p <= 24)
+CB_FN void plc_lpc(i16* out, const i32* ac, i32* lpc, int p) {
+  CB_NOUNROLL for (int i = 0; i < p; i++) lpc[i] = 0;
+  i32 error = ac[0];
+  if (ac[0] != 0) {
+    CB_NOUNROLL for (int i = 0; i < p; i++) {
+      i32 rr = 0;
+      CB_NOUNROLL for (int j = 0; j < i; j++) rr = add32(rr, mult32_32_q31(lpc[j], ac[i - j]));
+      rr = add32(rr, ac[i + 1] >> 3);
+      i32 r = neg32(cb_frac_div32(shl32(rr, 3), error));
+      lpc[i] = r >> 3;
+      CB_NOUNROLL for (int j = 0; j < (i + 1) >> 1; j++) {
+        i32 t1 = lpc[j], t2 = lpc[i - 1 - j];
+        lpc[j] = add32(t1, mult32_32_q31(r, t2));
+        lpc[i - 1 - j] = add32(t2, mult32_32_q31(r, t1));
+      }
+      error = sub32(error, mult32_32_q31(mult32_32_q31(r, r), error));
+      if (error < (ac[0] >> 10)) break;
+    }
+  }
+  CB_NOUNROLL for (int i = 0; i < p; i++) out[i] = round16(lpc[i], 16);
+}
+
+// find_best_pitch (pitch.c:45-103), uniform
+CB_FN void plc_find_best_pitch(const i32* xcorr, const i16* y, int len, int max_pitch, int* best_pitch,
+                               int yshift, i32 maxcorr) {
+  i32 Syy = 1;
+  i32 best_num0 = -1, best_num1 = -1;
+  i32 best_den0 = 0, best_den1 = 0;
+  const int xshift = cb_ilog2(maxcorr) - 14;
+  best_pitch[0] = 0;
+  best_pitch[1] = 1;
+  {
+    i32 part = 0;
+    CB_LANE_LOOP(j, len) part = add32(part, mult16_16(y[j], y[j]) >> yshift);
+    Syy = add32(Syy, cb_wsum(part));
+  }
+  CB_NOUNROLL for (int i = 0; i < max_pitch; i++) {
+    if (xcorr[i] > 0) {
+      i32 xcorr16 = (i16)vshr32(xcorr[i], xshift);
+      i32 num = (i16)mult16_16_q15(xcorr16, xcorr16);
+      if (mult16_32_q15(num, best_den1) > mult16_32_q15(best_num1, Syy)) {
+        if (mult16_32_q15(num, best_den0) > mult16_32_q15(best_num0, Syy)) {
+          best_num1 = best_num0; best_den1 = best_den0; best_pitch[1] = best_pitch[0];
+          best_num0 = num; best_den0 = Syy; best_pitch[0] = i;
+        } else {
+          best_num1 = num; best_den1 = Syy; best_pitch[1] = i;
+        }
+      }
+    }
+    Syy = add32(Syy, sub32(mult16_16(y[i + len], y[i + len]) >> yshift, mult16_16(y[i], y[i]) >> yshift));
+    Syy = max32(1, Syy);
+  }
+}
+
+// celt_plc_pitch_search (celt_decoder.c:399-413) = pitch_downsample + pitch_search
+CB_FN int plc_pitch_search(PlcWork& w, const CeltDecState* st) {
+  const int C = st->channels;
+  const int len = CB_HIST;
+  i16* x_lp = w.xlp;
+  // ---- pitch_downsample (pitch.c:147-222) ----
+  i32 mx = 0, mn = 0;
+  CB_NOUNROLL for (int c = 0; c < C; c++) {
+    const i32* h = st->hist[c];
+    const int pos = st->hist_pos[c];
+    CB_LANE_LOOP(i, len) {
+      i32 v = hist_at(h, pos, i);
+      mx = max32(mx, v);
+      mn = min32(mn, v);
+    }
+  }
+  mx = cb_wmax(mx);
+  mn = cb_wmin(mn);
+  i32 maxabs = max32(mx, neg32(mn));
+  if (maxabs < 1) maxabs = 1;
+  int shift = cb_ilog2(maxabs) - 10;
+  if (shift < 0) shift = 0;
+  if (C == 2) shift++;
+  CB_WSYNC();
+  CB_LANE_LOOP(i, len >> 1) {
+    i32 acc = 0;
+    for (int c = 0; c < C; c++) {
+      const i32* h = st->hist[c];
+      const int pos = st->hist_pos[c];
+      i32 v;
+      if (i == 0) v = half32(add32(half32(hist_at(h, pos, 1)), hist_at(h, pos, 0))) >> shift;
+      else v = half32(add32(half32(add32(hist_at(h, pos, 2 * i - 1), hist_at(h, pos, 2 * i + 1))), hist_at(h, pos, 2 * i))) >> shift;
+      // x_lp is opus_val16: the first channel is stored (truncated), the second added in 16 bits
+      acc = (c == 0) ? (i32)(i16)v : (i32)(i16)(acc + v);
+    }
+    x_lp[i] = (i16)acc;
+  }
+  CB_WSYNC();
+  i32* ac = w.ac;
+  plc_autocorr(x_lp, ac, w.xx, 0, 4, len >> 1);
+  i16 lpc[4];
+  {
+    i32 a[5];
+    for (int i = 0; i < 5; i++) a[i] = ac[i];
+    a[0] = add32(a[0], a[0] >> 13);
+    for (int i = 1; i <= 4; i++) a[i] = sub32(a[i], mult16_32_q15(2 * i * i, a[i]));
+    CB_WSYNC();
+    for (int i = 0; i < 5; i++) ac[i] = a[i];
+    CB_WSYNC();
+    i16 l4[4];
+    plc_lpc(l4, ac, w.lpc32, 4);
+    i32 tmp = CB_Q15ONE;
+    for (int i = 0; i < 4; i++) {
+      tmp = (i16)mult16_16_q15(29491, tmp);            // QCONST16(.9f,15)
+      lpc[i] = (i16)mult16_16_q15(l4[i], tmp);
+    }
+  }
+  const i32 c1 = 26214;                                // QCONST16(.8f,15)
+  i16 n0 = (i16)(lpc[0] + 3277);                       // QCONST16(.8f,SIG_SHIFT)
+  i16 n1 = (i16)(lpc[1] + mult16_16_q15(c1, lpc[0]));
+  i16 n2 = (i16)(lpc[2] + mult16_16_q15(c1, lpc[1]));
+  i16 n3 = (i16)(lpc[3] + mult16_16_q15(c1, lpc[2]));
+  i16 n4 = (i16)mult16_16_q15(c1, lpc[3]);
+  // celt_fir5 (pitch.c:105-145): FIR on the inputs, so out of place via xx then copy back
+  CB_WSYNC();
+  CB_LANE_LOOP(i, len >> 1) {
+    i32 sum = shl32((i32)x_lp[i], CB_SIG_SHIFT);
+    sum = mac16_16(sum, n0, i >= 1 ? x_lp[i - 1] : 0);
+    sum = mac16_16(sum, n1, i >= 2 ? x_lp[i - 2] : 0);
+    sum = mac16_16(sum, n2, i >= 3 ? x_lp[i - 3] : 0);
+    sum = mac16_16(sum, n3, i >= 4 ? x_lp[i - 4] : 0);
+    sum = mac16_16(sum, n4, i >= 5 ? x_lp[i - 5] : 0);
+    w.xx[i] = round16(sum, CB_SIG_SHIFT);
+  }
+  CB_WSYNC();
+  CB_LANE_LOOP(i, len >> 1) x_lp[i] = w.xx[i];
+  CB_WSYNC();
+  // ---- pitch_search (pitch.c:260-369): x = x_lp + 360, y = x_lp, len 1328, max_pitch 620 ----
+  const i16* xs = x_lp + (CB_PLC_PITCH_LAG_MAX >> 1);
+  const i16* y = x_lp;
+  const int plen = CB_HIST - CB_PLC_PITCH_LAG_MAX;
+  const int max_pitch = CB_PLC_PITCH_LAG_MAX - CB_PLC_PITCH_LAG_MIN;
+  const int lag = plen + max_pitch;
+  i32 xm = 0, xn = 0;
+  CB_LANE_LOOP(j, plen >> 2) { i16 v = xs[2 * j]; w.xlp4[j] = v; xm = max32(xm, v); xn = min32(xn, v); }
+  i32 ym = 0, yn = 0;
+  CB_LANE_LOOP(j, lag >> 2) { i16 v = y[2 * j]; w.ylp4[j] = v; ym = max32(ym, v); yn = min32(yn, v); }
+  i32 xmax = max32(cb_wmax(xm), neg32(cb_wmin(xn)));
+  i32 ymax = max32(cb_wmax(ym), neg32(cb_wmin(yn)));
+  int sh = cb_ilog2(max32(1, max32(xmax, ymax))) - 11;
+  CB_WSYNC();
+  if (sh > 0) {
+    CB_LANE_LOOP(j, plen >> 2) w.xlp4[j] = (i16)(w.xlp4[j] >> sh);
+    CB_LANE_LOOP(j, lag >> 2) w.ylp4[j] = (i16)(w.ylp4[j] >> sh);
+    sh *= 2;
+  } else {
+    sh = 0;
+  }
+  CB_WSYNC();
+  // coarse search, 4x decimation (celt_pitch_xcorr, pitch.c:225-258)
+  i32 maxcorr = 1;
+  CB_NOUNROLL for (int i = 0; i < (max_pitch >> 2); i++) {
+    i32 d = 0;
+    CB_LANE_LOOP(j, plen >> 2) d = mac16_16(d, w.xlp4[j], w.ylp4[i + j]);
+    d = cb_wsum(d);
+    w.xcorr[i] = d;
+    maxcorr = max32(maxcorr, d);
+  }
+  CB_WSYNC();
+  int best_pitch[2] = {0, 0};
+  plc_find_best_pitch(w.xcorr, w.ylp4, plen >> 2, max_pitch >> 2, best_pitch, 0, maxcorr);
+  // finer search, 2x decimation
+  maxcorr = 1;
+  CB_WSYNC();
+  CB_NOUNROLL for (int i = 0; i < (max_pitch >> 1); i++) {
+    int d0 = i - 2 * best_pitch[0], d1 = i - 2 * best_pitch[1];
+    if (d0 < 0) d0 = -d0;
+    if (d1 < 0) d1 = -d1;
+    i32 val = 0;
+    if (!(d0 > 2 && d1 > 2)) {
+      i32 sum = 0;
+      CB_LANE_LOOP(j, plen >> 1) sum = add32(sum, mult16_16(xs[j], y[i + j]) >> sh);
+      sum = cb_wsum(sum);
+      val = max32(-1, sum);
+      maxcorr = max32(maxcorr, sum);
+    }
+    w.xcorr[i] = val;
+  }
+  CB_WSYNC();
+  plc_find_best_pitch(w.xcorr, y, plen >> 1, max_pitch >> 1, best_pitch, sh + 1, maxcorr);
+  int offset = 0;
+  if (best_pitch[0] > 0 && best_pitch[0] < (max_pitch >> 1) - 1) {
+    i32 a = w.xcorr[best_pitch[0] - 1], b = w.xcorr[best_pitch[0]], c = w.xcorr[best_pitch[0] + 1];
+    if (sub32(c, a) > mult16_32_q15(22938, sub32(b, a))) offset = 1;          // QCONST16(.7f,15)
+    else if (sub32(a, c) > mult16_32_q15(22938, sub32(b, c))) offset = -1;
+  }
+  int pitch = 2 * best_pitch[0] - offset;
+  return CB_PLC_PITCH_LAG_MAX - pitch;
+}
+
+// Pitch-based concealment of one frame of N samples (celt_decoder.c:507-706) + de-emphasis.
+CB_FN void celt_plc_pitch(PlcWork& w, CeltDecState* st, int N, i16* pcm, int accum) {
+  const int C = st->channels;
+  const int loss_count = st->loss_count;
+  i32 fade = CB_Q15ONE;
+  int pitch_index;
+  if (loss_count == 0) {
+    pitch_index = plc_pitch_search(w, st);
+    st->last_pitch_index = pitch_index;
+  } else {
+    pitch_index = st->last_pitch_index;
+    fade = 26214;                                      // QCONST16(.8f,15)
+  }
+  CB_NOUNROLL for (int c = 0; c < C; c++) {
+    const i32* hist = st->hist[c];
+    const int pos = st->hist_pos[c];                   // D_old[i] = hist[(pos+i)&2047]
+    i16* exc = w.exc;
+    i16* lpc = st->lpc + c * CB_LPC_ORDER;
+    CB_WSYNC();
+    CB_LANE_LOOP(i, CB_MAX_PERIOD) exc[i] = round16(hist_at(hist, pos, CB_HIST - CB_MAX_PERIOD + i), CB_SIG_SHIFT);
+    CB_WSYNC();
+    if (loss_count == 0) {
+      plc_autocorr(exc, w.ac, w.xx, 1, CB_LPC_ORDER, CB_MAX_PERIOD);
+      i32 a0 = add32(w.ac[0], w.ac[0] >> 13);
+      CB_WSYNC();
+      CB_LANE_LOOP(i, CB_LPC_ORDER + 1) {
+        if (i == 0) w.ac[0] = a0;
+        else w.ac[i] = sub32(w.ac[i], mult16_32_q15(2 * i * i, w.ac[i]));
+      }
+      CB_WSYNC();
+      i16 l[CB_LPC_ORDER];
+      plc_lpc(l, w.ac, w.lpc32, CB_LPC_ORDER);
+      CB_NOUNROLL for (int i = 0; i < CB_LPC_ORDER; i++) lpc[i] = l[i];
+    }
+    CB_WSYNC();
+    const int exc_length = cb_imin(2 * pitch_index, CB_MAX_PERIOD);
+    // celt_fir (celt_lpc.c:95-149) on the last exc_length samples; memory = samples just before
+    CB_LANE_LOOP(i, CB_LPC_ORDER) w.lpcmem[i] = round16(hist_at(hist, pos, CB_HIST - exc_length - 1 - i), CB_SIG_SHIFT);
+    CB_WSYNC();
+    {
+      i16* x = exc + CB_MAX_PERIOD - exc_length;
+      CB_LANE_LOOP(i, exc_length) {
+        i32 sum = 0;
+        for (int j = 0; j < CB_LPC_ORDER; j++) {
+          int k = i - 1 - j;
+          i32 xv = k >= 0 ? x[k] : w.lpcmem[-k - 1];
+          sum = mac16_16(sum, lpc[j], xv);
+        }
+        w.xx[i] = sat16(add32((i32)x[i], pshr32(sum, CB_SIG_SHIFT)));
+      }
+      CB_WSYNC();
+      CB_LANE_LOOP(i, exc_length) x[i] = w.xx[i];
+      CB_WSYNC();
+    }
+    // decay of the excitation energy over the last two pitch periods
+    i32 decay;
+    {
+      i32 mx = 0, mn = 0;
+      CB_LANE_LOOP(i, exc_length) { i32 v = exc[CB_MAX_PERIOD - exc_length + i]; mx = max32(mx, v); mn = min32(mn, v); }
+      i32 maxabs = max32(cb_wmax(mx), neg32(cb_wmin(mn)));
+      int shift = cb_imax(0, 2 * cb_zlog2(maxabs) - 20);
+      int decay_length = exc_length >> 1;
+      i32 e1 = 0, e2 = 0;
+      CB_LANE_LOOP(i, decay_length) {
+        i32 e = exc[CB_MAX_PERIOD - decay_length + i];
+        e1 = add32(e1, mult16_16(e, e) >> shift);
+        e = exc[CB_MAX_PERIOD - 2 * decay_length + i];
+        e2 = add32(e2, mult16_16(e, e) >> shift);
+      }
+      i32 E1 = add32(1, cb_wsum(e1)), E2 = add32(1, cb_wsum(e2));
+      E1 = min32(E1, E2);
+      decay = (i16)cb_sqrt(cb_frac_div32(E1 >> 1, E2));
+    }
+    // extrapolate the excitation with period pitch_index, each period attenuated by `decay`
+    const int extrapolation_offset = CB_MAX_PERIOD - pitch_index;
+    const int extrapolation_len = N + CB_OVERLAP;
+    i32 S1p = 0;
+    CB_WSYNC();
+    CB_LANE_LOOP(i, extrapolation_len) {
+      int k = i / pitch_index, j = i - k * pitch_index;
+      i32 att = (i16)mult16_16_q15(fade, decay);
+      for (int t = 0; t < k; t++) att = (i16)mult16_16_q15(att, decay);
+      w.nb[i] = shl32((i32)(i16)mult16_16_q15(att, exc[extrapolation_offset + j]), CB_SIG_SHIFT);
+      i32 tmp = round16(hist_at(hist, pos, CB_HIST - CB_MAX_PERIOD + extrapolation_offset + j), CB_SIG_SHIFT);
+      S1p = add32(S1p, mult16_16(tmp, tmp) >> 8);
+    }
+    i32 S1 = cb_wsum(S1p);
+    CB_WSYNC();
+    // celt_iir (celt_lpc.c:151-230): y[i] = x[i] - sum_j lpc[j]*round16(y[i-1-j]); memory = last samples
+    {
+      i16* yh = w.yhist;                               // yh[CB_LPC_ORDER + i] = round16(y[i])
+      CB_LANE_LOOP(i, CB_LPC_ORDER) yh[CB_LPC_ORDER - 1 - i] = round16(hist_at(hist, pos, CB_HIST - 1 - i), CB_SIG_SHIFT);
+      CB_WSYNC();
+      CB_NOUNROLL for (int i = 0; i < extrapolation_len; i++) {
+        i32 part = 0;
+        CB_LANE_LOOP(j, CB_LPC_ORDER) part = sub32(part, mult16_16(lpc[j], yh[CB_LPC_ORDER + i - 1 - j]));
+        i32 sum = add32(w.nb[i], cb_wsum(part));
+        CB_WSYNC();
+        w.nb[i] = sum;
+        yh[CB_LPC_ORDER + i] = round16(sum, CB_SIG_SHIFT);
+        CB_WSYNC();
+      }
+    }
+    // energy guard
+    {
+      i32 s2 = 0;
+      CB_LANE_LOOP(i, extrapolation_len) {
+        i32 tmp = round16(w.nb[i], CB_SIG_SHIFT);
+        s2 = add32(s2, mult16_16(tmp, tmp) >> 8);
+      }
+      i32 S2 = cb_wsum(s2);
+      CB_WSYNC();
+      if (!(S1 > (S2 >> 2))) {
+        CB_LANE_LOOP(i, extrapolation_len) w.nb[i] = 0;
+      } else if (S1 < S2) {
+        i32 ratio = (i16)cb_sqrt(cb_frac_div32(add32(S1 >> 1, 1), add32(S2, 1)));
+        CB_LANE_LOOP(i, extrapolation_len) {
+          if (i < CB_OVERLAP) {
+            i32 tmp_g = (i16)(CB_Q15ONE - mult16_16_q15(cb_ldg(&ct_window120[i]), CB_Q15ONE - ratio));
+            w.nb[i] = mult16_32_q15(tmp_g, w.nb[i]);
+          } else {
+            w.nb[i] = mult16_32_q15(ratio, w.nb[i]);
+          }
+        }
+      }
+      CB_WSYNC();
+    }
+    // pre-filter the overlap for the next frame (comb_filter with x != y, negated gain) + TDAC
+    {
+      const int T = st->pf_period;
+      const i32 g = (i16)(-st->pf_gain);
+      const int tap = st->pf_tapset;
+      if (g == 0) {
+        CB_LANE_LOOP(i, CB_OVERLAP) w.etmp[i] = w.nb[N + i];
+      } else {
+        i32 g10 = mult16_16_p15(g, ct_comb_gains[tap][0]);
+        i32 g11 = mult16_16_p15(g, ct_comb_gains[tap][1]);
+        i32 g12 = mult16_16_p15(g, ct_comb_gains[tap][2]);
+        // x[k] = D_new[2048+k] = nb[N+k] (k >= -N) else the ring (D_new[m] = D_old[m+N])
+        CB_LANE_LOOP(i, CB_OVERLAP) {
+          i32 v[5];
+          for (int d = 0; d < 5; d++) {
+            int k = i - T + 2 - d;                     // x[i-T+2], x[i-T+1], x[i-T], x[i-T-1], x[i-T-2]
+            v[d] = (k >= -N) ? w.nb[N + k] : hist_at(hist, pos, CB_HIST + N + k);
+          }
+          i32 yv = w.nb[N + i];
+          yv = add32(yv, mult16_32_q15(g10, v[2]));
+          yv = add32(yv, mult16_32_q15(g11, add32(v[1], v[3])));
+          yv = add32(yv, mult16_32_q15(g12, add32(v[0], v[4])));
+          w.etmp[i] = yv;
+        }
+      }
+      CB_WSYNC();
+      CB_LANE_LOOP(i, CB_OVERLAP / 2) {
+        i32 w0 = cb_ldg(&ct_window120[i]), w1 = cb_ldg(&ct_window120[CB_OVERLAP - i - 1]);
+        st->tail[c][i] = add32(mult16_32_q15(w0, w.etmp[CB_OVERLAP - 1 - i]), mult16_32_q15(w1, w.etmp[i]));
+      }
+      CB_WSYNC();
+    }
+    emit_frame(w.nb, N, st, c, pcm, accum);
+  }
+  CB_WSYNC();
+  st->loss_count = loss_count + 1;
+}
+
+// Noise-based concealment / comfort noise (celt_decoder.c:451-506): runs in kernel A because it only
+// needs the small state; it fills the FrameSide exactly like a decoded frame (random normalised
+// bands at the decayed energies, no post-filter) and kernel B synthesises it.
+CB_FN void celt_plc_noise(EntWork& w, CeltDecState* stg, FrameSide* side, int LM, int start, int end) {
+  const int C = stg->channels;
+  const int M = 1 << LM, N = M * 120;
+  const int effEnd = cb_imax(start, cb_imin(end, CB_NBANDS));
+  const int loss_count = stg->loss_count;
+  const i32 decay = loss_count == 0 ? 1536 : 512;          // QCONST16(1.5f,DB_SHIFT) : QCONST16(.5f,DB_SHIFT)
+  CB_WSYNC();
+  CB_LANE_LOOP(j, 2 * CB_NBANDS) {
+    i16 e = stg->oldBandE[j];
+    int band = j % CB_NBANDS, c = j / CB_NBANDS;
+    if (c < C && band >= start && band < end) {
+      e = (i16)cb_imax(stg->backgroundLogE[j], e - decay);
+      stg->oldBandE[j] = e;
+    }
+    w.bandE[j] = e;
+  }
+  u32 seed = stg->rng;
+  CB_NOUNROLL for (int c = 0; c < C; c++) {
+    CB_NOUNROLL for (int i = start; i < effEnd; i++) {
+      const int boffs = N * c + (ct_eband5ms[i] << LM);
+      const int blen = (ct_eband5ms[i + 1] - ct_eband5ms[i]) << LM;
+      const u32 seed0 = seed;
+      CB_WSYNC();
+      CB_LANE_LOOP(j, blen) w.X[boffs + j] = (i16)((i32)cb_lcg_skip(seed0, (u32)j + 1) >> 20);
+      seed = cb_lcg_skip(seed0, (u32)blen);
+      v_renormalise(w.X + boffs, blen, CB_Q15ONE);
+    }
+  }
+  CB_WSYNC();
+  CB_LANE_LOOP(j, 2 * CB_NBANDS) side->bandE[j] = w.bandE[j];
+  {
+    const u32* src = (const u32*)w.X;
+    u32* dst = (u32*)side->X;
+    CB_LANE_LOOP(j, C * N / 2) dst[j] = src[j];
+  }
+  side->kind = 1; side->LM = LM; side->C = C; side->transient = 0; side->silence = 0;
+  side->start = start; side->effEnd = effEnd;
+  side->T0 = 15; side->T1 = 15; side->T2 = 15;
+  side->g0 = 0; side->g1 = 0; side->g2 = 0;
+  side->tap0 = 0; side->tap1 = 0; side->tap2 = 0;
+  side->accum = 0;
+  stg->rng = seed;
+  stg->loss_count = loss_count + 1;
+}

@@ -309,6 +309,38 @@ CB_FN void v_comb_filter(i32* buf, int off, int n, const i32* hist, int pos, int
   CB_WSYNC();
 }
 
+// De-emphasis + PCM store + ring update for a finished frame held in buf[0..N) (shared by the
+// synthesis kernel and the concealment kernel).  celt_decoder.c:185-275.
+//  * history ring: the frame overwrites the N oldest samples;
+//  * de-emphasis is a serial one-pole IIR (m = 0.85*(x+m), truncating multiply): one lane;
+//  * SIG2WORD16 + interleaved int16 store (optionally accumulated, hybrid mode) in a lane loop.
+CB_FN void emit_frame(i32* buf, int N, CeltDecState* st, int c, i16* pcm, int accum) {
+  const int CC = st->channels, downsample = st->downsample;
+  i32* hist = st->hist[c];
+  const int pos = st->hist_pos[c];
+  CB_WSYNC();
+  CB_LANE_LOOPU(j, N) hist[(pos + j) & (CB_HIST - 1)] = buf[j];
+  CB_WSYNC();
+  CB_IF_LANE0 {
+    i32 m = st->preemph_mem[c];
+    for (int j = 0; j < N; j++) {
+      i32 tmp = add32(buf[j], m);
+      m = mult16_32_q15(27853, tmp);
+      buf[j] = tmp;
+    }
+    st->preemph_mem[c] = m;
+    st->hist_pos[c] = (pos + N) & (CB_HIST - 1);
+  }
+  CB_WSYNC();
+  const int Nd = N / downsample;
+  if (accum) {
+    CB_LANE_LOOPU(j, Nd) pcm[j * CC + c] = sat16((i32)pcm[j * CC + c] + (i32)sig2word16(buf[j * downsample]));
+  } else {
+    CB_LANE_LOOPU(j, Nd) pcm[j * CC + c] = sig2word16(buf[j * downsample]);
+  }
+  CB_WSYNC();
+}
+
 // Synthesis of output channel `c` of one stream for one frame.
 // pcm -> first sample of this frame for this stream (interleaved, CC channels).
 CB_FN void celt_synth_channel(SynWork& w, CeltDecState* st, const FrameSide* side, int c, i16* pcm) {
@@ -344,27 +376,5 @@ CB_FN void celt_synth_channel(SynWork& w, CeltDecState* st, const FrameSide* sid
   v_comb_filter(w.buf, 0, 120, hist, pos, side->T0, side->T1, side->g0, side->g1, side->tap0, side->tap1, CB_OVERLAP);
   if (LM != 0)
     v_comb_filter(w.buf, 120, N - 120, hist, pos, side->T1, side->T2, side->g1, side->g2, side->tap1, side->tap2, CB_OVERLAP);
-  CB_WSYNC();
-  // 6. history ring: the frame overwrites the N oldest samples
-  CB_LANE_LOOPU(j, N) hist[(pos + j) & (CB_HIST - 1)] = w.buf[j];
-  // 7. de-emphasis (celt_decoder.c:185-275): serial one-pole IIR, one lane
-  CB_WSYNC();
-  CB_IF_LANE0 {
-    i32 m = st->preemph_mem[c];
-    for (int j = 0; j < N; j++) {
-      i32 tmp = add32(w.buf[j], m);
-      m = mult16_32_q15(27853, tmp);
-      w.buf[j] = tmp;
-    }
-    st->preemph_mem[c] = m;
-    st->hist_pos[c] = (pos + N) & (CB_HIST - 1);
-  }
-  CB_WSYNC();
-  const int Nd = N / downsample;
-  if (side->accum) {
-    CB_LANE_LOOPU(j, Nd) pcm[j * CC + c] = sat16((i32)pcm[j * CC + c] + (i32)sig2word16(w.buf[j * downsample]));
-  } else {
-    CB_LANE_LOOPU(j, Nd) pcm[j * CC + c] = sig2word16(w.buf[j * downsample]);
-  }
-  CB_WSYNC();
+  emit_frame(w.buf, N, st, c, pcm, side->accum);
 }

@@ -3,6 +3,7 @@
 #pragma once
 #include "cb_celt_entropy.h"
 #include "cb_celt_synth.h"
+#include "cb_celt_plc.h"
 #include "cb_opus_plan.h"
 
 // Kernel A, one stream, one pass.  `pkt` = per-warp staging area for the payload bytes.
@@ -20,10 +21,26 @@ CB_FN void decode_entropy_pass(EntWork& w, u8* pkt, OpusDecState* st, StreamPlan
   const int len = pl->len[pass];
   const int nsamp = pl->nsamp[pass];
   if (kind == CB_PLAN_PLC || len <= 1) {
-    // concealment (celt_decode_lost) is not built yet: flag it, never fake it
-    side->kind = 0;
-    pl->ret = CB_UNIMPLEMENTED;
-    *ret_slot = CB_UNIMPLEMENTED;
+    // lost / DTX frame: opus_decode_frame(data=NULL) (opus_decoder.c:246-292, 579-586)
+    if (st->prev_mode == 0) {                       // nothing decoded yet: zeros for this frame
+      side->kind = 4;
+      return;
+    }
+    int LMp = 0;
+    {
+      int fs48 = nsamp * st->celt.downsample;
+      while ((120 << LMp) < fs48) LMp++;
+    }
+    const int endp = opus_bandwidth_endband(st->bandwidth);
+    if (st->celt.loss_count >= 5) {
+      celt_plc_noise(w, &st->celt, side, LMp, 0, endp);      // synthesised by kernel B
+    } else {
+      side->kind = 2;                                          // pitch-based: kernel C
+      side->LM = LMp;
+      side->accum = 0;
+    }
+    st->rangeFinal = 0;
+    st->prev_redundancy = 0;
     return;
   }
   const i32 off = pl->off[pass];
@@ -60,5 +77,17 @@ CB_FN void decode_synth_pass(SynWork& w, OpusDecState* st, const StreamPlan* pl,
   } else if (side->kind == 3 && pass == 0) {
     const int total = pl->total_samples;
     CB_LANE_LOOP(j, total) row[j * CC + c] = 0;
+  } else if (side->kind == 4) {
+    i16* p = row + (size_t)pl->pcm_off[pass] * CC;
+    const int cnt = pl->nsamp[pass];
+    CB_LANE_LOOP(j, cnt) p[j * CC + c] = 0;
   }
+}
+
+// Kernel C, one stream, one pass: pitch-based concealment (both channels) when kernel A asked for it.
+CB_FN void decode_plc_pass(PlcWork& w, OpusDecState* st, const StreamPlan* pl, const FrameSide* side,
+                           i16* row, int pass) {
+  if (side->kind != 2) return;
+  const int N = 120 << side->LM;
+  celt_plc_pitch(w, &st->celt, N, row + (size_t)pl->pcm_off[pass] * st->channels, side->accum);
 }

@@ -60,6 +60,19 @@ celt_synth_kernel(OpusDecState* const* states, const StreamPlan* plans, const Fr
   decode_synth_pass(w, st, pl, side, row, c, pass);
 }
 
+__global__ void __launch_bounds__(128)
+celt_plc_kernel(OpusDecState* const* states, const StreamPlan* plans, const FrameSide* sides, i16* pcm,
+                i32 pcm_stride, int n, int pass) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int warp = threadIdx.x >> 5;
+  const int s = blockIdx.x * 4 + warp;
+  if (s >= n) return;
+  const FrameSide* side = &sides[s];
+  if (side->kind != 2) return;
+  PlcWork& w = *reinterpret_cast<PlcWork*>(smem + (size_t)warp * sizeof(PlcWork));
+  decode_plc_pass(w, states[s], &plans[s], side, pcm + (size_t)s * pcm_stride, pass);
+}
+
 // ---- launchers (host) ------------------------------------------------------------------------
 static int g_attr_done[64];
 
@@ -85,6 +98,8 @@ static int ensure_attrs() {
   e = cudaFuncSetAttribute(celt_entropy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
   if (e != cudaSuccess) return (int)e;
   e = cudaFuncSetAttribute(celt_synth_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  if (e != cudaSuccess) return (int)e;
+  e = cudaFuncSetAttribute(celt_plc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
   if (e != cudaSuccess) return (int)e;
   if (dev < 64) g_attr_done[dev] = 1;
   return 0;
@@ -112,6 +127,11 @@ extern "C" int cbk_launch_synth(OpusDecState* const* d_states, const StreamPlan*
   const int warpsB = n * 2;
   celt_synth_kernel<<<(warpsB + B_WARPS - 1) / B_WARPS, B_WARPS * 32, smemB, stream>>>(
       d_states, d_plans, d_sides, d_pcm, pcm_stride, n, pass);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return (int)e;
+  // kernel C: warps whose stream needs no pitch-based concealment exit at once
+  celt_plc_kernel<<<(n + 3) / 4, 128, sizeof(PlcWork) * 4, stream>>>(d_states, d_plans, d_sides, d_pcm, pcm_stride,
+                                                                   n, pass);
   return (int)cudaGetLastError();
 }
 

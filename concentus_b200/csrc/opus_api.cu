@@ -375,11 +375,12 @@ int opus_decode_group_device(OpusDecoderGroup* g, const unsigned char* d_data, c
 }
 
 // Upper bound on the passes a batch needs, from the packets themselves (host side, O(n) byte reads).
-static int scan_passes(const unsigned char* data, const i32* off, const i32* len, int n, int frame_size, int Fs_hint,
-                       int* max_len) {
+static int scan_passes(const unsigned char* data, const i32* off, const i32* len, const int* fec, int n,
+                       int frame_size, int Fs_hint, int* max_len) {
   int passes = 1, mlen = 0, any_lost = 0;
   for (int i = 0; i < n; i++) {
     if (off[i] < 0 || len[i] <= 0) { any_lost = 1; continue; }
+    if (fec && fec[i]) any_lost = 1;       // an FEC request on a CELT stream is served by concealment chunks
     if (len[i] > mlen) mlen = len[i];
     int nf = opus_packet_get_nb_frames(data + off[i], len[i]);
     if (nf > passes) passes = nf;
@@ -417,7 +418,7 @@ int opus_decode_group_flat(OpusDecoderGroup* g, const unsigned char* data, opus_
   DevCtx* c = ctx_for_current_device(&err);
   if (!c) return err;
   int max_len = 0;
-  int passes = scan_passes(data, offsets, len, n, frame_size, g->Fs, &max_len);
+  int passes = scan_passes(data, offsets, len, decode_fec, n, frame_size, g->Fs, &max_len);
   const size_t pkt_bytes = (size_t)data_bytes + 16;
   const size_t pcm_bytes = (size_t)n * pcm_stride * sizeof(i16);
   const size_t i32_bytes = (size_t)n * 3 * sizeof(i32);

@@ -46,6 +46,7 @@ int emu_opus_decode(void* state, const unsigned char* data, int len, short* pcm,
   static EntWork ew;
   static SynWork sw;
   static FrameSide side;
+  static PlcWork pw;
   static unsigned char pkt[1600];
   StreamPlan pl;
   i32 ret = 0;
@@ -54,6 +55,7 @@ int emu_opus_decode(void* state, const unsigned char* data, int len, short* pcm,
   for (int pass = 0; pass < pl.nframes; pass++) {
     decode_entropy_pass(ew, pkt, st, &pl, &side, data, &ret, pass);
     for (int c = 0; c < st->channels; c++) decode_synth_pass(sw, st, &pl, &side, pcm, c, pass);
+    decode_plc_pass(pw, st, &pl, &side, pcm, pass);
   }
   return ret;
 }

@@ -1,0 +1,54 @@
+"""Host-logic check (lane-loop emulation of the kernel sources, CPU) of the Opus layer and the
+concealment code against the compiled reference: losses, DTX, FEC requests, multi-frame packets,
+corrupted and truncated packets.  Return value, PCM and final range must all be identical."""
+import ctypes
+
+import numpy as np
+import pytest
+
+from conftest import RefDecoder, needs_ref
+from scenarios import fuzz_scenario, loss_scenario
+
+LOSS = ["c2_96k_cbr_st", "vbr_128k_st", "f10_64k_st", "f2_5_96k_st", "mono_12k", "low_24k_st",
+        "st_to_mono_out", "mono_to_st_out", "st_to_24k_out", "mono_to_16k_out", "nb_20k_mono"]
+FUZZ = ["c2_96k_cbr_st", "vbr_128k_st", "f5_64k_st", "f2_5_96k_st", "mono_64k", "low_24k_st",
+        "st_to_24k_out", "mono_to_st_out"]
+
+
+def _run(emu_lib, meta, calls):
+    emu_lib.emu_opus_create.restype = ctypes.c_void_p
+    emu_lib.emu_opus_create.argtypes = [ctypes.c_int, ctypes.c_int]
+    emu_lib.emu_opus_destroy.argtypes = [ctypes.c_void_p]
+    emu_lib.emu_opus_decode.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int, ctypes.c_void_p,
+                                        ctypes.c_int, ctypes.c_int]
+    emu_lib.emu_opus_final_range.argtypes = [ctypes.c_void_p]
+    emu_lib.emu_opus_final_range.restype = ctypes.c_uint
+    fs, ch = meta["fs"], meta["channels"]
+    ref = RefDecoder(fs, ch)
+    st = emu_lib.emu_opus_create(fs, ch)
+    try:
+        for n, (data, fsz, fec) in enumerate(calls):
+            ra, pa = ref.decode_raw(data, fsz, fec)
+            pb = np.zeros((fsz, ch), dtype=np.int16)
+            rb = emu_lib.emu_opus_decode(st, data, len(data) if data else 0, pb.ctypes.data, fsz, fec)
+            assert ra == rb, "return value, call %d" % n
+            if ra > 0:
+                assert np.array_equal(pa[:ra], pb[:ra]), "pcm, call %d" % n
+            assert ref.final_range == emu_lib.emu_opus_final_range(st), "final range, call %d" % n
+    finally:
+        emu_lib.emu_opus_destroy(st)
+
+
+@needs_ref
+@pytest.mark.parametrize("name", LOSS)
+def test_emu_loss_concealment(emu_lib, name):
+    meta, calls = loss_scenario(name, seed=len(name) * 7 + 1)
+    assert sum(1 for d, _, f in calls if d is None or len(d) <= 1 or f) > 20
+    _run(emu_lib, meta, calls)
+
+
+@needs_ref
+@pytest.mark.parametrize("name", FUZZ)
+def test_emu_multiframe_and_corruption(emu_lib, name):
+    meta, calls = fuzz_scenario(name, seed=len(name) + 3)
+    _run(emu_lib, meta, calls)
