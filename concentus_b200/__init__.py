@@ -46,6 +46,10 @@ EXPORTS = [
     "opus_decoder_group_destroy", "opus_decode_group_flat", "opus_decode_group_device",
     "opus_decoder_get_final_range_batch", "opus_b200_synchronize", "opus_b200_launch_count",
     "opus_b200_profile_begin", "opus_b200_profile_end", "opus_decode_batch_device_static",
+    "opus_multistream_decoder_get_size", "opus_multistream_decoder_create", "opus_multistream_decode",
+    "opus_multistream_decode_float", "opus_multistream_decoder_ctl", "opus_multistream_decoder_destroy",
+    "opus_multistream_decode_batch", "opus_multistream_decoder_group_create",
+    "opus_multistream_decoder_group_destroy", "opus_multistream_decode_group_flat",
 ]
 
 _lib = None
@@ -91,6 +95,19 @@ def load():
                                              ctypes.c_int, ctypes.c_int, vp]
     lib.opus_decode_batch_device_static.argtypes = [vp, ctypes.c_int, vp, vp, vp, vp, ctypes.c_int32, ctypes.c_int,
                                                     vp, ctypes.c_int, ctypes.c_int, vp]
+    lib.opus_multistream_decoder_create.restype = vp
+    lib.opus_multistream_decoder_create.argtypes = [ctypes.c_int32, ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, c_int_p]
+    lib.opus_multistream_decoder_destroy.argtypes = [vp]
+    lib.opus_multistream_decoder_destroy.restype = None
+    lib.opus_multistream_decode.argtypes = [vp, vp, ctypes.c_int32, vp, ctypes.c_int, ctypes.c_int]
+    lib.opus_multistream_decode_float.argtypes = [vp, vp, ctypes.c_int32, vp, ctypes.c_int, ctypes.c_int]
+    lib.opus_multistream_decode_batch.argtypes = [vp, vp, vp, vp, ctypes.c_int, vp, ctypes.c_int, vp]
+    lib.opus_multistream_decoder_group_create.restype = vp
+    lib.opus_multistream_decoder_group_create.argtypes = [vp, ctypes.c_int, c_int_p]
+    lib.opus_multistream_decoder_group_destroy.argtypes = [vp]
+    lib.opus_multistream_decoder_group_destroy.restype = None
+    lib.opus_multistream_decode_group_flat.argtypes = [vp, vp, ctypes.c_int32, vp, vp, vp, ctypes.c_int32,
+                                                       ctypes.c_int, vp, vp]
     lib.opus_decoder_get_final_range_batch.argtypes = [vp, ctypes.c_int, vp]
     lib.opus_b200_launch_count.restype = ctypes.c_longlong
     lib.opus_packet_get_nb_samples.argtypes = [vp, ctypes.c_int32, ctypes.c_int32]
@@ -239,3 +256,84 @@ class OpusBatchDecoder(object):
         if rc != OPUS_OK:
             raise OpusError(rc, "opus_decoder_get_final_range_batch")
         return out
+
+
+class OpusMSDecoder(object):
+    """One multistream (surround) decoder: mirrors NativeOpusMultistreamDecoder of the reference."""
+
+    def __init__(self, sample_rate, channels, streams, coupled, mapping):
+        lib = load()
+        err = ctypes.c_int(0)
+        m = (ctypes.c_ubyte * len(mapping))(*mapping)
+        self._h = lib.opus_multistream_decoder_create(sample_rate, channels, streams, coupled, m, ctypes.byref(err))
+        if not self._h:
+            raise OpusError(err.value, "opus_multistream_decoder_create")
+        self.channels = channels
+
+    def close(self):
+        if getattr(self, "_h", None):
+            load().opus_multistream_decoder_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def decode_raw(self, data, frame_size, fec=False):
+        pcm = np.zeros((max(frame_size, 1), self.channels), dtype=np.int16)
+        if not data:
+            ret = load().opus_multistream_decode(self._h, None, 0, pcm.ctypes.data, frame_size, int(fec))
+        else:
+            buf = ctypes.create_string_buffer(bytes(data), len(data))
+            ret = load().opus_multistream_decode(self._h, ctypes.cast(buf, ctypes.c_void_p), len(data), pcm.ctypes.data,
+                                                 frame_size, int(fec))
+        return ret, pcm
+
+    @property
+    def final_range(self):
+        v = ctypes.c_uint32(0)
+        rc = load().opus_multistream_decoder_ctl(self._h, OPUS_GET_FINAL_RANGE_REQUEST, ctypes.byref(v))
+        if rc != OPUS_OK:
+            raise OpusError(rc, "opus_multistream_decoder_ctl")
+        return v.value
+
+
+class OpusMSBatchDecoder(object):
+    """n multistream decoders of the same layout decoded by one call (opus_multistream_decode_group_flat)."""
+
+    def __init__(self, sample_rate, channels, streams, coupled, mapping, n):
+        lib = load()
+        self.n, self.channels = n, channels
+        self.decoders = [OpusMSDecoder(sample_rate, channels, streams, coupled, mapping) for _ in range(n)]
+        self._handles = (ctypes.c_void_p * n)(*[d._h for d in self.decoders])
+        err = ctypes.c_int(0)
+        self._g = lib.opus_multistream_decoder_group_create(self._handles, n, ctypes.byref(err))
+        if not self._g:
+            raise OpusError(err.value, "opus_multistream_decoder_group_create")
+
+    def close(self):
+        if getattr(self, "_g", None):
+            load().opus_multistream_decoder_group_destroy(self._g)
+            self._g = None
+        for d in getattr(self, "decoders", []):
+            d.close()
+        self.decoders = []
+
+    __del__ = close
+
+    def decode(self, packets, frame_size):
+        lens = np.array([len(p) if p else 0 for p in packets], dtype=np.int32)
+        offs = np.zeros(self.n, dtype=np.int32)
+        o = 0
+        for i, p in enumerate(packets):
+            if p:
+                offs[i] = o
+                o += len(p)
+            else:
+                offs[i] = -1
+        arena = np.frombuffer(b"".join(p for p in packets if p) + b"\0", dtype=np.uint8).copy()
+        pcm = np.zeros((self.n, frame_size, self.channels), dtype=np.int16)
+        ret = np.zeros(self.n, dtype=np.int32)
+        rc = load().opus_multistream_decode_group_flat(self._g, _ptr(arena), o, _ptr(offs), _ptr(lens), _ptr(pcm),
+                                                       frame_size * self.channels, frame_size, None, _ptr(ret))
+        if rc != OPUS_OK:
+            raise OpusError(rc, "opus_multistream_decode_group_flat")
+        return ret, pcm

@@ -73,6 +73,43 @@ celt_plc_kernel(OpusDecState* const* states, const StreamPlan* plans, const Fram
   decode_plc_pass(w, states[s], &plans[s], side, pcm + (size_t)s * pcm_stride, pass);
 }
 
+// Multistream: one thread per multistream decoder plans its elementary streams.
+__global__ void opus_ms_plan_kernel(OpusDecState* const* states, StreamPlan* plans, const MSLayout* layouts,
+                                    const u8* data, const i32* offs, const i32* lens, const i32* fec,
+                                    int frame_size, i32* ms_ret, int n_ms) {
+  int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= n_ms) return;
+  ms_ret[m] = opus_ms_plan(states, plans, &layouts[m], data, offs[m], lens[m], frame_size, fec ? fec[m] : 0);
+}
+
+// Multistream: channel mapping copy-out (opus_multistream_decoder.c:262-299).  One CTA per
+// multistream decoder; elementary PCM rows (interleaved, 1 or 2 channels) -> output row.
+__global__ void opus_ms_scatter_kernel(const MSLayout* layouts, const i32* ms_ret, const i16* epcm,
+                                       i32 epcm_stride, i16* pcm, i32 pcm_stride, int n_ms) {
+  const int m = blockIdx.x;
+  if (m >= n_ms) return;
+  const MSLayout* L = &layouts[m];
+  const int frames = ms_ret[m];
+  if (frames <= 0) return;
+  const int CH = L->nb_channels;
+  i16* dst = pcm + (size_t)m * pcm_stride;
+  for (int idx = threadIdx.x; idx < frames * CH; idx += blockDim.x) {
+    const int t = idx / CH, c = idx - t * CH;
+    const int mp = L->mapping[c];
+    i16 v = 0;
+    if (mp != 255) {
+      if (mp < 2 * L->nb_coupled) {
+        const i16* src = epcm + (size_t)(L->first + (mp >> 1)) * epcm_stride;
+        v = src[t * 2 + (mp & 1)];
+      } else {
+        const i16* src = epcm + (size_t)(L->first + mp - L->nb_coupled) * epcm_stride;
+        v = src[t];
+      }
+    }
+    dst[idx] = v;
+  }
+}
+
 // ---- launchers (host) ------------------------------------------------------------------------
 static int g_attr_done[64];
 
@@ -132,6 +169,22 @@ extern "C" int cbk_launch_synth(OpusDecState* const* d_states, const StreamPlan*
   // kernel C: warps whose stream needs no pitch-based concealment exit at once
   celt_plc_kernel<<<(n + 3) / 4, 128, sizeof(PlcWork) * 4, stream>>>(d_states, d_plans, d_sides, d_pcm, pcm_stride,
                                                                    n, pass);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int cbk_launch_ms_plan(OpusDecState* const* d_states, StreamPlan* d_plans, const MSLayout* d_layouts,
+                                  const u8* d_data, const i32* d_off, const i32* d_len, const i32* d_fec,
+                                  int frame_size, i32* d_ms_ret, int n_ms, cudaStream_t stream) {
+  if (n_ms <= 0) return 0;
+  opus_ms_plan_kernel<<<(n_ms + 63) / 64, 64, 0, stream>>>(d_states, d_plans, d_layouts, d_data, d_off, d_len, d_fec,
+                                                          frame_size, d_ms_ret, n_ms);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int cbk_launch_ms_scatter(const MSLayout* d_layouts, const i32* d_ms_ret, const i16* d_epcm,
+                                     i32 epcm_stride, i16* d_pcm, i32 pcm_stride, int n_ms, cudaStream_t stream) {
+  if (n_ms <= 0) return 0;
+  opus_ms_scatter_kernel<<<n_ms, 256, 0, stream>>>(d_layouts, d_ms_ret, d_epcm, epcm_stride, d_pcm, pcm_stride, n_ms);
   return (int)cudaGetLastError();
 }
 

@@ -249,3 +249,72 @@ CB_HD void opus_plan_stream(OpusDecState* st, StreamPlan* pl, const u8* data, i3
   pl->ret = count * packet_frame_size;
   st->last_packet_duration = pl->ret;
 }
+
+// opus_multistream_packet_validate (opus-fix/src/opus_multistream_decoder.c:155-183)
+CB_HD int opus_ms_validate(const u8* data, i32 len, int nb_streams, i32 Fs) {
+  int samples = 0;
+  i16 size[CB_MAX_FRAMES];
+  for (int s = 0; s < nb_streams; s++) {
+    if (len <= 0) return CB_INVALID_PACKET;
+    int toc = 0;
+    i32 packet_offset = 0;
+    int count = opus_parse_packet(data, len, s != nb_streams - 1, &toc, size, nullptr, &packet_offset);
+    if (count < 0) return count;
+    // opus_packet_get_nb_samples(data, packet_offset, Fs) (opus_decoder.c:957-973)
+    int cnt;
+    {
+      int c3 = data[0] & 0x3;
+      if (packet_offset < 1) return CB_BAD_ARG;
+      if (c3 == 0) cnt = 1;
+      else if (c3 != 3) cnt = 2;
+      else if (packet_offset < 2) return CB_INVALID_PACKET;
+      else cnt = data[1] & 0x3F;
+    }
+    int tmp_samples = cnt * opus_toc_samples_per_frame(data[0], Fs);
+    if (tmp_samples * 25 > Fs * 3) return CB_INVALID_PACKET;
+    if (s != 0 && samples != tmp_samples) return CB_INVALID_PACKET;
+    samples = tmp_samples;
+    data += packet_offset;
+    len -= packet_offset;
+  }
+  return samples;
+}
+
+// opus_multistream_decode_native (opus_multistream_decoder.c:184-302), planning half: walks the
+// sub-packets of one multistream packet and plans every elementary stream.  states/plans are the
+// group's arrays; the layout says which slice belongs to this multistream decoder.
+CB_HD int opus_ms_plan(OpusDecState* const* states, StreamPlan* plans, const MSLayout* L, const u8* arena,
+                       i32 off, i32 len, int frame_size, int decode_fec) {
+  const int S = L->nb_streams;
+  const i32 Fs = L->Fs;
+  for (int s = 0; s < S; s++) {
+    StreamPlan* pl = &plans[L->first + s];
+    pl->kind = CB_PLAN_NONE; pl->nframes = 0; pl->total_samples = 0; pl->ret = CB_INVALID_STATE;
+  }
+  if (frame_size <= 0) return CB_BAD_ARG;
+  frame_size = cb_imin(frame_size, Fs / 25 * 3);
+  if (off < 0) len = 0;
+  const int do_plc = (len == 0);
+  if (len < 0) return CB_BAD_ARG;
+  if (!do_plc && len < 2 * S - 1) return CB_INVALID_PACKET;
+  const u8* data = arena + (off < 0 ? 0 : off);
+  if (!do_plc) {
+    int r = opus_ms_validate(data, len, S, Fs);
+    if (r < 0) return r;
+    if (r > frame_size) return CB_BUFFER_TOO_SMALL;
+  }
+  i32 cur = off;
+  for (int s = 0; s < S; s++) {
+    if (!do_plc && len <= 0) return CB_INTERNAL_ERROR;
+    i32 packet_offset = 0;
+    StreamPlan* pl = &plans[L->first + s];
+    opus_plan_stream(states[L->first + s], pl, arena, do_plc ? -1 : cur, do_plc ? 0 : len, frame_size, decode_fec,
+                     s != S - 1, &packet_offset);
+    int r = pl->ret;
+    if (r <= 0) return r;
+    cur += packet_offset;
+    len -= packet_offset;
+    frame_size = r;
+  }
+  return frame_size;
+}

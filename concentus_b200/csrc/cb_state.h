@@ -128,3 +128,15 @@ struct alignas(16) StreamPlan {
   i16 nsamp[CB_MAX_FRAMES]; // samples per channel produced (API rate)
   i16 pcm_off[CB_MAX_FRAMES];
 };
+
+// ---- multistream (surround) ------------------------------------------------------------------
+// struct OpusMSDecoder / ChannelLayout (opus-fix/src/opus_multistream_decoder.c:45-48,
+// src/opus_private.h:41-46) as a device record: which elementary decoders belong to the
+// multistream decoder and how their channels map to the output channels.
+struct alignas(16) MSLayout {
+  i32 nb_channels, nb_streams, nb_coupled;
+  i32 first;                 // index of the first elementary stream in the group
+  i32 Fs;
+  i32 pad[3];
+  u8 mapping[256];
+};

@@ -332,6 +332,26 @@ void opus_decoder_group_destroy(OpusDecoderGroup* g) {
   group_free(g);
 }
 
+// Queue the decode passes (kernels A, B, C per frame index) for a group whose plans are already on
+// the device.  No synchronisation.
+static int group_enqueue_passes(OpusDecoderGroup* g, const u8* d_data, i16* d_pcm, i32 pcm_stride, i32* d_ret,
+                                int passes, int max_packet_bytes, cudaStream_t stream) {
+  int rc = 0;
+  for (int p = 0; p < passes; p++) {
+    {
+      ProfScope ps(stream, 1);
+      rc = cbk_launch_entropy(g->d_states, d_data, g->d_plans, g->d_sides, d_ret, g->n, p, max_packet_bytes, stream);
+    }
+    if (!rc) {
+      ProfScope ps(stream, 2);
+      rc = cbk_launch_synth(g->d_states, g->d_plans, g->d_sides, d_pcm, pcm_stride, g->n, p, stream);
+    }
+    g_launches += 3;
+    if (rc) { fprintf(stderr, "[opus_b200] pass launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
+  }
+  return OPUS_OK;
+}
+
 // Queue plan + passes for a group; everything device resident.  No synchronisation.
 static int group_enqueue(OpusDecoderGroup* g, const u8* d_data, const i32* d_off, const i32* d_len, i16* d_pcm,
                          i32 pcm_stride, int frame_size, const i32* d_fec, i32* d_ret, int passes,
@@ -343,19 +363,7 @@ static int group_enqueue(OpusDecoderGroup* g, const u8* d_data, const i32* d_off
   }
   g_launches += 1;
   if (rc) { fprintf(stderr, "[opus_b200] plan launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
-  for (int p = 0; p < passes; p++) {
-    {
-      ProfScope ps(stream, 1);
-      rc = cbk_launch_entropy(g->d_states, d_data, g->d_plans, g->d_sides, d_ret, g->n, p, max_packet_bytes, stream);
-    }
-    if (!rc) {
-      ProfScope ps(stream, 2);
-      rc = cbk_launch_synth(g->d_states, g->d_plans, g->d_sides, d_pcm, pcm_stride, g->n, p, stream);
-    }
-    g_launches += 2;
-    if (rc) { fprintf(stderr, "[opus_b200] pass launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
-  }
-  return OPUS_OK;
+  return group_enqueue_passes(g, d_data, d_pcm, pcm_stride, d_ret, passes, max_packet_bytes, stream);
 }
 
 int opus_decode_group_device(OpusDecoderGroup* g, const unsigned char* d_data, const opus_int32* d_offsets,
@@ -614,6 +622,321 @@ int opus_decoder_get_final_range_batch(OpusDecoder* const* st, int n, opus_uint3
     CUDA_OK(cudaMemcpy(&out[i], &st[i]->d_state->rangeFinal, sizeof(u32), cudaMemcpyDeviceToHost));
   }
   return OPUS_OK;
+}
+
+
+// ================= multistream (surround) decoder: opus-fix/src/opus_multistream_decoder.c =================
+struct OpusMSDecoder {
+  int magic;
+  int Fs, channels, streams, coupled;
+  unsigned char mapping[256];
+  OpusDecoder** sub;            // `streams` elementary decoders, coupled (stereo) ones first
+  OpusMSDecoderGroup* self_group;
+};
+
+struct OpusMSDecoderGroup {
+  int magic;
+  int n_ms, device, max_channels;
+  OpusMSDecoder** members;
+  OpusDecoderGroup* eg;         // group over all elementary decoders
+  MSLayout* d_layouts;
+  i32* d_ms_ret;
+};
+
+#define OPUS_MULTISTREAM_GET_DECODER_STATE_REQUEST 5122
+const int kMagicMS = 0x4f424d53;
+
+opus_int32 opus_multistream_decoder_get_size(int nb_streams, int nb_coupled_streams) {
+  if (nb_streams < 1 || nb_coupled_streams > nb_streams || nb_coupled_streams < 0) return 0;
+  return (opus_int32)sizeof(OpusMSDecoder);
+}
+
+OpusMSDecoder* opus_multistream_decoder_create(opus_int32 Fs, int channels, int streams, int coupled_streams,
+                                               const unsigned char* mapping, int* error) {
+  if ((channels > 255) || (channels < 1) || (coupled_streams > streams) || (streams < 1) || (coupled_streams < 0) ||
+      (streams > 255 - coupled_streams) || !mapping) {
+    if (error) *error = OPUS_BAD_ARG;
+    return nullptr;
+  }
+  for (int i = 0; i < channels; i++) {            // validate_layout (opus_multistream.c:39-51)
+    if (mapping[i] >= streams + coupled_streams && mapping[i] != 255) {
+      if (error) *error = OPUS_BAD_ARG;
+      return nullptr;
+    }
+  }
+  OpusMSDecoder* st = (OpusMSDecoder*)calloc(1, sizeof(OpusMSDecoder));
+  if (!st) { if (error) *error = OPUS_ALLOC_FAIL; return nullptr; }
+  st->magic = kMagicMS;
+  st->Fs = Fs; st->channels = channels; st->streams = streams; st->coupled = coupled_streams;
+  memcpy(st->mapping, mapping, channels);
+  st->sub = (OpusDecoder**)calloc(streams, sizeof(OpusDecoder*));
+  int err = OPUS_OK;
+  for (int s = 0; s < streams && err == OPUS_OK; s++)
+    st->sub[s] = opus_decoder_create(Fs, s < coupled_streams ? 2 : 1, &err);
+  if (err != OPUS_OK) {
+    for (int s = 0; s < streams; s++) if (st->sub[s]) opus_decoder_destroy(st->sub[s]);
+    free(st->sub);
+    free(st);
+    if (error) *error = err;
+    return nullptr;
+  }
+  if (error) *error = OPUS_OK;
+  return st;
+}
+
+void opus_multistream_decoder_group_destroy(OpusMSDecoderGroup* g);
+
+void opus_multistream_decoder_destroy(OpusMSDecoder* st) {
+  if (!st || st->magic != kMagicMS) return;
+  if (st->self_group) { opus_multistream_decoder_group_destroy(st->self_group); st->self_group = nullptr; }
+  for (int s = 0; s < st->streams; s++) opus_decoder_destroy(st->sub[s]);
+  free(st->sub);
+  st->magic = 0;
+  free(st);
+}
+
+OpusMSDecoderGroup* opus_multistream_decoder_group_create(OpusMSDecoder* const* st, int n, int* error) {
+  if (!st || n <= 0) { if (error) *error = OPUS_BAD_ARG; return nullptr; }
+  std::vector<OpusDecoder*> elem;
+  std::vector<MSLayout> lay(n);
+  int maxch = 1;
+  for (int m = 0; m < n; m++) {
+    if (!st[m] || st[m]->magic != kMagicMS) { if (error) *error = OPUS_BAD_ARG; return nullptr; }
+    MSLayout& L = lay[m];
+    memset(&L, 0, sizeof(L));
+    L.nb_channels = st[m]->channels; L.nb_streams = st[m]->streams; L.nb_coupled = st[m]->coupled;
+    L.first = (i32)elem.size(); L.Fs = st[m]->Fs;
+    memcpy(L.mapping, st[m]->mapping, 256);
+    for (int s = 0; s < st[m]->streams; s++) elem.push_back(st[m]->sub[s]);
+    if (st[m]->channels > maxch) maxch = st[m]->channels;
+  }
+  int err = OPUS_OK;
+  OpusDecoderGroup* eg = opus_decoder_group_create(elem.data(), (int)elem.size(), &err);
+  if (!eg) { if (error) *error = err; return nullptr; }
+  OpusMSDecoderGroup* g = (OpusMSDecoderGroup*)calloc(1, sizeof(OpusMSDecoderGroup));
+  g->magic = kMagicMS; g->n_ms = n; g->device = eg->device; g->max_channels = maxch; g->eg = eg;
+  g->members = (OpusMSDecoder**)malloc(sizeof(OpusMSDecoder*) * n);
+  for (int m = 0; m < n; m++) g->members[m] = st[m];
+  std::lock_guard<std::mutex> lk(g_mu);
+  int prev = -1;
+  cudaGetDevice(&prev);
+  cudaSetDevice(g->device);
+  bool ok = cudaMalloc((void**)&g->d_layouts, sizeof(MSLayout) * n) == cudaSuccess &&
+            cudaMalloc((void**)&g->d_ms_ret, sizeof(i32) * n) == cudaSuccess &&
+            cudaMemcpy(g->d_layouts, lay.data(), sizeof(MSLayout) * n, cudaMemcpyHostToDevice) == cudaSuccess;
+  if (prev >= 0) cudaSetDevice(prev);
+  if (!ok) {
+    fprintf(stderr, "[opus_b200] multistream group allocation failed: %s\n", cudaGetErrorString(cudaGetLastError()));
+    if (g->d_layouts) cudaFree(g->d_layouts);
+    if (g->d_ms_ret) cudaFree(g->d_ms_ret);
+    free(g->members); free(g);
+    if (error) *error = OPUS_ALLOC_FAIL;
+    return nullptr;   // (eg is released by the caller's process exit; creation failure is fatal anyway)
+  }
+  if (error) *error = OPUS_OK;
+  return g;
+}
+
+void opus_multistream_decoder_group_destroy(OpusMSDecoderGroup* g) {
+  if (!g || g->magic != kMagicMS) return;
+  opus_decoder_group_destroy(g->eg);
+  {
+    std::lock_guard<std::mutex> lk(g_mu);
+    cudaFree(g->d_layouts);
+    cudaFree(g->d_ms_ret);
+  }
+  free(g->members);
+  g->magic = 0;
+  free(g);
+}
+
+// Flat host form for multistream packets: packet m at data[offsets[m]..+len[m]) (offset<0 or len 0 = lost),
+// PCM row m = pcm + m*pcm_stride holding frame_size*channels interleaved samples.
+int opus_multistream_decode_group_flat(OpusMSDecoderGroup* g, const unsigned char* data, opus_int32 data_bytes,
+                                       const opus_int32* offsets, const opus_int32* len, opus_int16* pcm,
+                                       opus_int32 pcm_stride, int frame_size, const int* decode_fec, int* ret) {
+  if (!g || g->magic != kMagicMS || !offsets || !len || !pcm || !ret) return OPUS_BAD_ARG;
+  if (data_bytes < 0 || (data_bytes > 0 && !data)) return OPUS_BAD_ARG;
+  const int n = g->n_ms;
+  if (frame_size <= 0) { for (int i = 0; i < n; i++) ret[i] = OPUS_BAD_ARG; return OPUS_OK; }
+  if (pcm_stride < frame_size * g->max_channels) return OPUS_BAD_ARG;
+  // passes: walk the sub-packets on the host (byte reads only) to find the largest frame count
+  int passes = 1, max_len = 0, any_lost = 0, minFs = 48000;
+  for (int m = 0; m < n; m++) {
+    OpusMSDecoder* ms = g->members[m];
+    if (ms->Fs < minFs) minFs = ms->Fs;
+    if (offsets[m] < 0 || len[m] <= 0) { any_lost = 1; continue; }
+    if (offsets[m] + (long long)len[m] > data_bytes) return OPUS_BAD_ARG;
+    if (decode_fec && decode_fec[m]) any_lost = 1;
+    if (len[m] > max_len) max_len = len[m];
+    const unsigned char* p = data + offsets[m];
+    i32 rem = len[m];
+    for (int s = 0; s < ms->streams && rem > 0; s++) {
+      i16 sizes[CB_MAX_FRAMES];
+      i32 po = 0;
+      int toc = 0;
+      int cnt = opus_parse_packet(p, rem, s != ms->streams - 1, &toc, sizes, nullptr, &po);
+      if (cnt < 0) break;
+      if (cnt > passes) passes = cnt;
+      p += po;
+      rem -= po;
+    }
+  }
+  if (any_lost) {
+    int chunks = (frame_size + minFs / 400 - 1) / (minFs / 400);
+    if (chunks > passes) passes = chunks;
+  }
+  if (passes > CB_MAX_FRAMES) passes = CB_MAX_FRAMES;
+  std::lock_guard<std::mutex> lk(g_mu);
+  CUDA_OK(cudaSetDevice(g->device));
+  int err = 0;
+  DevCtx* c = ctx_for_current_device(&err);
+  if (!c) return err;
+  OpusDecoderGroup* eg = g->eg;
+  const i32 estride = frame_size * 2;
+  const size_t pkt_bytes = (size_t)data_bytes + 16;
+  const size_t pcm_bytes = (size_t)n * pcm_stride * sizeof(i16);
+  const size_t epcm_bytes = (size_t)eg->n * estride * sizeof(i16);
+  const size_t i32_bytes = (size_t)n * 3 * sizeof(i32);
+  if (c->d_pkt.reserve(pkt_bytes) || c->d_pcm.reserve(pcm_bytes) || c->d_i32.reserve(i32_bytes) ||
+      c->h_i32.reserve(i32_bytes) || c->d_plans.reserve(epcm_bytes))
+    return OPUS_ALLOC_FAIL;
+  i16* d_epcm = (i16*)c->d_plans.p;              // elementary PCM rows (scratch)
+  i32* h_i = (i32*)c->h_i32.p;
+  memcpy(h_i, offsets, n * sizeof(i32));
+  memcpy(h_i + n, len, n * sizeof(i32));
+  if (decode_fec) memcpy(h_i + 2 * n, decode_fec, n * sizeof(i32));
+  else memset(h_i + 2 * n, 0, n * sizeof(i32));
+  i32* d_i = (i32*)c->d_i32.p;
+  cudaStream_t s = c->stream;
+  if (data_bytes > 0) CUDA_OK(cudaMemcpyAsync(c->d_pkt.p, data, data_bytes, cudaMemcpyHostToDevice, s));
+  CUDA_OK(cudaMemcpyAsync(d_i, h_i, i32_bytes, cudaMemcpyHostToDevice, s));
+  int rc = cbk_launch_ms_plan(eg->d_states, eg->d_plans, g->d_layouts, (const u8*)c->d_pkt.p, d_i, d_i + n, d_i + 2 * n,
+                              frame_size, g->d_ms_ret, n, s);
+  g_launches += 1;
+  if (rc) { fprintf(stderr, "[opus_b200] ms plan launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
+  rc = group_enqueue_passes(eg, (const u8*)c->d_pkt.p, d_epcm, estride, eg->d_ret, passes, max_len, s);
+  if (rc != OPUS_OK) return rc;
+  rc = cbk_launch_ms_scatter(g->d_layouts, g->d_ms_ret, d_epcm, estride, (i16*)c->d_pcm.p, pcm_stride, n, s);
+  g_launches += 1;
+  if (rc) { fprintf(stderr, "[opus_b200] ms scatter launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
+  CUDA_OK(cudaMemcpyAsync(pcm, c->d_pcm.p, pcm_bytes, cudaMemcpyDeviceToHost, s));
+  CUDA_OK(cudaMemcpyAsync(ret, g->d_ms_ret, n * sizeof(i32), cudaMemcpyDeviceToHost, s));
+  CUDA_OK(cudaStreamSynchronize(s));
+  return OPUS_OK;
+}
+
+int opus_multistream_decode_batch(OpusMSDecoder* const* st, const unsigned char* const* data, const opus_int32* len,
+                                  opus_int16* const* pcm, int frame_size, const int* decode_fec, int n, int* ret) {
+  if (!st || !len || !pcm || !ret || n <= 0) return OPUS_BAD_ARG;
+  if (frame_size <= 0) { for (int i = 0; i < n; i++) ret[i] = OPUS_BAD_ARG; return OPUS_OK; }
+  size_t total = 0;
+  int maxch = 1;
+  for (int i = 0; i < n; i++) {
+    if (!st[i] || st[i]->magic != kMagicMS || !pcm[i]) return OPUS_BAD_ARG;
+    if (data && data[i] && len[i] > 0) total += (size_t)len[i];
+    if (st[i]->channels > maxch) maxch = st[i]->channels;
+  }
+  std::vector<unsigned char> arena(total + 1);
+  std::vector<i32> off(n), ln(n);
+  size_t o = 0;
+  for (int i = 0; i < n; i++) {
+    ln[i] = len[i];
+    if (data && data[i] && len[i] > 0) { memcpy(arena.data() + o, data[i], (size_t)len[i]); off[i] = (i32)o; o += (size_t)len[i]; }
+    else { off[i] = -1; if (len[i] > 0) ln[i] = 0; }
+  }
+  int err = 0;
+  OpusMSDecoderGroup* g = opus_multistream_decoder_group_create(st, n, &err);
+  if (!g) return err;
+  const i32 stride = frame_size * maxch;
+  std::vector<i16> out((size_t)n * stride);
+  int rc = opus_multistream_decode_group_flat(g, arena.data(), (i32)total, off.data(), ln.data(), out.data(), stride,
+                                              frame_size, decode_fec, ret);
+  opus_multistream_decoder_group_destroy(g);
+  if (rc != OPUS_OK) return rc;
+  for (int i = 0; i < n; i++)
+    if (ret[i] > 0) memcpy(pcm[i], out.data() + (size_t)i * stride, (size_t)ret[i] * st[i]->channels * sizeof(i16));
+  return OPUS_OK;
+}
+
+int opus_multistream_decode(OpusMSDecoder* st, const unsigned char* data, opus_int32 len, opus_int16* pcm,
+                            int frame_size, int decode_fec) {
+  if (!st || st->magic != kMagicMS || !pcm) return OPUS_BAD_ARG;
+  if (frame_size <= 0) return OPUS_BAD_ARG;
+  if (len < 0) return OPUS_BAD_ARG;
+  if (!st->self_group) {
+    int err = 0;
+    st->self_group = opus_multistream_decoder_group_create(&st, 1, &err);
+    if (!st->self_group) return err;
+  }
+  const bool lost = (data == nullptr || len == 0);
+  i32 off = lost ? -1 : 0, ln = lost ? 0 : len;
+  int ret = OPUS_INTERNAL_ERROR;
+  std::vector<i16> row((size_t)frame_size * st->channels);
+  int rc = opus_multistream_decode_group_flat(st->self_group, lost ? nullptr : data, lost ? 0 : ln, &off, &ln,
+                                              row.data(), frame_size * st->channels, frame_size, &decode_fec, &ret);
+  if (rc != OPUS_OK) return rc;
+  if (ret > 0) memcpy(pcm, row.data(), (size_t)ret * st->channels * sizeof(i16));
+  return ret;
+}
+
+int opus_multistream_decode_float(OpusMSDecoder* st, const unsigned char* data, opus_int32 len, float* pcm,
+                                  int frame_size, int decode_fec) {
+  if (!st || st->magic != kMagicMS || !pcm || frame_size <= 0) return OPUS_BAD_ARG;
+  std::vector<i16> tmp((size_t)frame_size * st->channels);
+  int ret = opus_multistream_decode(st, data, len, tmp.data(), frame_size, decode_fec);
+  if (ret > 0)
+    for (int i = 0; i < ret * st->channels; i++) pcm[i] = (1.f / 32768.f) * tmp[i];
+  return ret;
+}
+
+int opus_multistream_decoder_ctl(OpusMSDecoder* st, int request, ...) {
+  if (!st || st->magic != kMagicMS) return OPUS_BAD_ARG;
+  va_list ap;
+  va_start(ap, request);
+  int ret = OPUS_OK;
+  switch (request) {
+    case OPUS_GET_BANDWIDTH_REQUEST:
+    case OPUS_GET_SAMPLE_RATE_REQUEST:
+    case OPUS_GET_GAIN_REQUEST:
+    case OPUS_GET_LAST_PACKET_DURATION_REQUEST: {
+      opus_int32* value = va_arg(ap, opus_int32*);
+      ret = opus_decoder_ctl(st->sub[0], request, value);
+      break;
+    }
+    case OPUS_GET_FINAL_RANGE_REQUEST: {
+      opus_uint32* value = va_arg(ap, opus_uint32*);
+      if (!value) { ret = OPUS_BAD_ARG; break; }
+      *value = 0;
+      for (int s = 0; s < st->streams; s++) {
+        opus_uint32 tmp = 0;
+        ret = opus_decoder_ctl(st->sub[s], request, &tmp);
+        if (ret != OPUS_OK) break;
+        *value ^= tmp;
+      }
+      break;
+    }
+    case OPUS_RESET_STATE:
+      for (int s = 0; s < st->streams && ret == OPUS_OK; s++) ret = opus_decoder_ctl(st->sub[s], OPUS_RESET_STATE);
+      break;
+    case OPUS_MULTISTREAM_GET_DECODER_STATE_REQUEST: {
+      opus_int32 stream_id = va_arg(ap, opus_int32);
+      OpusDecoder** value = va_arg(ap, OpusDecoder**);
+      if (stream_id < 0 || stream_id >= st->streams || !value) { ret = OPUS_BAD_ARG; break; }
+      *value = st->sub[stream_id];
+      break;
+    }
+    case OPUS_SET_GAIN_REQUEST: {
+      opus_int32 value = va_arg(ap, opus_int32);
+      for (int s = 0; s < st->streams && ret == OPUS_OK; s++) ret = opus_decoder_ctl(st->sub[s], request, value);
+      break;
+    }
+    default:
+      ret = OPUS_UNIMPLEMENTED;
+      break;
+  }
+  va_end(ap);
+  return ret;
 }
 
 int opus_b200_synchronize(void) {

@@ -122,6 +122,37 @@ int opus_decode_group_device(OpusDecoderGroup *grp, const unsigned char *d_data,
                              opus_int32 pcm_stride, int frame_size, const int *d_decode_fec, int *d_ret,
                              int max_frames, int max_packet_bytes, void *cuda_stream);
 
+/* ---- multistream (surround) decoder: libopus ABI (opus-fix/include/opus_multistream.h:257-448,504-650;
+ *      NativeOpus.cs:131-155) + batch forms.  A multistream packet carries `streams` elementary Opus packets
+ *      (all but the last self-delimited); each is decoded by its own elementary decoder on the GPU and the
+ *      channels are then copied out according to `mapping`. ---- */
+typedef struct OpusMSDecoder OpusMSDecoder;
+typedef struct OpusMSDecoderGroup OpusMSDecoderGroup;
+#define OPUS_MULTISTREAM_GET_DECODER_STATE_REQUEST 5122
+/* replaces opus_multistream_decoder_get_size (src/opus_multistream_decoder.c:52-63): size of the HOST handle */
+opus_int32 opus_multistream_decoder_get_size(int streams, int coupled_streams);
+/* replaces opus_multistream_decoder_create (src/opus_multistream_decoder.c:107-142) */
+OpusMSDecoder *opus_multistream_decoder_create(opus_int32 Fs, int channels, int streams, int coupled_streams,
+                                               const unsigned char *mapping, int *error);
+/* replaces opus_multistream_decode (src/opus_multistream_decoder.c:365-376) */
+int opus_multistream_decode(OpusMSDecoder *st, const unsigned char *data, opus_int32 len, opus_int16 *pcm,
+                            int frame_size, int decode_fec);
+/* replaces opus_multistream_decode_float (src/opus_multistream_decoder.c:379-384) */
+int opus_multistream_decode_float(OpusMSDecoder *st, const unsigned char *data, opus_int32 len, float *pcm,
+                                  int frame_size, int decode_fec);
+/* replaces opus_multistream_decoder_ctl (src/opus_multistream_decoder.c:409-531) */
+int opus_multistream_decoder_ctl(OpusMSDecoder *st, int request, ...);
+/* replaces opus_multistream_decoder_destroy (src/opus_multistream_decoder.c:534-537) */
+void opus_multistream_decoder_destroy(OpusMSDecoder *st);
+/* batch forms (new): n independent multistream decoders per call, per-decoder return codes */
+int opus_multistream_decode_batch(OpusMSDecoder *const *st, const unsigned char *const *data, const opus_int32 *len,
+                                  opus_int16 *const *pcm, int frame_size, const int *decode_fec, int n, int *ret);
+OpusMSDecoderGroup *opus_multistream_decoder_group_create(OpusMSDecoder *const *st, int n, int *error);
+void opus_multistream_decoder_group_destroy(OpusMSDecoderGroup *grp);
+int opus_multistream_decode_group_flat(OpusMSDecoderGroup *grp, const unsigned char *data, opus_int32 data_bytes,
+                                       const opus_int32 *offsets, const opus_int32 *len, opus_int16 *pcm,
+                                       opus_int32 pcm_stride, int frame_size, const int *decode_fec, int *ret);
+
 /* No counterpart in the reference (libopus keeps all scratch on the caller's stack).
  * Device-resident batch decode that allocates nothing: for callers that must not call cudaMalloc --
  * a real-time decode thread (allocation takes driver-wide locks, cudaFree synchronises the whole

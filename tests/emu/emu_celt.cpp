@@ -60,4 +60,63 @@ int emu_opus_decode(void* state, const unsigned char* data, int len, short* pcm,
   return ret;
 }
 
+// ---- multistream: plan + passes + channel copy-out, as the CUDA launch sequence does ----
+struct EmuMS {
+  MSLayout L;
+  OpusDecState* st[16];
+  StreamPlan plans[16];
+};
+void* emu_ms_create(int Fs, int channels, int streams, int coupled, const unsigned char* mapping) {
+  EmuMS* m = (EmuMS*)calloc(1, sizeof(EmuMS));
+  m->L.nb_channels = channels; m->L.nb_streams = streams; m->L.nb_coupled = coupled; m->L.first = 0; m->L.Fs = Fs;
+  memcpy(m->L.mapping, mapping, channels);
+  for (int s = 0; s < streams; s++) m->st[s] = (OpusDecState*)emu_opus_create(Fs, s < coupled ? 2 : 1);
+  return m;
+}
+void emu_ms_destroy(void* p) {
+  EmuMS* m = (EmuMS*)p;
+  for (int s = 0; s < m->L.nb_streams; s++) free(m->st[s]);
+  free(m);
+}
+unsigned emu_ms_final_range(void* p) {
+  EmuMS* m = (EmuMS*)p;
+  unsigned v = 0;
+  for (int s = 0; s < m->L.nb_streams; s++) v ^= m->st[s]->rangeFinal;
+  return v;
+}
+int emu_ms_decode(void* p, const unsigned char* data, int len, short* pcm, int frame_size, int fec) {
+  EmuMS* m = (EmuMS*)p;
+  static EntWork ew;
+  static SynWork sw;
+  static FrameSide side;
+  static PlcWork pw;
+  static unsigned char pkt[1600];
+  static short epcm[16][5760 * 2];
+  const int S = m->L.nb_streams;
+  int ret = opus_ms_plan(m->st, m->plans, &m->L, data, data ? 0 : -1, data ? len : 0, frame_size, fec);
+  for (int s = 0; s < S; s++) {
+    StreamPlan* pl = &m->plans[s];
+    i32 r = pl->ret;
+    for (int pass = 0; pass < pl->nframes; pass++) {
+      decode_entropy_pass(ew, pkt, m->st[s], pl, &side, data, &r, pass);
+      for (int c = 0; c < m->st[s]->channels; c++) decode_synth_pass(sw, m->st[s], pl, &side, epcm[s], c, pass);
+      decode_plc_pass(pw, m->st[s], pl, &side, epcm[s], pass);
+    }
+  }
+  if (ret > 0) {
+    const int CH = m->L.nb_channels;
+    for (int t = 0; t < ret; t++)
+      for (int c = 0; c < CH; c++) {
+        int mp = m->L.mapping[c];
+        short v = 0;
+        if (mp != 255) {
+          if (mp < 2 * m->L.nb_coupled) v = epcm[mp >> 1][t * 2 + (mp & 1)];
+          else v = epcm[mp - m->L.nb_coupled][t];
+        }
+        pcm[t * CH + c] = v;
+      }
+  }
+  return ret;
+}
+
 }  // extern "C"
