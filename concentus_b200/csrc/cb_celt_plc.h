@@ -288,7 +288,7 @@ CB_FN int plc_pitch_search(PlcWork& w, const CeltDecState* st) {
 }
 
 // Pitch-based concealment of one frame of N samples (celt_decoder.c:507-706) + de-emphasis.
-CB_FN void celt_plc_pitch(PlcWork& w, CeltDecState* st, int N, i16* pcm, int accum) {
+CB_FN void celt_plc_pitch(PlcWork& w, CeltDecState* st, int N, i16* pcm, int accum, int decode_gain = 0) {
   const int C = st->channels;
   const int loss_count = st->loss_count;
   i32 fade = CB_Q15ONE;
@@ -446,7 +446,7 @@ CB_FN void celt_plc_pitch(PlcWork& w, CeltDecState* st, int N, i16* pcm, int acc
       }
       CB_WSYNC();
     }
-    emit_frame(w.nb, N, st, c, pcm, accum);
+    emit_frame(w.nb, N, st, c, pcm, accum, decode_gain);
   }
   CB_WSYNC();
   st->loss_count = loss_count + 1;

@@ -314,7 +314,7 @@ CB_FN void v_comb_filter(i32* buf, int off, int n, const i32* hist, int pos, int
 //  * history ring: the frame overwrites the N oldest samples;
 //  * de-emphasis is a serial one-pole IIR (m = 0.85*(x+m), truncating multiply): one lane;
 //  * SIG2WORD16 + interleaved int16 store (optionally accumulated, hybrid mode) in a lane loop.
-CB_FN void emit_frame(i32* buf, int N, CeltDecState* st, int c, i16* pcm, int accum) {
+CB_FN void emit_frame(i32* buf, int N, CeltDecState* st, int c, i16* pcm, int accum, int decode_gain) {
   const int CC = st->channels, downsample = st->downsample;
   i32* hist = st->hist[c];
   const int pos = st->hist_pos[c];
@@ -333,17 +333,29 @@ CB_FN void emit_frame(i32* buf, int N, CeltDecState* st, int c, i16* pcm, int ac
   }
   CB_WSYNC();
   const int Nd = N / downsample;
-  if (accum) {
-    CB_LANE_LOOPU(j, Nd) pcm[j * CC + c] = sat16((i32)pcm[j * CC + c] + (i32)sig2word16(buf[j * downsample]));
+  if (decode_gain == 0) {
+    if (accum) {
+      CB_LANE_LOOPU(j, Nd) pcm[j * CC + c] = sat16((i32)pcm[j * CC + c] + (i32)sig2word16(buf[j * downsample]));
+    } else {
+      CB_LANE_LOOPU(j, Nd) pcm[j * CC + c] = sig2word16(buf[j * downsample]);
+    }
   } else {
-    CB_LANE_LOOPU(j, Nd) pcm[j * CC + c] = sig2word16(buf[j * downsample]);
+    // OPUS_SET_GAIN (opus_decoder.c:567-577): Q8 dB -> linear Q16, rounded multiply, clamp to +-32767
+    const i32 gain = cb_exp2(mult16_16_p15(21771, decode_gain));     // QCONST16(6.48814081e-4f, 25)
+    CB_LANE_LOOPU(j, Nd) {
+      i32 v = sig2word16(buf[j * downsample]);
+      if (accum) v = sat16((i32)pcm[j * CC + c] + v);
+      i32 x = mult16_32_p16(v, gain);
+      pcm[j * CC + c] = (i16)(x > 32767 ? 32767 : x < -32767 ? -32767 : x);
+    }
   }
   CB_WSYNC();
 }
 
 // Synthesis of output channel `c` of one stream for one frame.
 // pcm -> first sample of this frame for this stream (interleaved, CC channels).
-CB_FN void celt_synth_channel(SynWork& w, CeltDecState* st, const FrameSide* side, int c, i16* pcm) {
+CB_FN void celt_synth_channel(SynWork& w, CeltDecState* st, const FrameSide* side, int c, i16* pcm,
+                               int decode_gain = 0) {
   const int LM = side->LM, C = side->C, CC = st->channels;
   const int M = 1 << LM, N = M * 120;
   const int downsample = st->downsample;
@@ -376,5 +388,5 @@ CB_FN void celt_synth_channel(SynWork& w, CeltDecState* st, const FrameSide* sid
   v_comb_filter(w.buf, 0, 120, hist, pos, side->T0, side->T1, side->g0, side->g1, side->tap0, side->tap1, CB_OVERLAP);
   if (LM != 0)
     v_comb_filter(w.buf, 120, N - 120, hist, pos, side->T1, side->T2, side->g1, side->g2, side->tap1, side->tap2, CB_OVERLAP);
-  emit_frame(w.buf, N, st, c, pcm, side->accum);
+  emit_frame(w.buf, N, st, c, pcm, side->accum, decode_gain);
 }

@@ -73,7 +73,7 @@ CB_FN void decode_synth_pass(SynWork& w, OpusDecState* st, const StreamPlan* pl,
                              i16* row, int c, int pass) {
   const int CC = st->channels;
   if (side->kind == 1) {
-    celt_synth_channel(w, &st->celt, side, c, row + (size_t)pl->pcm_off[pass] * CC);
+    celt_synth_channel(w, &st->celt, side, c, row + (size_t)pl->pcm_off[pass] * CC, st->decode_gain);
   } else if (side->kind == 3 && pass == 0) {
     const int total = pl->total_samples;
     CB_LANE_LOOP(j, total) row[j * CC + c] = 0;
@@ -89,5 +89,5 @@ CB_FN void decode_plc_pass(PlcWork& w, OpusDecState* st, const StreamPlan* pl, c
                            i16* row, int pass) {
   if (side->kind != 2) return;
   const int N = 120 << side->LM;
-  celt_plc_pitch(w, &st->celt, N, row + (size_t)pl->pcm_off[pass] * st->channels, side->accum);
+  celt_plc_pitch(w, &st->celt, N, row + (size_t)pl->pcm_off[pass] * st->channels, side->accum, st->decode_gain);
 }

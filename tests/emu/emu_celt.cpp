@@ -39,6 +39,7 @@ void* emu_opus_create(int Fs, int channels) {
 }
 void emu_opus_destroy(void* s) { free(s); }
 unsigned emu_opus_final_range(void* s) { return ((OpusDecState*)s)->rangeFinal; }
+void emu_opus_set_gain(void* s, int g) { ((OpusDecState*)s)->decode_gain = g; }
 int emu_opus_last_packet_duration(void* s) { return ((OpusDecState*)s)->last_packet_duration; }
 
 int emu_opus_decode(void* state, const unsigned char* data, int len, short* pcm, int frame_size, int fec) {

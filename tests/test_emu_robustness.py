@@ -52,3 +52,26 @@ def test_emu_loss_concealment(emu_lib, name):
 def test_emu_multiframe_and_corruption(emu_lib, name):
     meta, calls = fuzz_scenario(name, seed=len(name) + 3)
     _run(emu_lib, meta, calls)
+
+
+@needs_ref
+@pytest.mark.parametrize("gain", [-3000, 256, 1537, 5000])
+def test_emu_decode_gain(emu_lib, gain):
+    """OPUS_SET_GAIN (opus_decoder.c:567-577, 867-876): Q8 dB gain applied to the int16 output."""
+    from conftest import golden_case
+    emu_lib.emu_opus_create.restype = ctypes.c_void_p
+    emu_lib.emu_opus_create.argtypes = [ctypes.c_int, ctypes.c_int]
+    emu_lib.emu_opus_set_gain.argtypes = [ctypes.c_void_p, ctypes.c_int]
+    emu_lib.emu_opus_decode.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int, ctypes.c_void_p,
+                                        ctypes.c_int, ctypes.c_int]
+    meta, pk = golden_case("vbr_128k_st")
+    ref = RefDecoder(48000, 2)
+    assert RefDecoder.lib().opus_decoder_ctl(ctypes.c_void_p(ref.h), 4034, ctypes.c_int(gain)) == 0
+    st = emu_lib.emu_opus_create(48000, 2)
+    emu_lib.emu_opus_set_gain(st, gain)
+    for n, (p, _) in enumerate(pk[:40]):
+        data = None if n in (7, 8, 20) else p
+        ra, pa = ref.decode_raw(data, 960)
+        pb = np.zeros((960, 2), dtype=np.int16)
+        rb = emu_lib.emu_opus_decode(st, data, len(data) if data else 0, pb.ctypes.data, 960, 0)
+        assert ra == rb == 960 and np.array_equal(pa, pb), n

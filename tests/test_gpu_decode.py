@@ -160,3 +160,23 @@ def test_decode_float_and_ctl():
     finally:
         dec.close()
         dec2.close()
+
+
+@needs_ref
+def test_decode_gain_matches_reference():
+    """OPUS_SET_GAIN through opus_decoder_ctl, applied on the device (opus_decoder.c:567-577)."""
+    meta, pk = golden_case("vbr_128k_st")
+    for gain in (-3000, 1537):
+        ref = RefDecoder(48000, 2)
+        assert RefDecoder.lib().opus_decoder_ctl(ctypes.c_void_p(ref.h), 4034, ctypes.c_int(gain)) == 0
+        dec = cb.OpusDecoder(48000, 2)
+        dec.gain = gain
+        assert dec.gain == gain
+        try:
+            for n, (p, _) in enumerate(pk[:30]):
+                data = None if n in (7, 8, 20) else p
+                ra, pa = ref.decode_raw(data, 960)
+                rb, pb = dec.decode_raw(data, 960)
+                assert ra == rb == 960 and np.array_equal(pa, pb), (gain, n)
+        finally:
+            dec.close()
