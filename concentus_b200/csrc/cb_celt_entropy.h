@@ -59,6 +59,8 @@ struct alignas(16) EntWork {
   i8 tf_res[CB_NBANDS];
   u8 collapse[2 * CB_NBANDS];
   PartFrame stack[5];
+  struct BandJobS { i16* X; i16* lowband; i16* lowband_out; i16* scratch; i32 b, gain, fill, pad; } jobs[2];
+  struct { int inv, imid, iside, delta, itheta, qalloc, b, fill; } sp_store;   // see struct Split
   RangeDec rd;                   // coder registers; in shared memory so the rd_* routines can be real calls
 };
 
@@ -300,15 +302,17 @@ CB_FN int bitexact_log2tan(int isin, int icos) {   // bands.c:82-93
   return (ls - lc) * (1 << 11) + frac_mul16(isin, frac_mul16(isin, -2597) + 7932)
          - frac_mul16(icos, frac_mul16(icos, -2597) + 7932);
 }
-struct Split { int inv, imid, iside, delta, itheta, qalloc; };
+struct Split { int inv, imid, iside, delta, itheta, qalloc, b, fill; };   // b/fill: updated in/out values
 
-CB_FN void dec_theta(BandCtx& cx, RangeDec& rd, Split& sp, int N, int& b, int B, int B0, int LM,
-                     int stereo, int& fill) {
+// A real call (one copy of the code): inputs by value, results through the Split record, which
+// lives in shared memory (EntWork::sp).
+CB_FN_NOINLINE void dec_theta(RangeDec& rd, Split& sp, int band, int intensity, i32 remaining_bits, int N, int b,
+                              int B, int B0, int LM, int stereo, int fill) {
   int itheta = 0, inv = 0;
-  int pulse_cap = ct_logN400[cx.i] + LM * (1 << CB_BITRES);
+  int pulse_cap = ct_logN400[band] + LM * (1 << CB_BITRES);
   int offset = (pulse_cap >> 1) - (stereo && N == 2 ? 16 : 4);
   int qn = compute_qn(N, b, offset, pulse_cap, stereo);
-  if (stereo && cx.i >= cx.intensity) qn = 1;
+  if (stereo && band >= intensity) qn = 1;
   i32 tell = (i32)rd_tell_frac(rd);
   if (qn != 1) {
     if (stereo && N > 2) {                    // step pdf
@@ -342,7 +346,7 @@ CB_FN void dec_theta(BandCtx& cx, RangeDec& rd, Split& sp, int N, int& b, int B,
     }
     itheta = (int)((u32)(itheta * 16384) / (u32)qn);
   } else if (stereo) {
-    if (b > 2 << CB_BITRES && cx.remaining_bits > 2 << CB_BITRES) inv = rd_bit_logp(rd, 2);
+    if (b > 2 << CB_BITRES && remaining_bits > 2 << CB_BITRES) inv = rd_bit_logp(rd, 2);
     else inv = 0;
     itheta = 0;
   }
@@ -363,6 +367,7 @@ CB_FN void dec_theta(BandCtx& cx, RangeDec& rd, Split& sp, int N, int& b, int B,
     delta = frac_mul16((N - 1) << 7, bitexact_log2tan(iside, imid));
   }
   sp.inv = inv; sp.imid = imid; sp.iside = iside; sp.delta = delta; sp.itheta = itheta; sp.qalloc = qalloc;
+  sp.b = b; sp.fill = fill;
 }
 
 // ---- leaf of the split recursion (bands.c:966-1038, decoder side) ---------------------------
@@ -426,21 +431,23 @@ CB_FN u32 dec_partition(EntWork& w, BandCtx& cx, RangeDec& rd, i16* X0, int N0, 
         LM -= 1;
         if (B == 1) fill = (fill & 1) | (fill << 1);
         B = (B + 1) >> 1;
-        Split s;
-        dec_theta(cx, rd, s, N, b, B, B0, LM, 0, fill);
+        Split& s = *reinterpret_cast<Split*>(&w.sp_store);
+        dec_theta(rd, s, cx.i, cx.intensity, cx.remaining_bits, N, b, B, B0, LM, 0, fill);
+        b = s.b; fill = s.fill;
         int delta = s.delta, itheta = s.itheta;
+        const int s_qalloc = s.qalloc, s_imid = s.imid, s_iside = s.iside;
         if (B0 > 1 && (itheta & 0x3fff)) {
           if (itheta > 8192) delta -= delta >> (4 - LM);
           else delta = cb_imin(0, delta + (N << CB_BITRES >> (5 - LM)));
         }
         int mbits = cb_imax(0, cb_imin(b, (b - delta) / 2));
         int sbits = b - mbits;
-        cx.remaining_bits -= s.qalloc;
+        cx.remaining_bits -= s_qalloc;
         f.N = N; f.B = B; f.LM = LM; f.fill = fill; f.B0 = B0;
         f.mbits = mbits; f.sbits = sbits; f.itheta = itheta;
         f.rebal0 = cx.remaining_bits;
-        f.gmid = mult16_16_p15(f.gain, s.imid);
-        f.gside = mult16_16_p15(f.gain, s.iside);
+        f.gmid = mult16_16_p15(f.gain, s_imid);
+        f.gside = mult16_16_p15(f.gain, s_iside);
         f.stage = (mbits >= sbits) ? 1 : 3;    // 1: mid first, 3: side first
         PartFrame& c = st[sp + 1];
         c.N = N; c.B = B; c.LM = LM; c.stage = 0;
@@ -597,7 +604,6 @@ CB_FN void v_stereo_merge(i16* X, i16* Y, i32 mid, int N) {
 
 // One call of quant_band() as data, so that the (large) band decoder is instantiated at exactly
 // one call site: instruction-cache footprint is what bounds this kernel (see profiles/).
-struct BandJob { i16* X; i16* lowband; i16* lowband_out; i16* scratch; i32 b, gain, fill; };
 
 // quant_all_bands (bands.c:1337-1502) with quant_band_stereo (bands.c:1176-1334) folded in as a
 // small job list per band.  Decoder side.  Xc = channel-0 spectrum, channel stride = N.
@@ -668,35 +674,37 @@ CB_FN void dec_all_bands(EntWork& w, RangeDec& rd, int start, int end, int C, in
     i16* lout = last ? nullptr : norm + M * ebands(i) - norm_offset;
     i16* lout2 = last ? nullptr : norm2 + M * ebands(i) - norm_offset;
 
-    // ---- build the job list for this band ----
-    BandJob J0, J1;
+    // ---- build the job list for this band (kept in shared memory: two fixed slots) ----
+    EntWork::BandJobS* J = w.jobs;
     int njobs = 0;
     int mode;                       // 0 mono, 1 dual stereo, 2 joint stereo N>2, 3 joint stereo N==2, 4 done
     Split s;
-    s.inv = 0; s.itheta = 0; s.imid = 0; s.iside = 0; s.delta = 0; s.qalloc = 0;
+    s.inv = 0; s.itheta = 0; s.imid = 0; s.iside = 0; s.delta = 0; s.qalloc = 0; s.b = 0; s.fill = 0;
     int mbits = 0, sbits = 0, mid_first = 1, n2_swap = 0, n2_sign = 1;
     i32 rebalance0 = 0;
     u32 cm = 0;
     if (dual_stereo) {
       mode = 1;
-      J0.X = X; J0.lowband = lb; J0.lowband_out = lout; J0.scratch = lowband_scratch; J0.b = b / 2; J0.gain = CB_Q15ONE; J0.fill = (i32)x_cm;
-      J1.X = Y; J1.lowband = lb2; J1.lowband_out = lout2; J1.scratch = lowband_scratch; J1.b = b / 2; J1.gain = CB_Q15ONE; J1.fill = (i32)y_cm;
+      J[0].X = X; J[0].lowband = lb; J[0].lowband_out = lout; J[0].scratch = lowband_scratch; J[0].b = b / 2; J[0].gain = CB_Q15ONE; J[0].fill = (i32)x_cm;
+      J[1].X = Y; J[1].lowband = lb2; J[1].lowband_out = lout2; J[1].scratch = lowband_scratch; J[1].b = b / 2; J[1].gain = CB_Q15ONE; J[1].fill = (i32)y_cm;
       njobs = 2;
     } else if (Y == nullptr) {
       mode = 0;
-      J0.X = X; J0.lowband = lb; J0.lowband_out = lout; J0.scratch = lowband_scratch; J0.b = b; J0.gain = CB_Q15ONE; J0.fill = (i32)(x_cm | y_cm);
-      J1 = J0;
+      J[0].X = X; J[0].lowband = lb; J[0].lowband_out = lout; J[0].scratch = lowband_scratch; J[0].b = b; J[0].gain = CB_Q15ONE; J[0].fill = (i32)(x_cm | y_cm);
       njobs = 1;
     } else if (N == 1) {
       mode = 4;
       cm = dec_band_n1(cx, rd, X, Y, lout);
-      J0.X = X; J0.lowband = nullptr; J0.lowband_out = nullptr; J0.scratch = nullptr; J0.b = 0; J0.gain = 0; J0.fill = 0;
-      J1 = J0;
     } else {
       int fill = (int)(x_cm | y_cm);
       const int orig_fill = fill;
       int bb = b;
-      dec_theta(cx, rd, s, N, bb, B, B, LM, 1, fill);
+      {
+        Split& sh = *reinterpret_cast<Split*>(&w.sp_store);
+        dec_theta(rd, sh, cx.i, cx.intensity, cx.remaining_bits, N, bb, B, B, LM, 1, fill);
+        s = sh;
+        bb = s.b; fill = s.fill;
+      }
       if (N == 2) {
         mode = 3;
         mbits = bb;
@@ -708,9 +716,8 @@ CB_FN void dec_all_bands(EntWork& w, RangeDec& rd, int start, int end, int C, in
         int sign = 0;
         if (sbits) sign = (int)rd_bits(rd, 1);
         n2_sign = 1 - 2 * sign;
-        J0.X = n2_swap ? Y : X; J0.lowband = lb; J0.lowband_out = lout; J0.scratch = lowband_scratch;
-        J0.b = mbits; J0.gain = CB_Q15ONE; J0.fill = orig_fill;
-        J1 = J0;
+        J[0].X = n2_swap ? Y : X; J[0].lowband = lb; J[0].lowband_out = lout; J[0].scratch = lowband_scratch;
+        J[0].b = mbits; J[0].gain = CB_Q15ONE; J[0].fill = orig_fill;
         njobs = 1;
       } else {
         mode = 2;
@@ -719,24 +726,24 @@ CB_FN void dec_all_bands(EntWork& w, RangeDec& rd, int start, int end, int C, in
         cx.remaining_bits -= s.qalloc;
         rebalance0 = cx.remaining_bits;
         mid_first = mbits >= sbits;
-        BandJob Jm, Js;
-        Jm.X = X; Jm.lowband = lb; Jm.lowband_out = lout; Jm.scratch = lowband_scratch; Jm.b = mbits; Jm.gain = CB_Q15ONE; Jm.fill = fill;
-        Js.X = Y; Js.lowband = nullptr; Js.lowband_out = nullptr; Js.scratch = nullptr; Js.b = sbits; Js.gain = s.iside; Js.fill = fill >> B;
-        if (mid_first) { J0 = Jm; J1 = Js; } else { J0 = Js; J1 = Jm; }
+        const int im = mid_first ? 0 : 1, is = 1 - im;      // slot of the mid / side job
+        J[im].X = X; J[im].lowband = lb; J[im].lowband_out = lout; J[im].scratch = lowband_scratch; J[im].b = mbits; J[im].gain = CB_Q15ONE; J[im].fill = fill;
+        J[is].X = Y; J[is].lowband = nullptr; J[is].lowband_out = nullptr; J[is].scratch = nullptr; J[is].b = sbits; J[is].gain = s.iside; J[is].fill = fill >> B;
         njobs = 2;
       }
     }
     // ---- run the jobs: the one and only call site of dec_band ----
     u32 cm0 = 0, cm1 = 0;
     CB_NOUNROLL for (int jn = 0; jn < njobs; jn++) {
-      BandJob J = jn == 0 ? J0 : J1;
+      i32 jb = J[jn].b;
       if (mode == 2 && jn == 1) {
         i32 first_bits = mid_first ? mbits : sbits;
         i32 rebalance = first_bits - (rebalance0 - cx.remaining_bits);
         int blocked = mid_first ? (s.itheta == 0) : (s.itheta == 16384);
-        if (rebalance > 3 << CB_BITRES && !blocked) J.b += rebalance - (3 << CB_BITRES);
+        if (rebalance > 3 << CB_BITRES && !blocked) jb += rebalance - (3 << CB_BITRES);
       }
-      u32 r = dec_band(w, cx, rd, J.X, N, J.b, B, J.lowband, LM, J.lowband_out, J.gain, J.scratch, J.fill);
+      u32 r = dec_band(w, cx, rd, J[jn].X, N, jb, B, J[jn].lowband, LM, J[jn].lowband_out, J[jn].gain, J[jn].scratch,
+                       J[jn].fill);
       if (jn == 0) cm0 = r; else cm1 = r;
     }
     // ---- per-mode epilogue ----
