@@ -38,6 +38,8 @@ CB_UTABLE u8 ct_bit_deinterleave[16] = {0x00, 0x03, 0x0C, 0x0F, 0x30, 0x33, 0x3C
 #define CB_FINE_OFFSET 21
 #define CB_ALLOC_STEPS 6
 
+struct Split { int inv, imid, iside, delta, itheta, qalloc, b, fill; };   // b/fill: updated in/out values
+
 // One level of the split recursion (quant_partition), kept in shared memory.
 struct PartFrame {
   i16* X; i16* lowband;
@@ -60,7 +62,7 @@ struct alignas(16) EntWork {
   u8 collapse[2 * CB_NBANDS];
   PartFrame stack[5];
   struct BandJobS { i16* X; i16* lowband; i16* lowband_out; i16* scratch; i32 b, gain, fill, pad; } jobs[2];
-  struct { int inv, imid, iside, delta, itheta, qalloc, b, fill; } sp_store;   // see struct Split
+  Split sp_store;                // result record of dec_theta
   RangeDec rd;                   // coder registers; in shared memory so the rd_* routines can be real calls
 };
 
@@ -302,7 +304,6 @@ CB_FN int bitexact_log2tan(int isin, int icos) {   // bands.c:82-93
   return (ls - lc) * (1 << 11) + frac_mul16(isin, frac_mul16(isin, -2597) + 7932)
          - frac_mul16(icos, frac_mul16(icos, -2597) + 7932);
 }
-struct Split { int inv, imid, iside, delta, itheta, qalloc, b, fill; };   // b/fill: updated in/out values
 
 // A real call (one copy of the code): inputs by value, results through the Split record, which
 // lives in shared memory (EntWork::sp).
@@ -431,7 +432,7 @@ CB_FN u32 dec_partition(EntWork& w, BandCtx& cx, RangeDec& rd, i16* X0, int N0, 
         LM -= 1;
         if (B == 1) fill = (fill & 1) | (fill << 1);
         B = (B + 1) >> 1;
-        Split& s = *reinterpret_cast<Split*>(&w.sp_store);
+        Split& s = w.sp_store;
         dec_theta(rd, s, cx.i, cx.intensity, cx.remaining_bits, N, b, B, B0, LM, 0, fill);
         b = s.b; fill = s.fill;
         int delta = s.delta, itheta = s.itheta;
@@ -700,7 +701,7 @@ CB_FN void dec_all_bands(EntWork& w, RangeDec& rd, int start, int end, int C, in
       const int orig_fill = fill;
       int bb = b;
       {
-        Split& sh = *reinterpret_cast<Split*>(&w.sp_store);
+        Split& sh = w.sp_store;
         dec_theta(rd, sh, cx.i, cx.intensity, cx.remaining_bits, N, bb, B, B, LM, 1, fill);
         s = sh;
         bb = s.b; fill = s.fill;

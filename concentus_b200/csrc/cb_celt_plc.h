@@ -12,6 +12,7 @@
 #include "cb_state.h"
 #include "cb_celt_synth.h"
 #include "cb_celt_entropy.h"
+#include "cb_pitch.h"
 
 #define CB_MAX_PERIOD 1024
 #define CB_PLC_PITCH_LAG_MAX 720
@@ -33,119 +34,6 @@ struct alignas(16) PlcWork {
 };
 
 CB_FN i32 hist_at(const i32* hist, int pos, int i) { return hist[(pos + i) & (CB_HIST - 1)]; }
-
-// _celt_autocorr (celt_lpc.c:232-328) without the SIMD split: ac[k] = sum_{i>=k} x[i]x[i-k], then
-// the fixed-point normalisation.  x: n samples; xx: scratch of n samples.
-CB_FN int plc_autocorr(const i16* x, i32* ac, i16* xx, int use_window, int lag, int n) {
-  const i16* xptr = x;
-  CB_WSYNC();
-  if (use_window) {
-    CB_LANE_LOOP(i, n) xx[i] = x[i];
-    CB_WSYNC();
-    CB_LANE_LOOP(i, CB_OVERLAP) {
-      i32 w = cb_ldg(&ct_window120[i]);
-      xx[i] = (i16)mult16_16_q15(x[i], w);
-      xx[n - i - 1] = (i16)mult16_16_q15(x[n - i - 1], w);
-    }
-    CB_WSYNC();
-    xptr = xx;
-  }
-  i32 part = 0;
-  CB_LANE_LOOP(i, n) part = add32(part, mult16_16(xptr[i], xptr[i]) >> 9);
-  i32 ac0 = add32(1 + (n << 7), cb_wsum(part));
-  int shift = cb_ilog2(ac0) - 30 + 10;
-  shift = shift / 2;
-  if (shift > 0) {
-    CB_WSYNC();
-    CB_LANE_LOOP(i, n) {
-      i32 v = xptr[i];
-      xx[i] = (i16)pshr32(v, shift);
-    }
-    CB_WSYNC();
-    xptr = xx;
-  } else {
-    shift = 0;
-  }
-  CB_NOUNROLL for (int k = 0; k <= lag; k++) {
-    i32 d = 0;
-    CB_LANE_LOOP(t, n - k) d = mac16_16(d, xptr[t + k], xptr[t]);
-    ac[k] = cb_wsum(d);
-  }
-  CB_WSYNC();
-  shift = 2 * shift;
-  i32 a0 = ac[0];
-  if (shift <= 0) a0 = add32(a0, shl32(1, -shift));
-  CB_WSYNC();
-  ac[0] = a0;
-  CB_WSYNC();
-  if (a0 < 268435456) {
-    int shift2 = 29 - cb_ilog((u32)a0);
-    CB_LANE_LOOP(i, lag + 1) ac[i] = shl32(ac[i], shift2);
-    shift -= shift2;
-  } else if (a0 >= 536870912) {
-    int shift2 = 1;
-    if (a0 >= 1073741824) shift2++;
-    CB_LANE_LOOP(i, lag + 1) ac[i] = ac[i] >> shift2;
-    shift += shift2;
-  }
-  CB_WSYNC();
-  return shift;
-}
-
-// _celt_lpc (celt_lpc.c:37-93): Levinson-Durbin, uniform (p <= 24)
-CB_FN void plc_lpc(i16* out, const i32* ac, i32* lpc, int p) {
-  CB_NOUNROLL for (int i = 0; i < p; i++) lpc[i] = 0;
-  i32 error = ac[0];
-  if (ac[0] != 0) {
-    CB_NOUNROLL for (int i = 0; i < p; i++) {
-      i32 rr = 0;
-      CB_NOUNROLL for (int j = 0; j < i; j++) rr = add32(rr, mult32_32_q31(lpc[j], ac[i - j]));
-      rr = add32(rr, ac[i + 1] >> 3);
-      i32 r = neg32(cb_frac_div32(shl32(rr, 3), error));
-      lpc[i] = r >> 3;
-      CB_NOUNROLL for (int j = 0; j < (i + 1) >> 1; j++) {
-        i32 t1 = lpc[j], t2 = lpc[i - 1 - j];
-        lpc[j] = add32(t1, mult32_32_q31(r, t2));
-        lpc[i - 1 - j] = add32(t2, mult32_32_q31(r, t1));
-      }
-      error = sub32(error, mult32_32_q31(mult32_32_q31(r, r), error));
-      if (error < (ac[0] >> 10)) break;
-    }
-  }
-  CB_NOUNROLL for (int i = 0; i < p; i++) out[i] = round16(lpc[i], 16);
-}
-
-// find_best_pitch (pitch.c:45-103), uniform
-CB_FN void plc_find_best_pitch(const i32* xcorr, const i16* y, int len, int max_pitch, int* best_pitch,
-                               int yshift, i32 maxcorr) {
-  i32 Syy = 1;
-  i32 best_num0 = -1, best_num1 = -1;
-  i32 best_den0 = 0, best_den1 = 0;
-  const int xshift = cb_ilog2(maxcorr) - 14;
-  best_pitch[0] = 0;
-  best_pitch[1] = 1;
-  {
-    i32 part = 0;
-    CB_LANE_LOOP(j, len) part = add32(part, mult16_16(y[j], y[j]) >> yshift);
-    Syy = add32(Syy, cb_wsum(part));
-  }
-  CB_NOUNROLL for (int i = 0; i < max_pitch; i++) {
-    if (xcorr[i] > 0) {
-      i32 xcorr16 = (i16)vshr32(xcorr[i], xshift);
-      i32 num = (i16)mult16_16_q15(xcorr16, xcorr16);
-      if (mult16_32_q15(num, best_den1) > mult16_32_q15(best_num1, Syy)) {
-        if (mult16_32_q15(num, best_den0) > mult16_32_q15(best_num0, Syy)) {
-          best_num1 = best_num0; best_den1 = best_den0; best_pitch[1] = best_pitch[0];
-          best_num0 = num; best_den0 = Syy; best_pitch[0] = i;
-        } else {
-          best_num1 = num; best_den1 = Syy; best_pitch[1] = i;
-        }
-      }
-    }
-    Syy = add32(Syy, sub32(mult16_16(y[i + len], y[i + len]) >> yshift, mult16_16(y[i], y[i]) >> yshift));
-    Syy = max32(1, Syy);
-  }
-}
 
 // celt_plc_pitch_search (celt_decoder.c:399-413) = pitch_downsample + pitch_search
 CB_FN int plc_pitch_search(PlcWork& w, const CeltDecState* st) {
@@ -185,105 +73,9 @@ CB_FN int plc_pitch_search(PlcWork& w, const CeltDecState* st) {
     x_lp[i] = (i16)acc;
   }
   CB_WSYNC();
-  i32* ac = w.ac;
-  plc_autocorr(x_lp, ac, w.xx, 0, 4, len >> 1);
-  i16 lpc[4];
-  {
-    i32 a[5];
-    for (int i = 0; i < 5; i++) a[i] = ac[i];
-    a[0] = add32(a[0], a[0] >> 13);
-    for (int i = 1; i <= 4; i++) a[i] = sub32(a[i], mult16_32_q15(2 * i * i, a[i]));
-    CB_WSYNC();
-    for (int i = 0; i < 5; i++) ac[i] = a[i];
-    CB_WSYNC();
-    i16 l4[4];
-    plc_lpc(l4, ac, w.lpc32, 4);
-    i32 tmp = CB_Q15ONE;
-    for (int i = 0; i < 4; i++) {
-      tmp = (i16)mult16_16_q15(29491, tmp);            // QCONST16(.9f,15)
-      lpc[i] = (i16)mult16_16_q15(l4[i], tmp);
-    }
-  }
-  const i32 c1 = 26214;                                // QCONST16(.8f,15)
-  i16 n0 = (i16)(lpc[0] + 3277);                       // QCONST16(.8f,SIG_SHIFT)
-  i16 n1 = (i16)(lpc[1] + mult16_16_q15(c1, lpc[0]));
-  i16 n2 = (i16)(lpc[2] + mult16_16_q15(c1, lpc[1]));
-  i16 n3 = (i16)(lpc[3] + mult16_16_q15(c1, lpc[2]));
-  i16 n4 = (i16)mult16_16_q15(c1, lpc[3]);
-  // celt_fir5 (pitch.c:105-145): FIR on the inputs, so out of place via xx then copy back
-  CB_WSYNC();
-  CB_LANE_LOOP(i, len >> 1) {
-    i32 sum = shl32((i32)x_lp[i], CB_SIG_SHIFT);
-    sum = mac16_16(sum, n0, i >= 1 ? x_lp[i - 1] : 0);
-    sum = mac16_16(sum, n1, i >= 2 ? x_lp[i - 2] : 0);
-    sum = mac16_16(sum, n2, i >= 3 ? x_lp[i - 3] : 0);
-    sum = mac16_16(sum, n3, i >= 4 ? x_lp[i - 4] : 0);
-    sum = mac16_16(sum, n4, i >= 5 ? x_lp[i - 5] : 0);
-    w.xx[i] = round16(sum, CB_SIG_SHIFT);
-  }
-  CB_WSYNC();
-  CB_LANE_LOOP(i, len >> 1) x_lp[i] = w.xx[i];
-  CB_WSYNC();
-  // ---- pitch_search (pitch.c:260-369): x = x_lp + 360, y = x_lp, len 1328, max_pitch 620 ----
-  const i16* xs = x_lp + (CB_PLC_PITCH_LAG_MAX >> 1);
-  const i16* y = x_lp;
-  const int plen = CB_HIST - CB_PLC_PITCH_LAG_MAX;
-  const int max_pitch = CB_PLC_PITCH_LAG_MAX - CB_PLC_PITCH_LAG_MIN;
-  const int lag = plen + max_pitch;
-  i32 xm = 0, xn = 0;
-  CB_LANE_LOOP(j, plen >> 2) { i16 v = xs[2 * j]; w.xlp4[j] = v; xm = max32(xm, v); xn = min32(xn, v); }
-  i32 ym = 0, yn = 0;
-  CB_LANE_LOOP(j, lag >> 2) { i16 v = y[2 * j]; w.ylp4[j] = v; ym = max32(ym, v); yn = min32(yn, v); }
-  i32 xmax = max32(cb_wmax(xm), neg32(cb_wmin(xn)));
-  i32 ymax = max32(cb_wmax(ym), neg32(cb_wmin(yn)));
-  int sh = cb_ilog2(max32(1, max32(xmax, ymax))) - 11;
-  CB_WSYNC();
-  if (sh > 0) {
-    CB_LANE_LOOP(j, plen >> 2) w.xlp4[j] = (i16)(w.xlp4[j] >> sh);
-    CB_LANE_LOOP(j, lag >> 2) w.ylp4[j] = (i16)(w.ylp4[j] >> sh);
-    sh *= 2;
-  } else {
-    sh = 0;
-  }
-  CB_WSYNC();
-  // coarse search, 4x decimation (celt_pitch_xcorr, pitch.c:225-258)
-  i32 maxcorr = 1;
-  CB_NOUNROLL for (int i = 0; i < (max_pitch >> 2); i++) {
-    i32 d = 0;
-    CB_LANE_LOOP(j, plen >> 2) d = mac16_16(d, w.xlp4[j], w.ylp4[i + j]);
-    d = cb_wsum(d);
-    w.xcorr[i] = d;
-    maxcorr = max32(maxcorr, d);
-  }
-  CB_WSYNC();
-  int best_pitch[2] = {0, 0};
-  plc_find_best_pitch(w.xcorr, w.ylp4, plen >> 2, max_pitch >> 2, best_pitch, 0, maxcorr);
-  // finer search, 2x decimation
-  maxcorr = 1;
-  CB_WSYNC();
-  CB_NOUNROLL for (int i = 0; i < (max_pitch >> 1); i++) {
-    int d0 = i - 2 * best_pitch[0], d1 = i - 2 * best_pitch[1];
-    if (d0 < 0) d0 = -d0;
-    if (d1 < 0) d1 = -d1;
-    i32 val = 0;
-    if (!(d0 > 2 && d1 > 2)) {
-      i32 sum = 0;
-      CB_LANE_LOOP(j, plen >> 1) sum = add32(sum, mult16_16(xs[j], y[i + j]) >> sh);
-      sum = cb_wsum(sum);
-      val = max32(-1, sum);
-      maxcorr = max32(maxcorr, sum);
-    }
-    w.xcorr[i] = val;
-  }
-  CB_WSYNC();
-  plc_find_best_pitch(w.xcorr, y, plen >> 1, max_pitch >> 1, best_pitch, sh + 1, maxcorr);
-  int offset = 0;
-  if (best_pitch[0] > 0 && best_pitch[0] < (max_pitch >> 1) - 1) {
-    i32 a = w.xcorr[best_pitch[0] - 1], b = w.xcorr[best_pitch[0]], c = w.xcorr[best_pitch[0] + 1];
-    if (sub32(c, a) > mult16_32_q15(22938, sub32(b, a))) offset = 1;          // QCONST16(.7f,15)
-    else if (sub32(a, c) > mult16_32_q15(22938, sub32(b, c))) offset = -1;
-  }
-  int pitch = 2 * best_pitch[0] - offset;
+  pitch_whiten(x_lp, len >> 1, w.ac, w.lpc32, w.xx);
+  int pitch = pitch_search(x_lp + (CB_PLC_PITCH_LAG_MAX >> 1), x_lp, CB_HIST - CB_PLC_PITCH_LAG_MAX,
+                           CB_PLC_PITCH_LAG_MAX - CB_PLC_PITCH_LAG_MIN, w.xlp4, w.ylp4, w.xcorr);
   return CB_PLC_PITCH_LAG_MAX - pitch;
 }
 
@@ -309,7 +101,7 @@ CB_FN void celt_plc_pitch(PlcWork& w, CeltDecState* st, int N, i16* pcm, int acc
     CB_LANE_LOOP(i, CB_MAX_PERIOD) exc[i] = round16(hist_at(hist, pos, CB_HIST - CB_MAX_PERIOD + i), CB_SIG_SHIFT);
     CB_WSYNC();
     if (loss_count == 0) {
-      plc_autocorr(exc, w.ac, w.xx, 1, CB_LPC_ORDER, CB_MAX_PERIOD);
+      pitch_autocorr(exc, w.ac, w.xx, 1, CB_LPC_ORDER, CB_MAX_PERIOD);
       i32 a0 = add32(w.ac[0], w.ac[0] >> 13);
       CB_WSYNC();
       CB_LANE_LOOP(i, CB_LPC_ORDER + 1) {
@@ -318,7 +110,7 @@ CB_FN void celt_plc_pitch(PlcWork& w, CeltDecState* st, int N, i16* pcm, int acc
       }
       CB_WSYNC();
       i16 l[CB_LPC_ORDER];
-      plc_lpc(l, w.ac, w.lpc32, CB_LPC_ORDER);
+      pitch_lpc(l, w.ac, w.lpc32, CB_LPC_ORDER);
       CB_NOUNROLL for (int i = 0; i < CB_LPC_ORDER; i++) lpc[i] = l[i];
     }
     CB_WSYNC();
