@@ -103,7 +103,7 @@ def emu_lib():
     csrc = os.path.join(ROOT, "concentus_b200", "csrc")
     newest = max([os.path.getmtime(src)] + [os.path.getmtime(os.path.join(csrc, f)) for f in os.listdir(csrc)])
     if not os.path.exists(so) or os.path.getmtime(so) < newest:
-        subprocess.run(["g++", "-O2", "-fPIC", "-shared", "-Wall", "-Wno-unused-function", "-o", so, src],
+        subprocess.run(["g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-Wall", "-Wno-unused-function", "-o", so, src],
                        check=True)
     lib = ctypes.CDLL(so)
     lib.emu_celt_create.restype = ctypes.c_void_p
