@@ -32,6 +32,7 @@ CB_UTABLE u8 ct_bit_deinterleave[16] = {0x00, 0x03, 0x0C, 0x0F, 0x30, 0x33, 0x3C
                                         0xC0, 0xC3, 0xCC, 0xCF, 0xF0, 0xF3, 0xFC, 0xFF};
 
 #define CB_SPREAD_NONE 0
+#define CB_SPREAD_LIGHT 1
 #define CB_SPREAD_NORMAL 2
 #define CB_SPREAD_AGGRESSIVE 3
 #define CB_MAX_FINE_BITS 8
@@ -925,8 +926,17 @@ CB_FN void dec_tf(EntWork& w, RangeDec& rd, int start, int end, int isTransient,
 }
 
 // ---- bit allocation (rate.c:248-638), decoder side -------------------------------------------
-CB_FN int dec_allocation(EntWork& w, RangeDec& rd, int start, int end, int alloc_trim, int& intensity,
-                         int& dual_stereo, i32 total, i32& balance_out, int C, int LM) {
+// The three places where the bitstream is touched go through a coder policy `ac`, so the encoder
+// (cb_enc_quant.h) runs the same allocation with its own skip decision.
+struct AllocDecPolicy {
+  RangeDec& rd;
+  CB_MFN int skip(int, int, int, int, int, int) { return rd_bit_logp(rd, 1); }
+  CB_MFN int intensity(int, int start, int codedBands) { return start + (int)rd_uint(rd, (u32)(codedBands + 1 - start)); }
+  CB_MFN int dual(int) { return rd_bit_logp(rd, 1); }
+};
+template <class W, class AC>
+CB_FN int cb_allocation(W& w, AC& ac, int start, int end, int alloc_trim, int& intensity,
+                        int& dual_stereo, i32 total, i32& balance_out, int C, int LM) {
   i32* bits1 = w.tmp32;
   i32* bits2 = w.tmp32 + CB_NBANDS;
   i32* thresh = w.tmp32 + 2 * CB_NBANDS;
@@ -1036,7 +1046,7 @@ CB_FN int dec_allocation(EntWork& w, RangeDec& rd, int start, int end, int alloc
     int band_width = ebands(codedBands) - ebands(j);
     int band_bits = (int)(bits[j] + percoeff * band_width + rem);
     if (band_bits >= cb_imax(thresh[j], alloc_floor + (1 << CB_BITRES))) {
-      if (rd_bit_logp(rd, 1)) break;
+      if (ac.skip(codedBands, start, j, band_bits, band_width, LM)) break;
       psum += 1 << CB_BITRES;
       band_bits -= 1 << CB_BITRES;
     }
@@ -1050,13 +1060,13 @@ CB_FN int dec_allocation(EntWork& w, RangeDec& rd, int start, int end, int alloc
       bits[j] = 0;
     }
   }
-  if (intensity_rsv > 0) intensity = start + (int)rd_uint(rd, (u32)(codedBands + 1 - start));
+  if (intensity_rsv > 0) intensity = ac.intensity(intensity, start, codedBands);
   else intensity = 0;
   if (intensity <= start) {
     total += dual_stereo_rsv;
     dual_stereo_rsv = 0;
   }
-  if (dual_stereo_rsv > 0) dual_stereo = rd_bit_logp(rd, 1);
+  if (dual_stereo_rsv > 0) dual_stereo = ac.dual(dual_stereo);
   else dual_stereo = 0;
 
   i32 left = total - psum;
@@ -1092,7 +1102,7 @@ CB_FN int dec_allocation(EntWork& w, RangeDec& rd, int start, int end, int alloc
       eb = (int)((u32)eb / (u32)den) >> CB_BITRES;
       if (C * eb > (bits[j] >> CB_BITRES)) eb = bits[j] >> stereo >> CB_BITRES;
       eb = cb_imin(eb, CB_MAX_FINE_BITS);
-      w.fine_prio[j] = (i8)(eb * (den << CB_BITRES) >= bits[j] + offset);
+      w.fine_prio[j] = (eb * (den << CB_BITRES) >= bits[j] + offset);
       bits[j] -= C * eb << CB_BITRES;
     } else {
       excess = max32(0, bit - (C << CB_BITRES));
@@ -1104,20 +1114,26 @@ CB_FN int dec_allocation(EntWork& w, RangeDec& rd, int start, int end, int alloc
       int extra_fine = cb_imin(excess >> (stereo + CB_BITRES), CB_MAX_FINE_BITS - eb);
       eb += extra_fine;
       int extra_bits = extra_fine * C << CB_BITRES;
-      w.fine_prio[j] = (i8)(extra_bits >= excess - balance);
+      w.fine_prio[j] = (extra_bits >= excess - balance);
       excess -= extra_bits;
     }
     balance = excess;
-    w.fine_quant[j] = (i8)eb;
+    w.fine_quant[j] = eb;
   }
   balance_out = balance;
   CB_NOUNROLL for (; j < end; j++) {
     int eb = bits[j] >> stereo >> CB_BITRES;
-    w.fine_quant[j] = (i8)eb;
+    w.fine_quant[j] = eb;
     bits[j] = 0;
-    w.fine_prio[j] = (i8)(eb < 1);
+    w.fine_prio[j] = (eb < 1);
   }
   return codedBands;
+}
+
+CB_FN int dec_allocation(EntWork& w, RangeDec& rd, int start, int end, int alloc_trim, int& intensity,
+                         int& dual_stereo, i32 total, i32& balance_out, int C, int LM) {
+  AllocDecPolicy ac{rd};
+  return cb_allocation(w, ac, start, end, alloc_trim, intensity, dual_stereo, total, balance_out, C, LM);
 }
 
 // ---- one CELT frame, entropy half (celt_decoder.c:713-1062 minus synthesis/deemphasis) -------

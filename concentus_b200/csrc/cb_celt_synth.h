@@ -18,12 +18,6 @@ struct alignas(16) SynWork {
   i32 buf[CB_MAXN + CB_OVERLAP / 2]; // out_syn[0 .. N+overlap/2)
 };
 
-#if CB_DEVICE_BUILD
-#define CB_IF_LANE0 if (CB_LANE() == 0)
-#else
-#define CB_IF_LANE0 if (1)
-#endif
-
 CB_UTABLE i16 ct_comb_gains[3][3] = {{10048, 7112, 4248}, {15200, 8784, 0}, {26208, 3280, 0}};  // celt.c:191-194
 
 // S_MUL (celt/_kiss_fft_guts.h:57): 32-bit sample times 16-bit twiddle, Q15

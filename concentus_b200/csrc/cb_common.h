@@ -25,6 +25,7 @@ typedef int8_t i8;
 #if defined(__CUDACC__) && !defined(CB_HOST_EMU)
 #define CB_DEVICE_BUILD 1
 #define CB_FN __device__ __forceinline__
+#define CB_MFN __device__ __forceinline__   /* member functions */
 #define CB_HD __host__ __device__ __forceinline__
 #define CB_FN_NOINLINE static __device__ __noinline__
 #define CB_UTABLE static __constant__ const
@@ -40,9 +41,23 @@ CB_FN i32 cb_wmax(i32 v) { return __reduce_max_sync(0xffffffffu, v); }
 CB_FN i32 cb_wmin(i32 v) { return __reduce_min_sync(0xffffffffu, v); }
 CB_FN int cb_clz(u32 v) { return __clz((int)v); }
 template <typename T> CB_FN T cb_ldg(const T* p) { return __ldg(p); }
+// arg-max of a ratio num/den (den > 0) over the warp, ties to the lowest id (PVQ greedy search)
+struct CbBest { i32 num, den, id; };
+CB_FN CbBest cb_wbest(CbBest b) {
+  for (int o = 16; o > 0; o >>= 1) {
+    CbBest t;
+    t.num = __shfl_xor_sync(0xffffffffu, b.num, o);
+    t.den = __shfl_xor_sync(0xffffffffu, b.den, o);
+    t.id = __shfl_xor_sync(0xffffffffu, b.id, o);
+    i32 l = b.den * t.num, r = t.den * b.num;      // t better than b  <=>  b.den*t.num > t.den*b.num
+    if (l > r || (l == r && t.id < b.id)) b = t;
+  }
+  return b;
+}
 #else
 #define CB_DEVICE_BUILD 0
 #define CB_FN static inline
+#define CB_MFN inline
 #define CB_HD static inline
 #define CB_FN_NOINLINE static
 #define CB_UTABLE static const
@@ -58,6 +73,15 @@ CB_FN i32 cb_wmax(i32 v) { return v; }
 CB_FN i32 cb_wmin(i32 v) { return v; }
 CB_FN int cb_clz(u32 v) { return v ? __builtin_clz(v) : 32; }
 template <typename T> CB_FN T cb_ldg(const T* p) { return *p; }
+struct CbBest { i32 num, den, id; };
+CB_FN CbBest cb_wbest(CbBest b) { return b; }
+#endif
+
+// serial work of one stream: lane 0 on the device, the only "lane" on the host
+#if CB_DEVICE_BUILD
+#define CB_IF_LANE0 if (CB_LANE() == 0)
+#else
+#define CB_IF_LANE0 if (1)
 #endif
 
 // ---- integer helpers -------------------------------------------------------------------

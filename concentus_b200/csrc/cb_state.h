@@ -14,6 +14,8 @@
 #define CB_NBANDS 21
 #define CB_MAXN 960          // samples per channel per frame at LM=3
 #define CB_OVERLAP 120
+#define CB_SHORT_MDCT 120   // shortMdctSize
+#define CB_MAX_LM 3
 #define CB_HIST 2048         // DECODE_BUFFER_SIZE
 #define CB_LPC_ORDER 24
 #define CB_NORM_STRIDE 624   // 8*eBands[20]
