@@ -50,6 +50,10 @@ EXPORTS = [
     "opus_multistream_decode_float", "opus_multistream_decoder_ctl", "opus_multistream_decoder_destroy",
     "opus_multistream_decode_batch", "opus_multistream_decoder_group_create",
     "opus_multistream_decoder_group_destroy", "opus_multistream_decode_group_flat",
+    "opus_encoder_get_size", "opus_encoder_create", "opus_encode", "opus_encode_float", "opus_encoder_ctl",
+    "opus_encoder_destroy", "opus_encode_batch", "opus_encoder_group_create", "opus_encoder_group_destroy",
+    "opus_encode_group_flat", "opus_encode_group_device", "opus_encoder_get_final_range_batch",
+    "opus_b200_encode_profile_begin", "opus_b200_encode_profile_end",
 ]
 
 _lib = None
@@ -109,6 +113,21 @@ def load():
     lib.opus_multistream_decode_group_flat.argtypes = [vp, vp, ctypes.c_int32, vp, vp, vp, ctypes.c_int32,
                                                        ctypes.c_int, vp, vp]
     lib.opus_decoder_get_final_range_batch.argtypes = [vp, ctypes.c_int, vp]
+    lib.opus_encoder_create.restype = vp
+    lib.opus_encoder_create.argtypes = [ctypes.c_int32, ctypes.c_int, ctypes.c_int, c_int_p]
+    lib.opus_encoder_destroy.argtypes = [vp]
+    lib.opus_encoder_destroy.restype = None
+    lib.opus_encode.argtypes = [vp, vp, ctypes.c_int, vp, ctypes.c_int32]
+    lib.opus_encode_float.argtypes = [vp, vp, ctypes.c_int, vp, ctypes.c_int32]
+    lib.opus_encode_batch.argtypes = [vp, ctypes.c_int, vp, ctypes.c_int, vp, ctypes.c_int32, vp]
+    lib.opus_encoder_group_create.restype = vp
+    lib.opus_encoder_group_create.argtypes = [vp, ctypes.c_int, c_int_p]
+    lib.opus_encoder_group_destroy.argtypes = [vp]
+    lib.opus_encoder_group_destroy.restype = None
+    lib.opus_encode_group_flat.argtypes = [vp, vp, ctypes.c_int, vp, ctypes.c_int32, vp]
+    lib.opus_encode_group_device.argtypes = [vp, vp, ctypes.c_int, vp, ctypes.c_int32, vp]
+    lib.opus_encoder_get_final_range_batch.argtypes = [vp, ctypes.c_int, vp]
+    lib.opus_b200_encode_profile_end.argtypes = [vp, vp]
     lib.opus_b200_launch_count.restype = ctypes.c_longlong
     lib.opus_packet_get_nb_samples.argtypes = [vp, ctypes.c_int32, ctypes.c_int32]
     lib.opus_packet_get_nb_frames.argtypes = [vp, ctypes.c_int32]
@@ -337,3 +356,113 @@ class OpusMSBatchDecoder(object):
         if rc != OPUS_OK:
             raise OpusError(rc, "opus_multistream_decode_group_flat")
         return ret, pcm
+
+
+# ---- encoder (reference: CSharp/Concentus/Native/NativeOpusEncoder.cs) ---------------------------
+OPUS_APPLICATION_VOIP = 2048
+OPUS_APPLICATION_AUDIO = 2049
+OPUS_APPLICATION_RESTRICTED_LOWDELAY = 2051
+OPUS_SET_BITRATE_REQUEST = 4002
+OPUS_SET_VBR_REQUEST = 4006
+OPUS_SET_COMPLEXITY_REQUEST = 4010
+OPUS_SET_VBR_CONSTRAINT_REQUEST = 4020
+OPUS_SET_FORCE_MODE_REQUEST = 11002
+OPUS_GET_FINAL_RANGE_REQUEST_ENC = 4031
+
+
+class OpusEncoder(object):
+    """One stream.  Mirrors NativeOpusEncoder: encode(pcm int16 [frame*channels]) -> bytes."""
+
+    def __init__(self, sample_rate, channels, application=OPUS_APPLICATION_AUDIO):
+        lib = load()
+        err = ctypes.c_int(0)
+        self._h = lib.opus_encoder_create(sample_rate, channels, application, ctypes.byref(err))
+        if not self._h:
+            raise OpusError(err.value, "opus_encoder_create")
+        self.sample_rate = sample_rate
+        self.channels = channels
+
+    def close(self):
+        if getattr(self, "_h", None):
+            load().opus_encoder_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def ctl(self, request, value):
+        rc = load().opus_encoder_ctl(ctypes.c_void_p(self._h), ctypes.c_int(request), ctypes.c_int(value))
+        if rc < 0:
+            raise OpusError(rc, "opus_encoder_ctl(%d)" % request)
+
+    def get(self, request):
+        out = ctypes.c_int32(0)
+        rc = load().opus_encoder_ctl(ctypes.c_void_p(self._h), ctypes.c_int(request), ctypes.byref(out))
+        if rc < 0:
+            raise OpusError(rc, "opus_encoder_ctl(%d)" % request)
+        return out.value
+
+    @property
+    def final_range(self):
+        return self.get(OPUS_GET_FINAL_RANGE_REQUEST_ENC) & 0xFFFFFFFF
+
+    def encode(self, pcm, frame_size, max_data_bytes=1275):
+        """Returns the packet bytes; raises OpusError on a negative return code."""
+        pcm = np.ascontiguousarray(pcm, dtype=np.int16)
+        buf = np.zeros(max_data_bytes, dtype=np.uint8)
+        n = load().opus_encode(self._h, _ptr(pcm), frame_size, _ptr(buf), max_data_bytes)
+        if n < 0:
+            raise OpusError(n, "opus_encode")
+        return buf[:n].tobytes()
+
+
+class OpusBatchEncoder(object):
+    """n independent encoders driven by one kernel launch per frame."""
+
+    def __init__(self, n, sample_rate, channels, application=OPUS_APPLICATION_AUDIO):
+        self.encoders = [OpusEncoder(sample_rate, channels, application) for _ in range(n)]
+        self.n = n
+        self.channels = channels
+        lib = load()
+        arr = (ctypes.c_void_p * n)(*[e._h for e in self.encoders])
+        err = ctypes.c_int(0)
+        self._g = lib.opus_encoder_group_create(arr, n, ctypes.byref(err))
+        if not self._g:
+            raise OpusError(err.value, "opus_encoder_group_create")
+
+    def close(self):
+        if getattr(self, "_g", None):
+            load().opus_encoder_group_destroy(self._g)
+            self._g = None
+        for e in getattr(self, "encoders", []):
+            e.close()
+
+    __del__ = close
+
+    def ctl(self, request, value):
+        for e in self.encoders:
+            e.ctl(request, value)
+
+    def encode(self, pcm, frame_size, max_data_bytes=1275):
+        """pcm: int16 [n, frame_size*channels].  Returns (data uint8 [n, max_data_bytes], lens int32 [n])."""
+        pcm = np.ascontiguousarray(pcm, dtype=np.int16)
+        assert pcm.shape == (self.n, frame_size * self.channels)
+        data = np.zeros((self.n, max_data_bytes), dtype=np.uint8)
+        lens = np.zeros(self.n, dtype=np.int32)
+        rc = load().opus_encode_group_flat(self._g, _ptr(pcm), frame_size, _ptr(data), max_data_bytes, _ptr(lens))
+        if rc < 0:
+            raise OpusError(rc, "opus_encode_group_flat")
+        return data, lens
+
+    def encode_device(self, d_pcm_ptr, frame_size, d_data_ptr, max_data_bytes, d_len_ptr):
+        """Raw device pointers (e.g. torch tensors' data_ptr()); asynchronous."""
+        rc = load().opus_encode_group_device(self._g, d_pcm_ptr, frame_size, d_data_ptr, max_data_bytes, d_len_ptr)
+        if rc < 0:
+            raise OpusError(rc, "opus_encode_group_device")
+
+    def final_ranges(self):
+        arr = (ctypes.c_void_p * self.n)(*[e._h for e in self.encoders])
+        out = np.zeros(self.n, dtype=np.uint32)
+        rc = load().opus_encoder_get_final_range_batch(arr, self.n, _ptr(out))
+        if rc < 0:
+            raise OpusError(rc, "opus_encoder_get_final_range_batch")
+        return out

@@ -1,0 +1,52 @@
+// cb_enc_kernels.cu -- sm_100a kernel of the batched Opus (CELT-only) encoder and its launcher.
+//
+//   opus_encode_kernel : 1 warp / stream -- the whole frame: DC reject, pre-emphasis, pitch
+//   pre-filter, MDCT, band analysis, bit allocation, PVQ search, range coder, TOC / padding.
+//
+// Integer, latency-bound work (no tensor cores).  Per stream the kernel reads frame_size*channels
+// int16 samples and writes one packet; the large per-frame vectors (EncScratch, ~49 KB/stream)
+// sit in global memory and stay L2-resident, the band-level working set (EncWork) in shared memory.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "cb_opus_enc.h"
+#include "cb_enc_kernels.h"
+
+#define E_WARPS 4
+
+__global__ void __launch_bounds__(E_WARPS * 32)
+opus_encode_kernel(OpusEncState* const* states, EncScratch* scratch, const i16* pcm, i32 pcm_stride, int frame_size,
+                   u8* data, i32 data_stride, int max_data_bytes, i32* out_len, int n) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int warp = threadIdx.x >> 5;
+  const int s = blockIdx.x * E_WARPS + warp;
+  if (s >= n) return;
+  EncWork& w = *reinterpret_cast<EncWork*>(smem + (size_t)warp * sizeof(EncWork));
+  const int ret = opus_encode_stream(w, scratch[s], states[s], pcm + (size_t)s * pcm_stride, frame_size,
+                                     data + (size_t)s * data_stride, max_data_bytes);
+  if ((threadIdx.x & 31) == 0) out_len[s] = ret;
+}
+
+extern "C" {
+
+size_t cbk_sizeof_enc_state(void) { return sizeof(OpusEncState); }
+size_t cbk_sizeof_enc_scratch(void) { return sizeof(EncScratch); }
+
+int cbk_launch_encode(OpusEncState* const* d_states, void* d_scratch, const i16* d_pcm, i32 pcm_stride,
+                      int frame_size, u8* d_data, i32 data_stride, int max_data_bytes, i32* d_len, int n,
+                      cudaStream_t stream) {
+  static bool attr_set[16] = {false};
+  const size_t smem = sizeof(EncWork) * E_WARPS;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 0 && dev < 16 && !attr_set[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(opus_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    attr_set[dev] = true;
+  }
+  const int blocks = (n + E_WARPS - 1) / E_WARPS;
+  opus_encode_kernel<<<blocks, E_WARPS * 32, smem, stream>>>(d_states, (EncScratch*)d_scratch, d_pcm, pcm_stride,
+                                                            frame_size, d_data, data_stride, max_data_bytes, d_len, n);
+  return (int)cudaGetLastError();
+}
+
+}  // extern "C"

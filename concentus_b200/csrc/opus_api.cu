@@ -957,6 +957,18 @@ OpusDecState* opusb_internal_device_state(const OpusDecoder* st, int* device) {
   return st->d_state;
 }
 
+// internal (used by opus_enc_api.cu): the per-device stream all launches of this library go on,
+// so that opus_b200_synchronize() covers encoder launches too; and the launch counter.
+cudaStream_t opusb_internal_stream(int* err) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  DevCtx* c = ctx_for_current_device(err);
+  return c ? c->stream : nullptr;
+}
+void opusb_internal_count_launches(int n) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  g_launches += n;
+}
+
 int opus_b200_profile_begin(void) {
   std::lock_guard<std::mutex> lk(g_mu);
   g_prof_on = true;

@@ -1,0 +1,376 @@
+// opus_enc_api.cu -- host side of the encoder half of libopus_b200.so: the libopus encoder ABI
+// (opus_encoder_create / opus_encode / opus_encode_float / opus_encoder_ctl / opus_encoder_destroy,
+// opus-fix/src/opus_encoder.c) plus the batch entry points.  Holds no codec arithmetic: packets
+// are produced by opus_encode_kernel (cb_enc_kernels.cu).  There is NO CPU encode path.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <vector>
+#include "../../include/opus_b200.h"
+#include "cb_enc_ctl.h"
+#include "cb_enc_kernels.h"
+#include "cb_enc_state.h"
+
+#define CUDA_OK(call)                                                                            \
+  do {                                                                                           \
+    cudaError_t e_ = (call);                                                                     \
+    if (e_ != cudaSuccess) {                                                                     \
+      fprintf(stderr, "[opus_b200] CUDA error %s at %s:%d: %s\n", cudaGetErrorName(e_), __FILE__, \
+              __LINE__, cudaGetErrorString(e_));                                                 \
+      return OPUS_INTERNAL_ERROR;                                                                \
+    }                                                                                            \
+  } while (0)
+
+extern "C" cudaStream_t opusb_internal_stream(int* err);
+extern "C" void opusb_internal_count_launches(int n);
+
+namespace {
+const int kEncMagic = 0x4f453230;   // "OE20"
+
+struct EncProf { cudaEvent_t a, b; };
+bool g_enc_prof_on = false;
+std::vector<EncProf> g_enc_prof;
+}  // namespace
+
+struct OpusEncoderGroup;
+struct OpusEncoder {
+  int magic;
+  int Fs, channels, application;
+  int device;
+  OpusEncState* d_state;
+  OpusEncoderGroup* self_group;   // group of one, created on first opus_encode()
+};
+
+struct OpusEncoderGroup {
+  int magic;
+  int n, device;
+  int Fs, channels;               // common values, or -1 when the members differ
+  OpusEncoder** members;
+  OpusEncState** d_states;        // device array of n state pointers
+  void* d_scratch;                // n EncScratch
+  i32* d_len;                     // n
+  // staging for the host-buffer entry point (grow-only)
+  i16* d_pcm; size_t d_pcm_cap;
+  u8* d_data; size_t d_data_cap;
+  i16* h_pcm; size_t h_pcm_cap;   // pinned
+  u8* h_data; size_t h_data_cap;  // pinned
+  i32* h_len;                     // pinned, n
+};
+
+namespace {
+
+int grow_dev(void** p, size_t* cap, size_t bytes) {
+  if (bytes <= *cap) return OPUS_OK;
+  if (*p) cudaFree(*p);
+  *p = nullptr; *cap = 0;
+  if (cudaMalloc(p, bytes) != cudaSuccess) {
+    fprintf(stderr, "[opus_b200] cudaMalloc of %zu bytes failed\n", bytes);
+    return OPUS_ALLOC_FAIL;
+  }
+  *cap = bytes;
+  return OPUS_OK;
+}
+int grow_pinned(void** p, size_t* cap, size_t bytes) {
+  if (bytes <= *cap) return OPUS_OK;
+  if (*p) cudaFreeHost(*p);
+  *p = nullptr; *cap = 0;
+  if (cudaMallocHost(p, bytes) != cudaSuccess) {
+    fprintf(stderr, "[opus_b200] cudaMallocHost of %zu bytes failed\n", bytes);
+    return OPUS_ALLOC_FAIL;
+  }
+  *cap = bytes;
+  return OPUS_OK;
+}
+
+bool valid(const OpusEncoder* st) { return st && st->magic == kEncMagic; }
+bool valid(const OpusEncoderGroup* g) { return g && g->magic == kEncMagic + 1; }
+
+// launch one frame for every member; device buffers as described in cb_enc_kernels.h
+int group_launch(OpusEncoderGroup* g, const i16* d_pcm, i32 pcm_stride, int frame_size, u8* d_data, i32 data_stride,
+                 int max_data_bytes, i32* d_len, cudaStream_t stream) {
+  EncProf pr{nullptr, nullptr};
+  if (g_enc_prof_on) { cudaEventCreate(&pr.a); cudaEventCreate(&pr.b); cudaEventRecord(pr.a, stream); }
+  int rc = cbk_launch_encode(g->d_states, g->d_scratch, d_pcm, pcm_stride, frame_size, d_data, data_stride,
+                             max_data_bytes, d_len, g->n, stream);
+  if (g_enc_prof_on) { cudaEventRecord(pr.b, stream); g_enc_prof.push_back(pr); }
+  opusb_internal_count_launches(1);
+  if (rc != 0) {
+    fprintf(stderr, "[opus_b200] encode kernel launch failed: %s\n", cudaGetErrorString((cudaError_t)rc));
+    return OPUS_INTERNAL_ERROR;
+  }
+  return OPUS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int opus_encoder_get_size(int channels) {
+  if (channels < 1 || channels > 2) return 0;
+  return (int)sizeof(OpusEncoder);           // the codec state itself lives in device memory
+}
+
+OpusEncoder* opus_encoder_create(opus_int32 Fs, int channels, int application, int* error) {
+  if ((Fs != 48000 && Fs != 24000 && Fs != 16000 && Fs != 12000 && Fs != 8000) || (channels != 1 && channels != 2) ||
+      (application != OPUS_APPLICATION_VOIP && application != OPUS_APPLICATION_AUDIO &&
+       application != OPUS_APPLICATION_RESTRICTED_LOWDELAY)) {
+    if (error) *error = OPUS_BAD_ARG;
+    return nullptr;
+  }
+  int err = 0;
+  cudaStream_t stream = opusb_internal_stream(&err);
+  if (!stream) { if (error) *error = err; return nullptr; }
+  OpusEncoder* st = (OpusEncoder*)calloc(1, sizeof(OpusEncoder));
+  OpusEncState* h = (OpusEncState*)malloc(sizeof(OpusEncState));
+  if (!st || !h) { free(st); free(h); if (error) *error = OPUS_ALLOC_FAIL; return nullptr; }
+  opus_enc_init(h, Fs, channels, application);
+  cudaGetDevice(&st->device);
+  if (cudaMalloc((void**)&st->d_state, sizeof(OpusEncState)) != cudaSuccess ||
+      cudaMemcpy(st->d_state, h, sizeof(OpusEncState), cudaMemcpyHostToDevice) != cudaSuccess) {
+    fprintf(stderr, "[opus_b200] encoder state allocation failed: %s\n", cudaGetErrorString(cudaGetLastError()));
+    if (st->d_state) cudaFree(st->d_state);
+    free(st); free(h);
+    if (error) *error = OPUS_ALLOC_FAIL;
+    return nullptr;
+  }
+  free(h);
+  st->magic = kEncMagic;
+  st->Fs = Fs; st->channels = channels; st->application = application;
+  if (error) *error = OPUS_OK;
+  return st;
+}
+
+void opus_encoder_group_destroy(OpusEncoderGroup* g);
+
+void opus_encoder_destroy(OpusEncoder* st) {
+  if (!valid(st)) return;
+  if (st->self_group) opus_encoder_group_destroy(st->self_group);
+  cudaFree(st->d_state);
+  st->magic = 0;
+  free(st);
+}
+
+OpusEncoderGroup* opus_encoder_group_create(OpusEncoder* const* st, int n, int* error) {
+  if (!st || n <= 0) { if (error) *error = OPUS_BAD_ARG; return nullptr; }
+  for (int i = 0; i < n; i++)
+    if (!valid(st[i]) || st[i]->device != st[0]->device) { if (error) *error = OPUS_BAD_ARG; return nullptr; }
+  OpusEncoderGroup* g = (OpusEncoderGroup*)calloc(1, sizeof(OpusEncoderGroup));
+  if (!g) { if (error) *error = OPUS_ALLOC_FAIL; return nullptr; }
+  g->n = n; g->device = st[0]->device;
+  g->Fs = st[0]->Fs; g->channels = st[0]->channels;
+  g->members = (OpusEncoder**)malloc(sizeof(OpusEncoder*) * n);
+  std::vector<OpusEncState*> ptrs(n);
+  for (int i = 0; i < n; i++) {
+    g->members[i] = st[i];
+    ptrs[i] = st[i]->d_state;
+    if (st[i]->Fs != g->Fs) g->Fs = -1;
+    if (st[i]->channels != g->channels) g->channels = -1;
+  }
+  bool ok = cudaMalloc((void**)&g->d_states, sizeof(OpusEncState*) * n) == cudaSuccess &&
+            cudaMalloc(&g->d_scratch, cbk_sizeof_enc_scratch() * (size_t)n) == cudaSuccess &&
+            cudaMalloc((void**)&g->d_len, sizeof(i32) * n) == cudaSuccess &&
+            cudaMallocHost((void**)&g->h_len, sizeof(i32) * n) == cudaSuccess &&
+            cudaMemcpy(g->d_states, ptrs.data(), sizeof(OpusEncState*) * n, cudaMemcpyHostToDevice) == cudaSuccess;
+  if (!ok) {
+    fprintf(stderr, "[opus_b200] encoder group allocation failed: %s\n", cudaGetErrorString(cudaGetLastError()));
+    g->magic = kEncMagic + 1;
+    opus_encoder_group_destroy(g);
+    if (error) *error = OPUS_ALLOC_FAIL;
+    return nullptr;
+  }
+  g->magic = kEncMagic + 1;
+  if (error) *error = OPUS_OK;
+  return g;
+}
+
+void opus_encoder_group_destroy(OpusEncoderGroup* g) {
+  if (!valid(g)) return;
+  cudaFree(g->d_states); cudaFree(g->d_scratch); cudaFree(g->d_len);
+  cudaFree(g->d_pcm); cudaFree(g->d_data);
+  cudaFreeHost(g->h_pcm); cudaFreeHost(g->h_data); cudaFreeHost(g->h_len);
+  free(g->members);
+  g->magic = 0;
+  free(g);
+}
+
+// Device-resident batch: d_pcm holds n rows of frame_size*channels int16 (row stride = that count),
+// d_data n rows of max_data_bytes, d_len n lengths.  Asynchronous on the library stream
+// (opus_b200_synchronize() waits for it).
+int opus_encode_group_device(OpusEncoderGroup* g, const opus_int16* d_pcm, int frame_size, unsigned char* d_data,
+                             opus_int32 max_data_bytes, opus_int32* d_len) {
+  if (!valid(g) || !d_pcm || !d_data || !d_len || frame_size <= 0 || max_data_bytes <= 0) return OPUS_BAD_ARG;
+  if (g->channels < 0) return OPUS_BAD_ARG;
+  int err = 0;
+  cudaStream_t stream = opusb_internal_stream(&err);
+  if (!stream) return err;
+  return group_launch(g, d_pcm, frame_size * g->channels, frame_size, d_data, max_data_bytes, max_data_bytes, d_len,
+                      stream);
+}
+
+// Host-buffer batch: pcm = n rows of frame_size*channels int16, data = n rows of max_data_bytes,
+// out_len[n].  Copies in, encodes, copies packets and lengths back; synchronous.
+int opus_encode_group_flat(OpusEncoderGroup* g, const opus_int16* pcm, int frame_size, unsigned char* data,
+                           opus_int32 max_data_bytes, opus_int32* out_len) {
+  if (!valid(g) || !pcm || !data || !out_len || frame_size <= 0 || max_data_bytes <= 0) return OPUS_BAD_ARG;
+  if (g->channels < 0) return OPUS_BAD_ARG;
+  int err = 0;
+  cudaStream_t stream = opusb_internal_stream(&err);
+  if (!stream) return err;
+  const size_t row = (size_t)frame_size * g->channels;
+  const size_t pcm_bytes = row * sizeof(i16) * g->n, data_bytes = (size_t)max_data_bytes * g->n;
+  int rc;
+  if ((rc = grow_dev((void**)&g->d_pcm, &g->d_pcm_cap, pcm_bytes)) != OPUS_OK) return rc;
+  if ((rc = grow_dev((void**)&g->d_data, &g->d_data_cap, data_bytes)) != OPUS_OK) return rc;
+  if ((rc = grow_pinned((void**)&g->h_pcm, &g->h_pcm_cap, pcm_bytes)) != OPUS_OK) return rc;
+  if ((rc = grow_pinned((void**)&g->h_data, &g->h_data_cap, data_bytes)) != OPUS_OK) return rc;
+  memcpy(g->h_pcm, pcm, pcm_bytes);
+  CUDA_OK(cudaMemcpyAsync(g->d_pcm, g->h_pcm, pcm_bytes, cudaMemcpyHostToDevice, stream));
+  rc = group_launch(g, g->d_pcm, (i32)row, frame_size, g->d_data, max_data_bytes, max_data_bytes, g->d_len, stream);
+  if (rc != OPUS_OK) return rc;
+  CUDA_OK(cudaMemcpyAsync(g->h_data, g->d_data, data_bytes, cudaMemcpyDeviceToHost, stream));
+  CUDA_OK(cudaMemcpyAsync(g->h_len, g->d_len, sizeof(i32) * g->n, cudaMemcpyDeviceToHost, stream));
+  CUDA_OK(cudaStreamSynchronize(stream));
+  memcpy(data, g->h_data, data_bytes);
+  memcpy(out_len, g->h_len, sizeof(i32) * g->n);
+  return OPUS_OK;
+}
+
+// The reference call, one stream (opus_encoder.c:2012-2031): a group of one.
+opus_int32 opus_encode(OpusEncoder* st, const opus_int16* pcm, int frame_size, unsigned char* data,
+                       opus_int32 max_data_bytes) {
+  if (!valid(st) || !pcm || !data) return OPUS_BAD_ARG;
+  if (frame_size <= 0 || max_data_bytes <= 0) return OPUS_BAD_ARG;
+  if (!st->self_group) {
+    int err = 0;
+    st->self_group = opus_encoder_group_create(&st, 1, &err);
+    if (!st->self_group) return err;
+  }
+  const int mb = max_data_bytes > 1276 ? 1276 : max_data_bytes;   // the encoder never writes more (opus_encoder.c:980)
+  opus_int32 len = 0;
+  int rc = opus_encode_group_flat(st->self_group, pcm, frame_size, data, mb, &len);
+  if (rc != OPUS_OK) return rc;
+  return len;
+}
+
+// FIXED_POINT opus_encode_float (opus_encoder.c:1968-2008): FLOAT2INT16 on the host, then opus_encode.
+opus_int32 opus_encode_float(OpusEncoder* st, const float* pcm, int frame_size, unsigned char* data,
+                             opus_int32 max_data_bytes) {
+  if (!valid(st) || !pcm || !data || frame_size <= 0) return OPUS_BAD_ARG;
+  std::vector<opus_int16> in((size_t)frame_size * st->channels);
+  for (size_t i = 0; i < in.size(); i++) {
+    float x = pcm[i] * 32768.f;
+    x = x > -32768.f ? x : -32768.f;
+    x = x < 32767.f ? x : 32767.f;
+    in[i] = (opus_int16)lrintf(x);
+  }
+  return opus_encode(st, in.data(), frame_size, data, max_data_bytes);
+}
+
+// Pointer-array batch over arbitrary encoders (mixed rates / channel counts allowed): streams are
+// bucketed by nothing -- each call builds a transient group; for steady-state use make a group once.
+int opus_encode_batch(OpusEncoder* const* st, int n, const opus_int16* const* pcm, int frame_size,
+                      unsigned char* const* data, opus_int32 max_data_bytes, opus_int32* out_len) {
+  if (!st || !pcm || !data || !out_len || n <= 0 || frame_size <= 0 || max_data_bytes <= 0) return OPUS_BAD_ARG;
+  int err = 0;
+  OpusEncoderGroup* g = opus_encoder_group_create(st, n, &err);
+  if (!g) return err;
+  int rc = OPUS_OK;
+  if (g->channels < 0) rc = OPUS_BAD_ARG;   // a flat batch needs one channel count; mixed groups go one by one
+  if (rc == OPUS_OK) {
+    const int mb = max_data_bytes > 1276 ? 1276 : max_data_bytes;
+    const size_t row = (size_t)frame_size * g->channels;
+    std::vector<opus_int16> flat(row * n);
+    std::vector<unsigned char> out((size_t)mb * n);
+    for (int i = 0; i < n; i++) memcpy(&flat[row * i], pcm[i], row * sizeof(opus_int16));
+    rc = opus_encode_group_flat(g, flat.data(), frame_size, out.data(), mb, out_len);
+    if (rc == OPUS_OK)
+      for (int i = 0; i < n; i++)
+        if (out_len[i] > 0) memcpy(data[i], &out[(size_t)mb * i], (size_t)out_len[i]);
+  }
+  opus_encoder_group_destroy(g);
+  return rc;
+}
+
+int opus_encoder_ctl(OpusEncoder* st, int request, ...) {
+  if (!valid(st)) return OPUS_BAD_ARG;
+  va_list ap;
+  va_start(ap, request);
+  int ret = OPUS_OK;
+  int err = 0;
+  cudaStream_t stream = opusb_internal_stream(&err);
+  if (!stream) { va_end(ap); return err; }
+  cudaStreamSynchronize(stream);
+  if (request == OPUS_RESET_STATE) {
+    OpusEncState* h = (OpusEncState*)malloc(sizeof(OpusEncState));
+    if (!h) { va_end(ap); return OPUS_ALLOC_FAIL; }
+    if (cudaMemcpy(h, st->d_state, sizeof(OpusEncState), cudaMemcpyDeviceToHost) != cudaSuccess) ret = OPUS_INTERNAL_ERROR;
+    if (ret == OPUS_OK) {
+      opus_enc_reset(h);
+      if (cudaMemcpy(st->d_state, h, sizeof(OpusEncState), cudaMemcpyHostToDevice) != cudaSuccess) ret = OPUS_INTERNAL_ERROR;
+    }
+    free(h);
+    va_end(ap);
+    return ret;
+  }
+  // scalars only: read both scalar blocks, apply, write back when it was a setter
+  OpusEncScalars o;
+  CeltEncScalars cs;
+  CeltEncScalars* d_cs = (CeltEncScalars*)((char*)st->d_state + offsetof(OpusEncState, celt));
+  if (cudaMemcpy(&o, st->d_state, sizeof(o), cudaMemcpyDeviceToHost) != cudaSuccess ||
+      cudaMemcpy(&cs, d_cs, sizeof(cs), cudaMemcpyDeviceToHost) != cudaSuccess) {
+    va_end(ap);
+    return OPUS_INTERNAL_ERROR;
+  }
+  if (opus_enc_ctl_is_get(request)) {
+    opus_int32* out = va_arg(ap, opus_int32*);
+    if (!out) { va_end(ap); return OPUS_BAD_ARG; }
+    ret = opus_enc_ctl_scalars(&o, &cs, request, 0, out);
+  } else {
+    opus_int32 value = va_arg(ap, opus_int32);
+    i32 dummy = 0;
+    ret = opus_enc_ctl_scalars(&o, &cs, request, value, &dummy);
+    if (ret == OPUS_OK) {
+      if (cudaMemcpy(st->d_state, &o, sizeof(o), cudaMemcpyHostToDevice) != cudaSuccess ||
+          cudaMemcpy(d_cs, &cs, sizeof(cs), cudaMemcpyHostToDevice) != cudaSuccess)
+        ret = OPUS_INTERNAL_ERROR;
+    }
+  }
+  va_end(ap);
+  return ret;
+}
+
+int opus_encoder_get_final_range_batch(OpusEncoder* const* st, int n, opus_uint32* out) {
+  if (!st || !out || n <= 0) return OPUS_BAD_ARG;
+  int err = 0;
+  cudaStream_t stream = opusb_internal_stream(&err);
+  if (!stream) return err;
+  CUDA_OK(cudaStreamSynchronize(stream));
+  for (int i = 0; i < n; i++) {
+    if (!valid(st[i])) return OPUS_BAD_ARG;
+    CUDA_OK(cudaMemcpy(&out[i], (char*)st[i]->d_state + offsetof(OpusEncScalars, rangeFinal), sizeof(opus_uint32),
+                       cudaMemcpyDeviceToHost));
+  }
+  return OPUS_OK;
+}
+
+// per-launch timing of the encode kernel (CUDA events on the launching stream), for bench.py
+int opus_b200_encode_profile_begin(void) { g_enc_prof_on = true; return OPUS_OK; }
+int opus_b200_encode_profile_end(double* ms, long long* count) {
+  g_enc_prof_on = false;
+  cudaDeviceSynchronize();
+  double total = 0; long long c = 0;
+  for (auto& r : g_enc_prof) {
+    float t = 0;
+    if (cudaEventElapsedTime(&t, r.a, r.b) == cudaSuccess) { total += t; c++; }
+    cudaEventDestroy(r.a); cudaEventDestroy(r.b);
+  }
+  g_enc_prof.clear();
+  if (ms) *ms = total;
+  if (count) *count = c;
+  return OPUS_OK;
+}
+
+}  // extern "C"

@@ -176,6 +176,99 @@ int opus_decode_batch_device_static(OpusDecoder *const *st, int n, const unsigne
 /* Batched OPUS_GET_FINAL_RANGE: out[i] = final range of the last packet decoded by st[i]. */
 int opus_decoder_get_final_range_batch(OpusDecoder *const *st, int n, opus_uint32 *out);
 
+/* ---- Encoder (CELT-only Opus packets) ---------------------------------------------------- */
+
+/* Applications and special values (opus-fix/include/opus_defines.h:190-214) */
+#define OPUS_AUTO -1000
+#define OPUS_BITRATE_MAX -1
+#define OPUS_APPLICATION_VOIP 2048
+#define OPUS_APPLICATION_AUDIO 2049
+#define OPUS_APPLICATION_RESTRICTED_LOWDELAY 2051
+#define OPUS_SIGNAL_VOICE 3001
+#define OPUS_SIGNAL_MUSIC 3002
+#define OPUS_BANDWIDTH_NARROWBAND 1101
+#define OPUS_BANDWIDTH_MEDIUMBAND 1102
+#define OPUS_BANDWIDTH_WIDEBAND 1103
+#define OPUS_BANDWIDTH_SUPERWIDEBAND 1104
+#define OPUS_BANDWIDTH_FULLBAND 1105
+#define OPUS_FRAMESIZE_ARG 5000
+/* ctl requests understood by opus_encoder_ctl (opus_defines.h:130-167; opus_encoder.c:2031-2504):
+ * setters take an opus_int32, getters an opus_int32* (OPUS_GET_FINAL_RANGE an opus_uint32*). */
+#define OPUS_SET_APPLICATION_REQUEST 4000
+#define OPUS_GET_APPLICATION_REQUEST 4001
+#define OPUS_SET_BITRATE_REQUEST 4002
+#define OPUS_GET_BITRATE_REQUEST 4003
+#define OPUS_SET_MAX_BANDWIDTH_REQUEST 4004
+#define OPUS_GET_MAX_BANDWIDTH_REQUEST 4005
+#define OPUS_SET_VBR_REQUEST 4006
+#define OPUS_GET_VBR_REQUEST 4007
+#define OPUS_SET_BANDWIDTH_REQUEST 4008
+#define OPUS_SET_COMPLEXITY_REQUEST 4010
+#define OPUS_GET_COMPLEXITY_REQUEST 4011
+#define OPUS_SET_INBAND_FEC_REQUEST 4012
+#define OPUS_GET_INBAND_FEC_REQUEST 4013
+#define OPUS_SET_PACKET_LOSS_PERC_REQUEST 4014
+#define OPUS_GET_PACKET_LOSS_PERC_REQUEST 4015
+#define OPUS_SET_DTX_REQUEST 4016
+#define OPUS_GET_DTX_REQUEST 4017
+#define OPUS_SET_VBR_CONSTRAINT_REQUEST 4020
+#define OPUS_GET_VBR_CONSTRAINT_REQUEST 4021
+#define OPUS_SET_FORCE_CHANNELS_REQUEST 4022
+#define OPUS_GET_FORCE_CHANNELS_REQUEST 4023
+#define OPUS_SET_SIGNAL_REQUEST 4024
+#define OPUS_GET_SIGNAL_REQUEST 4025
+#define OPUS_GET_LOOKAHEAD_REQUEST 4027
+#define OPUS_SET_LSB_DEPTH_REQUEST 4036
+#define OPUS_GET_LSB_DEPTH_REQUEST 4037
+#define OPUS_SET_EXPERT_FRAME_DURATION_REQUEST 4040
+#define OPUS_GET_EXPERT_FRAME_DURATION_REQUEST 4041
+#define OPUS_SET_PREDICTION_DISABLED_REQUEST 4042
+#define OPUS_GET_PREDICTION_DISABLED_REQUEST 4043
+#define OPUS_SET_FORCE_MODE_REQUEST 11002 /* src/opus_private.h:79; 1002 = CELT-only */
+
+typedef struct OpusEncoder OpusEncoder;
+typedef struct OpusEncoderGroup OpusEncoderGroup;
+
+/* The libopus encoder ABI that Concentus binds (CSharp/Concentus/Native/NativeOpus.cs:105-150,180-225;
+ * C prototypes opus-fix/include/opus.h:165-350).  Packets are byte-identical to the reference's
+ * fixed-point encoder whenever its mode decision is CELT-only (always for
+ * OPUS_APPLICATION_RESTRICTED_LOWDELAY or OPUS_SET_FORCE_MODE(1002); for OPUS_APPLICATION_AUDIO at
+ * the rates where the reference picks CELT).  Frames the reference would code with SILK or hybrid,
+ * OPUS_APPLICATION_VOIP, and 40/60 ms frames return OPUS_UNIMPLEMENTED. */
+/* replaces opus_encoder_get_size (src/opus_encoder.c:150-164): size of the host handle only */
+int opus_encoder_get_size(int channels);
+/* replaces opus_encoder_create (src/opus_encoder.c:482-510; NativeOpus.cs:105,180) */
+OpusEncoder *opus_encoder_create(opus_int32 Fs, int channels, int application, int *error);
+/* replaces opus_encode (src/opus_encoder.c:2007-2031; NativeOpus.cs:111,186): a batch of one */
+opus_int32 opus_encode(OpusEncoder *st, const opus_int16 *pcm, int frame_size, unsigned char *data,
+                       opus_int32 max_data_bytes);
+/* replaces the FIXED_POINT opus_encode_float (src/opus_encoder.c:1968-2005; NativeOpus.cs:114,189) */
+opus_int32 opus_encode_float(OpusEncoder *st, const float *pcm, int frame_size, unsigned char *data,
+                             opus_int32 max_data_bytes);
+/* replaces opus_encoder_ctl (src/opus_encoder.c:2031-2489; NativeOpus.cs:129-132,204-207) */
+int opus_encoder_ctl(OpusEncoder *st, int request, ...);
+/* replaces opus_encoder_destroy (src/opus_encoder.c:2491-2494; NativeOpus.cs:150,225) */
+void opus_encoder_destroy(OpusEncoder *st);
+
+/* Batch entry points (new).  n independent streams, one frame each per call; semantics are those
+ * of n opus_encode() calls.  out_len[i] is stream i's packet length or negative error code. */
+int opus_encode_batch(OpusEncoder *const *st, int n, const opus_int16 *const *pcm, int frame_size,
+                      unsigned char *const *data, opus_int32 max_data_bytes, opus_int32 *out_len);
+/* A fixed set of encoders (same device; same channel count for the flat/device calls). */
+OpusEncoderGroup *opus_encoder_group_create(OpusEncoder *const *st, int n, int *error);
+void opus_encoder_group_destroy(OpusEncoderGroup *grp);
+/* Host buffers: pcm = n rows of frame_size*channels samples, data = n rows of max_data_bytes. */
+int opus_encode_group_flat(OpusEncoderGroup *grp, const opus_int16 *pcm, int frame_size, unsigned char *data,
+                           opus_int32 max_data_bytes, opus_int32 *out_len);
+/* Device buffers, same layout; asynchronous on the library stream (opus_b200_synchronize waits). */
+int opus_encode_group_device(OpusEncoderGroup *grp, const opus_int16 *d_pcm, int frame_size,
+                             unsigned char *d_data, opus_int32 max_data_bytes, opus_int32 *d_len);
+/* Batched OPUS_GET_FINAL_RANGE for encoders. */
+int opus_encoder_get_final_range_batch(OpusEncoder *const *st, int n, opus_uint32 *out);
+/* Device timing of the encode kernel with CUDA events on the launching stream (bench.py). */
+int opus_b200_encode_profile_begin(void);
+int opus_b200_encode_profile_end(double *ms, long long *count);
+
 /* Blocks until all work queued by this library on the current device has finished. */
 int opus_b200_synchronize(void);
 /* Number of kernel launches issued by this library so far (process-wide counter). */

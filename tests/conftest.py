@@ -114,6 +114,98 @@ def emu_lib():
     return lib
 
 
+class RefEncoder(object):
+    """The UNMODIFIED reference encoder (oracle/_ref/libopus_ref.so)."""
+
+    _lib = None
+
+    @classmethod
+    def lib(cls):
+        if cls._lib is None:
+            lib = ctypes.CDLL(REF_SO)
+            lib.opus_encoder_create.restype = ctypes.c_void_p
+            lib.opus_encoder_create.argtypes = [ctypes.c_int32, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_int)]
+            lib.opus_encode.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int32]
+            lib.opus_encoder_destroy.argtypes = [ctypes.c_void_p]
+            lib.opus_encoder_destroy.restype = None
+            cls._lib = lib
+        return cls._lib
+
+    def __init__(self, fs, ch, app):
+        err = ctypes.c_int(0)
+        self.h = self.lib().opus_encoder_create(fs, ch, app, ctypes.byref(err))
+        assert self.h and err.value == 0
+
+    def ctl(self, req, val):
+        return self.lib().opus_encoder_ctl(ctypes.c_void_p(self.h), ctypes.c_int(req), ctypes.c_int(val))
+
+    def encode(self, pcm, frame_size, max_bytes):
+        """Returns (return code, packet bytes, final range)."""
+        pcm = np.ascontiguousarray(pcm, dtype=np.int16)
+        buf = (ctypes.c_ubyte * max(max_bytes, 1))()
+        n = self.lib().opus_encode(self.h, pcm.ctypes.data, frame_size, buf, max_bytes)
+        v = ctypes.c_uint32(0)
+        self.lib().opus_encoder_ctl(ctypes.c_void_p(self.h), 4031, ctypes.byref(v))
+        return n, bytes(buf[:max(n, 0)]), v.value
+
+    def close(self):
+        if self.h:
+            self.lib().opus_encoder_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+
+class EmuEncoder(object):
+    """Host-emulation build of the encoder kernel source (tests/emu/emu_enc.cpp)."""
+
+    def __init__(self, lib, fs, ch, app):
+        self.lib = lib
+        self.h = lib.emu_enc_create(fs, ch, app)
+        assert self.h
+
+    def ctl(self, req, val):
+        return self.lib.emu_enc_ctl(self.h, req, val, None)
+
+    def encode(self, pcm, frame_size, max_bytes):
+        pcm = np.ascontiguousarray(pcm, dtype=np.int16)
+        buf = (ctypes.c_ubyte * max(max_bytes, 1))()
+        n = self.lib.emu_enc_encode(self.h, pcm.ctypes.data, frame_size, buf, max_bytes)
+        return n, bytes(buf[:max(n, 0)]), self.lib.emu_enc_final_range(self.h)
+
+    def close(self):
+        if self.h:
+            self.lib.emu_enc_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+
+@pytest.fixture(scope="session")
+def emu_enc_lib():
+    """Host build of the encoder headers (tests/emu/emu_enc.cpp), compiled with g++ on demand."""
+    src = os.path.join(ROOT, "tests", "emu", "emu_enc.cpp")
+    so = os.path.join(ROOT, "tests", "emu", "libemu_enc.so")
+    csrc = os.path.join(ROOT, "concentus_b200", "csrc")
+    newest = max([os.path.getmtime(src)] + [os.path.getmtime(os.path.join(csrc, f)) for f in os.listdir(csrc)])
+    if not os.path.exists(so) or os.path.getmtime(so) < newest:
+        subprocess.run(["g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-Wall", "-Wno-unused-function", "-o", so, src],
+                       check=True)
+    lib = ctypes.CDLL(so)
+    lib.emu_enc_create.restype = ctypes.c_void_p
+    lib.emu_enc_create.argtypes = [ctypes.c_int] * 3
+    lib.emu_enc_destroy.argtypes = [ctypes.c_void_p]
+    lib.emu_enc_encode.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int]
+    lib.emu_enc_ctl.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+    lib.emu_enc_final_range.argtypes = [ctypes.c_void_p]
+    lib.emu_enc_final_range.restype = ctypes.c_uint
+    return lib
+
+
+def enc_golden_index():
+    return json.load(open(os.path.join(GOLDEN, "enc_index.json")))
+
+
 def cuda_available():
     try:
         import torch

@@ -1,0 +1,155 @@
+"""Encoder parity on the GPU: the CUDA library, called through its C ABI, against the committed golden
+packets (made by the reference encoder) and against the compiled reference itself (oracle/_ref) on the
+same seeded PCM.  Bar: identical packet bytes and OPUS_GET_FINAL_RANGE for every frame."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+
+import concentus_b200 as cb
+import enc_cases
+from conftest import GOLDEN, RefEncoder, have_ref, needs_ref, read_bit
+
+pytestmark = pytest.mark.gpu
+
+CASES = {c.name: c for c in enc_cases.golden_cases()}
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_single_stream_matches_golden(name):
+    """opus_encoder_create / opus_encoder_ctl / opus_encode / OPUS_GET_FINAL_RANGE, frame by frame."""
+    c = CASES[name]
+    gold = read_bit(os.path.join(GOLDEN, "enc_%s.bit" % name))
+    enc = cb.OpusEncoder(c.fs, c.ch, c.app)
+    try:
+        for req, val in c.ctls:
+            enc.ctl(req, val)
+        for i, frame in enumerate(c.frames()):
+            pkt = enc.encode(frame, c.frame, c.max_bytes)
+            assert pkt == gold[i][0], (name, i, len(pkt), len(gold[i][0]))
+            assert enc.final_range == gold[i][1], (name, i)
+    finally:
+        enc.close()
+
+
+@needs_ref
+def test_batch_of_different_streams_matches_reference():
+    """One launch per frame carries 96 streams with their own signal, bit rate, VBR mode and complexity."""
+    n, frame, ch, nframes = 96, 960, 2, 10
+    rng = np.random.default_rng(9)
+    be = cb.OpusBatchEncoder(n, 48000, ch, enc_cases.LOWDELAY)
+    refs = []
+    pcms = []
+    try:
+        for s in range(n):
+            r = RefEncoder(48000, ch, enc_cases.LOWDELAY)
+            ctls = [(enc_cases.SET_BITRATE, int(rng.choice([24000, 48000, 64000, 96000, 160000, 320000])))]
+            if s % 3 == 1:
+                ctls.append((enc_cases.SET_VBR, 0))
+            if s % 3 == 2:
+                ctls.append((enc_cases.SET_VBR_CONSTRAINT, 0))
+            if s % 4 == 0:
+                ctls.append((enc_cases.SET_COMPLEXITY, int(rng.integers(0, 11))))
+            for req, val in ctls:
+                assert r.ctl(req, val) == 0
+                be.encoders[s].ctl(req, val)
+            refs.append(r)
+            pcms.append(enc_cases.signal(enc_cases.KINDS[s % len(enc_cases.KINDS)], frame * nframes, ch, 1000 + s))
+        for t in range(nframes):
+            rows = np.stack([p[t * frame * ch:(t + 1) * frame * ch] for p in pcms])
+            data, lens = be.encode(rows, frame, 1275)
+            fr = be.final_ranges()
+            for s in range(n):
+                rn, rpkt, rrng = refs[s].encode(rows[s], frame, 1275)
+                assert lens[s] == rn, (s, t, lens[s], rn)
+                assert data[s, :rn].tobytes() == rpkt, (s, t)
+                assert int(fr[s]) == rrng, (s, t)
+    finally:
+        be.close()
+
+
+@needs_ref
+def test_sweep_matches_reference():
+    """Randomized sweep over sample rates, frame sizes, rates, buffers and applications (single-stream API)."""
+    for c in enc_cases.sweep_cases(count=40):
+        r = RefEncoder(c.fs, c.ch, c.app)
+        e = cb.OpusEncoder(c.fs, c.ch, c.app)
+        try:
+            for req, val in c.ctls:
+                assert r.ctl(req, val) == 0
+                e.ctl(req, val)
+            for i, frame in enumerate(c.frames()):
+                rn, rpkt, rrng = r.encode(frame, c.frame, c.max_bytes)
+                pkt = e.encode(frame, c.frame, c.max_bytes)
+                assert pkt == rpkt, (c.name, c.fs, c.ch, c.frame, c.kind, c.ctls, c.max_bytes, i)
+                assert e.final_range == rrng, (c.name, i)
+        finally:
+            e.close()
+
+
+def test_full_size_batch_properties():
+    """Config-3 size (4096 stereo streams, 20 ms): size-independent properties.  Streams are 64 distinct
+    signals repeated 64 times: copies must produce identical packets; the first 64 must equal the
+    golden-checked single-stream path; every packet must decode (own decoder) to the right length."""
+    import torch
+    n, frame, ch, nframes, distinct = 4096, 960, 2, 4, 64
+    be = cb.OpusBatchEncoder(n, 48000, ch, enc_cases.LOWDELAY)
+    singles = [cb.OpusEncoder(48000, ch, enc_cases.LOWDELAY) for _ in range(4)]
+    try:
+        be.ctl(enc_cases.SET_BITRATE, 96000)
+        for e in singles:
+            e.ctl(enc_cases.SET_BITRATE, 96000)
+        base = np.stack([enc_cases.signal(enc_cases.KINDS[s % len(enc_cases.KINDS)], frame * nframes, ch, 50 + s)
+                         for s in range(distinct)])
+        d_pcm = torch.empty((n, frame * ch), dtype=torch.int16, device="cuda")
+        d_data = torch.zeros((n, 1275), dtype=torch.uint8, device="cuda")
+        d_len = torch.zeros(n, dtype=torch.int32, device="cuda")
+        dec = cb.OpusDecoder(48000, ch)
+        for t in range(nframes):
+            rows = base[:, t * frame * ch:(t + 1) * frame * ch]
+            d_pcm.copy_(torch.from_numpy(np.tile(rows, (n // distinct, 1))))
+            torch.cuda.synchronize()
+            be.encode_device(d_pcm.data_ptr(), frame, d_data.data_ptr(), 1275, d_len.data_ptr())
+            cb.load().opus_b200_synchronize()
+            lens = d_len.cpu().numpy()
+            data = d_data.cpu().numpy()
+            assert (lens > 2).all() and (lens <= 1275).all()
+            for s in range(distinct):
+                same = data[s::distinct]
+                assert (lens[s::distinct] == lens[s]).all()
+                assert (same[:, :lens[s]] == same[0, :lens[s]]).all(), (t, s)
+            for k, e in enumerate(singles):
+                assert e.encode(rows[k], frame, 1275) == data[k, :lens[k]].tobytes(), (t, k)
+            ret, _ = dec.decode_raw(data[0, :lens[0]].tobytes(), frame)
+            assert ret == frame
+    finally:
+        be.close()
+        for e in singles:
+            e.close()
+
+
+def test_float_entry_point_and_errors():
+    lib = cb.load()
+    enc = cb.OpusEncoder(48000, 1, enc_cases.LOWDELAY)
+    enc2 = cb.OpusEncoder(48000, 1, enc_cases.LOWDELAY)
+    try:
+        x = enc_cases.signal("mix", 960, 1, 4)
+        xf = (x.astype(np.float32) / 32768.0)
+        buf = np.zeros(1275, dtype=np.uint8)
+        n = lib.opus_encode_float(enc._h, xf.ctypes.data, 960, buf.ctypes.data, 1275)
+        assert n > 0 and buf[:n].tobytes() == enc2.encode(x, 960, 1275)
+        assert lib.opus_encode(enc._h, x.ctypes.data, 1000, buf.ctypes.data, 1275) == -1     # bad frame size
+        assert lib.opus_encode(enc._h, x.ctypes.data, 960, buf.ctypes.data, 0) == -1
+        assert lib.opus_encoder_ctl(ctypes.c_void_p(enc._h), 4010, ctypes.c_int(11)) == -1
+        assert lib.opus_encoder_ctl(ctypes.c_void_p(enc._h), 4999, ctypes.c_int(0)) == -5
+        err = ctypes.c_int(0)
+        assert not lib.opus_encoder_create(44100, 1, 2049, ctypes.byref(err)) and err.value == -1
+        # frames the reference would code with SILK are refused, not mis-coded
+        voip = cb.OpusEncoder(16000, 1, enc_cases.AUDIO)
+        voip.ctl(enc_cases.SET_BITRATE, 12000)
+        assert lib.opus_encode(voip._h, x.ctypes.data, 320, buf.ctypes.data, 1275) == -5
+        voip.close()
+    finally:
+        enc.close()
+        enc2.close()
