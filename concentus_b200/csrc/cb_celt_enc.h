@@ -116,7 +116,8 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
   // ---- transient decision, MDCT, band energies ----
   int isTransient = 0, shortBlocks = 0, tf_chan = 0, transient_got_disabled = 0;
   if (s.complexity >= 1)
-    isTransient = enc_transient_analysis(sc.in[0], CB_MAXN + CB_OVERLAP, N + overlap, CC, &tf_estimate, &tf_chan, sc.ta_tmp);
+    isTransient = enc_transient_analysis(sc.in[0], CB_MAXN + CB_OVERLAP, N + overlap, CC, &tf_estimate, &tf_chan, sc.ta_tmp[0],
+                                         CB_MAXN + CB_OVERLAP);
   if (LM > 0 && re_tell(enc) + 3 <= total_bits) {
     if (isTransient) shortBlocks = M;
   } else {

@@ -77,6 +77,28 @@ struct CbBest { i32 num, den, id; };
 CB_FN CbBest cb_wbest(CbBest b) { return b; }
 #endif
 
+// Per-channel serial work: lane c runs channel c on the device; the host walks the channels.
+// cb_bcast(v, lane) hands a lane's result to the whole warp.
+#if CB_DEVICE_BUILD
+#define CB_CHANNEL_LANES(c, C) for (int c = CB_LANE(), once_ = 1; once_ && c < (C); once_ = 0)
+CB_FN i32 cb_bcast(i32 v, int lane) { return __shfl_sync(0xffffffffu, v, lane); }
+CB_FN u32 cb_wsumu(u32 v) { return __reduce_add_sync(0xffffffffu, v); }
+// exclusive prefix sum over lanes (lane 0 gets 0)
+CB_FN i32 cb_wscan_excl(i32 v) {
+  i32 x = v;
+  for (int o = 1; o < 32; o <<= 1) {
+    i32 t = __shfl_up_sync(0xffffffffu, x, o);
+    if (CB_LANE() >= o) x += t;
+  }
+  return x - v;
+}
+#else
+#define CB_CHANNEL_LANES(c, C) for (int c = 0; c < (C); c++)
+CB_FN i32 cb_bcast(i32 v, int) { return v; }
+CB_FN u32 cb_wsumu(u32 v) { return v; }
+CB_FN i32 cb_wscan_excl(i32) { return 0; }
+#endif
+
 // serial work of one stream: lane 0 on the device, the only "lane" on the host
 #if CB_DEVICE_BUILD
 #define CB_IF_LANE0 if (CB_LANE() == 0)

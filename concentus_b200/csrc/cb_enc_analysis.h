@@ -33,7 +33,7 @@ CB_FN void enc_preemphasis(const i16* pcm, i32* inp, int N, int CC, int upsample
 
 // comb_filter with separate input and output (celt.c:183-244): a pure FIR, every sample independent.
 // x may be indexed down to x[-T-2].
-CB_FN void enc_comb_fir(i32* y, const i32* x, int T0, int T1, int N, i32 g0, i32 g1, int tap0, int tap1,
+CB_FN_NOINLINE void enc_comb_fir(i32* y, const i32* x, int T0, int T1, int N, i32 g0, i32 g1, int tap0, int tap1,
                         int overlap) {
   CB_WSYNC();
   if (g0 == 0 && g1 == 0) {
@@ -97,7 +97,7 @@ CB_FN void enc_pitch_downsample(const i32* x0, const i32* x1, i16* x_lp, int len
 }
 
 // lane-parallel inner product of two int16 vectors
-CB_FN i32 enc_inner(const i16* a, const i16* b, int n) {
+CB_FN_NOINLINE i32 enc_inner(const i16* a, const i16* b, int n) {
   i32 s = 0;
   CB_LANE_LOOP(j, n) s = mac16_16(s, a[j], b[j]);
   return cb_wsum(s);
@@ -245,70 +245,73 @@ CB_FN int enc_run_prefilter(CeltEncScalars& s, CeltEncState* st, EncScratch& sc,
 }
 
 // transient_analysis (celt_encoder.c:227-376).  in: C channels of `len` samples, channel stride `cstride`.
-CB_UTABLE u8 ct_inv_table[128] = {
+CB_GTABLE u8 ct_inv_table[128] = {
     255, 255, 156, 110, 86, 70, 59, 51, 45, 40, 37, 33, 31, 28, 26, 25, 23, 22, 21, 20, 19, 18, 17, 16, 16, 15, 15, 14,
     13, 13, 12, 12, 12, 12, 11, 11, 11, 10, 10, 10, 9, 9, 9, 9, 9, 9, 8, 8, 8, 8, 8, 7, 7, 7, 7, 7, 7, 6, 6, 6, 6, 6, 6,
     6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 5, 5, 5, 5, 5, 5, 5, 5, 5, 5, 5, 5, 4, 4, 4, 4, 4, 4, 4, 4, 4, 4, 4, 4, 4, 4, 4, 4, 4,
     4, 4, 4, 4, 4, 4, 4, 4, 3, 3, 3, 3, 3, 3, 3, 3, 3, 3, 3, 3, 3, 3, 3, 3, 3, 2};
 
-CB_FN int enc_transient_analysis(const i32* in, int cstride, int len, int C, i32* tf_estimate, int* tf_chan,
-                                 i16* tmp) {
+CB_FN_NOINLINE int enc_transient_analysis(const i32* in, int cstride, int len, int C, i32* tf_estimate, int* tf_chan,
+                                          i16* tmp0, int tstride) {
   i32 mask_metric = 0;
   const int len2 = len / 2;
-  CB_NOUNROLL for (int c = 0; c < C; c++) {
+  CB_WSYNC();
+  CB_CHANNEL_LANES(c, C) {                                   // high-pass IIR: a serial recurrence per channel
     const i32* x_in = in + c * cstride;
-    CB_WSYNC();
-    CB_IF_LANE0 {                                            // high-pass IIR: serial recurrence
-      i32 mem0 = 0, mem1 = 0;
-      for (int i = 0; i < len; i++) {
-        i32 x = x_in[i] >> CB_SIG_SHIFT;
-        i32 y = add32(mem0, x);
-        mem0 = sub32(add32(mem1, y), shl32(x, 1));
-        mem1 = sub32(x, y >> 1);
-        tmp[i] = (i16)(y >> 2);
-      }
-      for (int i = 0; i < 12; i++) tmp[i] = 0;
+    i16* tmp = tmp0 + c * tstride;
+    i32 mem0 = 0, mem1 = 0;
+    CB_NOUNROLL for (int i = 0; i < len; i++) {
+      i32 x = x_in[i] >> CB_SIG_SHIFT;
+      i32 y = add32(mem0, x);
+      mem0 = sub32(add32(mem1, y), shl32(x, 1));
+      mem1 = sub32(x, y >> 1);
+      tmp[i] = (i16)(y >> 2);
     }
-    CB_WSYNC();
-    {
-      i32 mx = 0, mn = 0;
-      CB_LANE_LOOP(i, len) { i32 v = tmp[i]; mx = max32(mx, v); mn = min32(mn, v); }
-      i32 maxabs = max32(cb_wmax(mx), neg32(cb_wmin(mn)));
-      int shift = 14 - cb_ilog2(add32(1, maxabs));
-      if (shift != 0) {
-        CB_LANE_LOOP(i, len) tmp[i] = shl16(tmp[i], shift);
-      }
+    for (int i = 0; i < 12; i++) tmp[i] = 0;
+  }
+  CB_WSYNC();
+  CB_NOUNROLL for (int c = 0; c < C; c++) {                  // normalise to full range (lane-parallel)
+    i16* tmp = tmp0 + c * tstride;
+    i32 mx = 0, mn = 0;
+    CB_LANE_LOOP(i, len) { i32 v = tmp[i]; mx = max32(mx, v); mn = min32(mn, v); }
+    i32 maxabs = max32(cb_wmax(mx), neg32(cb_wmin(mn)));
+    int shift = 14 - cb_ilog2(add32(1, maxabs));
+    if (shift != 0) {
+      CB_LANE_LOOP(i, len) tmp[i] = shl16(tmp[i], shift);
     }
-    CB_WSYNC();
-    i32 mean = 0;
-    i32 maxE = 0;
-    CB_IF_LANE0 {                                            // forward / backward smoothing: serial
-      i32 mem0 = 0;
-      for (int i = 0; i < len2; i++) {
-        i16 x2 = (i16)pshr32(add32(mult16_16(tmp[2 * i], tmp[2 * i]), mult16_16(tmp[2 * i + 1], tmp[2 * i + 1])), 16);
-        mean = add32(mean, x2);
-        tmp[i] = (i16)add32(mem0, pshr32(sub32(x2, mem0), 4));
-        mem0 = tmp[i];
-      }
-      mem0 = 0;
-      for (int i = len2 - 1; i >= 0; i--) {
-        tmp[i] = (i16)add32(mem0, pshr32(sub32(tmp[i], mem0), 3));
-        mem0 = tmp[i];
-        maxE = max32(maxE, (i16)mem0);
-      }
+  }
+  CB_WSYNC();
+  i32 mean_c[2] = {0, 0}, maxE_c[2] = {0, 0};
+  CB_CHANNEL_LANES(c, C) {                                   // forward / backward smoothing: serial per channel
+    i16* tmp = tmp0 + c * tstride;
+    i32 mean = 0, maxE = 0, mem0 = 0;
+    CB_NOUNROLL for (int i = 0; i < len2; i++) {
+      i16 x2 = (i16)pshr32(add32(mult16_16(tmp[2 * i], tmp[2 * i]), mult16_16(tmp[2 * i + 1], tmp[2 * i + 1])), 16);
+      mean = add32(mean, x2);
+      tmp[i] = (i16)add32(mem0, pshr32(sub32(x2, mem0), 4));
+      mem0 = tmp[i];
     }
-#if CB_DEVICE_BUILD
-    mean = __shfl_sync(0xffffffffu, mean, 0);
-    maxE = __shfl_sync(0xffffffffu, maxE, 0);
-#endif
-    CB_WSYNC();
+    mem0 = 0;
+    CB_NOUNROLL for (int i = len2 - 1; i >= 0; i--) {
+      tmp[i] = (i16)add32(mem0, pshr32(sub32(tmp[i], mem0), 3));
+      mem0 = tmp[i];
+      maxE = max32(maxE, (i16)mem0);
+    }
+    mean_c[c] = mean;
+    maxE_c[c] = maxE;
+  }
+  CB_WSYNC();
+  CB_NOUNROLL for (int c = 0; c < C; c++) {
+    const i16* tmp = tmp0 + c * tstride;
+    i32 mean = cb_bcast(mean_c[c], c);
+    const i32 maxE = cb_bcast(maxE_c[c], c);
     mean = mult16_16(cb_sqrt(mean), cb_sqrt(mult16_16(maxE, len2 >> 1)));
     i32 norm = shl32(len2, 6 + 14) / add32(1, mean >> 1);
     i32 un = 0;
     CB_LANE_LOOP(q, (len2 - 5 - 12 + 3) / 4) {
       int i = 12 + 4 * q;
       int id = max32(0, min32(127, mult16_32_q15(add32(tmp[i], 1), norm)));
-      un += ct_inv_table[id];
+      un += cb_ldg(&ct_inv_table[id]);
     }
     i32 unmask = cb_wsum(un);
     unmask = 64 * unmask * 4 / (6 * (len2 - 17));
@@ -321,7 +324,7 @@ CB_FN int enc_transient_analysis(const i32* in, int cstride, int len, int C, i32
 }
 
 // patch_transient_decision (celt_encoder.c:380-415)
-CB_FN int enc_patch_transient(const i16* newE, const i16* oldE, int start, int end, int C) {
+CB_FN_NOINLINE int enc_patch_transient(const i16* newE, const i16* oldE, int start, int end, int C) {
   i32 mean_diff = 0;
   i16 spread_old[26];
   if (C == 1) {

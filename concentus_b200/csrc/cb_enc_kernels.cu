@@ -13,7 +13,7 @@
 
 #define E_WARPS 4
 
-__global__ void __launch_bounds__(E_WARPS * 32)
+__global__ void __launch_bounds__(E_WARPS * 32, 7)
 opus_encode_kernel(OpusEncState* const* states, EncScratch* scratch, const i16* pcm, i32 pcm_stride, int frame_size,
                    u8* data, i32 data_stride, int max_data_bytes, i32* out_len, int n) {
   extern __shared__ __align__(16) unsigned char smem[];

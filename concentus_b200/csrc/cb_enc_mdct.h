@@ -8,7 +8,7 @@
 
 // B interleaved forward MDCTs of NB output bins each.  in: channel base (B*NB + overlap samples);
 // out[b + B*k]; f2: B*NB words of scratch.  sh = maxLM - LM (long) or maxLM (short blocks).
-CB_FN void enc_mdct_forward(const i32* in, i32* out, i32* f2, int B, int NB, int sh) {
+CB_FN_NOINLINE void enc_mdct_forward(const i32* in, i32* out, i32* f2, int B, int NB, int sh) {
   const int N2 = NB, N4 = NB >> 1;
   const int ov = CB_OVERLAP, q = (ov + 3) >> 2;
   const int trig_off = sh == 0 ? 0 : sh == 1 ? 960 : sh == 2 ? 1440 : 1680;
@@ -80,7 +80,7 @@ CB_FN void enc_compute_mdcts(int shortBlocks, const i32* in0, const i32* in1, i3
 }
 
 // compute_band_energies (bands.c:94-144): one band at a time, samples across lanes.
-CB_FN void enc_band_energies(const i32* freq0, const i32* freq1, i32* bandE, int end, int C, int LM) {
+CB_FN_NOINLINE void enc_band_energies(const i32* freq0, const i32* freq1, i32* bandE, int end, int C, int LM) {
   CB_WSYNC();
   CB_NOUNROLL for (int c = 0; c < C; c++) {
     const i32* X = c ? freq1 : freq0;
@@ -126,7 +126,7 @@ CB_FN void enc_normalise_bands(const i32* freq0, const i32* freq1, i16* X, int N
 }
 
 // amp2Log2 (quant_bands.c:551-572)
-CB_FN void enc_amp2log2(int effEnd, int end, const i32* bandE, i16* bandLogE, int C) {
+CB_FN_NOINLINE void enc_amp2log2(int effEnd, int end, const i32* bandE, i16* bandLogE, int C) {
   CB_WSYNC();
   CB_LANE_LOOP(u, C * end) {
     const int c = u / end, i = u % end;

@@ -30,7 +30,7 @@ CB_FN i32 enc_atan2p(i32 y, i32 x) {
   return (i16)(25736 - ((i16)enc_atan01((i16)arg) >> 1));
 }
 // stereo_itheta (vq.c:375-412)
-CB_FN int enc_stereo_itheta(const i16* X, const i16* Y, int stereo, int N) {
+CB_FN_NOINLINE int enc_stereo_itheta(const i16* X, const i16* Y, int stereo, int N) {
   i32 em = 0, es = 0;
   CB_WSYNC();
   if (stereo) {
@@ -50,7 +50,7 @@ CB_FN int enc_stereo_itheta(const i16* X, const i16* Y, int stereo, int N) {
   return mult16_16_q15(20861, enc_atan2p(side, mid));          // QCONST16(0.63662f,15)
 }
 // intensity_stereo (bands.c:337-360)
-CB_FN void enc_intensity_stereo(i16* X, const i16* Y, const i32* bandE, int i, int N) {
+CB_FN_NOINLINE void enc_intensity_stereo(i16* X, const i16* Y, const i32* bandE, int i, int N) {
   const int shift = cb_zlog2(max32(bandE[i], bandE[i + CB_NBANDS])) - 13;
   const i32 left = (i16)vshr32(bandE[i], shift), right = (i16)vshr32(bandE[i + CB_NBANDS], shift);
   const i32 norm = (i16)(1 + cb_sqrt(add32(add32(1, mult16_16(left, left)), mult16_16(right, right))));
@@ -87,12 +87,39 @@ CB_FN void v_exp_rotation_enc(i16* X, int len, int stride, int K, int spread) {
   if (stride2) v_rot_pass(X, stride, len, stride2, s, (i16)(-c));
 }
 
-// icwrs (cwrs.c:440-456): index of a pulse vector; uniform walk from the last dimension.
+// icwrs (cwrs.c:440-456): index of a pulse vector.  The reference walks from the last dimension
+// with a running pulse count k; term j only needs the suffix count, so each lane takes a contiguous
+// run of dimensions, a warp scan supplies the counts to its right, and the terms add up mod 2^32.
+CB_FN u32 enc_pvq_u_g(int n, int k) {
+  const int lo = n < k ? n : k, hi = n < k ? k : n;
+  return cb_ldg(&ct_pvq_u_data_g[cb_ldg(&ct_pvq_u_row_g[lo]) + hi]);
+}
 CB_FN u32 enc_icwrs(int n, const i16* y) {
+#if CB_DEVICE_BUILD
+  const int per = (n + 31) >> 5;
+  const int lane = CB_LANE();
+  const int j0 = lane * per, j1 = cb_imin(n, j0 + per);
+  i32 mine = 0;
+  for (int j = j0; j < j1; j++) { const int v = y[j]; mine += v < 0 ? -v : v; }
+  const i32 total = cb_wsum(mine);
+  int k = total - cb_wscan_excl(mine) - mine;         // pulses strictly to the right of this lane's run
+  u32 acc = 0;
+  for (int j = j1 - 1; j >= j0; j--) {
+    const int v = y[j];
+    if (j == n - 1) {
+      acc += v < 0;
+    } else {
+      acc += enc_pvq_u_g(n - j, k);
+      if (v < 0) acc += enc_pvq_u_g(n - j, k + (v < 0 ? -v : v) + 1);
+    }
+    k += v < 0 ? -v : v;
+  }
+  return cb_wsumu(acc);
+#else
   int j = n - 1;
   u32 i = y[j] < 0;
   int k = y[j] < 0 ? -y[j] : y[j];
-  CB_NOUNROLL do {
+  do {
     j--;
     i += pvq_u(n - j, k);
     const int v = y[j];
@@ -100,11 +127,12 @@ CB_FN u32 enc_icwrs(int n, const i16* y) {
     if (v < 0) i += pvq_u(n - j, k + 1);
   } while (j > 0);
   return i;
+#endif
 }
 
 // alg_quant (vq.c:161-327): greedy pulse search.  Each lane owns the positions j = lane (mod 32);
 // one warp arg-max per pulse.  y/iy/signx live in the EncWork vectors.
-CB_FN void enc_alg_quant(EncWork& w, RangeEnc& enc, i16* X, int N, int K, int spread, int B) {
+CB_FN_NOINLINE void enc_alg_quant(EncWork& w, RangeEnc& enc, i16* X, int N, int K, int spread, int B) {
   i16* y = w.vtmp;
   i16* iy = w.iy;
   i16* signx = w.signx;

@@ -147,7 +147,7 @@ struct alignas(16) EncScratch {
   i16 xx[(CB_COMBFILTER_MAXPERIOD + CB_MAXN) >> 1];
   i16 x4[CB_MAXN >> 2];
   i16 y4[((CB_MAXN + CB_COMBFILTER_MAXPERIOD) >> 2) + 8];
-  i16 ta_tmp[CB_MAXN + CB_OVERLAP];                      // transient analysis
+  i16 ta_tmp[2][CB_MAXN + CB_OVERLAP];                   // transient analysis, per channel
   i16 pcm_buf[(CB_MAX_ENCODER_BUFFER + CB_MAXN) * 2];    // delay-compensated, dc-rejected input
   u8 intra_bits[256];                                    // coarse-energy two-pass byte save
 };

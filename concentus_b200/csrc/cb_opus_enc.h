@@ -57,7 +57,7 @@ CB_HD u8 enc_gen_toc(int mode, int framerate, int bandwidth, int channels) {
 
 // opus_packet_pad (repacketizer.c:102-258) for the single-frame packets this encoder produces:
 // code 0 -> code 3 with padding.  Returns 0 or a negative code.
-CB_FN int enc_packet_pad(u8* data, int len, int new_len) {
+CB_FN_NOINLINE int enc_packet_pad(u8* data, int len, int new_len) {
   if (len < 1) return CB_BAD_ARG;
   if (len == new_len) return CB_OK;
   if (len > new_len) return CB_BAD_ARG;

@@ -4,24 +4,40 @@ of the same .so, and aggregate by source function.
 usage: ncu_by_function.py <source.csv> <lib.so> <kernel-substring>"""
 import collections, csv, os, re, subprocess, sys, tempfile
 
-def sass_lines(lib, pat):
+HELPER_FILES = ("cb_common.h", "sm_30_intrinsics.hpp", "sm_32_intrinsics.hpp", "sm_80_rt.hpp", "device_functions.hpp")
+
+def sass_lines(lib, pat, outer=True):
+    """One (file, line) per SASS instruction of the sections matching pat.  With outer=True an
+    instruction inlined from a helper header (fixed-point primitives, shuffle intrinsics) is
+    attributed to the nearest enclosing frame that is not a helper."""
     with tempfile.TemporaryDirectory() as tmp:
         subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(lib)], cwd=tmp, check=True, stdout=subprocess.DEVNULL)
         text = ""
         for f in sorted(os.listdir(tmp)):
-            if f.endswith(".cubin"):
-                text += subprocess.run(["nvdisasm", "-g", "-c", os.path.join(tmp, f)], stdout=subprocess.PIPE, text=True).stdout
-    sec, cur, out = None, None, []
+            if f.endswith(".cubin") and "-" not in f:
+                text += subprocess.run(["nvdisasm", "-gi", "-c", os.path.join(tmp, f)], stdout=subprocess.PIPE, text=True).stdout
+    sec, chain, out = None, [], []
+    fresh = True
     for l in text.splitlines():
         m = re.match(r'\s*\.section\s+\.text\.(\S+),', l)
         if m:
             sec = m.group(1)
         m = re.search(r'//## File "([^"]+)", line (\d+)', l)
         if m:
-            cur = (m.group(1).split('/')[-1], int(m.group(2)))
+            if fresh:
+                chain = []
+                fresh = False
+            chain.append((m.group(1).split('/')[-1], int(m.group(2))))
             continue
         if sec and pat in sec and re.match(r'\s+/\*[0-9a-f]{4,}\*/', l):
+            cur = chain[0] if chain else None
+            if outer:
+                for fr in chain:
+                    if fr[0] not in HELPER_FILES:
+                        cur = fr
+                        break
             out.append(cur)
+            fresh = True
     return out
 
 def main():
