@@ -87,6 +87,7 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
   for (int c = 0; c < CC; c++)
     enc_preemphasis(pcm + c, sc.in[c] + overlap, N, CC, s.upsample, &s.preemph_memE[c]);
 
+  CB_ENC_PHASE(w);                                            // 2: pre-emphasis done
   // ---- pitch pre-filter ----
   int pitch_index = CB_COMBFILTER_MINPERIOD, pitch_change = 0, pf_on, prefilter_tapset;
   i32 gain1 = 0;
@@ -95,7 +96,7 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
     const int enabled = nbAvailableBytes > 12 * C && start == 0 && !silence && !s.disable_pf && s.complexity >= 5 &&
                         !(s.consec_transient && LM != 3 && s.variable_duration == 5010);
     prefilter_tapset = s.tapset_decision;
-    pf_on = enc_run_prefilter(s, st, sc, CC, N, prefilter_tapset, &pitch_index, &gain1, &qg, enabled, nbAvailableBytes);
+    pf_on = enc_run_prefilter(w, s, st, sc, CC, N, prefilter_tapset, &pitch_index, &gain1, &qg, enabled, nbAvailableBytes);
     if ((gain1 > 13107 || s.prefilter_gain > 13107) &&
         ((double)pitch_index > 1.26 * (double)s.prefilter_period || (double)pitch_index < .79 * (double)s.prefilter_period))
       pitch_change = 1;
@@ -113,10 +114,11 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
     }
   }
 
+  CB_ENC_PHASE(w);                                            // 3: pre-filter done
   // ---- transient decision, MDCT, band energies ----
   int isTransient = 0, shortBlocks = 0, tf_chan = 0, transient_got_disabled = 0;
   if (s.complexity >= 1)
-    isTransient = enc_transient_analysis(sc.in[0], CB_MAXN + CB_OVERLAP, N + overlap, CC, &tf_estimate, &tf_chan, sc.ta_tmp[0],
+    isTransient = enc_transient_analysis(sc.in[0], CB_MAXN + CB_OVERLAP, N + overlap, CC, &tf_estimate, &tf_chan, w.ta_tmp[0],
                                          CB_MAXN + CB_OVERLAP);
   if (LM > 0 && re_tell(enc) + 3 <= total_bits) {
     if (isTransient) shortBlocks = M;
@@ -124,6 +126,7 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
     isTransient = 0;
     transient_got_disabled = 1;
   }
+  CB_ENC_PHASE(w);                                            // 4: transient analysis done
   const int secondMdct = shortBlocks && s.complexity >= 8;
   if (secondMdct) {
     enc_compute_mdcts(0, sc.in[0], sc.in[1], sc.freq[0], sc.freq[1], sc.f2, C, CC, LM, s.upsample);
@@ -137,6 +140,7 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
   enc_band_energies(sc.freq[0], sc.freq[1], w.bandE, effEnd, C, LM);
   enc_amp2log2(effEnd, end, w.bandE, w.bandLogE, C);
 
+  CB_ENC_PHASE(w);                                            // 5: MDCT + band energies done
   // temporal VBR (celt_encoder.c:1795-1812)
   i32 temporal_vbr;
   {
@@ -174,6 +178,7 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
   if (LM > 0 && re_tell(enc) + 3 <= total_bits) re_bit_logp(enc, isTransient, 3);
   enc_normalise_bands(sc.freq[0], sc.freq[1], w.X, N, w.bandE, effEnd, C, M);
 
+  CB_ENC_PHASE(w);                                            // 6: normalised spectrum ready
   // ---- time/frequency resolution, coarse energy, spreading ----
   int tf_select, tf_sum;
   if (effectiveBytes >= 15 * C && start == 0 && s.complexity >= 2) {
@@ -206,6 +211,7 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
     re_icdf(enc, s.spread_decision, ct_spread_icdf, 5);
   }
 
+  CB_ENC_PHASE(w);                                            // 7: tf + coarse energy coded
   // ---- dynamic allocation boosts ----
   i32 tot_boost;
   const i32 maxDepth = enc_dynalloc_analysis(w, start, end, C, s.lsb_depth, isTransient, s.vbr, s.constrained_vbr, LM,
@@ -295,6 +301,7 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
     re_shrink(enc, (u32)nbCompressedBytes);
   }
 
+  CB_ENC_PHASE(w);                                            // 8: side decisions coded
   // ---- bit allocation, fine energy, residual ----
   i32 bits = (((i32)nbCompressedBytes * 8) << CB_BITRES) - (i32)re_tell_frac(enc) - 1;
   const int anti_collapse_rsv = isTransient && LM >= 2 && bits >= ((LM + 2) << CB_BITRES) ? (1 << CB_BITRES) : 0;
@@ -316,6 +323,7 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
   }
   enc_energy_finalise(w, enc, start, end, w.oldE, nbCompressedBytes * 8 - re_tell(enc), C);
 
+  CB_ENC_PHASE(w);                                            // 9: residual coded
   // ---- state update (celt_encoder.c:2156-2241) ----
   CB_WSYNC();
   CB_LANE_LOOP(i, 2 * CB_NBANDS) {

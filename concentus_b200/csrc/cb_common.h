@@ -41,9 +41,15 @@ CB_FN i32 cb_wmax(i32 v) { return __reduce_max_sync(0xffffffffu, v); }
 CB_FN i32 cb_wmin(i32 v) { return __reduce_min_sync(0xffffffffu, v); }
 CB_FN int cb_clz(u32 v) { return __clz((int)v); }
 template <typename T> CB_FN T cb_ldg(const T* p) { return __ldg(p); }
-// arg-max of a ratio num/den (den > 0) over the warp, ties to the lowest id (PVQ greedy search)
+// arg-max of a ratio num/den (num >= 0, den > 0; an empty lane carries num < 0) over the warp, ties
+// to the lowest id (PVQ greedy search).  cb_wbest_exact is the plain butterfly on the exact
+// cross-multiplied comparison.  cb_wbest first ranks lanes by a float quotient, which is only used
+// to discard lanes that cannot win: fast division is good to 2 ulp, so every lane whose true ratio
+// equals the maximum lies within 2^-19 of the largest quotient.  One survivor wins outright;
+// survivors with identical (num, den) are resolved by the smallest id; anything else goes through
+// the exact butterfly.
 struct CbBest { i32 num, den, id; };
-CB_FN CbBest cb_wbest(CbBest b) {
+CB_FN CbBest cb_wbest_exact(CbBest b) {
   for (int o = 16; o > 0; o >>= 1) {
     CbBest t;
     t.num = __shfl_xor_sync(0xffffffffu, b.num, o);
@@ -53,6 +59,27 @@ CB_FN CbBest cb_wbest(CbBest b) {
     if (l > r || (l == r && t.id < b.id)) b = t;
   }
   return b;
+}
+CB_FN CbBest cb_wbest(CbBest b) {
+  const bool have = b.num >= 0 && b.den > 0;
+  const float key = have ? __fdividef((float)b.num, (float)b.den) : -1.0f;
+  const int ikey = have ? __float_as_int(key) : -1;
+  const int mx = __reduce_max_sync(0xffffffffu, ikey);
+  if (mx > 0) {
+    const float thr = __int_as_float(mx) * (1.0f - 1.9073486e-6f);
+    const unsigned cand = __ballot_sync(0xffffffffu, have && key >= thr);
+    const int first = __ffs((int)cand) - 1;
+    const i32 n0 = __shfl_sync(0xffffffffu, b.num, first), d0 = __shfl_sync(0xffffffffu, b.den, first);
+    const unsigned same = __ballot_sync(0xffffffffu, b.num == n0 && b.den == d0);
+    if ((cand & ~same) == 0) {                     // all survivors are the same fraction
+      CbBest r;
+      r.num = n0; r.den = d0;
+      r.id = __reduce_min_sync(0xffffffffu, ((cand >> CB_LANE()) & 1u) ? b.id : 0x7fffffff);
+      return r;
+    }
+    if (!((cand >> CB_LANE()) & 1u)) { b.num = -32767; b.den = 0; b.id = 0x7fffffff; }
+  }
+  return cb_wbest_exact(b);
 }
 #else
 #define CB_DEVICE_BUILD 0

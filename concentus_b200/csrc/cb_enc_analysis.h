@@ -68,7 +68,7 @@ CB_FN_NOINLINE void enc_comb_fir(i32* y, const i32* x, int T0, int T1, int N, i3
 }
 
 // pitch_downsample head (pitch.c:147-182) for linear buffers x0/x1 of `len` samples.
-CB_FN void enc_pitch_downsample(const i32* x0, const i32* x1, i16* x_lp, int len, int C, EncScratch& sc) {
+CB_FN void enc_pitch_downsample(const i32* x0, const i32* x1, i16* x_lp, int len, int C, EncScratch& sc, i16* xx) {
   i32 mx = 0, mn = 0;
   CB_WSYNC();
   CB_LANE_LOOP(i, len) {
@@ -93,7 +93,7 @@ CB_FN void enc_pitch_downsample(const i32* x0, const i32* x1, i16* x_lp, int len
     x_lp[i] = (i16)acc;
   }
   CB_WSYNC();
-  pitch_whiten(x_lp, len >> 1, sc.ac, sc.lpc32, sc.xx);
+  pitch_whiten(x_lp, len >> 1, sc.ac, sc.lpc32, xx);
 }
 
 // lane-parallel inner product of two int16 vectors
@@ -177,7 +177,7 @@ CB_FN i32 enc_remove_doubling(const i16* xbuf, int maxperiod, int minperiod, int
 }
 
 // run_prefilter (celt_encoder.c:1067-1192).  Returns pf_on; *pitch, *gain, *qgain as in the reference.
-CB_FN int enc_run_prefilter(CeltEncScalars& s, CeltEncState* st, EncScratch& sc, int CC, int N, int prefilter_tapset, int* pitch,
+CB_FN int enc_run_prefilter(EncWork& w, CeltEncScalars& s, CeltEncState* st, EncScratch& sc, int CC, int N, int prefilter_tapset, int* pitch,
                             i32* gain, int* qgain, int enabled, int nbAvailableBytes) {
   const int overlap = CB_OVERLAP;
   CB_WSYNC();
@@ -189,11 +189,11 @@ CB_FN int enc_run_prefilter(CeltEncScalars& s, CeltEncState* st, EncScratch& sc,
   int pitch_index;
   i32 gain1;
   if (enabled) {
-    enc_pitch_downsample(sc.pre[0], sc.pre[1], sc.pitch_buf, CB_COMBFILTER_MAXPERIOD + N, CC, sc);
-    pitch_index = pitch_search(sc.pitch_buf + (CB_COMBFILTER_MAXPERIOD >> 1), sc.pitch_buf, N,
-                               CB_COMBFILTER_MAXPERIOD - 3 * CB_COMBFILTER_MINPERIOD, sc.x4, sc.y4, sc.xcorr);
+    enc_pitch_downsample(sc.pre[0], sc.pre[1], w.pitch_buf, CB_COMBFILTER_MAXPERIOD + N, CC, sc, w.pitch_xx);
+    pitch_index = pitch_search(w.pitch_buf + (CB_COMBFILTER_MAXPERIOD >> 1), w.pitch_buf, N,
+                               CB_COMBFILTER_MAXPERIOD - 3 * CB_COMBFILTER_MINPERIOD, w.pitch_x4, w.pitch_y4, sc.xcorr);
     pitch_index = CB_COMBFILTER_MAXPERIOD - pitch_index;
-    gain1 = enc_remove_doubling(sc.pitch_buf, CB_COMBFILTER_MAXPERIOD, CB_COMBFILTER_MINPERIOD, N, &pitch_index,
+    gain1 = enc_remove_doubling(w.pitch_buf, CB_COMBFILTER_MAXPERIOD, CB_COMBFILTER_MINPERIOD, N, &pitch_index,
                                 s.prefilter_period, s.prefilter_gain, sc.yy_lookup);
     if (pitch_index > CB_COMBFILTER_MAXPERIOD - 2) pitch_index = CB_COMBFILTER_MAXPERIOD - 2;
     gain1 = (i16)mult16_16_q15(22938, gain1);
@@ -260,12 +260,16 @@ CB_FN_NOINLINE int enc_transient_analysis(const i32* in, int cstride, int len, i
     const i32* x_in = in + c * cstride;
     i16* tmp = tmp0 + c * tstride;
     i32 mem0 = 0, mem1 = 0;
-    CB_NOUNROLL for (int i = 0; i < len; i++) {
-      i32 x = x_in[i] >> CB_SIG_SHIFT;
-      i32 y = add32(mem0, x);
-      mem0 = sub32(add32(mem1, y), shl32(x, 1));
-      mem1 = sub32(x, y >> 1);
-      tmp[i] = (i16)(y >> 2);
+    CB_NOUNROLL for (int i = 0; i < len; i += 4) {         // len is a multiple of 4 (N + overlap)
+      i32 xs[4];
+      for (int k = 0; k < 4; k++) xs[k] = x_in[i + k];
+      for (int k = 0; k < 4; k++) {
+        i32 x = xs[k] >> CB_SIG_SHIFT;
+        i32 y = add32(mem0, x);
+        mem0 = sub32(add32(mem1, y), shl32(x, 1));
+        mem1 = sub32(x, y >> 1);
+        tmp[i + k] = (i16)(y >> 2);
+      }
     }
     for (int i = 0; i < 12; i++) tmp[i] = 0;
   }

@@ -11,19 +11,25 @@
 #include "cb_opus_enc.h"
 #include "cb_enc_kernels.h"
 
-#define E_WARPS 4
+#define E_WARPS 28
 
-__global__ void __launch_bounds__(E_WARPS * 32, 7)
+__global__ void __launch_bounds__(E_WARPS * 32, 1)
 opus_encode_kernel(OpusEncState* const* states, EncScratch* scratch, const i16* pcm, i32 pcm_stride, int frame_size,
                    u8* data, i32 data_stride, int max_data_bytes, i32* out_len, int n) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int warp = threadIdx.x >> 5;
   const int s = blockIdx.x * E_WARPS + warp;
-  if (s >= n) return;
   EncWork& w = *reinterpret_cast<EncWork*>(smem + (size_t)warp * sizeof(EncWork));
-  const int ret = opus_encode_stream(w, scratch[s], states[s], pcm + (size_t)s * pcm_stride, frame_size,
-                                     data + (size_t)s * data_stride, max_data_bytes);
-  if ((threadIdx.x & 31) == 0) out_len[s] = ret;
+  if ((threadIdx.x & 31) == 0) w.nsync = 0;
+  __syncwarp();
+  if (s < n) {
+    const int ret = opus_encode_stream(w, scratch[s], states[s], pcm + (size_t)s * pcm_stride, frame_size,
+                                       data + (size_t)s * data_stride, max_data_bytes);
+    if ((threadIdx.x & 31) == 0) out_len[s] = ret;
+  }
+  __syncwarp();
+  // warps that left early (or have no stream) still owe the CTA their remaining rendezvous
+  for (int k = w.nsync; k < CB_ENC_PHASES; k++) __syncthreads();
 }
 
 extern "C" {

@@ -183,16 +183,25 @@ CB_FN_NOINLINE void enc_alg_quant(EncWork& w, RangeEnc& enc, i16* X, int N, int 
     CB_IF_LANE0 iy[0] = (i16)(iy[0] + pulsesLeft);
     pulsesLeft = 0;
   }
+  const int T = (N + 31) >> 5;                                 // positions per lane
   CB_NOUNROLL for (int i = 0; i < pulsesLeft; i++) {
     const int rshift = 1 + cb_ilog2(K - pulsesLeft + i + 1);
     yy = (i16)(yy + 1);
     CbBest best;
     best.num = -32767; best.den = 0; best.id = 0x7fffffff;
-    CB_LANE_LOOP(j, N) {
-      i32 Rxy = (i16)(add32(xy, X[j]) >> rshift);
-      const i32 Ryy = (i16)(yy + y[j]);
-      Rxy = (i16)mult16_16_q15(Rxy, Rxy);
-      if (mult16_16(best.den, Rxy) > mult16_16(Ryy, best.num)) { best.den = Ryy; best.num = Rxy; best.id = j; }
+#if CB_DEVICE_BUILD
+    CB_NOUNROLL for (int t = 0, j = CB_LANE(); t < T; t++, j += 32) {
+      if (j < N) {
+#else
+    (void)T;
+    for (int j = 0; j < N; j++) {
+      {
+#endif
+        i32 Rxy = (i16)(add32(xy, X[j]) >> rshift);
+        const i32 Ryy = (i16)(yy + y[j]);
+        Rxy = (i16)mult16_16_q15(Rxy, Rxy);
+        if (mult16_16(best.den, Rxy) > mult16_16(Ryy, best.num)) { best.den = Ryy; best.num = Rxy; best.id = j; }
+      }
     }
     best = cb_wbest(best);
     xy = add32(xy, X[best.id]);

@@ -137,20 +137,26 @@ struct alignas(16) EncScratch {
   i32 in[2][CB_MAXN + CB_OVERLAP];                       // pre-emphasised (then pre-filtered) signal
   i32 pre[2][CB_MAXN + CB_COMBFILTER_MAXPERIOD];         // pre-filter input with history
   i32 freq[2][CB_MAXN];                                  // MDCT coefficients
-  i32 f[CB_MAXN];                                        // forward-MDCT fold buffer
   i32 f2[CB_MAXN];                                       // forward-MDCT FFT buffer
   i32 xcorr[(CB_COMBFILTER_MAXPERIOD >> 1) + 8];
   i32 yy_lookup[(CB_COMBFILTER_MAXPERIOD >> 1) + 8];
   i32 ac[CB_LPC_ORDER + 1];
   i32 lpc32[CB_LPC_ORDER];
-  i16 pitch_buf[(CB_COMBFILTER_MAXPERIOD + CB_MAXN) >> 1];
-  i16 xx[(CB_COMBFILTER_MAXPERIOD + CB_MAXN) >> 1];
-  i16 x4[CB_MAXN >> 2];
-  i16 y4[((CB_MAXN + CB_COMBFILTER_MAXPERIOD) >> 2) + 8];
-  i16 ta_tmp[2][CB_MAXN + CB_OVERLAP];                   // transient analysis, per channel
   i16 pcm_buf[(CB_MAX_ENCODER_BUFFER + CB_MAXN) * 2];    // delay-compensated, dc-rejected input
   u8 intra_bits[256];                                    // coarse-energy two-pass byte save
 };
+
+// Phase rendezvous.  All warps of a CTA run the same stage of the frame at the same time, so the
+// SM's instruction caches hold one stage's code instead of every stage's: the encoder is ~18k SASS
+// instructions and instruction-fetch stalls dominated when every warp sat in a different stage.
+// No data crosses warps; the barrier is only pacing.  Every warp must reach CB_ENC_PHASES barriers
+// per frame: a warp that leaves early (error, silence) makes up the remainder in the kernel wrapper.
+#define CB_ENC_PHASES 9
+#if CB_DEVICE_BUILD
+#define CB_ENC_PHASE(w) do { __syncthreads(); if (CB_LANE() == 0) (w).nsync++; __syncwarp(); } while (0)
+#else
+#define CB_ENC_PHASE(w) ((void)0)
+#endif
 
 // One level of the encoder's split recursion (quant_partition).
 struct EncPartFrame {
@@ -159,18 +165,36 @@ struct EncPartFrame {
 };
 struct EncSplit { int inv, delta, itheta, qalloc, b; };
 
-// Per-warp shared-memory workspace of the encode kernel.
+// Per-warp shared-memory workspace of the encode kernel.  The first block is a union over the
+// stages of a frame: the pitch analysis and the transient detector run before anything of the band
+// stage exists, and their vectors are re-read many times, so they borrow the band stage's room
+// instead of living in global memory.
 struct alignas(16) EncWork {
-  i16 X[2 * CB_MAXN];            // normalised spectrum
-  i32 bandE[2 * CB_NBANDS];
-  i32 tmp32[4 * CB_NBANDS + 4];  // allocation scratch
-  i32 pulses[CB_NBANDS];
-  i32 offsets[CB_NBANDS];
-  i32 cap[CB_NBANDS];
-  i32 fine_quant[CB_NBANDS];
-  i32 fine_prio[CB_NBANDS];
-  i32 tf_res[CB_NBANDS];
-  i32 metric[CB_NBANDS], path0[CB_NBANDS], path1[CB_NBANDS];
+  union {
+    struct {                       // MDCT onwards
+      i16 X[2 * CB_MAXN];          // normalised spectrum
+      i32 bandE[2 * CB_NBANDS];
+      i32 tmp32[4 * CB_NBANDS + 4];  // allocation scratch
+      i32 pulses[CB_NBANDS];
+      i32 offsets[CB_NBANDS];
+      i32 cap[CB_NBANDS];
+      i32 fine_quant[CB_NBANDS];
+      i32 fine_prio[CB_NBANDS];
+      i32 tf_res[CB_NBANDS];
+      i32 metric[CB_NBANDS], path0[CB_NBANDS], path1[CB_NBANDS];
+    };
+    struct {                       // pitch pre-filter analysis
+      i16 pitch_buf[(CB_COMBFILTER_MAXPERIOD + CB_MAXN) >> 1];
+      union {
+        i16 pitch_xx[(CB_COMBFILTER_MAXPERIOD + CB_MAXN) >> 1];   // whitening temp, dead before the search
+        struct {
+          i16 pitch_x4[CB_MAXN >> 2];
+          i16 pitch_y4[((CB_MAXN + CB_COMBFILTER_MAXPERIOD) >> 2) + 8];
+        };
+      };
+    };
+    i16 ta_tmp[2][CB_MAXN + CB_OVERLAP];   // transient detector, per channel
+  };
   i16 bandLogE[2 * CB_NBANDS], bandLogE2[2 * CB_NBANDS], error[2 * CB_NBANDS];
   i16 oldE[2 * CB_NBANDS];      // working copy of the state's oldBandE
   i16 oldE_intra[2 * CB_NBANDS], error_intra[2 * CB_NBANDS];
@@ -179,5 +203,6 @@ struct alignas(16) EncWork {
   i16 iy[176], signx[176];
   EncPartFrame stack[5];
   EncSplit sp_store;
+  i32 nsync;                     // phase rendezvous points passed so far (CB_ENC_PHASE)
   RangeEnc enc, enc_save0, enc_save1;
 };

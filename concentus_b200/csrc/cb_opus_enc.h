@@ -111,15 +111,32 @@ CB_FN void enc_dc_reject(const i16* in, int cutoff_Hz, i16* out, i32* hp_mem, in
   for (int c = 0; c < channels; c++) {
 #endif
     i32 m0 = hp_mem[2 * c], m1 = hp_mem[2 * c + 1];
-    CB_NOUNROLL for (int i = 0; i < len; i++) {
-      const i32 x = shl32(in[channels * i + c], 15);
+    const i16* ip = in + c;
+    i16* op = out + c;
+    int i = 0;
+    CB_NOUNROLL for (; i + 4 <= len; i += 4) {              // four samples per trip: loads first, then the chain
+      i32 xs[4];
+      for (int k = 0; k < 4; k++) xs[k] = ip[channels * (i + k)];
+      for (int k = 0; k < 4; k++) {
+        const i32 x = shl32(xs[k], 15);
+        const i32 tmp = sub32(x, m0);
+        m0 = add32(m0, pshr32(tmp, shift));
+        const i32 y = sub32(tmp, m1);
+        m1 = add32(m1, pshr32(y, shift));
+        i32 v = pshr32(y, 15);
+        v = v > 32767 ? 32767 : (v < -32767 ? -32767 : v);
+        op[channels * (i + k)] = (i16)v;
+      }
+    }
+    for (; i < len; i++) {
+      const i32 x = shl32(ip[channels * i], 15);
       const i32 tmp = sub32(x, m0);
-      m0 = add32(m0, pshr32(sub32(x, m0), shift));
+      m0 = add32(m0, pshr32(tmp, shift));
       const i32 y = sub32(tmp, m1);
-      m1 = add32(m1, pshr32(sub32(tmp, m1), shift));
+      m1 = add32(m1, pshr32(y, shift));
       i32 v = pshr32(y, 15);
       v = v > 32767 ? 32767 : (v < -32767 ? -32767 : v);
-      out[channels * i + c] = (i16)v;
+      op[channels * i] = (i16)v;
     }
     hp_mem[2 * c] = m0;
     hp_mem[2 * c + 1] = m1;
@@ -318,6 +335,7 @@ CB_FN int opus_encode_stream(EncWork& w, EncScratch& sc, OpusEncState* st, const
   for (int k = 0; k < 4; k++) o.hp_mem[k] = __shfl_sync(0xffffffffu, o.hp_mem[k], k >> 1);
 #endif
 
+  CB_ENC_PHASE(w);                                            // 1: input conditioned
   // CELT set-up (opus_encoder.c:1697-1761)
   {
     int endband = 21;

@@ -70,6 +70,20 @@ def main():
         a[1] += int(r[ix['Instructions Executed']] or 0)
         a[2] += int(r[ix['# Samples']] or 0)
         a[3] += int(r[ix['stall_no_inst']] or 0)
+    if len(sys.argv) > 4:                                  # per-line view of one function
+        want = sys.argv[4]
+        per = collections.defaultdict(lambda: [0, 0, 0])
+        for loc, r in zip(lines, data):
+            if loc and func_of(*loc) == want:
+                a = per[loc]
+                a[0] += 1
+                a[1] += int(r[ix['Instructions Executed']] or 0)
+                a[2] += int(r[ix['# Samples']] or 0)
+        for loc, v in sorted(per.items(), key=lambda kv: kv[0]):
+            src = srcs.get(loc[0], [])
+            text = src[loc[1] - 1].strip() if 0 < loc[1] <= len(src) else ''
+            print("%s:%-4d %5d %11d %7d  %s" % (loc[0][:16], loc[1], v[0], v[1], v[2], text[:90]))
+        return
     tot = [sum(v[k] for v in agg.values()) for k in range(4)]
     print("%-40s %7s %12s %6s %8s %6s %8s" % ("function", "static", "executed", "%exec", "samples", "%smp", "no_inst"))
     for k, v in sorted(agg.items(), key=lambda kv: -kv[1][2])[:40]:
