@@ -18,6 +18,10 @@ CB_FN void decode_entropy_pass(EntWork& w, u8* pkt, OpusDecState* st, StreamPlan
     side->kind = 3;
     return;
   }
+  if (silk_owns_frame(st, pl, pass)) {              // SILK frames are decoded by the SILK kernel
+    side->kind = 0;
+    return;
+  }
   const int len = pl->len[pass];
   const int nsamp = pl->nsamp[pass];
   if (kind == CB_PLAN_PLC || len <= 1) {
@@ -41,6 +45,13 @@ CB_FN void decode_entropy_pass(EntWork& w, u8* pkt, OpusDecState* st, StreamPlan
     }
     st->rangeFinal = 0;
     st->prev_redundancy = 0;
+    return;
+  }
+  if (st->prev_mode != 0 && st->prev_mode != CB_MODE_CELT_ONLY && !st->prev_redundancy) {
+    // SILK -> CELT mode transition (opus_decoder.c:330-345): needs the SILK concealment cross-fade, not built yet
+    side->kind = 0;
+    pl->ret = CB_UNIMPLEMENTED;
+    *ret_slot = CB_UNIMPLEMENTED;
     return;
   }
   const i32 off = pl->off[pass];

@@ -198,6 +198,7 @@ CB_HD void opus_plan_stream(OpusDecState* st, StreamPlan* pl, const u8* data, i3
   pl->kind = CB_PLAN_NONE;
   pl->nframes = 0;
   pl->total_samples = 0;
+  pl->fec_frame = -1;
   const int Fs = st->Fs;
   if (frame_size <= 0) { pl->ret = CB_BAD_ARG; return; }
   if (decode_fec < 0 || decode_fec > 1) { pl->ret = CB_BAD_ARG; return; }
@@ -226,11 +227,39 @@ CB_HD void opus_plan_stream(OpusDecState* st, StreamPlan* pl, const u8* data, i3
       if (pl->ret >= 0) st->last_packet_duration = pl->ret;
       return;
     }
-    pl->ret = CB_UNIMPLEMENTED;   // SILK in-band FEC: not built yet
+    // SILK in-band FEC (opus_decoder.c:649-672): conceal everything but the last packet_frame_size
+    // samples, then decode the first frame's LBRR data into those
+    const int duration_copy = st->last_packet_duration;
+    int nf = 0, plc_samples = frame_size - packet_frame_size;
+    if (plc_samples != 0) {
+      opus_plan_plc(st, pl, plc_samples);
+      if (pl->ret < 0) { st->last_packet_duration = duration_copy; return; }
+      if (pl->kind == CB_PLAN_ZERO) {           // nothing decoded yet: one all-zero frame
+        pl->off[0] = 0; pl->len[0] = 0; pl->nsamp[0] = (i16)plc_samples; pl->pcm_off[0] = 0;
+        nf = 1;
+      } else {
+        nf = pl->nframes;
+      }
+      if (nf >= CB_MAX_FRAMES) { pl->ret = CB_BAD_ARG; pl->kind = CB_PLAN_NONE; pl->nframes = 0; return; }
+    }
+    st->mode = packet_mode;
+    st->bandwidth = packet_bandwidth;
+    st->frame_size = packet_frame_size;
+    st->stream_channels = packet_stream_channels;
+    pl->off[nf] = off + payload_offset;
+    pl->len[nf] = sizes[0];
+    pl->nsamp[nf] = (i16)packet_frame_size;
+    pl->pcm_off[nf] = (i16)plc_samples;
+    pl->fec_frame = sizes[0] > 1 ? nf : -1;     // a 0/1-byte first frame is concealed, not FEC-decoded
+    pl->kind = CB_PLAN_DECODE;
+    pl->nframes = nf + 1;
+    pl->total_samples = frame_size;
+    pl->ret = frame_size;
+    st->last_packet_duration = frame_size;
     return;
   }
   if (count * packet_frame_size > frame_size) { pl->ret = CB_BUFFER_TOO_SMALL; return; }
-  if (packet_mode != CB_MODE_CELT_ONLY) { pl->ret = CB_UNIMPLEMENTED; return; }   // SILK/hybrid: not built yet
+  if (packet_mode == CB_MODE_HYBRID) { pl->ret = CB_UNIMPLEMENTED; return; }   // hybrid: not built yet
   st->mode = packet_mode;
   st->bandwidth = packet_bandwidth;
   st->frame_size = packet_frame_size;
@@ -248,6 +277,18 @@ CB_HD void opus_plan_stream(OpusDecState* st, StreamPlan* pl, const u8* data, i3
   pl->total_samples = count * packet_frame_size;
   pl->ret = count * packet_frame_size;
   st->last_packet_duration = pl->ret;
+}
+
+// True when the SILK kernel (cb_silk_pass.h) owns frame `pass` of the plan rather than the CELT kernels.
+CB_HD bool silk_owns_frame(const OpusDecState* st, const StreamPlan* pl, int pass) {
+  if (pl->ret < 0 || pass >= pl->nframes) return false;
+  if (pl->kind == CB_PLAN_DECODE) {
+    const bool conceal = pl->len[pass] <= 1 && pl->fec_frame != pass;
+    const int mode = conceal ? st->prev_mode : st->mode;
+    return mode == CB_MODE_SILK_ONLY || mode == CB_MODE_HYBRID;
+  }
+  if (pl->kind == CB_PLAN_PLC) return st->prev_mode == CB_MODE_SILK_ONLY || st->prev_mode == CB_MODE_HYBRID;
+  return false;
 }
 
 // opus_multistream_packet_validate (opus-fix/src/opus_multistream_decoder.c:155-183)

@@ -223,3 +223,28 @@ struct SilkDecControl {           // silk_decoder_control (per frame)
   i16 LTPCoef_Q14[SK_LTP_ORDER * SK_MAX_NB_SUBFR];
   i32 LTP_scale_Q14;
 };
+
+// silk_init_decoder (init_decoder.c:38-56) with silk_CNG_Reset (CNG.c:63-79) and silk_PLC_Reset (PLC.c:54-63)
+// evaluated on the cleared state (LPC_order = frame_length = 0); usable from host and device.
+CB_HD void sk_init_channel(SilkChannel& ps) {
+  unsigned char* p = (unsigned char*)&ps;
+  for (size_t i = 0; i < sizeof(SilkChannel); i++) p[i] = 0;
+  ps.first_frame_after_reset = 1;
+  ps.prev_gain_Q16 = 65536;
+  ps.sCNG.CNG_smth_Gain_Q16 = 0;
+  ps.sCNG.rand_seed = 3176576;
+  ps.sPLC.pitchL_Q8 = 0;
+  ps.sPLC.prevGain_Q16[0] = 65536;
+  ps.sPLC.prevGain_Q16[1] = 65536;
+  ps.sPLC.subfr_length = 20;
+  ps.sPLC.nb_subfr = 2;
+}
+// silk_InitDecoder (dec_API.c:61-76)
+CB_HD void sk_init_decoder(SilkDecState& d) {
+  sk_init_channel(d.ch[0]);
+  sk_init_channel(d.ch[1]);
+  d.sStereo.pred_prev_Q13[0] = d.sStereo.pred_prev_Q13[1] = 0;
+  d.sStereo.sMid[0] = d.sStereo.sMid[1] = 0;
+  d.sStereo.sSide[0] = d.sStereo.sSide[1] = 0;
+  d.prev_decode_only_middle = 0;
+}

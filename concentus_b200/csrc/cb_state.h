@@ -9,6 +9,7 @@
 // oldest sample) plus a 60-sample overlap tail, so a frame costs N stores instead of ~2048.
 #pragma once
 #include "cb_common.h"
+#include "cb_silk_common.h"
 #include <stddef.h>
 
 #define CB_NBANDS 21
@@ -94,6 +95,7 @@ struct alignas(16) OpusDecState {
   u32 rangeFinal;
   i32 pad;
   CeltDecState celt;
+  SilkDecState silk;            // silk_dec + the persistent part of DecControl (opus_decoder.c:57,63)
 };
 // opus_decoder_init + OPUS_RESET_STATE (opus_decoder.c:96-137,833-843)
 static inline void opus_state_reset(OpusDecState* s, int Fs, int channels, int keep_gain) {
@@ -111,6 +113,11 @@ static inline void opus_state_reset(OpusDecState* s, int Fs, int channels, int k
   s->last_packet_duration = 0;
   s->rangeFinal = 0;
   s->pad = 0;
+  sk_init_decoder(s->silk);
+  if (!keep_gain) {               // opus_decoder_init clears the whole struct; OPUS_RESET_STATE keeps DecControl
+    s->silk.nChannelsAPI = s->silk.nChannelsInternal = 0;
+    s->silk.ctl_nChannelsInternal = s->silk.ctl_internalSampleRate = s->silk.ctl_payloadSize_ms = s->silk.ctl_prevPitchLag = 0;
+  }
 }
 
 // What the plan kernel decides for one stream of a batch call: which frames each later pass
@@ -125,6 +132,7 @@ struct alignas(16) StreamPlan {
   i32 nframes;
   i32 kind;
   i32 total_samples;        // samples per channel covered by the plan
+  i32 fec_frame;            // index of the frame decoded from in-band FEC (lost_flag 2), or -1
   i32 off[CB_MAX_FRAMES];   // payload offset in the arena
   i16 len[CB_MAX_FRAMES];   // payload bytes (<=1 means "conceal this frame")
   i16 nsamp[CB_MAX_FRAMES]; // samples per channel produced (API rate)

@@ -6,6 +6,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include "../../concentus_b200/csrc/cb_decode_pass.h"
+#include "../../concentus_b200/csrc/cb_silk_pass.h"
 
 extern "C" {
 
@@ -49,6 +50,7 @@ int emu_opus_decode(void* state, const unsigned char* data, int len, short* pcm,
   static FrameSide side;
   static PlcWork pw;
   static unsigned char pkt[1600];
+  static SilkCallWork cw;
   StreamPlan pl;
   i32 ret = 0;
   opus_plan_stream(st, &pl, data, data ? 0 : -1, data ? len : 0, frame_size, fec, 0, nullptr);
@@ -57,6 +59,7 @@ int emu_opus_decode(void* state, const unsigned char* data, int len, short* pcm,
     decode_entropy_pass(ew, pkt, st, &pl, &side, data, &ret, pass);
     for (int c = 0; c < st->channels; c++) decode_synth_pass(sw, st, &pl, &side, pcm, c, pass);
     decode_plc_pass(pw, st, &pl, &side, pcm, pass);
+    decode_silk_pass(st, &pl, data, pcm, &ret, pass, cw);
   }
   return ret;
 }

@@ -26,6 +26,10 @@ def grab(path, name):
     body = src[i:j - 1]
     body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
     body = re.sub(r"#.*", "", body)
+    # macro-valued entries (define.h:125-128)
+    for k, v in (("OFFSET_VL_Q10", "32"), ("OFFSET_VH_Q10", "100"), ("OFFSET_UVL_Q10", "100"), ("OFFSET_UVH_Q10", "240")):
+        body = body.replace(k, v)
+    assert not re.search(r"[A-Za-z_]", body), (name, body[:200])
     return [int(t) for t in re.findall(r"-?\d+", body)]
 
 
