@@ -202,6 +202,41 @@ def emu_enc_lib():
     return lib
 
 
+def silk_golden_index():
+    return json.load(open(os.path.join(GOLDEN, "index_silk.json")))
+
+
+class EmuOpusDecoder(object):
+    """Host-emulation build of the whole decode path (plan + CELT passes + SILK pass), one stream."""
+
+    def __init__(self, lib, fs, ch):
+        lib.emu_opus_create.restype = ctypes.c_void_p
+        lib.emu_opus_create.argtypes = [ctypes.c_int, ctypes.c_int]
+        lib.emu_opus_destroy.argtypes = [ctypes.c_void_p]
+        lib.emu_opus_decode.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
+                                        ctypes.c_int]
+        lib.emu_opus_final_range.argtypes = [ctypes.c_void_p]
+        lib.emu_opus_final_range.restype = ctypes.c_uint
+        self.lib, self.ch = lib, ch
+        self.h = lib.emu_opus_create(fs, ch)
+
+    def decode_raw(self, data, frame_size, fec=0):
+        pcm = np.zeros((max(frame_size, 1), self.ch), dtype=np.int16)
+        ret = self.lib.emu_opus_decode(self.h, data, len(data) if data else 0, pcm.ctypes.data, frame_size, int(fec))
+        return ret, pcm
+
+    @property
+    def final_range(self):
+        return self.lib.emu_opus_final_range(self.h)
+
+    def close(self):
+        if self.h:
+            self.lib.emu_opus_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+
 def enc_golden_index():
     return json.load(open(os.path.join(GOLDEN, "enc_index.json")))
 

@@ -103,3 +103,29 @@ def fuzz_scenario(name, seed):
         fsz = m * spf if rng.rand() < 0.9 else max(1, m * spf - spf // 2)
         calls.append((data, fsz, 0))
     return meta, calls
+
+
+def silk_calls(npackets, loss, fec, seed=11):
+    """The decode-call sequence of the SILK loss/FEC fixtures: yields (packet index or None, decode_fec).
+    A lost packet is concealed (None, 0); with FEC enabled the concealment is deferred to the arrival of
+    the next packet, whose in-band redundancy is decoded first: (next, 1) then (next, 0)."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    lost = [bool(loss > 0 and rng.random() < loss) for _ in range(npackets)]
+    lost[0] = False
+    out = []
+    pending = False
+    for i in range(npackets):
+        if lost[i]:
+            if fec:
+                if pending:
+                    out.append((None, 0))     # two losses in a row: the older one is plainly concealed
+                pending = True
+            else:
+                out.append((None, 0))
+            continue
+        if pending:
+            out.append((i, 1))
+            pending = False
+        out.append((i, 0))
+    return out

@@ -1,0 +1,121 @@
+"""CPU-side parity of the SILK decode path (host build of the kernel sources): SILK-only packets made by
+the reference encoder from the reference's test audio, replayed with losses / in-band FEC / DTX, against
+the committed goldens (PCM CRC32, return value and final range per decode call) and, where oracle/_ref is
+built, against the reference decoder on synthetic voice at every bandwidth / frame size / output rate."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import (GOLDEN, EmuOpusDecoder, RefDecoder, RefEncoder, crc32, needs_ref, read_bit, silk_golden_index)
+from scenarios import silk_calls
+
+CASES = sorted(silk_golden_index().keys())
+
+
+def replay(dec, meta, pk):
+    """Run the fixture's decode-call sequence on `dec`; yields (call number, ret, pcm, final range)."""
+    for k, (idx, use_fec) in enumerate(silk_calls(len(pk), meta["loss"], meta["fec"], seed=11)):
+        data = pk[idx][0] if idx is not None else None
+        ret, pcm = dec.decode_raw(data, meta["samples_per_frame"], use_fec)
+        yield k, ret, pcm, dec.final_range
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_emu_silk_matches_golden(emu_lib, name):
+    meta = silk_golden_index()[name]
+    pk = read_bit(os.path.join(GOLDEN, name + ".bit"))
+    dec = EmuOpusDecoder(emu_lib, meta["fs"], meta["channels"])
+    n = 0
+    for k, ret, pcm, rng in replay(dec, meta, pk):
+        assert ret == meta["ret"][k], (name, k, ret)
+        assert crc32(pcm[:ret]) == meta["pcm_crc32"][k], (name, "pcm of call", k)
+        assert rng == meta["final_range"][k], (name, k)
+        n += 1
+    assert n == len(meta["ret"])
+
+
+def voice(n, ch, seed, fs):
+    rng = np.random.default_rng(seed)
+    t = np.arange(n) / fs
+    f0 = 120 + 40 * np.sin(2 * np.pi * 0.7 * t)
+    ph = 2 * np.pi * np.cumsum(f0) / fs
+    voiced = sum(np.sin(k * ph) / k for k in range(1, 12)) * 4000
+    env = (np.sin(2 * np.pi * 1.3 * t) > -0.2) * (0.3 + 0.7 * np.abs(np.sin(2 * np.pi * 2.1 * t)))
+    x = voiced * env + rng.normal(0, 300, n) * (1 - env) * 3
+    x[n // 2: n // 2 + fs // 3] = 0
+    if ch == 2:
+        y = 0.7 * x + 0.3 * np.roll(x, 11) + rng.normal(0, 50, n)
+        x = np.stack([x, y], axis=1).reshape(-1)
+    return np.clip(np.round(x), -32768, 32767).astype(np.int16)
+
+
+def silk_packets(fs_enc, ch, ms, bitrate, nframes, ctls=(), seed=1):
+    enc = RefEncoder(fs_enc, ch, 2048)
+    assert enc.ctl(4002, bitrate) == 0
+    for r, v in ctls:
+        assert enc.ctl(r, v) == 0
+    fr = fs_enc * ms // 1000
+    pcm = voice(fr * nframes, ch, seed, fs_enc)
+    return [enc.encode(pcm[i * fr * ch:(i + 1) * fr * ch], fr, 1275)[1] for i in range(nframes)]
+
+
+@needs_ref
+@pytest.mark.parametrize("fs_enc", [16000, 12000, 8000])
+def test_emu_silk_matches_reference_all_shapes(emu_lib, fs_enc):
+    for ch in (1, 2):
+        for ms in (10, 20, 40, 60):
+            pk = silk_packets(fs_enc, ch, ms, 14000 * ch + fs_enc // 2, 25, ctls=[(4012, 1), (4014, 25)])
+            for fs_dec, chd in ((fs_enc, ch), (48000, 3 - ch), (8000, ch), (24000, 2), (12000, 1), (16000, 2)):
+                for loss, fec in ((0.0, False), (0.25, False), (0.25, True)):
+                    ref, emu = RefDecoder(fs_dec, chd), EmuOpusDecoder(emu_lib, fs_dec, chd)
+                    fsz = fs_dec * ms // 1000
+                    for idx, use_fec in silk_calls(len(pk), loss, fec, seed=5):
+                        data = pk[idx] if idx is not None else None
+                        r1, p1 = ref.decode_raw(data, fsz, use_fec)
+                        r2, p2 = emu.decode_raw(data, fsz, use_fec)
+                        assert r1 == r2, (fs_enc, ch, ms, fs_dec, chd, loss, fec, idx)
+                        assert np.array_equal(p1[:r1], p2[:r1]), (fs_enc, ch, ms, fs_dec, chd, loss, fec, idx)
+                        assert ref.final_range == emu.final_range
+
+
+@needs_ref
+def test_emu_silk_bandwidth_and_channel_switches(emu_lib):
+    """One decoder fed NB, then WB, then MB, then stereo, then mono SILK packets (resampler re-init, stereo
+    state transitions), with a few concealed frames at the joints."""
+    segs = [silk_packets(8000, 1, 20, 12000, 12, seed=2), silk_packets(16000, 1, 20, 24000, 12, seed=3),
+            silk_packets(12000, 1, 20, 18000, 12, seed=4), silk_packets(16000, 2, 20, 40000, 12, seed=5),
+            silk_packets(16000, 1, 20, 24000, 12, seed=6), silk_packets(8000, 2, 20, 20000, 12, seed=7)]
+    for fs_dec, chd in ((48000, 2), (16000, 1), (24000, 2)):
+        ref, emu = RefDecoder(fs_dec, chd), EmuOpusDecoder(emu_lib, fs_dec, chd)
+        fsz = fs_dec // 50
+        k = 0
+        for seg in segs:
+            for p in seg + [None, None]:
+                r1, p1 = ref.decode_raw(p, fsz)
+                r2, p2 = emu.decode_raw(p, fsz)
+                assert r1 == r2 and np.array_equal(p1[:r1], p2[:r1]), (fs_dec, chd, k)
+                assert ref.final_range == emu.final_range
+                k += 1
+
+
+@needs_ref
+def test_emu_unbuilt_modes_are_refused(emu_lib):
+    """Hybrid packets and CELT<->SILK transitions answer OPUS_UNIMPLEMENTED instead of wrong audio."""
+    enc = RefEncoder(48000, 1, 2048)
+    enc.ctl(4002, 32000)
+    pcm = voice(960 * 4, 1, 1, 48000)
+    hyb = [enc.encode(pcm[i * 960:(i + 1) * 960], 960, 1275)[1] for i in range(4)]
+    assert (hyb[-1][0] & 0xE0) in (0x60, 0x70), "expected a hybrid packet"
+    emu = EmuOpusDecoder(emu_lib, 48000, 1)
+    assert emu.decode_raw(hyb[-1], 960)[0] == -5
+    silk = silk_packets(16000, 1, 20, 24000, 3)
+    enc2 = RefEncoder(48000, 1, 2051)
+    enc2.ctl(4002, 32000)
+    celt = enc2.encode(pcm[:960], 960, 1275)[1]
+    emu = EmuOpusDecoder(emu_lib, 48000, 1)
+    assert emu.decode_raw(silk[0], 960)[0] == 960
+    assert emu.decode_raw(celt, 960)[0] == -5          # SILK -> CELT transition
+    emu = EmuOpusDecoder(emu_lib, 48000, 1)
+    assert emu.decode_raw(celt, 960)[0] == 960
+    assert emu.decode_raw(silk[0], 960)[0] == -5       # CELT -> SILK transition
