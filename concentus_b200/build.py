@@ -7,11 +7,14 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libopus_b200.so")
-SOURCES = ["cb_kernels.cu", "opus_api.cu", "cb_noalloc.cu", "cb_enc_kernels.cu", "opus_enc_api.cu", "cb_silk_kernels.cu"]
+SOURCES = ["cb_kernels.cu", "opus_api.cu", "cb_noalloc.cu", "cb_enc_kernels.cu", "opus_enc_api.cu", "cb_silk_kernels.cu", "cb_general_kernels.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "--compiler-options", "-fPIC", "-shared",
 ]
+
+
+OBJ = os.path.join(HERE, "_obj")
 
 
 def _newest(paths):
@@ -26,18 +29,57 @@ def needs_build():
     return _newest(srcs) > os.path.getmtime(LIB)
 
 
+def _deps(dfile):
+    """Prerequisites listed in a make-style dependency file written by nvcc -MD."""
+    txt = open(dfile).read().replace("\\\n", " ")
+    return [t for t in txt.split(":", 1)[1].split() if os.path.exists(t)]
+
+
+def _object_stale(obj, dfile, src):
+    if not (os.path.exists(obj) and os.path.exists(dfile)):
+        return True
+    t = os.path.getmtime(obj)
+    if os.path.getmtime(src) > t or os.path.getmtime(__file__) > t:
+        return True
+    try:
+        return any(os.path.getmtime(d) > t for d in _deps(dfile))
+    except (OSError, IndexError):
+        return True
+
+
 def build(force=False, verbose=False):
-    """Compile the library if sources are newer than the .so.  Returns the path."""
+    """Compile the library if sources are newer than the .so.  Returns the path.
+    One object per translation unit, compiled concurrently; an object is reused while none of the files
+    it included has changed."""
     if not force and not needs_build():
         return LIB
     nvcc = os.environ.get("NVCC", "nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + SOURCES
-    res = subprocess.run(cmd, cwd=CSRC, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    os.makedirs(OBJ, exist_ok=True)
+    jobs = []
+    objs = []
+    for src in SOURCES:
+        obj = os.path.join(OBJ, src[:-3] + ".o")
+        dfile = os.path.join(OBJ, src[:-3] + ".d")
+        objs.append(obj)
+        if not force and not _object_stale(obj, dfile, os.path.join(CSRC, src)):
+            continue
+        cmd = [nvcc] + NVCC_FLAGS[:-1] + (["-Xptxas", "-v"] if verbose else []) + ["-MD", "-MF", dfile, "-c", "-o", obj, src]
+        jobs.append((src, subprocess.Popen(cmd, cwd=CSRC, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+    failed = False
+    for src, pr in jobs:
+        out = pr.communicate()[0]
+        if pr.returncode != 0:
+            sys.stderr.write(out)
+            failed = True
+        elif verbose:
+            print(out)
+    if failed:
+        raise RuntimeError("nvcc failed building libopus_b200.so")
+    res = subprocess.run([nvcc] + NVCC_FLAGS + ["-o", LIB] + objs, cwd=CSRC, stdout=subprocess.PIPE,
+                         stderr=subprocess.STDOUT, text=True)
     if res.returncode != 0:
         sys.stderr.write(res.stdout)
-        raise RuntimeError("nvcc failed building libopus_b200.so")
-    if verbose:
-        print(res.stdout)
+        raise RuntimeError("nvcc failed linking libopus_b200.so")
     return LIB
 
 

@@ -1138,7 +1138,10 @@ CB_FN int dec_allocation(EntWork& w, RangeDec& rd, int start, int end, int alloc
 
 // ---- one CELT frame, entropy half (celt_decoder.c:713-1062 minus synthesis/deemphasis) -------
 // `pkt`/`len`: CELT payload staged in shared memory.  Returns 0 or a negative OPUS_* code.
-struct EntFrameCfg { int LM, C, start, end, accum; };
+struct EntFrameCfg {
+  int LM, C, start, end, accum;
+  const RangeDec* rd0;   // hybrid: the coder state the SILK layer left (same packet bytes); else nullptr
+};
 
 CB_FN int celt_entropy_decode(EntWork& w, CeltDecState* stg, FrameSide* side, const u8* pkt, int len,
                               const EntFrameCfg& cfg, u32* final_range) {
@@ -1153,7 +1156,13 @@ CB_FN int celt_entropy_decode(EntWork& w, CeltDecState* stg, FrameSide* side, co
   int effEnd = end > CB_NBANDS ? CB_NBANDS : end;
 
   RangeDec& rd = w.rd;
-  rd_init(rd, pkt, (u32)len);
+  if (cfg.rd0) {                     // celt_decode_with_ec(dec != NULL), celt_decoder.c:813-818
+    rd = *cfg.rd0;
+    rd.buf = pkt;
+    rd.storage = (u32)len;
+  } else {
+    rd_init(rd, pkt, (u32)len);
+  }
 
   if (C == 1) {
     CB_WSYNC();

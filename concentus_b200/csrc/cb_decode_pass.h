@@ -10,6 +10,12 @@
 CB_FN void decode_entropy_pass(EntWork& w, u8* pkt, OpusDecState* st, StreamPlan* pl, FrameSide* side,
                                const u8* data, i32* ret_slot, int pass) {
   const int kind = pl->kind;
+  // decide once per pass who decodes this stream's frame; the SILK and general kernels read it later
+  int route = -1;
+  if (!(pl->ret < 0 || pass >= pl->nframes || kind == CB_PLAN_NONE || kind == CB_PLAN_ZERO)) route = opus_frame_route(st, pl, pass);
+  CB_WSYNC();
+  CB_IF_LANE0 pl->route = route;
+  CB_WSYNC();
   if (pl->ret < 0 || pass >= pl->nframes || kind == CB_PLAN_NONE) {
     side->kind = 0;
     return;
@@ -18,7 +24,7 @@ CB_FN void decode_entropy_pass(EntWork& w, u8* pkt, OpusDecState* st, StreamPlan
     side->kind = 3;
     return;
   }
-  if (silk_owns_frame(st, pl, pass)) {              // SILK frames are decoded by the SILK kernel
+  if (route != CB_ROUTE_CELT) {                     // decoded by the SILK kernel or the general kernel
     side->kind = 0;
     return;
   }
@@ -47,13 +53,6 @@ CB_FN void decode_entropy_pass(EntWork& w, u8* pkt, OpusDecState* st, StreamPlan
     st->prev_redundancy = 0;
     return;
   }
-  if (st->prev_mode != 0 && st->prev_mode != CB_MODE_CELT_ONLY && !st->prev_redundancy) {
-    // SILK -> CELT mode transition (opus_decoder.c:330-345): needs the SILK concealment cross-fade, not built yet
-    side->kind = 0;
-    pl->ret = CB_UNIMPLEMENTED;
-    *ret_slot = CB_UNIMPLEMENTED;
-    return;
-  }
   const i32 off = pl->off[pass];
   CB_LANE_LOOP(i, len) pkt[i] = data[off + i];
   CB_WSYNC();
@@ -68,6 +67,7 @@ CB_FN void decode_entropy_pass(EntWork& w, u8* pkt, OpusDecState* st, StreamPlan
   cfg.start = 0;
   cfg.end = opus_bandwidth_endband(st->bandwidth);
   cfg.accum = 0;
+  cfg.rd0 = nullptr;
   u32 fr = 0;
   int rc = celt_entropy_decode(w, &st->celt, side, pkt, len, cfg, &fr);
   st->rangeFinal = fr;

@@ -1,0 +1,45 @@
+// cb_general_kernels.cu -- sm_100a kernel for the Opus frames the fast kernels do not take.
+//
+//   opus_general_kernel : 1 warp / stream -- opus_decode_frame in full (cb_opus_general.h): hybrid
+//   packets, CELT<->SILK/hybrid transitions and packets with a redundant CELT frame.  The SILK layer
+//   of such a frame runs on lane 0; the CELT layer, the fades and the gain on the whole warp.
+// Streams whose frame was not routed here leave at once; other batches pay one empty launch.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "cb_opus_general.h"
+#include "cb_kernels.h"
+
+#define G_WARPS 4
+
+__global__ void __launch_bounds__(G_WARPS * 32)
+opus_general_kernel(OpusDecState* const* states, StreamPlan* plans, FrameSide* sides, const u8* data, i16* pcm,
+                    i32 pcm_stride, i32* ret, int n, int pass) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int warp = threadIdx.x >> 5;
+  const int s = blockIdx.x * G_WARPS + warp;
+  if (s >= n) return;
+  StreamPlan* pl = &plans[s];
+  const int route = pl->route;
+  if (route != CB_ROUTE_GENERAL && route != CB_ROUTE_FINISH) return;
+  GenWork& g = *reinterpret_cast<GenWork*>(smem + (size_t)warp * sizeof(GenWork));
+  SilkCallWork cw;
+  decode_general_pass(g, states[s], pl, &sides[s], data, pcm + (size_t)s * pcm_stride, &ret[s], pass, cw);
+}
+
+extern "C" int cbk_launch_general(OpusDecState* const* d_states, StreamPlan* d_plans, FrameSide* d_sides, const u8* d_data,
+                                  i16* d_pcm, i32 pcm_stride, i32* d_ret, int n, int pass, cudaStream_t stream) {
+  if (n <= 0) return 0;
+  static bool attr_set[64];
+  const int smem = G_WARPS * (int)sizeof(GenWork);
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev >= 64 || !attr_set[dev]) {
+    e = cudaFuncSetAttribute(opus_general_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 64) attr_set[dev] = true;
+  }
+  opus_general_kernel<<<(n + G_WARPS - 1) / G_WARPS, G_WARPS * 32, smem, stream>>>(d_states, d_plans, d_sides, d_data, d_pcm,
+                                                                                    pcm_stride, d_ret, n, pass);
+  return (int)cudaGetLastError();
+}

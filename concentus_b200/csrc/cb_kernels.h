@@ -16,6 +16,8 @@ int cbk_launch_synth(OpusDecState* const* d_states, const StreamPlan* d_plans, c
 // SILK frames of pass `pass` (one thread per stream); streams whose frame is CELT return at once
 int cbk_launch_silk(OpusDecState* const* d_states, StreamPlan* d_plans, const u8* d_data, i16* d_pcm,
                     i32 pcm_stride, i32* d_ret, int n, int pass, cudaStream_t stream);
+int cbk_launch_general(OpusDecState* const* d_states, StreamPlan* d_plans, FrameSide* d_sides, const u8* d_data,
+                       i16* d_pcm, i32 pcm_stride, i32* d_ret, int n, int pass, cudaStream_t stream);
 int cbk_launch_ms_plan(OpusDecState* const* d_states, StreamPlan* d_plans, const MSLayout* d_layouts,
                        const u8* d_data, const i32* d_off, const i32* d_len, const i32* d_fec, int frame_size,
                        i32* d_ms_ret, int n_ms, cudaStream_t stream);

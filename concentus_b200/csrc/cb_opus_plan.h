@@ -259,7 +259,6 @@ CB_HD void opus_plan_stream(OpusDecState* st, StreamPlan* pl, const u8* data, i3
     return;
   }
   if (count * packet_frame_size > frame_size) { pl->ret = CB_BUFFER_TOO_SMALL; return; }
-  if (packet_mode == CB_MODE_HYBRID) { pl->ret = CB_UNIMPLEMENTED; return; }   // hybrid: not built yet
   st->mode = packet_mode;
   st->bandwidth = packet_bandwidth;
   st->frame_size = packet_frame_size;
@@ -279,16 +278,25 @@ CB_HD void opus_plan_stream(OpusDecState* st, StreamPlan* pl, const u8* data, i3
   st->last_packet_duration = pl->ret;
 }
 
-// True when the SILK kernel (cb_silk_pass.h) owns frame `pass` of the plan rather than the CELT kernels.
-CB_HD bool silk_owns_frame(const OpusDecState* st, const StreamPlan* pl, int pass) {
-  if (pl->ret < 0 || pass >= pl->nframes) return false;
-  if (pl->kind == CB_PLAN_DECODE) {
-    const bool conceal = pl->len[pass] <= 1 && pl->fec_frame != pass;
-    const int mode = conceal ? st->prev_mode : st->mode;
-    return mode == CB_MODE_SILK_ONLY || mode == CB_MODE_HYBRID;
+// where frame `pass` of the plan is decoded: 0 CELT kernels (A/B/C), 1 SILK kernel, 2 this file
+#define CB_ROUTE_CELT 0
+#define CB_ROUTE_SILK 1
+#define CB_ROUTE_GENERAL 2
+#define CB_ROUTE_FINISH 3      // SILK kernel decoded the SILK layer and found a redundant CELT frame: general kernel finishes
+CB_HD int opus_frame_route(const OpusDecState* st, const StreamPlan* pl, int pass) {
+  const bool conceal = pl->kind == CB_PLAN_PLC || (pl->len[pass] <= 1);
+  if (conceal) {
+    if (st->prev_mode == CB_MODE_SILK_ONLY) return CB_ROUTE_SILK;
+    if (st->prev_mode == CB_MODE_HYBRID) return CB_ROUTE_GENERAL;
+    return CB_ROUTE_CELT;
   }
-  if (pl->kind == CB_PLAN_PLC) return st->prev_mode == CB_MODE_SILK_ONLY || st->prev_mode == CB_MODE_HYBRID;
-  return false;
+  const int mode = st->mode, prev = st->prev_mode;
+  if (mode == CB_MODE_CELT_ONLY) {
+    if (prev == 0 || prev == CB_MODE_CELT_ONLY || st->prev_redundancy) return CB_ROUTE_CELT;
+    return CB_ROUTE_GENERAL;
+  }
+  if (mode == CB_MODE_SILK_ONLY && (prev == 0 || prev == CB_MODE_SILK_ONLY)) return CB_ROUTE_SILK;
+  return CB_ROUTE_GENERAL;
 }
 
 // opus_multistream_packet_validate (opus-fix/src/opus_multistream_decoder.c:155-183)

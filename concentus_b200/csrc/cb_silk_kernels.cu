@@ -22,7 +22,7 @@ silk_decode_kernel(OpusDecState* const* states, StreamPlan* plans, const u8* dat
   if (s >= n) return;
   OpusDecState* st = states[s];
   StreamPlan* pl = &plans[s];
-  if (!silk_owns_frame(st, pl, pass)) return;
+  if (pl->route != CB_ROUTE_SILK) return;
   SilkCallWork cw;
   decode_silk_pass(st, pl, data, pcm + (size_t)s * pcm_stride, &ret[s], pass, cw);
 }

@@ -10,7 +10,7 @@
 
 CB_FN void decode_silk_pass(OpusDecState* st, StreamPlan* pl, const u8* data, i16* row, i32* ret_slot, int pass,
                             SilkCallWork& cw) {
-  if (!silk_owns_frame(st, pl, pass)) return;
+  if (pl->route != CB_ROUTE_SILK) return;
   const int Fs = st->Fs, CC = st->channels;
   const int F20 = Fs / 50, F10 = F20 >> 1;
   const int decode_fec = pl->fec_frame == pass;
@@ -20,15 +20,6 @@ CB_FN void decode_silk_pass(OpusDecState* st, StreamPlan* pl, const u8* data, i1
   const int frame_size = audiosize;
   const int mode = have_data ? st->mode : st->prev_mode;
   i16* pcm = row + (size_t)pl->pcm_off[pass] * CC;
-  int err = 0;
-  if (mode == CB_MODE_HYBRID) err = CB_UNIMPLEMENTED;
-  if (have_data && st->prev_mode == CB_MODE_CELT_ONLY) err = CB_UNIMPLEMENTED;     // transition needs the CELT PLC
-  if (err) {
-    for (int i = 0; i < frame_size * CC; i++) pcm[i] = 0;
-    pl->ret = err;
-    *ret_slot = err;
-    return;
-  }
   RangeDec rd;
   const u8* pkt = data + pl->off[pass];
   if (have_data) rd_init(rd, pkt, (u32)len);
@@ -69,8 +60,11 @@ CB_FN void decode_silk_pass(OpusDecState* st, StreamPlan* pl, const u8* data, i1
     for (int i = 0; i < frame_size * CC; i++) pcm[i] = small[i];
   // a SILK-only packet with >= 17 bits left over carries a redundant CELT frame (opus_decoder.c:412-440)
   if (!decode_fec && have_data && (int)rd_tell(rd) + 17 <= 8 * len) {
-    pl->ret = CB_UNIMPLEMENTED;
-    *ret_slot = CB_UNIMPLEMENTED;
+    // the general kernel (cb_opus_general.h) decodes the CELT frame and does the cross-fade: hand over
+    // the coder state; gain and Opus-layer state are applied there
+    const u32* src = (const u32*)&rd;
+    for (int i = 0; i < (int)(sizeof(RangeDec) / 4); i++) pl->rd_save[i] = src[i];
+    pl->route = CB_ROUTE_FINISH;
     return;
   }
   if (st->decode_gain) {

@@ -60,7 +60,7 @@ struct alignas(16) FrameSide {
 
 // celt_decoder_init + OPUS_RESET_STATE (celt_decoder.c:134-172,1196-1204): all-zero except the
 // two log-energy memories, which start at -28 dB.  Host-side helper (the blob is then copied to HBM).
-static inline void celt_state_reset(CeltDecState* s, int channels, int downsample) {
+CB_HD void celt_state_reset(CeltDecState* s, int channels, int downsample) {
   unsigned char* p = (unsigned char*)s;
   for (size_t i = 0; i < sizeof(CeltDecState); i++) p[i] = 0;
   s->channels = channels;
@@ -133,6 +133,8 @@ struct alignas(16) StreamPlan {
   i32 kind;
   i32 total_samples;        // samples per channel covered by the plan
   i32 fec_frame;            // index of the frame decoded from in-band FEC (lost_flag 2), or -1
+  i32 route;                // who decodes the current pass's frame (CB_ROUTE_*), set by kernel A at pass start
+  u32 rd_save[16];          // range-decoder state handed from the SILK kernel to the general kernel (late redundancy)
   i32 off[CB_MAX_FRAMES];   // payload offset in the arena
   i16 len[CB_MAX_FRAMES];   // payload bytes (<=1 means "conceal this frame")
   i16 nsamp[CB_MAX_FRAMES]; // samples per channel produced (API rate)

@@ -347,7 +347,8 @@ static int group_enqueue_passes(OpusDecoderGroup* g, const u8* d_data, i16* d_pc
       rc = cbk_launch_synth(g->d_states, g->d_plans, g->d_sides, d_pcm, pcm_stride, g->n, p, stream);
     }
     if (!rc) rc = cbk_launch_silk(g->d_states, g->d_plans, d_data, d_pcm, pcm_stride, d_ret, g->n, p, stream);
-    g_launches += 4;
+    if (!rc) rc = cbk_launch_general(g->d_states, g->d_plans, g->d_sides, d_data, d_pcm, pcm_stride, d_ret, g->n, p, stream);
+    g_launches += 5;
     if (rc) { fprintf(stderr, "[opus_b200] pass launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
   }
   return OPUS_OK;

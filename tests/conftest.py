@@ -203,7 +203,10 @@ def emu_enc_lib():
 
 
 def silk_golden_index():
-    return json.load(open(os.path.join(GOLDEN, "index_silk.json")))
+    """SILK-only fixtures plus the hybrid / mode-transition fixtures (same replay format)."""
+    idx = json.load(open(os.path.join(GOLDEN, "index_silk.json")))
+    idx.update(json.load(open(os.path.join(GOLDEN, "index_hybrid.json"))))
+    return idx
 
 
 class EmuOpusDecoder(object):

@@ -7,6 +7,7 @@
 #include <string.h>
 #include "../../concentus_b200/csrc/cb_decode_pass.h"
 #include "../../concentus_b200/csrc/cb_silk_pass.h"
+#include "../../concentus_b200/csrc/cb_opus_general.h"
 
 extern "C" {
 
@@ -51,6 +52,7 @@ int emu_opus_decode(void* state, const unsigned char* data, int len, short* pcm,
   static PlcWork pw;
   static unsigned char pkt[1600];
   static SilkCallWork cw;
+  static GenWork gw;
   StreamPlan pl;
   i32 ret = 0;
   opus_plan_stream(st, &pl, data, data ? 0 : -1, data ? len : 0, frame_size, fec, 0, nullptr);
@@ -60,6 +62,7 @@ int emu_opus_decode(void* state, const unsigned char* data, int len, short* pcm,
     for (int c = 0; c < st->channels; c++) decode_synth_pass(sw, st, &pl, &side, pcm, c, pass);
     decode_plc_pass(pw, st, &pl, &side, pcm, pass);
     decode_silk_pass(st, &pl, data, pcm, &ret, pass, cw);
+    decode_general_pass(gw, st, &pl, &side, data, pcm, &ret, pass, cw);
   }
   return ret;
 }

@@ -1,5 +1,6 @@
-"""CPU-side parity of the SILK decode path (host build of the kernel sources): SILK-only packets made by
-the reference encoder from the reference's test audio, replayed with losses / in-band FEC / DTX, against
+"""CPU-side parity of the SILK / hybrid decode path (host build of the kernel sources): SILK-only and hybrid
+packets, mode transitions and redundant CELT frames made by the reference encoder from the reference's test
+audio, replayed with losses / in-band FEC / DTX, against
 the committed goldens (PCM CRC32, return value and final range per decode call) and, where oracle/_ref is
 built, against the reference decoder on synthetic voice at every bandwidth / frame size / output rate."""
 import os
@@ -99,23 +100,51 @@ def test_emu_silk_bandwidth_and_channel_switches(emu_lib):
                 k += 1
 
 
+FORCE_MODE, SET_BANDWIDTH = 11002, 4008
+MODE = {"silk": 1000, "hybrid": 1001, "celt": 1002, "auto": -1000}
+TRANSITION_SCRIPTS = {
+    "hybrid": [(20, "hybrid", None)],
+    "silk>celt>silk": [(7, "silk", 1103), (7, "celt", None), (7, "silk", 1101), (5, "celt", 1103)],
+    "hybrid>celt>hybrid": [(6, "hybrid", None), (6, "celt", None), (6, "hybrid", 1104), (5, "celt", 1104)],
+    "silk>hybrid>silk": [(6, "silk", 1103), (6, "hybrid", None), (6, "silk", 1102), (6, "hybrid", 1104)],
+    "mixed": [(4, "celt", None), (5, "silk", 1101), (3, "hybrid", 1105), (4, "celt", 1102), (5, "hybrid", 1104),
+              (3, "silk", 1103), (3, "celt", 1105)],
+}
+
+
+def scripted_packets(ch, ms, script, bitrate, seed=1, app=2049, ctls=()):
+    """48 kHz reference encoder with its mode (and bandwidth) forced per segment: hybrid packets, mode
+    transitions and the redundant CELT frames that go with them."""
+    enc = RefEncoder(48000, ch, app)
+    assert enc.ctl(4002, bitrate) == 0
+    for r, v in ctls:
+        assert enc.ctl(r, v) == 0
+    fr = 48 * ms
+    pcm = voice(fr * sum(n for n, _, _ in script), ch, seed, 48000)
+    out, k = [], 0
+    for n, mode, bw in script:
+        assert enc.ctl(FORCE_MODE, MODE[mode]) == 0
+        assert enc.ctl(SET_BANDWIDTH, bw if bw else -1000) == 0
+        for _ in range(n):
+            out.append(enc.encode(pcm[k * fr * ch:(k + 1) * fr * ch], fr, 1275)[1])
+            k += 1
+    return out
+
+
 @needs_ref
-def test_emu_unbuilt_modes_are_refused(emu_lib):
-    """Hybrid packets and CELT<->SILK transitions answer OPUS_UNIMPLEMENTED instead of wrong audio."""
-    enc = RefEncoder(48000, 1, 2048)
-    enc.ctl(4002, 32000)
-    pcm = voice(960 * 4, 1, 1, 48000)
-    hyb = [enc.encode(pcm[i * 960:(i + 1) * 960], 960, 1275)[1] for i in range(4)]
-    assert (hyb[-1][0] & 0xE0) in (0x60, 0x70), "expected a hybrid packet"
-    emu = EmuOpusDecoder(emu_lib, 48000, 1)
-    assert emu.decode_raw(hyb[-1], 960)[0] == -5
-    silk = silk_packets(16000, 1, 20, 24000, 3)
-    enc2 = RefEncoder(48000, 1, 2051)
-    enc2.ctl(4002, 32000)
-    celt = enc2.encode(pcm[:960], 960, 1275)[1]
-    emu = EmuOpusDecoder(emu_lib, 48000, 1)
-    assert emu.decode_raw(silk[0], 960)[0] == 960
-    assert emu.decode_raw(celt, 960)[0] == -5          # SILK -> CELT transition
-    emu = EmuOpusDecoder(emu_lib, 48000, 1)
-    assert emu.decode_raw(celt, 960)[0] == 960
-    assert emu.decode_raw(silk[0], 960)[0] == -5       # CELT -> SILK transition
+@pytest.mark.parametrize("script", sorted(TRANSITION_SCRIPTS))
+def test_emu_hybrid_and_transitions_match_reference(emu_lib, script):
+    for ch in (1, 2):
+        for ms in (20, 10, 40):
+            pk = scripted_packets(ch, ms, TRANSITION_SCRIPTS[script], 28000 * ch, ctls=[(4012, 1), (4014, 20)])
+            for fs_dec, chd in ((48000, ch), (16000, 3 - ch), (24000, 2), (8000, 1)):
+                for loss, fec in ((0.0, False), (0.2, False), (0.2, True)):
+                    ref, emu = RefDecoder(fs_dec, chd), EmuOpusDecoder(emu_lib, fs_dec, chd)
+                    fsz = fs_dec * ms // 1000
+                    for idx, use_fec in silk_calls(len(pk), loss, fec, seed=9):
+                        data = pk[idx] if idx is not None else None
+                        r1, p1 = ref.decode_raw(data, fsz, use_fec)
+                        r2, p2 = emu.decode_raw(data, fsz, use_fec)
+                        assert r1 == r2, (script, ch, ms, fs_dec, chd, loss, fec, idx)
+                        assert np.array_equal(p1[:r1], p2[:r1]), (script, ch, ms, fs_dec, chd, loss, fec, idx)
+                        assert ref.final_range == emu.final_range, (script, ch, ms, fs_dec, chd, loss, fec, idx)

@@ -1,6 +1,7 @@
-"""SILK decode parity on the GPU: the CUDA library through its C ABI against the committed SILK goldens
-(reference encoder packets from the reference's audio, with loss / FEC / DTX call sequences) and against
-the compiled reference on batches that mix SILK and CELT streams.  Bit-exact PCM + final range."""
+"""SILK / hybrid decode parity on the GPU: the CUDA library through its C ABI against the committed SILK and
+hybrid / mode-transition goldens (reference encoder packets from the reference's audio, with loss / FEC / DTX
+call sequences) and against the compiled reference on batches that mix SILK, hybrid and CELT streams whose
+modes change under way.  Bit-exact PCM + final range."""
 import os
 
 import numpy as np
@@ -9,7 +10,7 @@ import pytest
 import concentus_b200 as cb
 from conftest import GOLDEN, RefDecoder, crc32, golden_case, needs_ref, read_bit, silk_golden_index
 from scenarios import silk_calls
-from test_emu_silk import silk_packets
+from test_emu_silk import TRANSITION_SCRIPTS, scripted_packets, silk_packets
 
 pytestmark = pytest.mark.gpu
 
@@ -54,6 +55,37 @@ def test_batch_mixing_silk_and_celt_streams():
             fr = bd.final_ranges()
             for i in range(n):
                 r1, p1 = refs[i].decode_raw(pkts[i], 960)
+                assert ret[i] == r1, (i, t, ret[i], r1)
+                assert np.array_equal(pcm[i][:r1], p1[:r1]), (i, t)
+                assert int(fr[i]) == refs[i].final_range, (i, t)
+    finally:
+        bd.close()
+
+
+@needs_ref
+@pytest.mark.parametrize("fs,ch,ms", [(48000, 2, 20), (16000, 1, 10), (24000, 2, 40)])
+def test_batch_of_streams_changing_mode(fs, ch, ms):
+    """Every stream of the batch follows its own script of mode changes (SILK-only / hybrid / CELT-only at
+    varying bandwidths, mono and stereo packets, redundant frames at the joints), shifted in time against
+    the others, with some packets lost: each batch call holds a different mix of routes."""
+    names = sorted(TRANSITION_SCRIPTS)
+    streams = []
+    for i in range(20):
+        pk = scripted_packets(1 + i % 2, ms, TRANSITION_SCRIPTS[names[i % len(names)]], 26000 + 1500 * i, seed=40 + i)
+        streams.append(pk[i % 5:])
+    nfr = min(len(p) for p in streams)
+    n = len(streams)
+    fsz = fs * ms // 1000
+    bd = cb.OpusBatchDecoder(fs, ch, n)
+    refs = [RefDecoder(fs, ch) for _ in range(n)]
+    rng = np.random.default_rng(8)
+    try:
+        for t in range(nfr):
+            pkts = [None if (t > 1 and rng.random() < 0.12) else streams[i][t] for i in range(n)]
+            ret, pcm = bd.decode(pkts, fsz)
+            fr = bd.final_ranges()
+            for i in range(n):
+                r1, p1 = refs[i].decode_raw(pkts[i], fsz)
                 assert ret[i] == r1, (i, t, ret[i], r1)
                 assert np.array_equal(pcm[i][:r1], p1[:r1]), (i, t)
                 assert int(fr[i]) == refs[i].final_range, (i, t)
