@@ -308,7 +308,7 @@ def main():
         "clocks": sampler.summary(),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": None, "peak_kind": peak_kind,
-                     "kernel": ["opus_plan_kernel", "celt_entropy_kernel", "celt_synth_kernel"][dom],
+                     "kernel": ["plan_silk_kernel", "celt_entropy_kernel", "celt_synth_kernel"][dom],
                      "kernel_ms": {"plan": kern_ms[0], "entropy": kern_ms[1], "synth": kern_ms[2]},
                      "algorithmic_bytes_per_launch": alg_bytes,
                      "note": "integer/latency-bound path: HBM fraction is tiny by construction, see profiles/ for issue-slot utilisation"},

@@ -30,6 +30,9 @@ FS, CH, SPF = 16000, 1, 320
 FIXTURE = os.path.join(ROOT, "tests", "golden", "silk_wb_mono_32k.bit")
 METRIC = "aggregate realtime stream-sec/sec (16k mono SILK decode)"
 UNIT = "stream-seconds/s"
+WORKLOAD = "batched SILK decode: 16384 x 16 kHz mono 32 kbps 20 ms streams (config 4)"
+KERNEL = "silk_decode_kernel"
+NOTE = "step = plan + SILK kernel + (empty) CELT/general kernels; serial per-sample recurrences, latency bound"
 
 
 def main():
@@ -38,7 +41,17 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--streams", type=int, default=16384)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--hybrid", action="store_true",
+                    help="config 4's hybrid set: 48 kHz mono 32 kbps VOIP streams (every packet hybrid fullband 20 ms)")
     args = ap.parse_args()
+    global FS, SPF, FIXTURE, METRIC, WORKLOAD, KERNEL, NOTE
+    if args.hybrid:
+        FS, SPF = 48000, 960
+        FIXTURE = os.path.join(ROOT, "tests", "golden", "hyb_fb_mono_32k.bit")
+        METRIC = "aggregate realtime stream-sec/sec (48k mono hybrid decode)"
+        WORKLOAD = "batched hybrid decode: 16384 x 48 kHz mono 32 kbps 20 ms streams (config 4, hybrid set)"
+        KERNEL = "silk_decode_kernel + celt_entropy_kernel + celt_synth_kernel"
+        NOTE = "step = plan + SILK kernel (SILK layer, thread per stream) + CELT kernels (bands 17.., warp per stream)"
     import torch
     import concentus_b200 as cb
     lib = cb.load()
@@ -122,8 +135,8 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": K, "warmup": W,
         "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "int32/int16 fixed-point",
-        "data": "synthetic: rotations of one reference-encoded 200-packet SILK stream (tests/golden/silk_wb_mono_32k.bit)",
-        "config": {"workload": "batched SILK decode: 16384 x 16 kHz mono 32 kbps 20 ms streams (config 4)",
+        "data": "synthetic: rotations of one reference-encoded stream (tests/golden/%s)" % os.path.basename(FIXTURE),
+        "config": {"workload": WORKLOAD,
                    "streams_per_gpu": n, "frame_ms": 20, "mean_packet_bytes": float(plen.mean()),
                    "l2": "flushed between timed steps (256 MiB write, outside the event pair)"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(n * maxlen + 8 * n),
@@ -131,18 +144,18 @@ def main():
                 "api": "opus_decode_group_flat (host buffers)"},
         "gpu_launches": int(launches), "clocks": sampler.summary(),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_kind": peak_kind, "kernel": "silk_decode_kernel",
+                     "traffic": None, "peak_kind": peak_kind, "kernel": KERNEL,
                      "step_ms": dev_ms / K, "algorithmic_bytes_per_launch": alg_bytes,
-                     "note": "step = plan + (empty) CELT kernels + SILK kernel; serial per-sample recurrences, latency bound"},
+                     "note": NOTE},
     }
     exe = os.path.join(ROOT, "oracle", "_ref", "ref_bench")
     if not args.no_cpu_baseline and os.path.exists(exe):
         cores = os.cpu_count() or 1
         streams_s = 256 * cores
-        out = subprocess.run([exe, FIXTURE, str(FS), str(CH), str(streams_s), "200", str(cores)],
+        out = subprocess.run([exe, FIXTURE, str(FS), str(CH), str(streams_s), str(npk), str(cores)],
                              stdout=subprocess.PIPE, text=True, check=True).stdout.split()
         line["cpu_baseline"] = {"value": float(out[0]) / float(out[1]), "unit": UNIT, "cores": cores, "kind": "reference",
-                                "sample": "%d of 16384 streams x 200 frames (4 s each), one pass" % streams_s}
+                                "sample": "%d of 16384 streams x %d frames, one pass" % (streams_s, npk)}
     print(json.dumps(line))
     bd.close()
 

@@ -24,15 +24,22 @@ def _newest(paths):
 def needs_build():
     if not os.path.exists(LIB):
         return True
-    srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC)]
-    srcs.append(os.path.join(HERE, "..", "include", "opus_b200.h"))
-    return _newest(srcs) > os.path.getmtime(LIB)
+    t = os.path.getmtime(LIB)
+    for src in SOURCES:
+        obj = os.path.join(OBJ, src[:-3] + ".o")
+        if _object_stale(obj, os.path.join(OBJ, src[:-3] + ".d"), os.path.join(CSRC, src)) or os.path.getmtime(obj) > t:
+            return True
+    return False
 
 
 def _deps(dfile):
     """Prerequisites listed in a make-style dependency file written by nvcc -MD."""
     txt = open(dfile).read().replace("\\\n", " ")
-    return [t for t in txt.split(":", 1)[1].split() if os.path.exists(t)]
+    deps = [os.path.join(CSRC, t) for t in txt.split(":", 1)[1].split()]      # nvcc ran with cwd = csrc
+    local = [d for d in deps if os.path.dirname(os.path.abspath(d)) == CSRC]
+    if not local:
+        raise IndexError("no local prerequisites in " + dfile)
+    return [d for d in deps if os.path.exists(d)]
 
 
 def _object_stale(obj, dfile, src):

@@ -7,15 +7,15 @@
 #include "cb_opus_plan.h"
 
 // Kernel A, one stream, one pass.  `pkt` = per-warp staging area for the payload bytes.
+// Two instances: HYB = false takes the CELT-only frames (start band 0, fresh range decoder: the constants
+// fold into the decoder), HYB = true the CELT layer of hybrid frames whose SILK layer the SILK kernel has
+// already written to the PCM row (bands 17.., coder state continued, output accumulated).
+template <bool HYB>
 CB_FN void decode_entropy_pass(EntWork& w, u8* pkt, OpusDecState* st, StreamPlan* pl, FrameSide* side,
                                const u8* data, i32* ret_slot, int pass) {
   const int kind = pl->kind;
-  // decide once per pass who decodes this stream's frame; the SILK and general kernels read it later
-  int route = -1;
-  if (!(pl->ret < 0 || pass >= pl->nframes || kind == CB_PLAN_NONE || kind == CB_PLAN_ZERO)) route = opus_frame_route(st, pl, pass);
-  CB_WSYNC();
-  CB_IF_LANE0 pl->route = route;
-  CB_WSYNC();
+  const int route = pl->route;                       // decided by the SILK kernel at the start of this pass
+  if (HYB != (route == CB_ROUTE_HYBRID)) return;     // the other instance's stream (or nobody's, handled by HYB = false)
   if (pl->ret < 0 || pass >= pl->nframes || kind == CB_PLAN_NONE) {
     side->kind = 0;
     return;
@@ -24,13 +24,28 @@ CB_FN void decode_entropy_pass(EntWork& w, u8* pkt, OpusDecState* st, StreamPlan
     side->kind = 3;
     return;
   }
-  if (route != CB_ROUTE_CELT) {                     // decoded by the SILK kernel or the general kernel
+  if (route != CB_ROUTE_CELT && route != CB_ROUTE_HYBRID) {   // decoded by the SILK kernel or the general kernel
     side->kind = 0;
     return;
   }
+  constexpr bool hybrid = HYB;                     // SILK layer already in the PCM row: bands 17.. accumulate
   const int len = pl->len[pass];
   const int nsamp = pl->nsamp[pass];
-  if (kind == CB_PLAN_PLC || len <= 1) {
+  if (hybrid && (kind == CB_PLAN_PLC || len <= 1)) {
+    // concealment of a hybrid frame: celt_decode_lost with start != 0 is always noise-based
+    int LMp = 0;
+    {
+      int fs48 = nsamp * st->celt.downsample;
+      while ((120 << LMp) < fs48) LMp++;
+    }
+    celt_plc_noise(w, &st->celt, side, LMp, 17, opus_bandwidth_endband(st->bandwidth));
+    CB_WSYNC();
+    side->accum = 1;
+    st->rangeFinal = 0;
+    st->prev_redundancy = 0;
+    return;
+  }
+  if (!hybrid && (kind == CB_PLAN_PLC || len <= 1)) {
     // lost / DTX frame: opus_decode_frame(data=NULL) (opus_decoder.c:246-292, 579-586)
     if (st->prev_mode == 0) {                       // nothing decoded yet: zeros for this frame
       side->kind = 4;
@@ -64,14 +79,20 @@ CB_FN void decode_entropy_pass(EntWork& w, u8* pkt, OpusDecState* st, StreamPlan
   EntFrameCfg cfg;
   cfg.LM = LM;
   cfg.C = st->stream_channels;
-  cfg.start = 0;
+  cfg.start = hybrid ? 17 : 0;
   cfg.end = opus_bandwidth_endband(st->bandwidth);
-  cfg.accum = 0;
-  cfg.rd0 = nullptr;
+  cfg.accum = hybrid ? 1 : 0;
+  cfg.rd0 = hybrid ? reinterpret_cast<const RangeDec*>(pl->rd_save) : nullptr;
+  if (hybrid && st->prev_mode != CB_MODE_HYBRID && st->prev_mode > 0 && !st->prev_redundancy) {
+    CB_WSYNC();
+    CB_IF_LANE0 celt_state_reset(&st->celt, st->celt.channels, st->celt.downsample);   // opus_decoder.c:463-464
+    CB_WSYNC();
+  }
   u32 fr = 0;
   int rc = celt_entropy_decode(w, &st->celt, side, pkt, len, cfg, &fr);
+  CB_WSYNC();
   st->rangeFinal = fr;
-  st->prev_mode = CB_MODE_CELT_ONLY;
+  st->prev_mode = hybrid ? CB_MODE_HYBRID : CB_MODE_CELT_ONLY;
   st->prev_redundancy = 0;
   if (rc < 0) {
     pl->ret = rc;

@@ -3,7 +3,8 @@
 //   opus_general_kernel : 1 warp / stream -- opus_decode_frame in full (cb_opus_general.h): hybrid
 //   packets, CELT<->SILK/hybrid transitions and packets with a redundant CELT frame.  The SILK layer
 //   of such a frame runs on lane 0; the CELT layer, the fades and the gain on the whole warp.
-// Streams whose frame was not routed here leave at once; other batches pay one empty launch.
+// The same launch runs the pitch-based concealment of CELT frames (cb_celt_plc.h), the other rare
+// warp-per-stream path.  Streams with nothing to do here leave at once.
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "cb_opus_general.h"
@@ -20,8 +21,13 @@ opus_general_kernel(OpusDecState* const* states, StreamPlan* plans, FrameSide* s
   if (s >= n) return;
   StreamPlan* pl = &plans[s];
   const int route = pl->route;
-  if (route != CB_ROUTE_GENERAL && route != CB_ROUTE_FINISH) return;
   GenWork& g = *reinterpret_cast<GenWork*>(smem + (size_t)warp * sizeof(GenWork));
+  if (route == CB_ROUTE_CELT) {
+    // pitch-based concealment of a CELT frame, asked for by kernel A (celt_decode_lost, loss_count < 5)
+    if (sides[s].kind == 2) decode_plc_pass(g.pw, states[s], pl, &sides[s], pcm + (size_t)s * pcm_stride, pass);
+    return;
+  }
+  if (route != CB_ROUTE_GENERAL && route != CB_ROUTE_FINISH) return;
   SilkCallWork cw;
   decode_general_pass(g, states[s], pl, &sides[s], data, pcm + (size_t)s * pcm_stride, &ret[s], pass, cw);
 }

@@ -27,6 +27,7 @@ __global__ void opus_plan_kernel(OpusDecState* const* states, const u8* data, co
   ret[s] = pl->ret;
 }
 
+template <bool HYB>
 __global__ void __launch_bounds__(A_WARPS * 32, 7)
 celt_entropy_kernel(OpusDecState* const* states, const u8* data, StreamPlan* plans, FrameSide* sides,
                     i32* ret, int n, int pass, int per_warp_bytes) {
@@ -39,7 +40,7 @@ celt_entropy_kernel(OpusDecState* const* states, const u8* data, StreamPlan* pla
   OpusDecState* st = states[s];
   StreamPlan* pl = &plans[s];
   FrameSide* side = &sides[s];
-  decode_entropy_pass(w, pkt, st, pl, side, data, &ret[s], pass);
+  decode_entropy_pass<HYB>(w, pkt, st, pl, side, data, &ret[s], pass);
 }
 
 __global__ void __launch_bounds__(B_WARPS * 32, 7)
@@ -58,19 +59,6 @@ celt_synth_kernel(OpusDecState* const* states, const StreamPlan* plans, const Fr
   SynWork& w = *reinterpret_cast<SynWork*>(smem + (size_t)warp * sizeof(SynWork));
   i16* row = pcm + (size_t)s * pcm_stride;
   decode_synth_pass(w, st, pl, side, row, c, pass);
-}
-
-__global__ void __launch_bounds__(128)
-celt_plc_kernel(OpusDecState* const* states, const StreamPlan* plans, const FrameSide* sides, i16* pcm,
-                i32 pcm_stride, int n, int pass) {
-  extern __shared__ __align__(16) unsigned char smem[];
-  const int warp = threadIdx.x >> 5;
-  const int s = blockIdx.x * 4 + warp;
-  if (s >= n) return;
-  const FrameSide* side = &sides[s];
-  if (side->kind != 2) return;
-  PlcWork& w = *reinterpret_cast<PlcWork*>(smem + (size_t)warp * sizeof(PlcWork));
-  decode_plc_pass(w, states[s], &plans[s], side, pcm + (size_t)s * pcm_stride, pass);
 }
 
 // Multistream: one thread per multistream decoder plans its elementary streams.
@@ -132,11 +120,11 @@ static int ensure_attrs() {
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return (int)e;
   if (dev < 64 && g_attr_done[dev]) return 0;
-  e = cudaFuncSetAttribute(celt_entropy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  e = cudaFuncSetAttribute(celt_entropy_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  if (e != cudaSuccess) return (int)e;
+  e = cudaFuncSetAttribute(celt_entropy_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
   if (e != cudaSuccess) return (int)e;
   e = cudaFuncSetAttribute(celt_synth_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-  if (e != cudaSuccess) return (int)e;
-  e = cudaFuncSetAttribute(celt_plc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
   if (e != cudaSuccess) return (int)e;
   if (dev < 64) g_attr_done[dev] = 1;
   return 0;
@@ -150,7 +138,12 @@ extern "C" int cbk_launch_entropy(OpusDecState* const* d_states, const u8* d_dat
   if (rc) return rc;
   const int per_warp = (int)cbk_entropy_smem_per_warp(max_payload);
   const size_t smemA = (size_t)per_warp * A_WARPS;
-  celt_entropy_kernel<<<(n + A_WARPS - 1) / A_WARPS, A_WARPS * 32, smemA, stream>>>(
+  celt_entropy_kernel<false><<<(n + A_WARPS - 1) / A_WARPS, A_WARPS * 32, smemA, stream>>>(
+      d_states, d_data, d_plans, d_sides, d_ret, n, pass, per_warp);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return (int)e;
+  // CELT layer of hybrid frames: its warps leave at once in a batch without hybrid streams
+  celt_entropy_kernel<true><<<(n + A_WARPS - 1) / A_WARPS, A_WARPS * 32, smemA, stream>>>(
       d_states, d_data, d_plans, d_sides, d_ret, n, pass, per_warp);
   return (int)cudaGetLastError();
 }
@@ -164,11 +157,6 @@ extern "C" int cbk_launch_synth(OpusDecState* const* d_states, const StreamPlan*
   const int warpsB = n * 2;
   celt_synth_kernel<<<(warpsB + B_WARPS - 1) / B_WARPS, B_WARPS * 32, smemB, stream>>>(
       d_states, d_plans, d_sides, d_pcm, pcm_stride, n, pass);
-  cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) return (int)e;
-  // kernel C: warps whose stream needs no pitch-based concealment exit at once
-  celt_plc_kernel<<<(n + 3) / 4, 128, sizeof(PlcWork) * 4, stream>>>(d_states, d_plans, d_sides, d_pcm, pcm_stride,
-                                                                   n, pass);
   return (int)cudaGetLastError();
 }
 

@@ -278,25 +278,33 @@ CB_HD void opus_plan_stream(OpusDecState* st, StreamPlan* pl, const u8* data, i3
   st->last_packet_duration = pl->ret;
 }
 
-// where frame `pass` of the plan is decoded: 0 CELT kernels (A/B/C), 1 SILK kernel, 2 this file
-#define CB_ROUTE_CELT 0
-#define CB_ROUTE_SILK 1
-#define CB_ROUTE_GENERAL 2
+// Where frame `pass` of the plan is decoded.  The SILK kernel runs first in every pass and stores the
+// decision in the plan; the CELT kernels and the general kernel read it.
+#define CB_ROUTE_CELT 0        // CELT kernels (A/B/C)
+#define CB_ROUTE_SILK 1        // SILK kernel alone
+#define CB_ROUTE_GENERAL 2     // general kernel (cb_opus_general.h): transitions, FEC of hybrid frames, odd sizes
 #define CB_ROUTE_FINISH 3      // SILK kernel decoded the SILK layer and found a redundant CELT frame: general kernel finishes
+#define CB_ROUTE_HYBRID 4      // SILK kernel decodes the SILK layer, then the CELT kernels add bands 17.. on top
 CB_HD int opus_frame_route(const OpusDecState* st, const StreamPlan* pl, int pass) {
   const bool conceal = pl->kind == CB_PLAN_PLC || (pl->len[pass] <= 1);
+  const int prev = st->prev_mode;
+  // the two-kernel hybrid path needs the SILK layer written straight into the PCM row (frames of >= 10 ms,
+  // the reference's celt_accum case) and no output gain
+  const bool split_ok = pl->nsamp[pass] >= st->Fs / 100 && st->decode_gain == 0;
   if (conceal) {
-    if (st->prev_mode == CB_MODE_SILK_ONLY) return CB_ROUTE_SILK;
-    if (st->prev_mode == CB_MODE_HYBRID) return CB_ROUTE_GENERAL;
+    if (prev == CB_MODE_SILK_ONLY) return CB_ROUTE_SILK;
+    if (prev == CB_MODE_HYBRID) return split_ok ? CB_ROUTE_HYBRID : CB_ROUTE_GENERAL;
     return CB_ROUTE_CELT;
   }
-  const int mode = st->mode, prev = st->prev_mode;
+  const int mode = st->mode;
   if (mode == CB_MODE_CELT_ONLY) {
     if (prev == 0 || prev == CB_MODE_CELT_ONLY || st->prev_redundancy) return CB_ROUTE_CELT;
     return CB_ROUTE_GENERAL;
   }
-  if (mode == CB_MODE_SILK_ONLY && (prev == 0 || prev == CB_MODE_SILK_ONLY)) return CB_ROUTE_SILK;
-  return CB_ROUTE_GENERAL;
+  if (prev == CB_MODE_CELT_ONLY) return CB_ROUTE_GENERAL;
+  if (mode == CB_MODE_SILK_ONLY) return prev == CB_MODE_HYBRID ? CB_ROUTE_GENERAL : CB_ROUTE_SILK;
+  if (pl->fec_frame == pass || !split_ok) return CB_ROUTE_GENERAL;
+  return CB_ROUTE_HYBRID;
 }
 
 // opus_multistream_packet_validate (opus-fix/src/opus_multistream_decoder.c:155-183)

@@ -22,9 +22,33 @@ silk_decode_kernel(OpusDecState* const* states, StreamPlan* plans, const u8* dat
   if (s >= n) return;
   OpusDecState* st = states[s];
   StreamPlan* pl = &plans[s];
-  if (pl->route != CB_ROUTE_SILK) return;
   SilkCallWork cw;
   decode_silk_pass(st, pl, data, pcm + (size_t)s * pcm_stride, &ret[s], pass, cw);
+}
+
+// The first pass of a batch call: packet parsing / frame plan (opus_plan_stream) and the SILK pass of
+// frame 0 in one launch (both are one thread per stream).
+__global__ void __launch_bounds__(S_THREADS)
+plan_silk_kernel(OpusDecState* const* states, const u8* data, const i32* offs, const i32* lens, const i32* fec,
+                 int frame_size, StreamPlan* plans, i16* pcm, i32 pcm_stride, i32* ret, int n) {
+  const int s = blockIdx.x * S_THREADS + threadIdx.x;
+  if (s >= n) return;
+  OpusDecState* st = states[s];
+  StreamPlan* pl = &plans[s];
+  opus_plan_stream(st, pl, data, offs[s], lens[s], frame_size, fec ? fec[s] : 0, 0, nullptr);
+  ret[s] = pl->ret;
+  SilkCallWork cw;
+  decode_silk_pass(st, pl, data, pcm + (size_t)s * pcm_stride, &ret[s], 0, cw);
+}
+
+extern "C" int cbk_launch_plan_silk(OpusDecState* const* d_states, const u8* d_data, const i32* d_off, const i32* d_len,
+                                    const i32* d_fec, int frame_size, StreamPlan* d_plans, i16* d_pcm, i32 pcm_stride,
+                                    i32* d_ret, int n, cudaStream_t stream) {
+  if (n <= 0) return 0;
+  plan_silk_kernel<<<(n + S_THREADS - 1) / S_THREADS, S_THREADS, 0, stream>>>(d_states, d_data, d_off, d_len, d_fec,
+                                                                               frame_size, d_plans, d_pcm, pcm_stride,
+                                                                               d_ret, n);
+  return (int)cudaGetLastError();
 }
 
 extern "C" int cbk_launch_silk(OpusDecState* const* d_states, StreamPlan* d_plans, const u8* d_data, i16* d_pcm,

@@ -10,7 +10,15 @@
 
 CB_FN void decode_silk_pass(OpusDecState* st, StreamPlan* pl, const u8* data, i16* row, i32* ret_slot, int pass,
                             SilkCallWork& cw) {
-  if (pl->route != CB_ROUTE_SILK) return;
+  {
+    // first kernel of the pass: decide who decodes this stream's frame
+    const int kind = pl->kind;
+    int route = -1;
+    if (!(pl->ret < 0 || pass >= pl->nframes || kind == CB_PLAN_NONE || kind == CB_PLAN_ZERO)) route = opus_frame_route(st, pl, pass);
+    pl->route = route;
+    if (route != CB_ROUTE_SILK && route != CB_ROUTE_HYBRID) return;
+  }
+  const bool hybrid = pl->route == CB_ROUTE_HYBRID;
   const int Fs = st->Fs, CC = st->channels;
   const int F20 = Fs / 50, F10 = F20 >> 1;
   const int decode_fec = pl->fec_frame == pass;
@@ -28,7 +36,8 @@ CB_FN void decode_silk_pass(OpusDecState* st, StreamPlan* pl, const u8* data, i1
   sd.ctl_payloadSize_ms = cb_imax(10, 1000 * audiosize / Fs);
   if (have_data) {
     sd.ctl_nChannelsInternal = st->stream_channels;
-    if (st->bandwidth == CB_BW_NARROWBAND) sd.ctl_internalSampleRate = 8000;
+    if (hybrid) sd.ctl_internalSampleRate = 16000;
+    else if (st->bandwidth == CB_BW_NARROWBAND) sd.ctl_internalSampleRate = 8000;
     else if (st->bandwidth == CB_BW_MEDIUMBAND) sd.ctl_internalSampleRate = 12000;
     else sd.ctl_internalSampleRate = 16000;
   }
@@ -58,6 +67,19 @@ CB_FN void decode_silk_pass(OpusDecState* st, StreamPlan* pl, const u8* data, i1
   } while (decoded_samples < frame_size);
   if (!direct)
     for (int i = 0; i < frame_size * CC; i++) pcm[i] = small[i];
+  if (hybrid) {
+    // the CELT kernels continue from this coder state with bands 17.. accumulated onto the SILK output;
+    // a hybrid packet flags its redundant CELT frame explicitly (opus_decoder.c:412-440)
+    if (have_data) {
+      const RangeDec before = rd;
+      int red = 0;
+      if ((int)rd_tell(rd) + 37 <= 8 * len) red = rd_bit_logp(rd, 12);
+      const u32* src = (const u32*)(red ? &before : &rd);
+      for (int i = 0; i < (int)(sizeof(RangeDec) / 4); i++) pl->rd_save[i] = src[i];
+      if (red) pl->route = CB_ROUTE_FINISH;
+    }
+    return;
+  }
   // a SILK-only packet with >= 17 bits left over carries a redundant CELT frame (opus_decoder.c:412-440)
   if (!decode_fec && have_data && (int)rd_tell(rd) + 17 <= 8 * len) {
     // the general kernel (cb_opus_general.h) decodes the CELT frame and does the cross-fade: hand over

@@ -133,8 +133,8 @@ struct alignas(16) StreamPlan {
   i32 kind;
   i32 total_samples;        // samples per channel covered by the plan
   i32 fec_frame;            // index of the frame decoded from in-band FEC (lost_flag 2), or -1
-  i32 route;                // who decodes the current pass's frame (CB_ROUTE_*), set by kernel A at pass start
-  u32 rd_save[16];          // range-decoder state handed from the SILK kernel to the general kernel (late redundancy)
+  i32 route;                // who decodes the current pass's frame (CB_ROUTE_*), set by the SILK kernel at pass start
+  alignas(8) u32 rd_save[16];  // range-decoder state after the SILK layer, handed to the CELT / general kernel
   i32 off[CB_MAX_FRAMES];   // payload offset in the arena
   i16 len[CB_MAX_FRAMES];   // payload bytes (<=1 means "conceal this frame")
   i16 nsamp[CB_MAX_FRAMES]; // samples per channel produced (API rate)

@@ -335,10 +335,16 @@ void opus_decoder_group_destroy(OpusDecoderGroup* g) {
 // Queue the decode passes (kernels A, B, C per frame index) for a group whose plans are already on
 // the device.  No synchronisation.
 static int group_enqueue_passes(OpusDecoderGroup* g, const u8* d_data, i16* d_pcm, i32 pcm_stride, i32* d_ret,
-                                int passes, int max_packet_bytes, cudaStream_t stream) {
+                                int passes, int max_packet_bytes, cudaStream_t stream, bool silk0_done = false) {
   int rc = 0;
   for (int p = 0; p < passes; p++) {
-    {
+    // SILK kernel first: it also decides, per stream, which kernels own this pass's frame
+    rc = 0;
+    if (p > 0 || !silk0_done) {
+      rc = cbk_launch_silk(g->d_states, g->d_plans, d_data, d_pcm, pcm_stride, d_ret, g->n, p, stream);
+      g_launches += 1;
+    }
+    if (!rc) {
       ProfScope ps(stream, 1);
       rc = cbk_launch_entropy(g->d_states, d_data, g->d_plans, g->d_sides, d_ret, g->n, p, max_packet_bytes, stream);
     }
@@ -346,9 +352,8 @@ static int group_enqueue_passes(OpusDecoderGroup* g, const u8* d_data, i16* d_pc
       ProfScope ps(stream, 2);
       rc = cbk_launch_synth(g->d_states, g->d_plans, g->d_sides, d_pcm, pcm_stride, g->n, p, stream);
     }
-    if (!rc) rc = cbk_launch_silk(g->d_states, g->d_plans, d_data, d_pcm, pcm_stride, d_ret, g->n, p, stream);
     if (!rc) rc = cbk_launch_general(g->d_states, g->d_plans, g->d_sides, d_data, d_pcm, pcm_stride, d_ret, g->n, p, stream);
-    g_launches += 5;
+    g_launches += 4;
     if (rc) { fprintf(stderr, "[opus_b200] pass launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
   }
   return OPUS_OK;
@@ -361,11 +366,12 @@ static int group_enqueue(OpusDecoderGroup* g, const u8* d_data, const i32* d_off
   int rc;
   {
     ProfScope ps(stream, 0);
-    rc = cbk_launch_plan(g->d_states, d_data, d_off, d_len, d_fec, frame_size, g->d_plans, d_ret, g->n, stream);
+    rc = cbk_launch_plan_silk(g->d_states, d_data, d_off, d_len, d_fec, frame_size, g->d_plans, d_pcm, pcm_stride, d_ret,
+                              g->n, stream);
   }
   g_launches += 1;
   if (rc) { fprintf(stderr, "[opus_b200] plan launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
-  return group_enqueue_passes(g, d_data, d_pcm, pcm_stride, d_ret, passes, max_packet_bytes, stream);
+  return group_enqueue_passes(g, d_data, d_pcm, pcm_stride, d_ret, passes, max_packet_bytes, stream, true);
 }
 
 int opus_decode_group_device(OpusDecoderGroup* g, const unsigned char* d_data, const opus_int32* d_offsets,
