@@ -109,20 +109,36 @@ def main():
     launches = lib.opus_b200_launch_count() - launches0
     dev_ms = float(sum(a.elapsed_time(b) for a, b in ev))
     assert int((d_ret != SPF).sum().item()) == 0
-    # e2e
-    h_pcm = np.zeros(n * SPF * CH, dtype=np.int16)
-    h_ret = np.zeros(n, dtype=np.int32)
-    e0 = None
-    for k in range(K + 3):
-        if k == 3:
-            torch.cuda.synchronize()
-            e0 = time.perf_counter()
-        a, l = steps_data[t]
-        rc = lib.opus_decode_group_flat(bd._g, a.ctypes.data, a.size, offs.ctypes.data, l.ctypes.data, h_pcm.ctypes.data,
-                                        SPF * CH, SPF, None, h_ret.ctypes.data)
-        assert rc == 0 and (h_ret == SPF).all()
+    # e2e: page-locked host packets in, page-locked host PCM out, every step; (a) one synchronous call per step
+    # (opus_decode_group_flat), (b) the pipelined form (opus_decode_group_submit/_wait, two calls in flight)
+    h_pcm = [torch.zeros(n * SPF * CH, dtype=torch.int16).pin_memory() for _ in range(3)]
+    h_ret = [torch.zeros(n, dtype=torch.int32).pin_memory() for _ in range(3)]
+    h_off = torch.from_numpy(offs).pin_memory()
+    h_in = [(torch.from_numpy(a).pin_memory(), torch.from_numpy(l).pin_memory()) for a, l in steps_data]
+
+    def call(fn, t, slot):
+        a, l = h_in[t % len(h_in)]
+        return fn(bd._g, a.data_ptr(), a.numel(), h_off.data_ptr(), l.data_ptr(), h_pcm[slot].data_ptr(), SPF * CH, SPF,
+                  None, h_ret[slot].data_ptr())
+
+    for k in range(3):
+        assert call(lib.opus_decode_group_flat, t, 0) == 0
         t += 1
+    torch.cuda.synchronize()
+    s0 = time.perf_counter()
+    for k in range(K):
+        assert call(lib.opus_decode_group_flat, t, 0) == 0 and bool((h_ret[0] == SPF).all())
+        t += 1
+    sync_s = time.perf_counter() - s0
+    e0 = time.perf_counter()
+    for k in range(K):
+        assert call(lib.opus_decode_group_submit, t, k % 3) == 0
+        if k >= 2:
+            assert bool((h_ret[(k - 2) % 3] == SPF).all())
+        t += 1
+    assert lib.opus_decode_group_wait(bd._g) == 0
     e1 = time.perf_counter()
+    assert all(bool((r == SPF).all()) for r in h_ret)
     sampler.stop_flag = True
     sampler.join(timeout=2)
     units = n * SPF / FS
@@ -141,7 +157,8 @@ def main():
                    "l2": "flushed between timed steps (256 MiB write, outside the event pair)"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(n * maxlen + 8 * n),
                 "d2h_bytes_per_step": int(n * SPF * CH * 2 + 4 * n), "ms_per_step": 1e3 * (e1 - e0) / K,
-                "api": "opus_decode_group_flat (host buffers)"},
+                "api": "opus_decode_group_submit/_wait (pinned host buffers, two calls in flight)",
+                "synchronous_call_value": units * K / sync_s, "synchronous_call_api": "opus_decode_group_flat"},
         "gpu_launches": int(launches), "clocks": sampler.summary(),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": None, "peak_kind": peak_kind, "kernel": KERNEL,

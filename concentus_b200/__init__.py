@@ -44,6 +44,7 @@ EXPORTS = [
     "opus_packet_get_samples_per_frame", "opus_packet_get_nb_samples", "opus_decoder_get_nb_samples",
     "opus_packet_parse", "opus_decode_batch", "opus_decode_batch_flat", "opus_decoder_group_create",
     "opus_decoder_group_destroy", "opus_decode_group_flat", "opus_decode_group_device",
+    "opus_decode_group_submit", "opus_decode_group_wait", "opus_encode_group_submit", "opus_encode_group_wait",
     "opus_decoder_get_final_range_batch", "opus_b200_synchronize", "opus_b200_launch_count",
     "opus_b200_profile_begin", "opus_b200_profile_end", "opus_decode_batch_device_static",
     "opus_multistream_decoder_get_size", "opus_multistream_decoder_create", "opus_multistream_decode",
@@ -95,6 +96,8 @@ def load():
     lib.opus_decoder_group_destroy.argtypes = [vp]
     lib.opus_decoder_group_destroy.restype = None
     lib.opus_decode_group_flat.argtypes = [vp, vp, ctypes.c_int32, vp, vp, vp, ctypes.c_int32, ctypes.c_int, vp, vp]
+    lib.opus_decode_group_submit.argtypes = [vp, vp, ctypes.c_int32, vp, vp, vp, ctypes.c_int32, ctypes.c_int, vp, vp]
+    lib.opus_decode_group_wait.argtypes = [vp]
     lib.opus_decode_group_device.argtypes = [vp, vp, vp, vp, vp, ctypes.c_int32, ctypes.c_int, vp, vp,
                                              ctypes.c_int, ctypes.c_int, vp]
     lib.opus_decode_batch_device_static.argtypes = [vp, ctypes.c_int, vp, vp, vp, vp, ctypes.c_int32, ctypes.c_int,
@@ -125,6 +128,8 @@ def load():
     lib.opus_encoder_group_destroy.argtypes = [vp]
     lib.opus_encoder_group_destroy.restype = None
     lib.opus_encode_group_flat.argtypes = [vp, vp, ctypes.c_int, vp, ctypes.c_int32, vp]
+    lib.opus_encode_group_submit.argtypes = [vp, vp, ctypes.c_int, vp, ctypes.c_int32, vp]
+    lib.opus_encode_group_wait.argtypes = [vp]
     lib.opus_encode_group_device.argtypes = [vp, vp, ctypes.c_int, vp, ctypes.c_int32, vp]
     lib.opus_encoder_get_final_range_batch.argtypes = [vp, ctypes.c_int, vp]
     lib.opus_b200_encode_profile_end.argtypes = [vp, vp]
@@ -268,6 +273,22 @@ class OpusBatchDecoder(object):
         if rc != OPUS_OK:
             raise OpusError(rc, "opus_decode_group_flat")
         return ret, pcm
+
+    def submit_flat(self, arena, nbytes, offs, lens, frame_size, pcm, ret, fec=None):
+        """Pipelined form (opus_decode_group_submit): queues the call and returns.  The caller owns every
+        array and keeps it alive and unchanged until wait(); pcm / ret are filled by then."""
+        fec_a = None if fec is None else np.ascontiguousarray(fec, dtype=np.int32)
+        rc = load().opus_decode_group_submit(self._g, _ptr(arena), nbytes, _ptr(offs), _ptr(lens), _ptr(pcm),
+                                             frame_size * self.channels, frame_size, _ptr(fec_a), _ptr(ret))
+        if rc != OPUS_OK:
+            raise OpusError(rc, "opus_decode_group_submit")
+        self._keep = (getattr(self, "_keep", ()) + ((arena, offs, lens, fec_a, pcm, ret),))[-2:]
+
+    def wait(self):
+        rc = load().opus_decode_group_wait(self._g)
+        if rc != OPUS_OK:
+            raise OpusError(rc, "opus_decode_group_wait")
+        self._keep = ()
 
     def final_ranges(self):
         out = np.zeros(self.n, dtype=np.uint32)
@@ -452,6 +473,22 @@ class OpusBatchEncoder(object):
         if rc < 0:
             raise OpusError(rc, "opus_encode_group_flat")
         return data, lens
+
+    def submit(self, pcm, frame_size, data, lens):
+        """Pipelined form (opus_encode_group_submit): pcm int16 [n, frame_size*channels], data uint8
+        [n, max_data_bytes], lens int32 [n], all caller-owned and kept alive until wait()."""
+        assert pcm.dtype == np.int16 and pcm.flags.c_contiguous and pcm.shape == (self.n, frame_size * self.channels)
+        assert data.dtype == np.uint8 and data.flags.c_contiguous and data.shape[0] == self.n
+        rc = load().opus_encode_group_submit(self._g, _ptr(pcm), frame_size, _ptr(data), data.shape[1], _ptr(lens))
+        if rc < 0:
+            raise OpusError(rc, "opus_encode_group_submit")
+        self._keep = (getattr(self, "_keep", ()) + ((pcm, data, lens),))[-2:]
+
+    def wait(self):
+        rc = load().opus_encode_group_wait(self._g)
+        if rc < 0:
+            raise OpusError(rc, "opus_encode_group_wait")
+        self._keep = ()
 
     def encode_device(self, d_pcm_ptr, frame_size, d_data_ptr, max_data_bytes, d_len_ptr):
         """Raw device pointers (e.g. torch tensors' data_ptr()); asynchronous."""

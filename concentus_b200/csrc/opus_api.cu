@@ -112,6 +112,20 @@ struct OpusDecoder {
   OpusDecoderGroup* self_group;   // group of one, created on first opus_decode()
 };
 
+// Two-deep pipeline behind opus_decode_group_submit/_wait: while the kernels of one call run, the PCM of
+// the previous call drains to the host and the packets of the next one come in (separate copy streams).
+struct DecPipeSlot {
+  GrowBuf d_pkt, d_pcm, d_i32, h_i32;        // d_i32 = offsets, lengths, fec flags, return values (4n)
+  cudaEvent_t in_done = nullptr, k_done = nullptr, out_done = nullptr;
+  bool busy = false;
+  DecPipeSlot() { h_i32.pinned = true; }
+};
+struct DecPipe {
+  cudaStream_t s_in = nullptr, s_out = nullptr;
+  DecPipeSlot slot[2];
+  unsigned long long seq = 0;
+};
+
 struct OpusDecoderGroup {
   int magic;
   int n, device;
@@ -122,6 +136,7 @@ struct OpusDecoderGroup {
   FrameSide* d_sides;
   i32* d_ret;                  // n
   i32* d_maxframes;            // scratch for plan read-back (unused for now)
+  DecPipe* pipe;               // created by the first opus_decode_group_submit
 };
 
 extern "C" {
@@ -272,8 +287,27 @@ int opus_packet_parse(const unsigned char* data, opus_int32 len, unsigned char* 
 }
 
 // ---- groups --------------------------------------------------------------------------------
+static void pipe_free(DecPipe* p) {
+  if (!p) return;
+  for (DecPipeSlot& sl : p->slot) {
+    if (sl.busy && sl.out_done) cudaEventSynchronize(sl.out_done);
+    if (sl.d_pkt.p) cudaFree(sl.d_pkt.p);
+    if (sl.d_pcm.p) cudaFree(sl.d_pcm.p);
+    if (sl.d_i32.p) cudaFree(sl.d_i32.p);
+    if (sl.h_i32.p) cudaFreeHost(sl.h_i32.p);
+    if (sl.in_done) cudaEventDestroy(sl.in_done);
+    if (sl.k_done) cudaEventDestroy(sl.k_done);
+    if (sl.out_done) cudaEventDestroy(sl.out_done);
+  }
+  if (p->s_in) cudaStreamDestroy(p->s_in);
+  if (p->s_out) cudaStreamDestroy(p->s_out);
+  delete p;
+}
+
 static void group_free(OpusDecoderGroup* g) {
   if (!g) return;
+  pipe_free(g->pipe);
+  g->pipe = nullptr;
   if (g->d_states) cudaFree(g->d_states);
   if (g->d_plans) cudaFree(g->d_plans);
   if (g->d_sides) cudaFree(g->d_sides);
@@ -456,6 +490,86 @@ int opus_decode_group_flat(OpusDecoderGroup* g, const unsigned char* data, opus_
   CUDA_OK(cudaMemcpyAsync(pcm, c->d_pcm.p, pcm_bytes, cudaMemcpyDeviceToHost, s));
   CUDA_OK(cudaMemcpyAsync(ret, g->d_ret, n * sizeof(i32), cudaMemcpyDeviceToHost, s));
   CUDA_OK(cudaStreamSynchronize(s));
+  return OPUS_OK;
+}
+
+// Asynchronous form of opus_decode_group_flat: returns once the copies and kernels are queued.  `pcm` and
+// `ret` are filled when opus_decode_group_wait() returns; `data`, `offsets`, `len`, `decode_fec` are read
+// before this call returns only if they are pageable -- keep all buffers alive (and, for the copies to
+// overlap with the kernels, page-locked) until the wait.  At most two calls are in flight per group; a
+// third submit first waits for the oldest.  Calls on one group execute in submission order.
+int opus_decode_group_submit(OpusDecoderGroup* g, const unsigned char* data, opus_int32 data_bytes,
+                             const opus_int32* offsets, const opus_int32* len, opus_int16* pcm,
+                             opus_int32 pcm_stride, int frame_size, const int* decode_fec, int* ret) {
+  if (!g || g->magic != kMagic || !offsets || !len || !pcm || !ret) return OPUS_BAD_ARG;
+  if (data_bytes < 0 || (data_bytes > 0 && !data) || frame_size <= 0) return OPUS_BAD_ARG;
+  const int n = g->n;
+  int maxch = 1;
+  for (int i = 0; i < n; i++) {
+    if (g->members[i]->channels > maxch) maxch = g->members[i]->channels;
+    if (offsets[i] >= 0 && len[i] > 0 && (offsets[i] + (long long)len[i] > data_bytes)) return OPUS_BAD_ARG;
+  }
+  if (pcm_stride < frame_size * maxch) return OPUS_BAD_ARG;
+  std::lock_guard<std::mutex> lk(g_mu);
+  CUDA_OK(cudaSetDevice(g->device));
+  int err = 0;
+  DevCtx* c = ctx_for_current_device(&err);
+  if (!c) return err;
+  if (!g->pipe) {
+    DecPipe* p = new DecPipe();
+    bool ok = cudaStreamCreateWithFlags(&p->s_in, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&p->s_out, cudaStreamNonBlocking) == cudaSuccess;
+    for (DecPipeSlot& sl : p->slot)
+      ok = ok && cudaEventCreateWithFlags(&sl.in_done, cudaEventDisableTiming) == cudaSuccess &&
+           cudaEventCreateWithFlags(&sl.k_done, cudaEventDisableTiming) == cudaSuccess &&
+           cudaEventCreateWithFlags(&sl.out_done, cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) { pipe_free(p); return OPUS_ALLOC_FAIL; }
+    g->pipe = p;
+  }
+  DecPipe* p = g->pipe;
+  DecPipeSlot& sl = p->slot[p->seq & 1];
+  if (sl.busy) { CUDA_OK(cudaEventSynchronize(sl.out_done)); sl.busy = false; }
+  int max_len = 0;
+  const int passes = scan_passes(data, offsets, len, decode_fec, n, frame_size, g->Fs, &max_len);
+  const size_t pcm_bytes = (size_t)n * pcm_stride * sizeof(i16);
+  const size_t in_bytes = (size_t)n * 3 * sizeof(i32);
+  if (sl.d_pkt.reserve((size_t)data_bytes + 16) || sl.d_pcm.reserve(pcm_bytes) || sl.d_i32.reserve((size_t)n * 4 * sizeof(i32)) ||
+      sl.h_i32.reserve(in_bytes))
+    return OPUS_ALLOC_FAIL;
+  i32* h_i = (i32*)sl.h_i32.p;
+  memcpy(h_i, offsets, n * sizeof(i32));
+  memcpy(h_i + n, len, n * sizeof(i32));
+  if (decode_fec) memcpy(h_i + 2 * n, decode_fec, n * sizeof(i32));
+  else memset(h_i + 2 * n, 0, n * sizeof(i32));
+  i32* d_i = (i32*)sl.d_i32.p;
+  if (data_bytes > 0) CUDA_OK(cudaMemcpyAsync(sl.d_pkt.p, data, data_bytes, cudaMemcpyHostToDevice, p->s_in));
+  CUDA_OK(cudaMemcpyAsync(d_i, h_i, in_bytes, cudaMemcpyHostToDevice, p->s_in));
+  CUDA_OK(cudaEventRecord(sl.in_done, p->s_in));
+  cudaStream_t s = c->stream;
+  CUDA_OK(cudaStreamWaitEvent(s, sl.in_done, 0));
+  int rc = group_enqueue(g, (const u8*)sl.d_pkt.p, d_i, d_i + n, (i16*)sl.d_pcm.p, pcm_stride, frame_size, d_i + 2 * n,
+                         d_i + 3 * n, passes, max_len, s);
+  if (rc != OPUS_OK) return rc;
+  CUDA_OK(cudaEventRecord(sl.k_done, s));
+  CUDA_OK(cudaStreamWaitEvent(p->s_out, sl.k_done, 0));
+  CUDA_OK(cudaMemcpyAsync(pcm, sl.d_pcm.p, pcm_bytes, cudaMemcpyDeviceToHost, p->s_out));
+  CUDA_OK(cudaMemcpyAsync(ret, d_i + 3 * n, n * sizeof(i32), cudaMemcpyDeviceToHost, p->s_out));
+  CUDA_OK(cudaEventRecord(sl.out_done, p->s_out));
+  sl.busy = true;
+  p->seq++;
+  return OPUS_OK;
+}
+
+// Wait for every call submitted on this group; their pcm / ret buffers are complete afterwards.
+int opus_decode_group_wait(OpusDecoderGroup* g) {
+  if (!g || g->magic != kMagic) return OPUS_BAD_ARG;
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!g->pipe) return OPUS_OK;
+  CUDA_OK(cudaSetDevice(g->device));
+  for (int k = 0; k < 2; k++) {
+    DecPipeSlot& sl = g->pipe->slot[(g->pipe->seq + k) & 1];     // oldest first
+    if (sl.busy) { CUDA_OK(cudaEventSynchronize(sl.out_done)); sl.busy = false; }
+  }
   return OPUS_OK;
 }
 

@@ -44,6 +44,20 @@ struct OpusEncoder {
   OpusEncoderGroup* self_group;   // group of one, created on first opus_encode()
 };
 
+// Two-deep pipeline behind opus_encode_group_submit/_wait (copies on their own streams, see opus_api.cu)
+struct EncPipeSlot {
+  i16* d_pcm; size_t d_pcm_cap;
+  u8* d_data; size_t d_data_cap;
+  i32* d_len;
+  cudaEvent_t in_done, k_done, out_done;
+  bool busy;
+};
+struct EncPipe {
+  cudaStream_t s_in, s_out;
+  EncPipeSlot slot[2];
+  unsigned long long seq;
+};
+
 struct OpusEncoderGroup {
   int magic;
   int n, device;
@@ -58,6 +72,7 @@ struct OpusEncoderGroup {
   i16* h_pcm; size_t h_pcm_cap;   // pinned
   u8* h_data; size_t h_data_cap;  // pinned
   i32* h_len;                     // pinned, n
+  EncPipe* pipe;                  // created by the first opus_encode_group_submit
 };
 
 namespace {
@@ -186,8 +201,24 @@ OpusEncoderGroup* opus_encoder_group_create(OpusEncoder* const* st, int n, int* 
   return g;
 }
 
+static void enc_pipe_free(EncPipe* p) {
+  if (!p) return;
+  for (EncPipeSlot& sl : p->slot) {
+    if (sl.busy && sl.out_done) cudaEventSynchronize(sl.out_done);
+    cudaFree(sl.d_pcm); cudaFree(sl.d_data); cudaFree(sl.d_len);
+    if (sl.in_done) cudaEventDestroy(sl.in_done);
+    if (sl.k_done) cudaEventDestroy(sl.k_done);
+    if (sl.out_done) cudaEventDestroy(sl.out_done);
+  }
+  if (p->s_in) cudaStreamDestroy(p->s_in);
+  if (p->s_out) cudaStreamDestroy(p->s_out);
+  free(p);
+}
+
 void opus_encoder_group_destroy(OpusEncoderGroup* g) {
   if (!valid(g)) return;
+  enc_pipe_free(g->pipe);
+  g->pipe = nullptr;
   cudaFree(g->d_states); cudaFree(g->d_scratch); cudaFree(g->d_len);
   cudaFree(g->d_pcm); cudaFree(g->d_data);
   cudaFreeHost(g->h_pcm); cudaFreeHost(g->h_data); cudaFreeHost(g->h_len);
@@ -224,17 +255,71 @@ int opus_encode_group_flat(OpusEncoderGroup* g, const opus_int16* pcm, int frame
   int rc;
   if ((rc = grow_dev((void**)&g->d_pcm, &g->d_pcm_cap, pcm_bytes)) != OPUS_OK) return rc;
   if ((rc = grow_dev((void**)&g->d_data, &g->d_data_cap, data_bytes)) != OPUS_OK) return rc;
-  if ((rc = grow_pinned((void**)&g->h_pcm, &g->h_pcm_cap, pcm_bytes)) != OPUS_OK) return rc;
-  if ((rc = grow_pinned((void**)&g->h_data, &g->h_data_cap, data_bytes)) != OPUS_OK) return rc;
-  memcpy(g->h_pcm, pcm, pcm_bytes);
-  CUDA_OK(cudaMemcpyAsync(g->d_pcm, g->h_pcm, pcm_bytes, cudaMemcpyHostToDevice, stream));
+  // straight from / to the caller's buffers: page-locked ones go by DMA, pageable ones through the driver's staging
+  CUDA_OK(cudaMemcpyAsync(g->d_pcm, pcm, pcm_bytes, cudaMemcpyHostToDevice, stream));
   rc = group_launch(g, g->d_pcm, (i32)row, frame_size, g->d_data, max_data_bytes, max_data_bytes, g->d_len, stream);
   if (rc != OPUS_OK) return rc;
-  CUDA_OK(cudaMemcpyAsync(g->h_data, g->d_data, data_bytes, cudaMemcpyDeviceToHost, stream));
-  CUDA_OK(cudaMemcpyAsync(g->h_len, g->d_len, sizeof(i32) * g->n, cudaMemcpyDeviceToHost, stream));
+  CUDA_OK(cudaMemcpyAsync(data, g->d_data, data_bytes, cudaMemcpyDeviceToHost, stream));
+  CUDA_OK(cudaMemcpyAsync(out_len, g->d_len, sizeof(i32) * g->n, cudaMemcpyDeviceToHost, stream));
   CUDA_OK(cudaStreamSynchronize(stream));
-  memcpy(data, g->h_data, data_bytes);
-  memcpy(out_len, g->h_len, sizeof(i32) * g->n);
+  return OPUS_OK;
+}
+
+// Asynchronous form of opus_encode_group_flat: returns once copies and kernel are queued; `data` and
+// `out_len` are complete when opus_encode_group_wait() returns.  Keep `pcm`, `data`, `out_len` alive (and,
+// for the copies to overlap with the kernel, page-locked) until then.  At most two calls are in flight per
+// group; a third submit first waits for the oldest.  Calls on one group execute in submission order.
+int opus_encode_group_submit(OpusEncoderGroup* g, const opus_int16* pcm, int frame_size, unsigned char* data,
+                             opus_int32 max_data_bytes, opus_int32* out_len) {
+  if (!valid(g) || !pcm || !data || !out_len || frame_size <= 0 || max_data_bytes <= 0) return OPUS_BAD_ARG;
+  if (g->channels < 0) return OPUS_BAD_ARG;
+  int err = 0;
+  cudaStream_t stream = opusb_internal_stream(&err);
+  if (!stream) return err;
+  if (!g->pipe) {
+    EncPipe* p = (EncPipe*)calloc(1, sizeof(EncPipe));
+    if (!p) return OPUS_ALLOC_FAIL;
+    bool ok = cudaStreamCreateWithFlags(&p->s_in, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&p->s_out, cudaStreamNonBlocking) == cudaSuccess;
+    for (EncPipeSlot& sl : p->slot)
+      ok = ok && cudaEventCreateWithFlags(&sl.in_done, cudaEventDisableTiming) == cudaSuccess &&
+           cudaEventCreateWithFlags(&sl.k_done, cudaEventDisableTiming) == cudaSuccess &&
+           cudaEventCreateWithFlags(&sl.out_done, cudaEventDisableTiming) == cudaSuccess &&
+           cudaMalloc((void**)&sl.d_len, sizeof(i32) * g->n) == cudaSuccess;
+    if (!ok) { enc_pipe_free(p); return OPUS_ALLOC_FAIL; }
+    g->pipe = p;
+  }
+  EncPipe* p = g->pipe;
+  EncPipeSlot& sl = p->slot[p->seq & 1];
+  if (sl.busy) { CUDA_OK(cudaEventSynchronize(sl.out_done)); sl.busy = false; }
+  const size_t row = (size_t)frame_size * g->channels;
+  const size_t pcm_bytes = row * sizeof(i16) * g->n, data_bytes = (size_t)max_data_bytes * g->n;
+  int rc;
+  if ((rc = grow_dev((void**)&sl.d_pcm, &sl.d_pcm_cap, pcm_bytes)) != OPUS_OK) return rc;
+  if ((rc = grow_dev((void**)&sl.d_data, &sl.d_data_cap, data_bytes)) != OPUS_OK) return rc;
+  CUDA_OK(cudaMemcpyAsync(sl.d_pcm, pcm, pcm_bytes, cudaMemcpyHostToDevice, p->s_in));
+  CUDA_OK(cudaEventRecord(sl.in_done, p->s_in));
+  CUDA_OK(cudaStreamWaitEvent(stream, sl.in_done, 0));
+  rc = group_launch(g, sl.d_pcm, (i32)row, frame_size, sl.d_data, max_data_bytes, max_data_bytes, sl.d_len, stream);
+  if (rc != OPUS_OK) return rc;
+  CUDA_OK(cudaEventRecord(sl.k_done, stream));
+  CUDA_OK(cudaStreamWaitEvent(p->s_out, sl.k_done, 0));
+  CUDA_OK(cudaMemcpyAsync(data, sl.d_data, data_bytes, cudaMemcpyDeviceToHost, p->s_out));
+  CUDA_OK(cudaMemcpyAsync(out_len, sl.d_len, sizeof(i32) * g->n, cudaMemcpyDeviceToHost, p->s_out));
+  CUDA_OK(cudaEventRecord(sl.out_done, p->s_out));
+  sl.busy = true;
+  p->seq++;
+  return OPUS_OK;
+}
+
+// Wait for every call submitted on this group.
+int opus_encode_group_wait(OpusEncoderGroup* g) {
+  if (!valid(g)) return OPUS_BAD_ARG;
+  if (!g->pipe) return OPUS_OK;
+  for (int k = 0; k < 2; k++) {
+    EncPipeSlot& sl = g->pipe->slot[(g->pipe->seq + k) & 1];     // oldest first
+    if (sl.busy) { CUDA_OK(cudaEventSynchronize(sl.out_done)); sl.busy = false; }
+  }
   return OPUS_OK;
 }
 

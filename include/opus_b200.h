@@ -113,6 +113,18 @@ int opus_decode_group_flat(OpusDecoderGroup *grp, const unsigned char *data, opu
                            const opus_int32 *offsets, const opus_int32 *len, opus_int16 *pcm,
                            opus_int32 pcm_stride, int frame_size, const int *decode_fec, int *ret);
 
+/* Pipelined host form.  opus_decode_group_submit() queues the host->device copy of the packets, the
+ * kernels and the device->host copy of PCM + return values on separate streams and returns; up to two calls
+ * per group are in flight (a third submit waits for the oldest), so the copies of one call overlap with the
+ * kernels of its neighbours.  pcm / ret are complete after opus_decode_group_wait().  All buffers must stay
+ * alive until then and should be page-locked (cudaHostRegister / cudaMallocHost) for the overlap to happen.
+ * Calls on one group run in submission order, so decoder state advances exactly as with the synchronous
+ * form.  frame_size <= 0 is answered with OPUS_BAD_ARG for the whole call. */
+int opus_decode_group_submit(OpusDecoderGroup *grp, const unsigned char *data, opus_int32 data_bytes,
+                             const opus_int32 *offsets, const opus_int32 *len, opus_int16 *pcm,
+                             opus_int32 pcm_stride, int frame_size, const int *decode_fec, int *ret);
+int opus_decode_group_wait(OpusDecoderGroup *grp);
+
 /* Device-resident form: every data pointer is a DEVICE pointer on the group's device; nothing is
  * copied and nothing is synchronised -- the work is queued on `cuda_stream` (a cudaStream_t,
  * NULL = the library's own stream).  max_frames = upper bound on frames per packet in this batch
@@ -261,6 +273,11 @@ void opus_encoder_group_destroy(OpusEncoderGroup *grp);
 int opus_encode_group_flat(OpusEncoderGroup *grp, const opus_int16 *pcm, int frame_size, unsigned char *data,
                            opus_int32 max_data_bytes, opus_int32 *out_len);
 /* Device buffers, same layout; asynchronous on the library stream (opus_b200_synchronize waits). */
+/* Pipelined host form of opus_encode_group_flat (see opus_decode_group_submit): data / out_len are complete
+ * after opus_encode_group_wait(). */
+int opus_encode_group_submit(OpusEncoderGroup *grp, const opus_int16 *pcm, int frame_size, unsigned char *data,
+                             opus_int32 max_data_bytes, opus_int32 *out_len);
+int opus_encode_group_wait(OpusEncoderGroup *grp);
 int opus_encode_group_device(OpusEncoderGroup *grp, const opus_int16 *d_pcm, int frame_size,
                              unsigned char *d_data, opus_int32 max_data_bytes, opus_int32 *d_len);
 /* Batched OPUS_GET_FINAL_RANGE for encoders. */

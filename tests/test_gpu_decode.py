@@ -180,3 +180,37 @@ def test_decode_gain_matches_reference():
                 assert ra == rb == 960 and np.array_equal(pa, pb), (gain, n)
         finally:
             dec.close()
+
+
+def test_pipelined_submit_matches_golden():
+    """opus_decode_group_submit/_wait: 64 streams replay the config-2 golden from different offsets, six calls
+    in flight back to back (two at a time in the pipeline) with page-locked buffers; every call's PCM equals
+    the synchronous path's and stream 0 equals the golden CRCs."""
+    import torch
+    meta, pk = golden_case("c2_96k_cbr_st")
+    n, spf, ch, steps = 64, 960, 2, 12
+    plen = len(pk[0][0])
+    assert all(len(p) == plen for p, _ in pk)
+    bd = cb.OpusBatchDecoder(48000, ch, n)
+    sync = cb.OpusBatchDecoder(48000, ch, n)
+    offs = (np.arange(n, dtype=np.int32) * plen).astype(np.int32)
+    lens = np.full(n, plen, dtype=np.int32)
+    arenas = [torch.zeros(n * plen, dtype=torch.uint8).pin_memory() for _ in range(steps)]
+    pcms = [torch.zeros(n * spf * ch, dtype=torch.int16).pin_memory() for _ in range(steps)]
+    rets = [torch.zeros(n, dtype=torch.int32).pin_memory() for _ in range(steps)]
+    try:
+        for t in range(steps):
+            a = arenas[t].numpy()
+            for i in range(n):
+                a[i * plen:(i + 1) * plen] = np.frombuffer(pk[(3 * i + t) % len(pk)][0], dtype=np.uint8)
+            bd.submit_flat(a, n * plen, offs, lens, spf, pcms[t].numpy(), rets[t].numpy())
+        bd.wait()
+        for t in range(steps):
+            r2, p2 = sync.decode_flat(arenas[t].numpy(), n * plen, offs, lens, spf)
+            assert (rets[t].numpy() == spf).all() and (r2 == spf).all()
+            assert np.array_equal(pcms[t].numpy().reshape(n, spf, ch), p2), t
+            assert crc32(pcms[t].numpy().reshape(n, spf, ch)[0]) == meta["pcm_crc32"][t], t
+        assert np.array_equal(bd.final_ranges(), sync.final_ranges())
+    finally:
+        bd.close()
+        sync.close()

@@ -153,3 +153,33 @@ def test_float_entry_point_and_errors():
     finally:
         enc.close()
         enc2.close()
+
+
+def test_pipelined_submit_matches_synchronous_calls():
+    """opus_encode_group_submit/_wait against opus_encode_group_flat on a twin group: same packets, lengths and
+    final ranges for ten frames queued back to back (pageable and page-locked buffers both work)."""
+    import torch
+    n, frame, ch, nframes = 48, 960, 2, 10
+    a = cb.OpusBatchEncoder(n, 48000, ch, enc_cases.LOWDELAY)
+    b = cb.OpusBatchEncoder(n, 48000, ch, enc_cases.LOWDELAY)
+    try:
+        for g in (a, b):
+            g.ctl(enc_cases.SET_BITRATE, 96000)
+        sig = np.stack([enc_cases.signal(enc_cases.KINDS[s % len(enc_cases.KINDS)], frame * nframes, ch, 300 + s)
+                        for s in range(n)])
+        rows = [torch.from_numpy(np.ascontiguousarray(sig[:, t * frame * ch:(t + 1) * frame * ch])) for t in range(nframes)]
+        rows = [r.pin_memory() if t % 2 == 0 else r for t, r in enumerate(rows)]
+        datas = [torch.zeros((n, 1275), dtype=torch.uint8).pin_memory() for _ in range(nframes)]
+        lens = [np.zeros(n, dtype=np.int32) for _ in range(nframes)]
+        for t in range(nframes):
+            a.submit(rows[t].numpy(), frame, datas[t].numpy(), lens[t])
+        a.wait()
+        for t in range(nframes):
+            d2, l2 = b.encode(rows[t].numpy(), frame, 1275)
+            assert np.array_equal(lens[t], l2), t
+            for s in range(n):
+                assert np.array_equal(datas[t].numpy()[s, :l2[s]], d2[s, :l2[s]]), (t, s)
+        assert np.array_equal(a.final_ranges(), b.final_ranges())
+    finally:
+        a.close()
+        b.close()
