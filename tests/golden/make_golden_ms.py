@@ -17,19 +17,19 @@ AUDIO = "/root/reference/AudioData/48Khz 5.1.raw"
 FRAMES = 200
 
 
-def main():
+def gen(name, bitrate, force_celt, application, index):
     pcm = np.fromfile(AUDIO, dtype=np.int16).reshape(-1, 6)
     streams, coupled = ctypes.c_int(0), ctypes.c_int(0)
     mapping = (ctypes.c_ubyte * 6)()
     err = ctypes.c_int(0)
     lib.opus_multistream_surround_encoder_create.restype = ctypes.c_void_p
     enc = lib.opus_multistream_surround_encoder_create(48000, 6, 1, ctypes.byref(streams), ctypes.byref(coupled),
-                                                       mapping, 2049, ctypes.byref(err))   # OPUS_APPLICATION_AUDIO
+                                                       mapping, application, ctypes.byref(err))
     assert enc and err.value == 0
     enc = ctypes.c_void_p(enc)
-    lib.opus_multistream_encoder_ctl(enc, 4002, ctypes.c_int(256000))       # OPUS_SET_BITRATE
+    lib.opus_multistream_encoder_ctl(enc, 4002, ctypes.c_int(bitrate))       # OPUS_SET_BITRATE
     lib.opus_multistream_encoder_ctl(enc, 4010, ctypes.c_int(10))           # OPUS_SET_COMPLEXITY
-    for s in range(streams.value):                                          # force CELT on every stream
+    for s in range(streams.value if force_celt else 0):                     # force CELT on every stream
         sub = ctypes.c_void_p(0)
         assert lib.opus_multistream_encoder_ctl(enc, 5120, ctypes.c_int(s), ctypes.byref(sub)) == 0
         assert lib.opus_encoder_ctl(sub, 11002, ctypes.c_int(1002)) == 0    # OPUS_SET_FORCE_MODE(MODE_CELT_ONLY)
@@ -57,16 +57,39 @@ def main():
         lib.opus_multistream_decoder_ctl(dec, 4031, ctypes.byref(fr))
         packets.append((pkt, fr.value))
         crcs.append(zlib.crc32(dpcm.tobytes()) & 0xFFFFFFFF)
-    with open(os.path.join(HERE, "ms51_256k.bit"), "wb") as f:
+    tocs = set()
+    for p, _ in packets:                                                    # TOC config of every elementary stream
+        q = p
+        for s in range(streams.value):
+            if not q:
+                break
+            tocs.add(q[0] >> 3)
+            if s == streams.value - 1:
+                break
+            # self-delimited framing (opus.c:190-343): skip this sub-packet via the reference's own parser
+            off = ctypes.c_int(0)
+            sizes = (ctypes.c_short * 48)()
+            toc = ctypes.c_ubyte(0)
+            cnt = lib.opus_packet_parse_impl(q, len(q), 1, ctypes.byref(toc), None, sizes, None, ctypes.byref(off))
+            assert cnt > 0
+            q = q[off.value:]
+    with open(os.path.join(HERE, name + ".bit"), "wb") as f:
         for p, r in packets:
             f.write(struct.pack(">II", len(p), r) + p)
-    idx_path = os.path.join(HERE, "index_ms.json")
-    json.dump({"ms51_256k": {"fs": 48000, "channels": 6, "streams": streams.value, "coupled": coupled.value,
+    index.update({name: {"fs": 48000, "channels": 6, "streams": streams.value, "coupled": coupled.value,
                              "mapping": list(mapping), "frames": FRAMES, "samples_per_frame": 960,
-                             "pcm_crc32": crcs, "lost": [i for i, (p, _) in enumerate(packets) if not p]}},
-              open(idx_path, "w"))
-    print("streams", streams.value, "coupled", coupled.value, "mapping", list(mapping),
+                             "pcm_crc32": crcs, "lost": [i for i, (p, _) in enumerate(packets) if not p],
+                         "toc_configs": sorted(tocs)}})
+    print(name, "toc configs", sorted(tocs), "streams", streams.value, "coupled", coupled.value, "mapping", list(mapping),
           "avg bytes", sum(len(p) for p, _ in packets) / FRAMES, "lost", sum(1 for p, _ in packets if not p))
+
+
+def main():
+    index = {}
+    gen("ms51_256k", 256000, True, 2049, index)      # config 5: CELT on every stream
+    gen("ms51_80k_voip", 80000, False, 2048, index)  # low rate, automatic modes: SILK / hybrid / CELT (LFE) streams side by side
+    gen("ms51_40k_voip", 40000, False, 2048, index)  # lower still: SILK-only streams
+    json.dump(index, open(os.path.join(HERE, "index_ms.json"), "w"))
 
 
 if __name__ == "__main__":

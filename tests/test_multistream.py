@@ -12,13 +12,19 @@ import concentus_b200 as cb
 from conftest import GOLDEN, crc32, have_ref, needs_ref, read_bit, REF_SO
 
 
-def ms_case():
-    meta = json.load(open(os.path.join(GOLDEN, "index_ms.json")))["ms51_256k"]
-    return meta, read_bit(os.path.join(GOLDEN, "ms51_256k.bit"))
+# ms51_256k: config 5 (CELT on every stream); ms51_80k_voip: hybrid + CELT elementary streams side by side;
+# ms51_40k_voip: SILK-only + CELT elementary streams (the surround encoder's own mode decisions at low rates)
+MS_CASES = ["ms51_256k", "ms51_80k_voip", "ms51_40k_voip"]
 
 
-def test_emu_multistream_matches_golden(emu_lib):
-    meta, pk = ms_case()
+def ms_case(name="ms51_256k"):
+    meta = json.load(open(os.path.join(GOLDEN, "index_ms.json")))[name]
+    return meta, read_bit(os.path.join(GOLDEN, name + ".bit"))
+
+
+@pytest.mark.parametrize("case", MS_CASES)
+def test_emu_multistream_matches_golden(emu_lib, case):
+    meta, pk = ms_case(case)
     emu_lib.emu_ms_create.restype = ctypes.c_void_p
     emu_lib.emu_ms_create.argtypes = [ctypes.c_int] * 4 + [ctypes.c_char_p]
     emu_lib.emu_ms_decode.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
@@ -39,8 +45,9 @@ def test_emu_multistream_matches_golden(emu_lib):
 
 
 @pytest.mark.gpu
-def test_gpu_multistream_single_matches_golden():
-    meta, pk = ms_case()
+@pytest.mark.parametrize("case", MS_CASES)
+def test_gpu_multistream_single_matches_golden(case):
+    meta, pk = ms_case(case)
     dec = cb.OpusMSDecoder(48000, 6, meta["streams"], meta["coupled"], meta["mapping"])
     try:
         for n, (p, rng) in enumerate(pk[:100]):
@@ -53,10 +60,11 @@ def test_gpu_multistream_single_matches_golden():
 
 
 @pytest.mark.gpu
-def test_gpu_multistream_1024_streams():
+@pytest.mark.parametrize("case", MS_CASES)
+def test_gpu_multistream_1024_streams(case):
     """Config 5 at full size: 1024 six-channel decoders in one group; all play the fixture (same
     loss pattern), every decoder must reproduce the golden PCM of every packet."""
-    meta, pk = ms_case()
+    meta, pk = ms_case(case)
     n = 1024
     bd = cb.OpusMSBatchDecoder(48000, 6, meta["streams"], meta["coupled"], meta["mapping"], n)
     try:
