@@ -48,8 +48,8 @@ CB_FN void sk_decode_frame(SilkChannel& ps, RangeDec& rd, i16* pOut, int* pN, in
     sk_plc(ps, ctrl, pOut, 1, w);
   }
   const int mv_len = ps.ltp_mem_length - ps.frame_length;
-  for (int i = 0; i < mv_len; i++) ps.outBuf[i] = ps.outBuf[ps.frame_length + i];
-  for (int i = 0; i < ps.frame_length; i++) ps.outBuf[mv_len + i] = pOut[i];
+  sk_copy_i16(ps.outBuf, &ps.outBuf[ps.frame_length], mv_len);
+  sk_copy_i16(&ps.outBuf[mv_len], pOut, ps.frame_length);
   sk_cng(ps, ctrl, pOut, L, w);
   sk_plc_glue_frames(ps, pOut, L);
   ps.lagPrev = ctrl.pitchL[ps.nb_subfr - 1];
@@ -61,6 +61,7 @@ struct SilkCallWork {
   SilkWork w;
   SilkRsWork rs;
   i16 tmp[2][SK_MAX_FRAME + 2];     // samplesOut1_tmp: channel n at tmp[n], 2 samples of history in front
+  alignas(16) i16 obuf[2 * 960];    // resampled output of one SILK frame (<= 20 ms at 48 kHz, interleaved)
 };
 
 // silk_Decode (dec_API.c:79-380).  API_sampleRate / nChannelsAPI come from the Opus decoder; the
@@ -181,16 +182,19 @@ CB_FN int sk_decode(SilkDecState& d, i32 API_sampleRate, int nChannelsAPI, int l
     d.sStereo.sMid[1] = cw.tmp[0][nSamplesOutDec + 1];
   }
   *nSamplesOut = (nSamplesOutDec * API_sampleRate) / sk_smulbb(cs[0].fs_kHz, 1000);
+  // the resamplers write sample by sample into a private buffer; the PCM row gets it in 16-byte pieces
   const int nres = nChannelsAPI < nInt ? nChannelsAPI : nInt;
+  i16* const ob = cw.obuf;
   for (int n = 0; n < nres; n++)
-    sk_resampler(cs[n].resampler, out + n, nChannelsAPI, &cw.tmp[n][1], nSamplesOutDec, cw.rs);
+    sk_resampler(cs[n].resampler, ob + n, nChannelsAPI, &cw.tmp[n][1], nSamplesOutDec, cw.rs);
   if (nChannelsAPI == 2 && nInt == 1) {
     if (stereo_to_mono) {
-      sk_resampler(cs[1].resampler, out + 1, 2, &cw.tmp[0][1], nSamplesOutDec, cw.rs);
+      sk_resampler(cs[1].resampler, ob + 1, 2, &cw.tmp[0][1], nSamplesOutDec, cw.rs);
     } else {
-      for (int i = 0; i < *nSamplesOut; i++) out[1 + 2 * i] = out[2 * i];
+      for (int i = 0; i < *nSamplesOut; i++) ob[1 + 2 * i] = ob[2 * i];
     }
   }
+  sk_copy_i16(out, ob, *nSamplesOut * nChannelsAPI);
   if (cs[0].prevSignalType == SK_TYPE_VOICED) {
     const int mult = cs[0].fs_kHz == 8 ? 6 : cs[0].fs_kHz == 12 ? 4 : 3;
     d.ctl_prevPitchLag = cs[0].lagPrev * mult;

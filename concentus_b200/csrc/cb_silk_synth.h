@@ -8,7 +8,8 @@
 #include "cb_silk_params.h"
 
 // per-thread work arrays of one SILK frame
-struct SilkWork {
+struct alignas(16) SilkWork {
+  i32 exc_Q14[SK_MAX_FRAME];               // the frame's excitation; stored to the channel state in one go
   i16 pulses[SK_MAX_FRAME];
   i16 sLTP[SK_MAX_FRAME];
   i32 sLTP_Q15[2 * SK_MAX_FRAME];          // decode_core: Q15; PLC: Q14
@@ -19,13 +20,72 @@ struct SilkWork {
 };
 
 // silk_LPC_analysis_filter (LPC_analysis_filter.c:43-110, FIXED_POINT branch)
+// The last D inputs stay in registers (h[ix mod D] = in[ix]; the loops unroll so every index is a
+// constant): one load per sample instead of D.  The sum is a wrapping 32-bit one, so its order is free.
+template <int D>
+CB_FN void sk_lpc_analysis_filter_t(i16* out, const i16* in, const i16* B, int len) {
+  i32 c[D], h[D];
+#pragma unroll
+  for (int j = 0; j < D; j++) {
+    c[j] = (i32)(i16)(-B[j]);
+    h[j] = in[j];
+    out[j] = 0;
+  }
+  for (int base = D; base < len; base += D) {
+#pragma unroll
+    for (int u = 0; u < D; u++) {
+      const int ix = base + u;
+      if (ix < len) {
+        const i32 x = in[ix];
+        i32 s0 = 0, s1 = 0;
+#pragma unroll
+        for (int j = 0; j < D; j += 2) {
+          s0 = sk_add(s0, sk_mul(c[j], h[(u - 1 - j + 2 * D) % D]));
+          s1 = sk_add(s1, sk_mul(c[j + 1], h[(u - 2 - j + 2 * D) % D]));
+        }
+        out[ix] = (i16)sk_sat16(sk_add(x, pshr32(sk_add(s0, s1), 12)));
+        h[u] = x;
+      }
+    }
+  }
+}
 CB_FN void sk_lpc_analysis_filter(i16* out, const i16* in, const i16* B, int len, int d) {
+  if (d == 16) { sk_lpc_analysis_filter_t<16>(out, in, B, len); return; }
+  if (d == 10) { sk_lpc_analysis_filter_t<10>(out, in, B, len); return; }
   for (int ix = d; ix < len; ix++) {
     i32 sum = 0;
     for (int j = 0; j < d; j++) sum = sk_add(sum, sk_mul((i32)(i16)(-B[j]), (i32)in[ix - 1 - j]));
     out[ix] = (i16)sk_sat16(sk_add((i32)in[ix], pshr32(sum, 12)));
   }
   for (int j = 0; j < d; j++) out[j] = 0;
+}
+
+// LPC synthesis of one subframe (decode_core.c:197-226) with the last D outputs in registers.
+// s = sLPC_Q14 (SK_MAX_ORDER history values in front, filled by the caller); len % D == 0.
+template <int D>
+CB_FN void sk_lpc_synthesis_t(i32* s, const i32* pres_Q14, i16* pxq, const i16* A_Q12, i32 Gain_Q10, int len) {
+  i32 a[D], h[D];
+#pragma unroll
+  for (int j = 0; j < D; j++) {
+    a[j] = A_Q12[j];
+    h[j] = s[SK_MAX_ORDER - D + j];        // sample index -D + j; slot j = index mod D as len % D == 0
+  }
+  for (int base = 0; base < len; base += D) {
+#pragma unroll
+    for (int u = 0; u < D; u++) {
+      const int i = base + u;
+      i32 p0 = D >> 1, p1 = 0;
+#pragma unroll
+      for (int j = 0; j < D; j += 2) {
+        p0 = sk_smlawb(p0, h[(u - 1 - j + 2 * D) % D], a[j]);
+        p1 = sk_smlawb(p1, h[(u - 2 - j + 2 * D) % D], a[j + 1]);
+      }
+      const i32 v = sk_add(pres_Q14[i], sk_lshift(sk_add(p0, p1), 4));
+      h[u] = v;
+      s[SK_MAX_ORDER + i] = v;
+      pxq[i] = (i16)sk_sat16(sk_rshift_round(sk_smulww(v, Gain_Q10), 8));
+    }
+  }
 }
 
 // silk_decode_core (decode_core.c:38-239)
@@ -45,11 +105,12 @@ CB_FN void sk_decode_core(SilkChannel& ps, SilkDecControl& ctrl, i16* xq, SilkWo
     else if (e < 0) e += 80 << 4;
     e += offset_Q10 << 4;
     if (rand_seed < 0) e = -e;
-    ps.exc_Q14[i] = e;
+    w.exc_Q14[i] = e;
     rand_seed = sk_add(rand_seed, pulses[i]);
   }
+  sk_copy_i32(ps.exc_Q14, w.exc_Q14, ps.frame_length);
   for (int i = 0; i < SK_MAX_ORDER; i++) sLPC_Q14[i] = ps.sLPC_Q14_buf[i];
-  i32* pexc_Q14 = ps.exc_Q14;
+  i32* pexc_Q14 = w.exc_Q14;
   i16* pxq = xq;
   int sLTP_buf_idx = ps.ltp_mem_length;
   for (int k = 0; k < ps.nb_subfr; k++) {
@@ -78,7 +139,7 @@ CB_FN void sk_decode_core(SilkChannel& ps, SilkDecControl& ctrl, i16* xq, SilkWo
       if (k == 0 || (k == 2 && NLSF_interpolation_flag)) {
         const int start_idx = ps.ltp_mem_length - lag - ps.LPC_order - SK_LTP_ORDER / 2;
         if (k == 2) {
-          for (int i = 0; i < 2 * ps.subfr_length; i++) ps.outBuf[ps.ltp_mem_length + i] = xq[i];
+          sk_copy_i16(&ps.outBuf[ps.ltp_mem_length], xq, 2 * ps.subfr_length);
         }
         sk_lpc_analysis_filter(&sLTP[start_idx], &ps.outBuf[start_idx + k * ps.subfr_length], A_Q12,
                                ps.ltp_mem_length - start_idx, ps.LPC_order);
@@ -91,28 +152,40 @@ CB_FN void sk_decode_core(SilkChannel& ps, SilkDecControl& ctrl, i16* xq, SilkWo
       }
     }
     if (signalType == SK_TYPE_VOICED) {
-      i32* pred_lag_ptr = &sLTP_Q15[sLTP_buf_idx - lag + SK_LTP_ORDER / 2];
+      // the five taps slide through registers; the incoming one is loaded an iteration ahead (it was
+      // written lag - 3 >= 13 samples ago, so the look-ahead never passes the store below)
+      const i32* pred_lag_ptr = &sLTP_Q15[sLTP_buf_idx - lag + SK_LTP_ORDER / 2];
+      const i32 b0 = B_Q14[0], b1 = B_Q14[1], b2 = B_Q14[2], b3 = B_Q14[3], b4 = B_Q14[4];
+      i32 t0 = pred_lag_ptr[0], t1 = pred_lag_ptr[-1], t2 = pred_lag_ptr[-2], t3 = pred_lag_ptr[-3], t4 = pred_lag_ptr[-4];
       for (int i = 0; i < ps.subfr_length; i++) {
+        const i32 nxt = pred_lag_ptr[i + 1];
         i32 LTP_pred_Q13 = 2;
-        LTP_pred_Q13 = sk_smlawb(LTP_pred_Q13, pred_lag_ptr[0], B_Q14[0]);
-        LTP_pred_Q13 = sk_smlawb(LTP_pred_Q13, pred_lag_ptr[-1], B_Q14[1]);
-        LTP_pred_Q13 = sk_smlawb(LTP_pred_Q13, pred_lag_ptr[-2], B_Q14[2]);
-        LTP_pred_Q13 = sk_smlawb(LTP_pred_Q13, pred_lag_ptr[-3], B_Q14[3]);
-        LTP_pred_Q13 = sk_smlawb(LTP_pred_Q13, pred_lag_ptr[-4], B_Q14[4]);
-        pred_lag_ptr++;
-        pres_Q14[i] = sk_add(pexc_Q14[i], sk_lshift(LTP_pred_Q13, 1));
-        sLTP_Q15[sLTP_buf_idx] = sk_lshift(pres_Q14[i], 1);
+        LTP_pred_Q13 = sk_smlawb(LTP_pred_Q13, t0, b0);
+        LTP_pred_Q13 = sk_smlawb(LTP_pred_Q13, t1, b1);
+        LTP_pred_Q13 = sk_smlawb(LTP_pred_Q13, t2, b2);
+        LTP_pred_Q13 = sk_smlawb(LTP_pred_Q13, t3, b3);
+        LTP_pred_Q13 = sk_smlawb(LTP_pred_Q13, t4, b4);
+        t4 = t3; t3 = t2; t2 = t1; t1 = t0; t0 = nxt;
+        const i32 r = sk_add(pexc_Q14[i], sk_lshift(LTP_pred_Q13, 1));
+        pres_Q14[i] = r;
+        sLTP_Q15[sLTP_buf_idx] = sk_lshift(r, 1);
         sLTP_buf_idx++;
       }
     } else {
       pres_Q14 = pexc_Q14;
     }
-    for (int i = 0; i < ps.subfr_length; i++) {
-      i32 LPC_pred_Q10 = ps.LPC_order >> 1;
-      for (int j = 0; j < ps.LPC_order; j++)
-        LPC_pred_Q10 = sk_smlawb(LPC_pred_Q10, sLPC_Q14[SK_MAX_ORDER + i - 1 - j], A_Q12[j]);
-      sLPC_Q14[SK_MAX_ORDER + i] = sk_add(pres_Q14[i], sk_lshift(LPC_pred_Q10, 4));
-      pxq[i] = (i16)sk_sat16(sk_rshift_round(sk_smulww(sLPC_Q14[SK_MAX_ORDER + i], Gain_Q10), 8));
+    if (ps.LPC_order == 16 && ps.subfr_length % 16 == 0) {
+      sk_lpc_synthesis_t<16>(sLPC_Q14, pres_Q14, pxq, A_Q12, Gain_Q10, ps.subfr_length);
+    } else if (ps.LPC_order == 10 && ps.subfr_length % 10 == 0) {
+      sk_lpc_synthesis_t<10>(sLPC_Q14, pres_Q14, pxq, A_Q12, Gain_Q10, ps.subfr_length);
+    } else {
+      for (int i = 0; i < ps.subfr_length; i++) {
+        i32 LPC_pred_Q10 = ps.LPC_order >> 1;
+        for (int j = 0; j < ps.LPC_order; j++)
+          LPC_pred_Q10 = sk_smlawb(LPC_pred_Q10, sLPC_Q14[SK_MAX_ORDER + i - 1 - j], A_Q12[j]);
+        sLPC_Q14[SK_MAX_ORDER + i] = sk_add(pres_Q14[i], sk_lshift(LPC_pred_Q10, 4));
+        pxq[i] = (i16)sk_sat16(sk_rshift_round(sk_smulww(sLPC_Q14[SK_MAX_ORDER + i], Gain_Q10), 8));
+      }
     }
     for (int i = 0; i < SK_MAX_ORDER; i++) sLPC_Q14[i] = sLPC_Q14[ps.subfr_length + i];
     pexc_Q14 += ps.subfr_length;
@@ -338,9 +411,8 @@ CB_FN void sk_cng(SilkChannel& ps, SilkDecControl& ctrl, i16* frame, int length,
     for (int i = 0; i < ps.nb_subfr; i++) {
       if (ctrl.Gains_Q16[i] > max_Gain_Q16) { max_Gain_Q16 = ctrl.Gains_Q16[i]; subfr = i; }
     }
-    for (int i = (ps.nb_subfr - 1) * ps.subfr_length - 1; i >= 0; i--)      // memmove towards higher addresses
-      cng.CNG_exc_buf_Q14[ps.subfr_length + i] = cng.CNG_exc_buf_Q14[i];
-    for (int i = 0; i < ps.subfr_length; i++) cng.CNG_exc_buf_Q14[i] = ps.exc_Q14[subfr * ps.subfr_length + i];
+    sk_copy_i32_down(&cng.CNG_exc_buf_Q14[ps.subfr_length], cng.CNG_exc_buf_Q14, (ps.nb_subfr - 1) * ps.subfr_length);
+    sk_copy_i32(cng.CNG_exc_buf_Q14, &ps.exc_Q14[subfr * ps.subfr_length], ps.subfr_length);
     for (int i = 0; i < ps.nb_subfr; i++)
       cng.CNG_smth_Gain_Q16 += sk_smulwb(ctrl.Gains_Q16[i] - cng.CNG_smth_Gain_Q16, 4634);
   }
@@ -587,7 +659,9 @@ CB_FN i16* sk_rs_down_fir(SilkResampler& S, i16* out, int ostride, const i16* in
 }
 
 // silk_resampler (resampler.c:176-215).  Output written with stride `ostride` (interleaving folded in).
-CB_FN void sk_resampler(SilkResampler& S, i16* out, int ostride, const i16* in, int inLen, SilkRsWork& rw) {
+CB_FN void sk_resampler(SilkResampler& Sg, i16* out, int ostride, const i16* in, int inLen, SilkRsWork& rw) {
+  // the filter memories are touched once per sample: work on a private copy, store the memories back once
+  SilkResampler S = Sg;
   const int nSamples = S.Fs_in_kHz - S.inputDelay;
   for (int i = 0; i < nSamples; i++) S.delayBuf[S.inputDelay + i] = in[i];
   if (S.function == SK_RS_UP2) {
@@ -609,4 +683,7 @@ CB_FN void sk_resampler(SilkResampler& S, i16* out, int ostride, const i16* in, 
     for (int i = 0; i < inLen - S.Fs_in_kHz; i++) out[ostride * (S.Fs_out_kHz + i)] = in[nSamples + i];
   }
   for (int i = 0; i < S.inputDelay; i++) S.delayBuf[i] = in[inLen - S.inputDelay + i];
+  for (int i = 0; i < 6; i++) Sg.sIIR[i] = S.sIIR[i];
+  for (int i = 0; i < 36; i++) Sg.sFIR[i] = S.sFIR[i];
+  for (int i = 0; i < 48; i++) Sg.delayBuf[i] = S.delayBuf[i];
 }
