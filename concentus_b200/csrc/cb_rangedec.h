@@ -106,6 +106,28 @@ CB_FN_NOINLINE int rd_icdf(RangeDec& d, const u8* icdf, u32 ftb) {
   rd_normalize(d);
   return ret;
 }
+// ec_dec_icdf for per-lane tables in global memory (SILK): the linear search is a chain of dependent
+// loads, so four entries are fetched at once (the tables are padded by 4 bytes, tools/gen_silk_tables.py)
+CB_FN_NOINLINE int rd_icdf_g(RangeDec& d, const u8* icdf, u32 ftb) {
+  u32 s = d.rng, v = d.val, t;
+  const u32 r = s >> ftb;
+  int ret = 0;
+  CB_NOUNROLL for (;;) {
+    const u32 b0 = icdf[ret], b1 = icdf[ret + 1], b2 = icdf[ret + 2], b3 = icdf[ret + 3];
+    t = s; s = r * b0; if (v >= s) break;
+    ret++;
+    t = s; s = r * b1; if (v >= s) break;
+    ret++;
+    t = s; s = r * b2; if (v >= s) break;
+    ret++;
+    t = s; s = r * b3; if (v >= s) break;
+    ret++;
+  }
+  d.val = v - s;
+  d.rng = t - s;
+  rd_normalize(d);
+  return ret;
+}
 // ec_dec_bits (entdec.c:284-319): raw bits from the tail of the packet
 CB_FN_NOINLINE u32 rd_bits(RangeDec& d, u32 bits) {
   u32 window = d.end_window;

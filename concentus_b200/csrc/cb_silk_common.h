@@ -29,7 +29,12 @@
 #define SK_FLAG_DECODE_LBRR 2
 
 // ---- macros.h / SigProc_FIX.h ------------------------------------------------------------------
+#if CB_DEVICE_BUILD
+// (a * (i16)b) >> 16 == high word of a * ((i16)b << 16): one IMAD.HI instead of a wide multiply and a funnel shift
+CB_FN i32 sk_smulwb(i32 a, i32 b) { return __mulhi(a, (i32)((u32)b << 16)); }                // macros.h:53
+#else
 CB_FN i32 sk_smulwb(i32 a, i32 b) { return (i32)(((i64)a * (i64)(i16)b) >> 16); }          // macros.h:53
+#endif
 CB_FN i32 sk_smlawb(i32 a, i32 b, i32 c) { return (i32)((u32)a + (u32)sk_smulwb(b, c)); }  // macros.h:60
 CB_FN i32 sk_smulbb(i32 a, i32 b) { return (i32)(i16)a * (i32)(i16)b; }                    // macros.h:76
 CB_FN i32 sk_smlabb(i32 a, i32 b, i32 c) { return (i32)((u32)a + (u32)sk_smulbb(b, c)); }  // macros.h:79

@@ -110,7 +110,7 @@ CB_FN int sk_decode(SilkDecState& d, i32 API_sampleRate, int nChannelsAPI, int l
         if (cs[n].nFramesPerPacket == 1) {
           cs[n].LBRR_flags[0] = 1;
         } else {
-          const i32 sym = rd_icdf(rd, cs[n].nFramesPerPacket == 2 ? st_LBRR_flags_2_iCDF : st_LBRR_flags_3_iCDF, 8) + 1;
+          const i32 sym = rd_icdf_g(rd, cs[n].nFramesPerPacket == 2 ? st_LBRR_flags_2_iCDF : st_LBRR_flags_3_iCDF, 8) + 1;
           for (int i = 0; i < cs[n].nFramesPerPacket; i++) cs[n].LBRR_flags[i] = (sym >> i) & 1;
         }
       }
@@ -121,7 +121,7 @@ CB_FN int sk_decode(SilkDecState& d, i32 API_sampleRate, int nChannelsAPI, int l
           if (cs[n].LBRR_flags[i]) {
             if (nInt == 2 && n == 0) {
               sk_stereo_decode_pred(rd, MS_pred_Q13);
-              if (cs[1].LBRR_flags[i] == 0) decode_only_middle = rd_icdf(rd, st_stereo_only_code_mid_iCDF, 8);
+              if (cs[1].LBRR_flags[i] == 0) decode_only_middle = rd_icdf_g(rd, st_stereo_only_code_mid_iCDF, 8);
             }
             const int condCoding = (i > 0 && cs[n].LBRR_flags[i - 1]) ? SK_CODE_CONDITIONALLY : SK_CODE_INDEPENDENTLY;
             sk_decode_indices(cs[n], rd, i, 1, condCoding);
@@ -137,7 +137,7 @@ CB_FN int sk_decode(SilkDecState& d, i32 API_sampleRate, int nChannelsAPI, int l
       sk_stereo_decode_pred(rd, MS_pred_Q13);
       if ((lostFlag == SK_FLAG_DECODE_NORMAL && cs[1].VAD_flags[cs[0].nFramesDecoded] == 0) ||
           (lostFlag == SK_FLAG_DECODE_LBRR && cs[1].LBRR_flags[cs[0].nFramesDecoded] == 0))
-        decode_only_middle = rd_icdf(rd, st_stereo_only_code_mid_iCDF, 8);
+        decode_only_middle = rd_icdf_g(rd, st_stereo_only_code_mid_iCDF, 8);
       else
         decode_only_middle = 0;
     } else {

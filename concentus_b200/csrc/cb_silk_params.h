@@ -64,32 +64,32 @@ CB_FN void sk_decode_indices(SilkChannel& ps, RangeDec& rd, int FrameIndex, int 
   int Ix;
   i16 ec_ix[SK_MAX_ORDER];
   u8 pred_Q8[SK_MAX_ORDER];
-  if (decode_LBRR || ps.VAD_flags[FrameIndex]) Ix = rd_icdf(rd, st_type_offset_VAD_iCDF, 8) + 2;
-  else Ix = rd_icdf(rd, st_type_offset_no_VAD_iCDF, 8);
+  if (decode_LBRR || ps.VAD_flags[FrameIndex]) Ix = rd_icdf_g(rd, st_type_offset_VAD_iCDF, 8) + 2;
+  else Ix = rd_icdf_g(rd, st_type_offset_no_VAD_iCDF, 8);
   ix.signalType = (i8)(Ix >> 1);
   ix.quantOffsetType = (i8)(Ix & 1);
   if (condCoding == SK_CODE_CONDITIONALLY) {
-    ix.GainsIndices[0] = (i8)rd_icdf(rd, st_delta_gain_iCDF, 8);
+    ix.GainsIndices[0] = (i8)rd_icdf_g(rd, st_delta_gain_iCDF, 8);
   } else {
-    ix.GainsIndices[0] = (i8)(rd_icdf(rd, st_gain_iCDF + 8 * ix.signalType, 8) << 3);
-    ix.GainsIndices[0] = (i8)(ix.GainsIndices[0] + (i8)rd_icdf(rd, st_uniform8_iCDF, 8));
+    ix.GainsIndices[0] = (i8)(rd_icdf_g(rd, st_gain_iCDF + 8 * ix.signalType, 8) << 3);
+    ix.GainsIndices[0] = (i8)(ix.GainsIndices[0] + (i8)rd_icdf_g(rd, st_uniform8_iCDF, 8));
   }
-  for (int i = 1; i < ps.nb_subfr; i++) ix.GainsIndices[i] = (i8)rd_icdf(rd, st_delta_gain_iCDF, 8);
+  for (int i = 1; i < ps.nb_subfr; i++) ix.GainsIndices[i] = (i8)rd_icdf_g(rd, st_delta_gain_iCDF, 8);
   const SilkNLSFCB cb = sk_nlsf_cb(ps.LPC_order == 16);
-  ix.NLSFIndices[0] = (i8)rd_icdf(rd, &cb.CB1_iCDF[(ix.signalType >> 1) * cb.nVectors], 8);
+  ix.NLSFIndices[0] = (i8)rd_icdf_g(rd, &cb.CB1_iCDF[(ix.signalType >> 1) * cb.nVectors], 8);
   sk_nlsf_unpack(ec_ix, pred_Q8, cb, ix.NLSFIndices[0]);
   for (int i = 0; i < cb.order; i++) {
-    Ix = rd_icdf(rd, &cb.ec_iCDF[ec_ix[i]], 8);
-    if (Ix == 0) Ix -= rd_icdf(rd, st_NLSF_EXT_iCDF, 8);
-    else if (Ix == 2 * 4) Ix += rd_icdf(rd, st_NLSF_EXT_iCDF, 8);
+    Ix = rd_icdf_g(rd, &cb.ec_iCDF[ec_ix[i]], 8);
+    if (Ix == 0) Ix -= rd_icdf_g(rd, st_NLSF_EXT_iCDF, 8);
+    else if (Ix == 2 * 4) Ix += rd_icdf_g(rd, st_NLSF_EXT_iCDF, 8);
     ix.NLSFIndices[i + 1] = (i8)(Ix - 4);
   }
-  if (ps.nb_subfr == SK_MAX_NB_SUBFR) ix.NLSFInterpCoef_Q2 = (i8)rd_icdf(rd, st_NLSF_interp_iCDF, 8);
+  if (ps.nb_subfr == SK_MAX_NB_SUBFR) ix.NLSFInterpCoef_Q2 = (i8)rd_icdf_g(rd, st_NLSF_interp_iCDF, 8);
   else ix.NLSFInterpCoef_Q2 = 4;
   if (ix.signalType == SK_TYPE_VOICED) {
     int decode_absolute_lagIndex = 1;
     if (condCoding == SK_CODE_CONDITIONALLY && ps.ec_prevSignalType == SK_TYPE_VOICED) {
-      int delta_lagIndex = (i16)rd_icdf(rd, st_pitch_delta_iCDF, 8);
+      int delta_lagIndex = (i16)rd_icdf_g(rd, st_pitch_delta_iCDF, 8);
       if (delta_lagIndex > 0) {
         delta_lagIndex = delta_lagIndex - 9;
         ix.lagIndex = (i16)(ps.ec_prevLagIndex + delta_lagIndex);
@@ -97,25 +97,25 @@ CB_FN void sk_decode_indices(SilkChannel& ps, RangeDec& rd, int FrameIndex, int 
       }
     }
     if (decode_absolute_lagIndex) {
-      ix.lagIndex = (i16)((i16)rd_icdf(rd, st_pitch_lag_iCDF, 8) * (ps.fs_kHz >> 1));
-      ix.lagIndex = (i16)(ix.lagIndex + (i16)rd_icdf(rd, sk_pitch_lag_low_bits_icdf(ps.fs_kHz), 8));
+      ix.lagIndex = (i16)((i16)rd_icdf_g(rd, st_pitch_lag_iCDF, 8) * (ps.fs_kHz >> 1));
+      ix.lagIndex = (i16)(ix.lagIndex + (i16)rd_icdf_g(rd, sk_pitch_lag_low_bits_icdf(ps.fs_kHz), 8));
     }
     ps.ec_prevLagIndex = ix.lagIndex;
-    ix.contourIndex = (i8)rd_icdf(rd, sk_pitch_contour_icdf(ps.fs_kHz, ps.nb_subfr), 8);
-    ix.PERIndex = (i8)rd_icdf(rd, st_LTP_per_index_iCDF, 8);
+    ix.contourIndex = (i8)rd_icdf_g(rd, sk_pitch_contour_icdf(ps.fs_kHz, ps.nb_subfr), 8);
+    ix.PERIndex = (i8)rd_icdf_g(rd, st_LTP_per_index_iCDF, 8);
     const u8* gi = ix.PERIndex == 0 ? st_LTP_gain_iCDF_0 : ix.PERIndex == 1 ? st_LTP_gain_iCDF_1 : st_LTP_gain_iCDF_2;
-    for (int k = 0; k < ps.nb_subfr; k++) ix.LTPIndex[k] = (i8)rd_icdf(rd, gi, 8);
-    if (condCoding == SK_CODE_INDEPENDENTLY) ix.LTP_scaleIndex = (i8)rd_icdf(rd, st_LTPscale_iCDF, 8);
+    for (int k = 0; k < ps.nb_subfr; k++) ix.LTPIndex[k] = (i8)rd_icdf_g(rd, gi, 8);
+    if (condCoding == SK_CODE_INDEPENDENTLY) ix.LTP_scaleIndex = (i8)rd_icdf_g(rd, st_LTPscale_iCDF, 8);
     else ix.LTP_scaleIndex = 0;
   }
   ps.ec_prevSignalType = ix.signalType;
-  ix.Seed = (i8)rd_icdf(rd, st_uniform4_iCDF, 8);
+  ix.Seed = (i8)rd_icdf_g(rd, st_uniform4_iCDF, 8);
 }
 
 // decode_split / silk_shell_decoder (shell_coder.c:60-76,137-151)
 CB_FN void sk_decode_split(i16* c1, i16* c2, RangeDec& rd, int p, const u8* shell_table) {
   if (p > 0) {
-    c1[0] = (i16)rd_icdf(rd, &shell_table[st_shell_code_table_offsets[p]], 8);
+    c1[0] = (i16)rd_icdf_g(rd, &shell_table[st_shell_code_table_offsets[p]], 8);
     c2[0] = (i16)(p - c1[0]);
   } else {
     c1[0] = 0;
@@ -141,16 +141,16 @@ CB_FN void sk_shell_decoder(i16* pulses0, RangeDec& rd, int pulses4) {
 // silk_decode_pulses + silk_decode_signs (decode_pulses.c:38-115, code_signs.c:74-115)
 CB_FN void sk_decode_pulses(RangeDec& rd, i16* pulses, int signalType, int quantOffsetType, int frame_length) {
   int sum_pulses[SK_MAX_FRAME / 16], nLshifts[SK_MAX_FRAME / 16];
-  const int RateLevelIndex = rd_icdf(rd, st_rate_levels_iCDF + 9 * (signalType >> 1), 8);
+  const int RateLevelIndex = rd_icdf_g(rd, st_rate_levels_iCDF + 9 * (signalType >> 1), 8);
   int iter = frame_length >> 4;
   if (iter * 16 < frame_length) iter++;
   const u8* cdf_ptr = st_pulses_per_block_iCDF + 18 * RateLevelIndex;
   for (int i = 0; i < iter; i++) {
     nLshifts[i] = 0;
-    sum_pulses[i] = rd_icdf(rd, cdf_ptr, 8);
+    sum_pulses[i] = rd_icdf_g(rd, cdf_ptr, 8);
     while (sum_pulses[i] == 16 + 1) {
       nLshifts[i]++;
-      sum_pulses[i] = rd_icdf(rd, st_pulses_per_block_iCDF + 18 * 9 + (nLshifts[i] == 10), 8);
+      sum_pulses[i] = rd_icdf_g(rd, st_pulses_per_block_iCDF + 18 * 9 + (nLshifts[i] == 10), 8);
     }
   }
   for (int i = 0; i < iter; i++) {
@@ -165,7 +165,7 @@ CB_FN void sk_decode_pulses(RangeDec& rd, i16* pulses, int signalType, int quant
         int abs_q = pp[k];
         for (int j = 0; j < nLS; j++) {
           abs_q = abs_q << 1;
-          abs_q += rd_icdf(rd, st_lsb_iCDF, 8);
+          abs_q += rd_icdf_g(rd, st_lsb_iCDF, 8);
         }
         pp[k] = (i16)abs_q;
       }
@@ -173,8 +173,7 @@ CB_FN void sk_decode_pulses(RangeDec& rd, i16* pulses, int signalType, int quant
     }
   }
   // signs
-  u8 icdf[2];
-  icdf[1] = 0;
+  u8 icdf[8] = {0, 0, 0, 0, 0, 0, 0, 0};       // two entries + read-ahead room for rd_icdf_g
   const u8* icdf_ptr = &st_sign_iCDF[7 * (quantOffsetType + (signalType << 1))];
   const int nblk = (frame_length + 8) >> 4;
   i16* q = pulses;
@@ -183,7 +182,7 @@ CB_FN void sk_decode_pulses(RangeDec& rd, i16* pulses, int signalType, int quant
     if (p > 0) {
       icdf[0] = icdf_ptr[sk_min(p & 0x1F, 6)];
       for (int j = 0; j < 16; j++) {
-        if (q[j] > 0) q[j] = (i16)(q[j] * ((rd_icdf(rd, icdf, 8) << 1) - 1));
+        if (q[j] > 0) q[j] = (i16)(q[j] * ((rd_icdf_g(rd, icdf, 8) << 1) - 1));
       }
     }
     q += 16;
@@ -477,12 +476,12 @@ CB_FN void sk_decode_parameters(SilkChannel& ps, SilkDecControl& ctrl, int condC
 // silk_stereo_decode_pred / silk_stereo_decode_mid_only (stereo_decode_pred.c:35-73)
 CB_FN void sk_stereo_decode_pred(RangeDec& rd, i32* pred_Q13) {
   int ix[2][3];
-  int n = rd_icdf(rd, st_stereo_pred_joint_iCDF, 8);
+  int n = rd_icdf_g(rd, st_stereo_pred_joint_iCDF, 8);
   ix[0][2] = n / 5;
   ix[1][2] = n - 5 * ix[0][2];
   for (n = 0; n < 2; n++) {
-    ix[n][0] = rd_icdf(rd, st_uniform3_iCDF, 8);
-    ix[n][1] = rd_icdf(rd, st_uniform5_iCDF, 8);
+    ix[n][0] = rd_icdf_g(rd, st_uniform3_iCDF, 8);
+    ix[n][1] = rd_icdf_g(rd, st_uniform5_iCDF, 8);
   }
   for (n = 0; n < 2; n++) {
     ix[n][0] += 3 * ix[n][2];

@@ -98,15 +98,19 @@ CB_FN void sk_decode_core(SilkChannel& ps, SilkDecControl& ctrl, i16* xq, SilkWo
   const i32 offset_Q10 = st_quant_offsets_Q10[(ps.indices.signalType >> 1) * 2 + ps.indices.quantOffsetType];
   const int NLSF_interpolation_flag = ps.indices.NLSFInterpCoef_Q2 < 4;
   i32 rand_seed = ps.indices.Seed;
-  for (int i = 0; i < ps.frame_length; i++) {
-    rand_seed = sk_rand(rand_seed);
-    i32 e = sk_lshift((i32)pulses[i], 14);
-    if (e > 0) e -= 80 << 4;
-    else if (e < 0) e += 80 << 4;
-    e += offset_Q10 << 4;
-    if (rand_seed < 0) e = -e;
-    w.exc_Q14[i] = e;
-    rand_seed = sk_add(rand_seed, pulses[i]);
+  for (int i0 = 0; i0 < ps.frame_length; i0 += 4) {            // frame lengths are multiples of 40
+    const i32 q[4] = {pulses[i0], pulses[i0 + 1], pulses[i0 + 2], pulses[i0 + 3]};   // loads first: they overlap
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      rand_seed = sk_rand(rand_seed);
+      i32 e = sk_lshift(q[u], 14);
+      if (e > 0) e -= 80 << 4;
+      else if (e < 0) e += 80 << 4;
+      e += offset_Q10 << 4;
+      if (rand_seed < 0) e = -e;
+      w.exc_Q14[i0 + u] = e;
+      rand_seed = sk_add(rand_seed, q[u]);
+    }
   }
   sk_copy_i32(ps.exc_Q14, w.exc_Q14, ps.frame_length);
   for (int i = 0; i < SK_MAX_ORDER; i++) sLPC_Q14[i] = ps.sLPC_Q14_buf[i];
@@ -144,11 +148,29 @@ CB_FN void sk_decode_core(SilkChannel& ps, SilkDecControl& ctrl, i16* xq, SilkWo
         sk_lpc_analysis_filter(&sLTP[start_idx], &ps.outBuf[start_idx + k * ps.subfr_length], A_Q12,
                                ps.ltp_mem_length - start_idx, ps.LPC_order);
         if (k == 0) inv_gain_Q31 = sk_lshift(sk_smulwb(inv_gain_Q31, ctrl.LTP_scale_Q14), 2);
-        for (int i = 0; i < lag + SK_LTP_ORDER / 2; i++)
-          sLTP_Q15[sLTP_buf_idx - i - 1] = sk_smulwb(inv_gain_Q31, sLTP[ps.ltp_mem_length - i - 1]);
+        {
+          const int n = lag + SK_LTP_ORDER / 2;
+          int i = 0;
+          for (; i + 4 <= n; i += 4) {
+            const i32 v0 = sLTP[ps.ltp_mem_length - i - 1], v1 = sLTP[ps.ltp_mem_length - i - 2];
+            const i32 v2 = sLTP[ps.ltp_mem_length - i - 3], v3 = sLTP[ps.ltp_mem_length - i - 4];
+            sLTP_Q15[sLTP_buf_idx - i - 1] = sk_smulwb(inv_gain_Q31, v0);
+            sLTP_Q15[sLTP_buf_idx - i - 2] = sk_smulwb(inv_gain_Q31, v1);
+            sLTP_Q15[sLTP_buf_idx - i - 3] = sk_smulwb(inv_gain_Q31, v2);
+            sLTP_Q15[sLTP_buf_idx - i - 4] = sk_smulwb(inv_gain_Q31, v3);
+          }
+          for (; i < n; i++) sLTP_Q15[sLTP_buf_idx - i - 1] = sk_smulwb(inv_gain_Q31, sLTP[ps.ltp_mem_length - i - 1]);
+        }
       } else if (gain_adj_Q16 != 1 << 16) {
-        for (int i = 0; i < lag + SK_LTP_ORDER / 2; i++)
-          sLTP_Q15[sLTP_buf_idx - i - 1] = sk_smulww(gain_adj_Q16, sLTP_Q15[sLTP_buf_idx - i - 1]);
+        const int n = lag + SK_LTP_ORDER / 2;
+        int i = 0;
+        for (; i + 4 <= n; i += 4) {
+          i32* q = &sLTP_Q15[sLTP_buf_idx - i - 4];
+          const i32 v0 = q[0], v1 = q[1], v2 = q[2], v3 = q[3];
+          q[0] = sk_smulww(gain_adj_Q16, v0); q[1] = sk_smulww(gain_adj_Q16, v1);
+          q[2] = sk_smulww(gain_adj_Q16, v2); q[3] = sk_smulww(gain_adj_Q16, v3);
+        }
+        for (; i < n; i++) sLTP_Q15[sLTP_buf_idx - i - 1] = sk_smulww(gain_adj_Q16, sLTP_Q15[sLTP_buf_idx - i - 1]);
       }
     }
     if (signalType == SK_TYPE_VOICED) {
@@ -157,19 +179,24 @@ CB_FN void sk_decode_core(SilkChannel& ps, SilkDecControl& ctrl, i16* xq, SilkWo
       const i32* pred_lag_ptr = &sLTP_Q15[sLTP_buf_idx - lag + SK_LTP_ORDER / 2];
       const i32 b0 = B_Q14[0], b1 = B_Q14[1], b2 = B_Q14[2], b3 = B_Q14[3], b4 = B_Q14[4];
       i32 t0 = pred_lag_ptr[0], t1 = pred_lag_ptr[-1], t2 = pred_lag_ptr[-2], t3 = pred_lag_ptr[-3], t4 = pred_lag_ptr[-4];
-      for (int i = 0; i < ps.subfr_length; i++) {
-        const i32 nxt = pred_lag_ptr[i + 1];
-        i32 LTP_pred_Q13 = 2;
-        LTP_pred_Q13 = sk_smlawb(LTP_pred_Q13, t0, b0);
-        LTP_pred_Q13 = sk_smlawb(LTP_pred_Q13, t1, b1);
-        LTP_pred_Q13 = sk_smlawb(LTP_pred_Q13, t2, b2);
-        LTP_pred_Q13 = sk_smlawb(LTP_pred_Q13, t3, b3);
-        LTP_pred_Q13 = sk_smlawb(LTP_pred_Q13, t4, b4);
-        t4 = t3; t3 = t2; t2 = t1; t1 = t0; t0 = nxt;
-        const i32 r = sk_add(pexc_Q14[i], sk_lshift(LTP_pred_Q13, 1));
-        pres_Q14[i] = r;
-        sLTP_Q15[sLTP_buf_idx] = sk_lshift(r, 1);
-        sLTP_buf_idx++;
+      for (int i = 0; i < ps.subfr_length; i += 4) {            // subframe lengths are multiples of 4; lag >= 16
+        // four samples per trip: their inputs were all written more than a trip ago, so the loads go first
+        const i32 n1 = pred_lag_ptr[i + 1], n2 = pred_lag_ptr[i + 2], n3 = pred_lag_ptr[i + 3], n4 = pred_lag_ptr[i + 4];
+        const i32 e0 = pexc_Q14[i], e1 = pexc_Q14[i + 1], e2 = pexc_Q14[i + 2], e3 = pexc_Q14[i + 3];
+        i32 p;
+        p = sk_smlawb(sk_smlawb(sk_smlawb(sk_smlawb(sk_smlawb(2, t0, b0), t1, b1), t2, b2), t3, b3), t4, b4);
+        const i32 r0 = sk_add(e0, sk_lshift(p, 1));
+        p = sk_smlawb(sk_smlawb(sk_smlawb(sk_smlawb(sk_smlawb(2, n1, b0), t0, b1), t1, b2), t2, b3), t3, b4);
+        const i32 r1 = sk_add(e1, sk_lshift(p, 1));
+        p = sk_smlawb(sk_smlawb(sk_smlawb(sk_smlawb(sk_smlawb(2, n2, b0), n1, b1), t0, b2), t1, b3), t2, b4);
+        const i32 r2 = sk_add(e2, sk_lshift(p, 1));
+        p = sk_smlawb(sk_smlawb(sk_smlawb(sk_smlawb(sk_smlawb(2, n3, b0), n2, b1), n1, b2), t0, b3), t1, b4);
+        const i32 r3 = sk_add(e3, sk_lshift(p, 1));
+        t4 = t0; t3 = n1; t2 = n2; t1 = n3; t0 = n4;
+        pres_Q14[i] = r0; pres_Q14[i + 1] = r1; pres_Q14[i + 2] = r2; pres_Q14[i + 3] = r3;
+        sLTP_Q15[sLTP_buf_idx] = sk_lshift(r0, 1); sLTP_Q15[sLTP_buf_idx + 1] = sk_lshift(r1, 1);
+        sLTP_Q15[sLTP_buf_idx + 2] = sk_lshift(r2, 1); sLTP_Q15[sLTP_buf_idx + 3] = sk_lshift(r3, 1);
+        sLTP_buf_idx += 4;
       }
     } else {
       pres_Q14 = pexc_Q14;
@@ -680,7 +707,18 @@ CB_FN void sk_resampler(SilkResampler& Sg, i16* out, int ostride, const i16* in,
     sk_rs_down_fir(S, out + ostride * S.Fs_out_kHz, ostride, &in[nSamples], inLen - S.Fs_in_kHz, rw);
   } else {
     for (int i = 0; i < S.Fs_in_kHz; i++) out[ostride * i] = S.delayBuf[i];
-    for (int i = 0; i < inLen - S.Fs_in_kHz; i++) out[ostride * (S.Fs_out_kHz + i)] = in[nSamples + i];
+    {
+      const int n = inLen - S.Fs_in_kHz;
+      i16* o = out + ostride * S.Fs_out_kHz;
+      const i16* p = in + nSamples;
+      int i = 0;
+      for (; i + 8 <= n; i += 8) {                                 // loads first: their latencies overlap
+        const i16 v0 = p[i], v1 = p[i + 1], v2 = p[i + 2], v3 = p[i + 3], v4 = p[i + 4], v5 = p[i + 5], v6 = p[i + 6], v7 = p[i + 7];
+        o[ostride * i] = v0; o[ostride * (i + 1)] = v1; o[ostride * (i + 2)] = v2; o[ostride * (i + 3)] = v3;
+        o[ostride * (i + 4)] = v4; o[ostride * (i + 5)] = v5; o[ostride * (i + 6)] = v6; o[ostride * (i + 7)] = v7;
+      }
+      for (; i < n; i++) o[ostride * i] = p[i];
+    }
   }
   for (int i = 0; i < S.inputDelay; i++) S.delayBuf[i] = in[inLen - S.inputDelay + i];
   for (int i = 0; i < 6; i++) Sg.sIIR[i] = S.sIIR[i];

@@ -105,7 +105,9 @@ def main():
     for ours, ty, path, name, n in TABLES:
         vals = grab(path, name)
         assert len(vals) == n, (name, len(vals), n)
-        out.append("CB_GTABLE %s st_%s[%d] = {\n%s\n};\n" % (ty, ours, n, fmt(vals)))
+        # byte tables carry 4 zero bytes of padding: rd_icdf_g reads four entries ahead of its linear search
+        pad = 4 if ty == "uint8_t" else 0
+        out.append("CB_GTABLE %s st_%s[%d] = {\n%s\n};\n" % (ty, ours, n + pad, fmt(vals + [0] * pad)))
     # the two up2_hq coefficient triplets are written in the header as expressions; restate them
     hdr = open(os.path.join(REF, "resampler_rom.h")).read()
     m0 = re.search(r"silk_resampler_up2_hq_0\[ 3 \] = \{([^}]*)\}", hdr)
