@@ -107,8 +107,10 @@ CB_FN_NOINLINE int rd_icdf(RangeDec& d, const u8* icdf, u32 ftb) {
   return ret;
 }
 // ec_dec_icdf for per-lane tables in global memory (SILK): the linear search is a chain of dependent
-// loads, so four entries are fetched at once (the tables are padded by 4 bytes, tools/gen_silk_tables.py)
-CB_FN_NOINLINE int rd_icdf_g(RangeDec& d, const u8* icdf, u32 ftb) {
+// loads, so four entries are fetched at once (the tables are padded by 4 bytes, tools/gen_silk_tables.py).
+// Inlined, like everything else the one-thread-per-stream SILK decoder calls, so that the coder state
+// stays in registers from one symbol to the next.
+CB_FN int rd_icdf_g(RangeDec& d, const u8* icdf, u32 ftb) {
   u32 s = d.rng, v = d.val, t;
   const u32 r = s >> ftb;
   int ret = 0;
@@ -125,6 +127,26 @@ CB_FN_NOINLINE int rd_icdf_g(RangeDec& d, const u8* icdf, u32 ftb) {
   }
   d.val = v - s;
   d.rng = t - s;
+  rd_normalize(d);
+  return ret;
+}
+// ec_dec_icdf with the two-entry table {p0, 0} (SILK pulse signs and LSBs): no table at all
+CB_FN int rd_icdf2_g(RangeDec& d, u32 p0, u32 ftb) {
+  const u32 rng = d.rng, v = d.val;
+  const u32 s = (rng >> ftb) * p0;
+  const int ret = v < s;
+  d.val = ret ? v : v - s;
+  d.rng = ret ? s : rng - s;
+  rd_normalize(d);
+  return ret;
+}
+// ec_dec_bit_logp, inlined form for the SILK decoder
+CB_FN int rd_bit_logp_g(RangeDec& d, u32 logp) {
+  u32 r = d.rng, v = d.val;
+  u32 s = r >> logp;
+  int ret = v < s;
+  if (!ret) d.val = v - s;
+  d.rng = ret ? s : r - s;
   rd_normalize(d);
   return ret;
 }

@@ -101,8 +101,8 @@ CB_FN int sk_decode(SilkDecState& d, i32 API_sampleRate, int nChannelsAPI, int l
   if (API_sampleRate > 48000 || API_sampleRate < 8000) return -200;
   if (lostFlag != SK_FLAG_PACKET_LOST && cs[0].nFramesDecoded == 0) {
     for (int n = 0; n < nInt; n++) {
-      for (int i = 0; i < cs[n].nFramesPerPacket; i++) cs[n].VAD_flags[i] = rd_bit_logp(rd, 1);
-      cs[n].LBRR_flag = rd_bit_logp(rd, 1);
+      for (int i = 0; i < cs[n].nFramesPerPacket; i++) cs[n].VAD_flags[i] = rd_bit_logp_g(rd, 1);
+      cs[n].LBRR_flag = rd_bit_logp_g(rd, 1);
     }
     for (int n = 0; n < nInt; n++) {
       cs[n].LBRR_flags[0] = cs[n].LBRR_flags[1] = cs[n].LBRR_flags[2] = 0;

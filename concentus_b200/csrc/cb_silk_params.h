@@ -165,7 +165,7 @@ CB_FN void sk_decode_pulses(RangeDec& rd, i16* pulses, int signalType, int quant
         int abs_q = pp[k];
         for (int j = 0; j < nLS; j++) {
           abs_q = abs_q << 1;
-          abs_q += rd_icdf_g(rd, st_lsb_iCDF, 8);
+          abs_q += rd_icdf2_g(rd, 120, 8);               // silk_lsb_iCDF = {120, 0}
         }
         pp[k] = (i16)abs_q;
       }
@@ -173,16 +173,15 @@ CB_FN void sk_decode_pulses(RangeDec& rd, i16* pulses, int signalType, int quant
     }
   }
   // signs
-  u8 icdf[8] = {0, 0, 0, 0, 0, 0, 0, 0};       // two entries + read-ahead room for rd_icdf_g
   const u8* icdf_ptr = &st_sign_iCDF[7 * (quantOffsetType + (signalType << 1))];
   const int nblk = (frame_length + 8) >> 4;
   i16* q = pulses;
   for (int i = 0; i < nblk; i++) {
     const int p = sum_pulses[i];
     if (p > 0) {
-      icdf[0] = icdf_ptr[sk_min(p & 0x1F, 6)];
+      const u32 p0 = icdf_ptr[sk_min(p & 0x1F, 6)];            // the table is {p0, 0} (code_signs.c:98-113)
       for (int j = 0; j < 16; j++) {
-        if (q[j] > 0) q[j] = (i16)(q[j] * ((rd_icdf_g(rd, icdf, 8) << 1) - 1));
+        if (q[j] > 0) q[j] = (i16)(q[j] * ((rd_icdf2_g(rd, p0, 8) << 1) - 1));
       }
     }
     q += 16;

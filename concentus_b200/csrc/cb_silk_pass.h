@@ -73,7 +73,7 @@ CB_FN void decode_silk_pass(OpusDecState* st, StreamPlan* pl, const u8* data, i1
     if (have_data) {
       const RangeDec before = rd;
       int red = 0;
-      if ((int)rd_tell(rd) + 37 <= 8 * len) red = rd_bit_logp(rd, 12);
+      if ((int)rd_tell(rd) + 37 <= 8 * len) red = rd_bit_logp_g(rd, 12);
       const u32* src = (const u32*)(red ? &before : &rd);
       for (int i = 0; i < (int)(sizeof(RangeDec) / 4); i++) pl->rd_save[i] = src[i];
       if (red) pl->route = CB_ROUTE_FINISH;

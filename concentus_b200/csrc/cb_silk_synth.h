@@ -71,6 +71,9 @@ CB_FN void sk_lpc_synthesis_t(i32* s, const i32* pres_Q14, i16* pxq, const i16* 
     h[j] = s[SK_MAX_ORDER - D + j];        // sample index -D + j; slot j = index mod D as len % D == 0
   }
   for (int base = 0; base < len; base += D) {
+    i32 pr[D];
+#pragma unroll
+    for (int u = 0; u < D; u++) pr[u] = pres_Q14[base + u];      // the block's inputs: loads overlap
 #pragma unroll
     for (int u = 0; u < D; u++) {
       const int i = base + u;
@@ -80,7 +83,7 @@ CB_FN void sk_lpc_synthesis_t(i32* s, const i32* pres_Q14, i16* pxq, const i16* 
         p0 = sk_smlawb(p0, h[(u - 1 - j + 2 * D) % D], a[j]);
         p1 = sk_smlawb(p1, h[(u - 2 - j + 2 * D) % D], a[j + 1]);
       }
-      const i32 v = sk_add(pres_Q14[i], sk_lshift(sk_add(p0, p1), 4));
+      const i32 v = sk_add(pr[u], sk_lshift(sk_add(p0, p1), 4));
       h[u] = v;
       s[SK_MAX_ORDER + i] = v;
       pxq[i] = (i16)sk_sat16(sk_rshift_round(sk_smulww(v, Gain_Q10), 8));
@@ -179,10 +182,13 @@ CB_FN void sk_decode_core(SilkChannel& ps, SilkDecControl& ctrl, i16* xq, SilkWo
       const i32* pred_lag_ptr = &sLTP_Q15[sLTP_buf_idx - lag + SK_LTP_ORDER / 2];
       const i32 b0 = B_Q14[0], b1 = B_Q14[1], b2 = B_Q14[2], b3 = B_Q14[3], b4 = B_Q14[4];
       i32 t0 = pred_lag_ptr[0], t1 = pred_lag_ptr[-1], t2 = pred_lag_ptr[-2], t3 = pred_lag_ptr[-3], t4 = pred_lag_ptr[-4];
+      i32 n1 = pred_lag_ptr[1], n2 = pred_lag_ptr[2], n3 = pred_lag_ptr[3], n4 = pred_lag_ptr[4];
+      i32 e0 = pexc_Q14[0], e1 = pexc_Q14[1], e2 = pexc_Q14[2], e3 = pexc_Q14[3];
       for (int i = 0; i < ps.subfr_length; i += 4) {            // subframe lengths are multiples of 4; lag >= 16
-        // four samples per trip: their inputs were all written more than a trip ago, so the loads go first
-        const i32 n1 = pred_lag_ptr[i + 1], n2 = pred_lag_ptr[i + 2], n3 = pred_lag_ptr[i + 3], n4 = pred_lag_ptr[i + 4];
-        const i32 e0 = pexc_Q14[i], e1 = pexc_Q14[i + 1], e2 = pexc_Q14[i + 2], e3 = pexc_Q14[i + 3];
+        // four samples per trip, and the inputs of the next trip are fetched before this one computes: they
+        // were written at least lag - 10 > 0 samples ago (past the subframe's end the values are not used)
+        const i32 m1 = pred_lag_ptr[i + 5], m2 = pred_lag_ptr[i + 6], m3 = pred_lag_ptr[i + 7], m4 = pred_lag_ptr[i + 8];
+        const i32 f0 = pexc_Q14[i + 4], f1 = pexc_Q14[i + 5], f2 = pexc_Q14[i + 6], f3 = pexc_Q14[i + 7];
         i32 p;
         p = sk_smlawb(sk_smlawb(sk_smlawb(sk_smlawb(sk_smlawb(2, t0, b0), t1, b1), t2, b2), t3, b3), t4, b4);
         const i32 r0 = sk_add(e0, sk_lshift(p, 1));
@@ -193,6 +199,8 @@ CB_FN void sk_decode_core(SilkChannel& ps, SilkDecControl& ctrl, i16* xq, SilkWo
         p = sk_smlawb(sk_smlawb(sk_smlawb(sk_smlawb(sk_smlawb(2, n3, b0), n2, b1), n1, b2), t0, b3), t1, b4);
         const i32 r3 = sk_add(e3, sk_lshift(p, 1));
         t4 = t0; t3 = n1; t2 = n2; t1 = n3; t0 = n4;
+        n1 = m1; n2 = m2; n3 = m3; n4 = m4;
+        e0 = f0; e1 = f1; e2 = f2; e3 = f3;
         pres_Q14[i] = r0; pres_Q14[i + 1] = r1; pres_Q14[i + 2] = r2; pres_Q14[i + 3] = r3;
         sLTP_Q15[sLTP_buf_idx] = sk_lshift(r0, 1); sLTP_Q15[sLTP_buf_idx + 1] = sk_lshift(r1, 1);
         sLTP_Q15[sLTP_buf_idx + 2] = sk_lshift(r2, 1); sLTP_Q15[sLTP_buf_idx + 3] = sk_lshift(r3, 1);
