@@ -13,7 +13,9 @@
 #include "cb_silk_pass.h"
 #include "cb_kernels.h"
 
+#ifndef S_THREADS
 #define S_THREADS 32
+#endif
 
 __global__ void __launch_bounds__(S_THREADS)
 silk_decode_kernel(OpusDecState* const* states, StreamPlan* plans, const u8* data, i16* pcm, i32 pcm_stride, i32* ret,
