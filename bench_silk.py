@@ -109,6 +109,18 @@ def main():
     launches = lib.opus_b200_launch_count() - launches0
     dev_ms = float(sum(a.elapsed_time(b) for a, b in ev))
     assert int((d_ret != SPF).sum().item()) == 0
+    # per-kernel timing (library events around every launch), separate loop
+    lib.opus_b200_profile_begin()
+    with torch.cuda.stream(stream):
+        for k in range(min(K, 20)):
+            flush.fill_(k & 0xFF)
+            step_device(t % len(d_arena))
+            t += 1
+    ms3 = (ctypes.c_double * 3)()
+    cnt3 = (ctypes.c_longlong * 3)()
+    lib.opus_b200_profile_end(ms3, cnt3)
+    kern_ms = {"plan+silk": ms3[0] / max(1, cnt3[0]), "celt_entropy": ms3[1] / max(1, cnt3[1]),
+               "celt_synth": ms3[2] / max(1, cnt3[2])}
     # e2e: page-locked host packets in, page-locked host PCM out, every step; (a) one synchronous call per step
     # (opus_decode_group_flat), (b) the pipelined form (opus_decode_group_submit/_wait, two calls in flight)
     h_pcm = [torch.zeros(n * SPF * CH, dtype=torch.int16).pin_memory() for _ in range(3)]
@@ -162,7 +174,7 @@ def main():
         "gpu_launches": int(launches), "clocks": sampler.summary(),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": None, "peak_kind": peak_kind, "kernel": KERNEL,
-                     "step_ms": dev_ms / K, "algorithmic_bytes_per_launch": alg_bytes,
+                     "step_ms": dev_ms / K, "kernel_ms": kern_ms, "algorithmic_bytes_per_launch": alg_bytes,
                      "note": NOTE},
     }
     exe = os.path.join(ROOT, "oracle", "_ref", "ref_bench")

@@ -196,12 +196,22 @@ CB_FN void v_exp_rotation_dec(i16* X, int len, int stride, int K, int spread) {
 }
 
 // ---- PVQ index -> pulse vector (cwrs.c:463-541), uniform; every lane stores the same values ---
+#ifdef CB_PVQ_STATS
+static long g_pvq_calls, g_pvq_n, g_pvq_k, g_pvq_dense_pos, g_pvq_sparse_pos, g_pvq_sparse_nz, g_pvq_hist[8];
+#endif
 CB_FN i32 pvq_decode(i16* y, int n, int k, u32 i) {
+#ifdef CB_PVQ_STATS
+  g_pvq_calls++; g_pvq_n += n; g_pvq_k += k;
+  { int r = k ? n / k : 99; g_pvq_hist[r >= 7 ? 7 : r] += n; }
+#endif
   i32 yy = 0;
   u32 p, q;
   int s, k0;
   i16 val;
   CB_NOUNROLL while (n > 2) {
+#ifdef CB_PVQ_STATS
+    if (k >= n) g_pvq_dense_pos++; else g_pvq_sparse_pos++;
+#endif
     if (k >= n) {
       int rowoff = ct_pvq_u_row[n];
       p = ct_pvq_u_data[rowoff + k + 1];

@@ -17,19 +17,19 @@ opus_general_kernel(OpusDecState* const* states, StreamPlan* plans, FrameSide* s
                     i32 pcm_stride, i32* ret, int n, int pass) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int warp = threadIdx.x >> 5;
-  const int s = blockIdx.x * G_WARPS + warp;
-  if (s >= n) return;
-  StreamPlan* pl = &plans[s];
-  const int route = pl->route;
   GenWork& g = *reinterpret_cast<GenWork*>(smem + (size_t)warp * sizeof(GenWork));
-  if (route == CB_ROUTE_CELT) {
-    // pitch-based concealment of a CELT frame, asked for by kernel A (celt_decode_lost, loss_count < 5)
-    if (sides[s].kind == 2) decode_plc_pass(g.pw, states[s], pl, &sides[s], pcm + (size_t)s * pcm_stride, pass);
-    return;
-  }
-  if (route != CB_ROUTE_GENERAL && route != CB_ROUTE_FINISH) return;
   SilkCallWork cw;
-  decode_general_pass(g, states[s], pl, &sides[s], data, pcm + (size_t)s * pcm_stride, &ret[s], pass, cw);
+  for (int s = blockIdx.x * G_WARPS + warp; s < n; s += gridDim.x * G_WARPS) {
+    StreamPlan* pl = &plans[s];
+    const int route = pl->route;
+    if (route == CB_ROUTE_CELT) {
+      // pitch-based concealment of a CELT frame, asked for by kernel A (celt_decode_lost, loss_count < 5)
+      if (sides[s].kind == 2) decode_plc_pass(g.pw, states[s], pl, &sides[s], pcm + (size_t)s * pcm_stride, pass);
+    } else if (route == CB_ROUTE_GENERAL || route == CB_ROUTE_FINISH) {
+      decode_general_pass(g, states[s], pl, &sides[s], data, pcm + (size_t)s * pcm_stride, &ret[s], pass, cw);
+    }
+    __syncwarp();
+  }
 }
 
 extern "C" int cbk_launch_general(OpusDecState* const* d_states, StreamPlan* d_plans, FrameSide* d_sides, const u8* d_data,
@@ -45,7 +45,9 @@ extern "C" int cbk_launch_general(OpusDecState* const* d_states, StreamPlan* d_p
     if (e != cudaSuccess) return (int)e;
     if (dev < 64) attr_set[dev] = true;
   }
-  opus_general_kernel<<<(n + G_WARPS - 1) / G_WARPS, G_WARPS * 32, smem, stream>>>(d_states, d_plans, d_sides, d_data, d_pcm,
+  int grid = (n + G_WARPS - 1) / G_WARPS;
+  if (grid > 148 * 4) grid = 148 * 4;               // a few CTAs per SM; streams beyond are walked by a grid-stride loop
+  opus_general_kernel<<<grid, G_WARPS * 32, smem, stream>>>(d_states, d_plans, d_sides, d_data, d_pcm,
                                                                                     pcm_stride, d_ret, n, pass);
   return (int)cudaGetLastError();
 }
