@@ -42,7 +42,10 @@ EXPORTS = [
     "opus_decode", "opus_decode_float", "opus_decoder_ctl", "opus_decoder_destroy",
     "opus_packet_get_bandwidth", "opus_packet_get_nb_channels", "opus_packet_get_nb_frames",
     "opus_packet_get_samples_per_frame", "opus_packet_get_nb_samples", "opus_decoder_get_nb_samples",
-    "opus_packet_parse", "opus_decode_batch", "opus_decode_batch_flat", "opus_decoder_group_create",
+    "opus_packet_parse", "opus_repacketizer_get_size", "opus_repacketizer_init", "opus_repacketizer_create",
+    "opus_repacketizer_destroy", "opus_repacketizer_cat", "opus_repacketizer_out_range", "opus_repacketizer_get_nb_frames",
+    "opus_repacketizer_out", "opus_packet_pad", "opus_packet_unpad", "opus_multistream_packet_pad",
+    "opus_multistream_packet_unpad", "opus_b200_bit_index", "opus_decode_batch", "opus_decode_batch_flat", "opus_decoder_group_create",
     "opus_decoder_group_destroy", "opus_decode_group_flat", "opus_decode_group_device",
     "opus_decode_group_submit", "opus_decode_group_wait", "opus_encode_group_submit", "opus_encode_group_wait",
     "opus_decoder_get_final_range_batch", "opus_b200_synchronize", "opus_b200_launch_count",
@@ -95,6 +98,19 @@ def load():
     lib.opus_decoder_group_create.argtypes = [vp, ctypes.c_int, c_int_p]
     lib.opus_decoder_group_destroy.argtypes = [vp]
     lib.opus_decoder_group_destroy.restype = None
+    lib.opus_repacketizer_create.restype = vp
+    lib.opus_repacketizer_init.restype = vp
+    lib.opus_repacketizer_init.argtypes = [vp]
+    lib.opus_repacketizer_destroy.argtypes = [vp]
+    lib.opus_repacketizer_cat.argtypes = [vp, vp, ctypes.c_int32]
+    lib.opus_repacketizer_get_nb_frames.argtypes = [vp]
+    lib.opus_repacketizer_out.argtypes = [vp, vp, ctypes.c_int32]
+    lib.opus_repacketizer_out_range.argtypes = [vp, ctypes.c_int, ctypes.c_int, vp, ctypes.c_int32]
+    lib.opus_packet_pad.argtypes = [vp, ctypes.c_int32, ctypes.c_int32]
+    lib.opus_packet_unpad.argtypes = [vp, ctypes.c_int32]
+    lib.opus_multistream_packet_pad.argtypes = [vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_int]
+    lib.opus_multistream_packet_unpad.argtypes = [vp, ctypes.c_int32, ctypes.c_int]
+    lib.opus_b200_bit_index.argtypes = [vp, ctypes.c_int32, vp, vp, vp, ctypes.c_int32]
     lib.opus_decode_group_flat.argtypes = [vp, vp, ctypes.c_int32, vp, vp, vp, ctypes.c_int32, ctypes.c_int, vp, vp]
     lib.opus_decode_group_submit.argtypes = [vp, vp, ctypes.c_int32, vp, vp, vp, ctypes.c_int32, ctypes.c_int, vp, vp]
     lib.opus_decode_group_wait.argtypes = [vp]

@@ -84,6 +84,31 @@ int opus_decoder_get_nb_samples(const OpusDecoder *dec, const unsigned char pack
 int opus_packet_parse(const unsigned char *data, opus_int32 len, unsigned char *out_toc,
                       const unsigned char *frames[48], opus_int16 size[48], int *payload_offset);
 
+/* ---- repacketizer and padding (opus-fix/include/opus.h:886-981, src/repacketizer.c) ----
+ * Host-side byte surgery, identical results to the reference: merge frames of equal configuration into one
+ * packet (up to 120 ms), split them again, pad a packet to a fixed size (CBR transport) and strip padding. */
+typedef struct OpusRepacketizer OpusRepacketizer;
+int opus_repacketizer_get_size(void);
+OpusRepacketizer *opus_repacketizer_init(OpusRepacketizer *rp);
+OpusRepacketizer *opus_repacketizer_create(void);
+void opus_repacketizer_destroy(OpusRepacketizer *rp);
+int opus_repacketizer_cat(OpusRepacketizer *rp, const unsigned char *data, opus_int32 len);
+opus_int32 opus_repacketizer_out_range(OpusRepacketizer *rp, int begin, int end, unsigned char *data,
+                                       opus_int32 maxlen);
+int opus_repacketizer_get_nb_frames(OpusRepacketizer *rp);
+opus_int32 opus_repacketizer_out(OpusRepacketizer *rp, unsigned char *data, opus_int32 maxlen);
+int opus_packet_pad(unsigned char *data, opus_int32 len, opus_int32 new_len);
+opus_int32 opus_packet_unpad(unsigned char *data, opus_int32 len);
+int opus_multistream_packet_pad(unsigned char *data, opus_int32 len, opus_int32 new_len, int nb_streams);
+opus_int32 opus_multistream_packet_unpad(unsigned char *data, opus_int32 len, int nb_streams);
+
+/* Index an opus_demo ".bit" image (opus-fix/src/opus_demo.c:750-760: per packet BE32 length, BE32 encoder
+ * final range, payload) so that a recorded stream feeds the flat batch calls without per-packet host work:
+ * offsets[i] / lens[i] address packet i inside `file` (-1 / 0 for a lost packet), final_ranges[i] is the check
+ * value.  Returns the packet count (at most max_packets entries written) or OPUS_INVALID_PACKET. */
+opus_int32 opus_b200_bit_index(const unsigned char *file, opus_int32 file_bytes, opus_int32 *offsets,
+                               opus_int32 *lens, opus_uint32 *final_ranges, opus_int32 max_packets);
+
 /* ---- batch ABI (no counterpart in libopus; semantics = n x opus_decode) -------------------- */
 
 /* Pointer-array form.  data[i]==NULL or len[i]==0 => concealment for stream i.
