@@ -1,0 +1,743 @@
+// cb_celt_bands3.h -- quant_all_bands, decoder side (bands.c:1337-1502), as three phases per frame:
+//
+//   1. PARSE   the range decoder walks bands / stereo splits / partitions exactly as the reference
+//              does, but touches no spectrum: it notes the shape of the recursion on a small tape
+//              (split angles, a bit per node) and, for every leaf that carries pulses, the PVQ index
+//              and its parameters -- written into the leaf's own (still unused) slot of X.
+//   2. PULSES  the leaves are independent of each other: ONE LANE PER LEAF turns index -> pulse vector
+//              (cwrsi is a serial walk), normalises, applies the spreading rotation and leaves the
+//              collapse mask.  32 leaves at a time instead of one after the other on a uniform warp.
+//   3. REBUILD the same walk again, driven by the tape instead of the bitstream: folding / noise fill
+//              of the empty leaves, Hadamard / Haar recombination, stereo merge, lowband for the bands
+//              to come -- the lane-parallel vector work.
+//
+// Nothing the decoder reads from the bitstream depends on the spectrum (collapse masks and folding
+// only steer reconstruction), which is what makes the split legal.  Phases 1 and 3 are one piece of
+// code (template <bool REBUILD>), so the two walks cannot drift apart.  When the tape or the job list
+// cannot take another band, the bands parsed so far are finished (phases 2 + 3) and parsing resumes.
+#pragma once
+
+#define CB_B3_BUF 176           // 16-bit entries in flight: pending leaves from the front, tape notes from the back
+#define CB_B3_BITWORDS 16       // 512 node bits in flight
+#define CB_B3_MIN_N 6           // a deferred leaf keeps its 6-word record in its own X slot
+
+struct B3Cur {                  // cursors of the tape: written by PARSE, read by REBUILD (uniform registers)
+  int jobs, tape, bits;
+};
+
+CB_FN void b3_push_bit(EntWork& w, B3Cur& c, int v) {
+  if (v) w.b3_bits[c.bits >> 5] |= 1u << (c.bits & 31);
+  c.bits++;
+}
+CB_FN int b3_pop_bit(const EntWork& w, B3Cur& c) {
+  const int v = (w.b3_bits[c.bits >> 5] >> (c.bits & 31)) & 1;
+  c.bits++;
+  return v;
+}
+CB_FN void b3_push(EntWork& w, B3Cur& c, int v) { w.b3_buf[CB_B3_BUF - 1 - c.tape++] = (u16)v; }
+CB_FN int b3_pop(const EntWork& w, B3Cur& c) { return w.b3_buf[CB_B3_BUF - 1 - c.tape++]; }
+// Upper bounds of what one band can add: L = most leaves of one channel's partition tree (a node splits
+// while LM >= 0 and N > 2); per channel L - 1 split angles and L leaves (a pending-leaf entry or a mask
+// each), plus the stereo angle; per node a split bit, per split an order bit, per leaf two bits.
+CB_FN int b3_band_leaves(int N, int LM) {
+  int L = 1;
+  CB_NOUNROLL while (LM >= 0 && N > 2) { L <<= 1; N >>= 1; LM--; }
+  return L;
+}
+
+// ---- phase 2: one leaf on one lane --------------------------------------------------------------
+// cwrsi with per-lane table reads (global copy of the U(n,k) table; the constant-memory one wants a
+// uniform index).  Same walk as pvq_decode above.
+CB_FN u32 b3_u(int row, int col) { return cb_ldg(&ct_pvq_u_data_g[cb_ldg(&ct_pvq_u_row_g[row]) + col]); }
+CB_FN i32 b3_cwrsi(i16* y, int n, int k, u32 i) {
+  i32 yy = 0;
+  u32 p, q;
+  int s, k0;
+  i16 val;
+  CB_NOUNROLL while (n > 2) {
+    if (k >= n) {
+      const int rowoff = cb_ldg(&ct_pvq_u_row_g[n]);
+      p = cb_ldg(&ct_pvq_u_data_g[rowoff + k + 1]);
+      s = -(int)(i >= p);
+      i -= p & (u32)s;
+      k0 = k;
+      q = cb_ldg(&ct_pvq_u_data_g[rowoff + n]);
+      if (q > i) {
+        k = n;
+        CB_NOUNROLL do p = b3_u(--k, n); while (p > i);
+      } else {
+        CB_NOUNROLL for (p = cb_ldg(&ct_pvq_u_data_g[rowoff + k]); p > i; p = cb_ldg(&ct_pvq_u_data_g[rowoff + k])) k--;
+      }
+      i -= p;
+      val = (i16)((k0 - k + s) ^ s);
+      *y++ = val;
+      yy = mac16_16(yy, val, val);
+    } else {
+      p = b3_u(k, n);
+      q = b3_u(k + 1, n);
+      if (p <= i && i < q) {
+        i -= p;
+        *y++ = 0;
+      } else {
+        s = -(int)(i >= q);
+        i -= q & (u32)s;
+        k0 = k;
+        CB_NOUNROLL do p = b3_u(--k, n); while (p > i);
+        i -= p;
+        val = (i16)((k0 - k + s) ^ s);
+        *y++ = val;
+        yy = mac16_16(yy, val, val);
+      }
+    }
+    n--;
+  }
+  p = 2 * (u32)k + 1;
+  s = -(int)(i >= p);
+  i -= p & (u32)s;
+  k0 = k;
+  k = (int)((i + 1) >> 1);
+  if (k) i -= 2 * (u32)k - 1;
+  val = (i16)((k0 - k + s) ^ s);
+  *y++ = val;
+  yy = mac16_16(yy, val, val);
+  s = -(int)i;
+  val = (i16)((k + s) ^ s);
+  *y = val;
+  yy = mac16_16(yy, val, val);
+  return yy;
+}
+// exp_rotation1 (vq.c:43-67), one lane
+CB_FN void b3_rot1(i16* x, int len, int st, i32 c, i32 s) {
+  const i32 ms = (i16)(-s);
+  CB_NOUNROLL for (int i = 0; i < len - st; i++) {
+    const i32 x1 = x[i], x2 = x[i + st];
+    x[i + st] = ext16(pshr32(mac16_16(mult16_16(c, x2), s, x1), 15));
+    x[i] = ext16(pshr32(mac16_16(mult16_16(c, x1), ms, x2), 15));
+  }
+  CB_NOUNROLL for (int i = len - 2 * st - 1; i >= 0; i--) {
+    const i32 x1 = x[i], x2 = x[i + st];
+    x[i + st] = ext16(pshr32(mac16_16(mult16_16(c, x2), s, x1), 15));
+    x[i] = ext16(pshr32(mac16_16(mult16_16(c, x1), ms, x2), 15));
+  }
+}
+// alg_unquant after the index has been read (vq.c:329-347): cwrsi, normalise_residual (:117-137),
+// extract_collapse_mask (:139-159), exp_rotation with dir = -1 (:70-115).  X = the leaf, in place.
+CB_FN u32 b3_leaf(i16* X, int N, int K, u32 idx, i32 gain, int B, int spread) {
+  const i32 Ryy = b3_cwrsi(X, N, K, idx);
+  const int k = cb_ilog2(Ryy) >> 1;
+  const i32 t = vshr32(Ryy, 2 * (k - 7));
+  const i16 g = (i16)mult16_16_p15(cb_rsqrt_norm(t), gain);
+  u32 mask = 0;
+  const int N0 = N / B;
+  CB_NOUNROLL for (int b = 0; b < B; b++) {
+    i32 any = 0;
+    CB_NOUNROLL for (int j = 0; j < N0; j++) {
+      const i32 v = X[b * N0 + j];
+      any |= v;
+      X[b * N0 + j] = ext16(pshr32(mult16_16(g, v), k + 1));
+    }
+    if (any) mask |= 1u << b;
+  }
+  if (B <= 1) mask = 1;
+  if (2 * K < N && spread != CB_SPREAD_NONE) {
+    const int factor = spread == 1 ? 15 : spread == 2 ? 10 : 5;
+    const i16 gn = (i16)cb_div(mult16_16(CB_Q15ONE, N), N + factor * K);
+    const i16 theta = (i16)(mult16_16_q15(gn, gn) >> 1);
+    const i16 c = cb_cos_norm(theta);
+    const i16 s = cb_cos_norm(sub16(CB_Q15ONE, theta));
+    int stride2 = 0;
+    if (N >= 8 * B) {
+      stride2 = 1;
+      CB_NOUNROLL while ((stride2 * stride2 + stride2) * B + (B >> 2) < N) stride2++;
+    }
+    const int len = N / B;
+    CB_NOUNROLL for (int i = 0; i < B; i++) {
+      if (stride2) b3_rot1(X + i * len, len, stride2, s, c);
+      b3_rot1(X + i * len, len, 1, c, s);
+    }
+  }
+  return mask;
+}
+// record of a deferred leaf, kept in the leaf's own X slot until its lane picks it up
+CB_FN void b3_put_job(i16* X, int N, int K, u32 idx, i32 gain, int B, int spread) {
+  X[0] = (i16)(idx & 0xFFFF);
+  X[1] = (i16)(idx >> 16);
+  X[2] = (i16)N;
+  X[3] = (i16)K;
+  X[4] = (i16)gain;
+  X[5] = (i16)(B | (spread << 8));
+}
+// Phase 2: lanes take the pending leaves of w.b3_buf[0..njobs); the entry becomes the collapse mask.
+CB_FN void b3_run_jobs(EntWork& w, int njobs) {
+  CB_WSYNC();
+  CB_LANE_LOOP(j, njobs) {
+    i16* X = w.X + w.b3_buf[j];
+    const u32 idx = (u32)(u16)X[0] | ((u32)(u16)X[1] << 16);
+    const int N = X[2], K = X[3];
+    const i32 gain = X[4];
+    const int B = X[5] & 0xFF, spread = (X[5] >> 8) & 0xFF;
+    w.b3_buf[j] = (u16)b3_leaf(X, N, K, idx, gain, B, spread);
+  }
+  CB_WSYNC();
+}
+
+// alg_unquant for a leaf too small to carry its record (N < 6): decoded at once, warp-uniform as before
+CB_FN u32 b3_leaf_now(EntWork& w, i16* X, int N, int K, u32 idx, int spread, int B, i32 gain) {
+  i16* iy = (i16*)w.tmp32;
+  CB_WSYNC();
+  const i32 Ryy = pvq_decode(iy, N, K, idx);
+  CB_WSYNC();
+  const int k = cb_ilog2(Ryy) >> 1;
+  const i32 t = vshr32(Ryy, 2 * (k - 7));
+  const i16 g = (i16)mult16_16_p15(cb_rsqrt_norm(t), gain);
+  u32 mask = 0;
+  const int N0 = N / B;
+  CB_LANE_LOOP(j, N) {
+    const i32 v = iy[j];
+    X[j] = ext16(pshr32(mult16_16(g, v), k + 1));
+    if (v != 0) mask |= 1u << (j / N0);
+  }
+  mask = B <= 1 ? 1u : cb_wor(mask);
+  v_exp_rotation_dec(X, N, B, K, spread);
+  return mask;
+}
+
+// ---- leaf of the split recursion (bands.c:966-1038) ----------------------------------------------
+template <bool REBUILD>
+CB_FN u32 b3_leaf_node(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, i16* X, int N, int b, int B,
+                       const i16* lowband, int LM, i32 gain, int fill) {
+  if (!REBUILD) {
+    int q = bits2pulses(cx.i, LM, b);
+    int curr_bits = pulses2bits(cx.i, LM, q);
+    cx.remaining_bits -= curr_bits;
+    CB_NOUNROLL while (cx.remaining_bits < 0 && q > 0) {
+      cx.remaining_bits += curr_bits;
+      q--;
+      curr_bits = pulses2bits(cx.i, LM, q);
+      cx.remaining_bits -= curr_bits;
+    }
+    if (q != 0) {
+      const int K = get_pulses(q);
+      const u32 idx = rd_uint(rd, pvq_u(N, K) + pvq_u(N, K + 1));
+      b3_push_bit(w, cur, 1);
+      if (N >= CB_B3_MIN_N) {
+        b3_push_bit(w, cur, 1);
+        CB_WSYNC();
+        b3_put_job(X, N, K, idx, gain, B, cx.spread);
+        w.b3_buf[cur.jobs++] = (u16)(X - w.X);
+        CB_WSYNC();
+      } else {
+        b3_push_bit(w, cur, 0);
+        b3_push(w, cur, (int)b3_leaf_now(w, X, N, K, idx, cx.spread, B, gain));
+      }
+    } else {
+      b3_push_bit(w, cur, 0);
+    }
+    return 0;
+  }
+  if (b3_pop_bit(w, cur)) {                                     // the leaf carries pulses: decoded already
+    if (b3_pop_bit(w, cur)) return w.b3_buf[cur.jobs++];
+    return (u32)b3_pop(w, cur);
+  }
+  u32 cm = 0;
+  const u32 cm_mask = (u32)((1ull << B) - 1);
+  fill &= (int)cm_mask;
+  CB_WSYNC();
+  if (!fill) {
+    CB_LANE_LOOP(j, N) X[j] = 0;
+    CB_WSYNC();
+  } else {
+    const u32 seed0 = cx.seed;
+    if (lowband == nullptr) {                                   // noise
+      CB_LANE_LOOP(j, N) X[j] = (i16)((i32)cb_lcg_skip(seed0, (u32)j + 1) >> 20);
+      cm = cm_mask;
+    } else {                                                    // folded spectrum, +-1/256 dither
+      CB_LANE_LOOP(j, N) {
+        const u32 sd = cb_lcg_skip(seed0, (u32)j + 1);
+        const i32 t = (sd & 0x8000u) ? 4 : -4;
+        X[j] = (i16)(lowband[j] + t);
+      }
+      cm = (u32)fill;
+    }
+    cx.seed = cb_lcg_skip(seed0, (u32)N);
+    v_renormalise(X, N, gain);
+  }
+  return cm;
+}
+
+// ---- quant_partition (bands.c:864-1040) as an explicit stack ---------------------------------------
+template <bool REBUILD>
+CB_FN u32 b3_partition(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, i16* X0, int N0, int b0, int B_0,
+                       i16* lowband0, int LM0, i32 gain0, int fill0) {
+  PartFrame* st = w.stack;
+  int sp = 0;
+  i16* const base = (i16*)&w;
+  st[0].xo = (u16)(X0 - base); st[0].lo = lowband0 ? (u16)(lowband0 - base) : (u16)0xFFFF; st[0].N = N0; st[0].b = b0; st[0].B = B_0;
+  st[0].LM = LM0; st[0].gain = gain0; st[0].fill = fill0; st[0].stage = 0;
+  u32 ret = 0;
+  CB_NOUNROLL while (sp >= 0) {
+    PartFrame& f = st[sp];
+    if (f.stage == 0) {
+      int N = f.N, b = f.b, B = f.B, LM = f.LM, fill = f.fill;
+      int split;
+      if (!REBUILD) {
+        const u8* cache = pulse_cache(cx.i, LM);
+        split = LM != -1 && b > cache[cache[0]] + 12 && N > 2;
+        b3_push_bit(w, cur, split);
+      } else {
+        split = b3_pop_bit(w, cur);
+      }
+      if (split) {
+        const int B0 = B;
+        N >>= 1;
+        LM -= 1;
+        if (B == 1) fill = (fill & 1) | (fill << 1);
+        B = (B + 1) >> 1;
+        int itheta, imid, iside, mid_first;
+        int mbits = 0, sbits = 0;
+        if (!REBUILD) {
+          Split& s = w.sp_store;
+          dec_theta(rd, s, cx.i, cx.intensity, cx.remaining_bits, N, b, B, B0, LM, 0, fill);
+          b = s.b;
+          int delta = s.delta;
+          itheta = s.itheta; imid = s.imid; iside = s.iside;
+          const int s_qalloc = s.qalloc;
+          if (B0 > 1 && (itheta & 0x3fff)) {
+            if (itheta > 8192) delta -= delta >> (4 - LM);
+            else delta = cb_imin(0, delta + (N << CB_BITRES >> (5 - LM)));
+          }
+          mbits = cb_imax(0, cb_imin(b, (b - delta) / 2));
+          sbits = b - mbits;
+          cx.remaining_bits -= s_qalloc;
+          mid_first = mbits >= sbits;
+          b3_push(w, cur, itheta);
+          b3_push_bit(w, cur, mid_first);
+        } else {
+          itheta = b3_pop(w, cur);
+          mid_first = b3_pop_bit(w, cur);
+          if (itheta == 0) {
+            imid = 32767; iside = 0;
+            fill &= (1 << B) - 1;
+          } else if (itheta == 16384) {
+            imid = 0; iside = 32767;
+            fill &= ((1 << B) - 1) << B;
+          } else {
+            imid = bitexact_cos((i16)itheta);
+            iside = bitexact_cos((i16)(16384 - itheta));
+          }
+        }
+        f.N = N; f.B = B; f.LM = LM; f.fill = fill; f.B0 = B0;
+        f.mbits = mbits; f.sbits = sbits; f.itheta = itheta;
+        f.rebal0 = cx.remaining_bits;
+        f.gmid = mult16_16_p15(f.gain, imid);
+        f.gside = mult16_16_p15(f.gain, iside);
+        f.stage = mid_first ? 1 : 3;             // 1: mid first, 3: side first
+        PartFrame& c = st[sp + 1];
+        c.N = N; c.B = B; c.LM = LM; c.stage = 0;
+        if (mid_first) {
+          c.xo = f.xo; c.lo = f.lo; c.b = mbits; c.gain = (i16)f.gmid; c.fill = fill;
+        } else {
+          c.xo = f.xo + N; c.lo = f.lo != 0xFFFF ? f.lo + N : 0xFFFF; c.b = sbits;
+          c.gain = (i16)f.gside; c.fill = fill >> B;
+        }
+        sp++;
+      } else {
+        ret = b3_leaf_node<REBUILD>(w, cx, rd, cur, base + f.xo, N, b, B, f.lo != 0xFFFF ? base + f.lo : nullptr, LM, f.gain,
+                                    fill);
+        sp--;
+      }
+    } else if (f.stage == 1) {                   // mid done, now side
+      f.cm = (u16)ret;
+      if (!REBUILD) {
+        const i32 rebalance = f.mbits - (f.rebal0 - cx.remaining_bits);
+        if (rebalance > 3 << CB_BITRES && f.itheta != 0) f.sbits += rebalance - (3 << CB_BITRES);
+      }
+      PartFrame& c = st[sp + 1];
+      c.N = f.N; c.B = f.B; c.LM = f.LM; c.stage = 0;
+      c.xo = f.xo + f.N; c.lo = f.lo != 0xFFFF ? f.lo + f.N : 0xFFFF; c.b = f.sbits;
+      c.gain = (i16)f.gside; c.fill = f.fill >> f.B;
+      f.stage = 2;
+      sp++;
+    } else if (f.stage == 2) {
+      ret = (u32)f.cm | (ret << (f.B0 >> 1));
+      sp--;
+    } else if (f.stage == 3) {                   // side done, now mid
+      f.cm = (u16)(ret << (f.B0 >> 1));
+      if (!REBUILD) {
+        const i32 rebalance = f.sbits - (f.rebal0 - cx.remaining_bits);
+        if (rebalance > 3 << CB_BITRES && f.itheta != 16384) f.mbits += rebalance - (3 << CB_BITRES);
+      }
+      PartFrame& c = st[sp + 1];
+      c.N = f.N; c.B = f.B; c.LM = f.LM; c.stage = 0;
+      c.xo = f.xo; c.lo = f.lo; c.b = f.mbits; c.gain = (i16)f.gmid; c.fill = f.fill;
+      f.stage = 4;
+      sp++;
+    } else {
+      ret = (u32)f.cm | ret;
+      sp--;
+    }
+  }
+  return ret;
+}
+
+// ---- quant_band (bands.c:1044-1172) ----------------------------------------------------------------
+template <bool REBUILD>
+CB_FN u32 b3_band(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, i16* X, int N, int b, int B, i16* lowband,
+                  int LM, i16* lowband_out, i32 gain, i16* lowband_scratch, int fill) {
+  const int N0 = N;
+  int N_B = N / B, B0 = B;
+  int time_divide = 0, recombine = 0;
+  const int longBlocks = B0 == 1;
+  int tf_change = cx.tf_change;
+  i16* tmp = (i16*)w.tmp32;
+  if (N == 1) {                                                  // quant_band_n1 (bands.c:819-858), one channel
+    if (!REBUILD) {
+      int sign = 0;
+      if (cx.remaining_bits >= 1 << CB_BITRES) {
+        sign = (int)rd_bits(rd, 1);
+        cx.remaining_bits -= 1 << CB_BITRES;
+      }
+      X[0] = sign ? -CB_NORM_SCALING : CB_NORM_SCALING;
+    } else if (lowband_out) {
+      lowband_out[0] = (i16)(X[0] >> 4);
+    }
+    return 1;
+  }
+  if (tf_change > 0) recombine = tf_change;
+  if (REBUILD) {
+    if (lowband_scratch && lowband && (recombine || ((N_B & 1) == 0 && tf_change < 0) || B0 > 1)) {
+      CB_WSYNC();
+      CB_LANE_LOOP(j, N) lowband_scratch[j] = lowband[j];
+      CB_WSYNC();
+      lowband = lowband_scratch;
+    }
+  }
+  CB_NOUNROLL for (int k = 0; k < recombine; k++) {
+    if (REBUILD) {
+      if (lowband) v_haar1(lowband, N >> k, 1 << k);
+      fill = ct_bit_interleave[fill & 0xF] | ct_bit_interleave[fill >> 4] << 2;
+    }
+  }
+  B >>= recombine;
+  N_B <<= recombine;
+  CB_NOUNROLL while ((N_B & 1) == 0 && tf_change < 0) {
+    if (REBUILD) {
+      if (lowband) v_haar1(lowband, N_B, B);
+      fill |= fill << B;
+    }
+    B <<= 1;
+    N_B >>= 1;
+    time_divide++;
+    tf_change++;
+  }
+  B0 = B;
+  const int N_B0 = N_B;
+  if (REBUILD && B0 > 1 && lowband) v_deinterleave(lowband, tmp, N_B >> recombine, B0 << recombine, longBlocks);
+
+  u32 cm = b3_partition<REBUILD>(w, cx, rd, cur, X, N, b, B, lowband, LM, gain, fill);
+  if (!REBUILD) return 0;
+
+  if (B0 > 1) v_interleave(X, tmp, N_B >> recombine, B0 << recombine, longBlocks);
+  N_B = N_B0;
+  B = B0;
+  CB_NOUNROLL for (int k = 0; k < time_divide; k++) {
+    B >>= 1;
+    N_B <<= 1;
+    cm |= cm >> B;
+    v_haar1(X, N_B, B);
+  }
+  CB_NOUNROLL for (int k = 0; k < recombine; k++) {
+    cm = ct_bit_deinterleave[cm];
+    v_haar1(X, N0 >> k, 1 << k);
+  }
+  B <<= recombine;
+  if (lowband_out) {
+    const i16 n = (i16)cb_sqrt(shl32(N0, 22));
+    CB_WSYNC();
+    CB_LANE_LOOP(j, N0) lowband_out[j] = (i16)mult16_16_q15(n, X[j]);
+    CB_WSYNC();
+  }
+  cm &= (u32)((1 << B) - 1);
+  return cm;
+}
+
+// What the two walks carry from band to band.
+struct B3Parse { i32 balance; int dual_stereo; };
+struct B3Rebuild { int dual_stereo, lowband_offset, update_lowband; };
+
+// One band of quant_all_bands, with quant_band_stereo (bands.c:1176-1334) folded in.
+template <bool REBUILD>
+CB_FN void b3_one_band(EntWork& w, RangeDec& rd, B3Cur& cur, BandCtx& cx, B3Parse& ps, B3Rebuild& rs, int i, int start,
+                       int end, int C, int Nfrm, int B, int spread, int intensity, i32 total_bits, int LM, int codedBands) {
+  const int M = 1 << LM;
+  i16* X_ = w.X;
+  i16* Y_ = C == 2 ? w.X + Nfrm : nullptr;
+  const int norm_offset = M * ebands(start);
+  i16* norm = w.norm;
+  i16* norm2 = w.norm + CB_NORM_STRIDE;
+  const int last = (i == end - 1);
+  i16* lowband_scratch = last ? nullptr : X_ + M * ebands(CB_NBANDS - 1);
+  cx.i = i;
+  i16* X = X_ + M * ebands(i);
+  i16* Y = Y_ ? Y_ + M * ebands(i) : nullptr;
+  const int N = M * ebands(i + 1) - M * ebands(i);
+  const int tf_change = w.tf_res[i];
+  cx.tf_change = tf_change;
+  int b = 0;
+  i32 tell = 0;
+  if (!REBUILD) {
+    tell = (i32)rd_tell_frac(rd);
+    if (i != start) ps.balance -= tell;
+    const i32 remaining_bits = total_bits - tell - 1;
+    cx.remaining_bits = remaining_bits;
+    if (i <= codedBands - 1) {
+      const i32 curr_balance = ps.balance / cb_imin(3, codedBands - i);     // celt_sudiv
+      b = cb_imax(0, cb_imin(16383, cb_imin(remaining_bits + 1, w.pulses[i] + curr_balance)));
+    }
+  }
+  // folding source and the collapse masks it brings (REBUILD only)
+  i16 *lb = nullptr, *lb2 = nullptr, *lout = nullptr, *lout2 = nullptr;
+  u32 x_cm = 0, y_cm = 0;
+  if (REBUILD) {
+    if (M * ebands(i) - N >= M * ebands(start) && (rs.update_lowband || rs.lowband_offset == 0)) rs.lowband_offset = i;
+    int effective_lowband = -1;
+    if (rs.lowband_offset != 0 && (spread != CB_SPREAD_AGGRESSIVE || B > 1 || tf_change < 0)) {
+      effective_lowband = cb_imax(0, M * ebands(rs.lowband_offset) - norm_offset - N);
+      int fold_start = rs.lowband_offset;
+      CB_NOUNROLL while (M * ebands(--fold_start) > effective_lowband + norm_offset) {}
+      int fold_end = rs.lowband_offset - 1;
+      CB_NOUNROLL while (M * ebands(++fold_end) < effective_lowband + norm_offset + N) {}
+      int fold_i = fold_start;
+      CB_NOUNROLL do {
+        x_cm |= w.collapse[fold_i * C + 0];
+        y_cm |= w.collapse[fold_i * C + C - 1];
+      } while (++fold_i < fold_end);
+    } else {
+      x_cm = y_cm = (u32)((1 << B) - 1);
+    }
+    if (effective_lowband != -1) { lb = norm + effective_lowband; lb2 = norm2 + effective_lowband; }
+    if (!last) { lout = norm + M * ebands(i) - norm_offset; lout2 = norm2 + M * ebands(i) - norm_offset; }
+  }
+  int& dual_stereo = REBUILD ? rs.dual_stereo : ps.dual_stereo;
+  if (dual_stereo && i == intensity) {
+    dual_stereo = 0;
+    if (REBUILD) {
+      const int cnt = M * ebands(i) - norm_offset;
+      CB_WSYNC();
+      CB_LANE_LOOP(j, cnt) norm[j] = (i16)(((i32)norm[j] + (i32)norm2[j]) >> 1);
+      CB_WSYNC();
+    }
+  }
+  // The band decoder is big: it is instantiated at ONE call site per walk (instruction-cache footprint is what
+  // bounds this kernel), so the cases below only describe up to two calls -- the channel vector, its bit
+  // budget, gain and folding inputs -- and a loop makes them.
+  int mode;                       // 0 mono, 1 dual stereo, 2 joint stereo N > 2, 3 joint stereo N == 2, 4 done (N == 1)
+  int njobs = 0;
+  i16 *jX0 = X, *jX1 = Y;
+  int jb0 = 0, jb1 = 0, jfill0 = 0, jfill1 = 0;
+  i32 jgain1 = CB_Q15ONE;
+  bool j1_fold = true;            // second call gets lowband / lowband_out / scratch (dual stereo) or none (side)
+  int itheta = 0, inv = 0, imid = 0, iside = 0;
+  int mbits = 0, sbits = 0, mid_first = 1, n2_sign = 1;
+  i32 rebalance0 = 0;
+  u32 cm = 0;
+  if (dual_stereo) {
+    mode = 1;
+    njobs = 2;
+    jb0 = jb1 = b / 2;
+    jfill0 = (int)x_cm; jfill1 = (int)y_cm;
+  } else if (Y == nullptr) {
+    mode = 0;
+    njobs = 1;
+    jb0 = b;
+    jfill0 = (int)(x_cm | y_cm);
+  } else if (N == 1) {                                           // quant_band_n1 on both channels (bands.c:819-858)
+    mode = 4;
+    if (!REBUILD) {
+      i16* x = X;
+      CB_NOUNROLL for (int c = 0; c < 2; c++) {
+        int sign = 0;
+        if (cx.remaining_bits >= 1 << CB_BITRES) {
+          sign = (int)rd_bits(rd, 1);
+          cx.remaining_bits -= 1 << CB_BITRES;
+        }
+        x[0] = sign ? -CB_NORM_SCALING : CB_NORM_SCALING;
+        x = Y;
+      }
+    } else if (lout) {
+      lout[0] = (i16)(X[0] >> 4);
+    }
+    cm = 1;
+  } else {
+    // stereo split (compute_theta with stereo = 1, bands.c:1200-1220)
+    int fill = (int)(x_cm | y_cm);
+    const int orig_fill = fill;
+    if (!REBUILD) {
+      Split& sh = w.sp_store;
+      dec_theta(rd, sh, cx.i, cx.intensity, cx.remaining_bits, N, b, B, B, LM, 1, fill);
+      const Split s = sh;
+      itheta = s.itheta; inv = s.inv; imid = s.imid; iside = s.iside;
+      b3_push(w, cur, itheta);
+      b3_push_bit(w, cur, inv);
+      if (N == 2) {
+        mbits = s.b;
+        sbits = 0;
+        if (itheta != 0 && itheta != 16384) sbits = 1 << CB_BITRES;
+        mbits -= sbits;
+        cx.remaining_bits -= s.qalloc + sbits;
+        int sign = 0;
+        if (sbits) sign = (int)rd_bits(rd, 1);
+        b3_push_bit(w, cur, sign);
+      } else {
+        mbits = cb_imax(0, cb_imin(s.b, (s.b - s.delta) / 2));
+        sbits = s.b - mbits;
+        cx.remaining_bits -= s.qalloc;
+        rebalance0 = cx.remaining_bits;
+        mid_first = mbits >= sbits;
+        b3_push_bit(w, cur, mid_first);
+      }
+    } else {
+      itheta = b3_pop(w, cur);
+      inv = b3_pop_bit(w, cur);
+      if (itheta == 0) {
+        imid = 32767; iside = 0;
+        fill &= (1 << B) - 1;
+      } else if (itheta == 16384) {
+        imid = 0; iside = 32767;
+        fill &= ((1 << B) - 1) << B;
+      } else {
+        imid = bitexact_cos((i16)itheta);
+        iside = bitexact_cos((i16)(16384 - itheta));
+      }
+      if (N == 2) n2_sign = 1 - 2 * b3_pop_bit(w, cur);
+      else mid_first = b3_pop_bit(w, cur);
+    }
+    if (N == 2) {
+      mode = 3;
+      njobs = 1;
+      jX0 = itheta > 8192 ? Y : X;
+      jb0 = mbits;
+      jfill0 = orig_fill;
+    } else {
+      mode = 2;
+      njobs = 2;
+      j1_fold = false;
+      jgain1 = iside;
+      jX0 = X; jb0 = mbits; jfill0 = fill;                       // the mid call, always described in slot 0 ...
+      jX1 = Y; jb1 = sbits; jfill1 = fill >> B;                  // ... the side call in slot 1; mid_first picks the order
+    }
+  }
+  u32 cm0 = 0, cm1 = 0;
+  CB_NOUNROLL for (int jn = 0; jn < njobs; jn++) {
+    const int slot = (mode == 2 && !mid_first) ? 1 - jn : jn;    // which description this call uses
+    i32 jb = slot ? jb1 : jb0;
+    if (!REBUILD && mode == 2 && jn == 1) {
+      const i32 first_bits = mid_first ? mbits : sbits;
+      const i32 rebalance = first_bits - (rebalance0 - cx.remaining_bits);
+      const int blocked = mid_first ? (itheta == 0) : (itheta == 16384);
+      if (rebalance > 3 << CB_BITRES && !blocked) jb += rebalance - (3 << CB_BITRES);
+    }
+    const bool fold = slot == 0 || j1_fold;
+    const u32 r = b3_band<REBUILD>(w, cx, rd, cur, slot ? jX1 : jX0, N, jb, B, fold ? (slot ? lb2 : lb) : nullptr, LM,
+                                   fold ? (slot ? lout2 : lout) : nullptr, slot ? jgain1 : (i32)CB_Q15ONE,
+                                   fold ? lowband_scratch : nullptr, slot ? jfill1 : jfill0);
+    if (slot == 0) cm0 = r; else cm1 = r;
+  }
+  if (mode == 0) {
+    x_cm = y_cm = cm0;
+  } else if (mode == 1) {
+    x_cm = cm0;
+    y_cm = cm1;
+  } else if (mode == 4) {
+    x_cm = y_cm = cm;
+  } else {
+    if (mode == 3) {
+      if (REBUILD) {
+        i16* x2 = itheta > 8192 ? Y : X;
+        i16* y2 = itheta > 8192 ? X : Y;
+        CB_WSYNC();
+        y2[0] = (i16)(-n2_sign * x2[1]);
+        y2[1] = (i16)(n2_sign * x2[0]);
+        const i16 X0 = (i16)mult16_16_q15(imid, X[0]);
+        const i16 X1 = (i16)mult16_16_q15(imid, X[1]);
+        const i16 Y0 = (i16)mult16_16_q15(iside, Y[0]);
+        const i16 Y1 = (i16)mult16_16_q15(iside, Y[1]);
+        CB_WSYNC();
+        X[0] = (i16)sub16(X0, Y0);
+        Y[0] = add16(X0, Y0);
+        X[1] = (i16)sub16(X1, Y1);
+        Y[1] = add16(X1, Y1);
+        CB_WSYNC();
+      }
+      cm = cm0;
+    } else {
+      cm = cm0 | cm1;
+      if (REBUILD) v_stereo_merge(X, Y, imid, N);
+    }
+    if (REBUILD && inv) {
+      CB_WSYNC();
+      CB_LANE_LOOP(j, N) Y[j] = (i16)(-Y[j]);
+      CB_WSYNC();
+    }
+    x_cm = y_cm = cm;
+  }
+  if (!REBUILD) {
+    ps.balance += w.pulses[i] + tell;
+    b3_push_bit(w, cur, b > (N << CB_BITRES));
+  } else {
+    w.collapse[i * C + 0] = (u8)x_cm;
+    w.collapse[i * C + C - 1] = (u8)y_cm;
+    rs.update_lowband = b3_pop_bit(w, cur);
+  }
+}
+
+// quant_all_bands (bands.c:1337-1502), decoder side.  Same interface as dec_all_bands.
+CB_FN void dec_all_bands3(EntWork& w, RangeDec& rd, int start, int end, int C, int Nfrm, int shortBlocks,
+                          int spread, int dual_stereo, int intensity, i32 total_bits, i32 balance,
+                          int LM, int codedBands, u32& seed) {
+  const int M = 1 << LM;
+  const int B = shortBlocks ? M : 1;
+  BandCtx cxp, cxr;
+  cxp.intensity = cxr.intensity = intensity;
+  cxp.spread = cxr.spread = spread;
+  cxp.seed = 0;
+  cxr.seed = seed;
+  cxr.remaining_bits = 0;
+  B3Parse ps;
+  ps.balance = balance;
+  ps.dual_stereo = dual_stereo;
+  B3Rebuild rs;
+  rs.dual_stereo = dual_stereo;
+  rs.lowband_offset = 0;
+  rs.update_lowband = 1;
+  B3Cur wr;
+  wr.jobs = wr.tape = wr.bits = 0;
+  CB_WSYNC();
+  CB_LANE_LOOP(j, CB_B3_BITWORDS) w.b3_bits[j] = 0;
+  CB_WSYNC();
+  int first = start;                     // first band parsed but not yet rebuilt
+  CB_NOUNROLL for (int i = start; i <= end; i++) {
+    // finish what has been parsed when the tape could not take another band, before the band whose
+    // spectrum slot doubles as scratch for the others (the last band of the mode), and at the end
+    bool full = false;
+    if (i < end) {
+      const int L = b3_band_leaves(M * (ebands(i + 1) - ebands(i)), LM);
+      full = wr.jobs + wr.tape + 4 * L + 2 > CB_B3_BUF || wr.bits + 10 * L + 4 > 32 * CB_B3_BITWORDS;
+    }
+    if (i > first && (i == end || full || i == CB_NBANDS - 1)) {
+      b3_run_jobs(w, wr.jobs);
+      B3Cur rdc;
+      rdc.jobs = rdc.tape = rdc.bits = 0;
+      CB_NOUNROLL for (int r = first; r < i; r++)
+        b3_one_band<true>(w, rd, rdc, cxr, ps, rs, r, start, end, C, Nfrm, B, spread, intensity, total_bits, LM, codedBands);
+      first = i;
+      wr.jobs = wr.tape = wr.bits = 0;
+      CB_WSYNC();
+      CB_LANE_LOOP(j, CB_B3_BITWORDS) w.b3_bits[j] = 0;
+      CB_WSYNC();
+    }
+    if (i < end)
+      b3_one_band<false>(w, rd, wr, cxp, ps, rs, i, start, end, C, Nfrm, B, spread, intensity, total_bits, LM, codedBands);
+  }
+  seed = cxr.seed;
+}

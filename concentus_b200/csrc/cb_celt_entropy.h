@@ -42,10 +42,10 @@ CB_UTABLE u8 ct_bit_deinterleave[16] = {0x00, 0x03, 0x0C, 0x0F, 0x30, 0x33, 0x3C
 struct Split { int inv, imid, iside, delta, itheta, qalloc, b, fill; };   // b/fill: updated in/out values
 
 // One level of the split recursion (quant_partition), kept in shared memory.
-struct PartFrame {
-  i16* X; i16* lowband;
-  i32 N, b, B, LM, gain, fill;
-  i32 stage, mbits, sbits, itheta, rebal0, B0, cm, gmid, gside;
+struct PartFrame {                // positions are 16-bit word offsets from the start of EntWork (0xFFFF: none)
+  i32 b, mbits, sbits, rebal0;
+  u16 xo, lo, cm, fill;
+  i16 N, B, LM, gain, stage, itheta, B0, gmid, gside, pad;
 };
 
 // Per-warp shared-memory workspace of kernel A.
@@ -62,8 +62,13 @@ struct alignas(16) EntWork {
   i8 tf_res[CB_NBANDS];
   u8 collapse[2 * CB_NBANDS];
   PartFrame stack[5];
+#ifdef CB_BANDS_ONE_PHASE
   struct BandJobS { i16* X; i16* lowband; i16* lowband_out; i16* scratch; i32 b, gain, fill, pad; } jobs[2];
+#endif
   Split sp_store;                // result record of dec_theta
+  u16 b3_buf[176];               // cb_celt_bands3.h: pending leaves (X offset, then collapse mask) from the front,
+                                 //   split angles and other 16-bit notes of the parse walk from the back
+  u32 b3_bits[16];               //   one or two bits per node of the walk
   RangeDec rd;                   // coder registers; in shared memory so the rd_* routines can be real calls
 };
 
@@ -382,6 +387,7 @@ CB_FN_NOINLINE void dec_theta(RangeDec& rd, Split& sp, int band, int intensity, 
   sp.b = b; sp.fill = fill;
 }
 
+#ifdef CB_BANDS_ONE_PHASE
 // ---- leaf of the split recursion (bands.c:966-1038, decoder side) ---------------------------
 CB_FN u32 part_leaf(EntWork& w, BandCtx& cx, RangeDec& rd, i16* X, int N, int b, int B,
                     const i16* lowband, int LM, i32 gain, int fill) {
@@ -581,6 +587,8 @@ CB_FN u32 dec_band(EntWork& w, BandCtx& cx, RangeDec& rd, i16* X, int N, int b, 
   return cm;
 }
 
+#endif  // CB_BANDS_ONE_PHASE
+
 // stereo_merge (bands.c:375-425)
 CB_FN void v_stereo_merge(i16* X, i16* Y, i32 mid, int N) {
   CB_WSYNC();
@@ -614,6 +622,7 @@ CB_FN void v_stereo_merge(i16* X, i16* Y, i32 mid, int N) {
   CB_WSYNC();
 }
 
+#ifdef CB_BANDS_ONE_PHASE
 // One call of quant_band() as data, so that the (large) band decoder is instantiated at exactly
 // one call site: instruction-cache footprint is what bounds this kernel (see profiles/).
 
@@ -802,6 +811,10 @@ CB_FN void dec_all_bands(EntWork& w, RangeDec& rd, int start, int end, int C, in
   }
   seed = cx.seed;
 }
+
+#endif  // CB_BANDS_ONE_PHASE
+
+#include "cb_celt_bands3.h"
 
 // anti_collapse (bands.c:241-335)
 CB_FN void v_anti_collapse(EntWork& w, int LM, int C, int Nfrm, int start, int end, const i16* logE,
@@ -1247,7 +1260,11 @@ CB_FN int celt_entropy_decode(EntWork& w, CeltDecState* stg, FrameSide* side, co
   dec_fine_energy(w, rd, start, end, C);
 
   u32 seed = stg->rng;
+#ifndef CB_BANDS_ONE_PHASE
+  dec_all_bands3(w, rd, start, end, C, N, shortBlocks, spread_decision, dual_stereo, intensity,
+#else
   dec_all_bands(w, rd, start, end, C, N, shortBlocks, spread_decision, dual_stereo, intensity,
+#endif
                 len * (8 << CB_BITRES) - anti_collapse_rsv, balance, LM, codedBands, seed);
   int anti_collapse_on = 0;
   if (anti_collapse_rsv > 0) anti_collapse_on = (int)rd_bits(rd, 1);

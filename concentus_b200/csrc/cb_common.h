@@ -15,6 +15,7 @@
 #include <stdint.h>
 
 typedef int16_t i16;
+typedef uint16_t u16;
 typedef int32_t i32;
 typedef uint32_t u32;
 typedef int64_t i64;

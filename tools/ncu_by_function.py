@@ -4,7 +4,7 @@ of the same .so, and aggregate by source function.
 usage: ncu_by_function.py <source.csv> <lib.so> <kernel-substring>"""
 import collections, csv, os, re, subprocess, sys, tempfile
 
-HELPER_FILES = ("cb_common.h", "cb_silk_common.h", "cb_rangedec.h", "sm_30_intrinsics.hpp", "sm_32_intrinsics.hpp", "sm_80_rt.hpp", "device_functions.hpp")
+HELPER_FILES = ("cb_common.h", "sm_30_intrinsics.hpp", "sm_32_intrinsics.hpp", "sm_80_rt.hpp", "device_functions.hpp")
 
 def sass_lines(lib, pat, outer=True):
     """One (file, line) per SASS instruction of the sections matching pat.  With outer=True an
