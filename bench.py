@@ -55,6 +55,20 @@ def read_bit(path):
     return out
 
 
+def ncu_traffic():
+    """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
+    (profiles/r01_entropy_ncu_raw.txt: dram__bytes_read.sum + dram__bytes_write.sum), or None."""
+    tot, unit = 0.0, {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    try:
+        for line in open(os.path.join(ROOT, "profiles", "r01_entropy_ncu_raw.txt")):
+            f = line.split()
+            if len(f) == 3 and f[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                tot += float(f[2]) * unit[f[1]]
+    except (OSError, KeyError, ValueError):
+        return None
+    return tot or None
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -327,7 +341,7 @@ def main():
         "gpu_launches": int(launches),
         "clocks": sampler.summary(),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_kind": peak_kind,
+                     "frac": achieved / peak, "traffic": ncu_traffic(), "peak_kind": peak_kind,
                      "kernel": ["plan_silk_kernel", "celt_entropy_kernel", "celt_synth_kernel"][dom],
                      "kernel_ms": {"plan": kern_ms[0], "entropy": kern_ms[1], "synth": kern_ms[2]},
                      "algorithmic_bytes_per_launch": alg_bytes,

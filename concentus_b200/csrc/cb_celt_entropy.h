@@ -62,9 +62,6 @@ struct alignas(16) EntWork {
   i8 tf_res[CB_NBANDS];
   u8 collapse[2 * CB_NBANDS];
   PartFrame stack[5];
-#ifdef CB_BANDS_ONE_PHASE
-  struct BandJobS { i16* X; i16* lowband; i16* lowband_out; i16* scratch; i32 b, gain, fill, pad; } jobs[2];
-#endif
   Split sp_store;                // result record of dec_theta
   u16 b3_buf[176];               // cb_celt_bands3.h: pending leaves (X offset, then collapse mask) from the front,
                                  //   split angles and other 16-bit notes of the parse walk from the back
@@ -201,22 +198,12 @@ CB_FN void v_exp_rotation_dec(i16* X, int len, int stride, int K, int spread) {
 }
 
 // ---- PVQ index -> pulse vector (cwrs.c:463-541), uniform; every lane stores the same values ---
-#ifdef CB_PVQ_STATS
-static long g_pvq_calls, g_pvq_n, g_pvq_k, g_pvq_dense_pos, g_pvq_sparse_pos, g_pvq_sparse_nz, g_pvq_hist[8];
-#endif
 CB_FN i32 pvq_decode(i16* y, int n, int k, u32 i) {
-#ifdef CB_PVQ_STATS
-  g_pvq_calls++; g_pvq_n += n; g_pvq_k += k;
-  { int r = k ? n / k : 99; g_pvq_hist[r >= 7 ? 7 : r] += n; }
-#endif
   i32 yy = 0;
   u32 p, q;
   int s, k0;
   i16 val;
   CB_NOUNROLL while (n > 2) {
-#ifdef CB_PVQ_STATS
-    if (k >= n) g_pvq_dense_pos++; else g_pvq_sparse_pos++;
-#endif
     if (k >= n) {
       int rowoff = ct_pvq_u_row[n];
       p = ct_pvq_u_data[rowoff + k + 1];
@@ -267,29 +254,6 @@ CB_FN i32 pvq_decode(i16* y, int n, int k, u32 i) {
   *y = val;
   yy = mac16_16(yy, val, val);
   return yy;
-}
-
-// alg_unquant (vq.c:329-347)
-CB_FN u32 alg_unquant(EntWork& w, RangeDec& rd, i16* X, int N, int K, int spread, int B, i32 gain) {
-  i16* iy = (i16*)w.tmp32;
-  u32 idx = rd_uint(rd, pvq_u(N, K) + pvq_u(N, K + 1));
-  CB_WSYNC();
-  i32 Ryy = pvq_decode(iy, N, K, idx);
-  CB_WSYNC();
-  // normalise_residual (vq.c:117-137)
-  int k = cb_ilog2(Ryy) >> 1;
-  i32 t = vshr32(Ryy, 2 * (k - 7));
-  i16 g = (i16)mult16_16_p15(cb_rsqrt_norm(t), gain);
-  u32 mask = 0;
-  int N0 = N / B;
-  CB_LANE_LOOP(j, N) {
-    i32 v = iy[j];
-    X[j] = ext16(pshr32(mult16_16(g, v), k + 1));
-    if (v != 0) mask |= 1u << (j / N0);       // extract_collapse_mask (vq.c:139-159)
-  }
-  mask = B <= 1 ? 1u : cb_wor(mask);
-  v_exp_rotation_dec(X, N, B, K, spread);
-  return mask;
 }
 
 // ---- theta (bands.c:596-818, decoder side) --------------------------------------------------
@@ -387,207 +351,6 @@ CB_FN_NOINLINE void dec_theta(RangeDec& rd, Split& sp, int band, int intensity, 
   sp.b = b; sp.fill = fill;
 }
 
-#ifdef CB_BANDS_ONE_PHASE
-// ---- leaf of the split recursion (bands.c:966-1038, decoder side) ---------------------------
-CB_FN u32 part_leaf(EntWork& w, BandCtx& cx, RangeDec& rd, i16* X, int N, int b, int B,
-                    const i16* lowband, int LM, i32 gain, int fill) {
-  u32 cm = 0;
-  int q = bits2pulses(cx.i, LM, b);
-  int curr_bits = pulses2bits(cx.i, LM, q);
-  cx.remaining_bits -= curr_bits;
-  CB_NOUNROLL while (cx.remaining_bits < 0 && q > 0) {
-    cx.remaining_bits += curr_bits;
-    q--;
-    curr_bits = pulses2bits(cx.i, LM, q);
-    cx.remaining_bits -= curr_bits;
-  }
-  if (q != 0) {
-    cm = alg_unquant(w, rd, X, N, get_pulses(q), cx.spread, B, gain);
-  } else {
-    u32 cm_mask = (u32)((1ull << B) - 1);
-    fill &= (int)cm_mask;
-    CB_WSYNC();
-    if (!fill) {
-      CB_LANE_LOOP(j, N) X[j] = 0;
-      CB_WSYNC();
-    } else {
-      u32 seed0 = cx.seed;
-      if (lowband == nullptr) {               // noise
-        CB_LANE_LOOP(j, N) X[j] = (i16)((i32)cb_lcg_skip(seed0, (u32)j + 1) >> 20);
-        cm = cm_mask;
-      } else {                                // folded spectrum, +-1/256 dither
-        CB_LANE_LOOP(j, N) {
-          u32 sd = cb_lcg_skip(seed0, (u32)j + 1);
-          i32 t = (sd & 0x8000u) ? 4 : -4;
-          X[j] = (i16)(lowband[j] + t);
-        }
-        cm = (u32)fill;
-      }
-      cx.seed = cb_lcg_skip(seed0, (u32)N);
-      v_renormalise(X, N, gain);
-    }
-  }
-  return cm;
-}
-
-// ---- quant_partition (bands.c:864-1040) as an explicit stack ---------------------------------
-CB_FN u32 dec_partition(EntWork& w, BandCtx& cx, RangeDec& rd, i16* X0, int N0, int b0, int B_0,
-                        i16* lowband0, int LM0, i32 gain0, int fill0) {
-  PartFrame* st = w.stack;
-  int sp = 0;
-  st[0].X = X0; st[0].lowband = lowband0; st[0].N = N0; st[0].b = b0; st[0].B = B_0;
-  st[0].LM = LM0; st[0].gain = gain0; st[0].fill = fill0; st[0].stage = 0;
-  u32 ret = 0;
-  CB_NOUNROLL while (sp >= 0) {
-    PartFrame& f = st[sp];
-    if (f.stage == 0) {
-      int N = f.N, b = f.b, B = f.B, LM = f.LM, fill = f.fill;
-      const u8* cache = pulse_cache(cx.i, LM);
-      if (LM != -1 && b > cache[cache[0]] + 12 && N > 2) {
-        int B0 = B;
-        N >>= 1;
-        LM -= 1;
-        if (B == 1) fill = (fill & 1) | (fill << 1);
-        B = (B + 1) >> 1;
-        Split& s = w.sp_store;
-        dec_theta(rd, s, cx.i, cx.intensity, cx.remaining_bits, N, b, B, B0, LM, 0, fill);
-        b = s.b; fill = s.fill;
-        int delta = s.delta, itheta = s.itheta;
-        const int s_qalloc = s.qalloc, s_imid = s.imid, s_iside = s.iside;
-        if (B0 > 1 && (itheta & 0x3fff)) {
-          if (itheta > 8192) delta -= delta >> (4 - LM);
-          else delta = cb_imin(0, delta + (N << CB_BITRES >> (5 - LM)));
-        }
-        int mbits = cb_imax(0, cb_imin(b, (b - delta) / 2));
-        int sbits = b - mbits;
-        cx.remaining_bits -= s_qalloc;
-        f.N = N; f.B = B; f.LM = LM; f.fill = fill; f.B0 = B0;
-        f.mbits = mbits; f.sbits = sbits; f.itheta = itheta;
-        f.rebal0 = cx.remaining_bits;
-        f.gmid = mult16_16_p15(f.gain, s_imid);
-        f.gside = mult16_16_p15(f.gain, s_iside);
-        f.stage = (mbits >= sbits) ? 1 : 3;    // 1: mid first, 3: side first
-        PartFrame& c = st[sp + 1];
-        c.N = N; c.B = B; c.LM = LM; c.stage = 0;
-        if (mbits >= sbits) {
-          c.X = f.X; c.lowband = f.lowband; c.b = mbits; c.gain = (i16)f.gmid; c.fill = fill;
-        } else {
-          c.X = f.X + N; c.lowband = f.lowband ? f.lowband + N : nullptr; c.b = sbits;
-          c.gain = (i16)f.gside; c.fill = fill >> B;
-        }
-        sp++;
-      } else {
-        ret = part_leaf(w, cx, rd, f.X, N, b, B, f.lowband, LM, f.gain, fill);
-        sp--;
-      }
-    } else if (f.stage == 1) {                 // mid done, now side
-      f.cm = (i32)ret;
-      i32 rebalance = f.mbits - (f.rebal0 - cx.remaining_bits);
-      if (rebalance > 3 << CB_BITRES && f.itheta != 0) f.sbits += rebalance - (3 << CB_BITRES);
-      PartFrame& c = st[sp + 1];
-      c.N = f.N; c.B = f.B; c.LM = f.LM; c.stage = 0;
-      c.X = f.X + f.N; c.lowband = f.lowband ? f.lowband + f.N : nullptr; c.b = f.sbits;
-      c.gain = (i16)f.gside; c.fill = f.fill >> f.B;
-      f.stage = 2;
-      sp++;
-    } else if (f.stage == 2) {
-      ret = (u32)f.cm | (ret << (f.B0 >> 1));
-      sp--;
-    } else if (f.stage == 3) {                 // side done, now mid
-      f.cm = (i32)(ret << (f.B0 >> 1));
-      i32 rebalance = f.sbits - (f.rebal0 - cx.remaining_bits);
-      if (rebalance > 3 << CB_BITRES && f.itheta != 16384) f.mbits += rebalance - (3 << CB_BITRES);
-      PartFrame& c = st[sp + 1];
-      c.N = f.N; c.B = f.B; c.LM = f.LM; c.stage = 0;
-      c.X = f.X; c.lowband = f.lowband; c.b = f.mbits; c.gain = (i16)f.gmid; c.fill = f.fill;
-      f.stage = 4;
-      sp++;
-    } else {
-      ret = (u32)f.cm | ret;
-      sp--;
-    }
-  }
-  return ret;
-}
-
-// quant_band_n1 (bands.c:819-858)
-CB_FN u32 dec_band_n1(BandCtx& cx, RangeDec& rd, i16* X, i16* Y, i16* lowband_out) {
-  i16* x = X;
-  int nch = Y ? 2 : 1;
-  CB_NOUNROLL for (int c = 0; c < nch; c++) {
-    int sign = 0;
-    if (cx.remaining_bits >= 1 << CB_BITRES) {
-      sign = (int)rd_bits(rd, 1);
-      cx.remaining_bits -= 1 << CB_BITRES;
-    }
-    x[0] = sign ? -CB_NORM_SCALING : CB_NORM_SCALING;
-    x = Y;
-  }
-  if (lowband_out) lowband_out[0] = (i16)(X[0] >> 4);
-  return 1;
-}
-
-// quant_band (bands.c:1044-1172), decoder side
-CB_FN u32 dec_band(EntWork& w, BandCtx& cx, RangeDec& rd, i16* X, int N, int b, int B, i16* lowband,
-                   int LM, i16* lowband_out, i32 gain, i16* lowband_scratch, int fill) {
-  int N0 = N, N_B = N / B, B0 = B;
-  int time_divide = 0, recombine = 0;
-  int longBlocks = B0 == 1;
-  int tf_change = cx.tf_change;
-  i16* tmp = (i16*)w.tmp32;
-  if (N == 1) return dec_band_n1(cx, rd, X, nullptr, lowband_out);
-  if (tf_change > 0) recombine = tf_change;
-  if (lowband_scratch && lowband && (recombine || ((N_B & 1) == 0 && tf_change < 0) || B0 > 1)) {
-    CB_WSYNC();
-    CB_LANE_LOOP(j, N) lowband_scratch[j] = lowband[j];
-    CB_WSYNC();
-    lowband = lowband_scratch;
-  }
-  CB_NOUNROLL for (int k = 0; k < recombine; k++) {
-    if (lowband) v_haar1(lowband, N >> k, 1 << k);
-    fill = ct_bit_interleave[fill & 0xF] | ct_bit_interleave[fill >> 4] << 2;
-  }
-  B >>= recombine;
-  N_B <<= recombine;
-  CB_NOUNROLL while ((N_B & 1) == 0 && tf_change < 0) {
-    if (lowband) v_haar1(lowband, N_B, B);
-    fill |= fill << B;
-    B <<= 1;
-    N_B >>= 1;
-    time_divide++;
-    tf_change++;
-  }
-  B0 = B;
-  int N_B0 = N_B;
-  if (B0 > 1 && lowband) v_deinterleave(lowband, tmp, N_B >> recombine, B0 << recombine, longBlocks);
-
-  u32 cm = dec_partition(w, cx, rd, X, N, b, B, lowband, LM, gain, fill);
-
-  if (B0 > 1) v_interleave(X, tmp, N_B >> recombine, B0 << recombine, longBlocks);
-  N_B = N_B0;
-  B = B0;
-  CB_NOUNROLL for (int k = 0; k < time_divide; k++) {
-    B >>= 1;
-    N_B <<= 1;
-    cm |= cm >> B;
-    v_haar1(X, N_B, B);
-  }
-  CB_NOUNROLL for (int k = 0; k < recombine; k++) {
-    cm = ct_bit_deinterleave[cm];
-    v_haar1(X, N0 >> k, 1 << k);
-  }
-  B <<= recombine;
-  if (lowband_out) {
-    i16 n = (i16)cb_sqrt(shl32(N0, 22));
-    CB_WSYNC();
-    CB_LANE_LOOP(j, N0) lowband_out[j] = (i16)mult16_16_q15(n, X[j]);
-    CB_WSYNC();
-  }
-  cm &= (u32)((1 << B) - 1);
-  return cm;
-}
-
-#endif  // CB_BANDS_ONE_PHASE
 
 // stereo_merge (bands.c:375-425)
 CB_FN void v_stereo_merge(i16* X, i16* Y, i32 mid, int N) {
@@ -622,197 +385,6 @@ CB_FN void v_stereo_merge(i16* X, i16* Y, i32 mid, int N) {
   CB_WSYNC();
 }
 
-#ifdef CB_BANDS_ONE_PHASE
-// One call of quant_band() as data, so that the (large) band decoder is instantiated at exactly
-// one call site: instruction-cache footprint is what bounds this kernel (see profiles/).
-
-// quant_all_bands (bands.c:1337-1502) with quant_band_stereo (bands.c:1176-1334) folded in as a
-// small job list per band.  Decoder side.  Xc = channel-0 spectrum, channel stride = N.
-CB_FN void dec_all_bands(EntWork& w, RangeDec& rd, int start, int end, int C, int Nfrm, int shortBlocks,
-                         int spread, int dual_stereo, int intensity, i32 total_bits, i32 balance,
-                         int LM, int codedBands, u32& seed) {
-  const int M = 1 << LM;
-  const int B = shortBlocks ? M : 1;
-  i16* X_ = w.X;
-  i16* Y_ = C == 2 ? w.X + Nfrm : nullptr;
-  const int norm_offset = M * ebands(start);
-  i16* norm = w.norm;
-  i16* norm2 = w.norm + CB_NORM_STRIDE;
-  i16* lowband_scratch = X_ + M * ebands(CB_NBANDS - 1);
-  int lowband_offset = 0;
-  int update_lowband = 1;
-  BandCtx cx;
-  cx.intensity = intensity;
-  cx.seed = seed;
-  cx.spread = spread;
-  CB_NOUNROLL for (int i = start; i < end; i++) {
-    cx.i = i;
-    int last = (i == end - 1);
-    i16* X = X_ + M * ebands(i);
-    i16* Y = Y_ ? Y_ + M * ebands(i) : nullptr;
-    int N = M * ebands(i + 1) - M * ebands(i);
-    i32 tell = (i32)rd_tell_frac(rd);
-    if (i != start) balance -= tell;
-    i32 remaining_bits = total_bits - tell - 1;
-    cx.remaining_bits = remaining_bits;
-    int b;
-    if (i <= codedBands - 1) {
-      i32 curr_balance = balance / cb_imin(3, codedBands - i);     // celt_sudiv
-      b = cb_imax(0, cb_imin(16383, cb_imin(remaining_bits + 1, w.pulses[i] + curr_balance)));
-    } else {
-      b = 0;
-    }
-    if (M * ebands(i) - N >= M * ebands(start) && (update_lowband || lowband_offset == 0)) lowband_offset = i;
-    int tf_change = w.tf_res[i];
-    cx.tf_change = tf_change;
-    if (last) lowband_scratch = nullptr;
-    int effective_lowband = -1;
-    u32 x_cm, y_cm;
-    if (lowband_offset != 0 && (spread != CB_SPREAD_AGGRESSIVE || B > 1 || tf_change < 0)) {
-      effective_lowband = cb_imax(0, M * ebands(lowband_offset) - norm_offset - N);
-      int fold_start = lowband_offset;
-      CB_NOUNROLL while (M * ebands(--fold_start) > effective_lowband + norm_offset) {}
-      int fold_end = lowband_offset - 1;
-      CB_NOUNROLL while (M * ebands(++fold_end) < effective_lowband + norm_offset + N) {}
-      x_cm = y_cm = 0;
-      int fold_i = fold_start;
-      CB_NOUNROLL do {
-        x_cm |= w.collapse[fold_i * C + 0];
-        y_cm |= w.collapse[fold_i * C + C - 1];
-      } while (++fold_i < fold_end);
-    } else {
-      x_cm = y_cm = (u32)((1 << B) - 1);
-    }
-    if (dual_stereo && i == intensity) {
-      dual_stereo = 0;
-      int cnt = M * ebands(i) - norm_offset;
-      CB_WSYNC();
-      CB_LANE_LOOP(j, cnt) norm[j] = (i16)(((i32)norm[j] + (i32)norm2[j]) >> 1);
-      CB_WSYNC();
-    }
-    i16* lb = effective_lowband != -1 ? norm + effective_lowband : nullptr;
-    i16* lb2 = effective_lowband != -1 ? norm2 + effective_lowband : nullptr;
-    i16* lout = last ? nullptr : norm + M * ebands(i) - norm_offset;
-    i16* lout2 = last ? nullptr : norm2 + M * ebands(i) - norm_offset;
-
-    // ---- build the job list for this band (kept in shared memory: two fixed slots) ----
-    EntWork::BandJobS* J = w.jobs;
-    int njobs = 0;
-    int mode;                       // 0 mono, 1 dual stereo, 2 joint stereo N>2, 3 joint stereo N==2, 4 done
-    Split s;
-    s.inv = 0; s.itheta = 0; s.imid = 0; s.iside = 0; s.delta = 0; s.qalloc = 0; s.b = 0; s.fill = 0;
-    int mbits = 0, sbits = 0, mid_first = 1, n2_swap = 0, n2_sign = 1;
-    i32 rebalance0 = 0;
-    u32 cm = 0;
-    if (dual_stereo) {
-      mode = 1;
-      J[0].X = X; J[0].lowband = lb; J[0].lowband_out = lout; J[0].scratch = lowband_scratch; J[0].b = b / 2; J[0].gain = CB_Q15ONE; J[0].fill = (i32)x_cm;
-      J[1].X = Y; J[1].lowband = lb2; J[1].lowband_out = lout2; J[1].scratch = lowband_scratch; J[1].b = b / 2; J[1].gain = CB_Q15ONE; J[1].fill = (i32)y_cm;
-      njobs = 2;
-    } else if (Y == nullptr) {
-      mode = 0;
-      J[0].X = X; J[0].lowband = lb; J[0].lowband_out = lout; J[0].scratch = lowband_scratch; J[0].b = b; J[0].gain = CB_Q15ONE; J[0].fill = (i32)(x_cm | y_cm);
-      njobs = 1;
-    } else if (N == 1) {
-      mode = 4;
-      cm = dec_band_n1(cx, rd, X, Y, lout);
-    } else {
-      int fill = (int)(x_cm | y_cm);
-      const int orig_fill = fill;
-      int bb = b;
-      {
-        Split& sh = w.sp_store;
-        dec_theta(rd, sh, cx.i, cx.intensity, cx.remaining_bits, N, bb, B, B, LM, 1, fill);
-        s = sh;
-        bb = s.b; fill = s.fill;
-      }
-      if (N == 2) {
-        mode = 3;
-        mbits = bb;
-        sbits = 0;
-        if (s.itheta != 0 && s.itheta != 16384) sbits = 1 << CB_BITRES;
-        mbits -= sbits;
-        n2_swap = s.itheta > 8192;
-        cx.remaining_bits -= s.qalloc + sbits;
-        int sign = 0;
-        if (sbits) sign = (int)rd_bits(rd, 1);
-        n2_sign = 1 - 2 * sign;
-        J[0].X = n2_swap ? Y : X; J[0].lowband = lb; J[0].lowband_out = lout; J[0].scratch = lowband_scratch;
-        J[0].b = mbits; J[0].gain = CB_Q15ONE; J[0].fill = orig_fill;
-        njobs = 1;
-      } else {
-        mode = 2;
-        mbits = cb_imax(0, cb_imin(bb, (bb - s.delta) / 2));
-        sbits = bb - mbits;
-        cx.remaining_bits -= s.qalloc;
-        rebalance0 = cx.remaining_bits;
-        mid_first = mbits >= sbits;
-        const int im = mid_first ? 0 : 1, is = 1 - im;      // slot of the mid / side job
-        J[im].X = X; J[im].lowband = lb; J[im].lowband_out = lout; J[im].scratch = lowband_scratch; J[im].b = mbits; J[im].gain = CB_Q15ONE; J[im].fill = fill;
-        J[is].X = Y; J[is].lowband = nullptr; J[is].lowband_out = nullptr; J[is].scratch = nullptr; J[is].b = sbits; J[is].gain = s.iside; J[is].fill = fill >> B;
-        njobs = 2;
-      }
-    }
-    // ---- run the jobs: the one and only call site of dec_band ----
-    u32 cm0 = 0, cm1 = 0;
-    CB_NOUNROLL for (int jn = 0; jn < njobs; jn++) {
-      i32 jb = J[jn].b;
-      if (mode == 2 && jn == 1) {
-        i32 first_bits = mid_first ? mbits : sbits;
-        i32 rebalance = first_bits - (rebalance0 - cx.remaining_bits);
-        int blocked = mid_first ? (s.itheta == 0) : (s.itheta == 16384);
-        if (rebalance > 3 << CB_BITRES && !blocked) jb += rebalance - (3 << CB_BITRES);
-      }
-      u32 r = dec_band(w, cx, rd, J[jn].X, N, jb, B, J[jn].lowband, LM, J[jn].lowband_out, J[jn].gain, J[jn].scratch,
-                       J[jn].fill);
-      if (jn == 0) cm0 = r; else cm1 = r;
-    }
-    // ---- per-mode epilogue ----
-    if (mode == 0) {
-      x_cm = y_cm = cm0;
-    } else if (mode == 1) {
-      x_cm = cm0;
-      y_cm = cm1;
-    } else if (mode == 4) {
-      x_cm = y_cm = cm;
-    } else {
-      if (mode == 3) {
-        i16* x2 = n2_swap ? Y : X;
-        i16* y2 = n2_swap ? X : Y;
-        CB_WSYNC();
-        y2[0] = (i16)(-n2_sign * x2[1]);
-        y2[1] = (i16)(n2_sign * x2[0]);
-        i16 X0 = (i16)mult16_16_q15(s.imid, X[0]);
-        i16 X1 = (i16)mult16_16_q15(s.imid, X[1]);
-        i16 Y0 = (i16)mult16_16_q15(s.iside, Y[0]);
-        i16 Y1 = (i16)mult16_16_q15(s.iside, Y[1]);
-        CB_WSYNC();
-        X[0] = (i16)sub16(X0, Y0);
-        Y[0] = add16(X0, Y0);
-        X[1] = (i16)sub16(X1, Y1);
-        Y[1] = add16(X1, Y1);
-        CB_WSYNC();
-        cm = cm0;
-      } else {
-        cm = cm0 | cm1;
-        v_stereo_merge(X, Y, s.imid, N);
-      }
-      if (s.inv) {
-        CB_WSYNC();
-        CB_LANE_LOOP(j, N) Y[j] = (i16)(-Y[j]);
-        CB_WSYNC();
-      }
-      x_cm = y_cm = cm;
-    }
-    w.collapse[i * C + 0] = (u8)x_cm;
-    w.collapse[i * C + C - 1] = (u8)y_cm;
-    balance += w.pulses[i] + tell;
-    update_lowband = b > (N << CB_BITRES);
-  }
-  seed = cx.seed;
-}
-
-#endif  // CB_BANDS_ONE_PHASE
 
 #include "cb_celt_bands3.h"
 
@@ -1260,11 +832,7 @@ CB_FN int celt_entropy_decode(EntWork& w, CeltDecState* stg, FrameSide* side, co
   dec_fine_energy(w, rd, start, end, C);
 
   u32 seed = stg->rng;
-#ifndef CB_BANDS_ONE_PHASE
   dec_all_bands3(w, rd, start, end, C, N, shortBlocks, spread_decision, dual_stereo, intensity,
-#else
-  dec_all_bands(w, rd, start, end, C, N, shortBlocks, spread_decision, dual_stereo, intensity,
-#endif
                 len * (8 << CB_BITRES) - anti_collapse_rsv, balance, LM, codedBands, seed);
   int anti_collapse_on = 0;
   if (anti_collapse_rsv > 0) anti_collapse_on = (int)rd_bits(rd, 1);

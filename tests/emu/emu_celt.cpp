@@ -133,7 +133,3 @@ int emu_ms_decode(void* p, const unsigned char* data, int len, short* pcm, int f
 }
 
 }  // extern "C"
-
-#ifdef CB_PVQ_STATS
-extern "C" void emu_pvq_stats(long* o) { o[0]=g_pvq_calls; o[1]=g_pvq_n; o[2]=g_pvq_k; o[3]=g_pvq_dense_pos; o[4]=g_pvq_sparse_pos; for (int i=0;i<8;i++) o[5+i]=g_pvq_hist[i]; }
-#endif
