@@ -695,7 +695,13 @@ int opus_decoder_ctl(OpusDecoder* st, int request, ...) {
       if (request == OPUS_GET_BANDWIDTH_REQUEST) *value = hdr.bandwidth;
       else if (request == OPUS_GET_FINAL_RANGE_REQUEST) *(opus_uint32*)value = hdr.rangeFinal;
       else if (request == OPUS_GET_LAST_PACKET_DURATION_REQUEST) *value = hdr.last_packet_duration;
-      else *value = hdr.prev_mode == CB_MODE_CELT_ONLY ? hdr.celt.pf_period : 0;
+      else if (hdr.prev_mode == CB_MODE_CELT_ONLY) *value = hdr.celt.pf_period;
+      else {                                  // opus_decoder.c:836-849: the SILK decoder's last pitch lag (48 kHz units)
+        i32 lag = 0;
+        if (cudaMemcpy(&lag, &st->d_state->silk.ctl_prevPitchLag, sizeof(i32), cudaMemcpyDeviceToHost) != cudaSuccess)
+          ret = OPUS_INTERNAL_ERROR;
+        *value = lag;
+      }
       break;
     }
     case OPUS_GET_SAMPLE_RATE_REQUEST: {

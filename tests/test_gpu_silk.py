@@ -112,3 +112,33 @@ def test_full_size_silk_batch_properties():
             assert crc32(pcm[0]) == meta["pcm_crc32"][t], t       # stream 0 plays the fixture from its start
     finally:
         bd.close()
+
+
+@needs_ref
+@pytest.mark.parametrize("name", ["silk_wb_mono_32k", "hyb_fb_mono_32k", "trans_all_st_to24"])
+def test_decoder_queries_follow_the_reference(name):
+    """OPUS_GET_PITCH / GET_BANDWIDTH / GET_LAST_PACKET_DURATION after every packet of SILK, hybrid and
+    mode-switching streams (opus_decoder.c:836-849: the pitch comes from the SILK decoder unless the last
+    frame was CELT-only)."""
+    import ctypes
+    meta = silk_golden_index()[name]
+    pk = read_bit(os.path.join(GOLDEN, name + ".bit"))
+    dec = cb.OpusDecoder(meta["fs"], meta["channels"])
+    ref = RefDecoder(meta["fs"], meta["channels"])
+
+    def rget(req):
+        v = ctypes.c_int32(0)
+        assert ref.lib().opus_decoder_ctl(ctypes.c_void_p(ref.h), req, ctypes.byref(v)) == 0
+        return v.value
+    try:
+        for k, (p, _) in enumerate(pk[:60]):
+            data = None if (k % 11 == 7) else p
+            r1, _ = dec.decode_raw(data, meta["samples_per_frame"])
+            r2, _ = ref.decode_raw(data, meta["samples_per_frame"])
+            assert r1 == r2
+            assert dec.pitch == rget(4033), (name, k)
+            assert dec.bandwidth == rget(4009), (name, k)
+            assert dec.last_packet_duration == rget(4039), (name, k)
+    finally:
+        dec.close()
+        ref.close()
