@@ -45,7 +45,10 @@ EXPORTS = [
     "opus_packet_parse", "opus_repacketizer_get_size", "opus_repacketizer_init", "opus_repacketizer_create",
     "opus_repacketizer_destroy", "opus_repacketizer_cat", "opus_repacketizer_out_range", "opus_repacketizer_get_nb_frames",
     "opus_repacketizer_out", "opus_packet_pad", "opus_packet_unpad", "opus_multistream_packet_pad",
-    "opus_multistream_packet_unpad", "opus_b200_bit_index", "opus_decode_batch", "opus_decode_batch_flat", "opus_decoder_group_create",
+    "opus_multistream_packet_unpad", "opus_b200_bit_index", "opus_multistream_encoder_get_size",
+    "opus_multistream_surround_encoder_get_size", "opus_multistream_encoder_create",
+    "opus_multistream_surround_encoder_create", "opus_multistream_encode", "opus_multistream_encode_float",
+    "opus_multistream_encoder_ctl", "opus_multistream_encoder_destroy", "opus_decode_batch", "opus_decode_batch_flat", "opus_decoder_group_create",
     "opus_decoder_group_destroy", "opus_decode_group_flat", "opus_decode_group_device",
     "opus_decode_group_submit", "opus_decode_group_wait", "opus_encode_group_submit", "opus_encode_group_wait",
     "opus_decoder_get_final_range_batch", "opus_b200_synchronize", "opus_b200_launch_count",
@@ -110,6 +113,13 @@ def load():
     lib.opus_packet_unpad.argtypes = [vp, ctypes.c_int32]
     lib.opus_multistream_packet_pad.argtypes = [vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_int]
     lib.opus_multistream_packet_unpad.argtypes = [vp, ctypes.c_int32, ctypes.c_int]
+    lib.opus_multistream_encoder_create.restype = vp
+    lib.opus_multistream_encoder_create.argtypes = [ctypes.c_int32, ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, ctypes.c_int, vp]
+    lib.opus_multistream_surround_encoder_create.restype = vp
+    lib.opus_multistream_surround_encoder_create.argtypes = [ctypes.c_int32, ctypes.c_int, ctypes.c_int, vp, vp, vp, ctypes.c_int, vp]
+    lib.opus_multistream_encode.argtypes = [vp, vp, ctypes.c_int, vp, ctypes.c_int32]
+    lib.opus_multistream_encode_float.argtypes = [vp, vp, ctypes.c_int, vp, ctypes.c_int32]
+    lib.opus_multistream_encoder_destroy.argtypes = [vp]
     lib.opus_b200_bit_index.argtypes = [vp, ctypes.c_int32, vp, vp, vp, ctypes.c_int32]
     lib.opus_decode_group_flat.argtypes = [vp, vp, ctypes.c_int32, vp, vp, vp, ctypes.c_int32, ctypes.c_int, vp, vp]
     lib.opus_decode_group_submit.argtypes = [vp, vp, ctypes.c_int32, vp, vp, vp, ctypes.c_int32, ctypes.c_int, vp, vp]

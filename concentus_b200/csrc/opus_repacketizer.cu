@@ -9,14 +9,8 @@
 
 #include "../../include/opus_b200.h"
 #include "cb_opus_plan.h"
+#include "cb_repack_internal.h"
 
-struct OpusRepacketizer {
-  unsigned char toc;
-  int nb_frames;
-  const unsigned char* frames[48];
-  opus_int16 len[48];
-  int framesize;                 // samples per frame at 8 kHz (the 120 ms limit is 960 of them)
-};
 
 namespace {
 
@@ -29,7 +23,9 @@ inline int put_size(int size, unsigned char* p) {
 }
 inline int size_field_bytes(int size) { return size < 252 ? 1 : 2; }
 
-int rp_cat(OpusRepacketizer* rp, const unsigned char* data, opus_int32 len, int self_delimited) {
+}  // namespace
+
+int opusb_rp_cat(OpusRepacketizer* rp, const unsigned char* data, opus_int32 len, int self_delimited) {
   if (len < 1) return OPUS_INVALID_PACKET;
   if (rp->nb_frames == 0) {
     rp->toc = data[0];
@@ -55,8 +51,8 @@ int rp_cat(OpusRepacketizer* rp, const unsigned char* data, opus_int32 len, int 
 // Emit frames [begin, end) as one packet of at most maxlen bytes; with `pad` the packet is filled up to
 // exactly maxlen.  The header is planned first (code, VBR flag, padding bytes), then written, then the
 // frames are moved behind it (memmove: pad/unpad work in place).
-opus_int32 rp_emit(OpusRepacketizer* rp, int begin, int end, unsigned char* data, opus_int32 maxlen,
-                   int self_delimited, int pad) {
+opus_int32 opusb_rp_emit(OpusRepacketizer* rp, int begin, int end, unsigned char* data, opus_int32 maxlen,
+                         int self_delimited, int pad) {
   if (begin < 0 || begin >= end || end > rp->nb_frames) return OPUS_BAD_ARG;
   const int count = end - begin;
   const opus_int16* len = rp->len + begin;
@@ -109,7 +105,8 @@ opus_int32 rp_emit(OpusRepacketizer* rp, int begin, int end, unsigned char* data
   return total;
 }
 
-}  // namespace
+#define rp_cat opusb_rp_cat
+#define rp_emit opusb_rp_emit
 
 extern "C" {
 

@@ -229,6 +229,14 @@ int opus_decoder_get_final_range_batch(OpusDecoder *const *st, int n, opus_uint3
 #define OPUS_BANDWIDTH_SUPERWIDEBAND 1104
 #define OPUS_BANDWIDTH_FULLBAND 1105
 #define OPUS_FRAMESIZE_ARG 5000
+#define OPUS_FRAMESIZE_2_5_MS 5001
+#define OPUS_FRAMESIZE_5_MS 5002
+#define OPUS_FRAMESIZE_10_MS 5003
+#define OPUS_FRAMESIZE_20_MS 5004
+#define OPUS_FRAMESIZE_40_MS 5005
+#define OPUS_FRAMESIZE_60_MS 5006
+#define OPUS_FRAMESIZE_VARIABLE 5010
+#define OPUS_GET_VOICE_RATIO_REQUEST 11019
 /* ctl requests understood by opus_encoder_ctl (opus_defines.h:130-167; opus_encoder.c:2031-2504):
  * setters take an opus_int32, getters an opus_int32* (OPUS_GET_FINAL_RANGE an opus_uint32*). */
 #define OPUS_SET_APPLICATION_REQUEST 4000
@@ -307,6 +315,29 @@ int opus_encode_group_device(OpusEncoderGroup *grp, const opus_int16 *d_pcm, int
                              unsigned char *d_data, opus_int32 max_data_bytes, opus_int32 *d_len);
 /* Batched OPUS_GET_FINAL_RANGE for encoders. */
 int opus_encoder_get_final_range_batch(OpusEncoder *const *st, int n, opus_uint32 *out);
+
+/* ---- multistream encoder (opus-fix/include/opus_multistream.h:257-448, src/opus_multistream_encoder.c) ----
+ * The streams of one multistream frame are encoded one after the other (the byte budget of a stream depends
+ * on its predecessors), each by an ordinary elementary encoder on the GPU; channel copy-in, the rate split
+ * and the packet assembly are host code.  Built: explicit layouts (opus_multistream_encoder_create) and the
+ * surround families that need no masking analysis (family 0, family 255, family 1 up to 2 channels).
+ * Family 1 with 3..8 channels (surround analysis + LFE stream) returns OPUS_UNIMPLEMENTED, and so does any
+ * frame the elementary encoder refuses (see opus_encode above). */
+typedef struct OpusMSEncoder OpusMSEncoder;
+#define OPUS_MULTISTREAM_GET_ENCODER_STATE_REQUEST 5120
+opus_int32 opus_multistream_encoder_get_size(int streams, int coupled_streams);
+opus_int32 opus_multistream_surround_encoder_get_size(int channels, int mapping_family);
+OpusMSEncoder *opus_multistream_encoder_create(opus_int32 Fs, int channels, int streams, int coupled_streams,
+                                               const unsigned char *mapping, int application, int *error);
+OpusMSEncoder *opus_multistream_surround_encoder_create(opus_int32 Fs, int channels, int mapping_family,
+                                                        int *streams, int *coupled_streams,
+                                                        unsigned char *mapping, int application, int *error);
+int opus_multistream_encode(OpusMSEncoder *st, const opus_int16 *pcm, int frame_size, unsigned char *data,
+                            opus_int32 max_data_bytes);
+int opus_multistream_encode_float(OpusMSEncoder *st, const float *pcm, int frame_size, unsigned char *data,
+                                  opus_int32 max_data_bytes);
+int opus_multistream_encoder_ctl(OpusMSEncoder *st, int request, ...);
+void opus_multistream_encoder_destroy(OpusMSEncoder *st);
 /* Device timing of the encode kernel with CUDA events on the launching stream (bench.py). */
 int opus_b200_encode_profile_begin(void);
 int opus_b200_encode_profile_end(double *ms, long long *count);
