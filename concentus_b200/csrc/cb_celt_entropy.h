@@ -551,43 +551,62 @@ CB_FN int cb_allocation(W& w, AC& ac, int start, int end, int alloc_trim, int& i
       total -= dual_stereo_rsv;
     }
   }
-  CB_NOUNROLL for (int j = start; j < end; j++) {
-    int wdt = ebands(j + 1) - ebands(j);
+  // One band per lane: the thresholds, both bisections and the interpolation are sums over bands.  "done"
+  // of the reference's high-to-low scan (every band at or below the highest one that reaches its threshold)
+  // becomes a comparison with that band's index `top`.
+  const int nb = end - start;
+  CB_WSYNC();
+  CB_LANE_LOOP(jj, nb) {
+    const int j = start + jj;
+    const int wdt = cb_ldg(&ct_eband5ms_g[j + 1]) - cb_ldg(&ct_eband5ms_g[j]);
     thresh[j] = cb_imax(C << CB_BITRES, (3 * wdt << LM << CB_BITRES) >> 4);
-    trim_offset[j] = C * wdt * (alloc_trim - 5 - LM) * (end - j - 1) * (1 << (LM + CB_BITRES)) >> 6;
-    if (wdt << LM == 1) trim_offset[j] -= C << CB_BITRES;
+    i32 to = C * wdt * (alloc_trim - 5 - LM) * (end - j - 1) * (1 << (LM + CB_BITRES)) >> 6;
+    if (wdt << LM == 1) to -= C << CB_BITRES;
+    trim_offset[j] = to;
   }
+  CB_WSYNC();
   int lo = 1, hi = 11 - 1;                    // nbAllocVectors = 11
   CB_NOUNROLL do {
-    int done = 0, psum = 0;
-    int mid = (lo + hi) >> 1;
-    CB_NOUNROLL for (int j = end; j-- > start;) {
-      int wdt = ebands(j + 1) - ebands(j);
-      int bitsj = C * wdt * ct_band_alloc[mid * CB_NBANDS + j] << LM >> 2;
+    const int mid = (lo + hi) >> 1;
+    int top_l = -1;
+    CB_LANE_LOOP(jj, nb) {
+      const int j = start + jj;
+      const int wdt = cb_ldg(&ct_eband5ms_g[j + 1]) - cb_ldg(&ct_eband5ms_g[j]);
+      int bitsj = C * wdt * cb_ldg(&ct_band_alloc_g[mid * CB_NBANDS + j]) << LM >> 2;
       if (bitsj > 0) bitsj = cb_imax(0, bitsj + trim_offset[j]);
       bitsj += w.offsets[j];
-      if (bitsj >= thresh[j] || done) {
-        done = 1;
-        psum += cb_imin(bitsj, w.cap[j]);
-      } else if (bitsj >= C << CB_BITRES) {
-        psum += C << CB_BITRES;
-      }
+      bits[j] = bitsj;
+      if (bitsj >= thresh[j]) top_l = cb_imax(top_l, j);
     }
-    if (psum > total) hi = mid - 1; else lo = mid + 1;
+    const int top = cb_wmax(top_l);
+    i32 psum_l = 0;
+    CB_LANE_LOOP(jj, nb) {
+      const int j = start + jj;
+      const int bitsj = bits[j];
+      if (j <= top) psum_l += cb_imin(bitsj, w.cap[j]);
+      else if (bitsj >= C << CB_BITRES) psum_l += C << CB_BITRES;
+    }
+    const i32 psum0 = cb_wsum(psum_l);
+    if (psum0 > total) hi = mid - 1; else lo = mid + 1;
   } while (lo <= hi);
   hi = lo--;
-  CB_NOUNROLL for (int j = start; j < end; j++) {
-    int wdt = ebands(j + 1) - ebands(j);
-    int bits1j = C * wdt * ct_band_alloc[lo * CB_NBANDS + j] << LM >> 2;
-    int bits2j = hi >= 11 ? w.cap[j] : C * wdt * ct_band_alloc[hi * CB_NBANDS + j] << LM >> 2;
-    if (bits1j > 0) bits1j = cb_imax(0, bits1j + trim_offset[j]);
-    if (bits2j > 0) bits2j = cb_imax(0, bits2j + trim_offset[j]);
-    if (lo > 0) bits1j += w.offsets[j];
-    bits2j += w.offsets[j];
-    if (w.offsets[j] > 0) skip_start = j;
-    bits2j = cb_imax(0, bits2j - bits1j);
-    bits1[j] = bits1j;
-    bits2[j] = bits2j;
+  {
+    int ss_l = start;
+    CB_LANE_LOOP(jj, nb) {
+      const int j = start + jj;
+      const int wdt = cb_ldg(&ct_eband5ms_g[j + 1]) - cb_ldg(&ct_eband5ms_g[j]);
+      int bits1j = C * wdt * cb_ldg(&ct_band_alloc_g[lo * CB_NBANDS + j]) << LM >> 2;
+      int bits2j = hi >= 11 ? w.cap[j] : C * wdt * cb_ldg(&ct_band_alloc_g[(hi >= 11 ? 0 : hi) * CB_NBANDS + j]) << LM >> 2;
+      if (bits1j > 0) bits1j = cb_imax(0, bits1j + trim_offset[j]);
+      if (bits2j > 0) bits2j = cb_imax(0, bits2j + trim_offset[j]);
+      if (lo > 0) bits1j += w.offsets[j];
+      bits2j += w.offsets[j];
+      if (w.offsets[j] > 0) ss_l = cb_imax(ss_l, j);
+      bits2j = cb_imax(0, bits2j - bits1j);
+      bits1[j] = bits1j;
+      bits2[j] = bits2j;
+    }
+    skip_start = cb_wmax(ss_l);
   }
   // interp_bits2pulses (rate.c:248-525)
   const int alloc_floor = C << CB_BITRES;
@@ -597,34 +616,43 @@ CB_FN int cb_allocation(W& w, AC& ac, int start, int end, int alloc_trim, int& i
   lo = 0;
   hi = 1 << CB_ALLOC_STEPS;
   CB_NOUNROLL for (int it = 0; it < CB_ALLOC_STEPS; it++) {
-    int mid = (lo + hi) >> 1;
-    psum = 0;
-    int done = 0;
-    CB_NOUNROLL for (int j = end; j-- > start;) {
-      int tmp = bits1[j] + (int)((i32)mid * bits2[j] >> CB_ALLOC_STEPS);
-      if (tmp >= thresh[j] || done) {
-        done = 1;
-        psum += cb_imin(tmp, w.cap[j]);
-      } else if (tmp >= alloc_floor) {
-        psum += alloc_floor;
-      }
+    const int mid = (lo + hi) >> 1;
+    int top_l = -1;
+    CB_LANE_LOOP(jj, nb) {
+      const int j = start + jj;
+      const int tmp = bits1[j] + (int)((i32)mid * bits2[j] >> CB_ALLOC_STEPS);
+      if (tmp >= thresh[j]) top_l = cb_imax(top_l, j);
     }
+    const int top = cb_wmax(top_l);
+    i32 psum_l = 0;
+    CB_LANE_LOOP(jj, nb) {
+      const int j = start + jj;
+      const int tmp = bits1[j] + (int)((i32)mid * bits2[j] >> CB_ALLOC_STEPS);
+      if (j <= top) psum_l += cb_imin(tmp, w.cap[j]);
+      else if (tmp >= alloc_floor) psum_l += alloc_floor;
+    }
+    psum = cb_wsum(psum_l);
     if (psum > total) hi = mid; else lo = mid;
   }
-  psum = 0;
   {
-    int done = 0;
-    CB_NOUNROLL for (int j = end; j-- > start;) {
+    int top_l = -1;
+    CB_LANE_LOOP(jj, nb) {
+      const int j = start + jj;
+      const int tmp = bits1[j] + (lo * bits2[j] >> CB_ALLOC_STEPS);
+      if (tmp >= thresh[j]) top_l = cb_imax(top_l, j);
+    }
+    const int top = cb_wmax(top_l);
+    i32 psum_l = 0;
+    CB_LANE_LOOP(jj, nb) {
+      const int j = start + jj;
       int tmp = bits1[j] + (lo * bits2[j] >> CB_ALLOC_STEPS);
-      if (tmp < thresh[j] && !done) {
-        if (tmp >= alloc_floor) tmp = alloc_floor; else tmp = 0;
-      } else {
-        done = 1;
-      }
+      if (j > top) tmp = tmp >= alloc_floor ? alloc_floor : 0;
       tmp = cb_imin(tmp, w.cap[j]);
       bits[j] = tmp;
-      psum += tmp;
+      psum_l += tmp;
     }
+    psum = cb_wsum(psum_l);
+    CB_WSYNC();
   }
   int codedBands;
   CB_NOUNROLL for (codedBands = end;; codedBands--) {
