@@ -207,7 +207,7 @@ template <bool REBUILD>
 CB_FN u32 b3_leaf_node(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, i16* X, int N, int b, int B,
                        const i16* lowband, int LM, i32 gain, int fill) {
   if (!REBUILD) {
-    int q = bits2pulses(cx.i, LM, b);
+    int q = bits2pulses_lanes(cx.i, LM, b);
     int curr_bits = pulses2bits(cx.i, LM, q);
     cx.remaining_bits -= curr_bits;
     CB_NOUNROLL while (cx.remaining_bits < 0 && q > 0) {
