@@ -110,6 +110,8 @@ struct OpusDecoder {
   int decode_gain;
   OpusDecState* d_state;
   OpusDecoderGroup* self_group;   // group of one, created on first opus_decode()
+  int min_frame_48k;              // shortest frame any packet given to this decoder announced (samples at 48 kHz);
+                                  // 0: no packet yet, -1: unknown (packets went in through a device-resident call)
 };
 
 // Two-deep pipeline behind opus_decode_group_submit/_wait: while the kernels of one call run, the PCM of
@@ -420,25 +422,55 @@ int opus_decode_group_device(OpusDecoderGroup* g, const unsigned char* d_data, c
   DevCtx* c = ctx_for_current_device(&err);
   if (!c) return err;
   cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
+  for (int i = 0; i < g->n; i++) g->members[i]->min_frame_48k = -1;   // the host does not see these packets
   return group_enqueue(g, d_data, d_offsets, d_len, d_pcm, pcm_stride, frame_size, d_decode_fec, d_ret,
                        max_frames, max_packet_bytes, s);
 }
 
+// Upper bound on the pieces a concealed frame_size is cut into (opus_decoder.c:239-292, mirrored on the
+// device by opus_plan_plc): no piece is longer than the last decoded frame, which in turn is no shorter than
+// the shortest frame this group has ever been given.  Before any packet: pieces of 2.5 ms.
+// min_frame_48k: shortest frame the decoders concerned have been given (48 kHz samples), <= 0: not known.
+static int plc_passes(int frame_size, int Fs, int min_frame_48k) {
+  const int F20 = Fs / 50, F10 = F20 >> 1, F5 = F10 >> 1, F2_5 = F5 >> 1;
+  int cap = min_frame_48k > 0 ? (int)((long long)min_frame_48k * Fs / 48000) : F2_5;
+  if (cap < F2_5) cap = F2_5;
+  int count = 0;
+  for (int rem = frame_size; rem >= F2_5 && count < CB_MAX_FRAMES; count++) {
+    int a = rem < cap ? rem : cap;
+    if (a > F20) a = F20;
+    else if (a < F20) {
+      if (a > F10) a = F10;
+      else if (a > F5 && a < F10) a = F5;
+    }
+    rem -= a;
+  }
+  return count > 0 ? count : 1;
+}
+
 // Upper bound on the passes a batch needs, from the packets themselves (host side, O(n) byte reads).
-static int scan_passes(const unsigned char* data, const i32* off, const i32* len, const int* fec, int n,
-                       int frame_size, int Fs_hint, int* max_len) {
-  int passes = 1, mlen = 0, any_lost = 0;
+static int scan_passes(OpusDecoder* const* members, const unsigned char* data, const i32* off, const i32* len,
+                       const int* fec, int n, int frame_size, int Fs_hint, int* max_len) {
+  int passes = 1, mlen = 0, any_lost = 0, any_fec = 0;
+  int group_min = 1 << 30;                 // over the members that have decoded something
+  bool unknown = false;
   for (int i = 0; i < n; i++) {
+    int& mf = members[i]->min_frame_48k;
+    if (off[i] >= 0 && len[i] > 0) {
+      const int spf = opus_toc_samples_per_frame(data[off[i]], 48000);
+      if (mf == 0 || (mf > 0 && spf < mf)) mf = spf;
+    }
+    if (mf < 0) unknown = true;
+    else if (mf > 0 && mf < group_min) group_min = mf;
     if (off[i] < 0 || len[i] <= 0) { any_lost = 1; continue; }
-    if (fec && fec[i]) any_lost = 1;       // an FEC request on a CELT stream is served by concealment chunks
+    if (fec && fec[i]) any_lost = any_fec = 1;   // the frames before an FEC frame are concealment chunks
     if (len[i] > mlen) mlen = len[i];
     int nf = opus_packet_get_nb_frames(data + off[i], len[i]);
     if (nf > passes) passes = nf;
   }
   if (any_lost) {
-    // concealment is cut into chunks of at least 2.5 ms (opus_decoder.c:239-292)
-    int F2_5 = (Fs_hint > 0 ? Fs_hint : 8000) / 400;
-    int chunks = (frame_size + F2_5 - 1) / F2_5;
+    const int known = (unknown || Fs_hint <= 0 || group_min == 1 << 30) ? 0 : group_min;
+    const int chunks = plc_passes(frame_size, Fs_hint > 0 ? Fs_hint : 8000, known) + any_fec;
     if (chunks > passes) passes = chunks;
   }
   if (passes > CB_MAX_FRAMES) passes = CB_MAX_FRAMES;
@@ -468,7 +500,7 @@ int opus_decode_group_flat(OpusDecoderGroup* g, const unsigned char* data, opus_
   DevCtx* c = ctx_for_current_device(&err);
   if (!c) return err;
   int max_len = 0;
-  int passes = scan_passes(data, offsets, len, decode_fec, n, frame_size, g->Fs, &max_len);
+  int passes = scan_passes(g->members, data, offsets, len, decode_fec, n, frame_size, g->Fs, &max_len);
   const size_t pkt_bytes = (size_t)data_bytes + 16;
   const size_t pcm_bytes = (size_t)n * pcm_stride * sizeof(i16);
   const size_t i32_bytes = (size_t)n * 3 * sizeof(i32);
@@ -530,7 +562,7 @@ int opus_decode_group_submit(OpusDecoderGroup* g, const unsigned char* data, opu
   DecPipeSlot& sl = p->slot[p->seq & 1];
   if (sl.busy) { CUDA_OK(cudaEventSynchronize(sl.out_done)); sl.busy = false; }
   int max_len = 0;
-  const int passes = scan_passes(data, offsets, len, decode_fec, n, frame_size, g->Fs, &max_len);
+  const int passes = scan_passes(g->members, data, offsets, len, decode_fec, n, frame_size, g->Fs, &max_len);
   const size_t pcm_bytes = (size_t)n * pcm_stride * sizeof(i16);
   const size_t in_bytes = (size_t)n * 3 * sizeof(i32);
   if (sl.d_pkt.reserve((size_t)data_bytes + 16) || sl.d_pcm.reserve(pcm_bytes) || sl.d_i32.reserve((size_t)n * 4 * sizeof(i32)) ||
@@ -889,29 +921,42 @@ int opus_multistream_decode_group_flat(OpusMSDecoderGroup* g, const unsigned cha
   if (frame_size <= 0) { for (int i = 0; i < n; i++) ret[i] = OPUS_BAD_ARG; return OPUS_OK; }
   if (pcm_stride < frame_size * g->max_channels) return OPUS_BAD_ARG;
   // passes: walk the sub-packets on the host (byte reads only) to find the largest frame count
-  int passes = 1, max_len = 0, any_lost = 0, minFs = 48000;
+  int passes = 1, max_len = 0, any_lost = 0, any_fec = 0, minFs = 48000;
+  int group_min = 1 << 30;
+  bool unknown = false;
   for (int m = 0; m < n; m++) {
     OpusMSDecoder* ms = g->members[m];
     if (ms->Fs < minFs) minFs = ms->Fs;
     if (offsets[m] < 0 || len[m] <= 0) { any_lost = 1; continue; }
     if (offsets[m] + (long long)len[m] > data_bytes) return OPUS_BAD_ARG;
-    if (decode_fec && decode_fec[m]) any_lost = 1;
-    if (len[m] > max_len) max_len = len[m];
+    if (decode_fec && decode_fec[m]) any_lost = any_fec = 1;
     const unsigned char* p = data + offsets[m];
     i32 rem = len[m];
+    bool parsed_all = true;
     for (int s = 0; s < ms->streams && rem > 0; s++) {
       i16 sizes[CB_MAX_FRAMES];
       i32 po = 0;
       int toc = 0;
       int cnt = opus_parse_packet(p, rem, s != ms->streams - 1, &toc, sizes, nullptr, &po);
-      if (cnt < 0) break;
+      if (cnt < 0) { parsed_all = false; break; }
       if (cnt > passes) passes = cnt;
+      if (po > max_len) max_len = po;            // kernel A stages one frame of one elementary stream at a time
+      int& mf = ms->sub[s]->min_frame_48k;
+      const int spf = opus_toc_samples_per_frame(toc, 48000);
+      if (mf == 0 || (mf > 0 && spf < mf)) mf = spf;
       p += po;
       rem -= po;
     }
+    if (!parsed_all && len[m] > max_len) max_len = len[m];
   }
   if (any_lost) {
-    int chunks = (frame_size + minFs / 400 - 1) / (minFs / 400);
+    for (int m = 0; m < n; m++)
+      for (int s = 0; s < g->members[m]->streams; s++) {
+        const int mf = g->members[m]->sub[s]->min_frame_48k;
+        if (mf < 0) unknown = true;
+        else if (mf > 0 && mf < group_min) group_min = mf;
+      }
+    const int chunks = plc_passes(frame_size, minFs, (unknown || group_min == 1 << 30) ? 0 : group_min) + any_fec;
     if (chunks > passes) passes = chunks;
   }
   if (passes > CB_MAX_FRAMES) passes = CB_MAX_FRAMES;
@@ -1082,6 +1127,7 @@ long long opus_b200_launch_count(void) { return g_launches; }
 OpusDecState* opusb_internal_device_state(const OpusDecoder* st, int* device) {
   if (!st || st->magic != kMagic) return nullptr;
   if (device) *device = st->device;
+  const_cast<OpusDecoder*>(st)->min_frame_48k = -1;    // its caller feeds device-resident packets the host never sees
   return st->d_state;
 }
 

@@ -2,7 +2,9 @@
  * Links the UNMODIFIED reference objects (oracle/_ref) and times opus_decode() on the host cores:
  * T threads, each owning n/T independent OpusDecoder objects, all decoding the same packet
  * sequence a GPU batch gets (stream i starts at packet (37*i) mod count of a .bit fixture).
- * Usage: ref_bench <file.bit> <Fs> <channels> <streams> <frames> <threads>
+ * Usage: ref_bench <file.bit> <Fs> <channels> <streams> <frames> <threads> [ms_streams ms_coupled mapping,csv]
+ * With the three optional arguments the decoders are OpusMSDecoder objects of that layout
+ * (opus_multistream_decode; zero-length records of the fixture are lost packets).
  * Prints one line: stream_seconds wall_seconds threads checksum
  */
 #include <pthread.h>
@@ -12,10 +14,13 @@
 #include <string.h>
 #include <time.h>
 #include "opus.h"
+#include "opus_multistream.h"
 
 typedef struct { unsigned char *data; int len; } Packet;
 static Packet *g_pk; static int g_count;
 static int g_fs, g_ch, g_frames;
+static int g_ms_streams, g_ms_coupled;
+static unsigned char g_mapping[256];
 typedef struct { int first, last; uint32_t sum; double audio; } Job;
 
 static void *worker(void *arg) {
@@ -23,7 +28,19 @@ static void *worker(void *arg) {
   int err, i, t, k;
   opus_int16 *pcm = (opus_int16 *)malloc(sizeof(opus_int16) * 5760 * g_ch);
   uint32_t sum = 0;
-  for (i = job->first; i < job->last; i++) {
+  for (i = job->first; g_ms_streams && i < job->last; i++) {
+    OpusMSDecoder *dec = opus_multistream_decoder_create(g_fs, g_ch, g_ms_streams, g_ms_coupled, g_mapping, &err);
+    if (!dec) { fprintf(stderr, "create failed\n"); exit(1); }
+    for (t = 0; t < g_frames; t++) {
+      Packet *p = &g_pk[(37 * i + t) % g_count];
+      int ret = opus_multistream_decode(dec, p->len ? p->data : NULL, p->len, pcm, p->len ? 5760 : g_fs / 50, 0);
+      if (ret < 0) { fprintf(stderr, "decode failed %d\n", ret); exit(1); }
+      for (k = 0; k < ret * g_ch; k += 97) sum = sum * 31u + (uint16_t)pcm[k];
+      job->audio += (double)ret / g_fs;
+    }
+    opus_multistream_decoder_destroy(dec);
+  }
+  for (i = job->first; !g_ms_streams && i < job->last; i++) {
     OpusDecoder *dec = opus_decoder_create(g_fs, g_ch, &err);
     if (!dec) { fprintf(stderr, "create failed\n"); exit(1); }
     for (t = 0; t < g_frames; t++) {
@@ -47,6 +64,11 @@ int main(int argc, char **argv) {
   g_fs = atoi(argv[2]); g_ch = atoi(argv[3]);
   int streams = atoi(argv[4]); g_frames = atoi(argv[5]);
   int T = atoi(argv[6]);
+  if (argc >= 10) {
+    g_ms_streams = atoi(argv[7]); g_ms_coupled = atoi(argv[8]);
+    int c = 0;
+    for (char *tok = strtok(argv[9], ","); tok && c < 255; tok = strtok(NULL, ",")) g_mapping[c++] = (unsigned char)atoi(tok);
+  }
   int cap = 1024;
   g_pk = (Packet *)malloc(sizeof(Packet) * cap);
   for (;;) {
@@ -54,7 +76,7 @@ int main(int argc, char **argv) {
     if (fread(h, 1, 8, f) != 8) break;
     int len = (h[0] << 24) | (h[1] << 16) | (h[2] << 8) | h[3];
     if (g_count == cap) { cap *= 2; g_pk = (Packet *)realloc(g_pk, sizeof(Packet) * cap); }
-    g_pk[g_count].data = (unsigned char *)malloc(len);
+    g_pk[g_count].data = (unsigned char *)malloc(len + 1);
     g_pk[g_count].len = len;
     if (fread(g_pk[g_count].data, 1, len, f) != (size_t)len) break;
     g_count++;
