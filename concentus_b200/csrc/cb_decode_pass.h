@@ -24,10 +24,7 @@ CB_FN void decode_entropy_pass(EntWork& w, u8* pkt, OpusDecState* st, StreamPlan
     side->kind = 3;
     return;
   }
-  if (route != CB_ROUTE_CELT && route != CB_ROUTE_HYBRID) {   // decoded by the SILK kernel or the general kernel
-    side->kind = 0;
-    return;
-  }
+  if (route != CB_ROUTE_CELT && route != CB_ROUTE_HYBRID) return;   // SILK / general kernel (which may be running now)
   constexpr bool hybrid = HYB;                     // SILK layer already in the PCM row: bands 17.. accumulate
   const int len = pl->len[pass];
   const int nsamp = pl->nsamp[pass];
@@ -104,6 +101,8 @@ CB_FN void decode_entropy_pass(EntWork& w, u8* pkt, OpusDecState* st, StreamPlan
 CB_FN void decode_synth_pass(SynWork& w, OpusDecState* st, const StreamPlan* pl, const FrameSide* side,
                              i16* row, int c, int pass) {
   const int CC = st->channels;
+  const int route = pl->route;
+  if (route == CB_ROUTE_SILK || route == CB_ROUTE_GENERAL || route == CB_ROUTE_FINISH || route == CB_ROUTE_PLC) return;
   if (side->kind == 1) {
     celt_synth_channel(w, &st->celt, side, c, row + (size_t)pl->pcm_off[pass] * CC, st->decode_gain);
   } else if (side->kind == 3 && pass == 0) {
@@ -119,7 +118,7 @@ CB_FN void decode_synth_pass(SynWork& w, OpusDecState* st, const StreamPlan* pl,
 // Kernel C, one stream, one pass: pitch-based concealment (both channels) when kernel A asked for it.
 CB_FN void decode_plc_pass(PlcWork& w, OpusDecState* st, const StreamPlan* pl, const FrameSide* side,
                            i16* row, int pass) {
-  if (side->kind != 2) return;
+  if (pl->route != CB_ROUTE_PLC || side->kind != 2) return;
   const int N = 120 << side->LM;
   celt_plc_pitch(w, &st->celt, N, row + (size_t)pl->pcm_off[pass] * st->channels, side->accum, st->decode_gain);
 }

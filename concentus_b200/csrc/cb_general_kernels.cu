@@ -22,9 +22,9 @@ opus_general_kernel(OpusDecState* const* states, StreamPlan* plans, FrameSide* s
   for (int s = blockIdx.x * G_WARPS + warp; s < n; s += gridDim.x * G_WARPS) {
     StreamPlan* pl = &plans[s];
     const int route = pl->route;
-    if (route == CB_ROUTE_CELT) {
-      // pitch-based concealment of a CELT frame, asked for by kernel A (celt_decode_lost, loss_count < 5)
-      if (sides[s].kind == 2) decode_plc_pass(g.pw, states[s], pl, &sides[s], pcm + (size_t)s * pcm_stride, pass);
+    if (route == CB_ROUTE_PLC) {
+      // pitch-based concealment of a CELT frame (celt_decode_lost, loss_count < 5), set up by the SILK kernel
+      decode_plc_pass(g.pw, states[s], pl, &sides[s], pcm + (size_t)s * pcm_stride, pass);
     } else if (route == CB_ROUTE_GENERAL || route == CB_ROUTE_FINISH) {
       decode_general_pass(g, states[s], pl, &sides[s], data, pcm + (size_t)s * pcm_stride, &ret[s], pass, cw);
     }

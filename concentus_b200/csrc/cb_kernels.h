@@ -15,10 +15,10 @@ int cbk_launch_synth(OpusDecState* const* d_states, const StreamPlan* d_plans, c
                      i16* d_pcm, i32 pcm_stride, int n, int pass, cudaStream_t stream);
 // SILK frames of pass `pass` (one thread per stream); streams whose frame is CELT return at once
 int cbk_launch_plan_silk(OpusDecState* const* d_states, const u8* d_data, const i32* d_off, const i32* d_len,
-                         const i32* d_fec, int frame_size, StreamPlan* d_plans, i16* d_pcm, i32 pcm_stride, i32* d_ret,
-                         int n, cudaStream_t stream);
-int cbk_launch_silk(OpusDecState* const* d_states, StreamPlan* d_plans, const u8* d_data, i16* d_pcm,
-                    i32 pcm_stride, i32* d_ret, int n, int pass, cudaStream_t stream);
+                         const i32* d_fec, int frame_size, StreamPlan* d_plans, FrameSide* d_sides, i16* d_pcm,
+                         i32 pcm_stride, i32* d_ret, int n, cudaStream_t stream);
+int cbk_launch_silk(OpusDecState* const* d_states, StreamPlan* d_plans, FrameSide* d_sides, const u8* d_data,
+                    i16* d_pcm, i32 pcm_stride, i32* d_ret, int n, int pass, cudaStream_t stream);
 int cbk_launch_general(OpusDecState* const* d_states, StreamPlan* d_plans, FrameSide* d_sides, const u8* d_data,
                        i16* d_pcm, i32 pcm_stride, i32* d_ret, int n, int pass, cudaStream_t stream);
 int cbk_launch_ms_plan(OpusDecState* const* d_states, StreamPlan* d_plans, const MSLayout* d_layouts,

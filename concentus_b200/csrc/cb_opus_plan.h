@@ -285,6 +285,7 @@ CB_HD void opus_plan_stream(OpusDecState* st, StreamPlan* pl, const u8* data, i3
 #define CB_ROUTE_GENERAL 2     // general kernel (cb_opus_general.h): transitions, FEC of hybrid frames, odd sizes
 #define CB_ROUTE_FINISH 3      // SILK kernel decoded the SILK layer and found a redundant CELT frame: general kernel finishes
 #define CB_ROUTE_HYBRID 4      // SILK kernel decodes the SILK layer, then the CELT kernels add bands 17.. on top
+#define CB_ROUTE_PLC 5         // lost CELT frame, pitch-based concealment (celt_decode_lost, loss_count < 5): general kernel
 CB_HD int opus_frame_route(const OpusDecState* st, const StreamPlan* pl, int pass) {
   const bool conceal = pl->kind == CB_PLAN_PLC || (pl->len[pass] <= 1);
   const int prev = st->prev_mode;
@@ -294,7 +295,8 @@ CB_HD int opus_frame_route(const OpusDecState* st, const StreamPlan* pl, int pas
   if (conceal) {
     if (prev == CB_MODE_SILK_ONLY) return CB_ROUTE_SILK;
     if (prev == CB_MODE_HYBRID) return split_ok ? CB_ROUTE_HYBRID : CB_ROUTE_GENERAL;
-    return CB_ROUTE_CELT;
+    if (prev == CB_MODE_CELT_ONLY && st->celt.loss_count < 5) return CB_ROUTE_PLC;
+    return CB_ROUTE_CELT;                      // nothing decoded yet (zeros) or noise-based concealment
   }
   const int mode = st->mode;
   if (mode == CB_MODE_CELT_ONLY) {

@@ -8,14 +8,27 @@
 #include "cb_opus_plan.h"
 #include "cb_silk_dec.h"
 
-CB_FN void decode_silk_pass(OpusDecState* st, StreamPlan* pl, const u8* data, i16* row, i32* ret_slot, int pass,
-                            SilkCallWork& cw) {
+CB_FN void decode_silk_pass(OpusDecState* st, StreamPlan* pl, FrameSide* side, const u8* data, i16* row, i32* ret_slot,
+                            int pass, SilkCallWork& cw) {
   {
     // first kernel of the pass: decide who decodes this stream's frame
     const int kind = pl->kind;
     int route = -1;
     if (!(pl->ret < 0 || pass >= pl->nframes || kind == CB_PLAN_NONE || kind == CB_PLAN_ZERO)) route = opus_frame_route(st, pl, pass);
     pl->route = route;
+    if (route == CB_ROUTE_PLC) {
+      // lost CELT frame, pitch-based concealment: the general kernel does it, concurrently with the CELT
+      // kernels of the other streams; the Opus-layer bookkeeping of opus_decode_frame(data = NULL) is done here
+      int LMp = 0;
+      const int fs48 = pl->nsamp[pass] * st->celt.downsample;
+      while ((120 << LMp) < fs48) LMp++;
+      side->kind = 2;
+      side->LM = LMp;
+      side->accum = 0;
+      st->rangeFinal = 0;
+      st->prev_redundancy = 0;
+      return;
+    }
     if (route != CB_ROUTE_SILK && route != CB_ROUTE_HYBRID) return;
   }
   const bool hybrid = pl->route == CB_ROUTE_HYBRID;

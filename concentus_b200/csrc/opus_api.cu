@@ -53,6 +53,10 @@ struct GrowBuf {                 // grow-only buffer (device or pinned host)
 struct DevCtx {
   int device = -1;
   cudaStream_t stream = nullptr;
+  // The general kernel (mode switches, pitch-based concealment) works on streams the CELT kernels skip, so it
+  // runs beside them on its own stream: forked after the SILK kernel of a pass, joined at the end of the pass.
+  cudaStream_t side_stream = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   std::vector<OpusDecState*> slabs;
   std::vector<OpusDecState*> free_slots;
   // staging for the pointer-array / flat entry points
@@ -373,12 +377,28 @@ void opus_decoder_group_destroy(OpusDecoderGroup* g) {
 static int group_enqueue_passes(OpusDecoderGroup* g, const u8* d_data, i16* d_pcm, i32 pcm_stride, i32* d_ret,
                                 int passes, int max_packet_bytes, cudaStream_t stream, bool silk0_done = false) {
   int rc = 0;
+  DevCtx* c = (g->device >= 0 && g->device < 16) ? &g_ctx[g->device] : nullptr;
+  if (c && !c->side_stream) {
+    if (cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess) {
+      c->side_stream = nullptr;              // fall back to running everything on one stream
+    }
+  }
+  const bool fork = c && c->side_stream && c->ev_fork && c->ev_join;
   for (int p = 0; p < passes; p++) {
     // SILK kernel first: it also decides, per stream, which kernels own this pass's frame
     rc = 0;
     if (p > 0 || !silk0_done) {
-      rc = cbk_launch_silk(g->d_states, g->d_plans, d_data, d_pcm, pcm_stride, d_ret, g->n, p, stream);
+      rc = cbk_launch_silk(g->d_states, g->d_plans, g->d_sides, d_data, d_pcm, pcm_stride, d_ret, g->n, p, stream);
       g_launches += 1;
+    }
+    if (!rc && fork) {
+      // general kernel on the side stream, beside the CELT kernels of this pass
+      if (cudaEventRecord(c->ev_fork, stream) != cudaSuccess || cudaStreamWaitEvent(c->side_stream, c->ev_fork, 0) != cudaSuccess)
+        return OPUS_INTERNAL_ERROR;
+      rc = cbk_launch_general(g->d_states, g->d_plans, g->d_sides, d_data, d_pcm, pcm_stride, d_ret, g->n, p, c->side_stream);
+      if (!rc && cudaEventRecord(c->ev_join, c->side_stream) != cudaSuccess) return OPUS_INTERNAL_ERROR;
     }
     if (!rc) {
       ProfScope ps(stream, 1);
@@ -388,7 +408,9 @@ static int group_enqueue_passes(OpusDecoderGroup* g, const u8* d_data, i16* d_pc
       ProfScope ps(stream, 2);
       rc = cbk_launch_synth(g->d_states, g->d_plans, g->d_sides, d_pcm, pcm_stride, g->n, p, stream);
     }
-    if (!rc) rc = cbk_launch_general(g->d_states, g->d_plans, g->d_sides, d_data, d_pcm, pcm_stride, d_ret, g->n, p, stream);
+    if (!rc && !fork)
+      rc = cbk_launch_general(g->d_states, g->d_plans, g->d_sides, d_data, d_pcm, pcm_stride, d_ret, g->n, p, stream);
+    if (!rc && fork && cudaStreamWaitEvent(stream, c->ev_join, 0) != cudaSuccess) return OPUS_INTERNAL_ERROR;
     g_launches += 4;
     if (rc) { fprintf(stderr, "[opus_b200] pass launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
   }
@@ -402,8 +424,8 @@ static int group_enqueue(OpusDecoderGroup* g, const u8* d_data, const i32* d_off
   int rc;
   {
     ProfScope ps(stream, 0);
-    rc = cbk_launch_plan_silk(g->d_states, d_data, d_off, d_len, d_fec, frame_size, g->d_plans, d_pcm, pcm_stride, d_ret,
-                              g->n, stream);
+    rc = cbk_launch_plan_silk(g->d_states, d_data, d_off, d_len, d_fec, frame_size, g->d_plans, g->d_sides, d_pcm,
+                              pcm_stride, d_ret, g->n, stream);
   }
   g_launches += 1;
   if (rc) { fprintf(stderr, "[opus_b200] plan launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }

@@ -58,7 +58,7 @@ int emu_opus_decode(void* state, const unsigned char* data, int len, short* pcm,
   opus_plan_stream(st, &pl, data, data ? 0 : -1, data ? len : 0, frame_size, fec, 0, nullptr);
   ret = pl.ret;
   for (int pass = 0; pass < pl.nframes; pass++) {
-    decode_silk_pass(st, &pl, data, pcm, &ret, pass, cw);
+    decode_silk_pass(st, &pl, &side, data, pcm, &ret, pass, cw);
     decode_entropy_pass<false>(ew, pkt, st, &pl, &side, data, &ret, pass);
     decode_entropy_pass<true>(ew, pkt, st, &pl, &side, data, &ret, pass);
     for (int c = 0; c < st->channels; c++) decode_synth_pass(sw, st, &pl, &side, pcm, c, pass);
@@ -108,7 +108,7 @@ int emu_ms_decode(void* p, const unsigned char* data, int len, short* pcm, int f
     StreamPlan* pl = &m->plans[s];
     i32 r = pl->ret;
     for (int pass = 0; pass < pl->nframes; pass++) {
-      decode_silk_pass(m->st[s], pl, data, epcm[s], &r, pass, cw);
+      decode_silk_pass(m->st[s], pl, &side, data, epcm[s], &r, pass, cw);
       decode_entropy_pass<false>(ew, pkt, m->st[s], pl, &side, data, &r, pass);
       decode_entropy_pass<true>(ew, pkt, m->st[s], pl, &side, data, &r, pass);
       for (int c = 0; c < m->st[s]->channels; c++) decode_synth_pass(sw, m->st[s], pl, &side, epcm[s], c, pass);
