@@ -53,14 +53,9 @@ CB_FN void decode_entropy_pass(EntWork& w, u8* pkt, OpusDecState* st, StreamPlan
       int fs48 = nsamp * st->celt.downsample;
       while ((120 << LMp) < fs48) LMp++;
     }
-    const int endp = opus_bandwidth_endband(st->bandwidth);
-    if (st->celt.loss_count >= 5) {
-      celt_plc_noise(w, &st->celt, side, LMp, 0, endp);      // synthesised by kernel B
-    } else {
-      side->kind = 2;                                          // pitch-based: kernel C
-      side->LM = LMp;
-      side->accum = 0;
-    }
+    // noise-based concealment (five or more losses in a row; the pitch-based kind is the PLC route):
+    // synthesised by kernel B
+    celt_plc_noise(w, &st->celt, side, LMp, 0, opus_bandwidth_endband(st->bandwidth));
     st->rangeFinal = 0;
     st->prev_redundancy = 0;
     return;
