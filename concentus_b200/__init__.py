@@ -57,6 +57,7 @@ EXPORTS = [
     "opus_multistream_decode_float", "opus_multistream_decoder_ctl", "opus_multistream_decoder_destroy",
     "opus_multistream_decode_batch", "opus_multistream_decoder_group_create",
     "opus_multistream_decoder_group_destroy", "opus_multistream_decode_group_flat",
+    "opus_multistream_decode_group_submit", "opus_multistream_decode_group_wait",
     "opus_encoder_get_size", "opus_encoder_create", "opus_encode", "opus_encode_float", "opus_encoder_ctl",
     "opus_encoder_destroy", "opus_encode_batch", "opus_encoder_group_create", "opus_encoder_group_destroy",
     "opus_encode_group_flat", "opus_encode_group_device", "opus_encoder_get_final_range_batch",
@@ -141,6 +142,9 @@ def load():
     lib.opus_multistream_decoder_group_destroy.restype = None
     lib.opus_multistream_decode_group_flat.argtypes = [vp, vp, ctypes.c_int32, vp, vp, vp, ctypes.c_int32,
                                                        ctypes.c_int, vp, vp]
+    lib.opus_multistream_decode_group_submit.argtypes = [vp, vp, ctypes.c_int32, vp, vp, vp, ctypes.c_int32,
+                                                       ctypes.c_int, vp, vp]
+    lib.opus_multistream_decode_group_wait.argtypes = [vp]
     lib.opus_decoder_get_final_range_batch.argtypes = [vp, ctypes.c_int, vp]
     lib.opus_encoder_create.restype = vp
     lib.opus_encoder_create.argtypes = [ctypes.c_int32, ctypes.c_int, ctypes.c_int, c_int_p]

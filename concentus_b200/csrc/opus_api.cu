@@ -823,7 +823,38 @@ struct OpusMSDecoderGroup {
   OpusDecoderGroup* eg;         // group over all elementary decoders
   MSLayout* d_layouts;
   i32* d_ms_ret;
+  struct MSPipe* pipe;          // created by the first opus_multistream_decode_group_submit
 };
+
+// Two-deep pipeline behind opus_multistream_decode_group_submit/_wait (see DecPipe)
+struct MSPipeSlot {
+  GrowBuf d_pkt, d_pcm, d_epcm, d_i32, h_i32;     // d_i32 = offsets, lengths, fec flags, return values (4n)
+  cudaEvent_t in_done = nullptr, k_done = nullptr, out_done = nullptr;
+  bool busy = false;
+  MSPipeSlot() { h_i32.pinned = true; }
+};
+struct MSPipe {
+  cudaStream_t s_in = nullptr, s_out = nullptr;
+  MSPipeSlot slot[2];
+  unsigned long long seq = 0;
+};
+static void ms_pipe_free(MSPipe* p) {
+  if (!p) return;
+  for (MSPipeSlot& sl : p->slot) {
+    if (sl.busy && sl.out_done) cudaEventSynchronize(sl.out_done);
+    if (sl.d_pkt.p) cudaFree(sl.d_pkt.p);
+    if (sl.d_pcm.p) cudaFree(sl.d_pcm.p);
+    if (sl.d_epcm.p) cudaFree(sl.d_epcm.p);
+    if (sl.d_i32.p) cudaFree(sl.d_i32.p);
+    if (sl.h_i32.p) cudaFreeHost(sl.h_i32.p);
+    if (sl.in_done) cudaEventDestroy(sl.in_done);
+    if (sl.k_done) cudaEventDestroy(sl.k_done);
+    if (sl.out_done) cudaEventDestroy(sl.out_done);
+  }
+  if (p->s_in) cudaStreamDestroy(p->s_in);
+  if (p->s_out) cudaStreamDestroy(p->s_out);
+  delete p;
+}
 
 #define OPUS_MULTISTREAM_GET_DECODER_STATE_REQUEST 5122
 const int kMagicMS = 0x4f424d53;
@@ -921,6 +952,11 @@ OpusMSDecoderGroup* opus_multistream_decoder_group_create(OpusMSDecoder* const* 
 
 void opus_multistream_decoder_group_destroy(OpusMSDecoderGroup* g) {
   if (!g || g->magic != kMagicMS) return;
+  {
+    std::lock_guard<std::mutex> lk(g_mu);
+    ms_pipe_free(g->pipe);
+    g->pipe = nullptr;
+  }
   opus_decoder_group_destroy(g->eg);
   {
     std::lock_guard<std::mutex> lk(g_mu);
@@ -934,14 +970,12 @@ void opus_multistream_decoder_group_destroy(OpusMSDecoderGroup* g) {
 
 // Flat host form for multistream packets: packet m at data[offsets[m]..+len[m]) (offset<0 or len 0 = lost),
 // PCM row m = pcm + m*pcm_stride holding frame_size*channels interleaved samples.
-int opus_multistream_decode_group_flat(OpusMSDecoderGroup* g, const unsigned char* data, opus_int32 data_bytes,
-                                       const opus_int32* offsets, const opus_int32* len, opus_int16* pcm,
-                                       opus_int32 pcm_stride, int frame_size, const int* decode_fec, int* ret) {
-  if (!g || g->magic != kMagicMS || !offsets || !len || !pcm || !ret) return OPUS_BAD_ARG;
-  if (data_bytes < 0 || (data_bytes > 0 && !data)) return OPUS_BAD_ARG;
+// Host-side walk over the sub-packets of every multistream packet (byte reads only): number of passes the
+// elementary kernels need, the largest elementary frame (staged in shared memory by kernel A), and the
+// shortest-frame bookkeeping of the elementary decoders.  Returns OPUS_OK or OPUS_BAD_ARG.
+static int ms_scan(OpusMSDecoderGroup* g, const unsigned char* data, opus_int32 data_bytes, const opus_int32* offsets,
+                   const opus_int32* len, const int* decode_fec, int frame_size, int* passes_out, int* max_len_out) {
   const int n = g->n_ms;
-  if (frame_size <= 0) { for (int i = 0; i < n; i++) ret[i] = OPUS_BAD_ARG; return OPUS_OK; }
-  if (pcm_stride < frame_size * g->max_channels) return OPUS_BAD_ARG;
   // passes: walk the sub-packets on the host (byte reads only) to find the largest frame count
   int passes = 1, max_len = 0, any_lost = 0, any_fec = 0, minFs = 48000;
   int group_min = 1 << 30;
@@ -982,6 +1016,24 @@ int opus_multistream_decode_group_flat(OpusMSDecoderGroup* g, const unsigned cha
     if (chunks > passes) passes = chunks;
   }
   if (passes > CB_MAX_FRAMES) passes = CB_MAX_FRAMES;
+  *passes_out = passes;
+  *max_len_out = max_len;
+  return OPUS_OK;
+}
+
+int opus_multistream_decode_group_flat(OpusMSDecoderGroup* g, const unsigned char* data, opus_int32 data_bytes,
+                                       const opus_int32* offsets, const opus_int32* len, opus_int16* pcm,
+                                       opus_int32 pcm_stride, int frame_size, const int* decode_fec, int* ret) {
+  if (!g || g->magic != kMagicMS || !offsets || !len || !pcm || !ret) return OPUS_BAD_ARG;
+  if (data_bytes < 0 || (data_bytes > 0 && !data)) return OPUS_BAD_ARG;
+  const int n = g->n_ms;
+  if (frame_size <= 0) { for (int i = 0; i < n; i++) ret[i] = OPUS_BAD_ARG; return OPUS_OK; }
+  if (pcm_stride < frame_size * g->max_channels) return OPUS_BAD_ARG;
+  int passes = 1, max_len = 0;
+  {
+    const int rc0 = ms_scan(g, data, data_bytes, offsets, len, decode_fec, frame_size, &passes, &max_len);
+    if (rc0 != OPUS_OK) return rc0;
+  }
   std::lock_guard<std::mutex> lk(g_mu);
   CUDA_OK(cudaSetDevice(g->device));
   int err = 0;
@@ -1018,6 +1070,91 @@ int opus_multistream_decode_group_flat(OpusMSDecoderGroup* g, const unsigned cha
   CUDA_OK(cudaMemcpyAsync(pcm, c->d_pcm.p, pcm_bytes, cudaMemcpyDeviceToHost, s));
   CUDA_OK(cudaMemcpyAsync(ret, g->d_ms_ret, n * sizeof(i32), cudaMemcpyDeviceToHost, s));
   CUDA_OK(cudaStreamSynchronize(s));
+  return OPUS_OK;
+}
+
+// Asynchronous form of opus_multistream_decode_group_flat (same contract as opus_decode_group_submit: buffers
+// stay alive and unchanged until the wait, page-locked for the copies to overlap; two calls in flight).
+int opus_multistream_decode_group_submit(OpusMSDecoderGroup* g, const unsigned char* data, opus_int32 data_bytes,
+                                         const opus_int32* offsets, const opus_int32* len, opus_int16* pcm,
+                                         opus_int32 pcm_stride, int frame_size, const int* decode_fec, int* ret) {
+  if (!g || g->magic != kMagicMS || !offsets || !len || !pcm || !ret) return OPUS_BAD_ARG;
+  if (data_bytes < 0 || (data_bytes > 0 && !data) || frame_size <= 0) return OPUS_BAD_ARG;
+  const int n = g->n_ms;
+  if (pcm_stride < frame_size * g->max_channels) return OPUS_BAD_ARG;
+  int passes = 1, max_len = 0;
+  {
+    const int rc0 = ms_scan(g, data, data_bytes, offsets, len, decode_fec, frame_size, &passes, &max_len);
+    if (rc0 != OPUS_OK) return rc0;
+  }
+  std::lock_guard<std::mutex> lk(g_mu);
+  CUDA_OK(cudaSetDevice(g->device));
+  int err = 0;
+  DevCtx* c = ctx_for_current_device(&err);
+  if (!c) return err;
+  if (!g->pipe) {
+    MSPipe* p = new MSPipe();
+    bool ok = cudaStreamCreateWithFlags(&p->s_in, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&p->s_out, cudaStreamNonBlocking) == cudaSuccess;
+    for (MSPipeSlot& sl : p->slot)
+      ok = ok && cudaEventCreateWithFlags(&sl.in_done, cudaEventDisableTiming) == cudaSuccess &&
+           cudaEventCreateWithFlags(&sl.k_done, cudaEventDisableTiming) == cudaSuccess &&
+           cudaEventCreateWithFlags(&sl.out_done, cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) { ms_pipe_free(p); return OPUS_ALLOC_FAIL; }
+    g->pipe = p;
+  }
+  MSPipe* p = g->pipe;
+  MSPipeSlot& sl = p->slot[p->seq & 1];
+  if (sl.busy) { CUDA_OK(cudaEventSynchronize(sl.out_done)); sl.busy = false; }
+  OpusDecoderGroup* eg = g->eg;
+  const i32 estride = frame_size * 2;
+  const size_t pcm_bytes = (size_t)n * pcm_stride * sizeof(i16);
+  const size_t in_bytes = (size_t)n * 3 * sizeof(i32);
+  if (sl.d_pkt.reserve((size_t)data_bytes + 16) || sl.d_pcm.reserve(pcm_bytes) ||
+      sl.d_epcm.reserve((size_t)eg->n * estride * sizeof(i16)) || sl.d_i32.reserve((size_t)n * 4 * sizeof(i32)) ||
+      sl.h_i32.reserve(in_bytes))
+    return OPUS_ALLOC_FAIL;
+  i32* h_i = (i32*)sl.h_i32.p;
+  memcpy(h_i, offsets, n * sizeof(i32));
+  memcpy(h_i + n, len, n * sizeof(i32));
+  if (decode_fec) memcpy(h_i + 2 * n, decode_fec, n * sizeof(i32));
+  else memset(h_i + 2 * n, 0, n * sizeof(i32));
+  i32* d_i = (i32*)sl.d_i32.p;
+  i32* d_ms_ret = d_i + 3 * n;
+  i16* d_epcm = (i16*)sl.d_epcm.p;
+  if (data_bytes > 0) CUDA_OK(cudaMemcpyAsync(sl.d_pkt.p, data, data_bytes, cudaMemcpyHostToDevice, p->s_in));
+  CUDA_OK(cudaMemcpyAsync(d_i, h_i, in_bytes, cudaMemcpyHostToDevice, p->s_in));
+  CUDA_OK(cudaEventRecord(sl.in_done, p->s_in));
+  cudaStream_t s = c->stream;
+  CUDA_OK(cudaStreamWaitEvent(s, sl.in_done, 0));
+  int rc = cbk_launch_ms_plan(eg->d_states, eg->d_plans, g->d_layouts, (const u8*)sl.d_pkt.p, d_i, d_i + n, d_i + 2 * n,
+                              frame_size, d_ms_ret, n, s);
+  g_launches += 1;
+  if (rc) { fprintf(stderr, "[opus_b200] ms plan launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
+  rc = group_enqueue_passes(eg, (const u8*)sl.d_pkt.p, d_epcm, estride, eg->d_ret, passes, max_len, s);
+  if (rc != OPUS_OK) return rc;
+  rc = cbk_launch_ms_scatter(g->d_layouts, d_ms_ret, d_epcm, estride, (i16*)sl.d_pcm.p, pcm_stride, n, s);
+  g_launches += 1;
+  if (rc) { fprintf(stderr, "[opus_b200] ms scatter launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
+  CUDA_OK(cudaEventRecord(sl.k_done, s));
+  CUDA_OK(cudaStreamWaitEvent(p->s_out, sl.k_done, 0));
+  CUDA_OK(cudaMemcpyAsync(pcm, sl.d_pcm.p, pcm_bytes, cudaMemcpyDeviceToHost, p->s_out));
+  CUDA_OK(cudaMemcpyAsync(ret, d_ms_ret, n * sizeof(i32), cudaMemcpyDeviceToHost, p->s_out));
+  CUDA_OK(cudaEventRecord(sl.out_done, p->s_out));
+  sl.busy = true;
+  p->seq++;
+  return OPUS_OK;
+}
+
+int opus_multistream_decode_group_wait(OpusMSDecoderGroup* g) {
+  if (!g || g->magic != kMagicMS) return OPUS_BAD_ARG;
+  std::lock_guard<std::mutex> lk(g_mu);
+  if (!g->pipe) return OPUS_OK;
+  CUDA_OK(cudaSetDevice(g->device));
+  for (int k = 0; k < 2; k++) {
+    MSPipeSlot& sl = g->pipe->slot[(g->pipe->seq + k) & 1];      // oldest first
+    if (sl.busy) { CUDA_OK(cudaEventSynchronize(sl.out_done)); sl.busy = false; }
+  }
   return OPUS_OK;
 }
 

@@ -189,6 +189,11 @@ void opus_multistream_decoder_group_destroy(OpusMSDecoderGroup *grp);
 int opus_multistream_decode_group_flat(OpusMSDecoderGroup *grp, const unsigned char *data, opus_int32 data_bytes,
                                        const opus_int32 *offsets, const opus_int32 *len, opus_int16 *pcm,
                                        opus_int32 pcm_stride, int frame_size, const int *decode_fec, int *ret);
+/* Pipelined form (see opus_decode_group_submit): pcm / ret are complete after the wait. */
+int opus_multistream_decode_group_submit(OpusMSDecoderGroup *grp, const unsigned char *data, opus_int32 data_bytes,
+                                         const opus_int32 *offsets, const opus_int32 *len, opus_int16 *pcm,
+                                         opus_int32 pcm_stride, int frame_size, const int *decode_fec, int *ret);
+int opus_multistream_decode_group_wait(OpusMSDecoderGroup *grp);
 
 /* No counterpart in the reference (libopus keeps all scratch on the caller's stack).
  * Device-resident batch decode that allocates nothing: for callers that must not call cudaMalloc --

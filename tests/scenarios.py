@@ -129,3 +129,29 @@ def silk_calls(npackets, loss, fec, seed=11):
             pending = False
         out.append((i, 0))
     return out
+
+
+def silk_fuzz_calls(packets, seed, random_toc=False):
+    """Corrupted, truncated and random payloads for the SILK / hybrid fixtures (the TOC is kept unless
+    random_toc, which also throws the decoder between modes on garbage): list of packet bytes or None."""
+    import numpy as np
+    rng = np.random.RandomState(seed)
+    out = []
+    for p in packets:
+        u = rng.rand()
+        if u < 0.35:
+            b = bytearray(p)
+            for _ in range(rng.randint(1, 8)):
+                if len(b) > 1:
+                    b[rng.randint(1, len(b))] = rng.randint(0, 256)
+            p = bytes(b)
+        elif u < 0.5 and len(p) > 2:
+            p = p[:rng.randint(1, len(p))]
+        elif u < 0.6:
+            p = bytes([p[0]]) + bytes(rng.randint(0, 256, size=rng.randint(1, 120), dtype=np.uint8).tolist())
+        elif u < 0.65:
+            p = None
+        if p is not None and random_toc and rng.rand() < 0.3:
+            p = bytes([int(rng.randint(0, 256)) & 0xFC]) + p[1:]       # any configuration, one frame
+        out.append(p)
+    return out

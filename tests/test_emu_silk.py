@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 
 from conftest import (GOLDEN, EmuOpusDecoder, RefDecoder, RefEncoder, crc32, needs_ref, read_bit, silk_golden_index)
-from scenarios import silk_calls
+from scenarios import silk_calls, silk_fuzz_calls
 
 CASES = sorted(silk_golden_index().keys())
 
@@ -148,3 +148,27 @@ def test_emu_hybrid_and_transitions_match_reference(emu_lib, script):
                         assert r1 == r2, (script, ch, ms, fs_dec, chd, loss, fec, idx)
                         assert np.array_equal(p1[:r1], p2[:r1]), (script, ch, ms, fs_dec, chd, loss, fec, idx)
                         assert ref.final_range == emu.final_range, (script, ch, ms, fs_dec, chd, loss, fec, idx)
+
+
+@needs_ref
+@pytest.mark.parametrize("name", ["silk_wb_mono_32k", "silk_wb_st_40k", "silk_nb_st_40ms", "silk_wb_mono_60ms",
+                                  "hyb_fb_mono_32k", "hyb_swb_st_48k", "trans_all_st_to24", "trans_all_mono_10ms_loss"])
+@pytest.mark.parametrize("random_toc", [False, True])
+def test_emu_silk_corrupted_packets_follow_reference(emu_lib, name, random_toc):
+    """Damaged, truncated and random payloads (optionally with random TOC bytes, which throw the decoder
+    between SILK, hybrid and CELT on garbage): return value, PCM and final range must still equal the
+    reference's for every call -- the reference decodes garbage deterministically."""
+    meta = silk_golden_index()[name]
+    pk = [p for p, _ in read_bit(os.path.join(GOLDEN, name + ".bit"))]
+    calls = silk_fuzz_calls(pk, seed=len(name) * 3 + random_toc, random_toc=random_toc)
+    ref, emu = RefDecoder(meta["fs"], meta["channels"]), EmuOpusDecoder(emu_lib, meta["fs"], meta["channels"])
+    # a frame size that holds any one-frame packet of any configuration (60 ms)
+    fsz = meta["fs"] * 60 // 1000
+    for k, data in enumerate(calls):
+        want = fsz if data is not None else meta["samples_per_frame"]
+        r1, p1 = ref.decode_raw(data, want)
+        r2, p2 = emu.decode_raw(data, want)
+        assert r1 == r2, (name, k, r1, r2)
+        if r1 > 0:
+            assert np.array_equal(p1[:r1], p2[:r1]), (name, k)
+        assert ref.final_range == emu.final_range, (name, k)

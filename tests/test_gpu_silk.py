@@ -9,7 +9,7 @@ import pytest
 
 import concentus_b200 as cb
 from conftest import GOLDEN, RefDecoder, crc32, golden_case, needs_ref, read_bit, silk_golden_index
-from scenarios import silk_calls
+from scenarios import silk_calls, silk_fuzz_calls
 from test_emu_silk import TRANSITION_SCRIPTS, scripted_packets, silk_packets
 
 pytestmark = pytest.mark.gpu
@@ -142,3 +142,35 @@ def test_decoder_queries_follow_the_reference(name):
     finally:
         dec.close()
         ref.close()
+
+
+@needs_ref
+@pytest.mark.parametrize("fs,ch", [(48000, 2), (16000, 1)])
+def test_batch_of_corrupted_streams_follows_reference(fs, ch):
+    """Sixteen streams of damaged / truncated / random packets with random TOC bytes in one batch per call:
+    every route (CELT, SILK, hybrid, transitions, concealment, errors) mixes in each launch, and each stream
+    must still do exactly what the reference does with the same garbage."""
+    names = ["silk_wb_mono_32k", "silk_wb_st_40k", "silk_nb_st_40ms", "silk_wb_mono_60ms", "hyb_fb_mono_32k",
+             "hyb_swb_st_48k", "trans_all_st_to24", "trans_all_mono_10ms_loss"]
+    streams = []
+    for i in range(16):
+        pk = [p for p, _ in read_bit(os.path.join(GOLDEN, names[i % len(names)] + ".bit"))]
+        streams.append(silk_fuzz_calls(pk, seed=100 + i, random_toc=(i % 2 == 1)))
+    steps = min(len(c) for c in streams)
+    n = len(streams)
+    fsz = fs * 60 // 1000
+    bd = cb.OpusBatchDecoder(fs, ch, n)
+    refs = [RefDecoder(fs, ch) for _ in range(n)]
+    try:
+        for t in range(steps):
+            pkts = [streams[i][t] for i in range(n)]
+            ret, pcm = bd.decode(pkts, fsz)
+            fr = bd.final_ranges()
+            for i in range(n):
+                r1, p1 = refs[i].decode_raw(pkts[i], fsz)
+                assert ret[i] == r1, (i, t, ret[i], r1)
+                if r1 > 0:
+                    assert np.array_equal(pcm[i][:r1], p1[:r1]), (i, t)
+                assert int(fr[i]) == refs[i].final_range, (i, t)
+    finally:
+        bd.close()

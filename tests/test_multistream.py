@@ -97,3 +97,39 @@ def test_gpu_multistream_errors():
     err = ctypes.c_int(0)
     bad = (ctypes.c_ubyte * 6)(0, 4, 1, 2, 3, 9)       # mapping refers to a channel that does not exist
     assert not lib.opus_multistream_decoder_create(48000, 6, 4, 2, bad, ctypes.byref(err)) and err.value == cb.OPUS_BAD_ARG
+
+
+@pytest.mark.gpu
+def test_gpu_multistream_pipelined_submit_matches_golden():
+    """opus_multistream_decode_group_submit/_wait: 32 decoders replay the 5.1 fixture (with its lost packets)
+    from staggered offsets, ten calls queued back to back; decoder 0 must reproduce the golden CRCs."""
+    import torch
+    meta, pk = ms_case("ms51_256k")
+    lib = cb.load()
+    n, steps = 32, 10
+    bd = cb.OpusMSBatchDecoder(48000, 6, meta["streams"], meta["coupled"], meta["mapping"], n)
+    maxlen = max(len(p) for p, _ in pk)
+    try:
+        bufs = []
+        for t in range(steps):
+            arena = torch.zeros(n * maxlen, dtype=torch.uint8).pin_memory()
+            offs = torch.zeros(n, dtype=torch.int32).pin_memory()
+            lens = torch.zeros(n, dtype=torch.int32).pin_memory()
+            for i in range(n):
+                p = pk[(t + 5 * i) % len(pk)][0] if i else pk[t][0]
+                lens[i] = len(p)
+                offs[i] = i * maxlen if p else -1
+                if p:
+                    arena[i * maxlen:i * maxlen + len(p)] = torch.frombuffer(bytearray(p), dtype=torch.uint8)
+            pcm = torch.zeros(n * 960 * 6, dtype=torch.int16).pin_memory()
+            ret = torch.zeros(n, dtype=torch.int32).pin_memory()
+            bufs.append((arena, offs, lens, pcm, ret))
+            assert lib.opus_multistream_decode_group_submit(bd._g, arena.data_ptr(), arena.numel(), offs.data_ptr(),
+                                                            lens.data_ptr(), pcm.data_ptr(), 960 * 6, 960, None,
+                                                            ret.data_ptr()) == 0
+        assert lib.opus_multistream_decode_group_wait(bd._g) == 0
+        for t, (_, _, _, pcm, ret) in enumerate(bufs):
+            assert bool((ret == 960).all()), t
+            assert crc32(pcm.numpy().reshape(n, 960, 6)[0]) == meta["pcm_crc32"][t], t
+    finally:
+        bd.close()
