@@ -6,7 +6,9 @@
 #include "cb_celt_plc.h"
 #include "cb_opus_plan.h"
 
-// Kernel A, one stream, one pass.  `pkt` = per-warp staging area for the payload bytes.
+// Kernel A, one stream, one pass.  `pkt` = per-warp staging area for the payload bytes, or nullptr: the range
+// decoder then reads the packet where it lies in global memory (a few dozen dependent byte loads per frame are
+// nothing next to the frame's decode time; staging large packets would cost a resident CTA per SM).
 // Two instances: HYB = false takes the CELT-only frames (start band 0, fresh range decoder: the constants
 // fold into the decoder), HYB = true the CELT layer of hybrid frames whose SILK layer the SILK kernel has
 // already written to the PCM row (bands 17.., coder state continued, output accumulated).
@@ -61,7 +63,11 @@ CB_FN void decode_entropy_pass(EntWork& w, u8* pkt, OpusDecState* st, StreamPlan
     return;
   }
   const i32 off = pl->off[pass];
-  CB_LANE_LOOP(i, len) pkt[i] = data[off + i];
+  const u8* src = data + off;
+  if (pkt) {
+    CB_LANE_LOOP(i, len) pkt[i] = src[i];
+    src = pkt;
+  }
   CB_WSYNC();
   int LM = 0;
   {
@@ -81,7 +87,7 @@ CB_FN void decode_entropy_pass(EntWork& w, u8* pkt, OpusDecState* st, StreamPlan
     CB_WSYNC();
   }
   u32 fr = 0;
-  int rc = celt_entropy_decode(w, &st->celt, side, pkt, len, cfg, &fr);
+  int rc = celt_entropy_decode(w, &st->celt, side, src, len, cfg, &fr);
   CB_WSYNC();
   st->rangeFinal = fr;
   st->prev_mode = hybrid ? CB_MODE_HYBRID : CB_MODE_CELT_ONLY;

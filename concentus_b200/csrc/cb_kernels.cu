@@ -36,7 +36,7 @@ celt_entropy_kernel(OpusDecState* const* states, const u8* data, StreamPlan* pla
   const int s = blockIdx.x * A_WARPS + warp;
   if (s >= n) return;
   EntWork& w = *reinterpret_cast<EntWork*>(smem + (size_t)warp * per_warp_bytes);
-  u8* pkt = reinterpret_cast<u8*>(&w) + sizeof(EntWork);
+  u8* pkt = per_warp_bytes > (int)sizeof(EntWork) ? reinterpret_cast<u8*>(&w) + sizeof(EntWork) : nullptr;
   OpusDecState* st = states[s];
   StreamPlan* pl = &plans[s];
   FrameSide* side = &sides[s];
@@ -101,9 +101,13 @@ __global__ void opus_ms_scatter_kernel(const MSLayout* layouts, const i32* ms_re
 // ---- launchers (host) ------------------------------------------------------------------------
 static int g_attr_done[64];
 
+// Shared memory of one warp of kernel A: the work area plus, when it still leaves room for 7 CTAs per SM
+// (227 KB, 1 KB reserved per CTA), a staging area for the packet; larger packets are read from global memory.
 extern "C" size_t cbk_entropy_smem_per_warp(int max_payload) {
-  size_t b = sizeof(EntWork) + (size_t)((max_payload + 15) & ~15);
-  return (b + 15) & ~(size_t)15;
+  const size_t work = (sizeof(EntWork) + 15) & ~(size_t)15;
+  const size_t staged = work + (size_t)((max_payload + 15) & ~15);
+  const size_t limit = ((227 * 1024) / 7 - 1024) / A_WARPS;
+  return staged <= limit ? staged : work;
 }
 
 extern "C" int cbk_launch_plan(OpusDecState* const* d_states, const u8* d_data, const i32* d_off,
