@@ -34,14 +34,14 @@ CB_FN const u8* sk_pitch_contour_icdf(int fs_kHz, int nb_subfr) {
   if (fs_kHz == 8) return nb_subfr == 4 ? st_pitch_contour_NB_iCDF : st_pitch_contour_10ms_NB_iCDF;
   return nb_subfr == 4 ? st_pitch_contour_iCDF : st_pitch_contour_10ms_iCDF;
 }
-CB_UTABLE u8 st_uniform3_iCDF[3] = {171, 85, 0};
-CB_UTABLE u8 st_uniform4_iCDF[4] = {192, 128, 64, 0};
-CB_UTABLE u8 st_uniform5_iCDF[5] = {205, 154, 102, 51, 0};
-CB_UTABLE u8 st_uniform6_iCDF[6] = {213, 171, 128, 85, 43, 0};
-CB_UTABLE u8 st_uniform8_iCDF[8] = {224, 192, 160, 128, 96, 64, 32, 0};
-CB_UTABLE u8 st_lsb_iCDF[2] = {120, 0};
-CB_UTABLE u8 st_LTPscale_iCDF[3] = {128, 64, 0};
-CB_UTABLE u8 st_stereo_only_code_mid_iCDF[2] = {64, 0};
+// (indexed per lane like every SILK table, and padded by 4 for rd_icdf_g's read-ahead)
+CB_GTABLE u8 st_uniform3_iCDF[3 + 4] = {171, 85, 0, 0, 0, 0, 0};
+CB_GTABLE u8 st_uniform4_iCDF[4 + 4] = {192, 128, 64, 0, 0, 0, 0, 0};
+CB_GTABLE u8 st_uniform5_iCDF[5 + 4] = {205, 154, 102, 51, 0, 0, 0, 0, 0};
+CB_GTABLE u8 st_uniform6_iCDF[6 + 4] = {213, 171, 128, 85, 43, 0, 0, 0, 0, 0};
+CB_GTABLE u8 st_uniform8_iCDF[8 + 4] = {224, 192, 160, 128, 96, 64, 32, 0, 0, 0, 0, 0};
+CB_GTABLE u8 st_LTPscale_iCDF[3 + 4] = {128, 64, 0, 0, 0, 0, 0};
+CB_GTABLE u8 st_stereo_only_code_mid_iCDF[2 + 4] = {64, 0, 0, 0, 0, 0};
 CB_FN const u8* sk_pitch_lag_low_bits_icdf(int fs_kHz) {
   return fs_kHz == 16 ? st_uniform8_iCDF : fs_kHz == 12 ? st_uniform6_iCDF : st_uniform4_iCDF;
 }
@@ -461,7 +461,7 @@ CB_FN void sk_decode_parameters(SilkChannel& ps, SilkDecControl& ctrl, int condC
     const i8* cbk = ps.indices.PERIndex == 0 ? st_LTP_gain_vq_0 : ps.indices.PERIndex == 1 ? st_LTP_gain_vq_1 : st_LTP_gain_vq_2;
     for (int k = 0; k < ps.nb_subfr; k++) {
       const int Ix = ps.indices.LTPIndex[k];
-      for (int i = 0; i < SK_LTP_ORDER; i++) ctrl.LTPCoef_Q14[k * SK_LTP_ORDER + i] = (i16)(cbk[Ix * SK_LTP_ORDER + i] << 7);
+      for (int i = 0; i < SK_LTP_ORDER; i++) ctrl.LTPCoef_Q14[k * SK_LTP_ORDER + i] = (i16)sk_lshift(cbk[Ix * SK_LTP_ORDER + i], 7);
     }
     ctrl.LTP_scale_Q14 = st_LTPScales_Q14[ps.indices.LTP_scaleIndex];
   } else {
