@@ -135,9 +135,16 @@ static inline void opus_enc_init(OpusEncState* st, int Fs, int channels, int app
 // Large per-frame buffers of one stream (global memory).
 struct alignas(16) EncScratch {
   i32 in[2][CB_MAXN + CB_OVERLAP];                       // pre-emphasised (then pre-filtered) signal
-  i32 pre[2][CB_MAXN + CB_COMBFILTER_MAXPERIOD];         // pre-filter input with history
-  i32 freq[2][CB_MAXN];                                  // MDCT coefficients
-  i32 f2[CB_MAXN];                                       // forward-MDCT FFT buffer
+  // The pre-filter's input is dead once run_prefilter has written `in` and the filter memory back, and the
+  // MDCT buffers are first written after that: they share storage (11.5 KB less scratch per stream; the
+  // scratch of a 4096-stream batch is larger than the L2, so its size is DRAM traffic).
+  union {
+    i32 pre[2][CB_MAXN + CB_COMBFILTER_MAXPERIOD];       // pre-filter input with history
+    struct {
+      i32 freq[2][CB_MAXN];                              // MDCT coefficients
+      i32 f2[CB_MAXN];                                   // forward-MDCT FFT buffer
+    };
+  };
   i32 xcorr[(CB_COMBFILTER_MAXPERIOD >> 1) + 8];
   i32 yy_lookup[(CB_COMBFILTER_MAXPERIOD >> 1) + 8];
   i32 ac[CB_LPC_ORDER + 1];
