@@ -45,11 +45,11 @@ celt_entropy_kernel(OpusDecState* const* states, const u8* data, StreamPlan* pla
 
 __global__ void __launch_bounds__(B_WARPS * 32, 7)
 celt_synth_kernel(OpusDecState* const* states, const StreamPlan* plans, const FrameSide* sides, i16* pcm,
-                  i32 pcm_stride, int n, int pass) {
+                  i32 pcm_stride, int n, int pass, int max_ch) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int warp = threadIdx.x >> 5;
   const int gw = blockIdx.x * B_WARPS + warp;
-  const int s = gw >> 1, c = gw & 1;
+  const int s = max_ch == 2 ? gw >> 1 : gw, c = max_ch == 2 ? gw & 1 : 0;   // a warp per channel the group can have
   if (s >= n) return;
   OpusDecState* st = states[s];
   const int CC = st->channels;
@@ -153,14 +153,15 @@ extern "C" int cbk_launch_entropy(OpusDecState* const* d_states, const u8* d_dat
 }
 
 extern "C" int cbk_launch_synth(OpusDecState* const* d_states, const StreamPlan* d_plans, const FrameSide* d_sides,
-                                i16* d_pcm, i32 pcm_stride, int n, int pass, cudaStream_t stream) {
+                                i16* d_pcm, i32 pcm_stride, int n, int pass, int max_ch, cudaStream_t stream) {
   if (n <= 0) return 0;
   int rc = ensure_attrs();
   if (rc) return rc;
   const size_t smemB = sizeof(SynWork) * B_WARPS;
-  const int warpsB = n * 2;
+  if (max_ch != 1) max_ch = 2;
+  const int warpsB = n * max_ch;
   celt_synth_kernel<<<(warpsB + B_WARPS - 1) / B_WARPS, B_WARPS * 32, smemB, stream>>>(
-      d_states, d_plans, d_sides, d_pcm, pcm_stride, n, pass);
+      d_states, d_plans, d_sides, d_pcm, pcm_stride, n, pass, max_ch);
   return (int)cudaGetLastError();
 }
 

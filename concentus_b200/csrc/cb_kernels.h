@@ -12,7 +12,7 @@ int cbk_launch_plan(OpusDecState* const* d_states, const u8* d_data, const i32* 
 int cbk_launch_entropy(OpusDecState* const* d_states, const u8* d_data, StreamPlan* d_plans, FrameSide* d_sides,
                        i32* d_ret, int n, int pass, int max_payload, cudaStream_t stream);
 int cbk_launch_synth(OpusDecState* const* d_states, const StreamPlan* d_plans, const FrameSide* d_sides,
-                     i16* d_pcm, i32 pcm_stride, int n, int pass, cudaStream_t stream);
+                     i16* d_pcm, i32 pcm_stride, int n, int pass, int max_ch, cudaStream_t stream);
 // SILK frames of pass `pass` (one thread per stream); streams whose frame is CELT return at once
 int cbk_launch_plan_silk(OpusDecState* const* d_states, const u8* d_data, const i32* d_off, const i32* d_len,
                          const i32* d_fec, int frame_size, StreamPlan* d_plans, FrameSide* d_sides, i16* d_pcm,

@@ -117,7 +117,7 @@ extern "C" int opus_decode_batch_device_static(OpusDecoder* const* st, int n, co
   for (int p = 0; p < max_frames && !rc; p++) {
     if (p > 0) rc = cbk_launch_silk(s->states, s->plans, s->sides, d_data, d_pcm, pcm_stride, d_ret, n, p, stream);
     if (!rc) rc = cbk_launch_entropy(s->states, d_data, s->plans, s->sides, d_ret, n, p, max_packet_bytes, stream);
-    if (!rc) rc = cbk_launch_synth(s->states, s->plans, s->sides, d_pcm, pcm_stride, n, p, stream);
+    if (!rc) rc = cbk_launch_synth(s->states, s->plans, s->sides, d_pcm, pcm_stride, n, p, 2, stream);
     if (!rc) rc = cbk_launch_general(s->states, s->plans, s->sides, d_data, d_pcm, pcm_stride, d_ret, n, p, stream);
   }
   if (rc) {

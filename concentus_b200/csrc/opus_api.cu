@@ -406,7 +406,7 @@ static int group_enqueue_passes(OpusDecoderGroup* g, const u8* d_data, i16* d_pc
     }
     if (!rc) {
       ProfScope ps(stream, 2);
-      rc = cbk_launch_synth(g->d_states, g->d_plans, g->d_sides, d_pcm, pcm_stride, g->n, p, stream);
+      rc = cbk_launch_synth(g->d_states, g->d_plans, g->d_sides, d_pcm, pcm_stride, g->n, p, g->channels == 1 ? 1 : 2, stream);
     }
     if (!rc && !fork)
       rc = cbk_launch_general(g->d_states, g->d_plans, g->d_sides, d_data, d_pcm, pcm_stride, d_ret, g->n, p, stream);

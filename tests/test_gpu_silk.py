@@ -174,3 +174,24 @@ def test_batch_of_corrupted_streams_follows_reference(fs, ch):
                 assert int(fr[i]) == refs[i].final_range, (i, t)
     finally:
         bd.close()
+
+
+def test_full_size_hybrid_batch_properties():
+    """The hybrid set of config 4 at full size: 16384 mono 48 kHz streams of hybrid fullband packets.  Streams
+    replay the golden fixture from 64 start offsets; copies must agree with each other and the stream that
+    starts at packet 0 must reproduce the golden CRCs (SILK kernel + CELT layer kernels at full occupancy)."""
+    meta = silk_golden_index()["hyb_fb_mono_32k"]
+    pk = [p for p, _ in read_bit(os.path.join(GOLDEN, "hyb_fb_mono_32k.bit"))]
+    n, steps = 16384, 5
+    bd = cb.OpusBatchDecoder(48000, 1, n)
+    try:
+        rot = (3 * (np.arange(n) % 64))
+        for t in range(steps):
+            pkts = [pk[(rot[i] + t) % len(pk)] for i in range(n)]
+            ret, pcm = bd.decode(pkts, 960)
+            assert (ret == 960).all()
+            for i in range(64):
+                assert (pcm[i::64] == pcm[i]).all(), (t, i)
+            assert crc32(pcm[0]) == meta["pcm_crc32"][t], t
+    finally:
+        bd.close()
