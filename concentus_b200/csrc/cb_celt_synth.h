@@ -24,30 +24,43 @@ CB_UTABLE i16 ct_comb_gains[3][3] = {{10048, 7112, 4248}, {15200, 8784, 0}, {262
 CB_FN i32 s_mul(i32 a, i32 b) { return mult16_32_q15(b, a); }
 
 // denormalise_bands (bands.c:169-238) for one channel into dst[0..N)
+// denormalise_bands (bands.c:169-238).  The per-band gains are worked out one band per lane and parked in
+// `tmp` (2 x 21 words of free workspace); the spectrum is then one flat pass over the bins, whose loads do
+// not wait on each other -- a loop over the bands made 21 dependent round trips to the hand-off record.
 CB_FN void v_denormalise(const i16* X, i32* dst, const i16* bandLogE, int start, int end, int M,
-                         int downsample, int silence) {
+                         int downsample, int silence, i32* tmp) {
   const int N = M * 120;
   int bound = M * ct_eband5ms[end];
   if (downsample != 1) bound = cb_imin(bound, N / downsample);
   if (silence) { bound = 0; start = end = 0; }
+  const int jlo = M * ct_eband5ms[start];
+  const int LM = 31 - cb_clz((u32)M);
   CB_WSYNC();
-  CB_LANE_LOOPU(j, M * ct_eband5ms[start]) dst[j] = 0;
-  for (int i = start; i < end; i++) {
-    int j0 = M * ct_eband5ms[i], j1 = M * ct_eband5ms[i + 1];
-    i16 lg = add16(bandLogE[i], shl16((i16)ct_eMeans[i], 6));
-    int shift = 16 - (lg >> CB_DB_SHIFT);
-    i32 g;
-    if (shift > 31) { shift = 0; g = 0; }
-    else g = (i16)cb_exp2_frac(lg & ((1 << CB_DB_SHIFT) - 1));
-    if (shift < 0) {
+  CB_LANE_LOOP(i, CB_NBANDS) {
+    i32 g = 0;
+    int shift = 0;
+    if (i >= start && i < end) {
+      const i16 lg = add16(bandLogE[i], shl16((i16)cb_ldg(&ct_eMeans_g[i]), 6));
+      shift = 16 - (lg >> CB_DB_SHIFT);
+      if (shift > 31) { shift = 0; g = 0; }
+      else g = (i16)cb_exp2_frac(lg & ((1 << CB_DB_SHIFT) - 1));
       if (shift < -2) { g = 32767; shift = -2; }
-      CB_LANE_LOOPU(t, j1 - j0) dst[j0 + t] = shl32(mult16_16(X[j0 + t], g), -shift);
-    } else {
-      CB_LANE_LOOPU(t, j1 - j0) dst[j0 + t] = mult16_16(X[j0 + t], g) >> shift;
     }
+    tmp[i] = g;
+    tmp[CB_NBANDS + i] = shift;
   }
   CB_WSYNC();
-  CB_LANE_LOOPU(t, N - bound) dst[bound + t] = 0;
+  CB_LANE_LOOPU(j, N) {
+    i32 v = 0;
+    if (j >= jlo && j < bound) {
+      const int b = cb_ldg(&ct_band_of_bin_g[j >> LM]);
+      const i32 g = tmp[b];
+      const int shift = tmp[CB_NBANDS + b];
+      const i32 p = mult16_16(X[j], g);
+      v = shift < 0 ? shl32(p, -shift) : p >> shift;
+    }
+    dst[j] = v;
+  }
   CB_WSYNC();
 }
 
@@ -363,14 +376,14 @@ CB_FN void celt_synth_channel(SynWork& w, CeltDecState* st, const FrameSide* sid
   // 1. denormalise (celt_synthesis, celt_decoder.c:313-348)
   if (CC == 1 && C == 2) {
     i32* f2 = w.buf + (CB_OVERLAP >> 1);
-    v_denormalise(side->X, w.freq, side->bandE, side->start, side->effEnd, M, downsample, side->silence);
-    v_denormalise(side->X + N, f2, side->bandE + CB_NBANDS, side->start, side->effEnd, M, downsample, side->silence);
+    v_denormalise(side->X, w.freq, side->bandE, side->start, side->effEnd, M, downsample, side->silence, w.buf);
+    v_denormalise(side->X + N, f2, side->bandE + CB_NBANDS, side->start, side->effEnd, M, downsample, side->silence, w.buf);
     CB_LANE_LOOPU(i, N) w.freq[i] = half32(add32(w.freq[i], f2[i]));
     CB_WSYNC();
   } else {
     int sc = (C == 1) ? 0 : c;
     v_denormalise(side->X + sc * N, w.freq, side->bandE + sc * CB_NBANDS, side->start, side->effEnd, M,
-                  downsample, side->silence);
+                  downsample, side->silence, w.buf);
   }
   // 2. overlap tail of the previous frame becomes out_syn[0..60)
   CB_LANE_LOOPU(i, CB_OVERLAP / 2) w.buf[i] = st->tail[c][i];

@@ -106,6 +106,9 @@ def main():
     T["pvq_u_row"] = ("int16_t", rows)
     # lane-indexed copies for the encoder's parallel index computation (kernel header only)
     T["eband5ms_g"] = T["eband5ms"]
+    T["eMeans_g"] = T["eMeans"]
+    eb = T["eband5ms"][1]
+    T["band_of_bin_g"] = ("uint8_t", [max(b for b in range(21) if eb[b] <= j) for j in range(eb[21])])   # band of a 2.5 ms bin
     T["cache_bits50_g"] = (T["cache_bits50"][0], T["cache_bits50"][1] + [0] * 64)   # padded: lanes read 64 entries of a row
     T["band_alloc_g"] = T["band_alloc"]
     T["pvq_u_data_g"] = ("uint32_t", data)
@@ -120,7 +123,7 @@ def main():
                " * warp (constant cache); CB_GTABLE = tables indexed per lane (global, L1-cached). */\n")
     out.append("#pragma once\n#include <stdint.h>\n")
     lane_indexed = {"window120", "fft_tw480", "fft_bitrev480", "fft_bitrev240", "fft_bitrev120",
-                    "fft_bitrev60", "mdct_tw960", "eband5ms_g", "cache_bits50_g", "band_alloc_g", "pvq_u_data_g", "pvq_u_row_g"}
+                    "fft_bitrev60", "mdct_tw960", "eband5ms_g", "eMeans_g", "band_of_bin_g", "cache_bits50_g", "band_alloc_g", "pvq_u_data_g", "pvq_u_row_g"}
     for name, (ty, vals) in T.items():
         q = "CB_GTABLE" if name in lane_indexed else "CB_UTABLE"
         out.append("%s %s ct_%s[%d] = {\n%s\n};\n" % (q, ty, name, len(vals), fmt(vals)))
