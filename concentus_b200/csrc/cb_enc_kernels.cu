@@ -13,9 +13,10 @@
 
 #define E_WARPS 28
 
+template <bool MULTI>
 __global__ void __launch_bounds__(E_WARPS * 32, 1)
 opus_encode_kernel(OpusEncState* const* states, EncScratch* scratch, const i16* pcm, i32 pcm_stride, int frame_size,
-                   u8* data, i32 data_stride, int max_data_bytes, i32* out_len, int n) {
+                   u8* data, i32 data_stride, int max_data_bytes, i32* out_len, int n, int phases) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int warp = threadIdx.x >> 5;
   const int s = blockIdx.x * E_WARPS + warp;
@@ -23,13 +24,14 @@ opus_encode_kernel(OpusEncState* const* states, EncScratch* scratch, const i16* 
   if ((threadIdx.x & 31) == 0) w.nsync = 0;
   __syncwarp();
   if (s < n) {
-    const int ret = opus_encode_stream(w, scratch[s], states[s], pcm + (size_t)s * pcm_stride, frame_size,
+    const int ret = opus_encode_stream<MULTI>(w, scratch[s], states[s], pcm + (size_t)s * pcm_stride, frame_size,
                                        data + (size_t)s * data_stride, max_data_bytes);
     if ((threadIdx.x & 31) == 0) out_len[s] = ret;
   }
   __syncwarp();
   // warps that left early (or have no stream) still owe the CTA their remaining rendezvous
-  for (int k = w.nsync; k < CB_ENC_PHASES; k++) __syncthreads();
+  // (`phases` = CB_ENC_PHASES times the most 20 ms frames any stream of this launch codes for one call)
+  for (int k = w.nsync; k < phases; k++) __syncthreads();
 }
 
 extern "C" {
@@ -39,19 +41,27 @@ size_t cbk_sizeof_enc_scratch(void) { return sizeof(EncScratch); }
 
 int cbk_launch_encode(OpusEncState* const* d_states, void* d_scratch, const i16* d_pcm, i32 pcm_stride,
                       int frame_size, u8* d_data, i32 data_stride, int max_data_bytes, i32* d_len, int n,
-                      cudaStream_t stream) {
+                      int max_subframes, cudaStream_t stream) {
   static bool attr_set[16] = {false};
   const size_t smem = sizeof(EncWork) * E_WARPS;
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev >= 0 && dev < 16 && !attr_set[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(opus_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(opus_encode_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(opus_encode_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     attr_set[dev] = true;
   }
   const int blocks = (n + E_WARPS - 1) / E_WARPS;
-  opus_encode_kernel<<<blocks, E_WARPS * 32, smem, stream>>>(d_states, (EncScratch*)d_scratch, d_pcm, pcm_stride,
-                                                            frame_size, d_data, data_stride, max_data_bytes, d_len, n);
+  if (max_subframes > 1)
+    opus_encode_kernel<true><<<blocks, E_WARPS * 32, smem, stream>>>(d_states, (EncScratch*)d_scratch, d_pcm, pcm_stride,
+                                                                    frame_size, d_data, data_stride, max_data_bytes, d_len, n,
+                                                                    CB_ENC_PHASES * max_subframes);
+  else
+    opus_encode_kernel<false><<<blocks, E_WARPS * 32, smem, stream>>>(d_states, (EncScratch*)d_scratch, d_pcm, pcm_stride,
+                                                                     frame_size, d_data, data_stride, max_data_bytes, d_len, n,
+                                                                     CB_ENC_PHASES);
   return (int)cudaGetLastError();
 }
 

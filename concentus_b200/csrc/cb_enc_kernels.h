@@ -12,5 +12,5 @@ size_t cbk_sizeof_enc_scratch(void);
 // (max_data_bytes of room); d_len[s] = packet length or a negative OPUS_* code.
 int cbk_launch_encode(OpusEncState* const* d_states, void* d_scratch, const i16* d_pcm, i32 pcm_stride,
                       int frame_size, u8* d_data, i32 data_stride, int max_data_bytes, i32* d_len, int n,
-                      cudaStream_t stream);
+                      int max_subframes, cudaStream_t stream);
 }

@@ -151,6 +151,7 @@ struct alignas(16) EncScratch {
   i32 lpc32[CB_LPC_ORDER];
   i16 pcm_buf[(CB_MAX_ENCODER_BUFFER + CB_MAXN) * 2];    // delay-compensated, dc-rejected input
   u8 intra_bits[256];                                    // coarse-energy two-pass byte save
+  u8 multi_tmp[3 * 1276 + 4];                            // the 20 ms packets of a 40 / 60 ms frame before assembly
 };
 
 // Phase rendezvous.  All warps of a CTA run the same stage of the frame at the same time, so the

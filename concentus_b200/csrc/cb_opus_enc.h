@@ -7,6 +7,8 @@
 #include "cb_common.h"
 #include "cb_enc_state.h"
 #include "cb_celt_enc.h"
+#include "cb_opus_plan.h"
+#include "cb_repack.h"
 
 #define CB_SIGNAL_VOICE 3001
 #define CB_SIGNAL_MUSIC 3002
@@ -205,16 +207,18 @@ CB_FN i32 enc_stereo_width(const i16* pcm, int frame_size, int Fs, OpusEncScalar
 }
 
 // opus_encode (opus_encoder.c:2012-2031) + opus_encode_native (:938-1964), CELT-only path.
-// pcm: analysis_frame_size interleaved samples per channel; data: out_data_bytes of room.
-// Returns the packet length or a negative OPUS_* code.  All lanes run it uniformly.
-CB_FN int opus_encode_stream(EncWork& w, EncScratch& sc, OpusEncState* st, const i16* pcm, int analysis_frame_size,
-                             u8* data, int out_data_bytes) {
-  OpusEncScalars o = st->o;
-  CeltEncState* celt = &st->celt;
-  const int frame_size = enc_frame_size_select(analysis_frame_size, o.variable_duration, o.Fs);
-  int max_data_bytes = cb_imin(1276, out_data_bytes);
-  o.rangeFinal = 0;
-  if (frame_size < 0 || 400 * frame_size < o.Fs || max_data_bytes <= 0) return CB_BAD_ARG;
+//
+// enc_decide: the decisions opus_encode_native takes before any signal processing -- bit-rate bookkeeping,
+// the one-byte packet when there is too little room, channel count, mode, bandwidth (:1014-1359).  `o` is the
+// stream's scalar state (in registers), max_data_bytes comes in as min(1276, room) and goes out CBR-adjusted.
+// Returns 0 to go on, 1 when the packet is complete (*early_ret = its length), or a negative OPUS_* code.
+struct EncDecision {
+  int max_data_bytes, total_buffer, lsb_depth;
+  i32 equiv_rate;
+};
+CB_FN int enc_decide(OpusEncState* st, OpusEncScalars& o, const i16* pcm, int frame_size, u8* data, EncDecision& d,
+                     int* early_ret) {
+  int max_data_bytes = d.max_data_bytes;
   const int delay_compensation = o.application == CB_APP_LOWDELAY ? 0 : o.delay_compensation;
   const int lsb_depth = cb_imin(16, o.lsb_depth);
   o.voice_ratio = -1;
@@ -251,9 +255,8 @@ CB_FN int opus_encode_stream(EncWork& w, EncScratch& sc, OpusEncState* st, const
       ret = enc_packet_pad(data, ret, max_data_bytes);
       if (ret == CB_OK) ret = max_data_bytes;
     }
-    CB_IF_LANE0 st->o = o;
-    CB_WSYNC();
-    return ret;
+    *early_ret = ret;
+    return 1;
   }
   i32 equiv_rate = o.bitrate_bps - (40 * o.channels + 20) * (o.Fs / frame_size - 50);
   int voice_est;
@@ -290,8 +293,7 @@ CB_FN int opus_encode_stream(EncWork& w, EncScratch& sc, OpusEncState* st, const
   }
   if (o.mode != CB_MODE_CELT_ONLY && frame_size < o.Fs / 100) o.mode = CB_MODE_CELT_ONLY;
   if (max_data_bytes < (frame_rate > 50 ? 12000 : 8000) * frame_size / (o.Fs * 8)) o.mode = CB_MODE_CELT_ONLY;
-  if (o.mode != CB_MODE_CELT_ONLY || o.application == CB_APP_VOIP || frame_size > o.Fs / 50)
-    return CB_UNIMPLEMENTED;                                   // SILK / hybrid / VOIP high-pass / 40-60 ms
+  if (o.mode != CB_MODE_CELT_ONLY || o.application == CB_APP_VOIP) return CB_UNIMPLEMENTED;   // SILK / hybrid / VOIP high-pass
   // prev_mode is 0 or CELT-only here, so no redundancy / mode transition is ever needed.
 
   // automatic bandwidth (opus_encoder.c:1253-1304)
@@ -317,9 +319,29 @@ CB_FN int opus_encode_stream(EncWork& w, EncScratch& sc, OpusEncState* st, const
   if (o.Fs <= 16000 && o.bandwidth > CB_BW_WIDEBAND) o.bandwidth = CB_BW_WIDEBAND;
   if (o.Fs <= 12000 && o.bandwidth > CB_BW_MEDIUMBAND) o.bandwidth = CB_BW_MEDIUMBAND;
   if (o.Fs <= 8000 && o.bandwidth > CB_BW_NARROWBAND) o.bandwidth = CB_BW_NARROWBAND;
+  if (o.bandwidth == CB_BW_MEDIUMBAND) o.bandwidth = CB_BW_WIDEBAND;        // CELT has no mediumband (:1356-1357)
+  d.max_data_bytes = max_data_bytes;
+  d.total_buffer = total_buffer;
+  d.lsb_depth = lsb_depth;
+  d.equiv_rate = equiv_rate;
+  return 0;
+}
+
+// One frame of at most 20 ms: decisions, then the CELT encoder (:1442-1964).  Returns the packet length.
+CB_FN int enc_one_frame(EncWork& w, EncScratch& sc, OpusEncState* st, OpusEncScalars& o, const i16* pcm, int frame_size,
+                        u8* data, int out_data_bytes) {
+  CeltEncState* celt = &st->celt;
+  EncDecision d;
+  d.max_data_bytes = cb_imin(1276, out_data_bytes);
+  o.rangeFinal = 0;
+  int early = 0;
+  const int dr = enc_decide(st, o, pcm, frame_size, data, d, &early);
+  if (dr < 0) return dr;
+  if (dr == 1) return early;
+  const int max_data_bytes = d.max_data_bytes, total_buffer = d.total_buffer, lsb_depth = d.lsb_depth;
+  const i32 equiv_rate = d.equiv_rate;
   CeltEncScalars cs = celt->s;
   cs.lsb_depth = lsb_depth;
-  if (o.bandwidth == CB_BW_MEDIUMBAND) o.bandwidth = CB_BW_WIDEBAND;
   const int curr_bandwidth = o.bandwidth;
   const int bytes_target = cb_imin(max_data_bytes, o.bitrate_bps * frame_size / (o.Fs * 8)) - 1;
   u8* payload = data + 1;
@@ -406,6 +428,90 @@ CB_FN int opus_encode_stream(EncWork& w, EncScratch& sc, OpusEncState* st, const
     if (enc_packet_pad(data, ret, max_data_bytes) != CB_OK) return CB_INTERNAL_ERROR;
     ret = max_data_bytes;
   }
+  return ret;
+}
+
+// opus_encode for one stream.  pcm: analysis_frame_size interleaved samples per channel; data: out_data_bytes
+// of room.  Returns the packet length or a negative OPUS_* code.  All lanes run it uniformly.
+// A 40 / 60 ms frame in CELT-only mode is two or three 20 ms frames in one packet (opus_encoder.c:1362-1438):
+// the decisions are taken once for the long frame and forced on the short ones, each short frame is coded
+// into scratch, and the repacketizer's assembly (cb_repack.h) builds the packet.
+// MULTI = false leaves the long-frame path out (the kernel instance for launches in which no stream has one:
+// the 20 ms path then compiles exactly as it did before long frames were supported).
+template <bool MULTI>
+CB_FN int opus_encode_stream(EncWork& w, EncScratch& sc, OpusEncState* st, const i16* pcm, int analysis_frame_size,
+                             u8* data, int out_data_bytes) {
+  OpusEncScalars o = st->o;
+  const int frame_size = enc_frame_size_select(analysis_frame_size, o.variable_duration, o.Fs);
+  if (frame_size < 0 || 400 * frame_size < o.Fs || cb_imin(1276, out_data_bytes) <= 0) return CB_BAD_ARG;
+  int nb_frames = 1, bytes_per_frame = 0;
+  int bak_mode = 0, bak_bandwidth = 0, bak_channels = 0;
+  if (!MULTI && frame_size > o.Fs / 50) return CB_UNIMPLEMENTED;   // (the host picks the other instance for these)
+  if (MULTI && frame_size > o.Fs / 50) {
+    EncDecision d;
+    d.max_data_bytes = cb_imin(1276, out_data_bytes);
+    o.rangeFinal = 0;
+    int early = 0;
+    const int dr = enc_decide(st, o, pcm, frame_size, data, d, &early);
+    if (dr < 0) return dr;
+    if (dr == 1) {
+      CB_WSYNC();
+      CB_IF_LANE0 st->o = o;
+      CB_WSYNC();
+      return early;
+    }
+    nb_frames = frame_size > o.Fs / 25 ? 3 : 2;
+    bytes_per_frame = cb_imin(1276, (out_data_bytes - 3) / nb_frames);
+    bak_mode = o.user_forced_mode; bak_bandwidth = o.user_bandwidth; bak_channels = o.force_channels;
+    o.user_forced_mode = o.mode;
+    o.user_bandwidth = o.bandwidth;
+    o.force_channels = o.stream_channels;
+    o.prev_channels = o.stream_channels;
+  }
+  int ret = 0;
+  unsigned long long sub_len = 0;      // lengths of the short packets, 16 bits each
+  CB_NOUNROLL for (int i = 0; i < (MULTI ? nb_frames : 1); i++) {
+    const bool multi = MULTI && nb_frames > 1;
+    const int sub = multi ? o.Fs / 50 : frame_size;
+    ret = enc_one_frame(w, sc, st, o, multi ? pcm + (size_t)i * o.channels * sub : pcm, sub,
+                        multi ? sc.multi_tmp + i * bytes_per_frame : data, multi ? bytes_per_frame : out_data_bytes);
+    if (ret < 0) return multi ? CB_INTERNAL_ERROR : ret;
+    sub_len |= (unsigned long long)ret << (16 * i);
+  }
+  if (MULTI && nb_frames > 1) {
+    // opus_repacketizer_cat on each short packet (a CBR one is a padded code-3 packet), then out_range
+    CB_WSYNC();
+    const i32 repacketize_len = o.use_vbr ? out_data_bytes
+                                          : cb_imin(3 * o.bitrate_bps / (3 * 8 * 50 / nb_frames), out_data_bytes);
+    i32 total = 0;
+    CB_IF_LANE0 {
+      const u8* frames[3];
+      i16 flen[3];
+      u8 toc = 0;
+      total = 0;
+      for (int i = 0; i < nb_frames && total >= 0; i++) {
+        const u8* pk = sc.multi_tmp + i * bytes_per_frame;
+        int t = 0, poff = 0;
+        i16 sizes[CB_MAX_FRAMES];
+        const int cnt = opus_parse_packet(pk, (int)((sub_len >> (16 * i)) & 0xFFFF), 0, &t, sizes, &poff, nullptr);
+        if (cnt != 1 || (i > 0 && ((t ^ toc) & 0xFC))) { total = CB_INTERNAL_ERROR; break; }
+        if (i == 0) toc = (u8)t;
+        frames[i] = pk + poff;
+        flen[i] = sizes[0];
+      }
+      if (total >= 0) {
+        total = cb_rp_emit(frames, flen, nb_frames, toc, data, repacketize_len, 0, !o.use_vbr);
+        if (total < 0) total = CB_INTERNAL_ERROR;
+      }
+    }
+    CB_WSYNC();
+    ret = cb_bcast(total, 0);
+    if (ret < 0) return ret;
+    o.user_forced_mode = bak_mode;
+    o.user_bandwidth = bak_bandwidth;
+    o.force_channels = bak_channels;
+  }
+  CB_WSYNC();
   CB_IF_LANE0 st->o = o;
   CB_WSYNC();
   return ret;

@@ -108,8 +108,16 @@ int group_launch(OpusEncoderGroup* g, const i16* d_pcm, i32 pcm_stride, int fram
                  int max_data_bytes, i32* d_len, cudaStream_t stream) {
   EncProf pr{nullptr, nullptr};
   if (g_enc_prof_on) { cudaEventCreate(&pr.a); cudaEventCreate(&pr.b); cudaEventRecord(pr.a, stream); }
+  // a frame longer than 20 ms is coded as two or three 20 ms frames: the kernel's stage rendezvous has to
+  // know the most any member will do (members may run at different rates)
+  int max_sub = 1;
+  for (int i = 0; i < g->n && max_sub < 3; i++) {
+    const int Fs = g->members[i]->Fs;
+    const int nb = frame_size * 50 > Fs ? (frame_size * 25 > Fs ? 3 : 2) : 1;
+    if (nb > max_sub) max_sub = nb;
+  }
   int rc = cbk_launch_encode(g->d_states, g->d_scratch, d_pcm, pcm_stride, frame_size, d_data, data_stride,
-                             max_data_bytes, d_len, g->n, stream);
+                             max_data_bytes, d_len, g->n, max_sub, stream);
   if (g_enc_prof_on) { cudaEventRecord(pr.b, stream); g_enc_prof.push_back(pr); }
   opusb_internal_count_launches(1);
   if (rc != 0) {
@@ -333,7 +341,7 @@ opus_int32 opus_encode(OpusEncoder* st, const opus_int16* pcm, int frame_size, u
     st->self_group = opus_encoder_group_create(&st, 1, &err);
     if (!st->self_group) return err;
   }
-  const int mb = max_data_bytes > 1276 ? 1276 : max_data_bytes;   // the encoder never writes more (opus_encoder.c:980)
+  const int mb = max_data_bytes > 3 * 1276 + 3 ? 3 * 1276 + 3 : max_data_bytes;   // three 20 ms frames at most (opus_encoder.c:980, 1380)
   opus_int32 len = 0;
   int rc = opus_encode_group_flat(st->self_group, pcm, frame_size, data, mb, &len);
   if (rc != OPUS_OK) return rc;
@@ -365,7 +373,7 @@ int opus_encode_batch(OpusEncoder* const* st, int n, const opus_int16* const* pc
   int rc = OPUS_OK;
   if (g->channels < 0) rc = OPUS_BAD_ARG;   // a flat batch needs one channel count; mixed groups go one by one
   if (rc == OPUS_OK) {
-    const int mb = max_data_bytes > 1276 ? 1276 : max_data_bytes;
+    const int mb = max_data_bytes > 3 * 1276 + 3 ? 3 * 1276 + 3 : max_data_bytes;
     const size_t row = (size_t)frame_size * g->channels;
     std::vector<opus_int16> flat(row * n);
     std::vector<unsigned char> out((size_t)mb * n);

@@ -10,20 +10,9 @@
 #include "../../include/opus_b200.h"
 #include "cb_opus_plan.h"
 #include "cb_repack_internal.h"
+#include "cb_repack.h"
 
 
-namespace {
-
-// frame-length field of RFC 6716 3.2.1: one byte below 252, else two
-inline int put_size(int size, unsigned char* p) {
-  if (size < 252) { p[0] = (unsigned char)size; return 1; }
-  p[0] = (unsigned char)(252 + (size & 3));
-  p[1] = (unsigned char)((size - (int)p[0]) >> 2);
-  return 2;
-}
-inline int size_field_bytes(int size) { return size < 252 ? 1 : 2; }
-
-}  // namespace
 
 int opusb_rp_cat(OpusRepacketizer* rp, const unsigned char* data, opus_int32 len, int self_delimited) {
   if (len < 1) return OPUS_INVALID_PACKET;
@@ -54,55 +43,7 @@ int opusb_rp_cat(OpusRepacketizer* rp, const unsigned char* data, opus_int32 len
 opus_int32 opusb_rp_emit(OpusRepacketizer* rp, int begin, int end, unsigned char* data, opus_int32 maxlen,
                          int self_delimited, int pad) {
   if (begin < 0 || begin >= end || end > rp->nb_frames) return OPUS_BAD_ARG;
-  const int count = end - begin;
-  const opus_int16* len = rp->len + begin;
-  const unsigned char** frames = rp->frames + begin;
-  const unsigned char cfg = rp->toc & 0xFC;
-  const opus_int32 sd_bytes = self_delimited ? size_field_bytes(len[count - 1]) : 0;
-  opus_int32 payload = 0;
-  bool equal = true;
-  for (int i = 0; i < count; i++) {
-    payload += len[i];
-    if (len[i] != len[0]) equal = false;
-  }
-  // smallest framing for 1 or 2 frames
-  int code;
-  opus_int32 total;
-  if (count == 1) { code = 0; total = sd_bytes + 1 + payload; }
-  else if (count == 2 && equal) { code = 1; total = sd_bytes + 1 + payload; }
-  else if (count == 2) { code = 2; total = sd_bytes + 1 + size_field_bytes(len[0]) + payload; }
-  else { code = 3; total = 0; }
-  if (code != 3 && total > maxlen) return OPUS_BUFFER_TOO_SMALL;
-  if (code != 3 && pad && total < maxlen) code = 3;           // only code 3 can carry padding
-  unsigned char* p = data;
-  if (code == 3) {
-    total = sd_bytes + 2 + payload;
-    if (!equal)
-      for (int i = 0; i < count - 1; i++) total += size_field_bytes(len[i]);
-    if (total > maxlen) return OPUS_BUFFER_TOO_SMALL;
-    const opus_int32 pad_amount = pad ? maxlen - total : 0;
-    *p++ = cfg | 3;
-    *p++ = (unsigned char)(count | (equal ? 0 : 0x80) | (pad_amount ? 0x40 : 0));
-    if (pad_amount) {
-      const int n255 = (pad_amount - 1) / 255;                 // the length bytes count as padding themselves
-      for (int i = 0; i < n255; i++) *p++ = 255;
-      *p++ = (unsigned char)(pad_amount - 255 * n255 - 1);
-      total += pad_amount;
-    }
-    if (!equal)
-      for (int i = 0; i < count - 1; i++) p += put_size(len[i], p);
-  } else {
-    *p++ = cfg | (unsigned char)code;
-    if (code == 2) p += put_size(len[0], p);
-  }
-  if (self_delimited) p += put_size(len[count - 1], p);
-  for (int i = 0; i < count; i++) {
-    memmove(p, frames[i], (size_t)len[i]);
-    p += len[i];
-  }
-  if (pad)
-    while (p < data + maxlen) *p++ = 0;
-  return total;
+  return cb_rp_emit(rp->frames + begin, rp->len + begin, end - begin, rp->toc, data, maxlen, self_delimited, pad);
 }
 
 #define rp_cat opusb_rp_cat

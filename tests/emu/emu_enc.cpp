@@ -32,7 +32,7 @@ int emu_enc_encode(void* state, const short* pcm, int frame_size, unsigned char*
   OpusEncState* st = (OpusEncState*)state;
   static EncWork w;
   static EncScratch sc;
-  return opus_encode_stream(w, sc, st, pcm, frame_size, data, max_bytes);
+  return opus_encode_stream<true>(w, sc, st, pcm, frame_size, data, max_bytes);
 }
 
 }  // extern "C"

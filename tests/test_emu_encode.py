@@ -85,11 +85,32 @@ def test_emu_encoder_error_codes(emu_enc_lib):
     pcm = np.zeros(4000, dtype=np.int16)
     for frame in (100, 119, 121, 500, 1000, 1920, 2880):
         a, b = r.encode(pcm, frame, 1275), e.encode(pcm, frame, 1275)
-        if frame in (1920, 2880):
-            assert b[0] == -5          # 40/60 ms frames: documented OPUS_UNIMPLEMENTED
-        else:
-            assert a[0] == b[0], frame
+        assert a[0] == b[0], frame
     # out-of-range ctl values
     for req, val in [(4002, 0), (4002, -5), (4010, 11), (4010, -1), (4006, 2), (4022, 2), (4008, 1100), (4036, 7),
                      (4040, 4999), (4014, 101), (11002, 999), (4000, 2050)]:
         assert r.ctl(req, val) == e.ctl(req, val), (req, val)
+
+
+@needs_ref
+@pytest.mark.parametrize("ms", [40, 60])
+def test_emu_long_frames_match_reference(emu_enc_lib, ms):
+    """40 / 60 ms frames in CELT-only mode: two or three 20 ms frames in one packet (opus_encoder.c:1362-1438),
+    decisions taken once for the long frame.  Packets and final range against the reference for both
+    applications that reach CELT, mono / stereo, three rates, VBR / CBR, generous and tight buffers."""
+    for app in (enc_cases.LOWDELAY, 2049):
+        for ch in (1, 2):
+            for fs in (48000, 24000, 16000):
+                for vbr, maxb, rate in ((1, 1275, 64000), (0, 1275, 64000), (1, 300, 64000), (0, 200, 64000), (1, 3800, 250000)):
+                    ref, emu = RefEncoder(fs, ch, app), EmuEncoder(emu_enc_lib, fs, ch, app)
+                    for e in (ref, emu):
+                        assert e.ctl(enc_cases.SET_BITRATE, rate * ch) == 0
+                        assert e.ctl(enc_cases.SET_VBR, vbr) == 0
+                        if app == 2049:
+                            assert e.ctl(11002, 1002) == 0            # OPUS_SET_FORCE_MODE(MODE_CELT_ONLY)
+                    frame = fs * ms // 1000
+                    pcm = enc_cases.signal(enc_cases.KINDS[(ch + ms) % len(enc_cases.KINDS)], frame * 5, ch, 77)
+                    for t in range(5):
+                        x = pcm[t * frame * ch:(t + 1) * frame * ch]
+                        a, b = ref.encode(x, frame, maxb), emu.encode(x, frame, maxb)
+                        assert a == b, (app, ch, fs, ms, vbr, maxb, t, a[0], b[0])

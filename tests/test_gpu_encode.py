@@ -183,3 +183,53 @@ def test_pipelined_submit_matches_synchronous_calls():
     finally:
         a.close()
         b.close()
+
+
+@needs_ref
+@pytest.mark.parametrize("ms,vbr,maxb", [(40, 1, 1275), (60, 1, 1275), (60, 0, 1275), (40, 0, 250), (60, 1, 3000)])
+def test_long_frames_match_reference(ms, vbr, maxb):
+    """40 / 60 ms frames (two or three 20 ms CELT frames in one packet, opus_encoder.c:1362-1438): a batch of
+    24 stereo 48 kHz streams with their own signals and bit rates, eight frames, against the reference."""
+    n, ch, fs, nframes = 24, 2, 48000, 8
+    frame = fs * ms // 1000
+    be = cb.OpusBatchEncoder(n, fs, ch, enc_cases.LOWDELAY)
+    refs, pcms = [], []
+    try:
+        for s in range(n):
+            r = RefEncoder(fs, ch, enc_cases.LOWDELAY)
+            for req, val in ((enc_cases.SET_BITRATE, 32000 + 9000 * s), (enc_cases.SET_VBR, vbr)):
+                assert r.ctl(req, val) == 0
+                be.encoders[s].ctl(req, val)
+            refs.append(r)
+            pcms.append(enc_cases.signal(enc_cases.KINDS[s % len(enc_cases.KINDS)], frame * nframes, ch, 2000 + s))
+        for t in range(nframes):
+            rows = np.stack([p[t * frame * ch:(t + 1) * frame * ch] for p in pcms])
+            data, lens = be.encode(rows, frame, maxb)
+            fr = be.final_ranges()
+            for s in range(n):
+                rn, rpkt, rrng = refs[s].encode(rows[s], frame, maxb)
+                assert lens[s] == rn, (s, t, lens[s], rn)
+                assert data[s, :rn].tobytes() == rpkt, (s, t)
+                assert int(fr[s]) == rrng, (s, t)
+    finally:
+        be.close()
+
+
+@needs_ref
+def test_long_frames_single_stream_and_mixed_rates():
+    """opus_encode with 40 / 60 ms frames on single encoders at 16 / 24 / 48 kHz (the kernel's stage rendezvous
+    count follows the longest sub-frame count of the launch)."""
+    for fs, ch in ((16000, 1), (24000, 2), (48000, 1)):
+        for ms in (40, 60):
+            enc, ref = cb.OpusEncoder(fs, ch, enc_cases.LOWDELAY), RefEncoder(fs, ch, enc_cases.LOWDELAY)
+            try:
+                frame = fs * ms // 1000
+                pcm = enc_cases.signal("chirp", frame * 4, ch, 5)
+                for t in range(4):
+                    x = pcm[t * frame * ch:(t + 1) * frame * ch]
+                    n1, p1, r1 = ref.encode(x, frame, 1500)
+                    p2 = enc.encode(x, frame, 1500)
+                    assert n1 == len(p2) and p1 == p2, (fs, ch, ms, t, n1, len(p2))
+                    assert enc.final_range == r1
+            finally:
+                enc.close()
