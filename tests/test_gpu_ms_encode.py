@@ -52,7 +52,7 @@ LAYOUTS = [  # channels, streams, coupled, mapping
 
 @needs_ref
 @pytest.mark.parametrize("layout", LAYOUTS)
-@pytest.mark.parametrize("vbr,maxbytes,frame", [(1, 4000, 960), (0, 1500, 960), (1, 260, 480), (0, 400, 240)])
+@pytest.mark.parametrize("vbr,maxbytes,frame", [(1, 4000, 960), (0, 1500, 960), (1, 260, 480), (0, 400, 240), (1, 4000, 2880), (0, 2000, 1920)])
 def test_explicit_layouts_match_reference(layout, vbr, maxbytes, frame):
     ch, streams, coupled, mapping = layout
     ours, ref = cb.load(), _ref()
