@@ -1,6 +1,7 @@
 // cb_celt_enc.h -- one CELT frame, encoder side: celt_encode_with_ec
 // (opus-fix/celt/celt_encoder.c:1398-2274) for the static 48 kHz / 960 mode, FIXED_POINT,
-// DISABLE_FLOAT_API (no tonality analysis), no LFE, no surround energy mask, start band 0.
+// DISABLE_FLOAT_API (no tonality analysis), start band 0.  EXT = true adds what only the streams of a surround
+// multistream encoder use: the LFE restrictions (OPUS_SET_LFE) and the surround masking terms (OPUS_SET_ENERGY_MASK).
 // One warp encodes one stream's frame; the range coder lives in w.enc and has been initialised
 // by the Opus layer over the packet's payload bytes.
 #pragma once
@@ -19,6 +20,7 @@ CB_FN i32 enc_maxabs16(const i16* x, int len) {
 }
 
 // Returns the number of payload bytes, or a negative OPUS_* code.
+template <bool EXT>
 CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const i16* pcm, int frame_size,
                             int nbCompressedBytes) {
   RangeEnc& enc = w.enc;
@@ -26,6 +28,7 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
   const int CC = s.channels, C = s.stream_channels;
   const int start = s.start, end = s.end;
   const int overlap = CB_OVERLAP;
+  const int lfe = EXT ? s.lfe : 0, has_mask = EXT ? s.has_mask : 0;
   i32 tf_estimate = 0;
   if (nbCompressedBytes < 2) return CB_BAD_ARG;
   frame_size *= s.upsample;
@@ -93,7 +96,7 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
   i32 gain1 = 0;
   {
     int qg;
-    const int enabled = nbAvailableBytes > 12 * C && start == 0 && !silence && !s.disable_pf && s.complexity >= 5 &&
+    const int enabled = ((lfe && nbAvailableBytes > 3) || nbAvailableBytes > 12 * C) && start == 0 && !silence && !s.disable_pf && s.complexity >= 5 &&
                         !(s.consec_transient && LM != 3 && s.variable_duration == 5010);
     prefilter_tapset = s.tapset_decision;
     pf_on = enc_run_prefilter(w, s, st, sc, CC, N, prefilter_tapset, &pitch_index, &gain1, &qg, enabled, nbAvailableBytes);
@@ -117,7 +120,7 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
   CB_ENC_PHASE(w);                                            // 3: pre-filter done
   // ---- transient decision, MDCT, band energies ----
   int isTransient = 0, shortBlocks = 0, tf_chan = 0, transient_got_disabled = 0;
-  if (s.complexity >= 1)
+  if (s.complexity >= 1 && !lfe)
     isTransient = enc_transient_analysis(sc.in[0], CB_MAXN + CB_OVERLAP, N + overlap, CC, &tf_estimate, &tf_chan, w.ta_tmp[0],
                                          CB_MAXN + CB_OVERLAP);
   if (LM > 0 && re_tell(enc) + 3 <= total_bits) {
@@ -138,12 +141,78 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
   enc_compute_mdcts(shortBlocks, sc.in[0], sc.in[1], sc.freq[0], sc.freq[1], sc.f2, C, CC, LM, s.upsample);
   if (CC == 2 && C == 1) tf_chan = 0;
   enc_band_energies(sc.freq[0], sc.freq[1], w.bandE, effEnd, C, LM);
+  if (lfe) {                                                  // everything of interest is in the first bands (:1716-1723)
+    CB_NOUNROLL for (int i = 2; i < end; i++) {
+      const i32 e = max32(min32(w.bandE[i], mult16_32_q15(3, w.bandE[0])), 1);
+      CB_WSYNC();
+      w.bandE[i] = e;
+    }
+    CB_WSYNC();
+  }
   enc_amp2log2(effEnd, end, w.bandE, w.bandLogE, C);
 
   CB_ENC_PHASE(w);                                            // 5: MDCT + band energies done
-  // temporal VBR (celt_encoder.c:1795-1812)
-  i32 temporal_vbr;
-  {
+  // how much the other surround channels mask this one (celt_encoder.c:1726-1801)
+  i32 surround_masking = 0, surround_trim = 0;
+  if (EXT) {
+    CB_WSYNC();
+    CB_NOUNROLL for (int i = 0; i < CB_NBANDS; i++) w.surround_dynalloc[i] = 0;
+    if (start == 0 && has_mask && !lfe) {
+      const i16* em = st->energy_mask;
+      const int mask_end = cb_imax(2, s.lastCodedBands);
+      i32 mask_avg = 0, diff = 0;
+      int count = 0;
+      for (int c = 0; c < C; c++)
+        CB_NOUNROLL for (int i = 0; i < mask_end; i++) {
+          i32 mask = max32(min32(em[CB_NBANDS * c + i], 256), -2048);
+          if (mask > 0) mask >>= 1;
+          mask_avg += mult16_16(mask, ebands(i + 1) - ebands(i));
+          count += ebands(i + 1) - ebands(i);
+          diff += mult16_16(mask, 1 + 2 * i - mask_end);
+        }
+      mask_avg = (i16)(mask_avg / (i32)(i16)count);              // DIV32_16
+      mask_avg += 205;                                           // QCONST16(.2f, DB_SHIFT)
+      diff = diff * 6 / (C * (mask_end - 1) * (mask_end + 1) * mask_end);
+      diff = diff >> 1;
+      diff = max32(min32(diff, 32), -32);                        // QCONST32(.031f, DB_SHIFT)
+      int midband = 0;
+      while (ebands(midband + 1) < ebands(mask_end) / 2) midband++;
+      int count_dynalloc = 0;
+      CB_NOUNROLL for (int i = 0; i < mask_end; i++) {
+        const i32 lin = mask_avg + diff * (i - midband);
+        i32 unmask = C == 2 ? max32(em[i], em[CB_NBANDS + i]) : em[i];
+        unmask = min32(unmask, 0);
+        unmask = (i16)(unmask - lin);
+        if (unmask > 256) {
+          w.surround_dynalloc[i] = (i16)(unmask - 256);
+          count_dynalloc++;
+        }
+      }
+      CB_WSYNC();
+      if (count_dynalloc >= 3) {
+        // dynalloc wanted in many bands: the masking rate was probably too low
+        mask_avg += 256;
+        if (mask_avg > 0) {
+          mask_avg = 0;
+          diff = 0;
+          CB_NOUNROLL for (int i = 0; i < mask_end; i++) w.surround_dynalloc[i] = 0;
+        } else {
+          CB_NOUNROLL for (int i = 0; i < mask_end; i++) {
+            const i32 v = max32(0, w.surround_dynalloc[i] - 256);
+            CB_WSYNC();
+            w.surround_dynalloc[i] = (i16)v;
+          }
+        }
+      }
+      mask_avg += 205;
+      surround_trim = (i16)(64 * diff);
+      surround_masking = (i16)mask_avg;
+    }
+    CB_WSYNC();
+  }
+  // temporal VBR (celt_encoder.c:1795-1812), not for LFE
+  i32 temporal_vbr = 0;
+  if (!lfe) {
     i32 follow = -10240;
     i32 frame_avg = 0;
     const i32 offset = shortBlocks ? LM * 512 : 0;
@@ -163,7 +232,7 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
   }
   CB_LANE_LOOP(i, 2 * CB_NBANDS) w.oldE[i] = st->oldBandE[i];
   CB_WSYNC();
-  if (LM > 0 && re_tell(enc) + 3 <= total_bits && !isTransient && s.complexity >= 5) {
+  if (LM > 0 && re_tell(enc) + 3 <= total_bits && !isTransient && s.complexity >= 5 && !lfe) {
     if (enc_patch_transient(w.bandLogE, w.oldE, start, end, C)) {
       isTransient = 1;
       shortBlocks = M;
@@ -181,7 +250,7 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
   CB_ENC_PHASE(w);                                            // 6: normalised spectrum ready
   // ---- time/frequency resolution, coarse energy, spreading ----
   int tf_select, tf_sum;
-  if (effectiveBytes >= 15 * C && start == 0 && s.complexity >= 2) {
+  if (effectiveBytes >= 15 * C && start == 0 && s.complexity >= 2 && !lfe) {
     int lambda;
     if (effectiveBytes < 40) lambda = 12;
     else if (effectiveBytes < 60) lambda = 6;
@@ -199,10 +268,13 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
   }
   (void)tf_sum;
   enc_coarse_energy(w, sc, enc, start, end, effEnd, w.oldE, (u32)total_bits, C, LM, nbAvailableBytes, s.force_intra,
-                    &s.delayedIntra, s.complexity >= 4, s.loss_rate);
+                    &s.delayedIntra, s.complexity >= 4, s.loss_rate, lfe);
   enc_tf_encode(w, enc, start, end, isTransient, LM, tf_select);
   if (re_tell(enc) + 4 <= total_bits) {
-    if (shortBlocks || s.complexity < 3 || nbAvailableBytes < 10 * C || start != 0) {
+    if (lfe) {
+      s.tapset_decision = 0;
+      s.spread_decision = CB_SPREAD_NORMAL;
+    } else if (shortBlocks || s.complexity < 3 || nbAvailableBytes < 10 * C || start != 0) {
       s.spread_decision = s.complexity == 0 ? CB_SPREAD_NONE : CB_SPREAD_NORMAL;
     } else {
       s.spread_decision = enc_spreading_decision(w.X, &s.tonal_average, s.spread_decision, &s.hf_average,
@@ -215,7 +287,12 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
   // ---- dynamic allocation boosts ----
   i32 tot_boost;
   const i32 maxDepth = enc_dynalloc_analysis(w, start, end, C, s.lsb_depth, isTransient, s.vbr, s.constrained_vbr, LM,
-                                             effectiveBytes, &tot_boost);
+                                             effectiveBytes, &tot_boost, lfe, EXT ? w.surround_dynalloc : nullptr);
+  if (lfe) {
+    CB_WSYNC();
+    w.offsets[0] = cb_imin(8, effectiveBytes / 3);
+    CB_WSYNC();
+  }
   CB_NOUNROLL for (int i = 0; i < CB_NBANDS; i++) {              // init_caps (celt.c:255-264)
     const int Nb = (ebands(i + 1) - ebands(i)) << LM;
     w.cap[i] = (ct_cache_caps50[CB_NBANDS * (2 * LM + C - 1) + i] + 64) * C * Nb >> 2;
@@ -254,7 +331,9 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
   }
   int alloc_trim = 5;
   if (tell + (6 << CB_BITRES) <= total_bits - total_boost) {
-    alloc_trim = enc_alloc_trim_analysis(w.X, w.bandLogE, end, LM, C, N, &s.stereo_saving, tf_estimate, s.intensity);
+    if (!lfe)
+      alloc_trim = enc_alloc_trim_analysis(w.X, w.bandLogE, end, LM, C, N, &s.stereo_saving, tf_estimate, s.intensity,
+                                           surround_trim);
     re_icdf(enc, alloc_trim, ct_trim_icdf, 7);
     tell = (i32)re_tell_frac(enc);
   }
@@ -266,7 +345,8 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
     i32 base_target = vbr_rate - ((40 * C + 20) << CB_BITRES);
     if (s.constrained_vbr) base_target += (s.vbr_offset >> lm_diff);
     i32 target = enc_compute_vbr(base_target, LM, equiv_rate, s.lastCodedBands, C, s.intensity, s.constrained_vbr,
-                                 s.stereo_saving, tot_boost, tf_estimate, maxDepth, s.variable_duration, temporal_vbr);
+                                 s.stereo_saving, tot_boost, tf_estimate, maxDepth, s.variable_duration, temporal_vbr,
+                                 lfe, has_mask, surround_masking);
     (void)pitch_change;
     target = target + tell;
     const i32 min_allowed = ((tell + total_boost + (1 << (CB_BITRES + 3)) - 1) >> (CB_BITRES + 3)) + 2 - nbFilledBytes;
@@ -306,7 +386,7 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
   i32 bits = (((i32)nbCompressedBytes * 8) << CB_BITRES) - (i32)re_tell_frac(enc) - 1;
   const int anti_collapse_rsv = isTransient && LM >= 2 && bits >= ((LM + 2) << CB_BITRES) ? (1 << CB_BITRES) : 0;
   bits -= anti_collapse_rsv;
-  const int signalBandwidth = end - 1;
+  const int signalBandwidth = lfe ? 1 : end - 1;
   i32 balance;
   int intensity = s.intensity;
   AllocEncPolicy ac{enc, s.lastCodedBands, signalBandwidth};

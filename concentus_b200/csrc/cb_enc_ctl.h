@@ -40,6 +40,8 @@
 #define CB_REQ_SET_PREDICTION_DISABLED 4042
 #define CB_REQ_GET_PREDICTION_DISABLED 4043
 #define CB_REQ_SET_FORCE_MODE 11002
+#define CB_REQ_SET_LFE 10024          // celt.h:113 (used by the multistream surround encoder)
+#define CB_REQ_SET_ENERGY_MASK 10026  // celt.h:116; takes a pointer, handled by the caller
 
 // True for the requests that only read the scalars.
 static inline bool opus_enc_ctl_is_get(int request) {
@@ -156,6 +158,10 @@ static inline int opus_enc_ctl_scalars(OpusEncScalars* o, CeltEncScalars* cs, in
       o->reduced_dependency = value;
       return CB_OK;
     case CB_REQ_GET_PREDICTION_DISABLED: *out = o->reduced_dependency; return CB_OK;
+    case CB_REQ_SET_LFE:                     // opus_encoder.c:2455-2460, celt_encoder.c:2500-2504
+      o->lfe = value;
+      cs->lfe = value;
+      return CB_OK;
     case CB_REQ_SET_FORCE_MODE:
       if ((value < CB_MODE_SILK_ONLY || value > CB_MODE_CELT_ONLY) && value != CB_OPUS_AUTO) return CB_BAD_ARG;
       o->user_forced_mode = value;

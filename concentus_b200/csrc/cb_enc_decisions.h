@@ -2,8 +2,8 @@
 // dynamic allocation boosts, allocation trim, dual stereo, intensity hysteresis and the VBR target.
 // Bit-exact with tf_analysis / alloc_trim_analysis / stereo_analysis / dynalloc_analysis /
 // compute_vbr (opus-fix/celt/celt_encoder.c:538-1066,1196-1313) and spreading_decision /
-// hysteresis_decision (celt/bands.c:48-61,428-519).  No float analysis (DISABLE_FLOAT_API),
-// no LFE, no surround masking: those belong to the multistream surround encoder.
+// hysteresis_decision (celt/bands.c:48-61,428-519).  No float analysis (DISABLE_FLOAT_API).
+// The LFE flag and the surround mask terms are only non-zero for the streams of a surround multistream encoder.
 #pragma once
 #include "cb_common.h"
 #include "cb_celt_entropy.h"   // v_haar1, ct_tf_select, ebands
@@ -168,7 +168,8 @@ CB_FN i32 enc_median3(const i16* x) {
 // dynalloc_analysis (celt_encoder.c:937-1065).  21-band recurrences, run uniformly; every
 // opus_val16 assignment of the reference is an explicit (i16) here.  Returns maxDepth.
 CB_FN i32 enc_dynalloc_analysis(EncWork& w, int start, int end, int C, int lsb_depth, int isTransient, int vbr,
-                                int constrained_vbr, int LM, int effectiveBytes, i32* tot_boost_) {
+                                int constrained_vbr, int LM, int effectiveBytes, i32* tot_boost_, int lfe = 0,
+                                const i16* surround_dynalloc = nullptr) {
   const i16* bandLogE = w.bandLogE;
   const i16* bandLogE2 = w.bandLogE2;
   i16* follower = w.follower;
@@ -184,7 +185,7 @@ CB_FN i32 enc_dynalloc_analysis(EncWork& w, int start, int end, int C, int lsb_d
   for (int c = 0; c < C; c++)
     CB_NOUNROLL for (int i = 0; i < end; i++)
       maxDepth = (i16)max32(maxDepth, bandLogE[c * CB_NBANDS + i] - noise_floor[i]);
-  if (effectiveBytes > 50 && LM >= 1) {
+  if (effectiveBytes > 50 && LM >= 1 && !lfe) {
     int last = 0;
     for (int c = 0; c < C; c++) {
       i16* f = &follower[c * CB_NBANDS];
@@ -231,9 +232,9 @@ CB_FN i32 enc_dynalloc_analysis(EncWork& w, int start, int end, int C, int lsb_d
       }
     }
     CB_WSYNC();
-    // surround_dynalloc is all zero here: MAX16(follower, 0) keeps follower (it is >= 0 already or wrapped as in the reference)
+    // without a surround mask surround_dynalloc is all zero
     CB_NOUNROLL for (int i = start; i < end; i++) {
-      i32 fo = max32(follower[i], 0);
+      i32 fo = max32(follower[i], surround_dynalloc ? surround_dynalloc[i] : 0);
       if ((!vbr || constrained_vbr) && !isTransient) fo = (i16)(fo >> 1);
       if (i < 8) fo = (i16)(fo * 2);
       if (i >= 12) fo = (i16)(fo >> 1);
@@ -276,7 +277,7 @@ CB_FN i32 enc_inner_norm(const i16* a, const i16* b, int n) {
 
 // alloc_trim_analysis (celt_encoder.c:756-841); *stereo_saving is a caller local.
 CB_FN int enc_alloc_trim_analysis(const i16* X, const i16* bandLogE, int end, int LM, int C, int N0,
-                                  i32* stereo_saving, i32 tf_estimate, int intensity) {
+                                  i32* stereo_saving, i32 tf_estimate, int intensity, i32 surround_trim = 0) {
   i32 diff = 0;
   i32 trim = 1280;                                            // QCONST16(5.f, 8)
   CB_WSYNC();
@@ -306,6 +307,7 @@ CB_FN int enc_alloc_trim_analysis(const i16* X, const i16* bandLogE, int end, in
     CB_NOUNROLL for (int i = 0; i < end - 1; i++) diff += bandLogE[i + c * CB_NBANDS] * (i32)(2 + 2 * i - end);
   diff /= C * (end - 1);
   trim = (i16)(trim - max32(-512, min32(512, ((diff + 1024) >> (CB_DB_SHIFT - 8)) / 6)));
+  trim = (i16)(trim - ((i16)surround_trim >> (CB_DB_SHIFT - 8)));
   trim = (i16)(trim - 2 * (tf_estimate >> (14 - 8)));
   int trim_index = pshr32(trim, 8);
   return cb_imax(0, cb_imin(10, trim_index));
@@ -329,10 +331,11 @@ CB_FN int enc_stereo_analysis(const i16* X, int LM, int N0) {
   return mult16_32_q15((ebands(13) << (LM + 1)) + thetas, sumMS) > mult16_32_q15(ebands(13) << (LM + 1), sumLR);
 }
 
-// compute_vbr (celt_encoder.c:1196-1313) without analysis / surround mask / lfe
+// compute_vbr (celt_encoder.c:1196-1313) without analysis
 CB_FN i32 enc_compute_vbr(i32 base_target, int LM, i32 bitrate, int lastCodedBands, int C, int intensity,
                           int constrained_vbr, i32 stereo_saving, int tot_boost, i32 tf_estimate, i32 maxDepth,
-                          int variable_duration, i32 temporal_vbr) {
+                          int variable_duration, i32 temporal_vbr, int lfe = 0, int has_surround_mask = 0,
+                          i32 surround_masking = 0) {
   const int coded_bands = lastCodedBands ? lastCodedBands : CB_NBANDS;
   int coded_bins = ebands(coded_bands) << LM;
   if (C == 2) coded_bins += ebands(cb_imin(intensity, coded_bands)) << LM;
@@ -348,18 +351,22 @@ CB_FN i32 enc_compute_vbr(i32 base_target, int LM, i32 bitrate, int lastCodedBan
   target += tot_boost - (16 << LM);
   const i32 tf_calibration = variable_duration == 5010 ? 328 : 655;     // OPUS_FRAMESIZE_VARIABLE
   target += shl32(mult16_32_q15(tf_estimate - tf_calibration, target), 1);
+  if (has_surround_mask && !lfe) {
+    const i32 surround_target = target + (mult16_16((i16)surround_masking, (i16)(coded_bins << CB_BITRES)) >> CB_DB_SHIFT);
+    target = cb_imax(target / 4, surround_target);
+  }
   {
     const int bins = ebands(CB_NBANDS - 2) << LM;
     i32 floor_depth = mult16_16((C * bins << CB_BITRES), maxDepth) >> CB_DB_SHIFT;
     floor_depth = max32(floor_depth, target >> 2);
     target = min32(target, floor_depth);
   }
-  if (constrained_vbr || bitrate < 64000) {
+  if ((!has_surround_mask || lfe) && (constrained_vbr || bitrate < 64000)) {
     i32 rate_factor = max32(0, bitrate - 32000);
     if (constrained_vbr) rate_factor = min32(rate_factor, 21955);
     target = base_target + mult16_32_q15(rate_factor, target - base_target);
   }
-  if (tf_estimate < 3277) {
+  if (!has_surround_mask && tf_estimate < 3277) {
     const i32 amount = (i16)mult16_16_q15(3329, cb_imax(0, cb_imin(32000, 96000 - bitrate)));
     const i32 tvbr_factor = (i16)(mult16_16(temporal_vbr, amount) >> CB_DB_SHIFT);
     target += mult16_32_q15(tvbr_factor, target);

@@ -41,7 +41,7 @@ size_t cbk_sizeof_enc_scratch(void) { return sizeof(EncScratch); }
 
 int cbk_launch_encode(OpusEncState* const* d_states, void* d_scratch, const i16* d_pcm, i32 pcm_stride,
                       int frame_size, u8* d_data, i32 data_stride, int max_data_bytes, i32* d_len, int n,
-                      int max_subframes, cudaStream_t stream) {
+                      int max_subframes, int general, cudaStream_t stream) {
   static bool attr_set[16] = {false};
   const size_t smem = sizeof(EncWork) * E_WARPS;
   int dev = 0;
@@ -54,7 +54,7 @@ int cbk_launch_encode(OpusEncState* const* d_states, void* d_scratch, const i16*
     attr_set[dev] = true;
   }
   const int blocks = (n + E_WARPS - 1) / E_WARPS;
-  if (max_subframes > 1)
+  if (max_subframes > 1 || general)
     opus_encode_kernel<true><<<blocks, E_WARPS * 32, smem, stream>>>(d_states, (EncScratch*)d_scratch, d_pcm, pcm_stride,
                                                                     frame_size, d_data, data_stride, max_data_bytes, d_len, n,
                                                                     CB_ENC_PHASES * max_subframes);

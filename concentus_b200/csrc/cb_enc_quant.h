@@ -481,7 +481,7 @@ CB_FN i32 enc_loss_distortion(const i16* eBands, const i16* oldEBands, int start
 // quant_coarse_energy_impl (quant_bands.c:157-261).  Serial Laplace coding, run uniformly.
 CB_FN_NOINLINE int enc_coarse_impl(RangeEnc& enc, int start, int end, const i16* eBands, i16* oldEBands, i32 budget,
                                    i32 tell, const u8* prob_model, i16* error, int C, int LM, int intra,
-                                   i32 max_decay) {
+                                   i32 max_decay, int lfe) {
   int badness = 0;
   i32 prev[2] = {0, 0};
   i32 coef, beta;
@@ -507,6 +507,7 @@ CB_FN_NOINLINE int enc_coarse_impl(RangeEnc& enc, int start, int end, const i16*
         if (bits_left < 24) qi = cb_imin(1, qi);
         if (bits_left < 16) qi = cb_imax(-1, qi);
       }
+      if (lfe && i >= 2) qi = cb_imin(qi, 0);
       if (budget - tell >= 15) {
         const int pi = 2 * cb_imin(i, 20);
         re_laplace(enc, &qi, (u32)prob_model[pi] << 7, (int)prob_model[pi + 1] << 6);
@@ -528,14 +529,14 @@ CB_FN_NOINLINE int enc_coarse_impl(RangeEnc& enc, int start, int end, const i16*
       prev[c] = sub32(add32(prev[c], shl32(q, 7)), mult16_16(beta, pshr32(q, 8)));
     }
   }
-  return badness;
+  return lfe ? 0 : badness;
 }
 
 // quant_coarse_energy (quant_bands.c:263-362): intra and inter passes, keep the cheaper one.
 // oldEBands is the state's oldBandE; w.error receives the residual; *delayedIntra is a caller local.
 CB_FN void enc_coarse_energy(EncWork& w, EncScratch& sc, RangeEnc& enc, int start, int end, int effEnd,
                              i16* oldEBands, u32 budget, int C, int LM, int nbAvailableBytes, int force_intra,
-                             i32* delayedIntra, int two_pass, int loss_rate) {
+                             i32* delayedIntra, int two_pass, int loss_rate, int lfe = 0) {
   const i16* eBands = w.bandLogE;
   int intra = force_intra || (!two_pass && *delayedIntra > 2 * C * (end - start) && nbAvailableBytes > (end - start) * C);
   const i32 intra_bias = (i32)((budget * (u32)*delayedIntra * (u32)loss_rate) / (u32)(C * 512));
@@ -545,13 +546,14 @@ CB_FN void enc_coarse_energy(EncWork& w, EncScratch& sc, RangeEnc& enc, int star
   if (tell + 3 > budget) two_pass = intra = 0;
   i32 max_decay = 16384;
   if (end - start > 10) max_decay = (i16)min32(max_decay, shl32(nbAvailableBytes, CB_DB_SHIFT - 3));
+  if (lfe) max_decay = 3072;
   w.enc_save0 = enc;                                           // enc_start_state
   CB_LANE_LOOP(i, C * CB_NBANDS) w.oldE_intra[i] = oldEBands[i];
   CB_WSYNC();
   int badness1 = 0;
   if (two_pass || intra)
     badness1 = enc_coarse_impl(enc, start, end, eBands, w.oldE_intra, (i32)budget, (i32)tell,
-                               ct_e_prob_model + (LM * 2 + 1) * 42, w.error_intra, C, LM, 1, max_decay);
+                               ct_e_prob_model + (LM * 2 + 1) * 42, w.error_intra, C, LM, 1, max_decay, lfe);
   CB_WSYNC();
   if (!intra) {
     const i32 tell_intra = (i32)re_tell_frac(enc);
@@ -564,7 +566,7 @@ CB_FN void enc_coarse_energy(EncWork& w, EncScratch& sc, RangeEnc& enc, int star
     CB_WSYNC();
     enc = w.enc_save0;
     const int badness2 = enc_coarse_impl(enc, start, end, eBands, oldEBands, (i32)budget, (i32)tell,
-                                         ct_e_prob_model + (LM * 2 + 0) * 42, w.error, C, LM, 0, max_decay);
+                                         ct_e_prob_model + (LM * 2 + 0) * 42, w.error, C, LM, 0, max_decay, lfe);
     CB_WSYNC();
     if (two_pass && (badness1 < badness2 ||
                      (badness1 == badness2 && (i32)re_tell_frac(enc) + intra_bias > tell_intra))) {

@@ -32,12 +32,17 @@ struct CeltEncScalars {
   i32 preemph_memE[2];
   i32 vbr_reservoir, vbr_drift, vbr_offset, vbr_count;
   i32 overlap_max, stereo_saving, intensity, spec_avg;
+  i32 has_mask;                   // energy_mask != NULL (celt_encoder.c:115, opus_encoder.c:103): energy_mask[] below is valid
 };
 struct alignas(16) CeltEncState {
   CeltEncScalars s;
   i32 in_mem[2][CB_OVERLAP];
   i32 prefilter_mem[2][CB_COMBFILTER_MAXPERIOD];
   i16 oldBandE[2 * CB_NBANDS], oldLogE[2 * CB_NBANDS], oldLogE2[2 * CB_NBANDS];
+  // Surround masking of this stream's channels, [channel][band], Q10 (celt_encoder.c:115): the reference keeps a
+  // pointer to the caller's array, here the values are copied in (by the ctl, or by the surround analysis
+  // kernel of the multistream encoder).  OPUS_RESET_STATE drops the mask (has_mask = 0), as it clears the pointer.
+  i16 energy_mask[2 * CB_NBANDS];
 };
 
 struct OpusEncScalars {

@@ -292,6 +292,7 @@ CB_FN int enc_decide(OpusEncState* st, OpusEncScalars& o, const i16* pcm, int fr
     o.mode = o.user_forced_mode;
   }
   if (o.mode != CB_MODE_CELT_ONLY && frame_size < o.Fs / 100) o.mode = CB_MODE_CELT_ONLY;
+  if (o.lfe) o.mode = CB_MODE_CELT_ONLY;
   if (max_data_bytes < (frame_rate > 50 ? 12000 : 8000) * frame_size / (o.Fs * 8)) o.mode = CB_MODE_CELT_ONLY;
   if (o.mode != CB_MODE_CELT_ONLY || o.application == CB_APP_VOIP) return CB_UNIMPLEMENTED;   // SILK / hybrid / VOIP high-pass
   // prev_mode is 0 or CELT-only here, so no redundancy / mode transition is ever needed.
@@ -320,6 +321,7 @@ CB_FN int enc_decide(OpusEncState* st, OpusEncScalars& o, const i16* pcm, int fr
   if (o.Fs <= 12000 && o.bandwidth > CB_BW_MEDIUMBAND) o.bandwidth = CB_BW_MEDIUMBAND;
   if (o.Fs <= 8000 && o.bandwidth > CB_BW_NARROWBAND) o.bandwidth = CB_BW_NARROWBAND;
   if (o.bandwidth == CB_BW_MEDIUMBAND) o.bandwidth = CB_BW_WIDEBAND;        // CELT has no mediumband (:1356-1357)
+  if (o.lfe) o.bandwidth = CB_BW_NARROWBAND;
   d.max_data_bytes = max_data_bytes;
   d.total_buffer = total_buffer;
   d.lsb_depth = lsb_depth;
@@ -328,6 +330,8 @@ CB_FN int enc_decide(OpusEncState* st, OpusEncScalars& o, const i16* pcm, int fr
 }
 
 // One frame of at most 20 ms: decisions, then the CELT encoder (:1442-1964).  Returns the packet length.
+// EXT: the LFE / surround-mask terms are compiled in (cb_celt_enc.h).
+template <bool EXT>
 CB_FN int enc_one_frame(EncWork& w, EncScratch& sc, OpusEncState* st, OpusEncScalars& o, const i16* pcm, int frame_size,
                         u8* data, int out_data_bytes) {
   CeltEncState* celt = &st->celt;
@@ -394,7 +398,7 @@ CB_FN int enc_one_frame(EncWork& w, EncScratch& sc, OpusEncState* st, OpusEncSca
   CB_WSYNC();
   o.prev_HB_gain = CB_Q15ONE;
   o.silk_stereoWidth_Q14 = cb_imin(1 << 14, 2 * cb_imax(0, equiv_rate - 30000));
-  if (o.channels == 2) {
+  if (!(EXT && cs.has_mask) && o.channels == 2) {                 // no width reduction under a surround mask (:1792)
     if (o.hybrid_stereo_width_Q14 < (1 << 14) || o.silk_stereoWidth_Q14 < (1 << 14)) {
       i32 g1 = (i16)o.hybrid_stereo_width_Q14, g2 = (i16)o.silk_stereoWidth_Q14;
       g1 = g1 == 16384 ? CB_Q15ONE : shl16(g1, 1);
@@ -412,7 +416,7 @@ CB_FN int enc_one_frame(EncWork& w, EncScratch& sc, OpusEncState* st, OpusEncSca
   CB_WSYNC();
   int ret = 0;
   if (re_tell(w.enc) <= 8 * nb_compr_bytes) {
-    ret = celt_encode_frame(w, sc, celt, pcm_buf, frame_size, nb_compr_bytes);
+    ret = celt_encode_frame<EXT>(w, sc, celt, pcm_buf, frame_size, nb_compr_bytes);
     if (ret < 0) return CB_INTERNAL_ERROR;
   }
   CB_WSYNC();
@@ -436,8 +440,8 @@ CB_FN int enc_one_frame(EncWork& w, EncScratch& sc, OpusEncState* st, OpusEncSca
 // A 40 / 60 ms frame in CELT-only mode is two or three 20 ms frames in one packet (opus_encoder.c:1362-1438):
 // the decisions are taken once for the long frame and forced on the short ones, each short frame is coded
 // into scratch, and the repacketizer's assembly (cb_repack.h) builds the packet.
-// MULTI = false leaves the long-frame path out (the kernel instance for launches in which no stream has one:
-// the 20 ms path then compiles exactly as it did before long frames were supported).
+// MULTI = false leaves the long-frame path and the LFE / surround-mask terms out (the kernel instance for launches
+// in which no stream needs them: the plain 20 ms path then compiles exactly as it did before they were supported).
 template <bool MULTI>
 CB_FN int opus_encode_stream(EncWork& w, EncScratch& sc, OpusEncState* st, const i16* pcm, int analysis_frame_size,
                              u8* data, int out_data_bytes) {
@@ -473,7 +477,7 @@ CB_FN int opus_encode_stream(EncWork& w, EncScratch& sc, OpusEncState* st, const
   CB_NOUNROLL for (int i = 0; i < (MULTI ? nb_frames : 1); i++) {
     const bool multi = MULTI && nb_frames > 1;
     const int sub = multi ? o.Fs / 50 : frame_size;
-    ret = enc_one_frame(w, sc, st, o, multi ? pcm + (size_t)i * o.channels * sub : pcm, sub,
+    ret = enc_one_frame<MULTI>(w, sc, st, o, multi ? pcm + (size_t)i * o.channels * sub : pcm, sub,
                         multi ? sc.multi_tmp + i * bytes_per_frame : data, multi ? bytes_per_frame : out_data_bytes);
     if (ret < 0) return multi ? CB_INTERNAL_ERROR : ret;
     sub_len |= (unsigned long long)ret << (16 * i);

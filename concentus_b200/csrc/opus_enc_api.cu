@@ -42,6 +42,7 @@ struct OpusEncoder {
   int device;
   OpusEncState* d_state;
   OpusEncoderGroup* self_group;   // group of one, created on first opus_encode()
+  bool ext;                       // has had OPUS_SET_LFE / OPUS_SET_ENERGY_MASK: launches use the general kernel instance
 };
 
 // Two-deep pipeline behind opus_encode_group_submit/_wait (copies on their own streams, see opus_api.cu)
@@ -110,14 +111,15 @@ int group_launch(OpusEncoderGroup* g, const i16* d_pcm, i32 pcm_stride, int fram
   if (g_enc_prof_on) { cudaEventCreate(&pr.a); cudaEventCreate(&pr.b); cudaEventRecord(pr.a, stream); }
   // a frame longer than 20 ms is coded as two or three 20 ms frames: the kernel's stage rendezvous has to
   // know the most any member will do (members may run at different rates)
-  int max_sub = 1;
-  for (int i = 0; i < g->n && max_sub < 3; i++) {
+  int max_sub = 1, general = 0;
+  for (int i = 0; i < g->n; i++) {
     const int Fs = g->members[i]->Fs;
     const int nb = frame_size * 50 > Fs ? (frame_size * 25 > Fs ? 3 : 2) : 1;
     if (nb > max_sub) max_sub = nb;
+    if (g->members[i]->ext) general = 1;
   }
   int rc = cbk_launch_encode(g->d_states, g->d_scratch, d_pcm, pcm_stride, frame_size, d_data, data_stride,
-                             max_data_bytes, d_len, g->n, max_sub, stream);
+                             max_data_bytes, d_len, g->n, max_sub, general, stream);
   if (g_enc_prof_on) { cudaEventRecord(pr.b, stream); g_enc_prof.push_back(pr); }
   opusb_internal_count_launches(1);
   if (rc != 0) {
@@ -408,6 +410,22 @@ int opus_encoder_ctl(OpusEncoder* st, int request, ...) {
     va_end(ap);
     return ret;
   }
+  if (request == CB_REQ_SET_ENERGY_MASK) {
+    // opus_encoder.c:2462-2467: the reference keeps the pointer and reads 21 values per channel at the next
+    // opus_encode(); here they are copied into the device state now.  NULL drops the mask.
+    const opus_int16* mask = va_arg(ap, const opus_int16*);
+    va_end(ap);
+    char* d_celt = (char*)st->d_state + offsetof(OpusEncState, celt);
+    const i32 has = mask ? 1 : 0;
+    if (mask && cudaMemcpy(d_celt + offsetof(CeltEncState, energy_mask), mask, sizeof(i16) * CB_NBANDS * st->channels,
+                           cudaMemcpyHostToDevice) != cudaSuccess)
+      return OPUS_INTERNAL_ERROR;
+    if (cudaMemcpy(d_celt + offsetof(CeltEncState, s) + offsetof(CeltEncScalars, has_mask), &has, sizeof(has),
+                   cudaMemcpyHostToDevice) != cudaSuccess)
+      return OPUS_INTERNAL_ERROR;
+    if (mask) st->ext = true;
+    return OPUS_OK;
+  }
   // scalars only: read both scalar blocks, apply, write back when it was a setter
   OpusEncScalars o;
   CeltEncScalars cs;
@@ -425,6 +443,7 @@ int opus_encoder_ctl(OpusEncoder* st, int request, ...) {
     opus_int32 value = va_arg(ap, opus_int32);
     i32 dummy = 0;
     ret = opus_enc_ctl_scalars(&o, &cs, request, value, &dummy);
+    if (ret == OPUS_OK && request == CB_REQ_SET_LFE && value) st->ext = true;
     if (ret == OPUS_OK) {
       if (cudaMemcpy(st->d_state, &o, sizeof(o), cudaMemcpyHostToDevice) != cudaSuccess ||
           cudaMemcpy(d_cs, &cs, sizeof(cs), cudaMemcpyHostToDevice) != cudaSuccess)
@@ -433,6 +452,18 @@ int opus_encoder_ctl(OpusEncoder* st, int request, ...) {
   }
   va_end(ap);
   return ret;
+}
+
+// For the multistream surround encoder (opus_ms_enc_api.cu): where this encoder's CELT state keeps the surround
+// mask of channel `side` (0 / 1) and the flag that says one is set; the surround analysis kernel writes both.
+// Launches of this encoder use the kernel instance with the surround terms from now on.
+int opusb_internal_encoder_mask_slots(OpusEncoder* st, int side, opus_int16** mask, opus_int32** has_mask) {
+  if (!valid(st) || side < 0 || side >= st->channels || !mask || !has_mask) return OPUS_BAD_ARG;
+  char* d_celt = (char*)st->d_state + offsetof(OpusEncState, celt);
+  *mask = (opus_int16*)(d_celt + offsetof(CeltEncState, energy_mask)) + CB_NBANDS * side;
+  *has_mask = (opus_int32*)(d_celt + offsetof(CeltEncState, s) + offsetof(CeltEncScalars, has_mask));
+  st->ext = true;
+  return OPUS_OK;
 }
 
 int opus_encoder_get_final_range_batch(OpusEncoder* const* st, int n, opus_uint32* out) {

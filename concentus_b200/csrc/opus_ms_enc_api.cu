@@ -5,11 +5,13 @@
 // and the byte budget of stream s depends on what streams 0..s-1 produced (opus_multistream_encoder.c:
 // 820-905), so the streams of one multistream frame are encoded one after the other; each is an ordinary
 // opus_encode() on its own elementary encoder.  Host code here: channel copy-in, rate split, packet
-// assembly.  Built: opus_multistream_encoder_create() layouts and the surround_encoder_create() families
-// that need no surround analysis (family 0, family 255, family 1 with <= 2 channels).  Family 1 with
-// three or more channels (masking analysis + LFE stream, :224-360) answers OPUS_UNIMPLEMENTED.
-// What the elementary encoder does not build (SILK / hybrid mode decisions, 40/60 ms) comes back from
-// opus_encode() as OPUS_UNIMPLEMENTED and is passed on.
+// assembly.  Built: opus_multistream_encoder_create() layouts and every opus_multistream_surround_encoder_create()
+// family (0, 1, 255).  Family 1 with three or more channels is the surround case (:224-360, 525, 816-887): a
+// masking analysis of all input channels runs first (surround_analysis_kernel, cb_surround_kernels.cu) and writes
+// each channel's masks into the CELT state of its stream on the device; the sixth channel of 5.1 and up is an
+// LFE stream; coupled streams are forced to stereo CELT and the bandwidth follows the total rate.
+// What the elementary encoder does not build (SILK / hybrid mode decisions: a mono stream below ~23 kbit/s)
+// comes back from opus_encode() as OPUS_UNIMPLEMENTED and is passed on.
 #include <stdarg.h>
 #include <stdlib.h>
 #include <string.h>
@@ -17,8 +19,17 @@
 
 #include <vector>
 
+#include <cuda_runtime.h>
+
 #include "../../include/opus_b200.h"
 #include "cb_repack_internal.h"
+#include "cb_surround_kernels.h"
+
+extern "C" cudaStream_t opusb_internal_stream(int* err);
+extern "C" void opusb_internal_count_launches(int n);
+extern "C" int opusb_internal_encoder_mask_slots(OpusEncoder* st, int side, opus_int16** mask, opus_int32** has_mask);
+
+#define OPUS_SET_LFE_REQUEST 10024          // celt/celt.h:113
 
 struct OpusMSEncoder {
   int magic;
@@ -29,6 +40,13 @@ struct OpusMSEncoder {
   opus_int32 bitrate_bps;
   int variable_duration;
   OpusEncoder** enc;             // nb_streams elementary encoders: the coupled (stereo) ones first
+  int surround, lfe_stream;      // family 1 with >= 3 channels; index of the LFE stream or -1
+  // surround analysis (device): SurroundState, work buffers, the frame's PCM, where each channel's masks go
+  void* d_surround_state;
+  void* d_surround_scratch;
+  opus_int16* d_pcm;
+  size_t d_pcm_cap;
+  SurroundDst dst;
 };
 
 namespace {
@@ -72,28 +90,32 @@ int select_frame_size(int frame_size, int variable_duration, opus_int32 Fs) {
   return new_size;
 }
 
-// surround_rate_allocation (opus_multistream_encoder.c:621-695) without an LFE stream
+// surround_rate_allocation (opus_multistream_encoder.c:621-695)
 opus_int32 split_rate(const OpusMSEncoder* st, opus_int32* rate, int frame_size) {
   const opus_int32 Fs = st->Fs;
   int stream_offset;
   if (st->bitrate_bps > st->nb_channels * 40000) stream_offset = 20000;
   else stream_offset = st->bitrate_bps / st->nb_channels / 2;
   stream_offset += 60 * (Fs / frame_size - 50);
+  const int lfe_offset = 3500 + 60 * (Fs / frame_size - 50);
   const int coupled_ratio = 512;                       // Q8: a coupled stream gets twice the mono rate
+  const int lfe_ratio = 32;                            // Q8: the LFE stream gets 1/8 of it
   opus_int32 channel_rate;
   if (st->bitrate_bps == OPUS_AUTO) {
     channel_rate = Fs + 60 * Fs / frame_size;
   } else if (st->bitrate_bps == OPUS_BITRATE_MAX) {
     channel_rate = 300000;
   } else {
-    const int nb_coupled = st->nb_coupled, nb_uncoupled = st->nb_streams - nb_coupled;
-    const int total = (nb_uncoupled << 8) + coupled_ratio * nb_coupled;
-    channel_rate = 256 * (st->bitrate_bps - stream_offset * (nb_coupled + nb_uncoupled)) / total;
+    const int nb_lfe = st->lfe_stream != -1;
+    const int nb_coupled = st->nb_coupled, nb_uncoupled = st->nb_streams - nb_coupled - nb_lfe;
+    const int total = (nb_uncoupled << 8) + coupled_ratio * nb_coupled + nb_lfe * lfe_ratio;
+    channel_rate = 256 * (st->bitrate_bps - lfe_offset * nb_lfe - stream_offset * (nb_coupled + nb_uncoupled)) / total;
   }
   opus_int32 sum = 0;
   for (int i = 0; i < st->nb_streams; i++) {
     if (i < st->nb_coupled) rate[i] = stream_offset + (channel_rate * coupled_ratio >> 8);
-    else rate[i] = stream_offset + channel_rate;
+    else if (i != st->lfe_stream) rate[i] = stream_offset + channel_rate;
+    else rate[i] = lfe_offset + (channel_rate * lfe_ratio >> 8);
     if (rate[i] < 500) rate[i] = 500;
     sum += rate[i];
   }
@@ -107,12 +129,15 @@ void free_encoder(OpusMSEncoder* st) {
       if (st->enc[i]) opus_encoder_destroy(st->enc[i]);
     free(st->enc);
   }
+  cudaFree(st->d_surround_state);
+  cudaFree(st->d_surround_scratch);
+  cudaFree(st->d_pcm);
   st->magic = 0;
   free(st);
 }
 
 OpusMSEncoder* create_impl(opus_int32 Fs, int channels, int streams, int coupled_streams, const unsigned char* mapping,
-                           int application, int* error) {
+                           int application, int* error, int surround = 0, int lfe_stream = -1) {
   int err = OPUS_OK;
   OpusMSEncoder* st = nullptr;
   do {
@@ -126,6 +151,8 @@ OpusMSEncoder* create_impl(opus_int32 Fs, int channels, int streams, int coupled
     st->Fs = Fs; st->application = application;
     st->bitrate_bps = OPUS_AUTO;
     st->variable_duration = OPUS_FRAMESIZE_ARG;
+    st->surround = surround;
+    st->lfe_stream = surround ? lfe_stream : -1;
     const int max_channel = streams + coupled_streams;           // validate_layout (opus_multistream.c:39-51)
     bool ok = max_channel <= 255;
     for (int i = 0; i < channels && ok; i++) {
@@ -142,6 +169,23 @@ OpusMSEncoder* create_impl(opus_int32 Fs, int channels, int streams, int coupled
     for (int i = 0; i < streams; i++) {
       st->enc[i] = opus_encoder_create(Fs, i < coupled_streams ? 2 : 1, application, &err);
       if (!st->enc[i]) break;
+      if (i == st->lfe_stream) err = opus_encoder_ctl(st->enc[i], OPUS_SET_LFE_REQUEST, 1);
+      if (err != OPUS_OK) break;
+    }
+    if (err != OPUS_OK || !surround) break;
+    // surround analysis state (zero: :466-470) and buffers; channel c's masks go to the stream that codes it
+    if (cudaMalloc(&st->d_surround_state, cbk_sizeof_surround_state()) != cudaSuccess ||
+        cudaMalloc(&st->d_surround_scratch, cbk_sizeof_surround_scratch()) != cudaSuccess ||
+        cudaMemset(st->d_surround_state, 0, cbk_sizeof_surround_state()) != cudaSuccess) { err = OPUS_ALLOC_FAIL; break; }
+    for (int s = 0; s < streams && err == OPUS_OK; s++) {
+      if (s < coupled_streams) {
+        const int l = left_channel(st, s), r = right_channel(st, s);
+        err = opusb_internal_encoder_mask_slots(st->enc[s], 0, &st->dst.mask[l], &st->dst.has_mask[l]);
+        if (err == OPUS_OK) err = opusb_internal_encoder_mask_slots(st->enc[s], 1, &st->dst.mask[r], &st->dst.has_mask[r]);
+      } else {
+        const int c = mono_channel(st, s);
+        err = opusb_internal_encoder_mask_slots(st->enc[s], 0, &st->dst.mask[c], &st->dst.has_mask[c]);
+      }
     }
   } while (0);
   if (err != OPUS_OK) {
@@ -176,9 +220,42 @@ int encode_impl(OpusMSEncoder* st, const opus_int16* pcm16, int analysis_frame_s
       if (cap < max_data_bytes) max_data_bytes = cap;
     }
   }
+  if (st->surround) {
+    // masks of this frame, written into the streams' states on the device (:787-790, 862-887)
+    int err = 0;
+    cudaStream_t stream = opusb_internal_stream(&err);
+    if (!stream) return err;
+    const size_t bytes = sizeof(opus_int16) * (size_t)frame_size * st->nb_channels;
+    if (bytes > st->d_pcm_cap) {
+      cudaFree(st->d_pcm);
+      st->d_pcm = nullptr; st->d_pcm_cap = 0;
+      if (cudaMalloc((void**)&st->d_pcm, bytes) != cudaSuccess) return OPUS_ALLOC_FAIL;
+      st->d_pcm_cap = bytes;
+    }
+    if (cudaMemcpyAsync(st->d_pcm, pcm16, bytes, cudaMemcpyHostToDevice, stream) != cudaSuccess) return OPUS_INTERNAL_ERROR;
+    if (cbk_launch_surround(st->d_pcm, st->nb_channels, frame_size, Fs, st->d_surround_state, st->d_surround_scratch,
+                            &st->dst, stream) != 0)
+      return OPUS_INTERNAL_ERROR;
+    opusb_internal_count_launches(1);
+    if (cudaStreamSynchronize(stream) != cudaSuccess) return OPUS_INTERNAL_ERROR;   // pcm16 may be pageable
+  }
   for (int s = 0; s < st->nb_streams; s++) {
     rc = opus_encoder_ctl(st->enc[s], OPUS_SET_BITRATE_REQUEST, bitrates[s]);
     if (rc != OPUS_OK) return rc;
+    if (st->surround) {
+      opus_int32 equiv_rate = st->bitrate_bps;
+      if (frame_size * 50 < Fs) equiv_rate -= 60 * (Fs / frame_size - 50) * st->nb_channels;
+      const int bw = equiv_rate > 10000 * st->nb_channels ? OPUS_BANDWIDTH_FULLBAND
+                     : equiv_rate > 7000 * st->nb_channels ? OPUS_BANDWIDTH_SUPERWIDEBAND
+                     : equiv_rate > 5000 * st->nb_channels ? OPUS_BANDWIDTH_WIDEBAND : OPUS_BANDWIDTH_NARROWBAND;
+      rc = opus_encoder_ctl(st->enc[s], OPUS_SET_BANDWIDTH_REQUEST, bw);
+      if (rc == OPUS_OK && s < st->nb_coupled) {
+        // the spatial image needs stereo CELT on the coupled streams (:831-836)
+        rc = opus_encoder_ctl(st->enc[s], OPUS_SET_FORCE_MODE_REQUEST, 1002);   // MODE_CELT_ONLY
+        if (rc == OPUS_OK) rc = opus_encoder_ctl(st->enc[s], OPUS_SET_FORCE_CHANNELS_REQUEST, 2);
+      }
+      if (rc != OPUS_OK) return rc;
+    }
   }
   std::vector<opus_int16> buf((size_t)2 * frame_size);
   unsigned char tmp_data[MS_FRAME_TMP];
@@ -258,17 +335,21 @@ OpusMSEncoder* opus_multistream_surround_encoder_create(opus_int32 Fs, int chann
     *coupled_streams = channels - 1;
     mapping[0] = 0;
     if (channels == 2) mapping[1] = 1;
-  } else if (mapping_family == 1 && channels <= 2) {
-    *streams = 1;
-    *coupled_streams = channels - 1;
-    mapping[0] = 0;
-    if (channels == 2) mapping[1] = 1;
+  } else if (mapping_family == 1 && channels <= 8) {
+    // vorbis_mappings (:49-62)
+    static const struct { int nb_streams, nb_coupled; unsigned char mapping[8]; } vorbis[8] = {
+        {1, 0, {0}}, {1, 1, {0, 1}}, {2, 1, {0, 2, 1}}, {2, 2, {0, 1, 2, 3}}, {3, 2, {0, 4, 1, 2, 3}},
+        {4, 2, {0, 4, 1, 2, 3, 5}}, {4, 3, {0, 4, 1, 2, 3, 5, 6}}, {5, 3, {0, 6, 1, 2, 3, 4, 5, 7}}};
+    *streams = vorbis[channels - 1].nb_streams;
+    *coupled_streams = vorbis[channels - 1].nb_coupled;
+    for (int i = 0; i < channels; i++) mapping[i] = vorbis[channels - 1].mapping[i];
+    return create_impl(Fs, channels, *streams, *coupled_streams, mapping, application, error, channels > 2,
+                       channels >= 6 ? *streams - 1 : -1);
   } else if (mapping_family == 255) {
     *streams = channels;
     *coupled_streams = 0;
     for (int i = 0; i < channels; i++) mapping[i] = (unsigned char)i;
   } else {
-    // family 1 with 3..8 channels needs the surround masking analysis and the LFE stream: not built
     if (error) *error = OPUS_UNIMPLEMENTED;
     return nullptr;
   }
@@ -392,6 +473,10 @@ int opus_multistream_encoder_ctl(OpusMSEncoder* st, int request, ...) {
       break;
     }
     case OPUS_RESET_STATE: {
+      if (st->surround && cudaMemset(st->d_surround_state, 0, cbk_sizeof_surround_state()) != cudaSuccess) {
+        ret = OPUS_INTERNAL_ERROR;
+        break;
+      }
       for (int s = 0; s < st->nb_streams; s++) {
         ret = opus_encoder_ctl(st->enc[s], OPUS_RESET_STATE);
         if (ret != OPUS_OK) break;

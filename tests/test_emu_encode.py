@@ -114,3 +114,90 @@ def test_emu_long_frames_match_reference(emu_enc_lib, ms):
                         x = pcm[t * frame * ch:(t + 1) * frame * ch]
                         a, b = ref.encode(x, frame, maxb), emu.encode(x, frame, maxb)
                         assert a == b, (app, ch, fs, ms, vbr, maxb, t, a[0], b[0])
+
+
+@needs_ref
+def test_emu_lfe_and_surround_mask_match_reference(emu_enc_lib):
+    """The two settings only a surround multistream encoder uses on its elementary encoders: OPUS_SET_LFE
+    (celt_encoder.c:1649-2117 `st->lfe` branches, quant_bands.c:232,266,302) and OPUS_SET_ENERGY_MASK
+    (celt_encoder.c:1726-1801 masking terms; opus_encoder.c:1792 no stereo width reduction).  Masks here are
+    random Q10 values in the range surround_analysis produces (and beyond it, to hit the clamps); a new one is
+    set before every frame, as the multistream encoder does."""
+    import ctypes
+    rng = np.random.RandomState(11)
+    emu_enc_lib.emu_enc_set_mask.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+    rlib = RefEncoder.lib()
+    for ch, lfe, rate, vbr, cvbr, ms, fs in [(1, 1, 6000, 1, 1, 20, 48000), (1, 1, 3500, 1, 0, 20, 48000),
+                                            (1, 1, 8000, 0, 0, 10, 48000), (1, 1, 5000, 1, 1, 40, 48000),
+                                            (2, 0, 96000, 1, 1, 20, 48000), (2, 0, 64000, 1, 0, 20, 48000),
+                                            (1, 0, 48000, 1, 1, 20, 48000), (2, 0, 80000, 0, 0, 20, 48000),
+                                            (2, 0, 40000, 1, 1, 10, 48000), (1, 0, 32000, 1, 0, 5, 48000),
+                                            (2, 0, 120000, 1, 1, 60, 48000), (2, 0, 70000, 1, 1, 20, 24000)]:
+        ref, emu = RefEncoder(fs, ch, 2049), EmuEncoder(emu_enc_lib, fs, ch, 2049)
+        for e in (ref, emu):
+            assert e.ctl(enc_cases.SET_BITRATE, rate) == 0
+            assert e.ctl(enc_cases.SET_VBR, vbr) == 0
+            assert e.ctl(4020, cvbr) == 0
+            assert e.ctl(11002, 1002) == 0
+            if lfe:
+                assert e.ctl(10024, 1) == 0
+        frame = fs * ms // 1000
+        nfr = 12
+        pcm = enc_cases.signal(enc_cases.KINDS[(ch + ms + rate // 1000) % len(enc_cases.KINDS)], frame * nfr, ch, 5)
+        masks = []                                   # keep the arrays alive: the reference holds the pointer
+        for t in range(nfr):
+            if not lfe:
+                scale = [300, 1500, 4000][t % 3]
+                m = np.ascontiguousarray(rng.randint(-scale, scale // 4 + 1, size=21 * ch).astype(np.int16))
+                if t % 5 == 4:
+                    m[:] = -3000                      # heavy masking everywhere
+                masks.append(m)
+                assert rlib.opus_encoder_ctl(ctypes.c_void_p(ref.h), ctypes.c_int(10026), ctypes.c_void_p(m.ctypes.data)) == 0
+                emu_enc_lib.emu_enc_set_mask(emu.h, m.ctypes.data)
+            x = pcm[t * frame * ch:(t + 1) * frame * ch]
+            a, b = ref.encode(x, frame, 1275), emu.encode(x, frame, 1275)
+            assert a == b, (ch, lfe, rate, vbr, ms, fs, t, a[0], b[0])
+
+
+@needs_ref
+def test_emu_surround_analysis_matches_reference(emu_enc_lib):
+    """surround_analysis (opus_multistream_encoder.c:224-360) -- the per-channel masks a surround multistream
+    encoder hands to its elementary encoders -- against the reference's own function on 3..8 channel frames of
+    2.5..60 ms at three rates, the window / pre-emphasis memories carried over several frames."""
+    import ctypes
+    rlib = RefEncoder.lib()
+    rlib.opus_custom_mode_create.restype = ctypes.c_void_p
+    rlib.opus_custom_mode_create.argtypes = [ctypes.c_int32, ctypes.c_int, ctypes.c_void_p]
+    mode = rlib.opus_custom_mode_create(48000, 960, None)
+    assert mode
+    COPY = ctypes.CFUNCTYPE(None, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int)
+
+    def copy_in(dst, dst_stride, src, src_stride, src_channel, frame_size):
+        s = np.ctypeslib.as_array(ctypes.cast(src, ctypes.POINTER(ctypes.c_int16)), shape=(frame_size * src_stride,))
+        d = np.ctypeslib.as_array(ctypes.cast(dst, ctypes.POINTER(ctypes.c_int16)), shape=(frame_size * dst_stride,))
+        d[::dst_stride] = s[src_channel::src_stride]
+    cb = COPY(copy_in)
+    rlib.surround_analysis.restype = None
+    rlib.surround_analysis.argtypes = [ctypes.c_void_p] * 5 + [ctypes.c_int] * 4 + [COPY, ctypes.c_int]
+    emu_enc_lib.emu_surround_analysis.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int] + [ctypes.c_void_p] * 3
+    rng = np.random.RandomState(3)
+    for channels in (3, 4, 5, 6, 7, 8):
+        for fs, ms10 in ((48000, 200), (48000, 25), (48000, 100), (48000, 400), (48000, 600), (24000, 200), (16000, 50),
+                         (24000, 400), (8000, 200)):
+            len_ = fs * ms10 // 10000
+            mem_r = np.zeros(channels * 120, dtype=np.int32); pre_r = np.zeros(channels, dtype=np.int32)
+            mem_e = mem_r.copy(); pre_e = pre_r.copy()
+            for t in range(4):
+                pcm = np.zeros((len_, channels), dtype=np.int16)
+                for c in range(channels):
+                    kind = enc_cases.KINDS[(c + t + channels) % len(enc_cases.KINDS)]
+                    gain = [1.0, 0.3, 0.05, 0.0][(c + t) % 4] if t else 1.0
+                    pcm[:, c] = (enc_cases.signal(kind, len_, 1, 100 * t + c).astype(np.float64) * gain).astype(np.int16)
+                pcm = np.ascontiguousarray(pcm.reshape(-1))
+                out_r = np.zeros(21 * channels, dtype=np.int16); out_e = out_r.copy()
+                rlib.surround_analysis(mode, pcm.ctypes.data, out_r.ctypes.data, mem_r.ctypes.data, pre_r.ctypes.data,
+                                       len_, 120, channels, fs, cb, 0)
+                emu_enc_lib.emu_surround_analysis(pcm.ctypes.data, channels, len_, fs, mem_e.ctypes.data,
+                                                  pre_e.ctypes.data, out_e.ctypes.data)
+                assert np.array_equal(out_r, out_e), (channels, fs, ms10, t, out_r[:8], out_e[:8])
+                assert np.array_equal(mem_r, mem_e) and np.array_equal(pre_r, pre_e), (channels, fs, ms10, t)

@@ -1,6 +1,7 @@
 """Multistream encoder on the GPU against the compiled reference: same packets (bytes) and final range for
-explicit layouts (coupled + mono streams), surround families 0 / 255, VBR and CBR, generous and tight output
-buffers (the byte budget of a stream depends on the streams before it), plus the creation error codes."""
+explicit layouts (coupled + mono streams), surround families 0 / 255 / 1 (3..8 channels: masking analysis on the
+device, LFE stream), VBR and CBR, generous and tight output buffers (the byte budget of a stream depends on the
+streams before it), plus the creation error codes."""
 import ctypes
 
 import numpy as np
@@ -111,15 +112,74 @@ def test_surround_create_families_without_analysis(family, ch):
         ref.opus_multistream_encoder_destroy(b)
 
 
+def surround_pcm(channels, frames, frame, fs):
+    """Channels of different material and level (some silent for a while), so that the masks move."""
+    cols = []
+    for c in range(channels):
+        x = enc_cases.signal(enc_cases.KINDS[(2 * c + 1) % len(enc_cases.KINDS)], frame * frames, 1, 900 + c).astype(np.float64)
+        g = np.ones(frame * frames)
+        for t in range(frames):
+            g[t * frame:(t + 1) * frame] = [1.0, 0.5, 0.1, 0.02, 0.0, 1.0][(t + 2 * c) % 6]
+        cols.append((x * g).astype(np.int16))
+    return np.ascontiguousarray(np.stack(cols, axis=1))
+
+
+@needs_ref
+@pytest.mark.parametrize("ch", [3, 4, 5, 6, 7, 8])
+@pytest.mark.parametrize("app,fs,vbr,cvbr,rate_per_ch,maxbytes,frame_ms", [
+    (LOWDELAY, 48000, 1, 1, 42000, 4000, 20), (2049, 48000, 1, 1, 48000, 4000, 20), (2049, 48000, 0, 0, 40000, 1500, 20),
+    (LOWDELAY, 48000, 1, 0, 24000, 600, 10), (LOWDELAY, 48000, 1, 1, 64000, 4000, 40), (2049, 24000, 1, 1, 56000, 4000, 20),
+    (LOWDELAY, 48000, 0, 0, 30000, 900, 5), (LOWDELAY, 48000, 1, 1, 6500, 4000, 20), (2049, 48000, 1, 1, 96000, 4000, 60)])
+def test_surround_family1_matches_reference(ch, app, fs, vbr, cvbr, rate_per_ch, maxbytes, frame_ms):
+    """opus_multistream_surround_encoder_create(family 1, 3..8 channels): vorbis channel order, surround masking
+    analysis (surround_analysis, on the device) feeding OPUS_SET_ENERGY_MASK of every stream, the LFE stream of
+    5.1 / 6.1 / 7.1, forced stereo CELT on coupled streams, bandwidth from the total rate.  Packets byte-identical
+    with the reference, final range too; a reset in the middle."""
+    ours, ref = cb.load(), _ref()
+    res = []
+    for lib in (ours, ref):
+        streams, coupled, err = ctypes.c_int(0), ctypes.c_int(0), ctypes.c_int(0)
+        mapping = (ctypes.c_ubyte * 8)()
+        h = lib.opus_multistream_surround_encoder_create(fs, ch, 1, ctypes.byref(streams), ctypes.byref(coupled),
+                                                         mapping, app, ctypes.byref(err))
+        assert h and err.value == 0
+        res.append((h, streams.value, coupled.value, list(mapping)[:ch]))
+    assert res[0][1:] == res[1][1:]
+    a, b = res[0][0], res[1][0]
+    try:
+        ctl_both((ours, ref), (a, b), enc_cases.SET_BITRATE, rate_per_ch * ch)
+        ctl_both((ours, ref), (a, b), enc_cases.SET_VBR, vbr)
+        ctl_both((ours, ref), (a, b), 4020, cvbr)
+        frame = fs * frame_ms // 1000
+        nframes = 10
+        pcm = surround_pcm(ch, nframes, frame, fs)
+        for t in range(nframes):
+            if t == 6:
+                for lib, h in ((ours, a), (ref, b)):
+                    assert lib.opus_multistream_encoder_ctl(ctypes.c_void_p(h), 4028) == 0      # OPUS_RESET_STATE
+            x = np.ascontiguousarray(pcm[t * frame:(t + 1) * frame])
+            o1, o2 = ctypes.create_string_buffer(maxbytes), ctypes.create_string_buffer(maxbytes)
+            n1 = ours.opus_multistream_encode(a, x.ctypes.data, frame, o1, maxbytes)
+            n2 = ref.opus_multistream_encode(b, x.ctypes.data, frame, o2, maxbytes)
+            assert n1 == n2, (ch, app, t, n1, n2)
+            assert n1 > 0 and o1.raw[:n1] == o2.raw[:n2], (ch, app, t)
+            assert final_range(ours, a) == final_range(ref, b), (ch, t)
+    finally:
+        ours.opus_multistream_encoder_destroy(a)
+        ref.opus_multistream_encoder_destroy(b)
+
+
 def test_creation_errors():
     ours = cb.load()
     err = ctypes.c_int(0)
     streams, coupled = ctypes.c_int(0), ctypes.c_int(0)
     mapping = (ctypes.c_ubyte * 8)()
-    # 5.1 surround needs the masking analysis and the LFE stream: refused, not approximated
-    assert not ours.opus_multistream_surround_encoder_create(48000, 6, 1, ctypes.byref(streams), ctypes.byref(coupled),
-                                                             mapping, LOWDELAY, ctypes.byref(err))
-    assert err.value == cb.OPUS_UNIMPLEMENTED
+    # families other than 0 / 1 / 255, family 1 above 8 channels, family 0 above stereo (:488-537)
+    for fam, ch in ((2, 6), (1, 9), (0, 3)):
+        big = (ctypes.c_ubyte * 16)()
+        assert not ours.opus_multistream_surround_encoder_create(48000, ch, fam, ctypes.byref(streams), ctypes.byref(coupled),
+                                                                 big, LOWDELAY, ctypes.byref(err))
+        assert err.value == cb.OPUS_UNIMPLEMENTED
     bad = (ctypes.c_ubyte * 3)(0, 1, 1)                 # stream 1 (mono) has no channel: mapping never names index 2
     assert not ours.opus_multistream_encoder_create(48000, 3, 2, 1, bad, LOWDELAY, ctypes.byref(err))
     assert err.value == cb.OPUS_BAD_ARG
