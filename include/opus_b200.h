@@ -326,9 +326,11 @@ int opus_encoder_get_final_range_batch(OpusEncoder *const *st, int n, opus_uint3
  * The streams of one multistream frame are encoded one after the other (the byte budget of a stream depends
  * on its predecessors), each by an ordinary elementary encoder on the GPU; channel copy-in, the rate split
  * and the packet assembly are host code.  Built: explicit layouts (opus_multistream_encoder_create) and the
- * surround families that need no masking analysis (family 0, family 255, family 1 up to 2 channels).
- * Family 1 with 3..8 channels (surround analysis + LFE stream) returns OPUS_UNIMPLEMENTED, and so does any
- * frame the elementary encoder refuses (see opus_encode above). */
+ * surround families 0, 1 and 255.  Family 1 with 3..8 channels is the surround encoder proper
+ * (opus_multistream_encoder.c:224-360, 525, 816-887): a masking analysis of all input channels runs on the device
+ * before the streams are coded and hands every stream its masks (the reference's OPUS_SET_ENERGY_MASK), the
+ * sixth channel of 5.1 / 6.1 / 7.1 is an LFE stream (OPUS_SET_LFE).  A frame the elementary encoder refuses
+ * (see opus_encode above: a stream for which the reference would pick SILK or hybrid) returns OPUS_UNIMPLEMENTED. */
 typedef struct OpusMSEncoder OpusMSEncoder;
 #define OPUS_MULTISTREAM_GET_ENCODER_STATE_REQUEST 5120
 opus_int32 opus_multistream_encoder_get_size(int streams, int coupled_streams);
