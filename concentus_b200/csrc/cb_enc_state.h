@@ -107,7 +107,7 @@ static inline void opus_enc_reset(OpusEncState* st) {
   s->first = 1;
   s->mode = CB_MODE_HYBRID;
   s->bandwidth = CB_BW_FULLBAND;
-  s->variable_HP_smth2_Q15 = 0;   // only the SILK/VOIP high-pass uses it (not built)
+  s->variable_HP_smth2_Q15 = 756 << 8;   // silk_lin2log(VARIABLE_HP_MIN_CUTOFF_HZ = 60) << 8 (opus_encoder.c:242, 2442)
   s->silk_stereoWidth_Q14 = 0;
 }
 static inline void opus_enc_init(OpusEncState* st, int Fs, int channels, int application) {

@@ -168,6 +168,68 @@ CB_FN void enc_stereo_fade(i16* buf, i32 g1, i32 g2, int frame_size, int Fs) {
   CB_WSYNC();
 }
 
+// The few SILK fixed-point primitives the VOIP high-pass needs (silk/macros.h:53,60,92; SigProc_FIX.h:561;
+// lin2log.c, log2lin.c), 64-bit forms as the reference compiles on x86-64.
+CB_FN i32 esk_smulwb(i32 a, i32 b) { return (i32)(((long long)a * (long long)(i16)b) >> 16); }
+CB_FN i32 esk_smlawb(i32 a, i32 b, i32 c) { return (i32)((u32)a + (u32)esk_smulwb(b, c)); }
+CB_FN i32 esk_smulww(i32 a, i32 b) { return (i32)(((long long)a * (long long)b) >> 16); }
+CB_FN i32 esk_rshift_round(i32 a, int s) { return s == 1 ? (a >> 1) + (a & 1) : ((a >> (s - 1)) + 1) >> 1; }
+CB_FN i32 esk_lin2log(i32 inLin) {
+  const int lz = cb_clz((u32)inLin);
+  const u32 x = (u32)inLin;
+  const int rot = 24 - lz;                                    // silk_ROR32
+  const u32 r = rot == 0 ? x : rot < 0 ? ((x << (-rot)) | (x >> (32 + rot))) : ((x << (32 - rot)) | (x >> rot));
+  const i32 frac_Q7 = (i32)(r & 0x7f);
+  return ((31 - lz) << 7) + esk_smlawb(frac_Q7, frac_Q7 * (128 - frac_Q7), 179);
+}
+CB_FN i32 esk_log2lin(i32 inLog_Q7) {
+  if (inLog_Q7 < 0) return 0;
+  if (inLog_Q7 >= 3967) return 0x7fffffff;
+  i32 out = (i32)(1u << (inLog_Q7 >> 7));
+  const i32 frac_Q7 = inLog_Q7 & 0x7F;
+  const i32 t = esk_smlawb(frac_Q7, (i32)(i16)frac_Q7 * (i32)(i16)(128 - frac_Q7), -174);
+  if (inLog_Q7 < 2048) out = out + ((out * t) >> 7);
+  else out = out + (out >> 7) * t;
+  return out;
+}
+
+// hp_cutoff (opus_encoder.c:325-360) + silk_biquad_alt (silk/biquad_alt.c:41-78): the VOIP application's input
+// high-pass, a second-order section per channel (direct form II transposed); one lane per channel.
+CB_FN void enc_hp_cutoff(const i16* in, i32 cutoff_Hz, i16* out, i32* hp_mem, int len, int channels, int Fs) {
+  const i32 Fc_Q19 = ((i32)(i16)2471 * (i32)(i16)cutoff_Hz) / (i32)(i16)(Fs / 1000);   // 1.5*pi/1000 in Q19
+  const i32 r_Q28 = (1 << 28) - 471 * Fc_Q19;                                               // 0.92 in Q9
+  const i32 B0 = r_Q28, B1 = (i32)((u32)(-r_Q28) << 1), B2 = r_Q28;
+  const i32 r_Q22 = r_Q28 >> 6;
+  const i32 A0 = esk_smulww(r_Q22, esk_smulww(Fc_Q19, Fc_Q19) - (2 << 22));
+  const i32 A1 = esk_smulww(r_Q22, r_Q22);
+  const i32 A0_L = (-A0) & 0x3FFF, A0_U = (-A0) >> 14, A1_L = (-A1) & 0x3FFF, A1_U = (-A1) >> 14;
+  CB_WSYNC();
+#if CB_DEVICE_BUILD
+  const int c = CB_LANE();
+  if (c < channels) {
+#else
+  for (int c = 0; c < channels; c++) {
+#endif
+    i32 S0 = hp_mem[2 * c], S1 = hp_mem[2 * c + 1];
+    CB_NOUNROLL for (int k = 0; k < len; k++) {
+      const i32 inval = in[k * channels + c];
+      const i32 out32_Q14 = (i32)((u32)esk_smlawb(S0, B0, inval) << 2);
+      S0 = S1 + esk_rshift_round(esk_smulwb(out32_Q14, A0_L), 14);
+      S0 = esk_smlawb(S0, out32_Q14, A0_U);
+      S0 = esk_smlawb(S0, B1, inval);
+      S1 = esk_rshift_round(esk_smulwb(out32_Q14, A1_L), 14);
+      S1 = esk_smlawb(S1, out32_Q14, A1_U);
+      S1 = esk_smlawb(S1, B2, inval);
+      i32 v = (out32_Q14 + (1 << 14) - 1) >> 14;
+      v = v > 32767 ? 32767 : (v < -32768 ? -32768 : v);
+      out[k * channels + c] = (i16)v;
+    }
+    hp_mem[2 * c] = S0;
+    hp_mem[2 * c + 1] = S1;
+  }
+  CB_WSYNC();
+}
+
 // compute_stereo_width (opus_encoder.c:861-936); the StereoWidthState lives in the scalars
 CB_FN i32 enc_stereo_width(const i16* pcm, int frame_size, int Fs, OpusEncScalars& o) {
   const int frame_rate = Fs / frame_size;
@@ -294,7 +356,7 @@ CB_FN int enc_decide(OpusEncState* st, OpusEncScalars& o, const i16* pcm, int fr
   if (o.mode != CB_MODE_CELT_ONLY && frame_size < o.Fs / 100) o.mode = CB_MODE_CELT_ONLY;
   if (o.lfe) o.mode = CB_MODE_CELT_ONLY;
   if (max_data_bytes < (frame_rate > 50 ? 12000 : 8000) * frame_size / (o.Fs * 8)) o.mode = CB_MODE_CELT_ONLY;
-  if (o.mode != CB_MODE_CELT_ONLY || o.application == CB_APP_VOIP) return CB_UNIMPLEMENTED;   // SILK / hybrid / VOIP high-pass
+  if (o.mode != CB_MODE_CELT_ONLY) return CB_UNIMPLEMENTED;   // SILK / hybrid are not built
   // prev_mode is 0 or CELT-only here, so no redundancy / mode transition is ever needed.
 
   // automatic bandwidth (opus_encoder.c:1253-1304)
@@ -356,7 +418,15 @@ CB_FN int enc_one_frame(EncWork& w, EncScratch& sc, OpusEncState* st, OpusEncSca
   const int ch = o.channels;
   CB_WSYNC();
   CB_LANE_LOOP(i, total_buffer * ch) pcm_buf[i] = st->delay_buffer[(o.encoder_buffer - total_buffer) * ch + i];
-  enc_dc_reject(pcm, 3, &pcm_buf[total_buffer * ch], o.hp_mem, frame_size, ch, o.Fs);
+  {
+    // variable high-pass smoother (opus_encoder.c:1456-1467): in CELT-only mode its input is the constant minimum
+    // cut-off, so it stays where init / reset put it (60 Hz); kept as the reference computes it
+    const i32 hp_freq_smth1 = esk_lin2log(60) << 8;
+    o.variable_HP_smth2_Q15 = esk_smlawb(o.variable_HP_smth2_Q15, hp_freq_smth1 - o.variable_HP_smth2_Q15, 983);
+    const i32 cutoff_Hz = esk_log2lin(o.variable_HP_smth2_Q15 >> 8);
+    if (o.application == CB_APP_VOIP) enc_hp_cutoff(pcm, cutoff_Hz, &pcm_buf[total_buffer * ch], o.hp_mem, frame_size, ch, o.Fs);
+    else enc_dc_reject(pcm, 3, &pcm_buf[total_buffer * ch], o.hp_mem, frame_size, ch, o.Fs);
+  }
 #if CB_DEVICE_BUILD
   for (int k = 0; k < 4; k++) o.hp_mem[k] = __shfl_sync(0xffffffffu, o.hp_mem[k], k >> 1);
 #endif

@@ -282,9 +282,9 @@ typedef struct OpusEncoderGroup OpusEncoderGroup;
 /* The libopus encoder ABI that Concentus binds (CSharp/Concentus/Native/NativeOpus.cs:105-150,180-225;
  * C prototypes opus-fix/include/opus.h:165-350).  Packets are byte-identical to the reference's
  * fixed-point encoder whenever its mode decision is CELT-only (always for
- * OPUS_APPLICATION_RESTRICTED_LOWDELAY or OPUS_SET_FORCE_MODE(1002); for OPUS_APPLICATION_AUDIO at
- * the rates where the reference picks CELT).  Frames the reference would code with SILK or hybrid,
- * and OPUS_APPLICATION_VOIP, return OPUS_UNIMPLEMENTED.  40 / 60 ms frames are coded as the reference codes
+ * OPUS_APPLICATION_RESTRICTED_LOWDELAY or OPUS_SET_FORCE_MODE(1002); for OPUS_APPLICATION_AUDIO / _VOIP at
+ * the rates and frame sizes where the reference picks CELT).  Frames the reference would code with SILK or
+ * hybrid return OPUS_UNIMPLEMENTED.  40 / 60 ms frames are coded as the reference codes
  * them in CELT-only mode: two or three 20 ms frames in one packet (opus_encoder.c:1362-1438). */
 /* replaces opus_encoder_get_size (src/opus_encoder.c:150-164): size of the host handle only */
 int opus_encoder_get_size(int channels);

@@ -201,3 +201,28 @@ def test_emu_surround_analysis_matches_reference(emu_enc_lib):
                                                   pre_e.ctypes.data, out_e.ctypes.data)
                 assert np.array_equal(out_r, out_e), (channels, fs, ms10, t, out_r[:8], out_e[:8])
                 assert np.array_equal(mem_r, mem_e) and np.array_equal(pre_r, pre_e), (channels, fs, ms10, t)
+
+
+@needs_ref
+def test_emu_voip_application_in_celt_mode_matches_reference(emu_enc_lib):
+    """OPUS_APPLICATION_VOIP when the frame is coded by CELT (forced, or chosen because the rate is high, or
+    because the frame is shorter than 10 ms): the input goes through the VOIP high-pass (hp_cutoff + silk_biquad_alt,
+    opus_encoder.c:325-360) instead of the DC rejection, and the mode thresholds move (voice_est 115, +8000)."""
+    for ch, fs, rate, force, ms10 in [(1, 48000, 64000, 1, 200), (2, 48000, 96000, 1, 200), (1, 16000, 32000, 1, 100),
+                                      (2, 24000, 64000, 1, 200), (1, 48000, 128000, 0, 200), (2, 48000, 200000, 0, 200),
+                                      (1, 48000, 24000, 0, 50), (2, 8000, 48000, 1, 400), (1, 48000, 40000, 0, 25)]:
+        ref, emu = RefEncoder(fs, ch, enc_cases.VOIP), EmuEncoder(emu_enc_lib, fs, ch, enc_cases.VOIP)
+        for e in (ref, emu):
+            assert e.ctl(enc_cases.SET_BITRATE, rate) == 0
+            if force:
+                assert e.ctl(11002, 1002) == 0
+        frame = fs * ms10 // 10000
+        pcm = enc_cases.signal(enc_cases.KINDS[(ch + ms10 + rate // 1000) % len(enc_cases.KINDS)], frame * 10, ch, 21)
+        pcm = (pcm.astype(np.int32) + 900).clip(-32768, 32767).astype(np.int16)       # a DC offset for the high-pass
+        for t in range(10):
+            if t == 5:
+                assert ref.ctl(4028, 0) == emu.ctl(4028, 0) == 0                    # OPUS_RESET_STATE
+            x = pcm[t * frame * ch:(t + 1) * frame * ch]
+            a, b = ref.encode(x, frame, 1275), emu.encode(x, frame, 1275)
+            assert a == b, (ch, fs, rate, force, ms10, t, a[0], b[0])
+            assert a[0] > 0 and (a[1][0] & 0x80), "expected a CELT packet"

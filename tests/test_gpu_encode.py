@@ -233,3 +233,46 @@ def test_long_frames_single_stream_and_mixed_rates():
                     assert enc.final_range == r1
             finally:
                 enc.close()
+
+
+@needs_ref
+def test_voip_application_and_surround_stream_settings_match_reference():
+    """Sixteen streams with the settings that used to be refused: OPUS_APPLICATION_VOIP coded by CELT (forced mode or a
+    rate above the speech threshold: VOIP high-pass, opus_encoder.c:325-360), an LFE stream (OPUS_SET_LFE), and
+    streams with a surround mask (OPUS_SET_ENERGY_MASK, a new one before every frame).  Against the reference."""
+    n, fs, frame, nframes = 16, 48000, 960, 8
+    rng = np.random.RandomState(5)
+    rlib = RefEncoder.lib()
+    lib = cb.load()
+    for ch in (1, 2):
+        encs = [cb.OpusEncoder(fs, ch, enc_cases.VOIP if s % 4 < 2 else enc_cases.AUDIO) for s in range(n)]
+        refs = [RefEncoder(fs, ch, enc_cases.VOIP if s % 4 < 2 else enc_cases.AUDIO) for s in range(n)]
+        try:
+            for s in range(n):
+                kind = s % 4                       # 0 VOIP forced CELT, 1 VOIP high rate, 2 masked, 3 LFE (mono) / masked
+                settings = [(enc_cases.SET_BITRATE, (150000 if kind == 1 else 40000 + 3000 * s) * ch)]
+                if kind != 1:
+                    settings.append((11002, 1002))
+                if kind == 3 and ch == 1:
+                    settings += [(10024, 1), (enc_cases.SET_BITRATE, 4000 + 500 * s)]
+                for req, val in settings:
+                    assert refs[s].ctl(req, val) == 0
+                    encs[s].ctl(req, val)
+            pcms = [enc_cases.signal(enc_cases.KINDS[s % len(enc_cases.KINDS)], frame * nframes, ch, 3100 + s) for s in range(n)]
+            keep = []
+            for t in range(nframes):
+                for s in range(n):
+                    if s % 4 >= 2 and not (s % 4 == 3 and ch == 1):
+                        m = np.ascontiguousarray(rng.randint(-2500, 400, size=21 * ch).astype(np.int16))
+                        keep.append(m)
+                        assert rlib.opus_encoder_ctl(ctypes.c_void_p(refs[s].h), ctypes.c_int(10026), ctypes.c_void_p(m.ctypes.data)) == 0
+                        assert lib.opus_encoder_ctl(ctypes.c_void_p(encs[s]._h), ctypes.c_int(10026), ctypes.c_void_p(m.ctypes.data)) == 0
+                for s in range(n):
+                    x = pcms[s][t * frame * ch:(t + 1) * frame * ch]
+                    rn, rpkt, rrng = refs[s].encode(x, frame, 1275)
+                    pkt = encs[s].encode(x, frame, 1275)
+                    assert len(pkt) == rn and pkt == rpkt, (ch, s, t, len(pkt), rn)
+                    assert encs[s].get(4031) & 0xFFFFFFFF == rrng, (ch, s, t)
+        finally:
+            for e in encs:
+                e.close()
