@@ -725,7 +725,9 @@ CB_FN void dec_all_bands3(EntWork& w, RangeDec& rd, int start, int end, int C, i
       full = wr.jobs + wr.tape + 4 * L + 2 > CB_B3_BUF || wr.bits + 10 * L + 4 > 32 * CB_B3_BITWORDS;
     }
     if (i > first && (i == end || full || i == CB_NBANDS - 1)) {
+      CB_ENT_PHASE(w);                   // parse walk -> pulses
       b3_run_jobs(w, wr.jobs);
+      CB_ENT_PHASE(w);                   // pulses -> rebuild walk
       B3Cur rdc;
       rdc.jobs = rdc.tape = rdc.bits = 0;
       CB_NOUNROLL for (int r = first; r < i; r++)
@@ -735,6 +737,7 @@ CB_FN void dec_all_bands3(EntWork& w, RangeDec& rd, int start, int end, int C, i
       CB_WSYNC();
       CB_LANE_LOOP(j, CB_B3_BITWORDS) w.b3_bits[j] = 0;
       CB_WSYNC();
+      CB_ENT_PHASE(w);                   // rebuild walk -> parse walk (or the frame's tail)
     }
     if (i < end)
       b3_one_band<false>(w, rd, wr, cxp, ps, rs, i, start, end, C, Nfrm, B, spread, intensity, total_bits, LM, codedBands);

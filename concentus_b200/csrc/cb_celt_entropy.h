@@ -67,7 +67,21 @@ struct alignas(16) EntWork {
                                  //   split angles and other 16-bit notes of the parse walk from the back
   u32 b3_bits[16];               //   one or two bits per node of the walk
   RangeDec rd;                   // coder registers; in shared memory so the rd_* routines can be real calls
+  i32 nsync, sync_on;            // stage rendezvous (CB_ENT_PHASE): barriers passed so far; on only in kernel A
 };
+
+// Stage rendezvous of kernel A.  The warps of a CTA pass the stages of a frame together (header + allocation,
+// then per tape flush: parse walk, pulse decode, rebuild walk), so that the SM's instruction caches hold one
+// stage's code at a time instead of every stage's.  No data crosses warps: the barrier is only pacing.  Every
+// warp of the CTA must pass CB_ENT_PHASES barriers per launch; a warp that needs fewer (fewer flushes, a frame
+// that is skipped or concealed) makes up the rest in the kernel wrapper.  Off (sync_on = 0) wherever the band
+// decoder runs outside kernel A (the general kernel, the host build).
+#define CB_ENT_PHASES (2 + 3 * (CB_NBANDS + 1))
+#if CB_DEVICE_BUILD
+#define CB_ENT_PHASE(w) do { if ((w).sync_on) { __syncthreads(); if (CB_LANE() == 0) (w).nsync++; __syncwarp(); } } while (0)
+#else
+#define CB_ENT_PHASE(w) ((void)0)
+#endif
 
 struct BandCtx {
   int i, intensity, spread, tf_change;
@@ -883,6 +897,7 @@ CB_FN int celt_entropy_decode(EntWork& w, CeltDecState* stg, FrameSide* side, co
   dec_fine_energy(w, rd, start, end, C);
 
   u32 seed = stg->rng;
+  CB_ENT_PHASE(w);                                            // header, energies and allocation done
   dec_all_bands3(w, rd, start, end, C, N, shortBlocks, spread_decision, dual_stereo, intensity,
                 len * (8 << CB_BITRES) - anti_collapse_rsv, balance, LM, codedBands, seed);
   int anti_collapse_on = 0;

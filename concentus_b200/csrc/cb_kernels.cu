@@ -13,7 +13,8 @@
 #include "cb_decode_pass.h"
 #include "cb_kernels.h"
 
-#define A_WARPS 4
+#define A_WARPS 4           // kernel A, small batches: 4 warps per CTA, 7 CTAs per SM
+#define A_WARPS_SM 28       // kernel A, batches that fill the GPU: one CTA spans the SM (stage rendezvous, CB_ENT_PHASE)
 #define B_WARPS 4
 
 __global__ void opus_plan_kernel(OpusDecState* const* states, const u8* data, const i32* offs,
@@ -28,19 +29,25 @@ __global__ void opus_plan_kernel(OpusDecState* const* states, const u8* data, co
 }
 
 template <bool HYB>
-__global__ void __launch_bounds__(A_WARPS * 32, 7)
+__global__ void __launch_bounds__(A_WARPS_SM * 32, 1)
 celt_entropy_kernel(OpusDecState* const* states, const u8* data, StreamPlan* plans, FrameSide* sides,
                     i32* ret, int n, int pass, int per_warp_bytes) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int warp = threadIdx.x >> 5;
-  const int s = blockIdx.x * A_WARPS + warp;
-  if (s >= n) return;
+  const int s = blockIdx.x * (blockDim.x >> 5) + warp;
   EntWork& w = *reinterpret_cast<EntWork*>(smem + (size_t)warp * per_warp_bytes);
-  u8* pkt = per_warp_bytes > (int)sizeof(EntWork) ? reinterpret_cast<u8*>(&w) + sizeof(EntWork) : nullptr;
-  OpusDecState* st = states[s];
-  StreamPlan* pl = &plans[s];
-  FrameSide* side = &sides[s];
-  decode_entropy_pass<HYB>(w, pkt, st, pl, side, data, &ret[s], pass);
+  if (CB_LANE() == 0) { w.nsync = 0; w.sync_on = 1; }
+  __syncwarp();
+  if (s < n) {
+    u8* pkt = per_warp_bytes > (int)sizeof(EntWork) ? reinterpret_cast<u8*>(&w) + sizeof(EntWork) : nullptr;
+    OpusDecState* st = states[s];
+    StreamPlan* pl = &plans[s];
+    FrameSide* side = &sides[s];
+    decode_entropy_pass<HYB>(w, pkt, st, pl, side, data, &ret[s], pass);
+  }
+  // stage rendezvous: every warp of the CTA passes the same number of barriers (cb_celt_entropy.h)
+  __syncwarp();
+  for (int k = w.nsync; k < CB_ENT_PHASES; k++) __syncthreads();
 }
 
 __global__ void __launch_bounds__(B_WARPS * 32, 7)
@@ -106,9 +113,12 @@ static int g_attr_done[64];
 extern "C" size_t cbk_entropy_smem_per_warp(int max_payload) {
   const size_t work = (sizeof(EntWork) + 15) & ~(size_t)15;
   const size_t staged = work + (size_t)((max_payload + 15) & ~15);
-  const size_t limit = ((227 * 1024) / 7 - 1024) / A_WARPS;
+  const size_t limit = ((227 * 1024) / 7 - 1024) / A_WARPS;       // the same 28 warps per SM in either CTA shape
   return staged <= limit ? staged : work;
 }
+// Warps per CTA of kernel A: once the batch gives every SM a full set of warps, one CTA spans the SM so that
+// its 28 warps can pass the frame's stages together; smaller batches keep small CTAs and spread over more SMs.
+static int entropy_cta_warps(int n) { return n >= 148 * A_WARPS_SM / 2 ? A_WARPS_SM : A_WARPS; }
 
 extern "C" int cbk_launch_plan(OpusDecState* const* d_states, const u8* d_data, const i32* d_off,
                                const i32* d_len, const i32* d_fec, int frame_size, StreamPlan* d_plans,
@@ -141,13 +151,14 @@ extern "C" int cbk_launch_entropy(OpusDecState* const* d_states, const u8* d_dat
   int rc = ensure_attrs();
   if (rc) return rc;
   const int per_warp = (int)cbk_entropy_smem_per_warp(max_payload);
-  const size_t smemA = (size_t)per_warp * A_WARPS;
-  celt_entropy_kernel<false><<<(n + A_WARPS - 1) / A_WARPS, A_WARPS * 32, smemA, stream>>>(
+  const int aw = entropy_cta_warps(n);
+  const size_t smemA = (size_t)per_warp * aw;
+  celt_entropy_kernel<false><<<(n + aw - 1) / aw, aw * 32, smemA, stream>>>(
       d_states, d_data, d_plans, d_sides, d_ret, n, pass, per_warp);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return (int)e;
   // CELT layer of hybrid frames: its warps leave at once in a batch without hybrid streams
-  celt_entropy_kernel<true><<<(n + A_WARPS - 1) / A_WARPS, A_WARPS * 32, smemA, stream>>>(
+  celt_entropy_kernel<true><<<(n + aw - 1) / aw, aw * 32, smemA, stream>>>(
       d_states, d_data, d_plans, d_sides, d_ret, n, pass, per_warp);
   return (int)cudaGetLastError();
 }

@@ -65,6 +65,9 @@ CB_FN_NOINLINE void gen_celt_decode(GenWork& g, OpusDecState* st, FrameSide* sid
   EntFrameCfg cfg;
   cfg.LM = LM; cfg.C = C; cfg.start = start; cfg.end = end; cfg.accum = accum; cfg.rd0 = rd0;
   u32 fr = 0;
+  CB_WSYNC();
+  CB_IF_LANE0 g.ew.sync_on = 0;                                // no stage rendezvous outside kernel A
+  CB_WSYNC();
   celt_entropy_decode(g.ew, celt, side, g.pkt, len, cfg, &fr);
   if (final_range) *final_range = fr;
   CB_WSYNC();
