@@ -17,8 +17,6 @@
 // cannot take another band, the bands parsed so far are finished (phases 2 + 3) and parsing resumes.
 #pragma once
 
-#define CB_B3_BUF 176           // 16-bit entries in flight: pending leaves from the front, tape notes from the back
-#define CB_B3_BITWORDS 16       // 512 node bits in flight
 #define CB_B3_MIN_N 6           // a deferred leaf keeps its 6-word record in its own X slot
 
 struct B3Cur {                  // cursors of the tape: written by PARSE, read by REBUILD (uniform registers)
@@ -723,11 +721,20 @@ CB_FN void dec_all_bands3(EntWork& w, RangeDec& rd, int start, int end, int C, i
     if (i < end) {
       const int L = b3_band_leaves(M * (ebands(i + 1) - ebands(i)), LM);
       full = wr.jobs + wr.tape + 4 * L + 2 > CB_B3_BUF || wr.bits + 10 * L + 4 > 32 * CB_B3_BITWORDS;
+#ifdef B3_PROBE
+      if (i != CB_NBANDS - 1) { if (wr.jobs + wr.tape + 4 * L + 2 > g_b3_needbuf) g_b3_needbuf = wr.jobs + wr.tape + 4 * L + 2;
+        if (wr.bits + 10 * L + 4 > g_b3_needbits) g_b3_needbits = wr.bits + 10 * L + 4; }
+#endif
     }
     if (i > first && (i == end || full || i == CB_NBANDS - 1)) {
+#ifdef B3_PROBE
+      g_b3_flush++; if (full && i != end && i != CB_NBANDS - 1) g_b3_full++;
+      if (wr.jobs + wr.tape > g_b3_maxbuf) g_b3_maxbuf = wr.jobs + wr.tape;
+      if (wr.bits > g_b3_maxbits) g_b3_maxbits = wr.bits;
+#endif
       CB_ENT_PHASE(w);                   // parse walk -> pulses
       b3_run_jobs(w, wr.jobs);
-      CB_ENT_PHASE(w);                   // pulses -> rebuild walk
+      // (pulses and the rebuild walk share a stage: a rendezvous between them cost more in waiting than it saved)
       B3Cur rdc;
       rdc.jobs = rdc.tape = rdc.bits = 0;
       CB_NOUNROLL for (int r = first; r < i; r++)

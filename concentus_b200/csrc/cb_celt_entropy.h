@@ -41,6 +41,14 @@ CB_UTABLE u8 ct_bit_deinterleave[16] = {0x00, 0x03, 0x0C, 0x0F, 0x30, 0x33, 0x3C
 
 struct Split { int inv, imid, iside, delta, itheta, qalloc, b, fill; };   // b/fill: updated in/out values
 
+// Three-phase band decoder (cb_celt_bands3.h): what one parse run may leave pending before a flush
+#ifndef CB_B3_BUF
+// (sized so that a 20 ms stereo frame of up to ~128 kbit/s parses bands 0..19 in one run: the flush count is then
+// the same for every stream and the stage rendezvous of kernel A lines up; larger frames flush in between)
+#define CB_B3_BUF 224           // 16-bit entries in flight: pending leaves from the front, tape notes from the back
+#define CB_B3_BITWORDS 20       // 640 node bits in flight
+#endif
+
 // One level of the split recursion (quant_partition), kept in shared memory.
 struct PartFrame {                // positions are 16-bit word offsets from the start of EntWork (0xFFFF: none)
   i32 b, mbits, sbits, rebal0;
@@ -63,9 +71,9 @@ struct alignas(16) EntWork {
   u8 collapse[2 * CB_NBANDS];
   PartFrame stack[5];
   Split sp_store;                // result record of dec_theta
-  u16 b3_buf[176];               // cb_celt_bands3.h: pending leaves (X offset, then collapse mask) from the front,
+  u16 b3_buf[CB_B3_BUF];               // cb_celt_bands3.h: pending leaves (X offset, then collapse mask) from the front,
                                  //   split angles and other 16-bit notes of the parse walk from the back
-  u32 b3_bits[16];               //   one or two bits per node of the walk
+  u32 b3_bits[CB_B3_BITWORDS];               //   one or two bits per node of the walk
   RangeDec rd;                   // coder registers; in shared memory so the rd_* routines can be real calls
   i32 nsync, sync_on;            // stage rendezvous (CB_ENT_PHASE): barriers passed so far; on only in kernel A
 };

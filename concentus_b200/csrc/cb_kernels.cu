@@ -110,10 +110,11 @@ static int g_attr_done[64];
 
 // Shared memory of one warp of kernel A: the work area plus, when it still leaves room for 7 CTAs per SM
 // (227 KB, 1 KB reserved per CTA), a staging area for the packet; larger packets are read from global memory.
-extern "C" size_t cbk_entropy_smem_per_warp(int max_payload) {
+extern "C" size_t cbk_entropy_smem_per_warp(int max_payload, int cta_warps) {
   const size_t work = (sizeof(EntWork) + 15) & ~(size_t)15;
   const size_t staged = work + (size_t)((max_payload + 15) & ~15);
-  const size_t limit = ((227 * 1024) / 7 - 1024) / A_WARPS;       // the same 28 warps per SM in either CTA shape
+  const int ctas = A_WARPS_SM / cta_warps;                        // 28 warps per SM in either CTA shape
+  const size_t limit = (((227 * 1024) / ctas - 1024) / cta_warps) & ~(size_t)15;
   return staged <= limit ? staged : work;
 }
 // Warps per CTA of kernel A: once the batch gives every SM a full set of warps, one CTA spans the SM so that
@@ -150,8 +151,8 @@ extern "C" int cbk_launch_entropy(OpusDecState* const* d_states, const u8* d_dat
   if (n <= 0) return 0;
   int rc = ensure_attrs();
   if (rc) return rc;
-  const int per_warp = (int)cbk_entropy_smem_per_warp(max_payload);
   const int aw = entropy_cta_warps(n);
+  const int per_warp = (int)cbk_entropy_smem_per_warp(max_payload, aw);
   const size_t smemA = (size_t)per_warp * aw;
   celt_entropy_kernel<false><<<(n + aw - 1) / aw, aw * 32, smemA, stream>>>(
       d_states, d_data, d_plans, d_sides, d_ret, n, pass, per_warp);

@@ -5,7 +5,7 @@
 #include "cb_state.h"
 
 extern "C" {
-size_t cbk_entropy_smem_per_warp(int max_payload);
+size_t cbk_entropy_smem_per_warp(int max_payload, int cta_warps);
 int cbk_launch_plan(OpusDecState* const* d_states, const u8* d_data, const i32* d_off, const i32* d_len,
                     const i32* d_fec, int frame_size, StreamPlan* d_plans, i32* d_ret, int n,
                     cudaStream_t stream);
