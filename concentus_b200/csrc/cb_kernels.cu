@@ -36,7 +36,11 @@ celt_entropy_kernel(OpusDecState* const* states, const u8* data, StreamPlan* pla
   const int warp = threadIdx.x >> 5;
   const int s = blockIdx.x * (blockDim.x >> 5) + warp;
   EntWork& w = *reinterpret_cast<EntWork*>(smem + (size_t)warp * per_warp_bytes);
-  if (CB_LANE() == 0) { w.nsync = 0; w.sync_on = 1; }
+  // a CTA none of whose streams has a frame for this instance (the hybrid instance in a CELT batch, both in a SILK
+  // batch) skips the rendezvous altogether
+  const int route = s < n ? plans[s].route : -1;
+  const int paced = __syncthreads_or(HYB ? route == CB_ROUTE_HYBRID : route == CB_ROUTE_CELT);
+  if (CB_LANE() == 0) { w.nsync = 0; w.sync_on = paced; }
   __syncwarp();
   if (s < n) {
     u8* pkt = per_warp_bytes > (int)sizeof(EntWork) ? reinterpret_cast<u8*>(&w) + sizeof(EntWork) : nullptr;
@@ -47,7 +51,8 @@ celt_entropy_kernel(OpusDecState* const* states, const u8* data, StreamPlan* pla
   }
   // stage rendezvous: every warp of the CTA passes the same number of barriers (cb_celt_entropy.h)
   __syncwarp();
-  for (int k = w.nsync; k < CB_ENT_PHASES; k++) __syncthreads();
+  if (paced)
+    for (int k = w.nsync; k < CB_ENT_PHASES; k++) __syncthreads();
 }
 
 __global__ void __launch_bounds__(B_WARPS * 32, 7)
