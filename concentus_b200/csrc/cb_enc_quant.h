@@ -439,6 +439,7 @@ CB_FN void enc_all_bands(EncWork& w, RangeEnc& enc, int start, int end, int C, i
   cx.intensity = intensity;
   cx.spread = spread;
   CB_NOUNROLL for (int i = start; i < end; i++) {
+    CB_ENC_PHASE(w);                   // the CTA's warps code band i together (same code in the instruction caches)
     cx.i = i;
     i16* X = w.X + M * ebands(i);
     i16* Y = C == 2 ? w.X + Nfrm + M * ebands(i) : nullptr;
