@@ -6,8 +6,10 @@
 //
 // A and B are launched once per frame index ("pass") of the packets in the batch; single-frame
 // packets (the normal case) need one pass.  All kernels are integer / latency bound (no tensor
-// cores): the design levers are warps resident per SM (7 CTAs x 4 warps = 28 warps, sized from the
-// 227 KB shared memory) and keeping every per-stream array in shared memory.
+// cores): the design levers are warps resident per SM (28, sized from the 227 KB shared memory), keeping
+// every per-stream array in shared memory, and -- for kernel A on a batch that fills the GPU -- one CTA per SM
+// whose 28 warps pass the stages of a frame together, so that the instruction caches hold one stage at a time
+// (CB_ENT_PHASE, cb_celt_entropy.h).
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "cb_decode_pass.h"
