@@ -199,15 +199,6 @@ def main():
     import concentus_b200 as cb
 
     torch.cuda.set_device(local_rank)
-    if world > 1 and not os.environ.get("BENCH_NO_AFFINITY"):
-        # one process per GPU: run on (and page-lock host buffers from) the CPUs next to this rank's GPU, so that the
-        # PCM copy-out of eight ranks does not cross the socket interconnect
-        try:
-            import pynvml
-            pynvml.nvmlInit()
-            pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(local_rank))
-        except Exception as e:      # affinity is an optimisation only
-            sys.stderr.write("[bench] cpu affinity not set: %r\n" % (e,))
     if world > 1:
         dist.init_process_group(backend="nccl", device_id=torch.device("cuda", local_rank))
     lib = cb.load()
