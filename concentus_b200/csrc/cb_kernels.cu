@@ -124,9 +124,17 @@ extern "C" size_t cbk_entropy_smem_per_warp(int max_payload, int cta_warps) {
   const size_t limit = (((227 * 1024) / ctas - 1024) / cta_warps) & ~(size_t)15;
   return staged <= limit ? staged : work;
 }
-// Warps per CTA of kernel A: once the batch gives every SM a full set of warps, one CTA spans the SM so that
-// its 28 warps can pass the frame's stages together; smaller batches keep small CTAs and spread over more SMs.
-static int entropy_cta_warps(int n) { return n >= 148 * A_WARPS_SM / 2 ? A_WARPS_SM : A_WARPS; }
+// Warps per CTA of kernel A.  An SM holds 28 of its warps (registers, shared memory).  A batch that gives every SM
+// at least a few warps runs as CTAs that each take an equal share of it -- ceil(n / 148) warps per CTA, one CTA
+// per SM, or the same over two, three ... waves when the batch is larger than 148 x 28 -- so that every SM is busy
+// for the whole kernel and the warps of an SM pass the frame's stages together (CB_ENT_PHASE).  Smaller batches
+// keep 4-warp CTAs and spread over the SMs.
+static int entropy_cta_warps(int n) {
+  if (n < 148 * (A_WARPS + 1)) return A_WARPS;
+  const int waves = (n + 148 * A_WARPS_SM - 1) / (148 * A_WARPS_SM);
+  const int w = (n + 148 * waves - 1) / (148 * waves);
+  return w > A_WARPS_SM ? A_WARPS_SM : w;
+}
 
 extern "C" int cbk_launch_plan(OpusDecState* const* d_states, const u8* d_data, const i32* d_off,
                                const i32* d_len, const i32* d_fec, int frame_size, StreamPlan* d_plans,
