@@ -19,7 +19,7 @@ opus_encode_kernel(OpusEncState* const* states, EncScratch* scratch, const i16* 
                    u8* data, i32 data_stride, int max_data_bytes, i32* out_len, int n, int phases) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int warp = threadIdx.x >> 5;
-  const int s = blockIdx.x * E_WARPS + warp;
+  const int s = blockIdx.x * (blockDim.x >> 5) + warp;
   EncWork& w = *reinterpret_cast<EncWork*>(smem + (size_t)warp * sizeof(EncWork));
   if ((threadIdx.x & 31) == 0) w.nsync = 0;
   __syncwarp();
@@ -53,13 +53,20 @@ int cbk_launch_encode(OpusEncState* const* d_states, void* d_scratch, const i16*
     if (e != cudaSuccess) return (int)e;
     attr_set[dev] = true;
   }
-  const int blocks = (n + E_WARPS - 1) / E_WARPS;
+  // CTA shape: an equal share of the batch for every SM (ceil(n / 148) warps per CTA, at most 28 = what an SM
+  // holds; the same over two or more waves for larger batches), so that a small batch still uses the whole GPU
+  const int waves = (n + 148 * E_WARPS - 1) / (148 * E_WARPS);
+  int ew = (n + 148 * waves - 1) / (148 * waves);
+  if (ew > E_WARPS) ew = E_WARPS;
+  if (ew < 1) ew = 1;
+  const int blocks = (n + ew - 1) / ew;
+  const size_t smem_l = sizeof(EncWork) * ew;
   if (max_subframes > 1 || general)
-    opus_encode_kernel<true><<<blocks, E_WARPS * 32, smem, stream>>>(d_states, (EncScratch*)d_scratch, d_pcm, pcm_stride,
+    opus_encode_kernel<true><<<blocks, ew * 32, smem_l, stream>>>(d_states, (EncScratch*)d_scratch, d_pcm, pcm_stride,
                                                                     frame_size, d_data, data_stride, max_data_bytes, d_len, n,
                                                                     CB_ENC_PHASES * max_subframes);
   else
-    opus_encode_kernel<false><<<blocks, E_WARPS * 32, smem, stream>>>(d_states, (EncScratch*)d_scratch, d_pcm, pcm_stride,
+    opus_encode_kernel<false><<<blocks, ew * 32, smem_l, stream>>>(d_states, (EncScratch*)d_scratch, d_pcm, pcm_stride,
                                                                      frame_size, d_data, data_stride, max_data_bytes, d_len, n,
                                                                      CB_ENC_PHASES);
   return (int)cudaGetLastError();
