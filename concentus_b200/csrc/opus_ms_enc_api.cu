@@ -29,7 +29,6 @@ extern "C" cudaStream_t opusb_internal_stream(int* err);
 extern "C" void opusb_internal_count_launches(int n);
 extern "C" int opusb_internal_encoder_mask_slots(OpusEncoder* st, int side, opus_int16** mask, opus_int32** has_mask);
 
-#define OPUS_SET_LFE_REQUEST 10024          // celt/celt.h:113
 
 struct OpusMSEncoder {
   int magic;

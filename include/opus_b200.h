@@ -275,6 +275,9 @@ int opus_decoder_get_final_range_batch(OpusDecoder *const *st, int n, opus_uint3
 #define OPUS_SET_PREDICTION_DISABLED_REQUEST 4042
 #define OPUS_GET_PREDICTION_DISABLED_REQUEST 4043
 #define OPUS_SET_FORCE_MODE_REQUEST 11002 /* src/opus_private.h:79; 1002 = CELT-only */
+#define OPUS_SET_LFE_REQUEST 10024         /* celt/celt.h:113: this encoder codes an LFE channel */
+#define OPUS_SET_ENERGY_MASK_REQUEST 10026 /* celt/celt.h:116: const opus_int16[21 * channels] surround masks (Q10),
+                                             copied at the call (the reference keeps the pointer); NULL clears */
 
 typedef struct OpusEncoder OpusEncoder;
 typedef struct OpusEncoderGroup OpusEncoderGroup;
