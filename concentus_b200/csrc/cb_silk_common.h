@@ -236,6 +236,12 @@ struct SilkCNG {                  // silk_CNG_struct
   i16 CNG_smth_NLSF_Q15[SK_MAX_ORDER];
   i32 CNG_synth_state[SK_MAX_ORDER];
   i32 CNG_smth_Gain_Q16, rand_seed, fs_kHz;
+  // CNG_exc_buf_Q14 is kept as a ring of four subframe slots while frames have four subframes: the reference's
+  // "shift everything down one subframe" (CNG.c:122) is then a change of ring_head instead of a 1 KB move per
+  // inactive frame.  Logical subframe k lives in slot (ring_head + k) & 3 of ring_sub samples; ring_head = 0 is
+  // the reference's layout, and anything that does not fit the ring (two-subframe frames, a rate change) first
+  // puts the buffer back in that layout (sk_cng_linearise).
+  i32 ring_head, ring_sub;
 };
 struct alignas(16) SilkChannel {  // silk_decoder_state
   alignas(16) i32 exc_Q14[SK_MAX_FRAME];

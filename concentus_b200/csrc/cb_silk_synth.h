@@ -430,10 +430,21 @@ CB_FN void sk_cng_reset(SilkChannel& ps) {                        // CNG.c:63-79
   ps.sCNG.CNG_smth_Gain_Q16 = 0;
   ps.sCNG.rand_seed = 3176576;
 }
+// Put CNG_exc_buf_Q14 back into the reference's linear layout (rotate left by ring_head slots, three reversals).
+CB_FN void sk_cng_linearise(SilkCNG& cng) {
+  if (cng.ring_head == 0) return;
+  i32* b = cng.CNG_exc_buf_Q14;
+  const int sl = cng.ring_sub, n = 4 * sl, k = cng.ring_head * sl;
+  for (int lo = 0, hi = k - 1; lo < hi; lo++, hi--) { const i32 t = b[lo]; b[lo] = b[hi]; b[hi] = t; }
+  for (int lo = k, hi = n - 1; lo < hi; lo++, hi--) { const i32 t = b[lo]; b[lo] = b[hi]; b[hi] = t; }
+  for (int lo = 0, hi = n - 1; lo < hi; lo++, hi--) { const i32 t = b[lo]; b[lo] = b[hi]; b[hi] = t; }
+  cng.ring_head = 0;
+}
 CB_FN void sk_cng(SilkChannel& ps, SilkDecControl& ctrl, i16* frame, int length, SilkWork& w) {   // CNG.c:82-181
   SilkCNG& cng = ps.sCNG;
   i16 A_Q12[SK_MAX_ORDER];
   if (ps.fs_kHz != cng.fs_kHz) {
+    sk_cng_linearise(cng);
     sk_cng_reset(ps);
     cng.fs_kHz = ps.fs_kHz;
   }
@@ -446,8 +457,19 @@ CB_FN void sk_cng(SilkChannel& ps, SilkDecControl& ctrl, i16* frame, int length,
     for (int i = 0; i < ps.nb_subfr; i++) {
       if (ctrl.Gains_Q16[i] > max_Gain_Q16) { max_Gain_Q16 = ctrl.Gains_Q16[i]; subfr = i; }
     }
-    sk_copy_i32_down(&cng.CNG_exc_buf_Q14[ps.subfr_length], cng.CNG_exc_buf_Q14, (ps.nb_subfr - 1) * ps.subfr_length);
-    sk_copy_i32(cng.CNG_exc_buf_Q14, &ps.exc_Q14[subfr * ps.subfr_length], ps.subfr_length);
+    if (ps.nb_subfr == SK_MAX_NB_SUBFR) {
+      // CNG.c:122-123 on the ring: the new subframe takes the slot of the oldest, which becomes logical slot 0
+      if (cng.ring_sub != ps.subfr_length) {
+        sk_cng_linearise(cng);
+        cng.ring_sub = ps.subfr_length;
+      }
+      cng.ring_head = (cng.ring_head + 3) & 3;
+      sk_copy_i32(&cng.CNG_exc_buf_Q14[cng.ring_head * ps.subfr_length], &ps.exc_Q14[subfr * ps.subfr_length], ps.subfr_length);
+    } else {
+      sk_cng_linearise(cng);
+      sk_copy_i32_down(&cng.CNG_exc_buf_Q14[ps.subfr_length], cng.CNG_exc_buf_Q14, (ps.nb_subfr - 1) * ps.subfr_length);
+      sk_copy_i32(cng.CNG_exc_buf_Q14, &ps.exc_Q14[subfr * ps.subfr_length], ps.subfr_length);
+    }
     for (int i = 0; i < ps.nb_subfr; i++)
       cng.CNG_smth_Gain_Q16 += sk_smulwb(ctrl.Gains_Q16[i] - cng.CNG_smth_Gain_Q16, 4634);
   }
@@ -467,9 +489,14 @@ CB_FN void sk_cng(SilkChannel& ps, SilkDecControl& ctrl, i16* frame, int length,
       int exc_mask = 255;
       while (exc_mask > length) exc_mask >>= 1;
       i32 seed = cng.rand_seed;
+      const int ring_head = cng.ring_head, ring_sub = cng.ring_sub;
       for (int i = 0; i < length; i++) {
         seed = sk_rand(seed);
-        const int idx = (seed >> 24) & exc_mask;
+        int idx = (seed >> 24) & exc_mask;
+        if (ring_head) {                                          // logical -> ring position
+          const int slot = (idx >= ring_sub) + (idx >= 2 * ring_sub) + (idx >= 3 * ring_sub);
+          idx = (((ring_head + slot) & 3) - slot) * ring_sub + idx;
+        }
         CNG_sig_Q10[SK_MAX_ORDER + i] = (i16)sk_sat16(sk_smulww(cng.CNG_exc_buf_Q14[idx], gain_Q16 >> 4));
       }
       cng.rand_seed = seed;
