@@ -386,8 +386,9 @@ CB_FN_NOINLINE void enc_band(EncWork& w, EncBandCtx& cx, RangeEnc& enc, i16* X, 
 
 // quant_band_stereo (bands.c:1176-1335, encoder side)
 CB_FN void enc_band_stereo(EncWork& w, EncBandCtx& cx, RangeEnc& enc, i16* X, i16* Y, int N, int b, int B, int LM) {
-  if (N == 1) { enc_band_n1(cx, enc, X, Y); return; }
+  if (N == 1) { CB_ENC_PHASE(w); enc_band_n1(cx, enc, X, Y); return; }
   enc_theta(w, enc, cx.i, cx.intensity, cx.remaining_bits, cx.bandE, X, Y, N, b, B, LM, 1);
+  CB_ENC_PHASE(w);                     // stereo angle coded: the CTA's warps start the band's two halves together
   const EncSplit s = w.sp_store;
   b = s.b;
   const int itheta = s.itheta;
@@ -456,11 +457,13 @@ CB_FN void enc_all_bands(EncWork& w, RangeEnc& enc, int start, int end, int C, i
     cx.tf_change = w.tf_res[i];
     if (dual_stereo && i == intensity) dual_stereo = 0;
     if (dual_stereo) {
+      CB_ENC_PHASE(w);
       enc_band(w, cx, enc, X, N, b / 2, B, LM);
       enc_band(w, cx, enc, Y, N, b / 2, B, LM);
     } else if (Y != nullptr) {
       enc_band_stereo(w, cx, enc, X, Y, N, b, B, LM);
     } else {
+      CB_ENC_PHASE(w);
       enc_band(w, cx, enc, X, N, b, B, LM);
     }
     balance += w.pulses[i] + tell;

@@ -164,7 +164,7 @@ struct alignas(16) EncScratch {
 // instructions and instruction-fetch stalls dominated when every warp sat in a different stage.
 // No data crosses warps; the barrier is only pacing.  Every warp must reach CB_ENC_PHASES barriers
 // per frame: a warp that leaves early (error, silence) makes up the remainder in the kernel wrapper.
-#define CB_ENC_PHASES (9 + CB_NBANDS)   // nine stage boundaries + one per band of the residual loop
+#define CB_ENC_PHASES (9 + 2 * CB_NBANDS)   // nine stage boundaries + two per band of the residual loop
 #if CB_DEVICE_BUILD
 #define CB_ENC_PHASE(w) do { __syncthreads(); if (CB_LANE() == 0) (w).nsync++; __syncwarp(); } while (0)
 #else
