@@ -185,3 +185,32 @@ def test_creation_errors():
     assert err.value == cb.OPUS_BAD_ARG
     assert not ours.opus_multistream_encoder_create(48000, 2, 1, 2, bad, LOWDELAY, ctypes.byref(err))
     assert err.value == cb.OPUS_BAD_ARG
+
+
+def test_surround_float_entry_equals_int16_entry():
+    """opus_multistream_encode_float on a FIXED_POINT build is FLOAT2INT16 followed by the int16 path
+    (opus_multistream_encoder.c:919-936, 1006-1022): two 5.1 surround encoders fed the same audio through the two
+    entry points produce the same packets."""
+    ours = cb.load()
+    hs = []
+    for _ in range(2):
+        streams, coupled, err = ctypes.c_int(0), ctypes.c_int(0), ctypes.c_int(0)
+        mapping = (ctypes.c_ubyte * 8)()
+        h = ours.opus_multistream_surround_encoder_create(48000, 6, 1, ctypes.byref(streams), ctypes.byref(coupled),
+                                                          mapping, LOWDELAY, ctypes.byref(err))
+        assert h and err.value == 0 and (streams.value, coupled.value) == (4, 2)
+        hs.append(h)
+    try:
+        for h in hs:
+            assert ours.opus_multistream_encoder_ctl(ctypes.c_void_p(h), enc_cases.SET_BITRATE, ctypes.c_int32(256000)) == 0
+        pcm = surround_pcm(6, 6, 960, 48000)
+        for t in range(6):
+            x = np.ascontiguousarray(pcm[t * 960:(t + 1) * 960])
+            xf = np.ascontiguousarray(x.astype(np.float32) / 32768.0)
+            o1, o2 = ctypes.create_string_buffer(4000), ctypes.create_string_buffer(4000)
+            n1 = ours.opus_multistream_encode(hs[0], x.ctypes.data, 960, o1, 4000)
+            n2 = ours.opus_multistream_encode_float(hs[1], xf.ctypes.data, 960, o2, 4000)
+            assert n1 == n2 and n1 > 0 and o1.raw[:n1] == o2.raw[:n2], t
+    finally:
+        for h in hs:
+            ours.opus_multistream_encoder_destroy(h)
