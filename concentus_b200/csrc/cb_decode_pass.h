@@ -6,14 +6,15 @@
 #include "cb_celt_plc.h"
 #include "cb_opus_plan.h"
 
-// Kernel A, one stream, one pass.  `pkt` = per-warp staging area for the payload bytes, or nullptr: the range
+// Kernel A, one stream, one pass.  `pkt` = per-warp staging area for the payload bytes (`pkt_cap` bytes; a longer
+// payload -- the device-resident entries cannot check the caller's max_packet_bytes -- is read in place), or nullptr: the range
 // decoder then reads the packet where it lies in global memory (a few dozen dependent byte loads per frame are
 // nothing next to the frame's decode time; staging large packets would cost a resident CTA per SM).
 // Two instances: HYB = false takes the CELT-only frames (start band 0, fresh range decoder: the constants
 // fold into the decoder), HYB = true the CELT layer of hybrid frames whose SILK layer the SILK kernel has
 // already written to the PCM row (bands 17.., coder state continued, output accumulated).
 template <bool HYB>
-CB_FN void decode_entropy_pass(EntWork& w, u8* pkt, OpusDecState* st, StreamPlan* pl, FrameSide* side,
+CB_FN void decode_entropy_pass(EntWork& w, u8* pkt, int pkt_cap, OpusDecState* st, StreamPlan* pl, FrameSide* side,
                                const u8* data, i32* ret_slot, int pass) {
   const int kind = pl->kind;
   const int route = pl->route;                       // decided by the SILK kernel at the start of this pass
@@ -64,7 +65,7 @@ CB_FN void decode_entropy_pass(EntWork& w, u8* pkt, OpusDecState* st, StreamPlan
   }
   const i32 off = pl->off[pass];
   const u8* src = data + off;
-  if (pkt) {
+  if (pkt && len <= pkt_cap) {
     CB_LANE_LOOP(i, len) pkt[i] = src[i];
     src = pkt;
   }

@@ -1,6 +1,6 @@
 // cb_kernels.cu -- sm_100a kernels of the batched Opus decoder and their launchers.
 //
-//   opus_plan_kernel    : 1 thread / stream  -- TOC + framing parse, argument checks, StreamPlan
+//   (the plan -- TOC + framing parse, argument checks, StreamPlan -- is fused with the SILK kernel: cb_silk_kernels.cu)
 //   celt_entropy_kernel : 1 warp   / stream  -- range decoder + PVQ/band reconstruction (kernel A)
 //   celt_synth_kernel   : 1 warp   / (stream, channel) -- IMDCT, post-filter, de-emphasis (kernel B)
 //
@@ -18,17 +18,6 @@
 #define A_WARPS 4           // kernel A, small batches: 4 warps per CTA, 7 CTAs per SM
 #define A_WARPS_SM 28       // kernel A, batches that fill the GPU: one CTA spans the SM (stage rendezvous, CB_ENT_PHASE)
 #define B_WARPS 4
-
-__global__ void opus_plan_kernel(OpusDecState* const* states, const u8* data, const i32* offs,
-                                 const i32* lens, const i32* fec, int frame_size, StreamPlan* plans,
-                                 i32* ret, int n) {
-  int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= n) return;
-  OpusDecState* st = states[s];
-  StreamPlan* pl = &plans[s];
-  opus_plan_stream(st, pl, data, offs[s], lens[s], frame_size, fec ? fec[s] : 0, 0, nullptr);
-  ret[s] = pl->ret;
-}
 
 template <bool HYB>
 __global__ void __launch_bounds__(A_WARPS_SM * 32, 1)
@@ -49,7 +38,7 @@ celt_entropy_kernel(OpusDecState* const* states, const u8* data, StreamPlan* pla
     OpusDecState* st = states[s];
     StreamPlan* pl = &plans[s];
     FrameSide* side = &sides[s];
-    decode_entropy_pass<HYB>(w, pkt, st, pl, side, data, &ret[s], pass);
+    decode_entropy_pass<HYB>(w, pkt, per_warp_bytes - (int)sizeof(EntWork), st, pl, side, data, &ret[s], pass);
   }
   // stage rendezvous: every warp of the CTA passes the same number of barriers (cb_celt_entropy.h)
   __syncwarp();
@@ -78,10 +67,10 @@ celt_synth_kernel(OpusDecState* const* states, const StreamPlan* plans, const Fr
 // Multistream: one thread per multistream decoder plans its elementary streams.
 __global__ void opus_ms_plan_kernel(OpusDecState* const* states, StreamPlan* plans, const MSLayout* layouts,
                                     const u8* data, const i32* offs, const i32* lens, const i32* fec,
-                                    int frame_size, i32* ms_ret, int n_ms) {
+                                    int frame_size, i32* ms_ret, int n_ms, int max_passes) {
   int m = blockIdx.x * blockDim.x + threadIdx.x;
   if (m >= n_ms) return;
-  ms_ret[m] = opus_ms_plan(states, plans, &layouts[m], data, offs[m], lens[m], frame_size, fec ? fec[m] : 0);
+  ms_ret[m] = opus_ms_plan(states, plans, &layouts[m], data, offs[m], lens[m], frame_size, fec ? fec[m] : 0, max_passes);
 }
 
 // Multistream: channel mapping copy-out (opus_multistream_decoder.c:262-299).  One CTA per
@@ -136,15 +125,6 @@ static int entropy_cta_warps(int n) {
   return w > A_WARPS_SM ? A_WARPS_SM : w;
 }
 
-extern "C" int cbk_launch_plan(OpusDecState* const* d_states, const u8* d_data, const i32* d_off,
-                               const i32* d_len, const i32* d_fec, int frame_size, StreamPlan* d_plans,
-                               i32* d_ret, int n, cudaStream_t stream) {
-  if (n <= 0) return 0;
-  opus_plan_kernel<<<(n + 127) / 128, 128, 0, stream>>>(d_states, d_data, d_off, d_len, d_fec, frame_size,
-                                                        d_plans, d_ret, n);
-  return (int)cudaGetLastError();
-}
-
 static int ensure_attrs() {
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
@@ -194,10 +174,10 @@ extern "C" int cbk_launch_synth(OpusDecState* const* d_states, const StreamPlan*
 
 extern "C" int cbk_launch_ms_plan(OpusDecState* const* d_states, StreamPlan* d_plans, const MSLayout* d_layouts,
                                   const u8* d_data, const i32* d_off, const i32* d_len, const i32* d_fec,
-                                  int frame_size, i32* d_ms_ret, int n_ms, cudaStream_t stream) {
+                                  int frame_size, i32* d_ms_ret, int n_ms, int max_passes, cudaStream_t stream) {
   if (n_ms <= 0) return 0;
   opus_ms_plan_kernel<<<(n_ms + 63) / 64, 64, 0, stream>>>(d_states, d_plans, d_layouts, d_data, d_off, d_len, d_fec,
-                                                          frame_size, d_ms_ret, n_ms);
+                                                          frame_size, d_ms_ret, n_ms, max_passes);
   return (int)cudaGetLastError();
 }
 

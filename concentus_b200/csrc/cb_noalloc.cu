@@ -60,7 +60,8 @@ __global__ void fill_static_scratch(StatePtrPack pack, StaticScratch* s, int n) 
 
 static StaticScratch* g_scratch_addr[16];   // per device, filled on first use
 
-extern "C" OpusDecState* opusb_internal_device_state(const OpusDecoder* st, int* device);
+extern "C" OpusDecState* opusb_internal_device_state(const OpusDecoder* st, int* device, int* channels);
+extern "C" cudaStream_t opusb_internal_stream(int* err);
 
 extern "C" int opus_decode_batch_device_static(OpusDecoder* const* st, int n, const unsigned char* d_data,
                                                const opus_int32* d_offsets, const opus_int32* d_len,
@@ -77,11 +78,12 @@ extern "C" int opus_decode_batch_device_static(OpusDecoder* const* st, int n, co
     return OPUS_BAD_ARG;
   }
   StatePtrPack pack;
-  int device = -1;
+  int device = -1, maxch = 1;
   for (int i = 0; i < n; i++) {
-    int dev = -1;
-    pack.p[i] = opusb_internal_device_state(st[i], &dev);
+    int dev = -1, ch = 1;
+    pack.p[i] = opusb_internal_device_state(st[i], &dev, &ch);
     if (!pack.p[i]) return OPUS_BAD_ARG;
+    if (ch > maxch) maxch = ch;
     if (i == 0) device = dev;
     else if (dev != device) {
       fprintf(stderr, "[opus_b200] opus_decode_batch_device_static: decoders live on different GPUs\n");
@@ -89,6 +91,7 @@ extern "C" int opus_decode_batch_device_static(OpusDecoder* const* st, int n, co
     }
   }
   if (device < 0 || device >= 16) return OPUS_BAD_ARG;
+  if ((long long)pcm_stride < (long long)frame_size * maxch) return OPUS_BAD_ARG;   // rows would overlap
   cudaError_t e = cudaSetDevice(device);
   if (e != cudaSuccess) {
     fprintf(stderr, "[opus_b200] cudaSetDevice(%d) failed: %s\n", device, cudaGetErrorString(e));
@@ -105,7 +108,14 @@ extern "C" int opus_decode_batch_device_static(OpusDecoder* const* st, int n, co
     g_scratch_addr[device] = (StaticScratch*)p;
   }
   StaticScratch* s = g_scratch_addr[device];
+  // NULL = the library's own stream, as in opus_decode_group_device: the call is then ordered with opus_decode /
+  // ctl work on the same decoders and opus_b200_synchronize() waits for it
   cudaStream_t stream = (cudaStream_t)cuda_stream;
+  if (!stream) {
+    int serr = 0;
+    stream = opusb_internal_stream(&serr);
+    if (!stream) return serr ? serr : OPUS_INTERNAL_ERROR;
+  }
   fill_static_scratch<<<(n + 127) / 128, 128, 0, stream>>>(pack, s, n);
   e = cudaGetLastError();
   if (e != cudaSuccess) {
@@ -113,7 +123,7 @@ extern "C" int opus_decode_batch_device_static(OpusDecoder* const* st, int n, co
     return OPUS_INTERNAL_ERROR;
   }
   int rc = cbk_launch_plan_silk(s->states, d_data, d_offsets, d_len, nullptr, frame_size, s->plans, s->sides, d_pcm,
-                                pcm_stride, d_ret, n, stream);
+                                pcm_stride, d_ret, n, max_frames, stream);
   for (int p = 0; p < max_frames && !rc; p++) {
     if (p > 0) rc = cbk_launch_silk(s->states, s->plans, s->sides, d_data, d_pcm, pcm_stride, d_ret, n, p, stream);
     if (!rc) rc = cbk_launch_entropy(s->states, d_data, s->plans, s->sides, d_ret, n, p, max_packet_bytes, stream);

@@ -156,7 +156,7 @@ CB_HD int opus_parse_packet(const u8* data, i32 len, int self_delimited, int* ou
 
 // Concealment plan for `frame_size` samples: the chunk sizes opus_decode_frame(data=NULL) picks
 // when called in the loop of opus_decode_native (opus_decoder.c:613-627, 239-292).
-CB_HD void opus_plan_plc(const OpusDecState* st, StreamPlan* pl, int frame_size) {
+CB_HD void opus_plan_plc(const OpusDecState* st, StreamPlan* pl, int frame_size, int max_passes = CB_MAX_FRAMES) {
   const int Fs = st->Fs;
   const int F20 = Fs / 50, F10 = F20 >> 1, F5 = F10 >> 1, F2_5 = F5 >> 1;
   const int mode = st->prev_mode;
@@ -180,11 +180,11 @@ CB_HD void opus_plan_plc(const OpusDecState* st, StreamPlan* pl, int frame_size)
       if (audiosize > F10) audiosize = F10;
       else if (mode != CB_MODE_SILK_ONLY && audiosize > F5 && audiosize < F10) audiosize = F5;
     }
-    if (nf >= CB_MAX_FRAMES) { pl->ret = CB_BAD_ARG; pl->kind = CB_PLAN_NONE; pl->nframes = 0; return; }
+    if (nf >= max_passes) { pl->ret = CB_BAD_ARG; pl->kind = CB_PLAN_NONE; pl->nframes = 0; return; }
     pl->off[nf] = 0;
     pl->len[nf] = 0;
     pl->nsamp[nf] = (i16)audiosize;
-    pl->pcm_off[nf] = (i16)done;
+    pl->pcm_off[nf] = done;
     nf++;
     done += audiosize;
   }
@@ -192,9 +192,14 @@ CB_HD void opus_plan_plc(const OpusDecState* st, StreamPlan* pl, int frame_size)
 }
 
 // opus_decode_native for one stream.  `data` = start of the packet arena, `off` = this packet's
-// offset or <0 for "no packet" (NULL), `len` its length.
+// offset or <0 for "no packet" (NULL), `len` its length.  `max_passes` = how many passes (frames of a packet,
+// concealment pieces, the pieces in front of an FEC frame) the caller is going to launch: a stream that needs
+// more fails with OPUS_BAD_ARG before any of its state is touched (the host entry points compute the count from
+// the packets; the device-resident ones take it from their max_frames argument).
 CB_HD void opus_plan_stream(OpusDecState* st, StreamPlan* pl, const u8* data, i32 off, i32 len,
-                            int frame_size, int decode_fec, int self_delimited, i32* packet_offset) {
+                            int frame_size, int decode_fec, int self_delimited, i32* packet_offset,
+                            int max_passes = CB_MAX_FRAMES) {
+  if (max_passes > CB_MAX_FRAMES) max_passes = CB_MAX_FRAMES;
   pl->kind = CB_PLAN_NONE;
   pl->nframes = 0;
   pl->total_samples = 0;
@@ -205,7 +210,7 @@ CB_HD void opus_plan_stream(OpusDecState* st, StreamPlan* pl, const u8* data, i3
   const int lost = (len == 0 || off < 0);
   if ((decode_fec || lost) && frame_size % (Fs / 400) != 0) { pl->ret = CB_BAD_ARG; return; }
   if (lost) {
-    opus_plan_plc(st, pl, frame_size);
+    opus_plan_plc(st, pl, frame_size, max_passes);
     if (pl->ret >= 0) st->last_packet_duration = pl->ret;
     return;
   }
@@ -223,7 +228,7 @@ CB_HD void opus_plan_stream(OpusDecState* st, StreamPlan* pl, const u8* data, i3
   if (decode_fec) {
     // No FEC in CELT-only packets: conceal instead (opus_decoder.c:647-648)
     if (frame_size < packet_frame_size || packet_mode == CB_MODE_CELT_ONLY || st->mode == CB_MODE_CELT_ONLY) {
-      opus_plan_plc(st, pl, frame_size);
+      opus_plan_plc(st, pl, frame_size, max_passes);
       if (pl->ret >= 0) st->last_packet_duration = pl->ret;
       return;
     }
@@ -232,7 +237,7 @@ CB_HD void opus_plan_stream(OpusDecState* st, StreamPlan* pl, const u8* data, i3
     const int duration_copy = st->last_packet_duration;
     int nf = 0, plc_samples = frame_size - packet_frame_size;
     if (plc_samples != 0) {
-      opus_plan_plc(st, pl, plc_samples);
+      opus_plan_plc(st, pl, plc_samples, max_passes);
       if (pl->ret < 0) { st->last_packet_duration = duration_copy; return; }
       if (pl->kind == CB_PLAN_ZERO) {           // nothing decoded yet: one all-zero frame
         pl->off[0] = 0; pl->len[0] = 0; pl->nsamp[0] = (i16)plc_samples; pl->pcm_off[0] = 0;
@@ -240,8 +245,8 @@ CB_HD void opus_plan_stream(OpusDecState* st, StreamPlan* pl, const u8* data, i3
       } else {
         nf = pl->nframes;
       }
-      if (nf >= CB_MAX_FRAMES) { pl->ret = CB_BAD_ARG; pl->kind = CB_PLAN_NONE; pl->nframes = 0; return; }
     }
+    if (nf >= max_passes) { pl->ret = CB_BAD_ARG; pl->kind = CB_PLAN_NONE; pl->nframes = 0; return; }
     st->mode = packet_mode;
     st->bandwidth = packet_bandwidth;
     st->frame_size = packet_frame_size;
@@ -249,7 +254,7 @@ CB_HD void opus_plan_stream(OpusDecState* st, StreamPlan* pl, const u8* data, i3
     pl->off[nf] = off + payload_offset;
     pl->len[nf] = sizes[0];
     pl->nsamp[nf] = (i16)packet_frame_size;
-    pl->pcm_off[nf] = (i16)plc_samples;
+    pl->pcm_off[nf] = plc_samples;
     pl->fec_frame = sizes[0] > 1 ? nf : -1;     // a 0/1-byte first frame is concealed, not FEC-decoded
     pl->kind = CB_PLAN_DECODE;
     pl->nframes = nf + 1;
@@ -259,6 +264,7 @@ CB_HD void opus_plan_stream(OpusDecState* st, StreamPlan* pl, const u8* data, i3
     return;
   }
   if (count * packet_frame_size > frame_size) { pl->ret = CB_BUFFER_TOO_SMALL; return; }
+  if (count > max_passes) { pl->ret = CB_BAD_ARG; return; }
   st->mode = packet_mode;
   st->bandwidth = packet_bandwidth;
   st->frame_size = packet_frame_size;
@@ -268,7 +274,7 @@ CB_HD void opus_plan_stream(OpusDecState* st, StreamPlan* pl, const u8* data, i3
     pl->off[i] = o;
     pl->len[i] = sizes[i];
     pl->nsamp[i] = (i16)packet_frame_size;
-    pl->pcm_off[i] = (i16)(i * packet_frame_size);
+    pl->pcm_off[i] = i * packet_frame_size;
     o += sizes[i];
   }
   pl->kind = CB_PLAN_DECODE;
@@ -343,7 +349,7 @@ CB_HD int opus_ms_validate(const u8* data, i32 len, int nb_streams, i32 Fs) {
 // sub-packets of one multistream packet and plans every elementary stream.  states/plans are the
 // group's arrays; the layout says which slice belongs to this multistream decoder.
 CB_HD int opus_ms_plan(OpusDecState* const* states, StreamPlan* plans, const MSLayout* L, const u8* arena,
-                       i32 off, i32 len, int frame_size, int decode_fec) {
+                       i32 off, i32 len, int frame_size, int decode_fec, int max_passes = CB_MAX_FRAMES) {
   const int S = L->nb_streams;
   const i32 Fs = L->Fs;
   for (int s = 0; s < S; s++) {
@@ -368,7 +374,7 @@ CB_HD int opus_ms_plan(OpusDecState* const* states, StreamPlan* plans, const MSL
     i32 packet_offset = 0;
     StreamPlan* pl = &plans[L->first + s];
     opus_plan_stream(states[L->first + s], pl, arena, do_plc ? -1 : cur, do_plc ? 0 : len, frame_size, decode_fec,
-                     s != S - 1, &packet_offset);
+                     s != S - 1, &packet_offset, max_passes);
     int r = pl->ret;
     if (r <= 0) return r;
     cur += packet_offset;

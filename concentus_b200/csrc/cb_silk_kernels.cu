@@ -32,12 +32,13 @@ silk_decode_kernel(OpusDecState* const* states, StreamPlan* plans, FrameSide* si
 // frame 0 in one launch (both are one thread per stream).
 __global__ void __launch_bounds__(S_THREADS)
 plan_silk_kernel(OpusDecState* const* states, const u8* data, const i32* offs, const i32* lens, const i32* fec,
-                 int frame_size, StreamPlan* plans, FrameSide* sides, i16* pcm, i32 pcm_stride, i32* ret, int n) {
+                 int frame_size, StreamPlan* plans, FrameSide* sides, i16* pcm, i32 pcm_stride, i32* ret, int n,
+                 int max_passes) {
   const int s = blockIdx.x * S_THREADS + threadIdx.x;
   if (s >= n) return;
   OpusDecState* st = states[s];
   StreamPlan* pl = &plans[s];
-  opus_plan_stream(st, pl, data, offs[s], lens[s], frame_size, fec ? fec[s] : 0, 0, nullptr);
+  opus_plan_stream(st, pl, data, offs[s], lens[s], frame_size, fec ? fec[s] : 0, 0, nullptr, max_passes);
   ret[s] = pl->ret;
   SilkCallWork cw;
   decode_silk_pass(st, pl, &sides[s], data, pcm + (size_t)s * pcm_stride, &ret[s], 0, cw);
@@ -45,11 +46,11 @@ plan_silk_kernel(OpusDecState* const* states, const u8* data, const i32* offs, c
 
 extern "C" int cbk_launch_plan_silk(OpusDecState* const* d_states, const u8* d_data, const i32* d_off, const i32* d_len,
                                     const i32* d_fec, int frame_size, StreamPlan* d_plans, FrameSide* d_sides, i16* d_pcm,
-                                    i32 pcm_stride, i32* d_ret, int n, cudaStream_t stream) {
+                                    i32 pcm_stride, i32* d_ret, int n, int max_passes, cudaStream_t stream) {
   if (n <= 0) return 0;
   plan_silk_kernel<<<(n + S_THREADS - 1) / S_THREADS, S_THREADS, 0, stream>>>(d_states, d_data, d_off, d_len, d_fec,
                                                                                frame_size, d_plans, d_sides, d_pcm,
-                                                                               pcm_stride, d_ret, n);
+                                                                               pcm_stride, d_ret, n, max_passes);
   return (int)cudaGetLastError();
 }
 

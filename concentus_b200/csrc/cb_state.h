@@ -138,7 +138,8 @@ struct alignas(16) StreamPlan {
   i32 off[CB_MAX_FRAMES];   // payload offset in the arena
   i16 len[CB_MAX_FRAMES];   // payload bytes (<=1 means "conceal this frame")
   i16 nsamp[CB_MAX_FRAMES]; // samples per channel produced (API rate)
-  i16 pcm_off[CB_MAX_FRAMES];
+  i32 pcm_off[CB_MAX_FRAMES];  // first sample of the frame in the stream's PCM row (48 concealment pieces of
+                               //   20 ms reach 46080 samples: wider than 16 bits)
 };
 
 // ---- multistream (surround) ------------------------------------------------------------------

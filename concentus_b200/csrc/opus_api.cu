@@ -425,7 +425,7 @@ static int group_enqueue(OpusDecoderGroup* g, const u8* d_data, const i32* d_off
   {
     ProfScope ps(stream, 0);
     rc = cbk_launch_plan_silk(g->d_states, d_data, d_off, d_len, d_fec, frame_size, g->d_plans, g->d_sides, d_pcm,
-                              pcm_stride, d_ret, g->n, stream);
+                              pcm_stride, d_ret, g->n, passes, stream);
   }
   g_launches += 1;
   if (rc) { fprintf(stderr, "[opus_b200] plan launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
@@ -438,6 +438,11 @@ int opus_decode_group_device(OpusDecoderGroup* g, const unsigned char* d_data, c
                              void* cuda_stream) {
   if (!g || g->magic != kMagic || !d_data || !d_offsets || !d_len || !d_pcm || !d_ret) return OPUS_BAD_ARG;
   if (frame_size <= 0 || max_frames < 1 || max_frames > CB_MAX_FRAMES || max_packet_bytes < 0) return OPUS_BAD_ARG;
+  {
+    int maxch = 1;
+    for (int i = 0; i < g->n; i++) if (g->members[i]->channels > maxch) maxch = g->members[i]->channels;
+    if ((long long)pcm_stride < (long long)frame_size * maxch) return OPUS_BAD_ARG;   // rows would overlap
+  }
   std::lock_guard<std::mutex> lk(g_mu);
   CUDA_OK(cudaSetDevice(g->device));
   int err = 0;
@@ -1059,7 +1064,7 @@ int opus_multistream_decode_group_flat(OpusMSDecoderGroup* g, const unsigned cha
   if (data_bytes > 0) CUDA_OK(cudaMemcpyAsync(c->d_pkt.p, data, data_bytes, cudaMemcpyHostToDevice, s));
   CUDA_OK(cudaMemcpyAsync(d_i, h_i, i32_bytes, cudaMemcpyHostToDevice, s));
   int rc = cbk_launch_ms_plan(eg->d_states, eg->d_plans, g->d_layouts, (const u8*)c->d_pkt.p, d_i, d_i + n, d_i + 2 * n,
-                              frame_size, g->d_ms_ret, n, s);
+                              frame_size, g->d_ms_ret, n, passes, s);
   g_launches += 1;
   if (rc) { fprintf(stderr, "[opus_b200] ms plan launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
   rc = group_enqueue_passes(eg, (const u8*)c->d_pkt.p, d_epcm, estride, eg->d_ret, passes, max_len, s);
@@ -1128,7 +1133,7 @@ int opus_multistream_decode_group_submit(OpusMSDecoderGroup* g, const unsigned c
   cudaStream_t s = c->stream;
   CUDA_OK(cudaStreamWaitEvent(s, sl.in_done, 0));
   int rc = cbk_launch_ms_plan(eg->d_states, eg->d_plans, g->d_layouts, (const u8*)sl.d_pkt.p, d_i, d_i + n, d_i + 2 * n,
-                              frame_size, d_ms_ret, n, s);
+                              frame_size, d_ms_ret, n, passes, s);
   g_launches += 1;
   if (rc) { fprintf(stderr, "[opus_b200] ms plan launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
   rc = group_enqueue_passes(eg, (const u8*)sl.d_pkt.p, d_epcm, estride, eg->d_ret, passes, max_len, s);
@@ -1283,9 +1288,10 @@ int opus_b200_synchronize(void) {
 long long opus_b200_launch_count(void) { return g_launches; }
 
 // internal (used by cb_noalloc.cu): device address of a decoder's state blob and its GPU index
-OpusDecState* opusb_internal_device_state(const OpusDecoder* st, int* device) {
+OpusDecState* opusb_internal_device_state(const OpusDecoder* st, int* device, int* channels) {
   if (!st || st->magic != kMagic) return nullptr;
   if (device) *device = st->device;
+  if (channels) *channels = st->channels;
   const_cast<OpusDecoder*>(st)->min_frame_48k = -1;    // its caller feeds device-resident packets the host never sees
   return st->d_state;
 }

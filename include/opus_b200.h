@@ -152,8 +152,14 @@ int opus_decode_group_wait(OpusDecoderGroup *grp);
 
 /* Device-resident form: every data pointer is a DEVICE pointer on the group's device; nothing is
  * copied and nothing is synchronised -- the work is queued on `cuda_stream` (a cudaStream_t,
- * NULL = the library's own stream).  max_frames = upper bound on frames per packet in this batch
- * (1 for ordinary one-frame packets), max_packet_bytes = upper bound on len[i]. */
+ * NULL = the library's own stream).  max_frames = the number of passes the call launches: it must cover the
+ * frames of the longest packet (1 for ordinary one-frame packets) AND, where packets can be lost or FEC is
+ * requested, the concealment pieces of a call -- a lost packet is concealed in pieces no longer than the last
+ * decoded frame, so frame_size / (shortest frame duration in use), plus one for an FEC frame.  A stream that would
+ * need more passes gets OPUS_BAD_ARG in d_ret and its state is left untouched (the host forms count the passes
+ * from the packets themselves).  max_packet_bytes = expected upper bound on len[i] (sizes the shared-memory
+ * staging; a longer packet is still decoded, read in place).  pcm_stride >= frame_size * channels, else
+ * OPUS_BAD_ARG. */
 int opus_decode_group_device(OpusDecoderGroup *grp, const unsigned char *d_data,
                              const opus_int32 *d_offsets, const opus_int32 *d_len, opus_int16 *d_pcm,
                              opus_int32 pcm_stride, int frame_size, const int *d_decode_fec, int *d_ret,
@@ -208,7 +214,8 @@ int opus_multistream_decode_group_wait(OpusMSDecoderGroup *grp);
  * previous call's records, which this call overwrites: calls that could run concurrently on one GPU
  * (different streams or threads) race and must be ordered by the caller.  The first call on a GPU
  * looks up the array's device address (cudaGetSymbolAddress); make it at start-up, before any
- * stream capture.  decode_fec is not offered here (treated as 0). */
+ * stream capture.  decode_fec is not offered here (treated as 0).  max_frames, max_packet_bytes, pcm_stride
+ * and cuda_stream (NULL = the library's own stream) mean what they mean for opus_decode_group_device(). */
 #define OPUS_B200_STATIC_MAX_STREAMS 256
 int opus_decode_batch_device_static(OpusDecoder *const *st, int n, const unsigned char *d_data,
                                     const opus_int32 *d_offsets, const opus_int32 *d_len, opus_int16 *d_pcm,

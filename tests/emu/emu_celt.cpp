@@ -44,7 +44,10 @@ unsigned emu_opus_final_range(void* s) { return ((OpusDecState*)s)->rangeFinal; 
 void emu_opus_set_gain(void* s, int g) { ((OpusDecState*)s)->decode_gain = g; }
 int emu_opus_last_packet_duration(void* s) { return ((OpusDecState*)s)->last_packet_duration; }
 
-int emu_opus_decode(void* state, const unsigned char* data, int len, short* pcm, int frame_size, int fec) {
+// max_passes: what a device-resident entry point would be given as max_frames (the host entry points count the
+// passes from the packets and never trip the check)
+int emu_opus_decode_capped(void* state, const unsigned char* data, int len, short* pcm, int frame_size, int fec,
+                           int max_passes) {
   OpusDecState* st = (OpusDecState*)state;
   static EntWork ew;
   static SynWork sw;
@@ -55,17 +58,21 @@ int emu_opus_decode(void* state, const unsigned char* data, int len, short* pcm,
   static GenWork gw;
   StreamPlan pl;
   i32 ret = 0;
-  opus_plan_stream(st, &pl, data, data ? 0 : -1, data ? len : 0, frame_size, fec, 0, nullptr);
+  opus_plan_stream(st, &pl, data, data ? 0 : -1, data ? len : 0, frame_size, fec, 0, nullptr, max_passes);
   ret = pl.ret;
   for (int pass = 0; pass < pl.nframes; pass++) {
     decode_silk_pass(st, &pl, &side, data, pcm, &ret, pass, cw);
-    decode_entropy_pass<false>(ew, pkt, st, &pl, &side, data, &ret, pass);
-    decode_entropy_pass<true>(ew, pkt, st, &pl, &side, data, &ret, pass);
+    decode_entropy_pass<false>(ew, pkt, 256, st, &pl, &side, data, &ret, pass);
+    decode_entropy_pass<true>(ew, pkt, 256, st, &pl, &side, data, &ret, pass);
     for (int c = 0; c < st->channels; c++) decode_synth_pass(sw, st, &pl, &side, pcm, c, pass);
     decode_plc_pass(pw, st, &pl, &side, pcm, pass);
     decode_general_pass(gw, st, &pl, &side, data, pcm, &ret, pass, cw);
   }
   return ret;
+}
+
+int emu_opus_decode(void* state, const unsigned char* data, int len, short* pcm, int frame_size, int fec) {
+  return emu_opus_decode_capped(state, data, len, pcm, frame_size, fec, CB_MAX_FRAMES);
 }
 
 // ---- multistream: plan + passes + channel copy-out, as the CUDA launch sequence does ----
@@ -109,8 +116,8 @@ int emu_ms_decode(void* p, const unsigned char* data, int len, short* pcm, int f
     i32 r = pl->ret;
     for (int pass = 0; pass < pl->nframes; pass++) {
       decode_silk_pass(m->st[s], pl, &side, data, epcm[s], &r, pass, cw);
-      decode_entropy_pass<false>(ew, pkt, m->st[s], pl, &side, data, &r, pass);
-      decode_entropy_pass<true>(ew, pkt, m->st[s], pl, &side, data, &r, pass);
+      decode_entropy_pass<false>(ew, pkt, 256, m->st[s], pl, &side, data, &r, pass);
+      decode_entropy_pass<true>(ew, pkt, 256, m->st[s], pl, &side, data, &r, pass);
       for (int c = 0; c < m->st[s]->channels; c++) decode_synth_pass(sw, m->st[s], pl, &side, epcm[s], c, pass);
       decode_plc_pass(pw, m->st[s], pl, &side, epcm[s], pass);
       decode_general_pass(gw, m->st[s], pl, &side, data, epcm[s], &r, pass, cw);

@@ -75,3 +75,58 @@ def test_emu_decode_gain(emu_lib, gain):
         pb = np.zeros((960, 2), dtype=np.int16)
         rb = emu_lib.emu_opus_decode(st, data, len(data) if data else 0, pb.ctypes.data, 960, 0)
         assert ra == rb == 960 and np.array_equal(pa, pb), n
+
+
+@needs_ref
+@pytest.mark.parametrize("name,fsz", [("c2_96k_cbr_st", 40320), ("c2_96k_cbr_st", 46080), ("f10_64k_st", 23040)])
+def test_emu_long_concealment(emu_lib, name, fsz):
+    """One lost call that asks for most of a second: up to 48 concealment pieces, PCM offsets beyond 32767 samples
+    (the plan's offsets are 32-bit).  libopus conceals any frame_size in pieces (opus_decoder.c:613-627)."""
+    from conftest import golden_case
+    meta, pk = golden_case(name)
+    spf = meta["frame_size"] if "frame_size" in meta else None
+    calls = []
+    for t in range(6):
+        d = pk[t][0]
+        calls.append((d, 5760, 0))
+    calls.append((None, fsz, 0))
+    calls.append((pk[6][0], 5760, 0))
+    _run(emu_lib, meta, calls)
+
+
+def test_emu_max_passes_cap(emu_lib):
+    """A device-resident call launches exactly max_frames passes: a stream that needs more (a two-frame packet, a
+    loss that takes several concealment pieces) must fail with OPUS_BAD_ARG and leave its state alone."""
+    from conftest import golden_case
+    emu_lib.emu_opus_create.restype = ctypes.c_void_p
+    emu_lib.emu_opus_create.argtypes = [ctypes.c_int, ctypes.c_int]
+    emu_lib.emu_opus_destroy.argtypes = [ctypes.c_void_p]
+    emu_lib.emu_opus_decode.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int, ctypes.c_void_p,
+                                        ctypes.c_int, ctypes.c_int]
+    emu_lib.emu_opus_decode_capped.argtypes = emu_lib.emu_opus_decode.argtypes + [ctypes.c_int]
+    emu_lib.emu_opus_final_range.argtypes = [ctypes.c_void_p]
+    emu_lib.emu_opus_final_range.restype = ctypes.c_uint
+    emu_lib.emu_opus_last_packet_duration.argtypes = [ctypes.c_void_p]
+    meta, pk = golden_case("f10_64k_st")          # 10 ms frames
+    a, b = emu_lib.emu_opus_create(48000, 2), emu_lib.emu_opus_create(48000, 2)
+    pa, pb = np.zeros((960, 2), np.int16), np.zeros((960, 2), np.int16)
+    try:
+        for t in range(4):
+            for st, p in ((a, pa), (b, pb)):
+                assert emu_lib.emu_opus_decode(st, pk[t][0], len(pk[t][0]), p.ctypes.data, 960, 0) == 480
+        # a 20 ms loss after 10 ms frames needs two pieces: one pass is not enough
+        assert emu_lib.emu_opus_decode_capped(a, None, 0, pa.ctypes.data, 960, 0, 1) == -1
+        assert emu_lib.emu_opus_last_packet_duration(a) == 480
+        # two frames in one packet (code 1), one pass allowed
+        two = bytes([pk[4][0][0] | 1]) + pk[4][0][1:] + pk[4][0][1:]
+        assert emu_lib.emu_opus_decode_capped(a, two, len(two), pa.ctypes.data, 960, 0, 1) == -1
+        assert emu_lib.emu_opus_final_range(a) == emu_lib.emu_opus_final_range(b)
+        # the failed calls left no trace: both decoders continue identically
+        for t in range(4, 8):
+            ra = emu_lib.emu_opus_decode_capped(a, pk[t][0], len(pk[t][0]), pa.ctypes.data, 960, 0, 1)
+            rb = emu_lib.emu_opus_decode(b, pk[t][0], len(pk[t][0]), pb.ctypes.data, 960, 0)
+            assert ra == rb == 480 and np.array_equal(pa, pb)
+            assert emu_lib.emu_opus_final_range(a) == emu_lib.emu_opus_final_range(b)
+    finally:
+        emu_lib.emu_opus_destroy(a)
+        emu_lib.emu_opus_destroy(b)

@@ -80,3 +80,85 @@ def test_gpu_multiframe_and_corruption_batch():
         for name in FUZZ:
             scripts.append(fuzz_scenario(name, seed=len(name) + 3 + 100 * rep))
     _run_batch(scripts)
+
+
+@needs_ref
+@pytest.mark.parametrize("fsz", [40320, 46080])
+def test_gpu_long_concealment(fsz):
+    """A lost call asking for most of a second (42 / 48 pieces of 20 ms): PCM offsets beyond 32767 samples."""
+    from conftest import golden_case
+    meta, pk = golden_case("c2_96k_cbr_st")
+    dec, ref = cb.OpusDecoder(48000, 2), RefDecoder(48000, 2)
+    try:
+        calls = [(pk[t][0], 960) for t in range(6)] + [(None, fsz), (pk[6][0], 960), (pk[7][0], 960)]
+        for n, (d, f) in enumerate(calls):
+            ra, pa = ref.decode_raw(d, f)
+            pb = dec.decode(d, f)
+            assert ra == pb.shape[0], "call %d" % n
+            assert np.array_equal(pa[:ra], pb), "pcm, call %d" % n
+            assert ref.final_range == dec.final_range
+    finally:
+        dec.close()
+
+
+@needs_ref
+def test_gpu_device_entry_limits():
+    """Device-resident entry: a stream needing more passes than max_frames fails alone with OPUS_BAD_ARG and keeps
+    its state; a packet longer than max_packet_bytes is decoded all the same (read in place instead of staged);
+    a pcm_stride shorter than a row is refused."""
+    import torch
+    from conftest import golden_case
+    lib = cb.load()
+    meta10, pk10 = golden_case("f10_64k_st")
+    metab, pkb = golden_case("hi_510k_st")               # 20 ms packets of ~1275 bytes
+    n, spf, ch = 8, 960, 2
+    grp = cb.OpusBatchDecoder(48000, ch, n)
+    ref10, refb = RefDecoder(48000, 2), RefDecoder(48000, 2)
+    stream = torch.cuda.Stream()
+    sp = ctypes.c_void_p(stream.cuda_stream)
+
+    def call(packets, max_frames, max_bytes, stride=spf * ch):
+        lens_h = np.array([len(p) if p else 0 for p in packets], dtype=np.int32)
+        offs_h = np.concatenate([[0], np.cumsum(lens_h)[:-1]]).astype(np.int32)
+        offs_h[lens_h == 0] = -1
+        blob = b"".join(p for p in packets if p) or b"\0"
+        arena = torch.from_numpy(np.frombuffer(blob, dtype=np.uint8).copy()).cuda()
+        offs, lens = torch.from_numpy(offs_h).cuda(), torch.from_numpy(lens_h).cuda()
+        pcm = torch.zeros(n * spf * ch, dtype=torch.int16, device="cuda")
+        ret = torch.zeros(n, dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        rc = lib.opus_decode_group_device(grp._g, arena.data_ptr(), offs.data_ptr(), lens.data_ptr(), pcm.data_ptr(),
+                                          stride, spf, None, ret.data_ptr(), max_frames, max_bytes, sp)
+        stream.synchronize()
+        return rc, ret.cpu().numpy(), pcm.cpu().numpy().reshape(n, spf, ch)
+
+    try:
+        # streams 0..3 play the 10 ms fixture, 4..7 the 510 kbit/s one; max_packet_bytes understated on purpose
+        for t in range(4):
+            rc, ret, pcm = call([pk10[t][0]] * 4 + [pkb[t][0]] * 4, 1, 64)
+            assert rc == 0
+            ra, pa = ref10.decode_raw(pk10[t][0], spf)
+            rb, pb = refb.decode_raw(pkb[t][0], spf)
+            assert (ret[:4] == ra).all() and (ret[4:] == rb).all()
+            for i in range(4):
+                assert np.array_equal(pcm[i, :ra], pa[:ra])
+                assert np.array_equal(pcm[4 + i, :rb], pb[:rb])
+        # a 20 ms loss after 10 ms frames takes two pieces: with max_frames = 1 those streams fail, the others decode
+        rc, ret, pcm = call([None] * 4 + [pkb[4][0]] * 4, 1, 1275)
+        assert rc == 0
+        assert (ret[:4] == cb.OPUS_BAD_ARG).all()
+        rb, pb = refb.decode_raw(pkb[4][0], spf)
+        assert (ret[4:] == rb).all() and np.array_equal(pcm[5, :rb], pb[:rb])
+        # the refused streams are where they were: the next packets decode as if nothing had happened
+        rc, ret, pcm = call([pk10[4][0]] * 4 + [pkb[5][0]] * 4, 1, 1275)
+        ra, pa = ref10.decode_raw(pk10[4][0], spf)
+        assert (ret[:4] == ra).all() and np.array_equal(pcm[2, :ra], pa[:ra])
+        # and with two passes the loss is concealed like the reference does
+        rc, ret, pcm = call([None] * 4 + [None] * 4, 2, 1275)
+        ra, pa = ref10.decode_raw(None, spf)
+        assert (ret[:4] == ra).all() and np.array_equal(pcm[1, :ra], pa[:ra])
+        # rows must not overlap
+        rc, _, _ = call([pk10[5][0]] * 8, 1, 1275, stride=spf * ch - 2)
+        assert rc == cb.OPUS_BAD_ARG
+    finally:
+        grp.close()
