@@ -34,6 +34,8 @@ opus_encode_kernel(OpusEncState* const* states, EncScratch* scratch, const i16* 
   for (int k = w.nsync; k < phases; k++) __syncthreads();
 }
 
+extern "C" int cbk_sm_count(void);   // SMs of the current device (opus_api.cu)
+
 extern "C" {
 
 size_t cbk_sizeof_enc_state(void) { return sizeof(OpusEncState); }
@@ -53,10 +55,11 @@ int cbk_launch_encode(OpusEncState* const* d_states, void* d_scratch, const i16*
     if (e != cudaSuccess) return (int)e;
     attr_set[dev] = true;
   }
-  // CTA shape: an equal share of the batch for every SM (ceil(n / 148) warps per CTA, at most 28 = what an SM
+  // CTA shape: an equal share of the batch for every SM (ceil(n / #SMs) warps per CTA, at most 28 = what an SM
   // holds; the same over two or more waves for larger batches), so that a small batch still uses the whole GPU
-  const int waves = (n + 148 * E_WARPS - 1) / (148 * E_WARPS);
-  int ew = (n + 148 * waves - 1) / (148 * waves);
+  const int sms = cbk_sm_count();
+  const int waves = (n + sms * E_WARPS - 1) / (sms * E_WARPS);
+  int ew = (n + sms * waves - 1) / (sms * waves);
   if (ew > E_WARPS) ew = E_WARPS;
   if (ew < 1) ew = 1;
   const int blocks = (n + ew - 1) / ew;

@@ -10,6 +10,8 @@
 #include "cb_opus_general.h"
 #include "cb_kernels.h"
 
+extern "C" int cbk_sm_count(void);
+
 #define G_WARPS 4
 
 __global__ void __launch_bounds__(G_WARPS * 32)
@@ -46,7 +48,8 @@ extern "C" int cbk_launch_general(OpusDecState* const* d_states, StreamPlan* d_p
     if (dev < 64) attr_set[dev] = true;
   }
   int grid = (n + G_WARPS - 1) / G_WARPS;
-  if (grid > 148 * 4) grid = 148 * 4;               // a few CTAs per SM; streams beyond are walked by a grid-stride loop
+  const int cap = cbk_sm_count() * 4;
+  if (grid > cap) grid = cap;               // a few CTAs per SM; streams beyond are walked by a grid-stride loop
   opus_general_kernel<<<grid, G_WARPS * 32, smem, stream>>>(d_states, d_plans, d_sides, d_data, d_pcm,
                                                                                     pcm_stride, d_ret, n, pass);
   return (int)cudaGetLastError();

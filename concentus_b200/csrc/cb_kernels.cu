@@ -15,6 +15,8 @@
 #include "cb_decode_pass.h"
 #include "cb_kernels.h"
 
+extern "C" int cbk_sm_count(void);   // SMs of the current device (opus_api.cu)
+
 #define A_WARPS 4           // kernel A, small batches: 4 warps per CTA, 7 CTAs per SM
 #define A_WARPS_SM 28       // kernel A, batches that fill the GPU: one CTA spans the SM (stage rendezvous, CB_ENT_PHASE)
 #define B_WARPS 4
@@ -114,14 +116,15 @@ extern "C" size_t cbk_entropy_smem_per_warp(int max_payload, int cta_warps) {
   return staged <= limit ? staged : work;
 }
 // Warps per CTA of kernel A.  An SM holds 28 of its warps (registers, shared memory).  A batch that gives every SM
-// at least a few warps runs as CTAs that each take an equal share of it -- ceil(n / 148) warps per CTA, one CTA
-// per SM, or the same over two, three ... waves when the batch is larger than 148 x 28 -- so that every SM is busy
+// at least a few warps runs as CTAs that each take an equal share of it -- ceil(n / #SMs) warps per CTA, one CTA
+// per SM, or the same over two, three ... waves when the batch is larger than #SMs x 28 -- so that every SM is busy
 // for the whole kernel and the warps of an SM pass the frame's stages together (CB_ENT_PHASE).  Smaller batches
 // keep 4-warp CTAs and spread over the SMs.
 static int entropy_cta_warps(int n) {
-  if (n < 148 * (A_WARPS + 1)) return A_WARPS;
-  const int waves = (n + 148 * A_WARPS_SM - 1) / (148 * A_WARPS_SM);
-  const int w = (n + 148 * waves - 1) / (148 * waves);
+  const int sms = cbk_sm_count();
+  if (n < sms * (A_WARPS + 1)) return A_WARPS;
+  const int waves = (n + sms * A_WARPS_SM - 1) / (sms * A_WARPS_SM);
+  const int w = (n + sms * waves - 1) / (sms * waves);
   return w > A_WARPS_SM ? A_WARPS_SM : w;
 }
 

@@ -9,9 +9,11 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <atomic>
 #include <mutex>
 #include <vector>
 #include "../../include/opus_b200.h"
+#include "cb_host.h"
 #include "cb_kernels.h"
 #include "cb_state.h"
 #include "cb_opus_plan.h"
@@ -50,28 +52,22 @@ struct GrowBuf {                 // grow-only buffer (device or pinned host)
   }
 };
 
-struct DevCtx {
-  int device = -1;
-  cudaStream_t stream = nullptr;
+struct DevCtx : OpusbDevice {
   // The general kernel (mode switches, pitch-based concealment) works on streams the CELT kernels skip, so it
   // runs beside them on its own stream: forked after the SILK kernel of a pass, joined at the end of the pass.
   cudaStream_t side_stream = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   std::vector<OpusDecState*> slabs;
   std::vector<OpusDecState*> free_slots;
-  // staging for the pointer-array / flat entry points
-  GrowBuf d_pkt, d_i32, d_pcm, d_states, d_plans, d_sides;
-  GrowBuf h_pkt, h_i32, h_pcm, h_states;
-  DevCtx() { h_pkt.pinned = h_i32.pinned = h_pcm.pinned = h_states.pinned = true; }
 };
 
-std::mutex g_mu;
-DevCtx g_ctx[16];
-long long g_launches = 0;
+DevCtx g_ctx[OPUSB_MAX_DEVICES];        // each guarded by its own mutex (cb_host.h)
+std::atomic<long long> g_launches{0};
+std::mutex g_prof_mu;                   // guards g_prof only
 
 // optional per-kernel timing (CUDA events on the launching stream), for bench.py's roofline line
 struct ProfRec { int kind; cudaEvent_t a, b; };
-bool g_prof_on = false;
+std::atomic<bool> g_prof_on{false};
 std::vector<ProfRec> g_prof;
 struct ProfScope {
   cudaStream_t s; int kind; cudaEvent_t a = nullptr, b = nullptr; bool on;
@@ -79,19 +75,23 @@ struct ProfScope {
     if (on) { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, s); }
   }
   ~ProfScope() {
-    if (on) { cudaEventRecord(b, s); g_prof.push_back({kind, a, b}); }
+    if (on) { cudaEventRecord(b, s); std::lock_guard<std::mutex> lk(g_prof_mu); g_prof.push_back({kind, a, b}); }
   }
 };
 
-DevCtx* ctx_for_current_device(int* err) {
-  int dev = -1;
-  cudaError_t e = cudaGetDevice(&dev);
-  if (e != cudaSuccess || dev < 0 || dev >= 16) {
+// Makes `device` current (device < 0: the thread's current device) and returns its context; first use creates
+// the stream under the device's mutex.  The caller must NOT hold that mutex.
+DevCtx* ctx_enter(int device, int* err) {
+  cudaError_t e = cudaSuccess;
+  if (device < 0) e = cudaGetDevice(&device);
+  else e = cudaSetDevice(device);
+  if (e != cudaSuccess || device < 0 || device >= OPUSB_MAX_DEVICES) {
     fprintf(stderr, "[opus_b200] no usable CUDA device: %s\n", cudaGetErrorString(e));
     if (err) *err = OPUS_INTERNAL_ERROR;
     return nullptr;
   }
-  DevCtx* c = &g_ctx[dev];
+  DevCtx* c = &g_ctx[device];
+  std::lock_guard<std::mutex> lk(c->mu);
   if (c->device < 0) {
     e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) {
@@ -99,12 +99,16 @@ DevCtx* ctx_for_current_device(int* err) {
       if (err) *err = OPUS_INTERNAL_ERROR;
       return nullptr;
     }
-    c->device = dev;
+    if (cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || c->sm_count <= 0)
+      c->sm_count = 148;
+    c->device = device;
   }
   return c;
 }
 
 }  // namespace
+
+OpusbDevice* opusb_device(int device, int* err) { return ctx_enter(device, err); }
 
 struct OpusDecoderGroup;
 struct OpusDecoder {
@@ -141,8 +145,8 @@ struct OpusDecoderGroup {
   StreamPlan* d_plans;
   FrameSide* d_sides;
   i32* d_ret;                  // n
-  i32* d_maxframes;            // scratch for plan read-back (unused for now)
   DecPipe* pipe;               // created by the first opus_decode_group_submit
+  GrowBuf d_pkt, d_i32, d_pcm; // staging of the synchronous host-buffer entry (opus_decode_group_flat)
 };
 
 extern "C" {
@@ -181,10 +185,10 @@ OpusDecoder* opus_decoder_create(opus_int32 Fs, int channels, int* error) {
     if (error) *error = OPUS_BAD_ARG;
     return nullptr;
   }
-  std::lock_guard<std::mutex> lk(g_mu);
   int err = OPUS_OK;
-  DevCtx* c = ctx_for_current_device(&err);
+  DevCtx* c = ctx_enter(-1, &err);
   if (!c) { if (error) *error = err; return nullptr; }
+  std::unique_lock<std::mutex> lk(c->mu);
   if (c->free_slots.empty()) {
     OpusDecState* slab = nullptr;
     cudaError_t e = cudaMalloc((void**)&slab, sizeof(OpusDecState) * kSlab);
@@ -205,8 +209,10 @@ OpusDecoder* opus_decoder_create(opus_int32 Fs, int channels, int* error) {
   st->decode_gain = 0;
   st->d_state = c->free_slots.back();
   c->free_slots.pop_back();
+  lk.unlock();
   int rc = upload_fresh_state(st, 0);
   if (rc != OPUS_OK) {
+    lk.lock();
     c->free_slots.push_back(st->d_state);
     free(st);
     if (error) *error = rc;
@@ -221,10 +227,10 @@ void opus_decoder_group_destroy(OpusDecoderGroup* g);
 void opus_decoder_destroy(OpusDecoder* st) {
   if (!st || st->magic != kMagic) return;
   if (st->self_group) { opus_decoder_group_destroy(st->self_group); st->self_group = nullptr; }
-  std::lock_guard<std::mutex> lk(g_mu);
-  if (st->device >= 0 && st->device < 16) {
+  if (st->device >= 0 && st->device < OPUSB_MAX_DEVICES) {
     DevCtx* c = &g_ctx[st->device];
     if (c->stream) cudaStreamSynchronize(c->stream);
+    std::lock_guard<std::mutex> lk(c->mu);
     c->free_slots.push_back(st->d_state);
   }
   st->magic = 0;
@@ -318,9 +324,12 @@ static void group_free(OpusDecoderGroup* g) {
   if (g->d_plans) cudaFree(g->d_plans);
   if (g->d_sides) cudaFree(g->d_sides);
   if (g->d_ret) cudaFree(g->d_ret);
+  if (g->d_pkt.p) cudaFree(g->d_pkt.p);
+  if (g->d_i32.p) cudaFree(g->d_i32.p);
+  if (g->d_pcm.p) cudaFree(g->d_pcm.p);
   free(g->members);
   g->magic = 0;
-  free(g);
+  delete g;
 }
 
 OpusDecoderGroup* opus_decoder_group_create(OpusDecoder* const* st, int n, int* error) {
@@ -331,11 +340,11 @@ OpusDecoderGroup* opus_decoder_group_create(OpusDecoder* const* st, int n, int* 
       return nullptr;
     }
   }
-  std::lock_guard<std::mutex> lk(g_mu);
   int prev = -1;
   cudaGetDevice(&prev);
   if (cudaSetDevice(st[0]->device) != cudaSuccess) { if (error) *error = OPUS_INTERNAL_ERROR; return nullptr; }
-  OpusDecoderGroup* g = (OpusDecoderGroup*)calloc(1, sizeof(OpusDecoderGroup));
+  OpusDecoderGroup* g = new OpusDecoderGroup();
+  g->d_states = nullptr; g->d_plans = nullptr; g->d_sides = nullptr; g->d_ret = nullptr; g->pipe = nullptr;
   std::vector<OpusDecState*> ptrs(n);
   g->magic = kMagic;
   g->n = n;
@@ -367,8 +376,7 @@ OpusDecoderGroup* opus_decoder_group_create(OpusDecoder* const* st, int n, int* 
 
 void opus_decoder_group_destroy(OpusDecoderGroup* g) {
   if (!g || g->magic != kMagic) return;
-  std::lock_guard<std::mutex> lk(g_mu);
-  if (g->device >= 0 && g->device < 16 && g_ctx[g->device].stream) cudaStreamSynchronize(g_ctx[g->device].stream);
+  if (g->device >= 0 && g->device < OPUSB_MAX_DEVICES && g_ctx[g->device].stream) cudaStreamSynchronize(g_ctx[g->device].stream);
   group_free(g);
 }
 
@@ -377,7 +385,7 @@ void opus_decoder_group_destroy(OpusDecoderGroup* g) {
 static int group_enqueue_passes(OpusDecoderGroup* g, const u8* d_data, i16* d_pcm, i32 pcm_stride, i32* d_ret,
                                 int passes, int max_packet_bytes, cudaStream_t stream, bool silk0_done = false) {
   int rc = 0;
-  DevCtx* c = (g->device >= 0 && g->device < 16) ? &g_ctx[g->device] : nullptr;
+  DevCtx* c = (g->device >= 0 && g->device < OPUSB_MAX_DEVICES) ? &g_ctx[g->device] : nullptr;   // its mutex is held by the caller
   if (c && !c->side_stream) {
     if (cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
@@ -443,11 +451,10 @@ int opus_decode_group_device(OpusDecoderGroup* g, const unsigned char* d_data, c
     for (int i = 0; i < g->n; i++) if (g->members[i]->channels > maxch) maxch = g->members[i]->channels;
     if ((long long)pcm_stride < (long long)frame_size * maxch) return OPUS_BAD_ARG;   // rows would overlap
   }
-  std::lock_guard<std::mutex> lk(g_mu);
-  CUDA_OK(cudaSetDevice(g->device));
   int err = 0;
-  DevCtx* c = ctx_for_current_device(&err);
+  DevCtx* c = ctx_enter(g->device, &err);
   if (!c) return err;
+  std::lock_guard<std::mutex> lk(c->mu);
   cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
   for (int i = 0; i < g->n; i++) g->members[i]->min_frame_48k = -1;   // the host does not see these packets
   return group_enqueue(g, d_data, d_offsets, d_len, d_pcm, pcm_stride, frame_size, d_decode_fec, d_ret,
@@ -521,34 +528,39 @@ int opus_decode_group_flat(OpusDecoderGroup* g, const unsigned char* data, opus_
     if (offsets[i] >= 0 && len[i] > 0 && (offsets[i] + (long long)len[i] > data_bytes)) return OPUS_BAD_ARG;
   }
   if (pcm_stride < frame_size * maxch) return OPUS_BAD_ARG;
-  std::lock_guard<std::mutex> lk(g_mu);
-  CUDA_OK(cudaSetDevice(g->device));
   int err = 0;
-  DevCtx* c = ctx_for_current_device(&err);
+  DevCtx* c = ctx_enter(g->device, &err);
   if (!c) return err;
   int max_len = 0;
   int passes = scan_passes(g->members, data, offsets, len, decode_fec, n, frame_size, g->Fs, &max_len);
   const size_t pkt_bytes = (size_t)data_bytes + 16;
   const size_t pcm_bytes = (size_t)n * pcm_stride * sizeof(i16);
   const size_t i32_bytes = (size_t)n * 3 * sizeof(i32);
-  if (c->d_pkt.reserve(pkt_bytes) || c->d_pcm.reserve(pcm_bytes) || c->d_i32.reserve(i32_bytes) ||
-      c->h_i32.reserve(i32_bytes))
-    return OPUS_ALLOC_FAIL;
-  i32* h_i = (i32*)c->h_i32.p;
-  memcpy(h_i, offsets, n * sizeof(i32));
-  memcpy(h_i + n, len, n * sizeof(i32));
-  if (decode_fec) memcpy(h_i + 2 * n, decode_fec, n * sizeof(i32));
-  else memset(h_i + 2 * n, 0, n * sizeof(i32));
-  i32* d_i = (i32*)c->d_i32.p;
+  // staging belongs to the group (a group is used by one thread at a time), so nothing shared is held while
+  // the host waits for the GPU below
+  if (g->d_pkt.reserve(pkt_bytes) || g->d_pcm.reserve(pcm_bytes) || g->d_i32.reserve(i32_bytes)) return OPUS_ALLOC_FAIL;
+  std::vector<i32> h_i((size_t)n * 3);
+  memcpy(h_i.data(), offsets, n * sizeof(i32));
+  memcpy(h_i.data() + n, len, n * sizeof(i32));
+  if (decode_fec) memcpy(h_i.data() + 2 * n, decode_fec, n * sizeof(i32));
+  i32* d_i = (i32*)g->d_i32.p;
   cudaStream_t s = c->stream;
-  if (data_bytes > 0) CUDA_OK(cudaMemcpyAsync(c->d_pkt.p, data, data_bytes, cudaMemcpyHostToDevice, s));
-  CUDA_OK(cudaMemcpyAsync(d_i, h_i, i32_bytes, cudaMemcpyHostToDevice, s));
-  int rc = group_enqueue(g, (const u8*)c->d_pkt.p, d_i, d_i + n, (i16*)c->d_pcm.p, pcm_stride, frame_size,
-                         d_i + 2 * n, g->d_ret, passes, max_len, s);
-  if (rc != OPUS_OK) return rc;
-  CUDA_OK(cudaMemcpyAsync(pcm, c->d_pcm.p, pcm_bytes, cudaMemcpyDeviceToHost, s));
-  CUDA_OK(cudaMemcpyAsync(ret, g->d_ret, n * sizeof(i32), cudaMemcpyDeviceToHost, s));
-  CUDA_OK(cudaStreamSynchronize(s));
+  cudaEvent_t done = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(c->mu);          // queueing order only; released before the wait
+    if (data_bytes > 0) CUDA_OK(cudaMemcpyAsync(g->d_pkt.p, data, data_bytes, cudaMemcpyHostToDevice, s));
+    CUDA_OK(cudaMemcpyAsync(d_i, h_i.data(), i32_bytes, cudaMemcpyHostToDevice, s));   // pageable source: staged before return
+    int rc = group_enqueue(g, (const u8*)g->d_pkt.p, d_i, d_i + n, (i16*)g->d_pcm.p, pcm_stride, frame_size,
+                           d_i + 2 * n, g->d_ret, passes, max_len, s);
+    if (rc != OPUS_OK) return rc;
+    CUDA_OK(cudaMemcpyAsync(pcm, g->d_pcm.p, pcm_bytes, cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaMemcpyAsync(ret, g->d_ret, n * sizeof(i32), cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaEventCreateWithFlags(&done, cudaEventDisableTiming));
+    CUDA_OK(cudaEventRecord(done, s));
+  }
+  cudaError_t e = cudaEventSynchronize(done);       // this call's work only, not whatever other threads queued behind it
+  cudaEventDestroy(done);
+  CUDA_OK(e);
   return OPUS_OK;
 }
 
@@ -569,10 +581,8 @@ int opus_decode_group_submit(OpusDecoderGroup* g, const unsigned char* data, opu
     if (offsets[i] >= 0 && len[i] > 0 && (offsets[i] + (long long)len[i] > data_bytes)) return OPUS_BAD_ARG;
   }
   if (pcm_stride < frame_size * maxch) return OPUS_BAD_ARG;
-  std::lock_guard<std::mutex> lk(g_mu);
-  CUDA_OK(cudaSetDevice(g->device));
   int err = 0;
-  DevCtx* c = ctx_for_current_device(&err);
+  DevCtx* c = ctx_enter(g->device, &err);
   if (!c) return err;
   if (!g->pipe) {
     DecPipe* p = new DecPipe();
@@ -605,6 +615,7 @@ int opus_decode_group_submit(OpusDecoderGroup* g, const unsigned char* data, opu
   CUDA_OK(cudaMemcpyAsync(d_i, h_i, in_bytes, cudaMemcpyHostToDevice, p->s_in));
   CUDA_OK(cudaEventRecord(sl.in_done, p->s_in));
   cudaStream_t s = c->stream;
+  std::lock_guard<std::mutex> lk(c->mu);
   CUDA_OK(cudaStreamWaitEvent(s, sl.in_done, 0));
   int rc = group_enqueue(g, (const u8*)sl.d_pkt.p, d_i, d_i + n, (i16*)sl.d_pcm.p, pcm_stride, frame_size, d_i + 2 * n,
                          d_i + 3 * n, passes, max_len, s);
@@ -622,7 +633,6 @@ int opus_decode_group_submit(OpusDecoderGroup* g, const unsigned char* data, opu
 // Wait for every call submitted on this group; their pcm / ret buffers are complete afterwards.
 int opus_decode_group_wait(OpusDecoderGroup* g) {
   if (!g || g->magic != kMagic) return OPUS_BAD_ARG;
-  std::lock_guard<std::mutex> lk(g_mu);
   if (!g->pipe) return OPUS_OK;
   CUDA_OK(cudaSetDevice(g->device));
   for (int k = 0; k < 2; k++) {
@@ -740,8 +750,8 @@ int opus_decoder_ctl(OpusDecoder* st, int request, ...) {
   va_list ap;
   va_start(ap, request);
   int ret = OPUS_OK;
-  std::lock_guard<std::mutex> lk(g_mu);
-  static OpusDecState hdr;   // only the leading fields are filled (guarded by g_mu)
+  // (no lock: the calls below touch this decoder's own state and the device's stream handle only)
+  static thread_local OpusDecState hdr;   // only the leading fields are filled
   switch (request) {
     case OPUS_GET_BANDWIDTH_REQUEST:
     case OPUS_GET_FINAL_RANGE_REQUEST:
@@ -801,7 +811,6 @@ int opus_decoder_ctl(OpusDecoder* st, int request, ...) {
 
 int opus_decoder_get_final_range_batch(OpusDecoder* const* st, int n, opus_uint32* out) {
   if (!st || !out || n <= 0) return OPUS_BAD_ARG;
-  std::lock_guard<std::mutex> lk(g_mu);
   for (int i = 0; i < n; i++) {
     if (!st[i] || st[i]->magic != kMagic) return OPUS_BAD_ARG;
     DevCtx* c = &g_ctx[st[i]->device];
@@ -829,6 +838,7 @@ struct OpusMSDecoderGroup {
   MSLayout* d_layouts;
   i32* d_ms_ret;
   struct MSPipe* pipe;          // created by the first opus_multistream_decode_group_submit
+  GrowBuf d_pkt, d_i32, d_pcm, d_epcm;   // staging of the synchronous host-buffer entry
 };
 
 // Two-deep pipeline behind opus_multistream_decode_group_submit/_wait (see DecPipe)
@@ -931,11 +941,11 @@ OpusMSDecoderGroup* opus_multistream_decoder_group_create(OpusMSDecoder* const* 
   int err = OPUS_OK;
   OpusDecoderGroup* eg = opus_decoder_group_create(elem.data(), (int)elem.size(), &err);
   if (!eg) { if (error) *error = err; return nullptr; }
-  OpusMSDecoderGroup* g = (OpusMSDecoderGroup*)calloc(1, sizeof(OpusMSDecoderGroup));
+  OpusMSDecoderGroup* g = new OpusMSDecoderGroup();
+  g->d_layouts = nullptr; g->d_ms_ret = nullptr; g->pipe = nullptr;
   g->magic = kMagicMS; g->n_ms = n; g->device = eg->device; g->max_channels = maxch; g->eg = eg;
   g->members = (OpusMSDecoder**)malloc(sizeof(OpusMSDecoder*) * n);
   for (int m = 0; m < n; m++) g->members[m] = st[m];
-  std::lock_guard<std::mutex> lk(g_mu);
   int prev = -1;
   cudaGetDevice(&prev);
   cudaSetDevice(g->device);
@@ -947,7 +957,7 @@ OpusMSDecoderGroup* opus_multistream_decoder_group_create(OpusMSDecoder* const* 
     fprintf(stderr, "[opus_b200] multistream group allocation failed: %s\n", cudaGetErrorString(cudaGetLastError()));
     if (g->d_layouts) cudaFree(g->d_layouts);
     if (g->d_ms_ret) cudaFree(g->d_ms_ret);
-    free(g->members); free(g);
+    free(g->members); delete g;
     if (error) *error = OPUS_ALLOC_FAIL;
     return nullptr;   // (eg is released by the caller's process exit; creation failure is fatal anyway)
   }
@@ -957,20 +967,18 @@ OpusMSDecoderGroup* opus_multistream_decoder_group_create(OpusMSDecoder* const* 
 
 void opus_multistream_decoder_group_destroy(OpusMSDecoderGroup* g) {
   if (!g || g->magic != kMagicMS) return;
-  {
-    std::lock_guard<std::mutex> lk(g_mu);
-    ms_pipe_free(g->pipe);
-    g->pipe = nullptr;
-  }
-  opus_decoder_group_destroy(g->eg);
-  {
-    std::lock_guard<std::mutex> lk(g_mu);
-    cudaFree(g->d_layouts);
-    cudaFree(g->d_ms_ret);
-  }
+  ms_pipe_free(g->pipe);
+  g->pipe = nullptr;
+  opus_decoder_group_destroy(g->eg);           // waits for the device's stream
+  cudaFree(g->d_layouts);
+  cudaFree(g->d_ms_ret);
+  if (g->d_pkt.p) cudaFree(g->d_pkt.p);
+  if (g->d_i32.p) cudaFree(g->d_i32.p);
+  if (g->d_pcm.p) cudaFree(g->d_pcm.p);
+  if (g->d_epcm.p) cudaFree(g->d_epcm.p);
   free(g->members);
   g->magic = 0;
-  free(g);
+  delete g;
 }
 
 // Flat host form for multistream packets: packet m at data[offsets[m]..+len[m]) (offset<0 or len 0 = lost),
@@ -1039,10 +1047,8 @@ int opus_multistream_decode_group_flat(OpusMSDecoderGroup* g, const unsigned cha
     const int rc0 = ms_scan(g, data, data_bytes, offsets, len, decode_fec, frame_size, &passes, &max_len);
     if (rc0 != OPUS_OK) return rc0;
   }
-  std::lock_guard<std::mutex> lk(g_mu);
-  CUDA_OK(cudaSetDevice(g->device));
   int err = 0;
-  DevCtx* c = ctx_for_current_device(&err);
+  DevCtx* c = ctx_enter(g->device, &err);
   if (!c) return err;
   OpusDecoderGroup* eg = g->eg;
   const i32 estride = frame_size * 2;
@@ -1050,31 +1056,38 @@ int opus_multistream_decode_group_flat(OpusMSDecoderGroup* g, const unsigned cha
   const size_t pcm_bytes = (size_t)n * pcm_stride * sizeof(i16);
   const size_t epcm_bytes = (size_t)eg->n * estride * sizeof(i16);
   const size_t i32_bytes = (size_t)n * 3 * sizeof(i32);
-  if (c->d_pkt.reserve(pkt_bytes) || c->d_pcm.reserve(pcm_bytes) || c->d_i32.reserve(i32_bytes) ||
-      c->h_i32.reserve(i32_bytes) || c->d_plans.reserve(epcm_bytes))
+  if (g->d_pkt.reserve(pkt_bytes) || g->d_pcm.reserve(pcm_bytes) || g->d_i32.reserve(i32_bytes) ||
+      g->d_epcm.reserve(epcm_bytes))
     return OPUS_ALLOC_FAIL;
-  i16* d_epcm = (i16*)c->d_plans.p;              // elementary PCM rows (scratch)
-  i32* h_i = (i32*)c->h_i32.p;
-  memcpy(h_i, offsets, n * sizeof(i32));
-  memcpy(h_i + n, len, n * sizeof(i32));
-  if (decode_fec) memcpy(h_i + 2 * n, decode_fec, n * sizeof(i32));
-  else memset(h_i + 2 * n, 0, n * sizeof(i32));
-  i32* d_i = (i32*)c->d_i32.p;
+  i16* d_epcm = (i16*)g->d_epcm.p;               // elementary PCM rows (scratch)
+  std::vector<i32> h_i((size_t)n * 3);
+  memcpy(h_i.data(), offsets, n * sizeof(i32));
+  memcpy(h_i.data() + n, len, n * sizeof(i32));
+  if (decode_fec) memcpy(h_i.data() + 2 * n, decode_fec, n * sizeof(i32));
+  i32* d_i = (i32*)g->d_i32.p;
   cudaStream_t s = c->stream;
-  if (data_bytes > 0) CUDA_OK(cudaMemcpyAsync(c->d_pkt.p, data, data_bytes, cudaMemcpyHostToDevice, s));
-  CUDA_OK(cudaMemcpyAsync(d_i, h_i, i32_bytes, cudaMemcpyHostToDevice, s));
-  int rc = cbk_launch_ms_plan(eg->d_states, eg->d_plans, g->d_layouts, (const u8*)c->d_pkt.p, d_i, d_i + n, d_i + 2 * n,
-                              frame_size, g->d_ms_ret, n, passes, s);
-  g_launches += 1;
-  if (rc) { fprintf(stderr, "[opus_b200] ms plan launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
-  rc = group_enqueue_passes(eg, (const u8*)c->d_pkt.p, d_epcm, estride, eg->d_ret, passes, max_len, s);
-  if (rc != OPUS_OK) return rc;
-  rc = cbk_launch_ms_scatter(g->d_layouts, g->d_ms_ret, d_epcm, estride, (i16*)c->d_pcm.p, pcm_stride, n, s);
-  g_launches += 1;
-  if (rc) { fprintf(stderr, "[opus_b200] ms scatter launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
-  CUDA_OK(cudaMemcpyAsync(pcm, c->d_pcm.p, pcm_bytes, cudaMemcpyDeviceToHost, s));
-  CUDA_OK(cudaMemcpyAsync(ret, g->d_ms_ret, n * sizeof(i32), cudaMemcpyDeviceToHost, s));
-  CUDA_OK(cudaStreamSynchronize(s));
+  cudaEvent_t done = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(c->mu);          // queueing order only; released before the wait
+    if (data_bytes > 0) CUDA_OK(cudaMemcpyAsync(g->d_pkt.p, data, data_bytes, cudaMemcpyHostToDevice, s));
+    CUDA_OK(cudaMemcpyAsync(d_i, h_i.data(), i32_bytes, cudaMemcpyHostToDevice, s));
+    int rc = cbk_launch_ms_plan(eg->d_states, eg->d_plans, g->d_layouts, (const u8*)g->d_pkt.p, d_i, d_i + n, d_i + 2 * n,
+                                frame_size, g->d_ms_ret, n, passes, s);
+    g_launches += 1;
+    if (rc) { fprintf(stderr, "[opus_b200] ms plan launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
+    rc = group_enqueue_passes(eg, (const u8*)g->d_pkt.p, d_epcm, estride, eg->d_ret, passes, max_len, s);
+    if (rc != OPUS_OK) return rc;
+    rc = cbk_launch_ms_scatter(g->d_layouts, g->d_ms_ret, d_epcm, estride, (i16*)g->d_pcm.p, pcm_stride, n, s);
+    g_launches += 1;
+    if (rc) { fprintf(stderr, "[opus_b200] ms scatter launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
+    CUDA_OK(cudaMemcpyAsync(pcm, g->d_pcm.p, pcm_bytes, cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaMemcpyAsync(ret, g->d_ms_ret, n * sizeof(i32), cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaEventCreateWithFlags(&done, cudaEventDisableTiming));
+    CUDA_OK(cudaEventRecord(done, s));
+  }
+  cudaError_t e = cudaEventSynchronize(done);
+  cudaEventDestroy(done);
+  CUDA_OK(e);
   return OPUS_OK;
 }
 
@@ -1092,10 +1105,8 @@ int opus_multistream_decode_group_submit(OpusMSDecoderGroup* g, const unsigned c
     const int rc0 = ms_scan(g, data, data_bytes, offsets, len, decode_fec, frame_size, &passes, &max_len);
     if (rc0 != OPUS_OK) return rc0;
   }
-  std::lock_guard<std::mutex> lk(g_mu);
-  CUDA_OK(cudaSetDevice(g->device));
   int err = 0;
-  DevCtx* c = ctx_for_current_device(&err);
+  DevCtx* c = ctx_enter(g->device, &err);
   if (!c) return err;
   if (!g->pipe) {
     MSPipe* p = new MSPipe();
@@ -1131,6 +1142,7 @@ int opus_multistream_decode_group_submit(OpusMSDecoderGroup* g, const unsigned c
   CUDA_OK(cudaMemcpyAsync(d_i, h_i, in_bytes, cudaMemcpyHostToDevice, p->s_in));
   CUDA_OK(cudaEventRecord(sl.in_done, p->s_in));
   cudaStream_t s = c->stream;
+  std::lock_guard<std::mutex> lk(c->mu);
   CUDA_OK(cudaStreamWaitEvent(s, sl.in_done, 0));
   int rc = cbk_launch_ms_plan(eg->d_states, eg->d_plans, g->d_layouts, (const u8*)sl.d_pkt.p, d_i, d_i + n, d_i + 2 * n,
                               frame_size, d_ms_ret, n, passes, s);
@@ -1153,7 +1165,6 @@ int opus_multistream_decode_group_submit(OpusMSDecoderGroup* g, const unsigned c
 
 int opus_multistream_decode_group_wait(OpusMSDecoderGroup* g) {
   if (!g || g->magic != kMagicMS) return OPUS_BAD_ARG;
-  std::lock_guard<std::mutex> lk(g_mu);
   if (!g->pipe) return OPUS_OK;
   CUDA_OK(cudaSetDevice(g->device));
   for (int k = 0; k < 2; k++) {
@@ -1277,15 +1288,14 @@ int opus_multistream_decoder_ctl(OpusMSDecoder* st, int request, ...) {
 }
 
 int opus_b200_synchronize(void) {
-  std::lock_guard<std::mutex> lk(g_mu);
   int err = 0;
-  DevCtx* c = ctx_for_current_device(&err);
+  DevCtx* c = ctx_enter(-1, &err);
   if (!c) return err;
   CUDA_OK(cudaStreamSynchronize(c->stream));
   return OPUS_OK;
 }
 
-long long opus_b200_launch_count(void) { return g_launches; }
+long long opus_b200_launch_count(void) { return g_launches.load(); }
 
 // internal (used by cb_noalloc.cu): device address of a decoder's state blob and its GPU index
 OpusDecState* opusb_internal_device_state(const OpusDecoder* st, int* device, int* channels) {
@@ -1299,26 +1309,29 @@ OpusDecState* opusb_internal_device_state(const OpusDecoder* st, int* device, in
 // internal (used by opus_enc_api.cu): the per-device stream all launches of this library go on,
 // so that opus_b200_synchronize() covers encoder launches too; and the launch counter.
 cudaStream_t opusb_internal_stream(int* err) {
-  std::lock_guard<std::mutex> lk(g_mu);
-  DevCtx* c = ctx_for_current_device(err);
+  DevCtx* c = ctx_enter(-1, err);
   return c ? c->stream : nullptr;
 }
-void opusb_internal_count_launches(int n) {
-  std::lock_guard<std::mutex> lk(g_mu);
-  g_launches += n;
+void opusb_internal_count_launches(int n) { g_launches += n; }
+int cbk_sm_count(void) {
+  int dev = -1;
+  if (cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < OPUSB_MAX_DEVICES && g_ctx[dev].sm_count > 0) return g_ctx[dev].sm_count;
+  int sm = 0;
+  if (dev >= 0 && cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && sm > 0) return sm;
+  return 148;
 }
 
 int opus_b200_profile_begin(void) {
-  std::lock_guard<std::mutex> lk(g_mu);
+  std::lock_guard<std::mutex> lk(g_prof_mu);
   g_prof_on = true;
   return OPUS_OK;
 }
 
 int opus_b200_profile_end(double* ms, long long* counts) {
-  std::lock_guard<std::mutex> lk(g_mu);
   g_prof_on = false;
   for (int k = 0; k < 3; k++) { if (ms) ms[k] = 0; if (counts) counts[k] = 0; }
   cudaDeviceSynchronize();
+  std::lock_guard<std::mutex> lk(g_prof_mu);
   for (auto& r : g_prof) {
     float t = 0;
     if (cudaEventElapsedTime(&t, r.a, r.b) == cudaSuccess && r.kind >= 0 && r.kind < 3) {

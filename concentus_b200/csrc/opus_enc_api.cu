@@ -8,8 +8,11 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <atomic>
+#include <mutex>
 #include <vector>
 #include "../../include/opus_b200.h"
+#include "cb_host.h"
 #include "cb_enc_ctl.h"
 #include "cb_enc_kernels.h"
 #include "cb_enc_state.h"
@@ -24,14 +27,13 @@
     }                                                                                            \
   } while (0)
 
-extern "C" cudaStream_t opusb_internal_stream(int* err);
-extern "C" void opusb_internal_count_launches(int n);
 
 namespace {
 const int kEncMagic = 0x4f453230;   // "OE20"
 
 struct EncProf { cudaEvent_t a, b; };
-bool g_enc_prof_on = false;
+std::atomic<bool> g_enc_prof_on{false};
+std::mutex g_enc_prof_mu;              // guards g_enc_prof only
 std::vector<EncProf> g_enc_prof;
 }  // namespace
 
@@ -108,7 +110,8 @@ bool valid(const OpusEncoderGroup* g) { return g && g->magic == kEncMagic + 1; }
 int group_launch(OpusEncoderGroup* g, const i16* d_pcm, i32 pcm_stride, int frame_size, u8* d_data, i32 data_stride,
                  int max_data_bytes, i32* d_len, cudaStream_t stream) {
   EncProf pr{nullptr, nullptr};
-  if (g_enc_prof_on) { cudaEventCreate(&pr.a); cudaEventCreate(&pr.b); cudaEventRecord(pr.a, stream); }
+  const bool prof = g_enc_prof_on.load();
+  if (prof) { cudaEventCreate(&pr.a); cudaEventCreate(&pr.b); cudaEventRecord(pr.a, stream); }
   // a frame longer than 20 ms is coded as two or three 20 ms frames: the kernel's stage rendezvous has to
   // know the most any member will do (members may run at different rates)
   int max_sub = 1, general = 0;
@@ -120,7 +123,7 @@ int group_launch(OpusEncoderGroup* g, const i16* d_pcm, i32 pcm_stride, int fram
   }
   int rc = cbk_launch_encode(g->d_states, g->d_scratch, d_pcm, pcm_stride, frame_size, d_data, data_stride,
                              max_data_bytes, d_len, g->n, max_sub, general, stream);
-  if (g_enc_prof_on) { cudaEventRecord(pr.b, stream); g_enc_prof.push_back(pr); }
+  if (prof) { cudaEventRecord(pr.b, stream); std::lock_guard<std::mutex> lk(g_enc_prof_mu); g_enc_prof.push_back(pr); }
   opusb_internal_count_launches(1);
   if (rc != 0) {
     fprintf(stderr, "[opus_b200] encode kernel launch failed: %s\n", cudaGetErrorString((cudaError_t)rc));
@@ -146,13 +149,13 @@ OpusEncoder* opus_encoder_create(opus_int32 Fs, int channels, int application, i
     return nullptr;
   }
   int err = 0;
-  cudaStream_t stream = opusb_internal_stream(&err);
-  if (!stream) { if (error) *error = err; return nullptr; }
+  OpusbDevice* dv = opusb_device(-1, &err);          // the thread's current GPU
+  if (!dv) { if (error) *error = err; return nullptr; }
   OpusEncoder* st = (OpusEncoder*)calloc(1, sizeof(OpusEncoder));
   OpusEncState* h = (OpusEncState*)malloc(sizeof(OpusEncState));
   if (!st || !h) { free(st); free(h); if (error) *error = OPUS_ALLOC_FAIL; return nullptr; }
   opus_enc_init(h, Fs, channels, application);
-  cudaGetDevice(&st->device);
+  st->device = dv->device;
   if (cudaMalloc((void**)&st->d_state, sizeof(OpusEncState)) != cudaSuccess ||
       cudaMemcpy(st->d_state, h, sizeof(OpusEncState), cudaMemcpyHostToDevice) != cudaSuccess) {
     fprintf(stderr, "[opus_b200] encoder state allocation failed: %s\n", cudaGetErrorString(cudaGetLastError()));
@@ -173,6 +176,11 @@ void opus_encoder_group_destroy(OpusEncoderGroup* g);
 void opus_encoder_destroy(OpusEncoder* st) {
   if (!valid(st)) return;
   if (st->self_group) opus_encoder_group_destroy(st->self_group);
+  {
+    int err = 0;
+    OpusbDevice* dv = opusb_device(st->device, &err);
+    if (dv) cudaStreamSynchronize(dv->stream);
+  }
   cudaFree(st->d_state);
   st->magic = 0;
   free(st);
@@ -182,6 +190,10 @@ OpusEncoderGroup* opus_encoder_group_create(OpusEncoder* const* st, int n, int* 
   if (!st || n <= 0) { if (error) *error = OPUS_BAD_ARG; return nullptr; }
   for (int i = 0; i < n; i++)
     if (!valid(st[i]) || st[i]->device != st[0]->device) { if (error) *error = OPUS_BAD_ARG; return nullptr; }
+  {
+    int err = 0;
+    if (!opusb_device(st[0]->device, &err)) { if (error) *error = err; return nullptr; }   // makes the group's GPU current
+  }
   OpusEncoderGroup* g = (OpusEncoderGroup*)calloc(1, sizeof(OpusEncoderGroup));
   if (!g) { if (error) *error = OPUS_ALLOC_FAIL; return nullptr; }
   g->n = n; g->device = st[0]->device;
@@ -227,6 +239,11 @@ static void enc_pipe_free(EncPipe* p) {
 
 void opus_encoder_group_destroy(OpusEncoderGroup* g) {
   if (!valid(g)) return;
+  {
+    int err = 0;
+    OpusbDevice* dv = opusb_device(g->device, &err);
+    if (dv) cudaStreamSynchronize(dv->stream);
+  }
   enc_pipe_free(g->pipe);
   g->pipe = nullptr;
   cudaFree(g->d_states); cudaFree(g->d_scratch); cudaFree(g->d_len);
@@ -245,10 +262,11 @@ int opus_encode_group_device(OpusEncoderGroup* g, const opus_int16* d_pcm, int f
   if (!valid(g) || !d_pcm || !d_data || !d_len || frame_size <= 0 || max_data_bytes <= 0) return OPUS_BAD_ARG;
   if (g->channels < 0) return OPUS_BAD_ARG;
   int err = 0;
-  cudaStream_t stream = opusb_internal_stream(&err);
-  if (!stream) return err;
+  OpusbDevice* dv = opusb_device(g->device, &err);
+  if (!dv) return err;
+  std::lock_guard<std::mutex> lk(dv->mu);
   return group_launch(g, d_pcm, frame_size * g->channels, frame_size, d_data, max_data_bytes, max_data_bytes, d_len,
-                      stream);
+                      dv->stream);
 }
 
 // Host-buffer batch: pcm = n rows of frame_size*channels int16, data = n rows of max_data_bytes,
@@ -258,20 +276,29 @@ int opus_encode_group_flat(OpusEncoderGroup* g, const opus_int16* pcm, int frame
   if (!valid(g) || !pcm || !data || !out_len || frame_size <= 0 || max_data_bytes <= 0) return OPUS_BAD_ARG;
   if (g->channels < 0) return OPUS_BAD_ARG;
   int err = 0;
-  cudaStream_t stream = opusb_internal_stream(&err);
-  if (!stream) return err;
+  OpusbDevice* dv = opusb_device(g->device, &err);
+  if (!dv) return err;
+  cudaStream_t stream = dv->stream;
   const size_t row = (size_t)frame_size * g->channels;
   const size_t pcm_bytes = row * sizeof(i16) * g->n, data_bytes = (size_t)max_data_bytes * g->n;
   int rc;
   if ((rc = grow_dev((void**)&g->d_pcm, &g->d_pcm_cap, pcm_bytes)) != OPUS_OK) return rc;
   if ((rc = grow_dev((void**)&g->d_data, &g->d_data_cap, data_bytes)) != OPUS_OK) return rc;
-  // straight from / to the caller's buffers: page-locked ones go by DMA, pageable ones through the driver's staging
-  CUDA_OK(cudaMemcpyAsync(g->d_pcm, pcm, pcm_bytes, cudaMemcpyHostToDevice, stream));
-  rc = group_launch(g, g->d_pcm, (i32)row, frame_size, g->d_data, max_data_bytes, max_data_bytes, g->d_len, stream);
-  if (rc != OPUS_OK) return rc;
-  CUDA_OK(cudaMemcpyAsync(data, g->d_data, data_bytes, cudaMemcpyDeviceToHost, stream));
-  CUDA_OK(cudaMemcpyAsync(out_len, g->d_len, sizeof(i32) * g->n, cudaMemcpyDeviceToHost, stream));
-  CUDA_OK(cudaStreamSynchronize(stream));
+  cudaEvent_t done = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(dv->mu);          // queueing order only; released before the wait
+    // straight from / to the caller's buffers: page-locked ones go by DMA, pageable ones through the driver's staging
+    CUDA_OK(cudaMemcpyAsync(g->d_pcm, pcm, pcm_bytes, cudaMemcpyHostToDevice, stream));
+    rc = group_launch(g, g->d_pcm, (i32)row, frame_size, g->d_data, max_data_bytes, max_data_bytes, g->d_len, stream);
+    if (rc != OPUS_OK) return rc;
+    CUDA_OK(cudaMemcpyAsync(data, g->d_data, data_bytes, cudaMemcpyDeviceToHost, stream));
+    CUDA_OK(cudaMemcpyAsync(out_len, g->d_len, sizeof(i32) * g->n, cudaMemcpyDeviceToHost, stream));
+    CUDA_OK(cudaEventCreateWithFlags(&done, cudaEventDisableTiming));
+    CUDA_OK(cudaEventRecord(done, stream));
+  }
+  cudaError_t e = cudaEventSynchronize(done);
+  cudaEventDestroy(done);
+  CUDA_OK(e);
   return OPUS_OK;
 }
 
@@ -284,8 +311,9 @@ int opus_encode_group_submit(OpusEncoderGroup* g, const opus_int16* pcm, int fra
   if (!valid(g) || !pcm || !data || !out_len || frame_size <= 0 || max_data_bytes <= 0) return OPUS_BAD_ARG;
   if (g->channels < 0) return OPUS_BAD_ARG;
   int err = 0;
-  cudaStream_t stream = opusb_internal_stream(&err);
-  if (!stream) return err;
+  OpusbDevice* dv = opusb_device(g->device, &err);
+  if (!dv) return err;
+  cudaStream_t stream = dv->stream;
   if (!g->pipe) {
     EncPipe* p = (EncPipe*)calloc(1, sizeof(EncPipe));
     if (!p) return OPUS_ALLOC_FAIL;
@@ -309,6 +337,7 @@ int opus_encode_group_submit(OpusEncoderGroup* g, const opus_int16* pcm, int fra
   if ((rc = grow_dev((void**)&sl.d_data, &sl.d_data_cap, data_bytes)) != OPUS_OK) return rc;
   CUDA_OK(cudaMemcpyAsync(sl.d_pcm, pcm, pcm_bytes, cudaMemcpyHostToDevice, p->s_in));
   CUDA_OK(cudaEventRecord(sl.in_done, p->s_in));
+  std::lock_guard<std::mutex> lk(dv->mu);
   CUDA_OK(cudaStreamWaitEvent(stream, sl.in_done, 0));
   rc = group_launch(g, sl.d_pcm, (i32)row, frame_size, sl.d_data, max_data_bytes, max_data_bytes, sl.d_len, stream);
   if (rc != OPUS_OK) return rc;
@@ -326,6 +355,7 @@ int opus_encode_group_submit(OpusEncoderGroup* g, const opus_int16* pcm, int fra
 int opus_encode_group_wait(OpusEncoderGroup* g) {
   if (!valid(g)) return OPUS_BAD_ARG;
   if (!g->pipe) return OPUS_OK;
+  CUDA_OK(cudaSetDevice(g->device));
   for (int k = 0; k < 2; k++) {
     EncPipeSlot& sl = g->pipe->slot[(g->pipe->seq + k) & 1];     // oldest first
     if (sl.busy) { CUDA_OK(cudaEventSynchronize(sl.out_done)); sl.busy = false; }
@@ -395,9 +425,9 @@ int opus_encoder_ctl(OpusEncoder* st, int request, ...) {
   va_start(ap, request);
   int ret = OPUS_OK;
   int err = 0;
-  cudaStream_t stream = opusb_internal_stream(&err);
-  if (!stream) { va_end(ap); return err; }
-  cudaStreamSynchronize(stream);
+  OpusbDevice* dv = opusb_device(st->device, &err);
+  if (!dv) { va_end(ap); return err; }
+  cudaStreamSynchronize(dv->stream);
   if (request == OPUS_RESET_STATE) {
     OpusEncState* h = (OpusEncState*)malloc(sizeof(OpusEncState));
     if (!h) { va_end(ap); return OPUS_ALLOC_FAIL; }
@@ -467,11 +497,11 @@ int opusb_internal_encoder_mask_slots(OpusEncoder* st, int side, opus_int16** ma
 }
 
 int opus_encoder_get_final_range_batch(OpusEncoder* const* st, int n, opus_uint32* out) {
-  if (!st || !out || n <= 0) return OPUS_BAD_ARG;
+  if (!st || !out || n <= 0 || !valid(st[0])) return OPUS_BAD_ARG;
   int err = 0;
-  cudaStream_t stream = opusb_internal_stream(&err);
-  if (!stream) return err;
-  CUDA_OK(cudaStreamSynchronize(stream));
+  OpusbDevice* dv = opusb_device(st[0]->device, &err);
+  if (!dv) return err;
+  CUDA_OK(cudaStreamSynchronize(dv->stream));
   for (int i = 0; i < n; i++) {
     if (!valid(st[i])) return OPUS_BAD_ARG;
     CUDA_OK(cudaMemcpy(&out[i], (char*)st[i]->d_state + offsetof(OpusEncScalars, rangeFinal), sizeof(opus_uint32),
@@ -481,10 +511,11 @@ int opus_encoder_get_final_range_batch(OpusEncoder* const* st, int n, opus_uint3
 }
 
 // per-launch timing of the encode kernel (CUDA events on the launching stream), for bench.py
-int opus_b200_encode_profile_begin(void) { g_enc_prof_on = true; return OPUS_OK; }
+int opus_b200_encode_profile_begin(void) { g_enc_prof_on = true; return OPUS_OK; }   // (one GPU at a time: bench use)
 int opus_b200_encode_profile_end(double* ms, long long* count) {
   g_enc_prof_on = false;
   cudaDeviceSynchronize();
+  std::lock_guard<std::mutex> lk(g_enc_prof_mu);
   double total = 0; long long c = 0;
   for (auto& r : g_enc_prof) {
     float t = 0;

@@ -25,8 +25,7 @@
 #include "cb_repack_internal.h"
 #include "cb_surround_kernels.h"
 
-extern "C" cudaStream_t opusb_internal_stream(int* err);
-extern "C" void opusb_internal_count_launches(int n);
+#include "cb_host.h"
 extern "C" int opusb_internal_encoder_mask_slots(OpusEncoder* st, int side, opus_int16** mask, opus_int32** has_mask);
 
 
@@ -46,6 +45,7 @@ struct OpusMSEncoder {
   opus_int16* d_pcm;
   size_t d_pcm_cap;
   SurroundDst dst;
+  int device;                    // GPU the encoder (and its elementary encoders) live on
 };
 
 namespace {
@@ -164,6 +164,7 @@ OpusMSEncoder* create_impl(opus_int32 Fs, int channels, int streams, int coupled
     }
     if (!ok) { err = OPUS_BAD_ARG; break; }
     st->enc = (OpusEncoder**)calloc((size_t)streams, sizeof(OpusEncoder*));
+    if (cudaGetDevice(&st->device) != cudaSuccess) st->device = -1;
     if (!st->enc) { err = OPUS_ALLOC_FAIL; break; }
     for (int i = 0; i < streams; i++) {
       st->enc[i] = opus_encoder_create(Fs, i < coupled_streams ? 2 : 1, application, &err);
@@ -222,8 +223,9 @@ int encode_impl(OpusMSEncoder* st, const opus_int16* pcm16, int analysis_frame_s
   if (st->surround) {
     // masks of this frame, written into the streams' states on the device (:787-790, 862-887)
     int err = 0;
-    cudaStream_t stream = opusb_internal_stream(&err);
-    if (!stream) return err;
+    OpusbDevice* dv = opusb_device(st->device, &err);        // the GPU this encoder was created on
+    if (!dv) return err;
+    cudaStream_t stream = dv->stream;
     const size_t bytes = sizeof(opus_int16) * (size_t)frame_size * st->nb_channels;
     if (bytes > st->d_pcm_cap) {
       cudaFree(st->d_pcm);
