@@ -122,3 +122,67 @@ def sweep_cases(seed=5, count=60):
         out.append(EncCase("sweep%d" % i, fs, ch, app, frame, r.choice(KINDS), 12, ctls,
                            max_bytes=r.choice([1275, 1275, 400, 60, 20]), seed=100 + i))
     return out
+
+
+# ---- real audio (tests/golden/audio_48k_*.pcm, excerpts of the reference's AudioData; make_golden_enc_real.py) ----
+REAL_FRAMES, REAL_SPF = 250, 960
+
+
+class RealCase(object):
+    """20 ms frames of the committed real-audio excerpt through one encoder configuration.  varrate_seed != 0:
+    the bitrate is re-drawn on about every tenth frame, like the reference's ParityTest driver does
+    (CSharp/ParityTest/TestDriver.cs:219-224: random.Next(6, 510) * 1024), from a fixed seed."""
+
+    def __init__(self, name, ch, app, ctls, nframes=REAL_FRAMES, varrate_seed=0, max_bytes=1275):
+        self.name, self.ch, self.app, self.ctls, self.nframes = name, ch, app, ctls, nframes
+        self.varrate_seed, self.max_bytes = varrate_seed, max_bytes
+        self.fs, self.frame = 48000, REAL_SPF
+
+    def bitrate_schedule(self):
+        """{frame index: new bitrate}"""
+        if not self.varrate_seed:
+            return {}
+        rng = np.random.default_rng(self.varrate_seed)
+        out = {}
+        for t in range(self.nframes):
+            if rng.random() < 0.1:
+                out[t] = int(rng.integers(6, 510)) * 1024
+        return out
+
+
+def real_pcm(ch):
+    import os
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    return np.fromfile(os.path.join(here, "audio_48k_%s_5s.pcm" % ("stereo" if ch == 2 else "mono")), dtype="<i2")
+
+
+def real_cases():
+    cx10 = (SET_COMPLEXITY, 10)
+    return [
+        RealCase("st_128k_cbr", 2, LOWDELAY, [(SET_BITRATE, 128000), (SET_VBR, 0), cx10]),                 # SURVEY 8d C3
+        RealCase("st_128k_vbr", 2, LOWDELAY, [(SET_BITRATE, 128000), (SET_VBR, 1), (SET_VBR_CONSTRAINT, 0), cx10]),
+        RealCase("st_96k_cvbr", 2, LOWDELAY, [(SET_BITRATE, 96000), cx10]),
+        RealCase("st_parity", 2, AUDIO, [(SET_BITRATE, 128 * 1024), (SET_FORCE_MODE, MODE_CELT_ONLY), cx10]),  # ParityTest flavour
+        RealCase("st_varrate", 2, AUDIO, [(SET_BITRATE, 64 * 1024), (SET_FORCE_MODE, MODE_CELT_ONLY), cx10], varrate_seed=11),
+        RealCase("st_cx5_64k", 2, LOWDELAY, [(SET_BITRATE, 64000), (SET_COMPLEXITY, 5)], nframes=120),
+        RealCase("mono_64k_cbr", 1, LOWDELAY, [(SET_BITRATE, 64000), (SET_VBR, 0), cx10]),
+        RealCase("mono_parity", 1, AUDIO, [(SET_BITRATE, 64 * 1024), (SET_FORCE_MODE, MODE_CELT_ONLY), cx10]),
+        RealCase("mono_varrate", 1, LOWDELAY, [(SET_BITRATE, 48 * 1024), cx10], varrate_seed=5),
+    ]
+
+
+def c3_rotations(n, seed=1234):
+    """stream i plays the excerpt rotated by a whole number of 20 ms frames drawn from a fixed-seed
+    LCG (the reference's celt_lcg_rand constants); returns the start frame of every stream."""
+    rot = np.zeros(n, dtype=np.int64)
+    s = seed & 0xFFFFFFFF
+    for i in range(n):
+        s = (1664525 * s + 1013904223) & 0xFFFFFFFF
+        rot[i] = (s >> 8) % REAL_FRAMES
+    return rot
+
+
+def c3_rows(pcm, ch, rot, t):
+    """int16 [n, 960*ch]: frame t of every stream (frame (rot[i] + t) mod 250 of the excerpt)."""
+    frames = pcm.reshape(REAL_FRAMES, REAL_SPF * ch)
+    return np.ascontiguousarray(frames[(rot + t) % REAL_FRAMES])

@@ -226,3 +226,41 @@ def test_emu_voip_application_in_celt_mode_matches_reference(emu_enc_lib):
             a, b = ref.encode(x, frame, 1275), emu.encode(x, frame, 1275)
             assert a == b, (ch, fs, rate, force, ms10, t, a[0], b[0])
             assert a[0] > 0 and (a[1][0] & 0x80), "expected a CELT packet"
+
+
+# ---- real audio: excerpts of the reference's AudioData, packets of the reference encoder -----------------------
+REAL = {c.name: c for c in enc_cases.real_cases()}
+
+
+def real_index():
+    import json
+    return json.load(open(os.path.join(GOLDEN, "enc_real_index.json")))
+
+
+def test_real_audio_index_matches_case_list():
+    import hashlib
+    idx = real_index()
+    assert [m["name"] for m in idx] == [c.name for c in enc_cases.real_cases()]
+    for m in idx:
+        assert hashlib.md5(enc_cases.real_pcm(m["ch"]).tobytes()).hexdigest() == m["pcm_md5"]
+
+
+@pytest.mark.parametrize("name", sorted(REAL))
+def test_emu_encoder_real_audio_matches_golden(emu_enc_lib, name):
+    """Every frame of the real-audio excerpt: packet bytes and final range equal the reference encoder's
+    (the procedure of CSharp/ParityTest/TestDriver.cs:253-275, incl. its random bitrate changes :219-224)."""
+    c = REAL[name]
+    gold = read_bit(os.path.join(GOLDEN, "encr_%s.bit" % name))
+    pcm = enc_cases.real_pcm(c.ch)
+    e = EmuEncoder(emu_enc_lib, 48000, c.ch, c.app)
+    for req, val in c.ctls:
+        assert e.ctl(req, val) == 0
+    sched = c.bitrate_schedule()
+    step = c.frame * c.ch
+    for t in range(c.nframes):
+        if t in sched:
+            assert e.ctl(enc_cases.SET_BITRATE, sched[t]) == 0
+        n, pkt, rng = e.encode(pcm[t * step:(t + 1) * step], c.frame, c.max_bytes)
+        assert n == len(gold[t][0]), (name, t, n, len(gold[t][0]))
+        assert pkt == gold[t][0], (name, t)
+        assert rng == gold[t][1], (name, t)

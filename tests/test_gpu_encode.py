@@ -276,3 +276,73 @@ def test_voip_application_and_surround_stream_settings_match_reference():
         finally:
             for e in encs:
                 e.close()
+
+
+# ---- real audio (excerpts of the reference's AudioData; tests/golden/make_golden_enc_real.py) -----------------
+REAL = {c.name: c for c in enc_cases.real_cases()}
+
+
+@pytest.mark.parametrize("name", sorted(REAL))
+def test_real_audio_matches_golden(name):
+    """Every frame of the real-audio excerpt through the C ABI: packet bytes and final range equal the reference
+    encoder's (procedure of CSharp/ParityTest/TestDriver.cs:253-275 with its random bitrate changes :219-224).
+    32 copies of the stream per launch so that the batch kernel shape is the one under test."""
+    c = REAL[name]
+    gold = read_bit(os.path.join(GOLDEN, "encr_%s.bit" % name))
+    pcm = enc_cases.real_pcm(c.ch)
+    n = 32
+    be = cb.OpusBatchEncoder(n, 48000, c.ch, c.app)
+    try:
+        for req, val in c.ctls:
+            be.ctl(req, val)
+        sched = c.bitrate_schedule()
+        step = c.frame * c.ch
+        for t in range(c.nframes):
+            if t in sched:
+                be.ctl(enc_cases.SET_BITRATE, sched[t])
+            data, lens = be.encode(np.tile(pcm[t * step:(t + 1) * step], (n, 1)), c.frame, c.max_bytes)
+            assert (lens == len(gold[t][0])).all(), (name, t, lens[:4], len(gold[t][0]))
+            for i in (0, 13, 31):
+                assert data[i, :lens[i]].tobytes() == gold[t][0], (name, t, i)
+            assert (be.final_ranges() == gold[t][1]).all(), (name, t)
+    finally:
+        be.close()
+
+
+@needs_ref
+@pytest.mark.parametrize("vbr", [0, 1])
+def test_4096_real_audio_streams_every_rotation(vbr):
+    """Config 3 as SURVEY 8d C3 states it: 4096 streams, each the real-audio excerpt rotated by its own number of
+    frames, 128 kbit/s, complexity 10, 20 ms, CBR (and VBR).  EVERY distinct rotation is held to a reference
+    encoder of its own, packet bytes + final range, on every frame."""
+    n, ch, frames = 4096, 2, 10
+    pcm = enc_cases.real_pcm(ch)
+    rot = enc_cases.c3_rotations(n)
+    distinct = sorted(set(int(r) for r in rot))
+    assert len(distinct) > 200
+    first = {r: int(np.nonzero(rot == r)[0][0]) for r in distinct}
+    refs = {}
+    for r in distinct:
+        e = RefEncoder(48000, ch, enc_cases.LOWDELAY)
+        for req, val in ((enc_cases.SET_BITRATE, 128000), (enc_cases.SET_VBR, vbr), (enc_cases.SET_COMPLEXITY, 10)):
+            assert e.ctl(req, val) == 0
+        refs[r] = e
+    be = cb.OpusBatchEncoder(n, 48000, ch, enc_cases.LOWDELAY)
+    try:
+        be.ctl(enc_cases.SET_BITRATE, 128000)
+        be.ctl(enc_cases.SET_VBR, vbr)
+        be.ctl(enc_cases.SET_COMPLEXITY, 10)
+        for t in range(frames):
+            rows = enc_cases.c3_rows(pcm, ch, rot, t)
+            data, lens = be.encode(rows, 960, 1275)
+            fr = be.final_ranges()
+            for r in distinct:
+                i = first[r]
+                rn, rpkt, rrng = refs[r].encode(rows[i], 960, 1275)
+                same = np.nonzero(rot == r)[0]
+                assert (lens[same] == rn).all(), (t, r, lens[same][:4], rn)
+                for j in same:
+                    assert data[j, :rn].tobytes() == rpkt, (t, r, int(j))
+                assert (fr[same] == rrng).all(), (t, r)
+    finally:
+        be.close()

@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 import concentus_b200 as cb
-from conftest import GOLDEN, RefDecoder, crc32, golden_case, needs_ref, read_bit, silk_golden_index
+from conftest import GOLDEN, RefDecoder, crc32, golden_case, have_ref, needs_ref, read_bit, silk_golden_index
 from scenarios import silk_calls, silk_fuzz_calls
 from test_emu_silk import TRANSITION_SCRIPTS, scripted_packets, silk_packets
 
@@ -93,25 +93,37 @@ def test_batch_of_streams_changing_mode(fs, ch, ms):
         bd.close()
 
 
-def test_full_size_silk_batch_properties():
-    """Config-4 size: 16384 mono 16 kHz streams, 20 ms.  The streams replay the golden fixture from 64
-    different start offsets; every stream's PCM must equal the golden CRC of the packet it decoded once its
-    history matches (a stream that starts at packet 0), and copies must agree with each other."""
-    meta = silk_golden_index()["silk_wb_mono_32k"]
-    pk = [p for p, _ in read_bit(os.path.join(GOLDEN, "silk_wb_mono_32k.bit"))]
-    n, steps = 16384, 6
-    bd = cb.OpusBatchDecoder(16000, 1, n)
+def _full_size_rotations(name, fs, fsz, n, steps):
+    """16384 streams replay a golden fixture from 64 different start offsets.  Every one of the 64 distinct
+    histories is held to a reference decoder of its own (PCM, return value, final range), every copy of it must
+    agree, and the stream that starts at packet 0 must also reproduce the golden CRCs."""
+    meta = silk_golden_index()[name]
+    pk = [p for p, _ in read_bit(os.path.join(GOLDEN, name + ".bit"))]
+    bd = cb.OpusBatchDecoder(fs, 1, n)
+    refs = [RefDecoder(fs, 1) for _ in range(64)] if have_ref() else None
     try:
         rot = (3 * (np.arange(n) % 64))
         for t in range(steps):
             pkts = [pk[(rot[i] + t) % len(pk)] for i in range(n)]
-            ret, pcm = bd.decode(pkts, 320)
-            assert (ret == 320).all()
+            ret, pcm = bd.decode(pkts, fsz)
+            assert (ret == fsz).all()
+            fr = bd.final_ranges()
             for i in range(64):
                 assert (pcm[i::64] == pcm[i]).all(), (t, i)
+                assert (fr[i::64] == fr[i]).all(), (t, i)
+                if refs is not None:
+                    r1, p1 = refs[i].decode_raw(pkts[i], fsz)
+                    assert r1 == fsz
+                    assert np.array_equal(pcm[i], p1[:fsz]), (t, i)
+                    assert int(fr[i]) == refs[i].final_range, (t, i)
             assert crc32(pcm[0]) == meta["pcm_crc32"][t], t       # stream 0 plays the fixture from its start
     finally:
         bd.close()
+
+
+def test_full_size_silk_batch_properties():
+    """Config-4 size: 16384 mono 16 kHz SILK wideband streams, 20 ms (thread-per-stream kernel at full size)."""
+    _full_size_rotations("silk_wb_mono_32k", 16000, 320, 16384, 6)
 
 
 @needs_ref
@@ -177,21 +189,6 @@ def test_batch_of_corrupted_streams_follows_reference(fs, ch):
 
 
 def test_full_size_hybrid_batch_properties():
-    """The hybrid set of config 4 at full size: 16384 mono 48 kHz streams of hybrid fullband packets.  Streams
-    replay the golden fixture from 64 start offsets; copies must agree with each other and the stream that
-    starts at packet 0 must reproduce the golden CRCs (SILK kernel + CELT layer kernels at full occupancy)."""
-    meta = silk_golden_index()["hyb_fb_mono_32k"]
-    pk = [p for p, _ in read_bit(os.path.join(GOLDEN, "hyb_fb_mono_32k.bit"))]
-    n, steps = 16384, 5
-    bd = cb.OpusBatchDecoder(48000, 1, n)
-    try:
-        rot = (3 * (np.arange(n) % 64))
-        for t in range(steps):
-            pkts = [pk[(rot[i] + t) % len(pk)] for i in range(n)]
-            ret, pcm = bd.decode(pkts, 960)
-            assert (ret == 960).all()
-            for i in range(64):
-                assert (pcm[i::64] == pcm[i]).all(), (t, i)
-            assert crc32(pcm[0]) == meta["pcm_crc32"][t], t
-    finally:
-        bd.close()
+    """The hybrid set of config 4 at full size: 16384 mono 48 kHz streams of hybrid fullband packets (SILK kernel +
+    CELT layer kernels at full occupancy)."""
+    _full_size_rotations("hyb_fb_mono_32k", 48000, 960, 16384, 5)
