@@ -5,6 +5,8 @@
  * Usage: ref_bench <file.bit> <Fs> <channels> <streams> <frames> <threads> [ms_streams ms_coupled mapping,csv]
  * With the three optional arguments the decoders are OpusMSDecoder objects of that layout
  * (opus_multistream_decode; zero-length records of the fixture are lost packets).
+ * Decoder objects are created before the clock starts and destroyed after it stops: the timed region holds
+ * decode calls only.
  * Prints one line: stream_seconds wall_seconds threads checksum
  */
 #include <pthread.h>
@@ -21,16 +23,25 @@ static Packet *g_pk; static int g_count;
 static int g_fs, g_ch, g_frames;
 static int g_ms_streams, g_ms_coupled;
 static unsigned char g_mapping[256];
-typedef struct { int first, last; uint32_t sum; double audio; } Job;
+typedef struct { int first, last; uint32_t sum; double audio; void **dec; } Job;
+static pthread_barrier_t g_start;
 
 static void *worker(void *arg) {
   Job *job = (Job *)arg;
   int err, i, t, k;
   opus_int16 *pcm = (opus_int16 *)malloc(sizeof(opus_int16) * 5760 * g_ch);
   uint32_t sum = 0;
+  job->dec = (void **)calloc(job->last - job->first + 1, sizeof(void *));
+  for (i = job->first; i < job->last; i++) {
+    job->dec[i - job->first] = g_ms_streams
+        ? (void *)opus_multistream_decoder_create(g_fs, g_ch, g_ms_streams, g_ms_coupled, g_mapping, &err)
+        : (void *)opus_decoder_create(g_fs, g_ch, &err);
+    if (!job->dec[i - job->first]) { fprintf(stderr, "create failed\n"); exit(1); }
+  }
+  pthread_barrier_wait(&g_start);          /* main takes t0 after this barrier */
+  pthread_barrier_wait(&g_start);
   for (i = job->first; g_ms_streams && i < job->last; i++) {
-    OpusMSDecoder *dec = opus_multistream_decoder_create(g_fs, g_ch, g_ms_streams, g_ms_coupled, g_mapping, &err);
-    if (!dec) { fprintf(stderr, "create failed\n"); exit(1); }
+    OpusMSDecoder *dec = (OpusMSDecoder *)job->dec[i - job->first];
     for (t = 0; t < g_frames; t++) {
       Packet *p = &g_pk[(37 * i + t) % g_count];
       int ret = opus_multistream_decode(dec, p->len ? p->data : NULL, p->len, pcm, p->len ? 5760 : g_fs / 50, 0);
@@ -38,11 +49,9 @@ static void *worker(void *arg) {
       for (k = 0; k < ret * g_ch; k += 97) sum = sum * 31u + (uint16_t)pcm[k];
       job->audio += (double)ret / g_fs;
     }
-    opus_multistream_decoder_destroy(dec);
   }
   for (i = job->first; !g_ms_streams && i < job->last; i++) {
-    OpusDecoder *dec = opus_decoder_create(g_fs, g_ch, &err);
-    if (!dec) { fprintf(stderr, "create failed\n"); exit(1); }
+    OpusDecoder *dec = (OpusDecoder *)job->dec[i - job->first];
     for (t = 0; t < g_frames; t++) {
       Packet *p = &g_pk[(37 * i + t) % g_count];
       int ret = opus_decode(dec, p->data, p->len, pcm, 5760, 0);
@@ -50,9 +59,14 @@ static void *worker(void *arg) {
       for (k = 0; k < ret * g_ch; k += 97) sum = sum * 31u + (uint16_t)pcm[k];
       job->audio += (double)ret / g_fs;
     }
-    opus_decoder_destroy(dec);
   }
   job->sum = sum;
+  pthread_barrier_wait(&g_start);          /* main takes t1 after this barrier */
+  for (i = job->first; i < job->last; i++) {
+    if (g_ms_streams) opus_multistream_decoder_destroy((OpusMSDecoder *)job->dec[i - job->first]);
+    else opus_decoder_destroy((OpusDecoder *)job->dec[i - job->first]);
+  }
+  free(job->dec);
   free(pcm);
   return NULL;
 }
@@ -87,15 +101,19 @@ int main(int argc, char **argv) {
   pthread_t *th = (pthread_t *)malloc(sizeof(pthread_t) * T);
   Job *jobs = (Job *)calloc(T, sizeof(Job));
   struct timespec t0, t1;
-  clock_gettime(CLOCK_MONOTONIC, &t0);
+  pthread_barrier_init(&g_start, NULL, T + 1);
   for (int i = 0; i < T; i++) {
     jobs[i].first = (int)((long long)streams * i / T);
     jobs[i].last = (int)((long long)streams * (i + 1) / T);
     pthread_create(&th[i], NULL, worker, &jobs[i]);
   }
+  pthread_barrier_wait(&g_start);          /* every decoder exists */
+  clock_gettime(CLOCK_MONOTONIC, &t0);
+  pthread_barrier_wait(&g_start);          /* go */
+  pthread_barrier_wait(&g_start);          /* every frame decoded */
+  clock_gettime(CLOCK_MONOTONIC, &t1);
   double audio = 0; uint32_t sum = 0;
   for (int i = 0; i < T; i++) { pthread_join(th[i], NULL); audio += jobs[i].audio; sum ^= jobs[i].sum; }
-  clock_gettime(CLOCK_MONOTONIC, &t1);
   double wall = (t1.tv_sec - t0.tv_sec) + 1e-9 * (t1.tv_nsec - t0.tv_nsec);
   printf("%.6f %.6f %d %08x\n", audio, wall, T, sum);
   return 0;

@@ -32,6 +32,9 @@ CASES = [
     ("swb_48k_st", 48000, 2, 2, ["48000", "-bandwidth", "SWB", "-complexity", "10", "-framesize", "20"], "48Khz Stereo.raw", 250),
     ("wb_40k_f10_st", 48000, 2, 2, ["40000", "-bandwidth", "WB", "-complexity", "10", "-framesize", "10"], "48Khz Stereo.raw", 0),
     ("nb_20k_mono", 48000, 1, 1, ["20000", "-bandwidth", "NB", "-complexity", "10", "-framesize", "20"], "48Khz Mono.raw", 300),
+    # two more rates for the mixed-bitrate batch of bench.py --config 2het
+    ("het_64k_cbr_st", 48000, 2, 2, ["64000", "-cbr", "-complexity", "10", "-framesize", "20"], "48Khz Stereo.raw", 450),
+    ("het_96k_vbr_st", 48000, 2, 2, ["96000", "-complexity", "10", "-framesize", "20"], "48Khz Stereo.raw", 550),
     # decoder channel count / rate different from the stream's
     ("st_to_mono_out", 48000, 1, 2, ["64000", "-complexity", "10", "-framesize", "20"], "48Khz Stereo.raw", 100),
     ("mono_to_st_out", 48000, 2, 1, ["48000", "-complexity", "10", "-framesize", "20"], "48Khz Mono.raw", 100),
