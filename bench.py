@@ -159,7 +159,7 @@ DECODE_SPECS = {
                  workload="batched CELT decode: 4096 x 48 kHz stereo streams, independently encoded at 64 / 96 / 128 kbps, "
                           "CBR and VBR, a tenth of them with 10 ms frames (config 2, heterogeneous variant)",
                  data="synthetic: rotations of six reference-encoded streams of different rates (tests/golden)", ncu=None),
-    "4": dict(fs=16000, ch=1, n=16384, fixtures=[("silk_wb_mono_32k", 1.0)], index="index_silk.json",
+    "4": dict(fs=16000, ch=1, n=16384, fixtures=[("silk_wb_mono_32k", 1.0)], index="index_silk.json", in_order=True,
               metric="aggregate realtime stream-sec/sec (16k mono SILK decode)",
               workload="batched SILK decode: 16384 x 16 kHz mono 32 kbps 20 ms streams (config 4)",
               data="synthetic: rotations of one reference-encoded stream (tests/golden/silk_wb_mono_32k.bit)",
@@ -225,6 +225,8 @@ class DecodeWorkload(object):
         self.offs = (np.arange(n, dtype=np.int32) * self.maxlen).astype(np.int32)
         self.total_steps = total_steps
         self.use_ref = use_ref
+        # distinct packet arenas the steps cycle through: one per packet of the longest fixture, at least 140 MB in all
+        self.nbuf = max(int(self.npk.max()), -(-140000000 // (n * self.maxlen)))
         if not gpu:                                            # the reference arm only wants describe()
             return
         import torch
@@ -235,7 +237,7 @@ class DecodeWorkload(object):
         self.d_off = torch.from_numpy(self.offs).cuda()
         self.d_ret = torch.zeros(n, dtype=torch.int32, device="cuda")
         self.d_pcm = [torch.zeros(n * self.fsz * self.ch, dtype=torch.int16, device="cuda") for _ in range(2)]
-        nbuf = min(total_steps, int(self.npk.max()))
+        nbuf = self.nbuf
         self.h_in = []
         for t in range(nbuf):
             a, l = self.inputs(t)
@@ -257,14 +259,35 @@ class DecodeWorkload(object):
         return np.ascontiguousarray(self.table[idx]).reshape(-1), self.plen[idx].copy()
 
     # ---- device-resident call ----
-    def step_device(self, t):
+    def step_device(self, t, own_stream=True):
+        """own_stream: queue on this bench's CUDA stream (calls run in order); else on the library's streams, where
+        consecutive calls are pipelined (the parse side of a call runs beside the rebuild / synthesis of the one before)."""
         a, l = self.d_in[t % len(self.d_in)]
         rc = self.lib.opus_decode_group_device(self.bd._g, a.data_ptr(), self.d_off.data_ptr(), l.data_ptr(),
                                                self.d_pcm[t & 1].data_ptr(), self.fsz * self.ch, self.fsz, None,
                                                self.d_ret.data_ptr(), 1, self.maxlen,
-                                               ctypes.c_void_p(self.stream.cuda_stream))
+                                               ctypes.c_void_p(self.stream.cuda_stream) if own_stream else None)
         if rc != 0:
             raise RuntimeError("opus_decode_group_device failed: %d" % rc)
+
+    def timed_pipelined(self, K):
+        """K device-resident steps on the library's own streams, one timing mark before and one after.  Every step
+        reads its own packet arena (len(self.d_in) distinct ones, larger than L2 together)."""
+        self.torch.cuda.synchronize()
+        for _ in range(3):
+            self.step_device(self.t, own_stream=False)
+            self.t += 1
+        assert self.lib.opus_b200_synchronize() == 0
+        assert self.lib.opus_b200_timer_mark(0) == 0
+        for _ in range(K):
+            self.step_device(self.t, own_stream=False)
+            self.t += 1
+        assert self.lib.opus_b200_timer_mark(1) == 0
+        ms = ctypes.c_double(0)
+        assert self.lib.opus_b200_timer_elapsed(0, 1, ctypes.byref(ms)) == 0
+        assert self.lib.opus_b200_synchronize() == 0
+        self.check_ret("pipelined device-resident steps")
+        return ms.value
 
     def check_ret(self, where):
         bad = int((self.d_ret != self.d_expect).sum().item())
@@ -346,18 +369,18 @@ class DecodeWorkload(object):
                 flush.fill_(k & 0xFF)
                 self.step_device(self.t)
                 self.t += 1
-        ms3 = (ctypes.c_double * 3)()
-        cnt3 = (ctypes.c_longlong * 3)()
-        self.lib.opus_b200_profile_end(ms3, cnt3)
-        return {"plan_silk": ms3[0] / max(1, cnt3[0]), "celt_entropy": ms3[1] / max(1, cnt3[1]),
-                "celt_synth": ms3[2] / max(1, cnt3[2])}
+        ms4 = (ctypes.c_double * 4)()
+        cnt4 = (ctypes.c_longlong * 4)()
+        self.lib.opus_b200_profile_end(ms4, cnt4)
+        return {"plan_silk": ms4[0] / max(1, cnt4[0]), "celt_parse": ms4[1] / max(1, cnt4[1]),
+                "celt_rebuild": ms4[2] / max(1, cnt4[2]), "celt_synth": ms4[3] / max(1, cnt4[3])}
 
     # ---- host-buffer calls ----
     def _host_bufs(self):
         if not hasattr(self, "h_pcm"):
             torch = self.torch
-            self.h_pcm = [torch.zeros(self.n * self.fsz * self.ch, dtype=torch.int16).pin_memory() for _ in range(3)]
-            self.h_ret = [torch.zeros(self.n, dtype=torch.int32).pin_memory() for _ in range(3)]
+            self.h_pcm = [torch.zeros(self.n * self.fsz * self.ch, dtype=torch.int16).pin_memory() for _ in range(4)]
+            self.h_ret = [torch.zeros(self.n, dtype=torch.int32).pin_memory() for _ in range(4)]
             self.h_expect = torch.from_numpy(self.expect)
 
     def _call(self, fn, t, slot):
@@ -379,17 +402,17 @@ class DecodeWorkload(object):
 
     def e2e_pipelined(self, K, barrier=None):
         self._host_bufs()
-        for k in range(3):                                   # warm-up of the pipelined entry (it allocates its two slots)
-            assert self._call(self.lib.opus_decode_group_submit, self.t, k % 3) == 0
+        for k in range(4):                                   # warm-up of the pipelined entry (it allocates its slots)
+            assert self._call(self.lib.opus_decode_group_submit, self.t, k % 4) == 0
             self.t += 1
         assert self.lib.opus_decode_group_wait(self.bd._g) == 0
         if barrier:
             barrier()
         e0 = time.perf_counter()
         for k in range(K):
-            assert self._call(self.lib.opus_decode_group_submit, self.t, k % 3) == 0
-            if k >= 2:
-                assert bool((self.h_ret[(k - 2) % 3] == self.h_expect).all())   # call k-2 completed before submit k returned
+            assert self._call(self.lib.opus_decode_group_submit, self.t, k % 4) == 0
+            if k >= 3:
+                assert bool((self.h_ret[(k - 3) % 4] == self.h_expect).all())   # call k-3 completed before submit k returned
             self.t += 1
         assert self.lib.opus_decode_group_wait(self.bd._g) == 0
         e1 = time.perf_counter()
@@ -401,16 +424,25 @@ class DecodeWorkload(object):
         pcm_bytes = float(self.expect.mean()) * self.ch * 2
         cfg = {"workload": self.spec["workload"], "streams_per_gpu": self.n, "frame_ms": 20,
                "mean_packet_bytes": mean_len,
-               "l2": "flushed between timed steps (256 MiB write, outside the event pair)",
                "step": "one packet of every stream"}
+        if self.spec.get("in_order"):
+            cfg["l2"] = "flushed between timed steps (256 MiB write, outside the event pair)"
+            cfg["device_resident_calls"] = "queued in order on the bench's stream (opus_decode_group_device with a stream)"
+        else:
+            cfg["l2"] = ("inputs larger than L2: every step reads its own packet arena from HBM (%d arenas, %.0f MB); the "
+                         "decoders' state is the streams' own working set.  isolated_steps gives the per-step figure with L2 "
+                         "flushed between steps" % (self.nbuf, self.nbuf * self.n * self.maxlen / 1e6))
+            cfg["device_resident_calls"] = ("queued back to back on the library's streams (opus_decode_group_device, cuda_stream "
+                                            "NULL): the parse side of a call runs beside the rebuild / synthesis of the call before")
         if len(self.names) > 1:
             cfg["mix"] = {nm: int((self.fix == k).sum()) for k, nm in enumerate(self.names)}
         return dict(metric=self.spec["metric"], data=self.spec["data"], config=cfg,
                     alg_bytes=int(self.n * (mean_len + pcm_bytes)),
                     h2d=int(self.n * self.maxlen + 3 * 4 * self.n), d2h=int(self.n * self.fsz * self.ch * 2 + 4 * self.n),
-                    api="opus_decode_group_submit/_wait (pinned host buffers, two calls in flight)",
+                    api="opus_decode_group_submit/_wait (pinned host buffers, three calls in flight)",
                     sync_api="opus_decode_group_flat",
-                    kernels={"plan_silk": "plan_silk_kernel", "celt_entropy": "celt_entropy_kernel", "celt_synth": "celt_synth_kernel"},
+                    kernels={"plan_silk": "plan_silk_kernel", "celt_parse": "celt_parse_kernel",
+                             "celt_rebuild": "celt_rebuild_kernel", "celt_synth": "celt_synth_kernel"},
                     ncu=self.spec.get("ncu"))
 
     def close(self):
@@ -614,8 +646,8 @@ class MSWorkload(object):
                                 torch.from_numpy(offs).pin_memory(), torch.from_numpy(lens).pin_memory()))
         m = self.meta
         self.bd = cb.OpusMSBatchDecoder(self.FS, self.CH, m["streams"], m["coupled"], m["mapping"], n)
-        self.h_pcm = [torch.zeros(n * self.SPF * self.CH, dtype=torch.int16).pin_memory() for _ in range(3)]
-        self.h_ret = [torch.zeros(n, dtype=torch.int32).pin_memory() for _ in range(3)]
+        self.h_pcm = [torch.zeros(n * self.SPF * self.CH, dtype=torch.int16).pin_memory() for _ in range(4)]
+        self.h_ret = [torch.zeros(n, dtype=torch.int32).pin_memory() for _ in range(4)]
         self.t = 0
 
     def _call(self, fn, t, slot):
@@ -681,10 +713,10 @@ class MSWorkload(object):
         for _ in range(K):
             assert self._call(self.lib.opus_multistream_decode_group_flat, self.t, 0) == 0
             self.t += 1
-        ms3 = (ctypes.c_double * 3)()
-        cnt3 = (ctypes.c_longlong * 3)()
-        self.lib.opus_b200_profile_end(ms3, cnt3)
-        return {"celt_entropy": ms3[1] / K, "celt_synth": ms3[2] / K}
+        ms4 = (ctypes.c_double * 4)()
+        cnt4 = (ctypes.c_longlong * 4)()
+        self.lib.opus_b200_profile_end(ms4, cnt4)
+        return {"celt_parse": ms4[1] / K, "celt_rebuild": ms4[2] / K, "celt_synth": ms4[3] / K}
 
     def e2e_sync(self, K):
         s0 = time.perf_counter()
@@ -696,17 +728,17 @@ class MSWorkload(object):
 
     def e2e_pipelined(self, K, barrier=None):
         fn = self.lib.opus_multistream_decode_group_submit
-        for k in range(3):
-            assert self._call(fn, self.t, k % 3) == 0
+        for k in range(4):
+            assert self._call(fn, self.t, k % 4) == 0
             self.t += 1
         assert self.lib.opus_multistream_decode_group_wait(self.bd._g) == 0
         if barrier:
             barrier()
         e0 = time.perf_counter()
         for k in range(K):
-            assert self._call(fn, self.t, k % 3) == 0
-            if k >= 2:
-                assert bool((self.h_ret[(k - 2) % 3] == self.SPF).all())
+            assert self._call(fn, self.t, k % 4) == 0
+            if k >= 3:
+                assert bool((self.h_ret[(k - 3) % 4] == self.SPF).all())
             self.t += 1
         assert self.lib.opus_multistream_decode_group_wait(self.bd._g) == 0
         e1 = time.perf_counter()
@@ -723,9 +755,10 @@ class MSWorkload(object):
                             "step": "one 20 ms frame of every decoder"},
                     alg_bytes=int(self.n * (mean_len + self.SPF * self.CH * 2)),
                     h2d=int(self.n * self.maxlen + 12 * self.n), d2h=int(self.n * self.SPF * self.CH * 2 + 4 * self.n),
-                    api="opus_multistream_decode_group_submit/_wait (pinned host buffers, two calls in flight)",
+                    api="opus_multistream_decode_group_submit/_wait (pinned host buffers, three calls in flight)",
                     sync_api="opus_multistream_decode_group_flat",
-                    kernels={"celt_entropy": "celt_entropy_kernel", "celt_synth": "celt_synth_kernel"}, ncu=None)
+                    kernels={"celt_parse": "celt_parse_kernel", "celt_rebuild": "celt_rebuild_kernel",
+                             "celt_synth": "celt_synth_kernel"}, ncu=None)
 
     def close(self):
         self.bd.close()
@@ -931,10 +964,20 @@ def main():
     wall1 = time.perf_counter()
     launches = lib.opus_b200_launch_count() - launches0
     kern_ms = {}
+    isolated = None
     if wl.kind == "decode":
-        dev_ms = float(sum(a.elapsed_time(b) for a, b in timed))
+        iso_ms = float(sum(a.elapsed_time(b) for a, b in timed))
         wl.check_ret("timed region")
+        isolated = {"ms_per_step": iso_ms / K,
+                    "what": "each step alone on one stream, L2 flushed between steps (256 MiB write outside the event pair)"}
         kern_ms = wl.profile(min(K, 50), flush)
+        barrier()
+        if wl.spec.get("in_order"):
+            # SILK-only packets have no parse work for the run-ahead to hide: the device-resident calls go on the
+            # bench's own stream, in order, and `value` is the per-step figure (L2 flushed between steps)
+            dev_ms = iso_ms
+        else:
+            dev_ms = wl.timed_pipelined(K)
     elif wl.kind == "encode":
         dev_ms, cnt = timed
         kern_ms = {"encode": dev_ms / max(1, cnt)}
@@ -959,8 +1002,14 @@ def main():
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dev_ms, e2e_s, e2e_sync_s = float(tt[0].item()), float(tt[1].item()), float(tt[2].item())
 
+    if world > 1 and isolated is not None:
+        tt = torch.tensor([isolated["ms_per_step"]], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        isolated["ms_per_step"] = float(tt[0].item())
     d = wl.describe()
     units = wl.units_per_step
+    if isolated is not None:
+        isolated["value"] = world * units / (isolated["ms_per_step"] * 1e-3)
     value = world * units * K / (dev_ms * 1e-3)
     e2e_value = world * units * K / e2e_s
     peak, peak_kind = peaks()
@@ -976,6 +1025,7 @@ def main():
         "gpu_launches": int(launches),
         "clocks": sampler.summary(),
         "parity_gate": gate,
+        "isolated_steps": isolated,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": ncu_traffic(d["ncu"]) if d["ncu"] else None, "peak_kind": peak_kind,
                      "kernel": d["kernels"][dom], "kernel_ms": kern_ms, "algorithmic_bytes_per_launch": d["alg_bytes"],

@@ -52,7 +52,9 @@ EXPORTS = [
     "opus_decoder_group_destroy", "opus_decode_group_flat", "opus_decode_group_device",
     "opus_decode_group_submit", "opus_decode_group_wait", "opus_encode_group_submit", "opus_encode_group_wait",
     "opus_decoder_get_final_range_batch", "opus_b200_synchronize", "opus_b200_launch_count",
-    "opus_b200_profile_begin", "opus_b200_profile_end", "opus_decode_batch_device_static",
+    "opus_b200_profile_begin", "opus_b200_profile_end", "opus_b200_timer_mark", "opus_b200_timer_elapsed",
+    "opus_b200_trace_begin", "opus_b200_trace_end",
+    "opus_decode_batch_device_static",
     "opus_multistream_decoder_get_size", "opus_multistream_decoder_create", "opus_multistream_decode",
     "opus_multistream_decode_float", "opus_multistream_decoder_ctl", "opus_multistream_decoder_destroy",
     "opus_multistream_decode_batch", "opus_multistream_decoder_group_create",
@@ -312,7 +314,7 @@ class OpusBatchDecoder(object):
                                              frame_size * self.channels, frame_size, _ptr(fec_a), _ptr(ret))
         if rc != OPUS_OK:
             raise OpusError(rc, "opus_decode_group_submit")
-        self._keep = (getattr(self, "_keep", ()) + ((arena, offs, lens, fec_a, pcm, ret),))[-2:]
+        self._keep = (getattr(self, "_keep", ()) + ((arena, offs, lens, fec_a, pcm, ret),))[-3:]
 
     def wait(self):
         rc = load().opus_decode_group_wait(self._g)

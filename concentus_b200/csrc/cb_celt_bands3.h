@@ -1,42 +1,86 @@
 // cb_celt_bands3.h -- quant_all_bands, decoder side (bands.c:1337-1502), as three phases per frame:
 //
 //   1. PARSE   the range decoder walks bands / stereo splits / partitions exactly as the reference
-//              does, but touches no spectrum: it notes the shape of the recursion on a small tape
-//              (split angles, a bit per node) and, for every leaf that carries pulses, the PVQ index
-//              and its parameters -- written into the leaf's own (still unused) slot of X.
+//              does, but touches no spectrum: it writes the shape of the recursion on a TAPE (FrameTape,
+//              cb_state.h: split angles as 16-bit notes, a bit per node) and, for every leaf that carries
+//              pulses, a job record (PVQ index and its parameters).  Nothing in this phase has any width,
+//              so it runs either warp-uniform or -- in the parse kernel (cb_parse_kernels.cu) -- ONE
+//              THREAD PER STREAM, 32 streams to a warp.
 //   2. PULSES  the leaves are independent of each other: ONE LANE PER LEAF turns index -> pulse vector
 //              (cwrsi is a serial walk), normalises, applies the spreading rotation and leaves the
-//              collapse mask.  32 leaves at a time instead of one after the other on a uniform warp.
+//              collapse mask.
 //   3. REBUILD the same walk again, driven by the tape instead of the bitstream: folding / noise fill
 //              of the empty leaves, Hadamard / Haar recombination, stereo merge, lowband for the bands
 //              to come -- the lane-parallel vector work.
 //
 // Nothing the decoder reads from the bitstream depends on the spectrum (collapse masks and folding
 // only steer reconstruction), which is what makes the split legal.  Phases 1 and 3 are one piece of
-// code (template <bool REBUILD>), so the two walks cannot drift apart.  When the tape or the job list
-// cannot take another band, the bands parsed so far are finished (phases 2 + 3) and parsing resumes.
+// code (template <bool REBUILD>), so the two walks cannot drift apart.  The tape is cut into segments
+// (runs of bands) whose notes and masks fit the rebuild warp's shared memory; phases 2 + 3 go segment by
+// segment.
 #pragma once
 
-#define CB_B3_MIN_N 6           // a deferred leaf keeps its 6-word record in its own X slot
+#define CB_B3_SEG_BITS (32 * CB_B3_BITWORDS)
 
-struct B3Cur {                  // cursors of the tape: written by PARSE, read by REBUILD (uniform registers)
+// Writer side of the tape (PARSE): cursors in registers, the tape itself in global memory.  Node bits are
+// collected in a register and stored a word at a time.
+struct TapeW {
+  FrameTape* t;
+  int jobs, notes, bitwords;        // totals written so far
+  int seg_jobs, seg_notes;          // counts inside the open segment
+  int seg_bits;                     // bits inside the open segment (its words start at bitwords - seg_bits / 32)
+  u32 acc;                          // the partly filled word
+  int nseg, seg_band0;
+};
+// Reader side (REBUILD): cursors into the segment's copy in shared memory
+struct B3Cur {
   int jobs, tape, bits;
+  TapeW* tw;                        // PARSE only
 };
 
-CB_FN void b3_push_bit(EntWork& w, B3Cur& c, int v) {
-  if (v) w.b3_bits[c.bits >> 5] |= 1u << (c.bits & 31);
-  c.bits++;
+CB_FN void b3_push_bit(EntWork&, B3Cur& c, int v) {
+  TapeW& tw = *c.tw;
+  tw.acc |= (u32)(v != 0) << (tw.seg_bits & 31);
+  tw.seg_bits++;
+  if ((tw.seg_bits & 31) == 0) {
+    tw.t->bits[tw.bitwords++] = tw.acc;
+    tw.acc = 0;
+  }
 }
 CB_FN int b3_pop_bit(const EntWork& w, B3Cur& c) {
   const int v = (w.b3_bits[c.bits >> 5] >> (c.bits & 31)) & 1;
   c.bits++;
   return v;
 }
-CB_FN void b3_push(EntWork& w, B3Cur& c, int v) { w.b3_buf[CB_B3_BUF - 1 - c.tape++] = (u16)v; }
+CB_FN void b3_push(EntWork&, B3Cur& c, int v) {
+  TapeW& tw = *c.tw;
+  tw.t->notes[tw.notes++] = (u16)v;
+  tw.seg_notes++;
+}
 CB_FN int b3_pop(const EntWork& w, B3Cur& c) { return w.b3_buf[CB_B3_BUF - 1 - c.tape++]; }
+CB_FN void b3_push_job(B3Cur& c, int xoff, int N, int K, u32 idx, i32 gain, int B, int spread) {
+  TapeW& tw = *c.tw;
+  TapeJob jb;
+  jb.idx = idx; jb.xoff = (u16)xoff; jb.N = (i16)N; jb.K = (i16)K; jb.gain = (i16)gain; jb.B = (u8)B; jb.spread = (u8)spread;
+  tw.t->jobs[tw.jobs++] = jb;
+  tw.seg_jobs++;
+}
+// close the open segment at band `band` (exclusive end) and start the next one there
+CB_FN void b3_close_segment(TapeW& tw, int band) {
+  if (tw.seg_bits & 31) {                       // the partly filled word; the next segment starts on a fresh one
+    tw.t->bits[tw.bitwords++] = tw.acc;
+    tw.acc = 0;
+  }
+  TapeSeg sg;
+  sg.band0 = (u8)tw.seg_band0; sg.band1 = (u8)band;
+  sg.jobs = (u16)tw.seg_jobs; sg.notes = (u16)tw.seg_notes; sg.bitwords = (u16)((tw.seg_bits + 31) >> 5);
+  tw.t->seg[tw.nseg++] = sg;
+  tw.seg_jobs = tw.seg_notes = tw.seg_bits = 0;
+  tw.seg_band0 = band;
+}
 // Upper bounds of what one band can add: L = most leaves of one channel's partition tree (a node splits
-// while LM >= 0 and N > 2); per channel L - 1 split angles and L leaves (a pending-leaf entry or a mask
-// each), plus the stereo angle; per node a split bit, per split an order bit, per leaf two bits.
+// while LM >= 0 and N > 2); per channel L - 1 split angles and L leaves (a job and a mask each), plus the
+// stereo angle; per node a split bit, per split an order bit, per leaf one bit, a few per band.
 CB_FN int b3_band_leaves(int N, int LM) {
   int L = 1;
   CB_NOUNROLL while (LM >= 0 && N > 2) { L <<= 1; N >>= 1; LM--; }
@@ -156,53 +200,20 @@ CB_FN u32 b3_leaf(i16* X, int N, int K, u32 idx, i32 gain, int B, int spread) {
   }
   return mask;
 }
-// record of a deferred leaf, kept in the leaf's own X slot until its lane picks it up
-CB_FN void b3_put_job(i16* X, int N, int K, u32 idx, i32 gain, int B, int spread) {
-  X[0] = (i16)(idx & 0xFFFF);
-  X[1] = (i16)(idx >> 16);
-  X[2] = (i16)N;
-  X[3] = (i16)K;
-  X[4] = (i16)gain;
-  X[5] = (i16)(B | (spread << 8));
-}
-// Phase 2: lanes take the pending leaves of w.b3_buf[0..njobs); the entry becomes the collapse mask.
-CB_FN void b3_run_jobs(EntWork& w, int njobs) {
+// Phase 2: lanes take the segment's jobs (records in the tape, global memory); the collapse mask of job j
+// goes to w.b3_buf[j].
+CB_FN void b3_run_jobs(EntWork& w, const TapeJob* jobs, int njobs) {
   CB_WSYNC();
   CB_LANE_LOOP(j, njobs) {
-    i16* X = w.X + w.b3_buf[j];
-    const u32 idx = (u32)(u16)X[0] | ((u32)(u16)X[1] << 16);
-    const int N = X[2], K = X[3];
-    const i32 gain = X[4];
-    const int B = X[5] & 0xFF, spread = (X[5] >> 8) & 0xFF;
-    w.b3_buf[j] = (u16)b3_leaf(X, N, K, idx, gain, B, spread);
+    const TapeJob jb = jobs[j];
+    w.b3_buf[j] = (u16)b3_leaf(w.X + jb.xoff, jb.N, jb.K, jb.idx, jb.gain, jb.B, jb.spread);
   }
   CB_WSYNC();
-}
-
-// alg_unquant for a leaf too small to carry its record (N < 6): decoded at once, warp-uniform as before
-CB_FN u32 b3_leaf_now(EntWork& w, i16* X, int N, int K, u32 idx, int spread, int B, i32 gain) {
-  i16* iy = (i16*)w.tmp32;
-  CB_WSYNC();
-  const i32 Ryy = pvq_decode(iy, N, K, idx);
-  CB_WSYNC();
-  const int k = cb_ilog2(Ryy) >> 1;
-  const i32 t = vshr32(Ryy, 2 * (k - 7));
-  const i16 g = (i16)mult16_16_p15(cb_rsqrt_norm(t), gain);
-  u32 mask = 0;
-  const int N0 = N / B;
-  CB_LANE_LOOP(j, N) {
-    const i32 v = iy[j];
-    X[j] = ext16(pshr32(mult16_16(g, v), k + 1));
-    if (v != 0) mask |= 1u << (j / N0);
-  }
-  mask = B <= 1 ? 1u : cb_wor(mask);
-  v_exp_rotation_dec(X, N, B, K, spread);
-  return mask;
 }
 
 // ---- leaf of the split recursion (bands.c:966-1038) ----------------------------------------------
 template <bool REBUILD>
-CB_FN u32 b3_leaf_node(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, i16* X, int N, int b, int B,
+CB_FN u32 b3_leaf_node(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, int xo, int N, int b, int B,
                        const i16* lowband, int LM, i32 gain, int fill) {
   if (!REBUILD) {
     int q = bits2pulses_lanes(cx.i, LM, b);
@@ -218,25 +229,14 @@ CB_FN u32 b3_leaf_node(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, i16* X
       const int K = get_pulses(q);
       const u32 idx = rd_uint(rd, pvq_u(N, K) + pvq_u(N, K + 1));
       b3_push_bit(w, cur, 1);
-      if (N >= CB_B3_MIN_N) {
-        b3_push_bit(w, cur, 1);
-        CB_WSYNC();
-        b3_put_job(X, N, K, idx, gain, B, cx.spread);
-        w.b3_buf[cur.jobs++] = (u16)(X - w.X);
-        CB_WSYNC();
-      } else {
-        b3_push_bit(w, cur, 0);
-        b3_push(w, cur, (int)b3_leaf_now(w, X, N, K, idx, cx.spread, B, gain));
-      }
+      b3_push_job(cur, xo, N, K, idx, gain, B, cx.spread);
     } else {
       b3_push_bit(w, cur, 0);
     }
     return 0;
   }
-  if (b3_pop_bit(w, cur)) {                                     // the leaf carries pulses: decoded already
-    if (b3_pop_bit(w, cur)) return w.b3_buf[cur.jobs++];
-    return (u32)b3_pop(w, cur);
-  }
+  if (b3_pop_bit(w, cur)) return w.b3_buf[cur.jobs++];          // the leaf carries pulses: decoded in phase 2
+  i16* const X = w.X + xo;
   u32 cm = 0;
   const u32 cm_mask = (u32)((1ull << B) - 1);
   fill &= (int)cm_mask;
@@ -265,12 +265,11 @@ CB_FN u32 b3_leaf_node(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, i16* X
 
 // ---- quant_partition (bands.c:864-1040) as an explicit stack ---------------------------------------
 template <bool REBUILD>
-CB_FN u32 b3_partition(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, i16* X0, int N0, int b0, int B_0,
+CB_FN u32 b3_partition(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, int xo0, int N0, int b0, int B_0,
                        i16* lowband0, int LM0, i32 gain0, int fill0) {
   PartFrame* st = w.stack;
   int sp = 0;
-  i16* const base = (i16*)&w;
-  st[0].xo = (u16)(X0 - base); st[0].lo = lowband0 ? (u16)(lowband0 - base) : (u16)0xFFFF; st[0].N = N0; st[0].b = b0; st[0].B = B_0;
+  st[0].xo = (u16)xo0; st[0].lo = lowband0; st[0].N = N0; st[0].b = b0; st[0].B = B_0;
   st[0].LM = LM0; st[0].gain = gain0; st[0].fill = fill0; st[0].stage = 0;
   u32 ret = 0;
   CB_NOUNROLL while (sp >= 0) {
@@ -335,13 +334,12 @@ CB_FN u32 b3_partition(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, i16* X
         if (mid_first) {
           c.xo = f.xo; c.lo = f.lo; c.b = mbits; c.gain = (i16)f.gmid; c.fill = fill;
         } else {
-          c.xo = f.xo + N; c.lo = f.lo != 0xFFFF ? f.lo + N : 0xFFFF; c.b = sbits;
+          c.xo = f.xo + N; c.lo = f.lo ? f.lo + N : nullptr; c.b = sbits;
           c.gain = (i16)f.gside; c.fill = fill >> B;
         }
         sp++;
       } else {
-        ret = b3_leaf_node<REBUILD>(w, cx, rd, cur, base + f.xo, N, b, B, f.lo != 0xFFFF ? base + f.lo : nullptr, LM, f.gain,
-                                    fill);
+        ret = b3_leaf_node<REBUILD>(w, cx, rd, cur, f.xo, N, b, B, f.lo, LM, f.gain, fill);
         sp--;
       }
     } else if (f.stage == 1) {                   // mid done, now side
@@ -352,7 +350,7 @@ CB_FN u32 b3_partition(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, i16* X
       }
       PartFrame& c = st[sp + 1];
       c.N = f.N; c.B = f.B; c.LM = f.LM; c.stage = 0;
-      c.xo = f.xo + f.N; c.lo = f.lo != 0xFFFF ? f.lo + f.N : 0xFFFF; c.b = f.sbits;
+      c.xo = f.xo + f.N; c.lo = f.lo ? f.lo + f.N : nullptr; c.b = f.sbits;
       c.gain = (i16)f.gside; c.fill = f.fill >> f.B;
       f.stage = 2;
       sp++;
@@ -380,9 +378,10 @@ CB_FN u32 b3_partition(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, i16* X
 
 // ---- quant_band (bands.c:1044-1172) ----------------------------------------------------------------
 template <bool REBUILD>
-CB_FN u32 b3_band(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, i16* X, int N, int b, int B, i16* lowband,
+CB_FN u32 b3_band(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, int xo, int N, int b, int B, i16* lowband,
                   int LM, i16* lowband_out, i32 gain, i16* lowband_scratch, int fill) {
   const int N0 = N;
+  i16* const X = REBUILD ? w.X + xo : nullptr;
   int N_B = N / B, B0 = B;
   int time_divide = 0, recombine = 0;
   const int longBlocks = B0 == 1;
@@ -395,9 +394,13 @@ CB_FN u32 b3_band(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, i16* X, int
         sign = (int)rd_bits(rd, 1);
         cx.remaining_bits -= 1 << CB_BITRES;
       }
+      b3_push_bit(w, cur, sign);
+    } else {
+      const int sign = b3_pop_bit(w, cur);
+      CB_WSYNC();
       X[0] = sign ? -CB_NORM_SCALING : CB_NORM_SCALING;
-    } else if (lowband_out) {
-      lowband_out[0] = (i16)(X[0] >> 4);
+      CB_WSYNC();
+      if (lowband_out) lowband_out[0] = (i16)(X[0] >> 4);
     }
     return 1;
   }
@@ -432,7 +435,7 @@ CB_FN u32 b3_band(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, i16* X, int
   const int N_B0 = N_B;
   if (REBUILD && B0 > 1 && lowband) v_deinterleave(lowband, tmp, N_B >> recombine, B0 << recombine, longBlocks);
 
-  u32 cm = b3_partition<REBUILD>(w, cx, rd, cur, X, N, b, B, lowband, LM, gain, fill);
+  u32 cm = b3_partition<REBUILD>(w, cx, rd, cur, xo, N, b, B, lowband, LM, gain, fill);
   if (!REBUILD) return 0;
 
   if (B0 > 1) v_interleave(X, tmp, N_B >> recombine, B0 << recombine, longBlocks);
@@ -468,16 +471,17 @@ template <bool REBUILD>
 CB_FN void b3_one_band(EntWork& w, RangeDec& rd, B3Cur& cur, BandCtx& cx, B3Parse& ps, B3Rebuild& rs, int i, int start,
                        int end, int C, int Nfrm, int B, int spread, int intensity, i32 total_bits, int LM, int codedBands) {
   const int M = 1 << LM;
-  i16* X_ = w.X;
-  i16* Y_ = C == 2 ? w.X + Nfrm : nullptr;
+  const bool stereo = C == 2;
   const int norm_offset = M * ebands(start);
-  i16* norm = w.norm;
-  i16* norm2 = w.norm + CB_NORM_STRIDE;
   const int last = (i == end - 1);
-  i16* lowband_scratch = last ? nullptr : X_ + M * ebands(CB_NBANDS - 1);
   cx.i = i;
-  i16* X = X_ + M * ebands(i);
-  i16* Y = Y_ ? Y_ + M * ebands(i) : nullptr;
+  const int xo = M * ebands(i), yo = Nfrm + M * ebands(i);     // the band in X, per channel
+  // (the spectrum exists in the REBUILD walk only; the PARSE walk works on offsets)
+  i16* norm = REBUILD ? w.norm : nullptr;
+  i16* norm2 = REBUILD ? w.norm + CB_NORM_STRIDE : nullptr;
+  i16* lowband_scratch = (!REBUILD || last) ? nullptr : w.X + M * ebands(CB_NBANDS - 1);
+  i16* X = REBUILD ? w.X + xo : nullptr;
+  i16* Y = (REBUILD && stereo) ? w.X + yo : nullptr;
   const int N = M * ebands(i + 1) - M * ebands(i);
   const int tf_change = w.tf_res[i];
   cx.tf_change = tf_change;
@@ -531,7 +535,7 @@ CB_FN void b3_one_band(EntWork& w, RangeDec& rd, B3Cur& cur, BandCtx& cx, B3Pars
   // budget, gain and folding inputs -- and a loop makes them.
   int mode;                       // 0 mono, 1 dual stereo, 2 joint stereo N > 2, 3 joint stereo N == 2, 4 done (N == 1)
   int njobs = 0;
-  i16 *jX0 = X, *jX1 = Y;
+  int jX0 = xo, jX1 = yo;
   int jb0 = 0, jb1 = 0, jfill0 = 0, jfill1 = 0;
   i32 jgain1 = CB_Q15ONE;
   bool j1_fold = true;            // second call gets lowband / lowband_out / scratch (dual stereo) or none (side)
@@ -544,7 +548,7 @@ CB_FN void b3_one_band(EntWork& w, RangeDec& rd, B3Cur& cur, BandCtx& cx, B3Pars
     njobs = 2;
     jb0 = jb1 = b / 2;
     jfill0 = (int)x_cm; jfill1 = (int)y_cm;
-  } else if (Y == nullptr) {
+  } else if (!stereo) {
     mode = 0;
     njobs = 1;
     jb0 = b;
@@ -552,18 +556,21 @@ CB_FN void b3_one_band(EntWork& w, RangeDec& rd, B3Cur& cur, BandCtx& cx, B3Pars
   } else if (N == 1) {                                           // quant_band_n1 on both channels (bands.c:819-858)
     mode = 4;
     if (!REBUILD) {
-      i16* x = X;
       CB_NOUNROLL for (int c = 0; c < 2; c++) {
         int sign = 0;
         if (cx.remaining_bits >= 1 << CB_BITRES) {
           sign = (int)rd_bits(rd, 1);
           cx.remaining_bits -= 1 << CB_BITRES;
         }
-        x[0] = sign ? -CB_NORM_SCALING : CB_NORM_SCALING;
-        x = Y;
+        b3_push_bit(w, cur, sign);
       }
-    } else if (lout) {
-      lout[0] = (i16)(X[0] >> 4);
+    } else {
+      const int sx = b3_pop_bit(w, cur), sy = b3_pop_bit(w, cur);
+      CB_WSYNC();
+      X[0] = sx ? -CB_NORM_SCALING : CB_NORM_SCALING;
+      Y[0] = sy ? -CB_NORM_SCALING : CB_NORM_SCALING;
+      CB_WSYNC();
+      if (lout) lout[0] = (i16)(X[0] >> 4);
     }
     cm = 1;
   } else {
@@ -613,7 +620,7 @@ CB_FN void b3_one_band(EntWork& w, RangeDec& rd, B3Cur& cur, BandCtx& cx, B3Pars
     if (N == 2) {
       mode = 3;
       njobs = 1;
-      jX0 = itheta > 8192 ? Y : X;
+      jX0 = itheta > 8192 ? yo : xo;
       jb0 = mbits;
       jfill0 = orig_fill;
     } else {
@@ -621,8 +628,8 @@ CB_FN void b3_one_band(EntWork& w, RangeDec& rd, B3Cur& cur, BandCtx& cx, B3Pars
       njobs = 2;
       j1_fold = false;
       jgain1 = iside;
-      jX0 = X; jb0 = mbits; jfill0 = fill;                       // the mid call, always described in slot 0 ...
-      jX1 = Y; jb1 = sbits; jfill1 = fill >> B;                  // ... the side call in slot 1; mid_first picks the order
+      jX0 = xo; jb0 = mbits; jfill0 = fill;                      // the mid call, always described in slot 0 ...
+      jX1 = yo; jb1 = sbits; jfill1 = fill >> B;                 // ... the side call in slot 1; mid_first picks the order
     }
   }
   u32 cm0 = 0, cm1 = 0;
@@ -689,18 +696,18 @@ CB_FN void b3_one_band(EntWork& w, RangeDec& rd, B3Cur& cur, BandCtx& cx, B3Pars
   }
 }
 
-// quant_all_bands (bands.c:1337-1502), decoder side.  Same interface as dec_all_bands.
-CB_FN void dec_all_bands3(EntWork& w, RangeDec& rd, int start, int end, int C, int Nfrm, int shortBlocks,
-                          int spread, int dual_stereo, int intensity, i32 total_bits, i32 balance,
-                          int LM, int codedBands, u32& seed) {
+// quant_all_bands (bands.c:1337-1502), decoder side, PARSE half: every band of the frame onto the tape.
+// A segment is closed when the next band might not fit the rebuild warp's buffers, and before the band whose
+// spectrum slot doubles as scratch for the others (the last band of the mode).
+CB_FN void dec_bands_parse(EntWork& w, RangeDec& rd, TapeW& tw, int start, int end, int C, int Nfrm, int shortBlocks,
+                           int spread, int dual_stereo, int intensity, i32 total_bits, i32 balance, int LM,
+                           int codedBands) {
   const int M = 1 << LM;
   const int B = shortBlocks ? M : 1;
-  BandCtx cxp, cxr;
-  cxp.intensity = cxr.intensity = intensity;
-  cxp.spread = cxr.spread = spread;
+  BandCtx cxp;
+  cxp.intensity = intensity;
+  cxp.spread = spread;
   cxp.seed = 0;
-  cxr.seed = seed;
-  cxr.remaining_bits = 0;
   B3Parse ps;
   ps.balance = balance;
   ps.dual_stereo = dual_stereo;
@@ -710,44 +717,54 @@ CB_FN void dec_all_bands3(EntWork& w, RangeDec& rd, int start, int end, int C, i
   rs.update_lowband = 1;
   B3Cur wr;
   wr.jobs = wr.tape = wr.bits = 0;
-  CB_WSYNC();
-  CB_LANE_LOOP(j, CB_B3_BITWORDS) w.b3_bits[j] = 0;
-  CB_WSYNC();
-  int first = start;                     // first band parsed but not yet rebuilt
-  CB_NOUNROLL for (int i = start; i <= end; i++) {
-    // finish what has been parsed when the tape could not take another band, before the band whose
-    // spectrum slot doubles as scratch for the others (the last band of the mode), and at the end
-    bool full = false;
-    if (i < end) {
-      const int L = b3_band_leaves(M * (ebands(i + 1) - ebands(i)), LM);
-      full = wr.jobs + wr.tape + 4 * L + 2 > CB_B3_BUF || wr.bits + 10 * L + 4 > 32 * CB_B3_BITWORDS;
-#ifdef B3_PROBE
-      if (i != CB_NBANDS - 1) { if (wr.jobs + wr.tape + 4 * L + 2 > g_b3_needbuf) g_b3_needbuf = wr.jobs + wr.tape + 4 * L + 2;
-        if (wr.bits + 10 * L + 4 > g_b3_needbits) g_b3_needbits = wr.bits + 10 * L + 4; }
-#endif
+  wr.tw = &tw;
+  tw.seg_band0 = start;
+  CB_NOUNROLL for (int i = start; i < end; i++) {
+    const int L = b3_band_leaves(M * (ebands(i + 1) - ebands(i)), LM);
+    const bool full = tw.seg_jobs + tw.seg_notes + 4 * L + 2 > CB_B3_BUF || tw.seg_bits + 10 * L + 4 > CB_B3_SEG_BITS;
+    if (i > tw.seg_band0 && (full || i == CB_NBANDS - 1)) b3_close_segment(tw, i);
+    b3_one_band<false>(w, rd, wr, cxp, ps, rs, i, start, end, C, Nfrm, B, spread, intensity, total_bits, LM, codedBands);
+  }
+  if (end > tw.seg_band0) b3_close_segment(tw, end);
+}
+
+// PULSES + REBUILD halves, segment by segment.  `seed` = celt_lcg_rand state, carried on to anti_collapse.
+CB_FN void dec_bands_rebuild(EntWork& w, const FrameTape* t, int start, int end, int C, int Nfrm, int B, int spread,
+                             int dual_stereo, int intensity, int LM, u32& seed) {
+  BandCtx cxr;
+  cxr.intensity = intensity;
+  cxr.spread = spread;
+  cxr.seed = seed;
+  cxr.remaining_bits = 0;
+  B3Parse ps;
+  ps.balance = 0;
+  ps.dual_stereo = dual_stereo;
+  B3Rebuild rs;
+  rs.dual_stereo = dual_stereo;
+  rs.lowband_offset = 0;
+  rs.update_lowband = 1;
+  const int nseg = t->nseg;
+  int job0 = 0, note0 = 0, word0 = 0;
+  CB_NOUNROLL for (int sgi = 0; sgi < nseg; sgi++) {
+    const TapeSeg sg = t->seg[sgi];
+    CB_WSYNC();
+    {
+      const u16* notes = t->notes + note0;
+      const int nn = sg.notes;
+      CB_LANE_LOOP(k, nn) w.b3_buf[CB_B3_BUF - 1 - k] = notes[k];
+      const u32* words = t->bits + word0;
+      const int nw = sg.bitwords;
+      CB_LANE_LOOP(k, nw) w.b3_bits[k] = words[k];
     }
-    if (i > first && (i == end || full || i == CB_NBANDS - 1)) {
-#ifdef B3_PROBE
-      g_b3_flush++; if (full && i != end && i != CB_NBANDS - 1) g_b3_full++;
-      if (wr.jobs + wr.tape > g_b3_maxbuf) g_b3_maxbuf = wr.jobs + wr.tape;
-      if (wr.bits > g_b3_maxbits) g_b3_maxbits = wr.bits;
-#endif
-      CB_ENT_PHASE(w);                   // parse walk -> pulses
-      b3_run_jobs(w, wr.jobs);
-      // (pulses and the rebuild walk share a stage: a rendezvous between them cost more in waiting than it saved)
-      B3Cur rdc;
-      rdc.jobs = rdc.tape = rdc.bits = 0;
-      CB_NOUNROLL for (int r = first; r < i; r++)
-        b3_one_band<true>(w, rd, rdc, cxr, ps, rs, r, start, end, C, Nfrm, B, spread, intensity, total_bits, LM, codedBands);
-      first = i;
-      wr.jobs = wr.tape = wr.bits = 0;
-      CB_WSYNC();
-      CB_LANE_LOOP(j, CB_B3_BITWORDS) w.b3_bits[j] = 0;
-      CB_WSYNC();
-      CB_ENT_PHASE(w);                   // rebuild walk -> parse walk (or the frame's tail)
-    }
-    if (i < end)
-      b3_one_band<false>(w, rd, wr, cxp, ps, rs, i, start, end, C, Nfrm, B, spread, intensity, total_bits, LM, codedBands);
+    b3_run_jobs(w, t->jobs + job0, sg.jobs);
+    B3Cur rdc;
+    rdc.jobs = rdc.tape = rdc.bits = 0;
+    rdc.tw = nullptr;
+    CB_NOUNROLL for (int r = sg.band0; r < sg.band1; r++)
+      b3_one_band<true>(w, w.rd, rdc, cxr, ps, rs, r, start, end, C, Nfrm, B, spread, intensity, 0, LM, 0);
+    job0 += sg.jobs;
+    note0 += sg.notes;
+    word0 += sg.bitwords;
   }
   seed = cxr.seed;
 }

@@ -41,26 +41,38 @@ CB_UTABLE u8 ct_bit_deinterleave[16] = {0x00, 0x03, 0x0C, 0x0F, 0x30, 0x33, 0x3C
 
 struct Split { int inv, imid, iside, delta, itheta, qalloc, b, fill; };   // b/fill: updated in/out values
 
-// Three-phase band decoder (cb_celt_bands3.h): what one parse run may leave pending before a flush
+// Three-phase band decoder (cb_celt_bands3.h): what one tape segment may hold (the rebuild warp's copy of it)
 #ifndef CB_B3_BUF
-// (sized so that a 20 ms stereo frame of up to ~128 kbit/s parses bands 0..19 in one run: the flush count is then
-// the same for every stream and the stage rendezvous of kernel A lines up; larger frames flush in between)
-#define CB_B3_BUF 224           // 16-bit entries in flight: pending leaves from the front, tape notes from the back
-#define CB_B3_BITWORDS 20       // 640 node bits in flight
+// (sized so that a 20 ms stereo frame of up to ~128 kbit/s has bands 0..19 in one segment)
+#define CB_B3_BUF 224           // 16-bit entries: collapse masks of the segment's jobs from the front, notes from the back
+#define CB_B3_BITWORDS 20       // 640 node bits
 #endif
 
 // One level of the split recursion (quant_partition), kept in shared memory.
-struct PartFrame {                // positions are 16-bit word offsets from the start of EntWork (0xFFFF: none)
+struct PartFrame {
+  const i16* lo;                  // folding source of this node (the stream's norm scratch in global memory, or the
+                                  //   band-scratch slot of X in shared memory), nullptr: none
   i32 b, mbits, sbits, rebal0;
-  u16 xo, lo, cm, fill;
+  u16 xo, cm, fill, pad0;         // xo: offset of the node in X
   i16 N, B, LM, gain, stage, itheta, B0, gmid, gside, pad;
 };
 
-// Per-warp shared-memory workspace of kernel A.
-struct alignas(16) EntWork {
+// Per-stream workspace of the entropy half (shared memory): one per warp, or -- in the parse kernel, which is
+// built with CB_THREAD_MODE and only ever runs the PARSE half -- one per thread without the spectrum.
+#ifndef CB_THREAD_MODE
+#define CB_ENTWORK_ALIGN 16
+#else
+#define CB_ENTWORK_ALIGN 8      // per-thread copies sit at a stride of an odd number of 8-byte words (bank spread)
+#endif
+struct alignas(CB_ENTWORK_ALIGN) EntWork {
+#ifndef CB_THREAD_MODE
   i16 X[2 * CB_MAXN];
-  i16 norm[2 * CB_NORM_STRIDE];
-  i32 tmp32[88];                 // iy[176] / Hadamard temp (as i16) or allocation scratch (4x21 i32)
+#else
+  i16 X[2];                      // parse-only build: named by shared code, never touched
+#endif
+  i16* norm;                     // REBUILD: the stream's folding memory, 2 x CB_NORM_STRIDE values in the scratch arena
+                                 //   (FrameTape::norm; lane-parallel reads and writes only, so it need not be on chip)
+  i32 tmp32[88];                 // Hadamard temp (as i16) or allocation scratch (4x21 i32)
   i32 pulses[CB_NBANDS];
   i16 bandE[2 * CB_NBANDS];
   i16 cap[CB_NBANDS];
@@ -71,25 +83,16 @@ struct alignas(16) EntWork {
   u8 collapse[2 * CB_NBANDS];
   PartFrame stack[5];
   Split sp_store;                // result record of dec_theta
-  u16 b3_buf[CB_B3_BUF];               // cb_celt_bands3.h: pending leaves (X offset, then collapse mask) from the front,
+#ifndef CB_THREAD_MODE
+  u16 b3_buf[CB_B3_BUF];         // cb_celt_bands3.h, current tape segment: collapse masks of its jobs from the front,
                                  //   split angles and other 16-bit notes of the parse walk from the back
-  u32 b3_bits[CB_B3_BITWORDS];               //   one or two bits per node of the walk
-  RangeDec rd;                   // coder registers; in shared memory so the rd_* routines can be real calls
-  i32 nsync, sync_on;            // stage rendezvous (CB_ENT_PHASE): barriers passed so far; on only in kernel A
-};
-
-// Stage rendezvous of kernel A.  The warps of a CTA pass the stages of a frame together (header + allocation,
-// then per tape flush: parse walk, pulse decode, rebuild walk), so that the SM's instruction caches hold one
-// stage's code at a time instead of every stage's.  No data crosses warps: the barrier is only pacing.  Every
-// warp of the CTA must pass CB_ENT_PHASES barriers per launch; a warp that needs fewer (fewer flushes, a frame
-// that is skipped or concealed) makes up the rest in the kernel wrapper.  Off (sync_on = 0) wherever the band
-// decoder runs outside kernel A (the general kernel, the host build).
-#define CB_ENT_PHASES (2 + 3 * (CB_NBANDS + 1))
-#if CB_DEVICE_BUILD
-#define CB_ENT_PHASE(w) do { if ((w).sync_on) { __syncthreads(); if (CB_LANE() == 0) (w).nsync++; __syncwarp(); } } while (0)
+  u32 b3_bits[CB_B3_BITWORDS];   //   a bit or two per node of the walk
 #else
-#define CB_ENT_PHASE(w) ((void)0)
+  u16 b3_buf[2];
+  u32 b3_bits[2];
 #endif
+  RangeDec rd;                   // coder registers; in shared memory so the rd_* routines can be real calls
+};
 
 struct BandCtx {
   int i, intensity, spread, tf_change;
@@ -224,83 +227,6 @@ CB_FN_NOINLINE void v_rot_pass(i16* X, int nblocks, int len, int st, i32 c, i32 
   }
   CB_WSYNC();
 }
-// exp_rotation, decoder direction (vq.c:70-115 with dir=-1)
-CB_FN void v_exp_rotation_dec(i16* X, int len, int stride, int K, int spread) {
-  if (2 * K >= len || spread == CB_SPREAD_NONE) return;
-  int factor = spread == 1 ? 15 : spread == 2 ? 10 : 5;   // SPREAD_FACTOR[spread-1]
-  i16 gain = (i16)cb_div(mult16_16(CB_Q15ONE, len), len + factor * K);
-  i16 theta = (i16)(mult16_16_q15(gain, gain) >> 1);
-  i16 c = cb_cos_norm(theta);
-  i16 s = cb_cos_norm(sub16(CB_Q15ONE, theta));
-  int stride2 = 0;
-  if (len >= 8 * stride) {
-    stride2 = 1;
-    CB_NOUNROLL while ((stride2 * stride2 + stride2) * stride + (stride >> 2) < len) stride2++;
-  }
-  len = len / stride;
-  if (stride2) v_rot_pass(X, stride, len, stride2, s, c);
-  v_rot_pass(X, stride, len, 1, c, s);
-}
-
-// ---- PVQ index -> pulse vector (cwrs.c:463-541), uniform; every lane stores the same values ---
-CB_FN i32 pvq_decode(i16* y, int n, int k, u32 i) {
-  i32 yy = 0;
-  u32 p, q;
-  int s, k0;
-  i16 val;
-  CB_NOUNROLL while (n > 2) {
-    if (k >= n) {
-      int rowoff = ct_pvq_u_row[n];
-      p = ct_pvq_u_data[rowoff + k + 1];
-      s = -(int)(i >= p);
-      i -= p & (u32)s;
-      k0 = k;
-      q = ct_pvq_u_data[rowoff + n];
-      if (q > i) {
-        k = n;
-        CB_NOUNROLL do p = ct_pvq_u_data[ct_pvq_u_row[--k] + n]; while (p > i);
-      } else {
-        CB_NOUNROLL for (p = ct_pvq_u_data[rowoff + k]; p > i; p = ct_pvq_u_data[rowoff + k]) k--;
-      }
-      i -= p;
-      val = (i16)((k0 - k + s) ^ s);
-      *y++ = val;
-      yy = mac16_16(yy, val, val);
-    } else {
-      p = ct_pvq_u_data[ct_pvq_u_row[k] + n];
-      q = ct_pvq_u_data[ct_pvq_u_row[k + 1] + n];
-      if (p <= i && i < q) {
-        i -= p;
-        *y++ = 0;
-      } else {
-        s = -(int)(i >= q);
-        i -= q & (u32)s;
-        k0 = k;
-        CB_NOUNROLL do p = ct_pvq_u_data[ct_pvq_u_row[--k] + n]; while (p > i);
-        i -= p;
-        val = (i16)((k0 - k + s) ^ s);
-        *y++ = val;
-        yy = mac16_16(yy, val, val);
-      }
-    }
-    n--;
-  }
-  p = 2 * (u32)k + 1;
-  s = -(int)(i >= p);
-  i -= p & (u32)s;
-  k0 = k;
-  k = (int)((i + 1) >> 1);
-  if (k) i -= 2 * (u32)k - 1;
-  val = (i16)((k0 - k + s) ^ s);
-  *y++ = val;
-  yy = mac16_16(yy, val, val);
-  s = -(int)i;
-  val = (i16)((k + s) ^ s);
-  *y = val;
-  yy = mac16_16(yy, val, val);
-  return yy;
-}
-
 // ---- theta (bands.c:596-818, decoder side) --------------------------------------------------
 CB_FN int compute_qn(int N, int b, int offset, int pulse_cap, int stereo) {
   int N2 = 2 * N - 1;
@@ -805,25 +731,31 @@ CB_FN int dec_allocation(EntWork& w, RangeDec& rd, int start, int end, int alloc
 }
 
 // ---- one CELT frame, entropy half (celt_decoder.c:713-1062 minus synthesis/deemphasis) -------
-// `pkt`/`len`: CELT payload staged in shared memory.  Returns 0 or a negative OPUS_* code.
+// Two halves.  celt_frame_parse is everything that hangs off the range decoder -- header flags, energies, tf,
+// allocation, the band walk (onto the tape), the frame's tail -- plus the small-state update; it has no width and
+// runs one thread or one warp per stream.  celt_frame_rebuild turns the tape into the normalised spectrum (one
+// warp per stream) and hands it to the synthesis kernel.
+// `pkt`/`len`: CELT payload (shared or global memory).  celt_frame_parse returns 0 or a negative OPUS_* code.
 struct EntFrameCfg {
   int LM, C, start, end, accum;
   const RangeDec* rd0;   // hybrid: the coder state the SILK layer left (same packet bytes); else nullptr
 };
 
-CB_FN int celt_entropy_decode(EntWork& w, CeltDecState* stg, FrameSide* side, const u8* pkt, int len,
-                              const EntFrameCfg& cfg, u32* final_range) {
+CB_FN int celt_frame_parse(EntWork& w, CeltDecState* stg, FrameSide* side, FrameTape* tape, const u8* pkt, int len,
+                           const EntFrameCfg& cfg, u32* final_range) {
   const int LM = cfg.LM, C = cfg.C, start = cfg.start, end = cfg.end;
   const int M = 1 << LM, N = M * 120;
-  const int CC = stg->channels;
-  const int lane = CB_LANE();
-  (void)lane;
   // load the small state
   CB_LANE_LOOP(j, 2 * CB_NBANDS) w.bandE[j] = stg->oldBandE[j];
   CB_WSYNC();
   int effEnd = end > CB_NBANDS ? CB_NBANDS : end;
 
+#ifdef CB_THREAD_MODE
+  RangeDec rd_regs;                  // one thread per stream: the coder state stays in registers
+  RangeDec& rd = rd_regs;
+#else
   RangeDec& rd = w.rd;
+#endif
   if (cfg.rd0) {                     // celt_decode_with_ec(dec != NULL), celt_decoder.c:813-818
     rd = *cfg.rd0;
     rd.buf = pkt;
@@ -904,31 +836,43 @@ CB_FN int celt_entropy_decode(EntWork& w, CeltDecState* stg, FrameSide* side, co
   int codedBands = dec_allocation(w, rd, start, end, alloc_trim, intensity, dual_stereo, bits, balance, C, LM);
   dec_fine_energy(w, rd, start, end, C);
 
-  u32 seed = stg->rng;
-  CB_ENT_PHASE(w);                                            // header, energies and allocation done
-  dec_all_bands3(w, rd, start, end, C, N, shortBlocks, spread_decision, dual_stereo, intensity,
-                len * (8 << CB_BITRES) - anti_collapse_rsv, balance, LM, codedBands, seed);
+  // ---- the band walk, onto the tape ----
+  TapeW tw;
+  tw.t = tape;
+  tw.jobs = tw.notes = tw.bitwords = 0;
+  tw.seg_jobs = tw.seg_notes = tw.seg_bits = 0;
+  tw.acc = 0;
+  tw.nseg = 0;
+  tw.seg_band0 = start;
+  dec_bands_parse(w, rd, tw, start, end, C, N, shortBlocks, spread_decision, dual_stereo, intensity,
+                  len * (8 << CB_BITRES) - anti_collapse_rsv, balance, LM, codedBands);
   int anti_collapse_on = 0;
   if (anti_collapse_rsv > 0) anti_collapse_on = (int)rd_bits(rd, 1);
   dec_energy_finalise(w, rd, start, end, len * 8 - rd_tell(rd), C);
-  if (anti_collapse_on)
-    v_anti_collapse(w, LM, C, N, start, end, w.bandE, stg->oldLogE, stg->oldLogE2, seed);
   CB_WSYNC();
   if (silence) {
     CB_LANE_LOOP(i, C * CB_NBANDS) w.bandE[i] = -28672;     // -QCONST16(28.f, DB_SHIFT)
     CB_WSYNC();
   }
 
-  // ---- hand-off to the synthesis kernel ----
+  // ---- hand-off: tape header for the rebuild half, frame record for the synthesis kernel ----
+  tape->kind = CB_TAPE_FRAME;
+  tape->nseg = tw.nseg;
+  tape->seed = stg->rng;
+  tape->LM = LM; tape->C = C; tape->start = start; tape->end = end; tape->B = shortBlocks ? M : 1;
+  tape->spread = spread_decision; tape->intensity = intensity; tape->dual_stereo = dual_stereo;
+  tape->anti_collapse_on = anti_collapse_on; tape->silence = silence;
+  CB_LANE_LOOP(j, CB_NBANDS) { tape->pulses[j] = (i16)w.pulses[j]; tape->tf_res[j] = w.tf_res[j]; }
+  if (anti_collapse_on) {
+    CB_LANE_LOOP(j, 2 * CB_NBANDS) {
+      tape->bandE[j] = w.bandE[j];
+      tape->prevLogE[0][j] = stg->oldLogE[j];
+      tape->prevLogE[1][j] = stg->oldLogE2[j];
+    }
+  }
   int pf_period = cb_imax(stg->pf_period, 15);               // COMBFILTER_MINPERIOD
   int pf_period_old = cb_imax(stg->pf_period_old, 15);
   CB_LANE_LOOP(j, 2 * CB_NBANDS) side->bandE[j] = w.bandE[j];
-  {
-    // X as 32-bit words, coalesced
-    const u32* src = (const u32*)w.X;
-    u32* dst = (u32*)side->X;
-    CB_LANE_LOOP(j, C * N / 2) dst[j] = src[j];
-  }
   side->accum = cfg.accum;
   side->kind = 1; side->LM = LM; side->C = C; side->transient = isTransient; side->silence = silence;
   side->start = start; side->effEnd = effEnd;
@@ -974,7 +918,114 @@ CB_FN int celt_entropy_decode(EntWork& w, CeltDecState* stg, FrameSide* side, co
   stg->loss_count = 0;
   if (rd.error) stg->error = 1;
   *final_range = rd.rng;
-  (void)CC;
   if (rd_tell(rd) > 8 * len) return -3;        // OPUS_INTERNAL_ERROR
   return 0;
 }
+
+#ifndef CB_THREAD_MODE
+// REBUILD half of a frame (one warp): tape -> normalised spectrum in side->X.
+CB_FN void celt_frame_rebuild(EntWork& w, FrameTape* tape, FrameSide* side) {
+  const int LM = tape->LM, C = tape->C, start = tape->start, end = tape->end;
+  const int N = 120 << LM;
+  CB_WSYNC();
+  CB_IF_LANE0 w.norm = tape->norm;
+  CB_LANE_LOOP(j, CB_NBANDS) { w.pulses[j] = tape->pulses[j]; w.tf_res[j] = tape->tf_res[j]; }
+  CB_WSYNC();
+  u32 seed = tape->seed;
+  dec_bands_rebuild(w, tape, start, end, C, N, tape->B, tape->spread, tape->dual_stereo, tape->intensity, LM, seed);
+  if (tape->anti_collapse_on) {
+    i16* e = (i16*)w.tmp32;                    // [0,42) bandE, [42,84) oldLogE, [84,126) oldLogE2, before this frame
+    CB_WSYNC();
+    CB_LANE_LOOP(j, 2 * CB_NBANDS) {
+      e[j] = tape->bandE[j];
+      e[2 * CB_NBANDS + j] = tape->prevLogE[0][j];
+      e[4 * CB_NBANDS + j] = tape->prevLogE[1][j];
+    }
+    CB_WSYNC();
+    v_anti_collapse(w, LM, C, N, start, end, e, e + 2 * CB_NBANDS, e + 4 * CB_NBANDS, seed);
+  }
+  CB_WSYNC();
+  {
+    // X as 32-bit words, coalesced
+    const u32* src = (const u32*)w.X;
+    u32* dst = (u32*)side->X;
+    CB_LANE_LOOP(j, C * N / 2) dst[j] = src[j];
+  }
+}
+
+// Both halves on one warp (the general kernel and the host build; the batch kernels run them apart).
+CB_FN int celt_entropy_decode(EntWork& w, CeltDecState* stg, FrameSide* side, FrameTape* tape, const u8* pkt, int len,
+                              const EntFrameCfg& cfg, u32* final_range) {
+  const int rc = celt_frame_parse(w, stg, side, tape, pkt, len, cfg, final_range);
+  CB_WSYNC();
+  celt_frame_rebuild(w, tape, side);
+  CB_WSYNC();
+  return rc;
+}
+#endif
+
+// Noise-based concealment / comfort noise (celt_decoder.c:451-506), in the two halves of the entropy stage: the
+// PARSE half (no width: one thread or one warp) decays the band energies, advances the noise generator and the
+// loss counter -- the small state -- and fills the frame record; the REBUILD half (one warp) draws the random
+// normalised bands from the seed the tape carries.  The synthesis kernel then treats it like a decoded frame.
+CB_FN void celt_plc_noise_parse(CeltDecState* stg, FrameSide* side, FrameTape* tape, int LM, int start, int end) {
+  const int C = stg->channels;
+  const int effEnd = cb_imax(start, cb_imin(end, CB_NBANDS));
+  const int loss_count = stg->loss_count;
+  const i32 decay = loss_count == 0 ? 1536 : 512;          // QCONST16(1.5f,DB_SHIFT) : QCONST16(.5f,DB_SHIFT)
+  CB_WSYNC();
+  CB_LANE_LOOP(j, 2 * CB_NBANDS) {
+    i16 e = stg->oldBandE[j];
+    int band = j % CB_NBANDS, c = j / CB_NBANDS;
+    if (c < C && band >= start && band < end) {
+      e = (i16)cb_imax(stg->backgroundLogE[j], e - decay);
+      stg->oldBandE[j] = e;
+    }
+    side->bandE[j] = e;
+  }
+  const u32 seed = stg->rng;
+  u32 total = 0;                                            // samples the generator is advanced by
+  CB_NOUNROLL for (int i = start; i < effEnd; i++) total += (u32)((ct_eband5ms[i + 1] - ct_eband5ms[i]) << LM);
+  tape->kind = CB_TAPE_NOISE;
+  tape->seed = seed;
+  tape->LM = LM; tape->C = C; tape->start = start; tape->end = effEnd;
+  side->kind = 1; side->LM = LM; side->C = C; side->transient = 0; side->silence = 0;
+  side->start = start; side->effEnd = effEnd;
+  side->T0 = 15; side->T1 = 15; side->T2 = 15;
+  side->g0 = 0; side->g1 = 0; side->g2 = 0;
+  side->tap0 = 0; side->tap1 = 0; side->tap2 = 0;
+  side->accum = 0;
+  stg->rng = cb_lcg_skip(seed, total * (u32)C);
+  stg->loss_count = loss_count + 1;
+}
+#ifndef CB_THREAD_MODE
+CB_FN void celt_plc_noise_rebuild(EntWork& w, const FrameTape* tape, FrameSide* side) {
+  const int LM = tape->LM, C = tape->C, start = tape->start, effEnd = tape->end;
+  const int N = 120 << LM;
+  u32 seed = tape->seed;
+  CB_NOUNROLL for (int c = 0; c < C; c++) {
+    CB_NOUNROLL for (int i = start; i < effEnd; i++) {
+      const int boffs = N * c + (ct_eband5ms[i] << LM);
+      const int blen = (ct_eband5ms[i + 1] - ct_eband5ms[i]) << LM;
+      const u32 seed0 = seed;
+      CB_WSYNC();
+      CB_LANE_LOOP(j, blen) w.X[boffs + j] = (i16)((i32)cb_lcg_skip(seed0, (u32)j + 1) >> 20);
+      seed = cb_lcg_skip(seed0, (u32)blen);
+      v_renormalise(w.X + boffs, blen, CB_Q15ONE);
+    }
+  }
+  CB_WSYNC();
+  {
+    const u32* src = (const u32*)w.X;
+    u32* dst = (u32*)side->X;
+    CB_LANE_LOOP(j, C * N / 2) dst[j] = src[j];
+  }
+}
+// both halves on one warp
+CB_FN void celt_plc_noise(EntWork& w, CeltDecState* stg, FrameSide* side, FrameTape* tape, int LM, int start, int end) {
+  celt_plc_noise_parse(stg, side, tape, LM, start, end);
+  CB_WSYNC();
+  celt_plc_noise_rebuild(w, tape, side);
+  CB_WSYNC();
+}
+#endif

@@ -244,50 +244,4 @@ CB_FN void celt_plc_pitch(PlcWork& w, CeltDecState* st, int N, i16* pcm, int acc
   st->loss_count = loss_count + 1;
 }
 
-// Noise-based concealment / comfort noise (celt_decoder.c:451-506): runs in kernel A because it only
-// needs the small state; it fills the FrameSide exactly like a decoded frame (random normalised
-// bands at the decayed energies, no post-filter) and kernel B synthesises it.
-CB_FN void celt_plc_noise(EntWork& w, CeltDecState* stg, FrameSide* side, int LM, int start, int end) {
-  const int C = stg->channels;
-  const int M = 1 << LM, N = M * 120;
-  const int effEnd = cb_imax(start, cb_imin(end, CB_NBANDS));
-  const int loss_count = stg->loss_count;
-  const i32 decay = loss_count == 0 ? 1536 : 512;          // QCONST16(1.5f,DB_SHIFT) : QCONST16(.5f,DB_SHIFT)
-  CB_WSYNC();
-  CB_LANE_LOOP(j, 2 * CB_NBANDS) {
-    i16 e = stg->oldBandE[j];
-    int band = j % CB_NBANDS, c = j / CB_NBANDS;
-    if (c < C && band >= start && band < end) {
-      e = (i16)cb_imax(stg->backgroundLogE[j], e - decay);
-      stg->oldBandE[j] = e;
-    }
-    w.bandE[j] = e;
-  }
-  u32 seed = stg->rng;
-  CB_NOUNROLL for (int c = 0; c < C; c++) {
-    CB_NOUNROLL for (int i = start; i < effEnd; i++) {
-      const int boffs = N * c + (ct_eband5ms[i] << LM);
-      const int blen = (ct_eband5ms[i + 1] - ct_eband5ms[i]) << LM;
-      const u32 seed0 = seed;
-      CB_WSYNC();
-      CB_LANE_LOOP(j, blen) w.X[boffs + j] = (i16)((i32)cb_lcg_skip(seed0, (u32)j + 1) >> 20);
-      seed = cb_lcg_skip(seed0, (u32)blen);
-      v_renormalise(w.X + boffs, blen, CB_Q15ONE);
-    }
-  }
-  CB_WSYNC();
-  CB_LANE_LOOP(j, 2 * CB_NBANDS) side->bandE[j] = w.bandE[j];
-  {
-    const u32* src = (const u32*)w.X;
-    u32* dst = (u32*)side->X;
-    CB_LANE_LOOP(j, C * N / 2) dst[j] = src[j];
-  }
-  side->kind = 1; side->LM = LM; side->C = C; side->transient = 0; side->silence = 0;
-  side->start = start; side->effEnd = effEnd;
-  side->T0 = 15; side->T1 = 15; side->T2 = 15;
-  side->g0 = 0; side->g1 = 0; side->g2 = 0;
-  side->tap0 = 0; side->tap1 = 0; side->tap2 = 0;
-  side->accum = 0;
-  stg->rng = seed;
-  stg->loss_count = loss_count + 1;
-}
+// (noise-based concealment, the other branch of celt_decode_lost: celt_plc_noise_parse / _rebuild in cb_celt_entropy.h)

@@ -5,9 +5,13 @@
 //     (range decoder, bit allocation, band recursion).  No divergence, no synchronisation.
 //   * "lane loops": CB_LANE_LOOP(i,n) distributes independent iterations over the lanes;
 //     cb_wsum/cb_wor/cb_wmax fold per-lane partials; CB_WSYNC() orders shared-memory traffic.
-// The same sources also compile as plain C++ (CB_HOST_EMU) where a lane loop is an ordinary
-// loop and the folds are identities.  That build exists only for the CPU-side unit tests under
-// tests/emu (host-logic checks without a GPU); it is never linked into the shipped library.
+// The same sources also compile with scalar semantics, where a lane loop is an ordinary loop and the
+// folds are identities:
+//   * CB_THREAD_MODE (device code): ONE THREAD PER STREAM.  The parse kernel (cb_parse_kernels.cu) builds
+//     the bitstream-only half of the CELT decoder this way -- that half has no width, so running it
+//     warp-uniform computed every scalar 32 times over.
+//   * CB_HOST_EMU (plain C++): exists only for the CPU-side unit tests under tests/emu (host-logic
+//     checks without a GPU); it is never linked into the shipped library.
 //
 // Fixed-point semantics follow libopus 1.1.2 FIXED_POINT (reference: opus-fix/celt/fixed_generic.h
 // and celt/arch.h); each helper cites the macro it stands for.  All adds wrap mod 2^32.
@@ -23,7 +27,7 @@ typedef uint64_t u64;
 typedef uint8_t u8;
 typedef int8_t i8;
 
-#if defined(__CUDACC__) && !defined(CB_HOST_EMU)
+#if defined(__CUDACC__) && !defined(CB_HOST_EMU) && !defined(CB_THREAD_MODE)
 #define CB_DEVICE_BUILD 1
 #define CB_FN __device__ __forceinline__
 #define CB_MFN __device__ __forceinline__   /* member functions */
@@ -84,12 +88,30 @@ CB_FN CbBest cb_wbest(CbBest b) {
 }
 #else
 #define CB_DEVICE_BUILD 0
+#if defined(__CUDACC__) && defined(CB_THREAD_MODE) && !defined(CB_HOST_EMU)
+// one thread per stream: device code, scalar semantics; every table is indexed per thread (global, L1-cached)
+#define CB_FN __device__ __forceinline__
+#define CB_MFN __device__ __forceinline__
+#define CB_HD __host__ __device__ __forceinline__
+#ifdef CB_THREAD_NOINLINE
+#define CB_FN_NOINLINE static __device__ __noinline__
+#else
+#define CB_FN_NOINLINE static __device__ __forceinline__   /* a lone thread wants its coder state in registers */
+#endif
+#ifdef CB_THREAD_GLOBAL_TABLES
+#define CB_UTABLE static __device__ const
+#else
+#define CB_UTABLE static __constant__ const   /* few streams to a warp: few distinct addresses per read */
+#endif
+#define CB_GTABLE static __device__ const
+#else
 #define CB_FN static inline
 #define CB_MFN inline
 #define CB_HD static inline
 #define CB_FN_NOINLINE static
 #define CB_UTABLE static const
 #define CB_GTABLE static const
+#endif
 #define CB_LANE() 0
 #define CB_LANE_LOOP(i, n) for (int i = 0; i < (n); ++i)
 #define CB_LANE_LOOPU(i, n) for (int i = 0; i < (n); ++i)
@@ -99,8 +121,13 @@ CB_FN i32 cb_wsum(i32 v) { return v; }
 CB_FN u32 cb_wor(u32 v) { return v; }
 CB_FN i32 cb_wmax(i32 v) { return v; }
 CB_FN i32 cb_wmin(i32 v) { return v; }
+#if defined(__CUDA_ARCH__)
+CB_FN int cb_clz(u32 v) { return __clz((int)v); }
+template <typename T> CB_FN T cb_ldg(const T* p) { return __ldg(p); }
+#else
 CB_FN int cb_clz(u32 v) { return v ? __builtin_clz(v) : 32; }
 template <typename T> CB_FN T cb_ldg(const T* p) { return *p; }
+#endif
 struct CbBest { i32 num, den, id; };
 CB_FN CbBest cb_wbest(CbBest b) { return b; }
 #endif

@@ -15,8 +15,8 @@ extern "C" int cbk_sm_count(void);
 #define G_WARPS 4
 
 __global__ void __launch_bounds__(G_WARPS * 32)
-opus_general_kernel(OpusDecState* const* states, StreamPlan* plans, FrameSide* sides, const u8* data, i16* pcm,
-                    i32 pcm_stride, i32* ret, int n, int pass) {
+opus_general_kernel(OpusDecState* const* states, StreamPlan* plans, FrameSide* sides, FrameTape* tapes, const u8* data,
+                    i16* pcm, i32 pcm_stride, i32* ret, int n, int pass) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int warp = threadIdx.x >> 5;
   GenWork& g = *reinterpret_cast<GenWork*>(smem + (size_t)warp * sizeof(GenWork));
@@ -28,14 +28,15 @@ opus_general_kernel(OpusDecState* const* states, StreamPlan* plans, FrameSide* s
       // pitch-based concealment of a CELT frame (celt_decode_lost, loss_count < 5), set up by the SILK kernel
       decode_plc_pass(g.pw, states[s], pl, &sides[s], pcm + (size_t)s * pcm_stride, pass);
     } else if (route == CB_ROUTE_GENERAL || route == CB_ROUTE_FINISH) {
-      decode_general_pass(g, states[s], pl, &sides[s], data, pcm + (size_t)s * pcm_stride, &ret[s], pass, cw);
+      decode_general_pass(g, states[s], pl, &sides[s], &tapes[s], data, pcm + (size_t)s * pcm_stride, &ret[s], pass, cw);
     }
     __syncwarp();
   }
 }
 
-extern "C" int cbk_launch_general(OpusDecState* const* d_states, StreamPlan* d_plans, FrameSide* d_sides, const u8* d_data,
-                                  i16* d_pcm, i32 pcm_stride, i32* d_ret, int n, int pass, cudaStream_t stream) {
+extern "C" int cbk_launch_general(OpusDecState* const* d_states, StreamPlan* d_plans, FrameSide* d_sides, FrameTape* d_tapes,
+                                  const u8* d_data, i16* d_pcm, i32 pcm_stride, i32* d_ret, int n, int pass,
+                                  cudaStream_t stream) {
   if (n <= 0) return 0;
   static bool attr_set[64];
   const int smem = G_WARPS * (int)sizeof(GenWork);
@@ -50,7 +51,7 @@ extern "C" int cbk_launch_general(OpusDecState* const* d_states, StreamPlan* d_p
   int grid = (n + G_WARPS - 1) / G_WARPS;
   const int cap = cbk_sm_count() * 4;
   if (grid > cap) grid = cap;               // a few CTAs per SM; streams beyond are walked by a grid-stride loop
-  opus_general_kernel<<<grid, G_WARPS * 32, smem, stream>>>(d_states, d_plans, d_sides, d_data, d_pcm,
-                                                                                    pcm_stride, d_ret, n, pass);
+  opus_general_kernel<<<grid, G_WARPS * 32, smem, stream>>>(d_states, d_plans, d_sides, d_tapes, d_data, d_pcm,
+                                                            pcm_stride, d_ret, n, pass);
   return (int)cudaGetLastError();
 }

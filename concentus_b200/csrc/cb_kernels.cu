@@ -1,15 +1,14 @@
 // cb_kernels.cu -- sm_100a kernels of the batched Opus decoder and their launchers.
 //
 //   (the plan -- TOC + framing parse, argument checks, StreamPlan -- is fused with the SILK kernel: cb_silk_kernels.cu)
-//   celt_entropy_kernel : 1 warp   / stream  -- range decoder + PVQ/band reconstruction (kernel A)
+//   celt_parse_kernel   : 1 thread / stream  -- everything that reads the bitstream (cb_parse_kernels.cu, kernel A1)
+//   celt_rebuild_kernel : 1 warp   / stream  -- PVQ pulse vectors + band reconstruction from the tape (kernel A2)
 //   celt_synth_kernel   : 1 warp   / (stream, channel) -- IMDCT, post-filter, de-emphasis (kernel B)
 //
-// A and B are launched once per frame index ("pass") of the packets in the batch; single-frame
+// They are launched once per frame index ("pass") of the packets in the batch; single-frame
 // packets (the normal case) need one pass.  All kernels are integer / latency bound (no tensor
-// cores): the design levers are warps resident per SM (28, sized from the 227 KB shared memory), keeping
-// every per-stream array in shared memory, and -- for kernel A on a batch that fills the GPU -- one CTA per SM
-// whose 28 warps pass the stages of a frame together, so that the instruction caches hold one stage at a time
-// (CB_ENT_PHASE, cb_celt_entropy.h).
+// cores): the design levers are warps resident per SM (28, sized from the 227 KB shared memory) and keeping
+// the per-stream arrays the warp works on in shared memory.
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "cb_decode_pass.h"
@@ -18,34 +17,25 @@
 extern "C" int cbk_sm_count(void);   // SMs of the current device (opus_api.cu)
 
 #define A_WARPS 4           // kernel A, small batches: 4 warps per CTA, 7 CTAs per SM
-#define A_WARPS_SM 28       // kernel A, batches that fill the GPU: one CTA spans the SM (stage rendezvous, CB_ENT_PHASE)
+#define A_WARPS_SM 28       // rebuild kernel: warps an SM holds
 #define B_WARPS 4
 
-template <bool HYB>
-__global__ void __launch_bounds__(A_WARPS_SM * 32, 1)
-celt_entropy_kernel(OpusDecState* const* states, const u8* data, StreamPlan* plans, FrameSide* sides,
-                    i32* ret, int n, int pass, int per_warp_bytes) {
+// Kernel A2: the REBUILD half of the entropy stage (cb_entropy_pass.h), one warp per stream: tape -> pulse vectors
+// (a lane per leaf) -> folding / recombination / stereo merge -> normalised spectrum for the synthesis kernel.
+// CELT-only frames and the CELT layer of hybrid frames alike (the tape says where the bands start).
+// Registers and shared memory are held to 64 per thread / ~5.4 KB per warp on purpose: the parse kernel of the NEXT
+// call runs beside this kernel (opus_api.cu: the control side runs a pass ahead), and its CTAs only fit on an SM
+// whose rebuild CTAs leave them room.
+__global__ void __launch_bounds__(1024, 1)
+celt_rebuild_kernel(FrameSide* sides, FrameTape* tapes, int n) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int warp = threadIdx.x >> 5;
   const int s = blockIdx.x * (blockDim.x >> 5) + warp;
-  EntWork& w = *reinterpret_cast<EntWork*>(smem + (size_t)warp * per_warp_bytes);
-  // a CTA none of whose streams has a frame for this instance (the hybrid instance in a CELT batch, both in a SILK
-  // batch) skips the rendezvous altogether
-  const int route = s < n ? plans[s].route : -1;
-  const int paced = __syncthreads_or(HYB ? route == CB_ROUTE_HYBRID : route == CB_ROUTE_CELT);
-  if (CB_LANE() == 0) { w.nsync = 0; w.sync_on = paced; }
-  __syncwarp();
-  if (s < n) {
-    u8* pkt = per_warp_bytes > (int)sizeof(EntWork) ? reinterpret_cast<u8*>(&w) + sizeof(EntWork) : nullptr;
-    OpusDecState* st = states[s];
-    StreamPlan* pl = &plans[s];
-    FrameSide* side = &sides[s];
-    decode_entropy_pass<HYB>(w, pkt, per_warp_bytes - (int)sizeof(EntWork), st, pl, side, data, &ret[s], pass);
-  }
-  // stage rendezvous: every warp of the CTA passes the same number of barriers (cb_celt_entropy.h)
-  __syncwarp();
-  if (paced)
-    for (int k = w.nsync; k < CB_ENT_PHASES; k++) __syncthreads();
+  if (s >= n) return;
+  const int route = sides[s].route;
+  if ((route != CB_ROUTE_CELT && route != CB_ROUTE_HYBRID) || tapes[s].kind == CB_TAPE_NONE) return;
+  EntWork& w = *reinterpret_cast<EntWork*>(smem + (size_t)warp * sizeof(EntWork));
+  decode_entropy_rebuild(w, &tapes[s], &sides[s]);
 }
 
 __global__ void __launch_bounds__(B_WARPS * 32, 7)
@@ -106,26 +96,18 @@ __global__ void opus_ms_scatter_kernel(const MSLayout* layouts, const i32* ms_re
 // ---- launchers (host) ------------------------------------------------------------------------
 static int g_attr_done[64];
 
-// Shared memory of one warp of kernel A: the work area plus, when it still leaves room for 7 CTAs per SM
-// (227 KB, 1 KB reserved per CTA), a staging area for the packet; larger packets are read from global memory.
-extern "C" size_t cbk_entropy_smem_per_warp(int max_payload, int cta_warps) {
-  const size_t work = (sizeof(EntWork) + 15) & ~(size_t)15;
-  const size_t staged = work + (size_t)((max_payload + 15) & ~15);
-  const int ctas = A_WARPS_SM / cta_warps;                        // 28 warps per SM in either CTA shape
-  const size_t limit = (((227 * 1024) / ctas - 1024) / cta_warps) & ~(size_t)15;
-  return staged <= limit ? staged : work;
-}
-// Warps per CTA of kernel A.  An SM holds 28 of its warps (registers, shared memory).  A batch that gives every SM
-// at least a few warps runs as CTAs that each take an equal share of it -- ceil(n / #SMs) warps per CTA, one CTA
-// per SM, or the same over two, three ... waves when the batch is larger than #SMs x 28 -- so that every SM is busy
-// for the whole kernel and the warps of an SM pass the frame's stages together (CB_ENT_PHASE).  Smaller batches
-// keep 4-warp CTAs and spread over the SMs.
+// Warps per CTA of the rebuild kernel.  An SM holds 28 of its warps (shared memory).  A batch that gives every SM at
+// least a few warps runs as CTAs that each take an equal share of it -- two CTAs per SM, ceil(n / (2 #SMs)) warps
+// each (the same over two, three ... waves when the batch is larger than #SMs x 28) -- so that every SM is busy for
+// the whole kernel.  Smaller batches keep 4-warp CTAs and spread over the SMs.
+// (The one-kernel entropy stage of round 1 had to pace its warps through the frame's stages with CTA-wide barriers
+// to keep 7 k instructions in the instruction caches; the rebuild half alone is small enough to go without.)
 static int entropy_cta_warps(int n) {
   const int sms = cbk_sm_count();
   if (n < sms * (A_WARPS + 1)) return A_WARPS;
   const int waves = (n + sms * A_WARPS_SM - 1) / (sms * A_WARPS_SM);
-  const int w = (n + sms * waves - 1) / (sms * waves);
-  return w > A_WARPS_SM ? A_WARPS_SM : w;
+  const int w = (n + 2 * sms * waves - 1) / (2 * sms * waves);
+  return w > A_WARPS_SM / 2 ? A_WARPS_SM / 2 : (w < 1 ? 1 : w);
 }
 
 static int ensure_attrs() {
@@ -133,33 +115,40 @@ static int ensure_attrs() {
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return (int)e;
   if (dev < 64 && g_attr_done[dev]) return 0;
-  e = cudaFuncSetAttribute(celt_entropy_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-  if (e != cudaSuccess) return (int)e;
-  e = cudaFuncSetAttribute(celt_entropy_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  e = cudaFuncSetAttribute(celt_rebuild_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
   if (e != cudaSuccess) return (int)e;
   e = cudaFuncSetAttribute(celt_synth_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  if (e != cudaSuccess) return (int)e;
+  // Kernels of neighbouring passes share SMs (the parse kernel of the next call runs beside rebuild / synthesis of
+  // this one): all of them ask for the largest shared-memory carve-out, so that an SM configured for one of them
+  // has room for the others' CTAs.
+  e = cudaFuncSetAttribute(celt_rebuild_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  if (e != cudaSuccess) return (int)e;
+  e = cudaFuncSetAttribute(celt_synth_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   if (e != cudaSuccess) return (int)e;
   if (dev < 64) g_attr_done[dev] = 1;
   return 0;
 }
 
-extern "C" int cbk_launch_entropy(OpusDecState* const* d_states, const u8* d_data, StreamPlan* d_plans,
-                                  FrameSide* d_sides, i32* d_ret, int n, int pass, int max_payload,
-                                  cudaStream_t stream) {
+extern "C" int cbk_launch_rebuild(FrameSide* d_sides, FrameTape* d_tapes, int n, cudaStream_t stream) {
   if (n <= 0) return 0;
   int rc = ensure_attrs();
   if (rc) return rc;
   const int aw = entropy_cta_warps(n);
-  const int per_warp = (int)cbk_entropy_smem_per_warp(max_payload, aw);
-  const size_t smemA = (size_t)per_warp * aw;
-  celt_entropy_kernel<false><<<(n + aw - 1) / aw, aw * 32, smemA, stream>>>(
-      d_states, d_data, d_plans, d_sides, d_ret, n, pass, per_warp);
-  cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) return (int)e;
-  // CELT layer of hybrid frames: its warps leave at once in a batch without hybrid streams
-  celt_entropy_kernel<true><<<(n + aw - 1) / aw, aw * 32, smemA, stream>>>(
-      d_states, d_data, d_plans, d_sides, d_ret, n, pass, per_warp);
+  celt_rebuild_kernel<<<(n + aw - 1) / aw, aw * 32, sizeof(EntWork) * (size_t)aw, stream>>>(d_sides, d_tapes, n);
   return (int)cudaGetLastError();
+}
+
+// The entropy stage of a pass: the parse kernel (cb_parse_kernels.cu, a thread per stream), then the rebuild kernel.
+extern "C" int cbk_launch_entropy(OpusDecState* const* d_states, const u8* d_data, StreamPlan* d_plans,
+                                  FrameSide* d_sides, FrameTape* d_tapes, i32* d_ret, int n, int pass, int max_payload,
+                                  cudaStream_t stream) {
+  if (n <= 0) return 0;
+  int rc = ensure_attrs();
+  if (rc) return rc;
+  rc = cbk_launch_parse(d_states, d_data, d_plans, d_sides, d_tapes, d_ret, n, pass, max_payload, stream);
+  if (rc) return rc;
+  return cbk_launch_rebuild(d_sides, d_tapes, n, stream);
 }
 
 extern "C" int cbk_launch_synth(OpusDecState* const* d_states, const StreamPlan* d_plans, const FrameSide* d_sides,
@@ -194,3 +183,4 @@ extern "C" int cbk_launch_ms_scatter(const MSLayout* d_layouts, const i32* d_ms_
 extern "C" size_t cbk_sizeof_state(void) { return sizeof(OpusDecState); }
 extern "C" size_t cbk_sizeof_plan(void) { return sizeof(StreamPlan); }
 extern "C" size_t cbk_sizeof_side(void) { return sizeof(FrameSide); }
+extern "C" size_t cbk_sizeof_tape(void) { return sizeof(FrameTape); }

@@ -36,6 +36,7 @@ struct StaticScratch {
   OpusDecState* states[STATIC_MAX];   // device addresses of the decoders' state blobs
   StreamPlan plans[STATIC_MAX];
   FrameSide sides[STATIC_MAX];
+  FrameTape tapes[STATIC_MAX];
 };
 
 // The scratch itself.  In host code this name is only a stand-in for the symbol, not a device
@@ -56,12 +57,15 @@ __global__ void fill_static_scratch(StatePtrPack pack, StaticScratch* s, int n) 
   s->plans[i].total_samples = 0;
   s->sides[i].kind = 0;
   s->sides[i].accum = 0;
+  s->tapes[i].kind = CB_TAPE_NONE;
+  s->tapes[i].nseg = 0;
 }
 
 static StaticScratch* g_scratch_addr[16];   // per device, filled on first use
 
 extern "C" OpusDecState* opusb_internal_device_state(const OpusDecoder* st, int* device, int* channels);
 extern "C" cudaStream_t opusb_internal_stream(int* err);
+extern "C" void opusb_internal_serial_call_done(int device);
 
 extern "C" int opus_decode_batch_device_static(OpusDecoder* const* st, int n, const unsigned char* d_data,
                                                const opus_int32* d_offsets, const opus_int32* d_len,
@@ -111,6 +115,7 @@ extern "C" int opus_decode_batch_device_static(OpusDecoder* const* st, int n, co
   // NULL = the library's own stream, as in opus_decode_group_device: the call is then ordered with opus_decode /
   // ctl work on the same decoders and opus_b200_synchronize() waits for it
   cudaStream_t stream = (cudaStream_t)cuda_stream;
+  const bool own_stream = !stream;
   if (!stream) {
     int serr = 0;
     stream = opusb_internal_stream(&serr);
@@ -126,10 +131,11 @@ extern "C" int opus_decode_batch_device_static(OpusDecoder* const* st, int n, co
                                 pcm_stride, d_ret, n, max_frames, stream);
   for (int p = 0; p < max_frames && !rc; p++) {
     if (p > 0) rc = cbk_launch_silk(s->states, s->plans, s->sides, d_data, d_pcm, pcm_stride, d_ret, n, p, stream);
-    if (!rc) rc = cbk_launch_entropy(s->states, d_data, s->plans, s->sides, d_ret, n, p, max_packet_bytes, stream);
+    if (!rc) rc = cbk_launch_entropy(s->states, d_data, s->plans, s->sides, s->tapes, d_ret, n, p, max_packet_bytes, stream);
     if (!rc) rc = cbk_launch_synth(s->states, s->plans, s->sides, d_pcm, pcm_stride, n, p, 2, stream);
-    if (!rc) rc = cbk_launch_general(s->states, s->plans, s->sides, d_data, d_pcm, pcm_stride, d_ret, n, p, stream);
+    if (!rc) rc = cbk_launch_general(s->states, s->plans, s->sides, s->tapes, d_data, d_pcm, pcm_stride, d_ret, n, p, stream);
   }
+  if (own_stream) opusb_internal_serial_call_done(device);
   if (rc) {
     fprintf(stderr, "[opus_b200] opus_decode_batch_device_static: launch failed: %s\n",
             cudaGetErrorString((cudaError_t)rc));

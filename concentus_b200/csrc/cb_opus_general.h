@@ -21,6 +21,7 @@ struct alignas(16) GenWork {
   i32 silk_err;
   i32 xfer[4];                   // lane 0 -> all lanes hand-off
   u8 sil[4];                     // the two-byte silence packet of the hybrid->SILK fade-out
+  FrameTape* tape;               // this stream's tape (scratch arena): every CELT frame decoded here goes through it
 };
 
 // smooth_fade (opus_decoder.c:185-204)
@@ -49,7 +50,7 @@ CB_FN_NOINLINE void gen_celt_decode(GenWork& g, OpusDecState* st, FrameSide* sid
   CB_WSYNC();
   if (data == nullptr || len <= 1) {
     if (celt->loss_count >= 5 || start != 0) {
-      celt_plc_noise(g.ew, celt, side, LM, start, end);
+      celt_plc_noise(g.ew, celt, side, g.tape, LM, start, end);
       CB_WSYNC();
       side->accum = accum;
       CB_WSYNC();
@@ -65,10 +66,7 @@ CB_FN_NOINLINE void gen_celt_decode(GenWork& g, OpusDecState* st, FrameSide* sid
   EntFrameCfg cfg;
   cfg.LM = LM; cfg.C = C; cfg.start = start; cfg.end = end; cfg.accum = accum; cfg.rd0 = rd0;
   u32 fr = 0;
-  CB_WSYNC();
-  CB_IF_LANE0 g.ew.sync_on = 0;                                // no stage rendezvous outside kernel A
-  CB_WSYNC();
-  celt_entropy_decode(g.ew, celt, side, g.pkt, len, cfg, &fr);
+  celt_entropy_decode(g.ew, celt, side, g.tape, g.pkt, len, cfg, &fr);
   if (final_range) *final_range = fr;
   CB_WSYNC();
   for (int c = 0; c < celt->channels; c++) celt_synth_channel(g.sw, celt, side, c, pcm, 0);
@@ -313,10 +311,13 @@ CB_FN int gen_decode_frame(GenWork& g, OpusDecState* st, FrameSide* side, const 
 }
 
 // Kernel G, one stream, one pass: frames routed here by kernel A (or handed over by the SILK kernel).
-CB_FN void decode_general_pass(GenWork& g, OpusDecState* st, StreamPlan* pl, FrameSide* side, const u8* data, i16* row,
-                               i32* ret_slot, int pass, SilkCallWork& cw) {
+CB_FN void decode_general_pass(GenWork& g, OpusDecState* st, StreamPlan* pl, FrameSide* side, FrameTape* tape, const u8* data,
+                               i16* row, i32* ret_slot, int pass, SilkCallWork& cw) {
   const int route = pl->route;
   if (route != CB_ROUTE_GENERAL && route != CB_ROUTE_FINISH) return;
+  CB_WSYNC();
+  CB_IF_LANE0 g.tape = tape;
+  CB_WSYNC();
   const int CC = st->channels;
   i16* pcm = row + (size_t)pl->pcm_off[pass] * CC;
   const int len = pl->len[pass];

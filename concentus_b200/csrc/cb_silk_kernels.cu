@@ -26,6 +26,7 @@ silk_decode_kernel(OpusDecState* const* states, StreamPlan* plans, FrameSide* si
   StreamPlan* pl = &plans[s];
   SilkCallWork cw;
   decode_silk_pass(st, pl, &sides[s], data, pcm + (size_t)s * pcm_stride, &ret[s], pass, cw);
+  sides[s].route = pl->route;
 }
 
 // The first pass of a batch call: packet parsing / frame plan (opus_plan_stream) and the SILK pass of
@@ -42,6 +43,7 @@ plan_silk_kernel(OpusDecState* const* states, const u8* data, const i32* offs, c
   ret[s] = pl->ret;
   SilkCallWork cw;
   decode_silk_pass(st, pl, &sides[s], data, pcm + (size_t)s * pcm_stride, &ret[s], 0, cw);
+  sides[s].route = pl->route;
 }
 
 extern "C" int cbk_launch_plan_silk(OpusDecState* const* d_states, const u8* d_data, const i32* d_off, const i32* d_len,

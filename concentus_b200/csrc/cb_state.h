@@ -52,10 +52,50 @@ struct alignas(16) FrameSide {
   i32 g0, g1, g2;
   i32 tap0, tap1, tap2;
   i32 accum;                 // hybrid: add into pcm (celt_decoder.c:236-245)
-  i32 pad[3];
+  i32 route;                 // copy of StreamPlan::route for this pass (the rebuild and synthesis kernels read it here:
+                             //   the plan's field is rewritten by the next pass's routing while they may still run)
+  i32 pad[2];
   i16 bandE[2 * CB_NBANDS];  // log energies used by denormalise_bands
   i16 pad2[6];
   i16 X[2 * CB_MAXN];        // normalised spectrum, channel-major
+};
+
+// The tape: what the PARSE half of a CELT frame (everything that reads the bitstream; one thread or one warp per
+// stream) leaves for the REBUILD half (one warp per stream: pulse vectors, folding, recombination, stereo merge,
+// anti-collapse).  It lives in the scratch arena, one per stream (cb_celt_bands3.h describes the entries).
+// Sizes are the worst case of a 20 ms stereo frame: a band's channel splits into at most 16 leaves (bands of
+// 32+ bins at LM = 3), 8 for 16 bins, 4 for 8 bins: 208 leaves per channel.
+#define CB_TAPE_MAX_JOBS 416
+#define CB_TAPE_MAX_NOTES 448      // one split angle per inner node (< leaves) plus the stereo angle of every band
+#define CB_TAPE_BITWORDS 160       // <= 10 bits per leaf + 4 per band, plus one word of slack per segment
+#define CB_TAPE_MAX_SEG 24
+#define CB_TAPE_NONE 0             // nothing for the rebuild half
+#define CB_TAPE_FRAME 1            // a decoded frame
+#define CB_TAPE_NOISE 2            // noise-based concealment: random normalised bands at the energies in bandE
+struct TapeJob {                   // a leaf with pulses (alg_unquant after the index has been read)
+  u32 idx;                         // PVQ index
+  u16 xoff;                        // where the leaf lies in X
+  i16 N, K, gain;
+  u8 B, spread;
+};
+struct TapeSeg {                   // a run of bands whose notes fit the rebuild warp's shared memory
+  u8 band0, band1;
+  u16 jobs, notes, bitwords;       // counts inside the segment (segments start on a word of bits)
+};
+struct alignas(16) FrameTape {
+  i32 kind;                        // CB_TAPE_*
+  i32 nseg;
+  u32 seed;                        // celt_lcg_rand state at the start of the frame
+  i32 LM, C, start, end, B, spread, intensity, dual_stereo, anti_collapse_on, silence;
+  i16 pulses[CB_NBANDS + 1];       // allocation per band (anti-collapse depth)
+  i8 tf_res[CB_NBANDS + 3];
+  i16 bandE[2 * CB_NBANDS];        // final log energies of the frame
+  i16 prevLogE[2][2 * CB_NBANDS];  // oldLogE / oldLogE2 as they were before this frame (anti_collapse)
+  TapeSeg seg[CB_TAPE_MAX_SEG];
+  u32 bits[CB_TAPE_BITWORDS];
+  u16 notes[CB_TAPE_MAX_NOTES];
+  TapeJob jobs[CB_TAPE_MAX_JOBS];
+  i16 norm[2 * CB_NORM_STRIDE];    // REBUILD's own scratch: the normalised lower bands kept for folding (bands.c:1380)
 };
 
 // celt_decoder_init + OPUS_RESET_STATE (celt_decoder.c:134-172,1196-1204): all-zero except the

@@ -53,10 +53,17 @@ struct GrowBuf {                 // grow-only buffer (device or pinned host)
 };
 
 struct DevCtx : OpusbDevice {
-  // The general kernel (mode switches, pitch-based concealment) works on streams the CELT kernels skip, so it
-  // runs beside them on its own stream: forked after the SILK kernel of a pass, joined at the end of the pass.
-  cudaStream_t side_stream = nullptr;
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  // A decode pass runs on three streams (group_enqueue_passes):
+  //   ctl_stream  -- everything that reads packets: plan / routing / SILK kernel, then the parse kernel.  Nothing
+  //                  here needs the previous pass's spectrum or output history, so it runs one pass AHEAD of
+  //   stream      -- (the library's main stream, OpusbDevice) rebuild + synthesis kernels, copies, scatter
+  //   side_stream -- the general kernel (mode switches, pitch-based concealment) works on streams the CELT kernels
+  //                  skip, so it runs beside them: forked after the routing of a pass, joined at the end of the pass.
+  cudaStream_t ctl_stream = nullptr, side_stream = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;      // single-stream calls: fork / join of the general kernel
+  cudaEvent_t ev_route = nullptr, ev_parse = nullptr, ev_gen = nullptr, ev_synth = nullptr, ev_in = nullptr;
+  cudaEvent_t ev_serial = nullptr;                       // end of the last one-stream call on `stream`
+  bool streams_ok = false, streams_tried = false;
   std::vector<OpusDecState*> slabs;
   std::vector<OpusDecState*> free_slots;
 };
@@ -65,13 +72,17 @@ DevCtx g_ctx[OPUSB_MAX_DEVICES];        // each guarded by its own mutex (cb_hos
 std::atomic<long long> g_launches{0};
 std::mutex g_prof_mu;                   // guards g_prof only
 
-// optional per-kernel timing (CUDA events on the launching stream), for bench.py's roofline line
+// optional per-kernel timing (CUDA events on the launching stream), for bench.py's roofline line.
+// kinds: 0 plan + routing + SILK kernel, 1 parse kernel, 2 rebuild kernel, 3 synthesis kernel.  While it is on,
+// calls are queued on one stream (no run-ahead of the parse side), so that the figures are per kernel.
+const int kProfKinds = 4;
 struct ProfRec { int kind; cudaEvent_t a, b; };
 std::atomic<bool> g_prof_on{false};
+std::atomic<bool> g_trace_on{false};      // tools/pipe_trace.py: event pairs around every launch WITHOUT giving up the run-ahead
 std::vector<ProfRec> g_prof;
 struct ProfScope {
   cudaStream_t s; int kind; cudaEvent_t a = nullptr, b = nullptr; bool on;
-  ProfScope(cudaStream_t s_, int k) : s(s_), kind(k), on(g_prof_on) {
+  ProfScope(cudaStream_t s_, int k) : s(s_), kind(k), on(g_prof_on || g_trace_on) {
     if (on) { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, s); }
   }
   ~ProfScope() {
@@ -122,8 +133,10 @@ struct OpusDecoder {
                                   // 0: no packet yet, -1: unknown (packets went in through a device-resident call)
 };
 
-// Two-deep pipeline behind opus_decode_group_submit/_wait: while the kernels of one call run, the PCM of
-// the previous call drains to the host and the packets of the next one come in (separate copy streams).
+// Pipeline behind opus_decode_group_submit/_wait, three calls deep: while the rebuild / synthesis kernels of one
+// call run, the PCM of the call before drains to the host, and the packets of the next one come in and are parsed
+// (separate copy streams, the control side of the next call ahead of the signal side of this one).
+const int kPipeDepth = 3;
 struct DecPipeSlot {
   GrowBuf d_pkt, d_pcm, d_i32, h_i32;        // d_i32 = offsets, lengths, fec flags, return values (4n)
   cudaEvent_t in_done = nullptr, k_done = nullptr, out_done = nullptr;
@@ -132,7 +145,7 @@ struct DecPipeSlot {
 };
 struct DecPipe {
   cudaStream_t s_in = nullptr, s_out = nullptr;
-  DecPipeSlot slot[2];
+  DecPipeSlot slot[kPipeDepth];
   unsigned long long seq = 0;
 };
 
@@ -142,8 +155,15 @@ struct OpusDecoderGroup {
   int Fs, channels;            // common values (or -1 when mixed)
   OpusDecoder** members;
   OpusDecState** d_states;     // device array of n state pointers
-  StreamPlan* d_plans;
-  FrameSide* d_sides;
+  // Scratch, two of each: the control side of a pass (plan, routing, parse) runs while the signal side of the
+  // previous pass (rebuild, synthesis) still reads its records.  Plans alternate per call, frame records and
+  // tapes per pass.
+  StreamPlan* d_plans2[2];
+  FrameSide* d_sides2[2];
+  FrameTape* d_tapes2[2];      // n each: parse half -> rebuild half of the entropy stage
+  unsigned call_seq, pass_seq;
+  int celt_packets, seen_packets;   // of the last host-scanned batch: packets with a CELT layer (CELT-only or hybrid TOC) / all
+  StreamPlan* d_plans;         // the current call's plan buffer (= d_plans2[call_seq & 1] after group_call_begin)
   i32* d_ret;                  // n
   DecPipe* pipe;               // created by the first opus_decode_group_submit
   GrowBuf d_pkt, d_i32, d_pcm; // staging of the synchronous host-buffer entry (opus_decode_group_flat)
@@ -321,8 +341,11 @@ static void group_free(OpusDecoderGroup* g) {
   pipe_free(g->pipe);
   g->pipe = nullptr;
   if (g->d_states) cudaFree(g->d_states);
-  if (g->d_plans) cudaFree(g->d_plans);
-  if (g->d_sides) cudaFree(g->d_sides);
+  for (int k = 0; k < 2; k++) {
+    if (g->d_plans2[k]) cudaFree(g->d_plans2[k]);
+    if (g->d_sides2[k]) cudaFree(g->d_sides2[k]);
+    if (g->d_tapes2[k]) cudaFree(g->d_tapes2[k]);
+  }
   if (g->d_ret) cudaFree(g->d_ret);
   if (g->d_pkt.p) cudaFree(g->d_pkt.p);
   if (g->d_i32.p) cudaFree(g->d_i32.p);
@@ -344,7 +367,10 @@ OpusDecoderGroup* opus_decoder_group_create(OpusDecoder* const* st, int n, int* 
   cudaGetDevice(&prev);
   if (cudaSetDevice(st[0]->device) != cudaSuccess) { if (error) *error = OPUS_INTERNAL_ERROR; return nullptr; }
   OpusDecoderGroup* g = new OpusDecoderGroup();
-  g->d_states = nullptr; g->d_plans = nullptr; g->d_sides = nullptr; g->d_ret = nullptr; g->pipe = nullptr;
+  g->d_states = nullptr; g->d_plans = nullptr; g->d_ret = nullptr; g->pipe = nullptr;
+  for (int k = 0; k < 2; k++) { g->d_plans2[k] = nullptr; g->d_sides2[k] = nullptr; g->d_tapes2[k] = nullptr; }
+  g->call_seq = g->pass_seq = 0;
+  g->celt_packets = g->seen_packets = 0;
   std::vector<OpusDecState*> ptrs(n);
   g->magic = kMagic;
   g->n = n;
@@ -359,9 +385,15 @@ OpusDecoderGroup* opus_decoder_group_create(OpusDecoder* const* st, int n, int* 
     if (st[i]->channels != g->channels) g->channels = -1;
   }
   bool ok = cudaMalloc((void**)&g->d_states, sizeof(OpusDecState*) * n) == cudaSuccess &&
-            cudaMalloc((void**)&g->d_plans, sizeof(StreamPlan) * n) == cudaSuccess &&
-            cudaMalloc((void**)&g->d_sides, sizeof(FrameSide) * n) == cudaSuccess &&
-            cudaMalloc((void**)&g->d_ret, sizeof(i32) * n) == cudaSuccess &&
+            cudaMalloc((void**)&g->d_ret, sizeof(i32) * n) == cudaSuccess;
+  for (int k = 0; k < 2 && ok; k++)
+    ok = cudaMalloc((void**)&g->d_plans2[k], sizeof(StreamPlan) * n) == cudaSuccess &&
+         cudaMalloc((void**)&g->d_sides2[k], sizeof(FrameSide) * n) == cudaSuccess &&
+         cudaMalloc((void**)&g->d_tapes2[k], sizeof(FrameTape) * n) == cudaSuccess &&
+         cudaMemset(g->d_sides2[k], 0, sizeof(FrameSide) * n) == cudaSuccess &&
+         cudaMemset(g->d_tapes2[k], 0, 64) == cudaSuccess;
+  g->d_plans = g->d_plans2[0];
+  ok = ok &&
             cudaMemcpy(g->d_states, ptrs.data(), sizeof(OpusDecState*) * n, cudaMemcpyHostToDevice) == cudaSuccess;
   if (prev >= 0) cudaSetDevice(prev);
   if (!ok) {
@@ -380,64 +412,128 @@ void opus_decoder_group_destroy(OpusDecoderGroup* g) {
   group_free(g);
 }
 
-// Queue the decode passes (kernels A, B, C per frame index) for a group whose plans are already on
-// the device.  No synchronisation.
-static int group_enqueue_passes(OpusDecoderGroup* g, const u8* d_data, i16* d_pcm, i32 pcm_stride, i32* d_ret,
-                                int passes, int max_packet_bytes, cudaStream_t stream, bool silk0_done = false) {
-  int rc = 0;
-  DevCtx* c = (g->device >= 0 && g->device < OPUSB_MAX_DEVICES) ? &g_ctx[g->device] : nullptr;   // its mutex is held by the caller
-  if (c && !c->side_stream) {
-    if (cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess) {
-      c->side_stream = nullptr;              // fall back to running everything on one stream
-    }
-  }
-  const bool fork = c && c->side_stream && c->ev_fork && c->ev_join;
-  for (int p = 0; p < passes; p++) {
-    // SILK kernel first: it also decides, per stream, which kernels own this pass's frame
-    rc = 0;
-    if (p > 0 || !silk0_done) {
-      rc = cbk_launch_silk(g->d_states, g->d_plans, g->d_sides, d_data, d_pcm, pcm_stride, d_ret, g->n, p, stream);
-      g_launches += 1;
-    }
-    if (!rc && fork) {
-      // general kernel on the side stream, beside the CELT kernels of this pass
-      if (cudaEventRecord(c->ev_fork, stream) != cudaSuccess || cudaStreamWaitEvent(c->side_stream, c->ev_fork, 0) != cudaSuccess)
-        return OPUS_INTERNAL_ERROR;
-      rc = cbk_launch_general(g->d_states, g->d_plans, g->d_sides, d_data, d_pcm, pcm_stride, d_ret, g->n, p, c->side_stream);
-      if (!rc && cudaEventRecord(c->ev_join, c->side_stream) != cudaSuccess) return OPUS_INTERNAL_ERROR;
-    }
-    if (!rc) {
-      ProfScope ps(stream, 1);
-      rc = cbk_launch_entropy(g->d_states, d_data, g->d_plans, g->d_sides, d_ret, g->n, p, max_packet_bytes, stream);
-    }
-    if (!rc) {
-      ProfScope ps(stream, 2);
-      rc = cbk_launch_synth(g->d_states, g->d_plans, g->d_sides, d_pcm, pcm_stride, g->n, p, g->channels == 1 ? 1 : 2, stream);
-    }
-    if (!rc && !fork)
-      rc = cbk_launch_general(g->d_states, g->d_plans, g->d_sides, d_data, d_pcm, pcm_stride, d_ret, g->n, p, stream);
-    if (!rc && fork && cudaStreamWaitEvent(stream, c->ev_join, 0) != cudaSuccess) return OPUS_INTERNAL_ERROR;
-    g_launches += 4;
-    if (rc) { fprintf(stderr, "[opus_b200] pass launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
+// Where a call's launches go.  Library-stream calls use the three streams of DevCtx (the control side runs one pass
+// ahead of the signal side); calls on a caller's stream, and calls made while per-kernel profiling is on, go on
+// that one stream in order (the general kernel still forks to the side stream).
+struct CallCtx {
+  cudaStream_t s_ctl;          // plan / routing / SILK / parse
+  cudaStream_t s_sig;          // rebuild / synthesis; a call is complete when this stream has passed it
+  bool ahead;                  // s_ctl is DevCtx::ctl_stream
+};
+
+static void ctx_make_streams(DevCtx* c) {               // under c->mu
+  if (c->streams_tried) return;
+  c->streams_tried = true;
+  bool ok = cudaStreamCreateWithFlags(&c->ctl_stream, cudaStreamNonBlocking) == cudaSuccess &&
+            cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking) == cudaSuccess;
+  cudaEvent_t* evs[] = {&c->ev_fork, &c->ev_join, &c->ev_route, &c->ev_parse, &c->ev_gen, &c->ev_synth, &c->ev_in,
+                        &c->ev_serial};
+  for (cudaEvent_t* e : evs) ok = ok && cudaEventCreateWithFlags(e, cudaEventDisableTiming) == cudaSuccess;
+  c->streams_ok = ok;                                    // else: everything on one stream, in order
+}
+
+// Start of a call (under c->mu).  `user_stream` = the caller's stream or nullptr; `inputs_ready` = an event the
+// control side has to wait for (the packet upload of the pipelined entries) or nullptr.
+// The run-ahead pays when there is parse work to hide (CELT-only / hybrid packets); a batch of SILK-only packets
+// has none, and the extra stream hops would only add to its critical path: the host entries, which see the TOC
+// bytes, then queue the call in order.
+static int group_call_begin(OpusDecoderGroup* g, DevCtx* c, cudaStream_t user_stream, cudaEvent_t inputs_ready, CallCtx* cc) {
+  ctx_make_streams(c);
+  const bool celt_work = g->seen_packets == 0 || 8 * g->celt_packets >= g->seen_packets;
+  g->d_plans = g->d_plans2[g->call_seq & 1];
+  g->call_seq++;
+  static const bool no_ahead = getenv("OPUSB_NO_AHEAD") != nullptr;       // diagnostic: every call on one stream
+  cc->ahead = !user_stream && c->streams_ok && !g_prof_on.load() && !no_ahead && celt_work;
+  cc->s_sig = user_stream ? user_stream : c->stream;
+  cc->s_ctl = cc->ahead ? c->ctl_stream : cc->s_sig;
+  if (inputs_ready && cudaStreamWaitEvent(cc->s_ctl, inputs_ready, 0) != cudaSuccess) return OPUS_INTERNAL_ERROR;
+  if (cc->ahead) {
+    // the routing of this call reads what the general kernel of the previous pass may still be writing (Opus-layer
+    // state, SILK state); ev_gen also stands behind that pass's predecessor on the signal side, so the control
+    // side is never more than one pass ahead and two scratch buffers are enough
+    if (cudaStreamWaitEvent(cc->s_ctl, c->ev_gen, 0) != cudaSuccess) return OPUS_INTERNAL_ERROR;
+    // ... and behind the last call that ran on the main stream alone (profiling, the static-scratch entry)
+    if (cudaStreamWaitEvent(cc->s_ctl, c->ev_serial, 0) != cudaSuccess) return OPUS_INTERNAL_ERROR;
+  } else if (c->streams_ok) {
+    // a one-stream call after run-ahead calls: order it behind both sides
+    if (cudaEventRecord(c->ev_in, c->ctl_stream) != cudaSuccess || cudaStreamWaitEvent(cc->s_sig, c->ev_in, 0) != cudaSuccess)
+      return OPUS_INTERNAL_ERROR;
+    if (user_stream && (cudaEventRecord(c->ev_in, c->stream) != cudaSuccess || cudaStreamWaitEvent(cc->s_sig, c->ev_in, 0) != cudaSuccess))
+      return OPUS_INTERNAL_ERROR;
   }
   return OPUS_OK;
 }
 
+// Queue the decode passes (per frame index: routing + SILK kernel, general kernel, parse, rebuild, synthesis) for a
+// group whose plans are already on the device.  No synchronisation.  silk0_done: the routing of pass 0 was fused
+// with the plan kernel (group_enqueue).
+static int group_enqueue_passes(OpusDecoderGroup* g, DevCtx* c, const CallCtx& cc, const u8* d_data, i16* d_pcm,
+                                i32 pcm_stride, i32* d_ret, int passes, int max_packet_bytes, bool silk0_done = false) {
+  int rc = 0;
+  const bool fork = c->streams_ok;
+  const int max_ch = g->channels == 1 ? 1 : 2;
+#define EV_OK(x) do { if ((x) != cudaSuccess) return OPUS_INTERNAL_ERROR; } while (0)
+  for (int p = 0; p < passes; p++) {
+    FrameSide* sides = g->d_sides2[g->pass_seq & 1];
+    FrameTape* tapes = g->d_tapes2[g->pass_seq & 1];
+    g->pass_seq++;
+    // routing (+ SILK kernel) first: it decides, per stream, which kernels own this pass's frame
+    if (p > 0 || !silk0_done) {
+      if (cc.ahead && p > 0) EV_OK(cudaStreamWaitEvent(cc.s_ctl, c->ev_gen, 0));       // general kernel of pass p - 1
+      ProfScope ps(cc.s_ctl, 0);
+      rc = cbk_launch_silk(g->d_states, g->d_plans, sides, d_data, d_pcm, pcm_stride, d_ret, g->n, p, cc.s_ctl);
+      g_launches += 1;
+    }
+    if (!rc && fork) {
+      // general kernel on the side stream: after this pass's routing and the previous pass's synthesis
+      cudaEvent_t routed = cc.ahead ? c->ev_route : c->ev_fork;
+      EV_OK(cudaEventRecord(routed, cc.s_ctl));
+      EV_OK(cudaStreamWaitEvent(c->side_stream, routed, 0));
+      if (cc.ahead) EV_OK(cudaStreamWaitEvent(c->side_stream, c->ev_synth, 0));
+      rc = cbk_launch_general(g->d_states, g->d_plans, sides, tapes, d_data, d_pcm, pcm_stride, d_ret, g->n, p, c->side_stream);
+      if (!rc) EV_OK(cudaEventRecord(cc.ahead ? c->ev_gen : c->ev_join, c->side_stream));
+    }
+    if (!rc) {
+      ProfScope ps(cc.s_ctl, 1);
+      rc = cbk_launch_parse(g->d_states, d_data, g->d_plans, sides, tapes, d_ret, g->n, p, max_packet_bytes, cc.s_ctl);
+    }
+    if (!rc && cc.ahead) {
+      EV_OK(cudaEventRecord(c->ev_parse, cc.s_ctl));
+      EV_OK(cudaStreamWaitEvent(cc.s_sig, c->ev_parse, 0));
+    }
+    if (!rc) {
+      ProfScope ps(cc.s_sig, 2);
+      rc = cbk_launch_rebuild(sides, tapes, g->n, cc.s_sig);
+    }
+    if (!rc) {
+      ProfScope ps(cc.s_sig, 3);
+      rc = cbk_launch_synth(g->d_states, g->d_plans, sides, d_pcm, pcm_stride, g->n, p, max_ch, cc.s_sig);
+    }
+    if (!rc && cc.ahead) EV_OK(cudaEventRecord(c->ev_synth, cc.s_sig));
+    if (!rc && !fork)
+      rc = cbk_launch_general(g->d_states, g->d_plans, sides, tapes, d_data, d_pcm, pcm_stride, d_ret, g->n, p, cc.s_sig);
+    if (!rc && fork) EV_OK(cudaStreamWaitEvent(cc.s_sig, cc.ahead ? c->ev_gen : c->ev_join, 0));
+    g_launches += 4;                           // parse, rebuild, synthesis, general
+    if (rc) { fprintf(stderr, "[opus_b200] pass launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
+  }
+  if (!cc.ahead && c->streams_ok && cc.s_sig == c->stream) EV_OK(cudaEventRecord(c->ev_serial, c->stream));
+#undef EV_OK
+  return OPUS_OK;
+}
+
 // Queue plan + passes for a group; everything device resident.  No synchronisation.
-static int group_enqueue(OpusDecoderGroup* g, const u8* d_data, const i32* d_off, const i32* d_len, i16* d_pcm,
-                         i32 pcm_stride, int frame_size, const i32* d_fec, i32* d_ret, int passes,
-                         int max_packet_bytes, cudaStream_t stream) {
+static int group_enqueue(OpusDecoderGroup* g, DevCtx* c, const CallCtx& cc, const u8* d_data, const i32* d_off,
+                         const i32* d_len, i16* d_pcm, i32 pcm_stride, int frame_size, const i32* d_fec, i32* d_ret,
+                         int passes, int max_packet_bytes) {
   int rc;
   {
-    ProfScope ps(stream, 0);
-    rc = cbk_launch_plan_silk(g->d_states, d_data, d_off, d_len, d_fec, frame_size, g->d_plans, g->d_sides, d_pcm,
-                              pcm_stride, d_ret, g->n, passes, stream);
+    ProfScope ps(cc.s_ctl, 0);
+    rc = cbk_launch_plan_silk(g->d_states, d_data, d_off, d_len, d_fec, frame_size, g->d_plans, g->d_sides2[g->pass_seq & 1],
+                              d_pcm, pcm_stride, d_ret, g->n, passes, cc.s_ctl);
   }
   g_launches += 1;
   if (rc) { fprintf(stderr, "[opus_b200] plan launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
-  return group_enqueue_passes(g, d_data, d_pcm, pcm_stride, d_ret, passes, max_packet_bytes, stream, true);
+  return group_enqueue_passes(g, c, cc, d_data, d_pcm, pcm_stride, d_ret, passes, max_packet_bytes, true);
 }
 
 int opus_decode_group_device(OpusDecoderGroup* g, const unsigned char* d_data, const opus_int32* d_offsets,
@@ -455,10 +551,13 @@ int opus_decode_group_device(OpusDecoderGroup* g, const unsigned char* d_data, c
   DevCtx* c = ctx_enter(g->device, &err);
   if (!c) return err;
   std::lock_guard<std::mutex> lk(c->mu);
-  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : c->stream;
   for (int i = 0; i < g->n; i++) g->members[i]->min_frame_48k = -1;   // the host does not see these packets
-  return group_enqueue(g, d_data, d_offsets, d_len, d_pcm, pcm_stride, frame_size, d_decode_fec, d_ret,
-                       max_frames, max_packet_bytes, s);
+  g->seen_packets = 0;
+  CallCtx cc;
+  int rc = group_call_begin(g, c, (cudaStream_t)cuda_stream, nullptr, &cc);
+  if (rc != OPUS_OK) return rc;
+  return group_enqueue(g, c, cc, d_data, d_offsets, d_len, d_pcm, pcm_stride, frame_size, d_decode_fec, d_ret,
+                       max_frames, max_packet_bytes);
 }
 
 // Upper bound on the pieces a concealed frame_size is cut into (opus_decoder.c:239-292, mirrored on the
@@ -484,8 +583,8 @@ static int plc_passes(int frame_size, int Fs, int min_frame_48k) {
 
 // Upper bound on the passes a batch needs, from the packets themselves (host side, O(n) byte reads).
 static int scan_passes(OpusDecoder* const* members, const unsigned char* data, const i32* off, const i32* len,
-                       const int* fec, int n, int frame_size, int Fs_hint, int* max_len) {
-  int passes = 1, mlen = 0, any_lost = 0, any_fec = 0;
+                       const int* fec, int n, int frame_size, int Fs_hint, int* max_len, int* celt_packets = nullptr) {
+  int passes = 1, mlen = 0, any_lost = 0, any_fec = 0, celt = 0;
   int group_min = 1 << 30;                 // over the members that have decoded something
   bool unknown = false;
   for (int i = 0; i < n; i++) {
@@ -501,7 +600,9 @@ static int scan_passes(OpusDecoder* const* members, const unsigned char* data, c
     if (len[i] > mlen) mlen = len[i];
     int nf = opus_packet_get_nb_frames(data + off[i], len[i]);
     if (nf > passes) passes = nf;
+    if ((data[off[i]] & 0x80) || (data[off[i]] & 0x60) == 0x60) celt++;
   }
+  if (celt_packets) *celt_packets = celt;
   if (any_lost) {
     const int known = (unknown || Fs_hint <= 0 || group_min == 1 << 30) ? 0 : group_min;
     const int chunks = plc_passes(frame_size, Fs_hint > 0 ? Fs_hint : 8000, known) + any_fec;
@@ -532,7 +633,8 @@ int opus_decode_group_flat(OpusDecoderGroup* g, const unsigned char* data, opus_
   DevCtx* c = ctx_enter(g->device, &err);
   if (!c) return err;
   int max_len = 0;
-  int passes = scan_passes(g->members, data, offsets, len, decode_fec, n, frame_size, g->Fs, &max_len);
+  int passes = scan_passes(g->members, data, offsets, len, decode_fec, n, frame_size, g->Fs, &max_len, &g->celt_packets);
+  g->seen_packets = n;
   const size_t pkt_bytes = (size_t)data_bytes + 16;
   const size_t pcm_bytes = (size_t)n * pcm_stride * sizeof(i16);
   const size_t i32_bytes = (size_t)n * 3 * sizeof(i32);
@@ -548,10 +650,13 @@ int opus_decode_group_flat(OpusDecoderGroup* g, const unsigned char* data, opus_
   cudaEvent_t done = nullptr;
   {
     std::lock_guard<std::mutex> lk(c->mu);          // queueing order only; released before the wait
-    if (data_bytes > 0) CUDA_OK(cudaMemcpyAsync(g->d_pkt.p, data, data_bytes, cudaMemcpyHostToDevice, s));
-    CUDA_OK(cudaMemcpyAsync(d_i, h_i.data(), i32_bytes, cudaMemcpyHostToDevice, s));   // pageable source: staged before return
-    int rc = group_enqueue(g, (const u8*)g->d_pkt.p, d_i, d_i + n, (i16*)g->d_pcm.p, pcm_stride, frame_size,
-                           d_i + 2 * n, g->d_ret, passes, max_len, s);
+    CallCtx cc;
+    int rc = group_call_begin(g, c, nullptr, nullptr, &cc);
+    if (rc != OPUS_OK) return rc;
+    if (data_bytes > 0) CUDA_OK(cudaMemcpyAsync(g->d_pkt.p, data, data_bytes, cudaMemcpyHostToDevice, cc.s_ctl));
+    CUDA_OK(cudaMemcpyAsync(d_i, h_i.data(), i32_bytes, cudaMemcpyHostToDevice, cc.s_ctl));   // pageable source: staged before return
+    rc = group_enqueue(g, c, cc, (const u8*)g->d_pkt.p, d_i, d_i + n, (i16*)g->d_pcm.p, pcm_stride, frame_size,
+                       d_i + 2 * n, g->d_ret, passes, max_len);
     if (rc != OPUS_OK) return rc;
     CUDA_OK(cudaMemcpyAsync(pcm, g->d_pcm.p, pcm_bytes, cudaMemcpyDeviceToHost, s));
     CUDA_OK(cudaMemcpyAsync(ret, g->d_ret, n * sizeof(i32), cudaMemcpyDeviceToHost, s));
@@ -596,10 +701,11 @@ int opus_decode_group_submit(OpusDecoderGroup* g, const unsigned char* data, opu
     g->pipe = p;
   }
   DecPipe* p = g->pipe;
-  DecPipeSlot& sl = p->slot[p->seq & 1];
+  DecPipeSlot& sl = p->slot[p->seq % kPipeDepth];
   if (sl.busy) { CUDA_OK(cudaEventSynchronize(sl.out_done)); sl.busy = false; }
   int max_len = 0;
-  const int passes = scan_passes(g->members, data, offsets, len, decode_fec, n, frame_size, g->Fs, &max_len);
+  const int passes = scan_passes(g->members, data, offsets, len, decode_fec, n, frame_size, g->Fs, &max_len, &g->celt_packets);
+  g->seen_packets = n;
   const size_t pcm_bytes = (size_t)n * pcm_stride * sizeof(i16);
   const size_t in_bytes = (size_t)n * 3 * sizeof(i32);
   if (sl.d_pkt.reserve((size_t)data_bytes + 16) || sl.d_pcm.reserve(pcm_bytes) || sl.d_i32.reserve((size_t)n * 4 * sizeof(i32)) ||
@@ -616,9 +722,11 @@ int opus_decode_group_submit(OpusDecoderGroup* g, const unsigned char* data, opu
   CUDA_OK(cudaEventRecord(sl.in_done, p->s_in));
   cudaStream_t s = c->stream;
   std::lock_guard<std::mutex> lk(c->mu);
-  CUDA_OK(cudaStreamWaitEvent(s, sl.in_done, 0));
-  int rc = group_enqueue(g, (const u8*)sl.d_pkt.p, d_i, d_i + n, (i16*)sl.d_pcm.p, pcm_stride, frame_size, d_i + 2 * n,
-                         d_i + 3 * n, passes, max_len, s);
+  CallCtx cc;
+  int rc = group_call_begin(g, c, nullptr, sl.in_done, &cc);
+  if (rc != OPUS_OK) return rc;
+  rc = group_enqueue(g, c, cc, (const u8*)sl.d_pkt.p, d_i, d_i + n, (i16*)sl.d_pcm.p, pcm_stride, frame_size, d_i + 2 * n,
+                     d_i + 3 * n, passes, max_len);
   if (rc != OPUS_OK) return rc;
   CUDA_OK(cudaEventRecord(sl.k_done, s));
   CUDA_OK(cudaStreamWaitEvent(p->s_out, sl.k_done, 0));
@@ -635,8 +743,8 @@ int opus_decode_group_wait(OpusDecoderGroup* g) {
   if (!g || g->magic != kMagic) return OPUS_BAD_ARG;
   if (!g->pipe) return OPUS_OK;
   CUDA_OK(cudaSetDevice(g->device));
-  for (int k = 0; k < 2; k++) {
-    DecPipeSlot& sl = g->pipe->slot[(g->pipe->seq + k) & 1];     // oldest first
+  for (int k = 0; k < kPipeDepth; k++) {
+    DecPipeSlot& sl = g->pipe->slot[(g->pipe->seq + k) % kPipeDepth];     // oldest first
     if (sl.busy) { CUDA_OK(cudaEventSynchronize(sl.out_done)); sl.busy = false; }
   }
   return OPUS_OK;
@@ -850,7 +958,7 @@ struct MSPipeSlot {
 };
 struct MSPipe {
   cudaStream_t s_in = nullptr, s_out = nullptr;
-  MSPipeSlot slot[2];
+  MSPipeSlot slot[kPipeDepth];
   unsigned long long seq = 0;
 };
 static void ms_pipe_free(MSPipe* p) {
@@ -993,6 +1101,7 @@ static int ms_scan(OpusMSDecoderGroup* g, const unsigned char* data, opus_int32 
   int passes = 1, max_len = 0, any_lost = 0, any_fec = 0, minFs = 48000;
   int group_min = 1 << 30;
   bool unknown = false;
+  int celt = 0, seen = 0;
   for (int m = 0; m < n; m++) {
     OpusMSDecoder* ms = g->members[m];
     if (ms->Fs < minFs) minFs = ms->Fs;
@@ -1009,7 +1118,9 @@ static int ms_scan(OpusMSDecoderGroup* g, const unsigned char* data, opus_int32 
       int cnt = opus_parse_packet(p, rem, s != ms->streams - 1, &toc, sizes, nullptr, &po);
       if (cnt < 0) { parsed_all = false; break; }
       if (cnt > passes) passes = cnt;
-      if (po > max_len) max_len = po;            // kernel A stages one frame of one elementary stream at a time
+      seen++;
+      if ((toc & 0x80) || (toc & 0x60) == 0x60) celt++;
+      if (po > max_len) max_len = po;            // the parse kernel stages one frame of one elementary stream at a time
       int& mf = ms->sub[s]->min_frame_48k;
       const int spf = opus_toc_samples_per_frame(toc, 48000);
       if (mf == 0 || (mf > 0 && spf < mf)) mf = spf;
@@ -1018,6 +1129,8 @@ static int ms_scan(OpusMSDecoderGroup* g, const unsigned char* data, opus_int32 
     }
     if (!parsed_all && len[m] > max_len) max_len = len[m];
   }
+  g->eg->celt_packets = celt;
+  g->eg->seen_packets = seen;
   if (any_lost) {
     for (int m = 0; m < n; m++)
       for (int s = 0; s < g->members[m]->streams; s++) {
@@ -1069,13 +1182,16 @@ int opus_multistream_decode_group_flat(OpusMSDecoderGroup* g, const unsigned cha
   cudaEvent_t done = nullptr;
   {
     std::lock_guard<std::mutex> lk(c->mu);          // queueing order only; released before the wait
-    if (data_bytes > 0) CUDA_OK(cudaMemcpyAsync(g->d_pkt.p, data, data_bytes, cudaMemcpyHostToDevice, s));
-    CUDA_OK(cudaMemcpyAsync(d_i, h_i.data(), i32_bytes, cudaMemcpyHostToDevice, s));
-    int rc = cbk_launch_ms_plan(eg->d_states, eg->d_plans, g->d_layouts, (const u8*)g->d_pkt.p, d_i, d_i + n, d_i + 2 * n,
-                                frame_size, g->d_ms_ret, n, passes, s);
+    CallCtx cc;
+    int rc = group_call_begin(eg, c, nullptr, nullptr, &cc);
+    if (rc != OPUS_OK) return rc;
+    if (data_bytes > 0) CUDA_OK(cudaMemcpyAsync(g->d_pkt.p, data, data_bytes, cudaMemcpyHostToDevice, cc.s_ctl));
+    CUDA_OK(cudaMemcpyAsync(d_i, h_i.data(), i32_bytes, cudaMemcpyHostToDevice, cc.s_ctl));
+    rc = cbk_launch_ms_plan(eg->d_states, eg->d_plans, g->d_layouts, (const u8*)g->d_pkt.p, d_i, d_i + n, d_i + 2 * n,
+                            frame_size, g->d_ms_ret, n, passes, cc.s_ctl);
     g_launches += 1;
     if (rc) { fprintf(stderr, "[opus_b200] ms plan launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
-    rc = group_enqueue_passes(eg, (const u8*)g->d_pkt.p, d_epcm, estride, eg->d_ret, passes, max_len, s);
+    rc = group_enqueue_passes(eg, c, cc, (const u8*)g->d_pkt.p, d_epcm, estride, eg->d_ret, passes, max_len);
     if (rc != OPUS_OK) return rc;
     rc = cbk_launch_ms_scatter(g->d_layouts, g->d_ms_ret, d_epcm, estride, (i16*)g->d_pcm.p, pcm_stride, n, s);
     g_launches += 1;
@@ -1120,7 +1236,7 @@ int opus_multistream_decode_group_submit(OpusMSDecoderGroup* g, const unsigned c
     g->pipe = p;
   }
   MSPipe* p = g->pipe;
-  MSPipeSlot& sl = p->slot[p->seq & 1];
+  MSPipeSlot& sl = p->slot[p->seq % kPipeDepth];
   if (sl.busy) { CUDA_OK(cudaEventSynchronize(sl.out_done)); sl.busy = false; }
   OpusDecoderGroup* eg = g->eg;
   const i32 estride = frame_size * 2;
@@ -1143,12 +1259,14 @@ int opus_multistream_decode_group_submit(OpusMSDecoderGroup* g, const unsigned c
   CUDA_OK(cudaEventRecord(sl.in_done, p->s_in));
   cudaStream_t s = c->stream;
   std::lock_guard<std::mutex> lk(c->mu);
-  CUDA_OK(cudaStreamWaitEvent(s, sl.in_done, 0));
-  int rc = cbk_launch_ms_plan(eg->d_states, eg->d_plans, g->d_layouts, (const u8*)sl.d_pkt.p, d_i, d_i + n, d_i + 2 * n,
-                              frame_size, d_ms_ret, n, passes, s);
+  CallCtx cc;
+  int rc = group_call_begin(eg, c, nullptr, sl.in_done, &cc);
+  if (rc != OPUS_OK) return rc;
+  rc = cbk_launch_ms_plan(eg->d_states, eg->d_plans, g->d_layouts, (const u8*)sl.d_pkt.p, d_i, d_i + n, d_i + 2 * n,
+                          frame_size, d_ms_ret, n, passes, cc.s_ctl);
   g_launches += 1;
   if (rc) { fprintf(stderr, "[opus_b200] ms plan launch failed: %s\n", cudaGetErrorString((cudaError_t)rc)); return OPUS_INTERNAL_ERROR; }
-  rc = group_enqueue_passes(eg, (const u8*)sl.d_pkt.p, d_epcm, estride, eg->d_ret, passes, max_len, s);
+  rc = group_enqueue_passes(eg, c, cc, (const u8*)sl.d_pkt.p, d_epcm, estride, eg->d_ret, passes, max_len);
   if (rc != OPUS_OK) return rc;
   rc = cbk_launch_ms_scatter(g->d_layouts, d_ms_ret, d_epcm, estride, (i16*)sl.d_pcm.p, pcm_stride, n, s);
   g_launches += 1;
@@ -1167,8 +1285,8 @@ int opus_multistream_decode_group_wait(OpusMSDecoderGroup* g) {
   if (!g || g->magic != kMagicMS) return OPUS_BAD_ARG;
   if (!g->pipe) return OPUS_OK;
   CUDA_OK(cudaSetDevice(g->device));
-  for (int k = 0; k < 2; k++) {
-    MSPipeSlot& sl = g->pipe->slot[(g->pipe->seq + k) & 1];      // oldest first
+  for (int k = 0; k < kPipeDepth; k++) {
+    MSPipeSlot& sl = g->pipe->slot[(g->pipe->seq + k) % kPipeDepth];      // oldest first
     if (sl.busy) { CUDA_OK(cudaEventSynchronize(sl.out_done)); sl.busy = false; }
   }
   return OPUS_OK;
@@ -1313,12 +1431,76 @@ cudaStream_t opusb_internal_stream(int* err) {
   return c ? c->stream : nullptr;
 }
 void opusb_internal_count_launches(int n) { g_launches += n; }
+// internal (cb_noalloc.cu): a call that queued its kernels on the device's main stream alone is over; later
+// run-ahead calls order themselves behind it
+void opusb_internal_serial_call_done(int device) {
+  if (device < 0 || device >= OPUSB_MAX_DEVICES) return;
+  DevCtx* c = &g_ctx[device];
+  std::lock_guard<std::mutex> lk(c->mu);
+  ctx_make_streams(c);
+  if (c->streams_ok) cudaEventRecord(c->ev_serial, c->stream);
+}
 int cbk_sm_count(void) {
   int dev = -1;
   if (cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < OPUSB_MAX_DEVICES && g_ctx[dev].sm_count > 0) return g_ctx[dev].sm_count;
   int sm = 0;
   if (dev >= 0 && cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && sm > 0) return sm;
   return 148;
+}
+
+// Timing marks for callers that queue work on the library's own stream (cuda_stream = NULL) and so have no stream
+// of their own to record events on: mark `idx` (0..15) is a timing event recorded on the current device's main
+// stream, behind everything queued so far; opus_b200_timer_elapsed waits for both marks and returns the milliseconds
+// between them.
+static cudaEvent_t g_marks[OPUSB_MAX_DEVICES][16];
+int opus_b200_timer_mark(int idx) {
+  if (idx < 0 || idx >= 16) return OPUS_BAD_ARG;
+  int err = 0;
+  DevCtx* c = ctx_enter(-1, &err);
+  if (!c) return err;
+  std::lock_guard<std::mutex> lk(c->mu);
+  cudaEvent_t& e = g_marks[c->device][idx];
+  if (!e) CUDA_OK(cudaEventCreate(&e));
+  CUDA_OK(cudaEventRecord(e, c->stream));
+  return OPUS_OK;
+}
+int opus_b200_timer_elapsed(int first, int second, double* ms) {
+  if (first < 0 || first >= 16 || second < 0 || second >= 16 || !ms) return OPUS_BAD_ARG;
+  int err = 0;
+  DevCtx* c = ctx_enter(-1, &err);
+  if (!c) return err;
+  cudaEvent_t a = g_marks[c->device][first], b = g_marks[c->device][second];
+  if (!a || !b) return OPUS_BAD_ARG;
+  CUDA_OK(cudaEventSynchronize(b));
+  float t = 0;
+  CUDA_OK(cudaEventElapsedTime(&t, a, b));
+  *ms = t;
+  return OPUS_OK;
+}
+
+// Diagnostic (tools/pipe_trace.py): between trace_begin and trace_end every launch is bracketed by an event pair as
+// with the profile calls, but calls keep their normal schedule; trace_end returns up to `cap` records of
+// (kind, start ms, end ms) relative to the first recorded event.
+int opus_b200_trace_begin(void) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_trace_on = true;
+  return OPUS_OK;
+}
+int opus_b200_trace_end(int* kinds, double* t0, double* t1, int cap) {
+  g_trace_on = false;
+  cudaDeviceSynchronize();
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  int n = 0;
+  cudaEvent_t ref = g_prof.empty() ? nullptr : g_prof[0].a;
+  for (auto& r : g_prof) {
+    float a = 0, b = 0;
+    if (n < cap && ref && cudaEventElapsedTime(&a, ref, r.a) == cudaSuccess && cudaEventElapsedTime(&b, ref, r.b) == cudaSuccess) {
+      kinds[n] = r.kind; t0[n] = a; t1[n] = b; n++;
+    }
+  }
+  for (auto& r : g_prof) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+  g_prof.clear();
+  return n;
 }
 
 int opus_b200_profile_begin(void) {
@@ -1329,12 +1511,12 @@ int opus_b200_profile_begin(void) {
 
 int opus_b200_profile_end(double* ms, long long* counts) {
   g_prof_on = false;
-  for (int k = 0; k < 3; k++) { if (ms) ms[k] = 0; if (counts) counts[k] = 0; }
+  for (int k = 0; k < kProfKinds; k++) { if (ms) ms[k] = 0; if (counts) counts[k] = 0; }
   cudaDeviceSynchronize();
   std::lock_guard<std::mutex> lk(g_prof_mu);
   for (auto& r : g_prof) {
     float t = 0;
-    if (cudaEventElapsedTime(&t, r.a, r.b) == cudaSuccess && r.kind >= 0 && r.kind < 3) {
+    if (cudaEventElapsedTime(&t, r.a, r.b) == cudaSuccess && r.kind >= 0 && r.kind < kProfKinds) {
       if (ms) ms[r.kind] += t;
       if (counts) counts[r.kind] += 1;
     }

@@ -139,8 +139,8 @@ int opus_decode_group_flat(OpusDecoderGroup *grp, const unsigned char *data, opu
                            opus_int32 pcm_stride, int frame_size, const int *decode_fec, int *ret);
 
 /* Pipelined host form.  opus_decode_group_submit() queues the host->device copy of the packets, the
- * kernels and the device->host copy of PCM + return values on separate streams and returns; up to two calls
- * per group are in flight (a third submit waits for the oldest), so the copies of one call overlap with the
+ * kernels and the device->host copy of PCM + return values on separate streams and returns; up to three calls
+ * per group are in flight (a fourth submit waits for the oldest), so the copies of one call overlap with the
  * kernels of its neighbours.  pcm / ret are complete after opus_decode_group_wait().  All buffers must stay
  * alive until then and should be page-locked (cudaHostRegister / cudaMallocHost) for the overlap to happen.
  * Calls on one group run in submission order, so decoder state advances exactly as with the synchronous
@@ -151,8 +151,13 @@ int opus_decode_group_submit(OpusDecoderGroup *grp, const unsigned char *data, o
 int opus_decode_group_wait(OpusDecoderGroup *grp);
 
 /* Device-resident form: every data pointer is a DEVICE pointer on the group's device; nothing is
- * copied and nothing is synchronised -- the work is queued on `cuda_stream` (a cudaStream_t,
- * NULL = the library's own stream).  max_frames = the number of passes the call launches: it must cover the
+ * copied and nothing is synchronised -- the work is queued on `cuda_stream` (a cudaStream_t), in order, or, with
+ * NULL, on the library's own streams, where consecutive calls are PIPELINED: everything of a call that reads
+ * packets (plan, routing, SILK layer, the parse kernel) runs ahead, beside the rebuild / synthesis kernels of the
+ * call before it.  Decoder state advances exactly as with in-order calls; but because the SILK layer of call k+1
+ * may be written while call k still adds its CELT layer, consecutive NULL-stream calls must be given different
+ * d_pcm buffers (two alternating ones are enough) -- or pass a stream.  opus_b200_synchronize() /
+ * opus_b200_timer_mark() order behind all of it.  max_frames = the number of passes the call launches: it must cover the
  * frames of the longest packet (1 for ordinary one-frame packets) AND, where packets can be lost or FEC is
  * requested, the concealment pieces of a call -- a lost packet is concealed in pieces no longer than the last
  * decoded frame, so frame_size / (shortest frame duration in use), plus one for an FEC frame.  A stream that would
@@ -366,11 +371,23 @@ int opus_b200_synchronize(void);
 long long opus_b200_launch_count(void);
 
 /* Per-kernel device timing with CUDA events on the launching stream (used by bench.py for the
- * roofline line).  Between begin and end every kernel launch is bracketed by an event pair;
- * end synchronises and returns summed milliseconds and launch counts for
- * [0] plan kernel, [1] entropy kernel, [2] synthesis kernel. */
+ * roofline line).  Between begin and end every kernel launch is bracketed by an event pair and calls are queued
+ * on one stream (no run-ahead of the parse side, see opus_decode_group_device); end synchronises and returns
+ * summed milliseconds and launch counts for [0] plan + routing + SILK kernel, [1] parse kernel, [2] rebuild
+ * kernel, [3] synthesis kernel. */
 int opus_b200_profile_begin(void);
-int opus_b200_profile_end(double ms[3], long long counts[3]);
+int opus_b200_profile_end(double ms[4], long long counts[4]);
+/* Timing marks for work queued on the library's own stream (cuda_stream = NULL), where the caller has no stream
+ * to record events on: opus_b200_timer_mark(idx), idx 0..15, records a timing event on the current device's main
+ * stream behind everything queued so far; opus_b200_timer_elapsed waits for both marks and returns the
+ * milliseconds from mark `first` to mark `second`.  (No counterpart in the reference.) */
+int opus_b200_timer_mark(int idx);
+int opus_b200_timer_elapsed(int first, int second, double *ms);
+/* Diagnostic (tools/pipe_trace.py): between trace_begin and trace_end every decode launch is bracketed by an event
+ * pair as with the profile calls, but the calls keep their normal schedule; trace_end returns the number of records
+ * (at most cap) of (kind as in opus_b200_profile_end, start ms, end ms) relative to the first recorded launch. */
+int opus_b200_trace_begin(void);
+int opus_b200_trace_end(int *kinds, double *t0, double *t1, int cap);
 
 #ifdef __cplusplus
 }

@@ -25,8 +25,9 @@ int emu_celt_decode(void* state, const unsigned char* payload, int len, int LM, 
   static EntWork ew;
   static SynWork sw;
   static FrameSide side;
+  static FrameTape tape;
   EntFrameCfg cfg = {LM, C, start, end, 0};
-  int rc = celt_entropy_decode(ew, st, &side, payload, len, cfg, final_range);
+  int rc = celt_entropy_decode(ew, st, &side, &tape, payload, len, cfg, final_range);
   if (rc < 0) return rc;
   for (int c = 0; c < st->channels; c++) celt_synth_channel(sw, st, &side, c, pcm);
   return (120 << LM) / st->downsample;
@@ -56,17 +57,19 @@ int emu_opus_decode_capped(void* state, const unsigned char* data, int len, shor
   static unsigned char pkt[1600];
   static SilkCallWork cw;
   static GenWork gw;
+  static FrameTape tape;
   StreamPlan pl;
   i32 ret = 0;
   opus_plan_stream(st, &pl, data, data ? 0 : -1, data ? len : 0, frame_size, fec, 0, nullptr, max_passes);
   ret = pl.ret;
   for (int pass = 0; pass < pl.nframes; pass++) {
     decode_silk_pass(st, &pl, &side, data, pcm, &ret, pass, cw);
-    decode_entropy_pass<false>(ew, pkt, 256, st, &pl, &side, data, &ret, pass);
-    decode_entropy_pass<true>(ew, pkt, 256, st, &pl, &side, data, &ret, pass);
+    side.route = pl.route;
+    decode_entropy_pass<false>(ew, pkt, 256, st, &pl, &side, &tape, data, &ret, pass);
+    decode_entropy_pass<true>(ew, pkt, 256, st, &pl, &side, &tape, data, &ret, pass);
     for (int c = 0; c < st->channels; c++) decode_synth_pass(sw, st, &pl, &side, pcm, c, pass);
     decode_plc_pass(pw, st, &pl, &side, pcm, pass);
-    decode_general_pass(gw, st, &pl, &side, data, pcm, &ret, pass, cw);
+    decode_general_pass(gw, st, &pl, &side, &tape, data, pcm, &ret, pass, cw);
   }
   return ret;
 }
@@ -109,6 +112,7 @@ int emu_ms_decode(void* p, const unsigned char* data, int len, short* pcm, int f
   static short epcm[16][5760 * 2];
   static SilkCallWork cw;
   static GenWork gw;
+  static FrameTape tape;
   const int S = m->L.nb_streams;
   int ret = opus_ms_plan(m->st, m->plans, &m->L, data, data ? 0 : -1, data ? len : 0, frame_size, fec);
   for (int s = 0; s < S; s++) {
@@ -116,11 +120,12 @@ int emu_ms_decode(void* p, const unsigned char* data, int len, short* pcm, int f
     i32 r = pl->ret;
     for (int pass = 0; pass < pl->nframes; pass++) {
       decode_silk_pass(m->st[s], pl, &side, data, epcm[s], &r, pass, cw);
-      decode_entropy_pass<false>(ew, pkt, 256, m->st[s], pl, &side, data, &r, pass);
-      decode_entropy_pass<true>(ew, pkt, 256, m->st[s], pl, &side, data, &r, pass);
+      side.route = pl->route;
+      decode_entropy_pass<false>(ew, pkt, 256, m->st[s], pl, &side, &tape, data, &r, pass);
+      decode_entropy_pass<true>(ew, pkt, 256, m->st[s], pl, &side, &tape, data, &r, pass);
       for (int c = 0; c < m->st[s]->channels; c++) decode_synth_pass(sw, m->st[s], pl, &side, epcm[s], c, pass);
       decode_plc_pass(pw, m->st[s], pl, &side, epcm[s], pass);
-      decode_general_pass(gw, m->st[s], pl, &side, data, epcm[s], &r, pass, cw);
+      decode_general_pass(gw, m->st[s], pl, &side, &tape, data, epcm[s], &r, pass, cw);
     }
   }
   if (ret > 0) {
