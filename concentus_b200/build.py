@@ -7,7 +7,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libopus_b200.so")
-SOURCES = ["cb_kernels.cu", "cb_parse_kernels.cu", "opus_api.cu", "cb_noalloc.cu", "cb_enc_kernels.cu", "opus_enc_api.cu", "cb_silk_kernels.cu", "cb_general_kernels.cu", "opus_repacketizer.cu", "opus_ms_enc_api.cu", "cb_surround_kernels.cu"]
+SOURCES = ["cb_kernels.cu", "cb_parse_kernels.cu", "opus_api.cu", "cb_noalloc.cu", "cb_enc_kernels.cu", "opus_enc_api.cu", "cb_silk_kernels.cu", "cb_general_kernels.cu", "opus_repacketizer.cu", "opus_ms_enc_api.cu", "cb_surround_kernels.cu", "cb_selftest.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "--compiler-options", "-fPIC", "-shared",

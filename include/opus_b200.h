@@ -389,6 +389,12 @@ int opus_b200_timer_elapsed(int first, int second, double *ms);
 int opus_b200_trace_begin(void);
 int opus_b200_trace_end(int *kinds, double *t0, double *t1, int cap);
 
+/* Test support (tests/test_kat.py): the kernels' PVQ index -> pulse vector routine (one lane per vector) and its inverse
+ * (one warp per vector) on arrays of (n, k, index); all pointers are device pointers, y holds count x 176 values.
+ * Follows the reference's celt/tests/test_unit_cwrs32.c. */
+int opus_b200_selftest_cwrs(const int *d_n, const int *d_k, const unsigned *d_idx, int count, short *d_y, int *d_yy,
+                            unsigned *d_back);
+
 #ifdef __cplusplus
 }
 #endif
