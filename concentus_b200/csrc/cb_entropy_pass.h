@@ -69,7 +69,15 @@ CB_FN void decode_entropy_parse(EntWork& w, u8* pkt, int pkt_cap, OpusDecState* 
   const i32 off = pl->off[pass];
   const u8* src = data + off;
   if (pkt && len <= pkt_cap) {
-    CB_LANE_LOOP(i, len) pkt[i] = src[i];
+    if ((((size_t)src | (size_t)pkt) & 3) == 0) {        // four bytes at a time when both ends are word aligned
+      const u32* s4 = (const u32*)src;
+      u32* d4 = (u32*)pkt;
+      const int nw = len >> 2;
+      CB_LANE_LOOP(i, nw) d4[i] = s4[i];
+      CB_LANE_LOOP(i, len & 3) pkt[4 * nw + i] = src[4 * nw + i];
+    } else {
+      CB_LANE_LOOP(i, len) pkt[i] = src[i];
+    }
     src = pkt;
   }
   CB_WSYNC();

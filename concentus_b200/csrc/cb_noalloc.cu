@@ -7,10 +7,10 @@
 // every other stream's audio.  The same goes for hosts that hand the library a fixed GPU memory
 // budget up front (all memory is carved out at start-up, nothing may be requested later).
 // The ordinary batch entry points need an OpusDecoderGroup, whose creation
-// allocates the per-stream scratch (StreamPlan + FrameSide records).  This entry point needs no
+// allocates the per-stream scratch (StreamPlan, FrameSide and FrameTape records).  This entry point needs no
 // group: its scratch is the fixed array below, which is part of the library image.
 //
-// Cost and limit.  The array is OPUS_B200_STATIC_MAX_STREAMS (256) records long, about 1.1 MB, and
+// Cost and limit.  The array is OPUS_B200_STATIC_MAX_STREAMS (256) records long, about 4.1 MB, and
 // every GPU that loads the library keeps it until the process exits.  Batches larger than that are
 // rejected; use a group for them.
 //

@@ -211,7 +211,7 @@ int opus_multistream_decode_group_wait(OpusMSDecoderGroup *grp);
  * a real-time decode thread (allocation takes driver-wide locks, cudaFree synchronises the whole
  * GPU and stalls every other stream's audio) or a host with a fixed, pre-carved GPU memory budget.
  * It takes the decoders directly (no OpusDecoderGroup, whose creation
- * allocates); the per-stream scratch is a fixed array inside the library image, about 1.1 MB, held
+ * allocates); the per-stream scratch is a fixed array inside the library image, about 4.1 MB, held
  * by every GPU that loads the library until the process exits.  Limit: n <= 256
  * (OPUS_B200_STATIC_MAX_STREAMS); more is rejected with OPUS_BAD_ARG and a message on stderr.
  * All pointers except `st` are device pointers; the decoding is bit-identical to
