@@ -328,41 +328,6 @@ CB_FN void emit_frame(i32* buf, int N, CeltDecState* st, int c, i16* pcm, int ac
   CB_WSYNC();
   CB_LANE_LOOPU(j, N) hist[(pos + j) & (CB_HIST - 1)] = buf[j];
   CB_WSYNC();
-#if CB_DEVICE_BUILD
-  {
-    // The recurrence is serial (the truncating multiply does not distribute), but nothing says it has to run out of
-    // shared memory: every lane takes a run of consecutive samples into registers, the lanes then go one after the
-    // other, each handing the filter memory to the next.  Per sample the chain is an add, a wide multiply and a shift
-    // (the 32-bit wrap of x + m is part of the reference's arithmetic and is kept).
-    const int per = (N + 31) >> 5;                 // <= 30 samples per lane (N <= 960)
-    const int lane = CB_LANE();
-    const int j0 = lane * per;
-    i32 y[30];
-#pragma unroll
-    for (int t = 0; t < 30; t++) y[t] = (t < per && j0 + t < N) ? buf[j0 + t] : 0;
-    i32 m = st->preemph_mem[c];
-    CB_NOUNROLL for (int L = 0; L < 32; L++) {
-      if (lane == L) {
-#pragma unroll
-        for (int t = 0; t < 30; t++) {
-          if (t < per && j0 + t < N) {
-            const i32 tmp = add32(y[t], m);
-            m = mult16_32_q15(27853, tmp);
-            y[t] = tmp;
-          }
-        }
-      }
-      m = __shfl_sync(0xffffffffu, m, L);
-    }
-#pragma unroll
-    for (int t = 0; t < 30; t++)
-      if (t < per && j0 + t < N) buf[j0 + t] = y[t];
-    CB_IF_LANE0 {
-      st->preemph_mem[c] = m;
-      st->hist_pos[c] = (pos + N) & (CB_HIST - 1);
-    }
-  }
-#else
   CB_IF_LANE0 {
     i32 m = st->preemph_mem[c];
     for (int j = 0; j < N; j++) {
@@ -373,7 +338,6 @@ CB_FN void emit_frame(i32* buf, int N, CeltDecState* st, int c, i16* pcm, int ac
     st->preemph_mem[c] = m;
     st->hist_pos[c] = (pos + N) & (CB_HIST - 1);
   }
-#endif
   CB_WSYNC();
   const int Nd = N / downsample;
   if (decode_gain == 0) {

@@ -25,7 +25,7 @@
 extern "C" int cbk_sm_count(void);   // SMs of the current device (opus_api.cu)
 
 #ifndef P_SPW
-#define P_SPW 4             // streams per warp (active lanes): fewer streams to a warp = less divergence, more warps
+#define P_SPW 2             // streams per warp (active lanes): fewer streams to a warp = less divergence, more warps
 #endif
 #define P_WARPS 1           // warps per CTA: small CTAs so that a 4096-stream batch spreads over all SMs
 
