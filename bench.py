@@ -151,7 +151,7 @@ DECODE_SPECS = {
               metric="aggregate realtime stream-sec/sec (48k stereo CELT decode)",
               workload="batched CELT decode: 4096 x 48 kHz stereo 96 kbps CBR 20 ms streams (config 2)",
               data="synthetic: rotations of one reference-encoded 250-packet stream (tests/golden/c2_96k_cbr_st.bit)",
-              ncu="r02_entropy_ncu_raw.txt"),
+              ncu=True),
     "2het": dict(fs=48000, ch=2, n=4096, index="index.json",
                  fixtures=[("het_64k_cbr_st", 0.20), ("c2_96k_cbr_st", 0.20), ("het_96k_vbr_st", 0.15),
                            ("c1_128k_cbr_st", 0.20), ("vbr_128k_st", 0.15), ("f10_64k_st", 0.10)],
@@ -163,7 +163,7 @@ DECODE_SPECS = {
               metric="aggregate realtime stream-sec/sec (16k mono SILK decode)",
               workload="batched SILK decode: 16384 x 16 kHz mono 32 kbps 20 ms streams (config 4)",
               data="synthetic: rotations of one reference-encoded stream (tests/golden/silk_wb_mono_32k.bit)",
-              ncu="r02_silk_ncu_raw.txt"),
+              ncu=True),
     "4h": dict(fs=48000, ch=1, n=16384, fixtures=[("hyb_fb_mono_32k", 1.0)], index="index_hybrid.json",
                metric="aggregate realtime stream-sec/sec (48k mono hybrid decode)",
                workload="batched hybrid decode: 16384 x 48 kHz mono 32 kbps 20 ms streams (config 4, hybrid set)",
@@ -173,6 +173,11 @@ ENC_METRIC = "aggregate realtime stream-sec/sec (48k stereo CELT encode)"
 ENC_WORKLOAD = "batched CELT encode: 4096 x 48 kHz stereo 128 kbps CBR cx10 20 ms streams (config 3)"
 MS_METRIC = "aggregate realtime stream-sec/sec (48k 5.1 multistream decode)"
 MS_WORKLOAD = "batched 5.1 multistream decode: 1024 x 48 kHz six-channel 256 kbps 20 ms, 4 % lost (config 5)"
+
+
+# committed ncu --set full summaries (profiles/) of the kernels a roofline line can name: DRAM bytes per launch
+NCU_FILES = {"celt_parse": "r02_parse_ncu_raw.txt", "celt_rebuild": "r02_rebuild_ncu_raw.txt",
+             "celt_synth": "r02_synth_ncu_raw.txt", "plan_silk": "r02_silk_ncu_raw.txt", "encode": "r02_encode_ncu_raw.txt"}
 
 
 class ParityError(RuntimeError):
@@ -604,7 +609,7 @@ class EncodeWorkload(object):
                     alg_bytes=int(self.n * (self.SPF * self.CH * 2 + mean_len)),
                     h2d=int(self.n * self.SPF * self.CH * 2), d2h=int(self.n * self.MAXB + 4 * self.n),
                     api="opus_encode_group_submit/_wait (pinned host buffers, two calls in flight)",
-                    sync_api="opus_encode_group_flat", kernels={"encode": "opus_encode_kernel"}, ncu="r02_encode_ncu_raw.txt")
+                    sync_api="opus_encode_group_flat", kernels={"encode": "opus_encode_kernel"}, ncu=True)
 
     def close(self):
         self.be.close()
@@ -1027,7 +1032,7 @@ def main():
         "parity_gate": gate,
         "isolated_steps": isolated,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": ncu_traffic(d["ncu"]) if d["ncu"] else None, "peak_kind": peak_kind,
+                     "traffic": ncu_traffic(NCU_FILES[dom]) if (dom in NCU_FILES and d["ncu"]) else None, "peak_kind": peak_kind,
                      "kernel": d["kernels"][dom], "kernel_ms": kern_ms, "algorithmic_bytes_per_launch": d["alg_bytes"],
                      "note": "integer/latency-bound path: the HBM fraction is small by construction, profiles/ holds the "
                              "issue-slot utilisation per kernel"},
