@@ -3,6 +3,7 @@ batch follows its own script (losses, DTX, FEC requests, multi-frame and damaged
 streams are decoded by ONE opus_decode_batch call per step, and each must match the compiled
 reference decoder fed the same calls (return value, PCM, final range)."""
 import ctypes
+import os
 
 import numpy as np
 import pytest
@@ -160,5 +161,60 @@ def test_gpu_device_entry_limits():
         # rows must not overlap
         rc, _, _ = call([pk10[5][0]] * 8, 1, 1275, stride=spf * ch - 2)
         assert rc == cb.OPUS_BAD_ARG
+    finally:
+        grp.close()
+
+
+@needs_ref
+def test_gpu_pipelined_device_calls_follow_reference():
+    """Device-resident calls queued back to back on the library's own streams (cuda_stream = NULL): the part of call
+    k+1 that reads packets (plan, routing, SILK layer, parse) runs beside the rebuild / synthesis kernels of call k.
+    A batch that mixes CELT, SILK, hybrid and mode-switching streams, with lost packets, must still do exactly what
+    the reference does, call for call.  Sixteen calls are queued without any synchronisation in between; every call
+    has its own PCM and return-value buffers, which are only read at the end."""
+    import torch
+    from conftest import GOLDEN, read_bit, golden_case
+    lib = cb.load()
+    names = ["c2_96k_cbr_st", "vbr_128k_st", "hyb_swb_st_48k", "silk_wb_st_40k", "trans_hyb_celt_st", "f10_64k_st",
+             "trans_all_st_to24", "hi_510k_st"]
+    packs = [[p for p, _ in read_bit(os.path.join(GOLDEN, nm + ".bit"))] for nm in names]
+    n, spf, ch, calls = 48, 960, 2, 16
+    rng = np.random.default_rng(21)
+    grp = cb.OpusBatchDecoder(48000, ch, n)
+    refs = [RefDecoder(48000, ch) for _ in range(n)]
+    script = []          # per call: list of packets (None = lost)
+    for t in range(calls):
+        row = []
+        for i in range(n):
+            pk = packs[i % len(packs)]
+            p = pk[(3 * i + t) % len(pk)]
+            row.append(None if (t > 1 and rng.random() < 0.08) else p)
+        script.append(row)
+    keep = []
+    try:
+        for t in range(calls):
+            row = script[t]
+            lens_h = np.array([len(p) if p else 0 for p in row], dtype=np.int32)
+            offs_h = np.concatenate([[0], np.cumsum(lens_h)[:-1]]).astype(np.int32)
+            offs_h[lens_h == 0] = -1
+            arena = torch.from_numpy(np.frombuffer(b"".join(p for p in row if p) or b"\0", dtype=np.uint8).copy()).cuda()
+            offs, lens = torch.from_numpy(offs_h).cuda(), torch.from_numpy(lens_h).cuda()
+            pcm = torch.zeros(n * spf * ch, dtype=torch.int16, device="cuda")
+            ret = torch.zeros(n, dtype=torch.int32, device="cuda")
+            keep.append((arena, offs, lens, pcm, ret))
+        torch.cuda.synchronize()
+        for arena, offs, lens, pcm, ret in keep:                     # queue everything, no waiting in between
+            rc = lib.opus_decode_group_device(grp._g, arena.data_ptr(), offs.data_ptr(), lens.data_ptr(), pcm.data_ptr(),
+                                              spf * ch, spf, None, ret.data_ptr(), 8, 1275, None)
+            assert rc == 0
+        assert lib.opus_b200_synchronize() == 0
+        for t in range(calls):
+            pcm = keep[t][3].cpu().numpy().reshape(n, spf, ch)
+            ret = keep[t][4].cpu().numpy()
+            for i in range(n):
+                ra, pa = refs[i].decode_raw(script[t][i], spf)
+                assert ret[i] == ra, (t, i, ret[i], ra)
+                if ra > 0:
+                    assert np.array_equal(pcm[i, :ra], pa[:ra]), (t, i)
     finally:
         grp.close()
