@@ -218,3 +218,92 @@ def test_gpu_pipelined_device_calls_follow_reference():
                     assert np.array_equal(pcm[i, :ra], pa[:ra]), (t, i)
     finally:
         grp.close()
+
+
+@needs_ref
+def test_gpu_entry_points_interleave_on_one_group():
+    """One group driven through every decode entry point in a random order -- the synchronous host call, the pipelined
+    host pair, device-resident calls on the library's streams and on a stream of the caller, the static-scratch call,
+    final-range queries in between -- has to stay in step with the reference: each form queues its work differently
+    (run-ahead or in order), and all of them must order themselves behind whatever the one before left in flight."""
+    import torch
+    from conftest import GOLDEN, read_bit
+    lib = cb.load()
+    names = ["c2_96k_cbr_st", "hyb_swb_st_48k", "silk_wb_st_40k", "vbr_128k_st", "trans_hyb_celt_st"]
+    packs = [[p for p, _ in read_bit(os.path.join(GOLDEN, nm + ".bit"))] for nm in names]
+    n, spf, ch, steps = 40, 960, 2, 36
+    rng = np.random.default_rng(77)
+    grp = cb.OpusBatchDecoder(48000, ch, n)
+    handles = (ctypes.c_void_p * n)(*[d._h for d in grp.decoders])
+    refs = [RefDecoder(48000, ch) for _ in range(n)]
+    stream = torch.cuda.Stream()
+    pending = []                      # (step, pcm tensor/array, ret tensor/array, packets) whose check is deferred
+    keep = []
+
+    def check(t, pcm, ret, row):
+        pcm = np.asarray(pcm.cpu() if hasattr(pcm, "cpu") else pcm).reshape(n, spf, ch)
+        ret = np.asarray(ret.cpu() if hasattr(ret, "cpu") else ret)
+        for i in range(n):
+            ra, pa = refs[i].decode_raw(row[i], spf)
+            assert ret[i] == ra, (t, i, ret[i], ra)
+            if ra > 0:
+                assert np.array_equal(pcm[i, :ra], pa[:ra]), (t, i)
+
+    def drain():
+        assert lib.opus_decode_group_wait(grp._g) == 0
+        assert lib.opus_b200_synchronize() == 0
+        torch.cuda.synchronize()
+        for item in pending:
+            check(*item)
+        del pending[:]
+
+    try:
+        for t in range(steps):
+            row = []
+            for i in range(n):
+                pk = packs[i % len(packs)]
+                row.append(None if (t > 1 and rng.random() < 0.06) else pk[(5 * i + t) % len(pk)])
+            lens_h = np.array([len(p) if p else 0 for p in row], dtype=np.int32)
+            offs_h = np.concatenate([[0], np.cumsum(lens_h)[:-1]]).astype(np.int32)
+            offs_h[lens_h == 0] = -1
+            blob = np.frombuffer(b"".join(p for p in row if p) or b"\0", dtype=np.uint8).copy()
+            mode = int(rng.integers(0, 5))
+            if mode == 0:                                     # synchronous host call
+                drain()
+                ret, pcm = grp.decode_flat(blob, len(blob), offs_h, lens_h, spf)
+                check(t, pcm, ret, row)
+            elif mode == 1:                                   # pipelined host pair
+                pcm = torch.zeros(n * spf * ch, dtype=torch.int16).pin_memory()
+                ret = torch.zeros(n, dtype=torch.int32).pin_memory()
+                a = torch.from_numpy(blob).pin_memory()
+                o, l = torch.from_numpy(offs_h).pin_memory(), torch.from_numpy(lens_h).pin_memory()
+                keep.append((a, o, l))
+                assert lib.opus_decode_group_submit(grp._g, a.data_ptr(), a.numel(), o.data_ptr(), l.data_ptr(), pcm.data_ptr(),
+                                                    spf * ch, spf, None, ret.data_ptr()) == 0
+                pending.append((t, pcm, ret, row))
+            else:                                             # device-resident forms
+                a, o, l = torch.from_numpy(blob).cuda(), torch.from_numpy(offs_h).cuda(), torch.from_numpy(lens_h).cuda()
+                pcm = torch.zeros(n * spf * ch, dtype=torch.int16, device="cuda")
+                ret = torch.zeros(n, dtype=torch.int32, device="cuda")
+                keep.append((a, o, l))
+                torch.cuda.synchronize()
+                if mode == 2:                                 # library streams (run-ahead)
+                    rc = lib.opus_decode_group_device(grp._g, a.data_ptr(), o.data_ptr(), l.data_ptr(), pcm.data_ptr(), spf * ch,
+                                                      spf, None, ret.data_ptr(), 8, 1275, None)
+                elif mode == 3:                               # the caller's stream: order it behind the library's work first
+                    drain()
+                    rc = lib.opus_decode_group_device(grp._g, a.data_ptr(), o.data_ptr(), l.data_ptr(), pcm.data_ptr(), spf * ch,
+                                                      spf, None, ret.data_ptr(), 8, 1275, ctypes.c_void_p(stream.cuda_stream))
+                    stream.synchronize()
+                else:                                         # static scratch, library stream
+                    rc = lib.opus_decode_batch_device_static(handles, n, a.data_ptr(), o.data_ptr(), l.data_ptr(), pcm.data_ptr(),
+                                                             spf * ch, spf, ret.data_ptr(), 8, 1275, None)
+                assert rc == 0
+                pending.append((t, pcm, ret, row))
+            if rng.random() < 0.2:
+                drain()
+                fr = grp.final_ranges()
+                assert [int(x) for x in fr] == [r.final_range for r in refs]
+        drain()
+    finally:
+        grp.close()
