@@ -53,7 +53,7 @@ EXPORTS = [
     "opus_decode_group_submit", "opus_decode_group_wait", "opus_encode_group_submit", "opus_encode_group_wait",
     "opus_decoder_get_final_range_batch", "opus_b200_synchronize", "opus_b200_launch_count",
     "opus_b200_profile_begin", "opus_b200_profile_end", "opus_b200_timer_mark", "opus_b200_timer_elapsed",
-    "opus_b200_trace_begin", "opus_b200_trace_end", "opus_b200_selftest_cwrs",
+    "opus_b200_trace_begin", "opus_b200_trace_end", "opus_b200_selftest_cwrs", "opus_b200_selftest_isqrt",
     "opus_decode_batch_device_static",
     "opus_multistream_decoder_get_size", "opus_multistream_decoder_create", "opus_multistream_decode",
     "opus_multistream_decode_float", "opus_multistream_decoder_ctl", "opus_multistream_decoder_destroy",

@@ -230,7 +230,16 @@ CB_FN i32 frac_mul16(i32 a, i32 b) { return (16384 + (i32)(i16)a * (i32)(i16)b) 
 #define CB_NORM_SCALING 16384
 
 // ---- celt/mathops.c ---------------------------------------------------------------------
-// isqrt32 (mathops.c:42-63): exact floor(sqrt(v))
+// isqrt32 (mathops.c:42-63): exact floor(sqrt(v)).  On the device: a float estimate (good to +-1 over the whole
+// 32-bit range) and an exact correction in 64-bit arithmetic; the reference's bit-by-bit loop is 16 dependent rounds.
+#if defined(__CUDA_ARCH__)
+CB_FN u32 cb_isqrt32(u32 v) {
+  u32 g = __float2uint_rz(__fsqrt_rn(__uint2float_rn(v)));
+  if ((u64)g * g > (u64)v) g--;
+  if ((u64)(g + 1) * (g + 1) <= (u64)v) g++;
+  return g;
+}
+#else
 CB_FN_NOINLINE u32 cb_isqrt32(u32 v) {
   u32 g = 0;
   int bshift = (cb_ilog(v) - 1) >> 1;
@@ -243,6 +252,7 @@ CB_FN_NOINLINE u32 cb_isqrt32(u32 v) {
   } while (bshift >= 0);
   return g;
 }
+#endif
 // celt_rsqrt_norm (mathops.c:90-115): Q16 in [0.25,1) -> Q14 reciprocal sqrt
 CB_FN i16 cb_rsqrt_norm(i32 x) {
   i16 n = (i16)(x - 32768);

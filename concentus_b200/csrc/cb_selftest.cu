@@ -34,3 +34,15 @@ extern "C" int opus_b200_selftest_cwrs(const int* d_n, const int* d_k, const uns
   if (cudaGetLastError() != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) return OPUS_INTERNAL_ERROR;
   return OPUS_OK;
 }
+
+__global__ void selftest_isqrt_kernel(const u32* in, int count, u32* out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < count) out[i] = cb_isqrt32(in[i]);
+}
+// the device form of isqrt32 (float estimate + exact correction, cb_common.h) on an array of inputs
+extern "C" int opus_b200_selftest_isqrt(const unsigned* d_in, int count, unsigned* d_out) {
+  if (count <= 0) return OPUS_BAD_ARG;
+  selftest_isqrt_kernel<<<(count + 255) / 256, 256>>>(d_in, count, d_out);
+  if (cudaGetLastError() != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) return OPUS_INTERNAL_ERROR;
+  return OPUS_OK;
+}

@@ -394,6 +394,8 @@ int opus_b200_trace_end(int *kinds, double *t0, double *t1, int cap);
  * Follows the reference's celt/tests/test_unit_cwrs32.c. */
 int opus_b200_selftest_cwrs(const int *d_n, const int *d_k, const unsigned *d_idx, int count, short *d_y, int *d_yy,
                             unsigned *d_back);
+/* Test support: the device form of isqrt32 (celt/mathops.c:42-63) on an array (device pointers). */
+int opus_b200_selftest_isqrt(const unsigned *d_in, int count, unsigned *d_out);
 
 #ifdef __cplusplus
 }

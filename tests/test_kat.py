@@ -332,3 +332,25 @@ def test_gpu_cwrs_bijection_over_the_mode_table(kat):
     for j in range(0, count, 37):
         kat.kat_cwrsi(ns[j], ks[j], idxs[j], ref.ctypes.data)
         assert np.array_equal(ref[:ns[j]], y[j, :ns[j]]), j
+
+
+@pytest.mark.gpu
+def test_gpu_isqrt_exact():
+    """The device form of isqrt32 (float estimate + 64-bit correction) is exact: every value up to 2^20, the
+    neighbourhood of every perfect square up to 2^32, and a random sample of the whole 32-bit range."""
+    import torch
+    import concentus_b200 as cb
+    lib = cb.load()
+    rng = np.random.default_rng(3)
+    k = np.arange(1, 65536, dtype=np.uint64)
+    near = np.concatenate([k * k - 1, k * k, k * k + 1, np.array([0xFFFFFFFF, 0xFFFE0001, 0xFFFE0000], dtype=np.uint64)])
+    vals = np.concatenate([np.arange(1, 1 << 20, dtype=np.uint64), near[near < (1 << 32)],
+                           rng.integers(1, 1 << 32, 2000000, dtype=np.uint64)]).astype(np.uint32)
+    d_in = torch.from_numpy(vals.view(np.int32)).cuda()
+    d_out = torch.zeros_like(d_in)
+    vp = ctypes.c_void_p
+    lib.opus_b200_selftest_isqrt.argtypes = [vp, ctypes.c_int, vp]
+    assert lib.opus_b200_selftest_isqrt(d_in.data_ptr(), len(vals), d_out.data_ptr()) == 0
+    got = d_out.cpu().numpy().view(np.uint32).astype(np.uint64)
+    v = vals.astype(np.uint64)
+    assert bool((got * got <= v).all()) and bool(((got + 1) * (got + 1) > v).all())
