@@ -539,6 +539,7 @@ CB_FN int cb_allocation(W& w, AC& ac, int start, int end, int alloc_trim, int& i
   int lo = 1, hi = 11 - 1;                    // nbAllocVectors = 11
   CB_NOUNROLL do {
     const int mid = (lo + hi) >> 1;
+#if CB_DEVICE_BUILD
     int top_l = -1;
     CB_LANE_LOOP(jj, nb) {
       const int j = start + jj;
@@ -558,6 +559,23 @@ CB_FN int cb_allocation(W& w, AC& ac, int start, int end, int alloc_trim, int& i
       else if (bitsj >= C << CB_BITRES) psum_l += C << CB_BITRES;
     }
     const i32 psum0 = cb_wsum(psum_l);
+#else
+    // scalar builds (one thread per stream): the reference's single high-to-low scan (rate.c:567-585)
+    i32 psum0 = 0;
+    int done = 0;
+    CB_NOUNROLL for (int j = end; j-- > start;) {
+      const int wdt = ebands(j + 1) - ebands(j);
+      int bitsj = C * wdt * ct_band_alloc[mid * CB_NBANDS + j] << LM >> 2;
+      if (bitsj > 0) bitsj = cb_imax(0, bitsj + trim_offset[j]);
+      bitsj += w.offsets[j];
+      if (bitsj >= thresh[j] || done) {
+        done = 1;
+        psum0 += cb_imin(bitsj, w.cap[j]);
+      } else if (bitsj >= C << CB_BITRES) {
+        psum0 += C << CB_BITRES;
+      }
+    }
+#endif
     if (psum0 > total) hi = mid - 1; else lo = mid + 1;
   } while (lo <= hi);
   hi = lo--;
@@ -588,6 +606,7 @@ CB_FN int cb_allocation(W& w, AC& ac, int start, int end, int alloc_trim, int& i
   hi = 1 << CB_ALLOC_STEPS;
   CB_NOUNROLL for (int it = 0; it < CB_ALLOC_STEPS; it++) {
     const int mid = (lo + hi) >> 1;
+#if CB_DEVICE_BUILD
     int top_l = -1;
     CB_LANE_LOOP(jj, nb) {
       const int j = start + jj;
@@ -603,6 +622,19 @@ CB_FN int cb_allocation(W& w, AC& ac, int start, int end, int alloc_trim, int& i
       else if (tmp >= alloc_floor) psum_l += alloc_floor;
     }
     psum = cb_wsum(psum_l);
+#else
+    psum = 0;                                                  // rate.c:275-293, one scan
+    int done = 0;
+    CB_NOUNROLL for (int j = end; j-- > start;) {
+      const int tmp = bits1[j] + (int)((i32)mid * bits2[j] >> CB_ALLOC_STEPS);
+      if (tmp >= thresh[j] || done) {
+        done = 1;
+        psum += cb_imin(tmp, w.cap[j]);
+      } else if (tmp >= alloc_floor) {
+        psum += alloc_floor;
+      }
+    }
+#endif
     if (psum > total) hi = mid; else lo = mid;
   }
   {
