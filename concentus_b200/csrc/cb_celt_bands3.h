@@ -29,6 +29,7 @@ struct TapeW {
   int jobs, notes, bitwords;        // totals written so far
   int seg_jobs, seg_notes;          // counts inside the open segment
   int seg_bits;                     // bits inside the open segment (its words start at bitwords - seg_bits / 32)
+  int call_empty;                   // leaves without pulses since the band call began
   u32 acc;                          // the partly filled word
   int nseg, seg_band0;
 };
@@ -36,6 +37,7 @@ struct TapeW {
 struct B3Cur {
   int jobs, tape, bits;
   TapeW* tw;                        // PARSE only
+  const TapeJob* seg_jobs;          // REBUILD only: the segment's leaf records (tape, global memory)
 };
 
 CB_FN void b3_push_bit(EntWork&, B3Cur& c, int v) {
@@ -58,10 +60,11 @@ CB_FN void b3_push(EntWork&, B3Cur& c, int v) {
   tw.seg_notes++;
 }
 CB_FN int b3_pop(const EntWork& w, B3Cur& c) { return w.b3_buf[CB_B3_BUF - 1 - c.tape++]; }
-CB_FN void b3_push_job(B3Cur& c, int xoff, int N, int K, u32 idx, i32 gain, int B, int spread) {
+CB_FN void b3_push_job(B3Cur& c, int xoff, int N, int K, u32 idx, i32 gain, int B, int spread, int sh) {
   TapeW& tw = *c.tw;
   TapeJob jb;
   jb.idx = idx; jb.xoff = (u16)xoff; jb.N = (i16)N; jb.K = (i16)K; jb.gain = (i16)gain; jb.B = (u8)B; jb.spread = (u8)spread;
+  jb.sh = (u8)sh; jb.pad = 0;
   tw.t->jobs[tw.jobs++] = jb;
   tw.seg_jobs++;
 }
@@ -79,8 +82,8 @@ CB_FN void b3_close_segment(TapeW& tw, int band) {
   tw.seg_band0 = band;
 }
 // Upper bounds of what one band can add: L = most leaves of one channel's partition tree (a node splits
-// while LM >= 0 and N > 2); per channel L - 1 split angles and L leaves (a job and a mask each), plus the
-// stereo angle; per node a split bit, per split an order bit, per leaf one bit, a few per band.
+// while LM >= 0 and N > 2); per channel L leaves (a record on the tape, a mask in the rebuild warp's buffer) and
+// the leaf count, plus the stereo angle; a handful of bits per band (signs, inv, order, update_lowband).
 CB_FN int b3_band_leaves(int N, int LM) {
   int L = 1;
   CB_NOUNROLL while (LM >= 0 && N > 2) { L <<= 1; N >>= 1; LM--; }
@@ -200,130 +203,78 @@ CB_FN u32 b3_leaf(i16* X, int N, int K, u32 idx, i32 gain, int B, int spread) {
   }
   return mask;
 }
-// Phase 2: lanes take the segment's jobs (records in the tape, global memory); the collapse mask of job j
-// goes to w.b3_buf[j].
+// Phase 2: lanes take the segment's leaves (records in the tape, global memory); the collapse mask of leaf j,
+// already at its place in the band's mask, goes to w.b3_buf[j].  Leaves without pulses wait for phase 3.
 CB_FN void b3_run_jobs(EntWork& w, const TapeJob* jobs, int njobs) {
   CB_WSYNC();
   CB_LANE_LOOP(j, njobs) {
     const TapeJob jb = jobs[j];
-    w.b3_buf[j] = (u16)b3_leaf(w.X + jb.xoff, jb.N, jb.K, jb.idx, jb.gain, jb.B, jb.spread);
+    u32 m = 0;
+    if (jb.K > 0) m = b3_leaf(w.X + jb.xoff, jb.N, jb.K, jb.idx, jb.gain, jb.B, jb.spread) << jb.sh;
+    w.b3_buf[j] = (u16)m;
   }
   CB_WSYNC();
 }
 
-// ---- leaf of the split recursion (bands.c:966-1038) ----------------------------------------------
-template <bool REBUILD>
-CB_FN u32 b3_leaf_node(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, int xo, int N, int b, int B,
-                       const i16* lowband, int LM, i32 gain, int fill) {
-  if (!REBUILD) {
-    int q = bits2pulses_lanes(cx.i, LM, b);
-    int curr_bits = pulses2bits(cx.i, LM, q);
+// ---- leaf of the split recursion (bands.c:966-1038), PARSE: the pulse count and the PVQ index -------------
+CB_FN void b3_leaf_node(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, int xo, int N, int b, int B, int LM,
+                        i32 gain, int sh, int fz) {
+  int q = bits2pulses_lanes(cx.i, LM, b);
+  int curr_bits = pulses2bits(cx.i, LM, q);
+  cx.remaining_bits -= curr_bits;
+  CB_NOUNROLL while (cx.remaining_bits < 0 && q > 0) {
+    cx.remaining_bits += curr_bits;
+    q--;
+    curr_bits = pulses2bits(cx.i, LM, q);
     cx.remaining_bits -= curr_bits;
-    CB_NOUNROLL while (cx.remaining_bits < 0 && q > 0) {
-      cx.remaining_bits += curr_bits;
-      q--;
-      curr_bits = pulses2bits(cx.i, LM, q);
-      cx.remaining_bits -= curr_bits;
-    }
-    if (q != 0) {
-      const int K = get_pulses(q);
-      const u32 idx = rd_uint(rd, pvq_u(N, K) + pvq_u(N, K + 1));
-      b3_push_bit(w, cur, 1);
-      b3_push_job(cur, xo, N, K, idx, gain, B, cx.spread);
-    } else {
-      b3_push_bit(w, cur, 0);
-    }
-    return 0;
   }
-  if (b3_pop_bit(w, cur)) return w.b3_buf[cur.jobs++];          // the leaf carries pulses: decoded in phase 2
-  i16* const X = w.X + xo;
-  u32 cm = 0;
-  const u32 cm_mask = (u32)((1ull << B) - 1);
-  fill &= (int)cm_mask;
-  CB_WSYNC();
-  if (!fill) {
-    CB_LANE_LOOP(j, N) X[j] = 0;
-    CB_WSYNC();
+  if (q != 0) {
+    const int K = get_pulses(q);
+    const u32 idx = rd_uint(rd, pvq_u(N, K) + pvq_u(N, K + 1));
+    b3_push_job(cur, xo, N, K, idx, gain, B, cx.spread, sh);
   } else {
-    const u32 seed0 = cx.seed;
-    if (lowband == nullptr) {                                   // noise
-      CB_LANE_LOOP(j, N) X[j] = (i16)((i32)cb_lcg_skip(seed0, (u32)j + 1) >> 20);
-      cm = cm_mask;
-    } else {                                                    // folded spectrum, +-1/256 dither
-      CB_LANE_LOOP(j, N) {
-        const u32 sd = cb_lcg_skip(seed0, (u32)j + 1);
-        const i32 t = (sd & 0x8000u) ? 4 : -4;
-        X[j] = (i16)(lowband[j] + t);
-      }
-      cm = (u32)fill;
-    }
-    cx.seed = cb_lcg_skip(seed0, (u32)N);
-    v_renormalise(X, N, gain);
+    b3_push_job(cur, xo, N, 0, (u32)fz, gain, B, 0, sh);
+    cur.tw->call_empty++;
   }
-  return cm;
 }
 
-// ---- quant_partition (bands.c:864-1040) as an explicit stack ---------------------------------------
-template <bool REBUILD>
-CB_FN u32 b3_partition(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, int xo0, int N0, int b0, int B_0,
-                       i16* lowband0, int LM0, i32 gain0, int fill0) {
+// ---- quant_partition (bands.c:864-1040) as an explicit stack, PARSE ----------------------------------
+// Besides the bitstream work this tracks, for every node, what the rebuild half needs of the recursion:
+// the gain (products of the split angles' cosines), where the node's collapse bits sit in the band's mask
+// (bands.c:957-960: the side half is shifted by B0 >> 1 -- the same shift its share of `fill` had on the way
+// down, bands.c:933,947) and whether an angle of 0 / 16384 above it masked that share off (bands.c:789-799).
+CB_FN void b3_partition(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, int xo0, int N0, int b0, int B_0, int LM0,
+                        i32 gain0) {
   PartFrame* st = w.stack;
   int sp = 0;
-  st[0].xo = (u16)xo0; st[0].lo = lowband0; st[0].N = N0; st[0].b = b0; st[0].B = B_0;
-  st[0].LM = LM0; st[0].gain = gain0; st[0].fill = fill0; st[0].stage = 0;
-  u32 ret = 0;
+  st[0].xo = (u16)xo0; st[0].N = N0; st[0].b = b0; st[0].B = B_0;
+  st[0].LM = LM0; st[0].gain = gain0; st[0].sh = 0; st[0].fz = 0; st[0].stage = 0;
   CB_NOUNROLL while (sp >= 0) {
     PartFrame& f = st[sp];
     if (f.stage == 0) {
-      int N = f.N, b = f.b, B = f.B, LM = f.LM, fill = f.fill;
-      int split;
-      if (!REBUILD) {
-        const u8* cache = pulse_cache(cx.i, LM);
-        split = LM != -1 && b > cache[cache[0]] + 12 && N > 2;
-        b3_push_bit(w, cur, split);
-      } else {
-        split = b3_pop_bit(w, cur);
-      }
+      int N = f.N, b = f.b, B = f.B, LM = f.LM;
+      const u8* cache = pulse_cache(cx.i, LM);
+      const int split = LM != -1 && b > cache[cache[0]] + 12 && N > 2;
       if (split) {
         const int B0 = B;
         N >>= 1;
         LM -= 1;
-        if (B == 1) fill = (fill & 1) | (fill << 1);
         B = (B + 1) >> 1;
-        int itheta, imid, iside, mid_first;
-        int mbits = 0, sbits = 0;
-        if (!REBUILD) {
-          Split& s = w.sp_store;
-          dec_theta(rd, s, cx.i, cx.intensity, cx.remaining_bits, N, b, B, B0, LM, 0, fill);
-          b = s.b;
-          int delta = s.delta;
-          itheta = s.itheta; imid = s.imid; iside = s.iside;
-          const int s_qalloc = s.qalloc;
-          if (B0 > 1 && (itheta & 0x3fff)) {
-            if (itheta > 8192) delta -= delta >> (4 - LM);
-            else delta = cb_imin(0, delta + (N << CB_BITRES >> (5 - LM)));
-          }
-          mbits = cb_imax(0, cb_imin(b, (b - delta) / 2));
-          sbits = b - mbits;
-          cx.remaining_bits -= s_qalloc;
-          mid_first = mbits >= sbits;
-          b3_push(w, cur, itheta);
-          b3_push_bit(w, cur, mid_first);
-        } else {
-          itheta = b3_pop(w, cur);
-          mid_first = b3_pop_bit(w, cur);
-          if (itheta == 0) {
-            imid = 32767; iside = 0;
-            fill &= (1 << B) - 1;
-          } else if (itheta == 16384) {
-            imid = 0; iside = 32767;
-            fill &= ((1 << B) - 1) << B;
-          } else {
-            imid = bitexact_cos((i16)itheta);
-            iside = bitexact_cos((i16)(16384 - itheta));
-          }
+        Split& s = w.sp_store;
+        dec_theta(rd, s, cx.i, cx.intensity, cx.remaining_bits, N, b, B, B0, LM, 0);
+        b = s.b;
+        int delta = s.delta;
+        const int itheta = s.itheta, imid = s.imid, iside = s.iside;
+        const int s_qalloc = s.qalloc;
+        if (B0 > 1 && (itheta & 0x3fff)) {
+          if (itheta > 8192) delta -= delta >> (4 - LM);
+          else delta = cb_imin(0, delta + (N << CB_BITRES >> (5 - LM)));
         }
-        f.N = N; f.B = B; f.LM = LM; f.fill = fill; f.B0 = B0;
+        const int mbits = cb_imax(0, cb_imin(b, (b - delta) / 2));
+        const int sbits = b - mbits;
+        cx.remaining_bits -= s_qalloc;
+        const int mid_first = mbits >= sbits;
+        f.N = N; f.B = B; f.LM = LM; f.dsh = (u8)(B0 >> 1);
         f.mbits = mbits; f.sbits = sbits; f.itheta = itheta;
         f.rebal0 = cx.remaining_bits;
         f.gmid = mult16_16_p15(f.gain, imid);
@@ -332,48 +283,84 @@ CB_FN u32 b3_partition(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, int xo
         PartFrame& c = st[sp + 1];
         c.N = N; c.B = B; c.LM = LM; c.stage = 0;
         if (mid_first) {
-          c.xo = f.xo; c.lo = f.lo; c.b = mbits; c.gain = (i16)f.gmid; c.fill = fill;
+          c.xo = f.xo; c.b = mbits; c.gain = (i16)f.gmid;
+          c.sh = f.sh; c.fz = (u8)(f.fz | (itheta == 16384));
         } else {
-          c.xo = f.xo + N; c.lo = f.lo ? f.lo + N : nullptr; c.b = sbits;
-          c.gain = (i16)f.gside; c.fill = fill >> B;
+          c.xo = f.xo + N; c.b = sbits; c.gain = (i16)f.gside;
+          c.sh = (u8)(f.sh + f.dsh); c.fz = (u8)(f.fz | (itheta == 0));
         }
         sp++;
       } else {
-        ret = b3_leaf_node<REBUILD>(w, cx, rd, cur, f.xo, N, b, B, f.lo, LM, f.gain, fill);
+        b3_leaf_node(w, cx, rd, cur, f.xo, N, b, B, LM, f.gain, f.sh, f.fz);
         sp--;
       }
     } else if (f.stage == 1) {                   // mid done, now side
-      f.cm = (u16)ret;
-      if (!REBUILD) {
-        const i32 rebalance = f.mbits - (f.rebal0 - cx.remaining_bits);
-        if (rebalance > 3 << CB_BITRES && f.itheta != 0) f.sbits += rebalance - (3 << CB_BITRES);
-      }
+      const i32 rebalance = f.mbits - (f.rebal0 - cx.remaining_bits);
+      if (rebalance > 3 << CB_BITRES && f.itheta != 0) f.sbits += rebalance - (3 << CB_BITRES);
       PartFrame& c = st[sp + 1];
       c.N = f.N; c.B = f.B; c.LM = f.LM; c.stage = 0;
-      c.xo = f.xo + f.N; c.lo = f.lo ? f.lo + f.N : nullptr; c.b = f.sbits;
-      c.gain = (i16)f.gside; c.fill = f.fill >> f.B;
+      c.xo = f.xo + f.N; c.b = f.sbits; c.gain = (i16)f.gside;
+      c.sh = (u8)(f.sh + f.dsh); c.fz = (u8)(f.fz | (f.itheta == 0));
       f.stage = 2;
       sp++;
-    } else if (f.stage == 2) {
-      ret = (u32)f.cm | (ret << (f.B0 >> 1));
-      sp--;
     } else if (f.stage == 3) {                   // side done, now mid
-      f.cm = (u16)(ret << (f.B0 >> 1));
-      if (!REBUILD) {
-        const i32 rebalance = f.sbits - (f.rebal0 - cx.remaining_bits);
-        if (rebalance > 3 << CB_BITRES && f.itheta != 16384) f.mbits += rebalance - (3 << CB_BITRES);
-      }
+      const i32 rebalance = f.sbits - (f.rebal0 - cx.remaining_bits);
+      if (rebalance > 3 << CB_BITRES && f.itheta != 16384) f.mbits += rebalance - (3 << CB_BITRES);
       PartFrame& c = st[sp + 1];
       c.N = f.N; c.B = f.B; c.LM = f.LM; c.stage = 0;
-      c.xo = f.xo; c.lo = f.lo; c.b = f.mbits; c.gain = (i16)f.gmid; c.fill = f.fill;
+      c.xo = f.xo; c.b = f.mbits; c.gain = (i16)f.gmid;
+      c.sh = f.sh; c.fz = (u8)(f.fz | (f.itheta == 16384));
       f.stage = 4;
       sp++;
-    } else {
-      ret = (u32)f.cm | ret;
+    } else {                                     // both halves done
       sp--;
     }
   }
-  return ret;
+}
+
+// ---- REBUILD: the leaves of one band call, in the order the walk reached them ----------------------------
+// Leaves with pulses were decoded in phase 2.  What is left of quant_partition is the collapse mask of the call --
+// the OR of the leaves' masks, each at its place (bands.c:957-960) -- and the leaves without pulses
+// (bands.c:1003-1036): zeros, noise, or the folded spectrum with a +-1/256 dither, renormalised to the leaf's gain.
+// `note` = the number of leaves, + 256 when one of them is without pulses.
+CB_FN u32 b3_leaves_rebuild(EntWork& w, BandCtx& cx, B3Cur& cur, int note, int xo, const i16* lowband, int fill) {
+  const int nl = note & 0xff;
+  const int j0 = cur.jobs;
+  cur.jobs += nl;
+  u32 cm = 0;
+  CB_LANE_LOOP(l, nl) cm |= w.b3_buf[j0 + l];
+  cm = cb_wor(cm);
+  if (!(note & 0x100)) return cm;
+  CB_NOUNROLL for (int l = 0; l < nl; l++) {
+    const TapeJob jb = cur.seg_jobs[j0 + l];
+    if (jb.K != 0) continue;
+    const int N = jb.N;
+    i16* const X = w.X + jb.xoff;
+    const u32 cm_mask = (u32)((1ull << jb.B) - 1);
+    const u32 lf = jb.idx ? 0u : (((u32)fill >> jb.sh) & cm_mask);
+    CB_WSYNC();
+    if (!lf) {
+      CB_LANE_LOOP(j, N) X[j] = 0;
+      CB_WSYNC();
+      continue;
+    }
+    const u32 seed0 = cx.seed;
+    if (lowband == nullptr) {                                     // noise
+      CB_LANE_LOOP(j, N) X[j] = (i16)((i32)cb_lcg_skip(seed0, (u32)j + 1) >> 20);
+      cm |= cm_mask << jb.sh;
+    } else {                                                      // folded spectrum, +-1/256 dither
+      const i16* lo = lowband + ((int)jb.xoff - xo);
+      CB_LANE_LOOP(j, N) {
+        const u32 sd = cb_lcg_skip(seed0, (u32)j + 1);
+        const i32 t = (sd & 0x8000u) ? 4 : -4;
+        X[j] = (i16)(lo[j] + t);
+      }
+      cm |= lf << jb.sh;
+    }
+    cx.seed = cb_lcg_skip(seed0, (u32)N);
+    v_renormalise(X, N, jb.gain);
+  }
+  return cm & 0xffffu;
 }
 
 // ---- quant_band (bands.c:1044-1172) ----------------------------------------------------------------
@@ -435,8 +422,15 @@ CB_FN u32 b3_band(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, int xo, int
   const int N_B0 = N_B;
   if (REBUILD && B0 > 1 && lowband) v_deinterleave(lowband, tmp, N_B >> recombine, B0 << recombine, longBlocks);
 
-  u32 cm = b3_partition<REBUILD>(w, cx, rd, cur, xo, N, b, B, lowband, LM, gain, fill);
-  if (!REBUILD) return 0;
+  if (!REBUILD) {                                                // the tree onto the tape: its leaves, then how many
+    TapeW& tw = *cur.tw;
+    const int j0 = tw.jobs;
+    tw.call_empty = 0;
+    b3_partition(w, cx, rd, cur, xo, N, b, B, LM, gain);
+    b3_push(w, cur, (tw.jobs - j0) | (tw.call_empty ? 0x100 : 0));
+    return 0;
+  }
+  u32 cm = b3_leaves_rebuild(w, cx, cur, b3_pop(w, cur), xo, lowband, fill);
 
   if (B0 > 1) v_interleave(X, tmp, N_B >> recombine, B0 << recombine, longBlocks);
   N_B = N_B0;
@@ -579,7 +573,7 @@ CB_FN void b3_one_band(EntWork& w, RangeDec& rd, B3Cur& cur, BandCtx& cx, B3Pars
     const int orig_fill = fill;
     if (!REBUILD) {
       Split& sh = w.sp_store;
-      dec_theta(rd, sh, cx.i, cx.intensity, cx.remaining_bits, N, b, B, B, LM, 1, fill);
+      dec_theta(rd, sh, cx.i, cx.intensity, cx.remaining_bits, N, b, B, B, LM, 1);
       const Split s = sh;
       itheta = s.itheta; inv = s.inv; imid = s.imid; iside = s.iside;
       b3_push(w, cur, itheta);
@@ -718,10 +712,12 @@ CB_FN void dec_bands_parse(EntWork& w, RangeDec& rd, TapeW& tw, int start, int e
   B3Cur wr;
   wr.jobs = wr.tape = wr.bits = 0;
   wr.tw = &tw;
+  wr.seg_jobs = nullptr;
   tw.seg_band0 = start;
+  tw.call_empty = 0;
   CB_NOUNROLL for (int i = start; i < end; i++) {
     const int L = b3_band_leaves(M * (ebands(i + 1) - ebands(i)), LM);
-    const bool full = tw.seg_jobs + tw.seg_notes + 4 * L + 2 > CB_B3_BUF || tw.seg_bits + 10 * L + 4 > CB_B3_SEG_BITS;
+    const bool full = tw.seg_jobs + tw.seg_notes + 2 * L + 3 > CB_B3_BUF || tw.seg_bits + 8 > CB_B3_SEG_BITS;
     if (i > tw.seg_band0 && (full || i == CB_NBANDS - 1)) b3_close_segment(tw, i);
     b3_one_band<false>(w, rd, wr, cxp, ps, rs, i, start, end, C, Nfrm, B, spread, intensity, total_bits, LM, codedBands);
   }
@@ -760,6 +756,7 @@ CB_FN void dec_bands_rebuild(EntWork& w, const FrameTape* t, int start, int end,
     B3Cur rdc;
     rdc.jobs = rdc.tape = rdc.bits = 0;
     rdc.tw = nullptr;
+    rdc.seg_jobs = t->jobs + job0;
     CB_NOUNROLL for (int r = sg.band0; r < sg.band1; r++)
       b3_one_band<true>(w, w.rd, rdc, cxr, ps, rs, r, start, end, C, Nfrm, B, spread, intensity, 0, LM, 0);
     job0 += sg.jobs;

@@ -39,7 +39,7 @@ CB_UTABLE u8 ct_bit_deinterleave[16] = {0x00, 0x03, 0x0C, 0x0F, 0x30, 0x33, 0x3C
 #define CB_FINE_OFFSET 21
 #define CB_ALLOC_STEPS 6
 
-struct Split { int inv, imid, iside, delta, itheta, qalloc, b, fill; };   // b/fill: updated in/out values
+struct Split { int inv, imid, iside, delta, itheta, qalloc, b; };   // b: updated in/out value
 
 // Three-phase band decoder (cb_celt_bands3.h): what one tape segment may hold (the rebuild warp's copy of it)
 #ifndef CB_B3_BUF
@@ -50,11 +50,13 @@ struct Split { int inv, imid, iside, delta, itheta, qalloc, b, fill; };   // b/f
 
 // One level of the split recursion (quant_partition), kept in shared memory.
 struct PartFrame {
-  const i16* lo;                  // folding source of this node (the stream's norm scratch in global memory, or the
-                                  //   band-scratch slot of X in shared memory), nullptr: none
   i32 b, mbits, sbits, rebal0;
-  u16 xo, cm, fill, pad0;         // xo: offset of the node in X
-  i16 N, B, LM, gain, stage, itheta, B0, gmid, gside, pad;
+  u16 xo;                         // offset of the node in X
+  i16 N, B, LM, gain, stage, itheta, gmid, gside;
+  u8 sh;                          // where this node's collapse bits (and its share of `fill`) sit in the band's mask
+  u8 fz;                          // an angle above (0 or 16384) leaves this node nothing to fold
+  u8 dsh;                         // B0 >> 1 of the split at this node: how far its side half is shifted
+  u8 pad;
 };
 
 // Per-stream workspace of the entropy half (shared memory): one per warp, or -- in the parse kernel, which is
@@ -259,7 +261,7 @@ CB_FN int bitexact_log2tan(int isin, int icos) {   // bands.c:82-93
 // A real call (one copy of the code): inputs by value, results through the Split record, which
 // lives in shared memory (EntWork::sp).
 CB_FN_NOINLINE void dec_theta(RangeDec& rd, Split& sp, int band, int intensity, i32 remaining_bits, int N, int b,
-                              int B, int B0, int LM, int stereo, int fill) {
+                              int B, int B0, int LM, int stereo) {
   int itheta = 0, inv = 0;
   int pulse_cap = ct_logN400[band] + LM * (1 << CB_BITRES);
   int offset = (pulse_cap >> 1) - (stereo && N == 2 ? 16 : 4);
@@ -307,11 +309,9 @@ CB_FN_NOINLINE void dec_theta(RangeDec& rd, Split& sp, int band, int intensity, 
   int imid, iside, delta;
   if (itheta == 0) {
     imid = 32767; iside = 0;
-    fill &= (1 << B) - 1;
     delta = -16384;
   } else if (itheta == 16384) {
     imid = 0; iside = 32767;
-    fill &= ((1 << B) - 1) << B;
     delta = 16384;
   } else {
     imid = bitexact_cos((i16)itheta);
@@ -319,7 +319,7 @@ CB_FN_NOINLINE void dec_theta(RangeDec& rd, Split& sp, int band, int intensity, 
     delta = frac_mul16((N - 1) << 7, bitexact_log2tan(iside, imid));
   }
   sp.inv = inv; sp.imid = imid; sp.iside = iside; sp.delta = delta; sp.itheta = itheta; sp.qalloc = qalloc;
-  sp.b = b; sp.fill = fill;
+  sp.b = b;
 }
 
 

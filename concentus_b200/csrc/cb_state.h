@@ -66,17 +66,21 @@ struct alignas(16) FrameSide {
 // Sizes are the worst case of a 20 ms stereo frame: a band's channel splits into at most 16 leaves (bands of
 // 32+ bins at LM = 3), 8 for 16 bins, 4 for 8 bins: 208 leaves per channel.
 #define CB_TAPE_MAX_JOBS 416
-#define CB_TAPE_MAX_NOTES 448      // one split angle per inner node (< leaves) plus the stereo angle of every band
-#define CB_TAPE_BITWORDS 160       // <= 10 bits per leaf + 4 per band, plus one word of slack per segment
+#define CB_TAPE_MAX_NOTES 448      // per band: the stereo angle and the leaf count of each channel call (far fewer than this)
+#define CB_TAPE_BITWORDS 160       // a few bits per band, plus one word of slack per segment
 #define CB_TAPE_MAX_SEG 24
 #define CB_TAPE_NONE 0             // nothing for the rebuild half
 #define CB_TAPE_FRAME 1            // a decoded frame
 #define CB_TAPE_NOISE 2            // noise-based concealment: random normalised bands at the energies in bandE
-struct TapeJob {                   // a leaf with pulses (alg_unquant after the index has been read)
-  u32 idx;                         // PVQ index
+struct TapeJob {                   // a leaf of a band's split tree, in the order the walk reaches them
+  u32 idx;                         // K > 0: PVQ index (alg_unquant after the index has been read)
+                                   // K == 0, a leaf without pulses (zeros / noise / folded spectrum): 1 = the
+                                   //   angles above it leave it nothing to fold (its share of `fill` is masked off)
   u16 xoff;                        // where the leaf lies in X
   i16 N, K, gain;
   u8 B, spread;
+  u8 sh;                           // where the leaf's collapse bits sit in the band's mask (and in `fill`)
+  u8 pad;
 };
 struct TapeSeg {                   // a run of bands whose notes fit the rebuild warp's shared memory
   u8 band0, band1;
