@@ -1,65 +1,41 @@
 // cb_celt_bands3.h -- quant_all_bands, decoder side (bands.c:1337-1502), as three phases per frame:
 //
 //   1. PARSE   the range decoder walks bands / stereo splits / partitions exactly as the reference
-//              does, but touches no spectrum: it writes the shape of the recursion on a TAPE (FrameTape,
-//              cb_state.h: split angles as 16-bit notes, a bit per node) and, for every leaf that carries
-//              pulses, a job record (PVQ index and its parameters).  Nothing in this phase has any width,
-//              so it runs either warp-uniform or -- in the parse kernel (cb_parse_kernels.cu) -- ONE
-//              THREAD PER STREAM, 32 streams to a warp.
+//              does, but touches no spectrum.  It leaves a TAPE (FrameTape, cb_state.h): one record per
+//              LEAF of the split trees in walk order (PVQ index and its parameters, the gain the angles
+//              above it give it, where its collapse bits go in the band's mask) and one record per
+//              BAND (stereo mode and angle, folding source, leaf counts).  Nothing in this phase has any
+//              width, so it runs either warp-uniform or -- in the parse kernel (cb_parse_kernels.cu) --
+//              ONE THREAD PER STREAM.
 //   2. PULSES  the leaves are independent of each other: ONE LANE PER LEAF turns index -> pulse vector
 //              (cwrsi is a serial walk), normalises, applies the spreading rotation and leaves the
 //              collapse mask.
-//   3. REBUILD the same walk again, driven by the tape instead of the bitstream: folding / noise fill
-//              of the empty leaves, Hadamard / Haar recombination, stereo merge, lowband for the bands
-//              to come -- the lane-parallel vector work.
+//   3. REBUILD band by band from the records, no tree walk: folding / noise fill of the leaves
+//              without pulses, Hadamard / Haar recombination, stereo merge, folding memory for the
+//              bands to come -- the lane-parallel vector work.
 //
 // Nothing the decoder reads from the bitstream depends on the spectrum (collapse masks and folding
-// only steer reconstruction), which is what makes the split legal.  Phases 1 and 3 are one piece of
-// code (template <bool REBUILD>), so the two walks cannot drift apart.  The tape is cut into segments
-// (runs of bands) whose notes and masks fit the rebuild warp's shared memory; phases 2 + 3 go segment by
+// only steer reconstruction), which is what makes the split legal.  The tape is cut into segments
+// (runs of bands) whose leaf masks fit the rebuild warp's shared memory; phases 2 + 3 go segment by
 // segment.
 #pragma once
 
-#define CB_B3_SEG_BITS (32 * CB_B3_BITWORDS)
-
-// Writer side of the tape (PARSE): cursors in registers, the tape itself in global memory.  Node bits are
-// collected in a register and stored a word at a time.
+// Writer side of the tape (PARSE): cursors in registers, the tape itself in global memory.
 struct TapeW {
   FrameTape* t;
-  int jobs, notes, bitwords;        // totals written so far
-  int seg_jobs, seg_notes;          // counts inside the open segment
-  int seg_bits;                     // bits inside the open segment (its words start at bitwords - seg_bits / 32)
+  int jobs;                         // leaf records written so far
+  int seg_jobs;                     // ... of them in the open segment
   int call_empty;                   // leaves without pulses since the band call began
-  u32 acc;                          // the partly filled word
   int nseg, seg_band0;
 };
-// Reader side (REBUILD): cursors into the segment's copy in shared memory
+// Reader side (REBUILD)
 struct B3Cur {
-  int jobs, tape, bits;
+  int jobs;                         // REBUILD: next leaf, counted from the segment's first
+  int seg_job0;                     // REBUILD: the segment's first leaf record
   TapeW* tw;                        // PARSE only
   const TapeJob* seg_jobs;          // REBUILD only: the segment's leaf records (tape, global memory)
 };
 
-CB_FN void b3_push_bit(EntWork&, B3Cur& c, int v) {
-  TapeW& tw = *c.tw;
-  tw.acc |= (u32)(v != 0) << (tw.seg_bits & 31);
-  tw.seg_bits++;
-  if ((tw.seg_bits & 31) == 0) {
-    tw.t->bits[tw.bitwords++] = tw.acc;
-    tw.acc = 0;
-  }
-}
-CB_FN int b3_pop_bit(const EntWork& w, B3Cur& c) {
-  const int v = (w.b3_bits[c.bits >> 5] >> (c.bits & 31)) & 1;
-  c.bits++;
-  return v;
-}
-CB_FN void b3_push(EntWork&, B3Cur& c, int v) {
-  TapeW& tw = *c.tw;
-  tw.t->notes[tw.notes++] = (u16)v;
-  tw.seg_notes++;
-}
-CB_FN int b3_pop(const EntWork& w, B3Cur& c) { return w.b3_buf[CB_B3_BUF - 1 - c.tape++]; }
 CB_FN void b3_push_job(B3Cur& c, int xoff, int N, int K, u32 idx, i32 gain, int B, int spread, int sh) {
   TapeW& tw = *c.tw;
   TapeJob jb;
@@ -70,20 +46,15 @@ CB_FN void b3_push_job(B3Cur& c, int xoff, int N, int K, u32 idx, i32 gain, int 
 }
 // close the open segment at band `band` (exclusive end) and start the next one there
 CB_FN void b3_close_segment(TapeW& tw, int band) {
-  if (tw.seg_bits & 31) {                       // the partly filled word; the next segment starts on a fresh one
-    tw.t->bits[tw.bitwords++] = tw.acc;
-    tw.acc = 0;
-  }
   TapeSeg sg;
   sg.band0 = (u8)tw.seg_band0; sg.band1 = (u8)band;
-  sg.jobs = (u16)tw.seg_jobs; sg.notes = (u16)tw.seg_notes; sg.bitwords = (u16)((tw.seg_bits + 31) >> 5);
+  sg.jobs = (u16)tw.seg_jobs;
   tw.t->seg[tw.nseg++] = sg;
-  tw.seg_jobs = tw.seg_notes = tw.seg_bits = 0;
+  tw.seg_jobs = 0;
   tw.seg_band0 = band;
 }
-// Upper bounds of what one band can add: L = most leaves of one channel's partition tree (a node splits
-// while LM >= 0 and N > 2); per channel L leaves (a record on the tape, a mask in the rebuild warp's buffer) and
-// the leaf count, plus the stereo angle; a handful of bits per band (signs, inv, order, update_lowband).
+// Upper bound of what one band can add: L = most leaves of one channel's partition tree (a node splits
+// while LM >= 0 and N > 2); per channel L leaves (a record on the tape, a mask in the rebuild warp's buffer).
 CB_FN int b3_band_leaves(int N, int LM) {
   int L = 1;
   CB_NOUNROLL while (LM >= 0 && N > 2) { L <<= 1; N >>= 1; LM--; }
@@ -322,15 +293,15 @@ CB_FN void b3_partition(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, int x
 // Leaves with pulses were decoded in phase 2.  What is left of quant_partition is the collapse mask of the call --
 // the OR of the leaves' masks, each at its place (bands.c:957-960) -- and the leaves without pulses
 // (bands.c:1003-1036): zeros, noise, or the folded spectrum with a +-1/256 dither, renormalised to the leaf's gain.
-// `note` = the number of leaves, + 256 when one of them is without pulses.
+// `note` = the number of leaves, + 128 when one of them is without pulses.
 CB_FN u32 b3_leaves_rebuild(EntWork& w, BandCtx& cx, B3Cur& cur, int note, int xo, const i16* lowband, int fill) {
-  const int nl = note & 0xff;
+  const int nl = note & 127;
   const int j0 = cur.jobs;
   cur.jobs += nl;
   u32 cm = 0;
   CB_LANE_LOOP(l, nl) cm |= w.b3_buf[j0 + l];
   cm = cb_wor(cm);
-  if (!(note & 0x100)) return cm;
+  if (!(note & 128)) return cm;
   CB_NOUNROLL for (int l = 0; l < nl; l++) {
     const TapeJob jb = cur.seg_jobs[j0 + l];
     if (jb.K != 0) continue;
@@ -363,56 +334,189 @@ CB_FN u32 b3_leaves_rebuild(EntWork& w, BandCtx& cx, B3Cur& cur, int note, int x
   return cm & 0xffffu;
 }
 
-// ---- quant_band (bands.c:1044-1172) ----------------------------------------------------------------
-template <bool REBUILD>
-CB_FN u32 b3_band(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, int xo, int N, int b, int B, i16* lowband,
-                  int LM, i16* lowband_out, i32 gain, i16* lowband_scratch, int fill) {
+// ---- quant_band (bands.c:1044-1172), PARSE ----------------------------------------------------------
+// What the band call reads from the bitstream: a sign when N == 1 (bands.c:819-858), else the split tree on the
+// block layout tf_change leaves (the Haar / interleave steps themselves are the rebuild's).  Returns the note for
+// the band record: the number of leaves the call wrote, + 128 when one of them is without pulses; N == 1: the sign.
+CB_FN int b3_band_parse(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, int xo, int N, int b, int B, int LM,
+                        i32 gain) {
+  if (N == 1) {
+    int sign = 0;
+    if (cx.remaining_bits >= 1 << CB_BITRES) {
+      sign = (int)rd_bits(rd, 1);
+      cx.remaining_bits -= 1 << CB_BITRES;
+    }
+    return sign;
+  }
+  int tf_change = cx.tf_change;
+  int N_B = N >> cb_ilog2(B);                                    // block counts are powers of two
+  if (tf_change > 0) {
+    B >>= tf_change;
+    N_B <<= tf_change;
+  }
+  CB_NOUNROLL while ((N_B & 1) == 0 && tf_change < 0) {
+    B <<= 1;
+    N_B >>= 1;
+    tf_change++;
+  }
+  TapeW& tw = *cur.tw;
+  const int j0 = tw.jobs;
+  tw.call_empty = 0;
+  b3_partition(w, cx, rd, cur, xo, N, b, B, LM, gain);
+  return (tw.jobs - j0) | (tw.call_empty ? 128 : 0);
+}
+
+// What the parse walk carries from band to band.
+struct B3Parse { i32 balance; int dual_stereo, lowband_offset, update_lowband; };
+
+// One band of quant_all_bands (bands.c:1383-1498) with quant_band_stereo (bands.c:1176-1334) folded in, PARSE:
+// the band's bit budget, stereo angle and split trees from the bitstream, and the band record for the rebuild.
+CB_FN void b3_one_band_parse(EntWork& w, RangeDec& rd, B3Cur& cur, BandCtx& cx, B3Parse& ps, int i, int start, int end,
+                             int C, int Nfrm, int B, int spread, int intensity, i32 total_bits, int LM, int codedBands) {
+  const int M = 1 << LM;
+  const bool stereo = C == 2;
+  const int norm_offset = M * ebands(start);
+  cx.i = i;
+  const int xo = M * ebands(i), yo = Nfrm + xo;                  // the band in X, per channel
+  const int N = M * ebands(i + 1) - xo;
+  const int tf_change = w.tf_res[i];
+  cx.tf_change = tf_change;
+  const i32 tell = (i32)rd_tell_frac(rd);
+  if (i != start) ps.balance -= tell;
+  const i32 remaining_bits = total_bits - tell - 1;
+  cx.remaining_bits = remaining_bits;
+  int b = 0;
+  if (i <= codedBands - 1) {
+    const i32 curr_balance = ps.balance / cb_imin(3, codedBands - i);     // celt_sudiv
+    b = cb_imax(0, cb_imin(16383, cb_imin(remaining_bits + 1, w.pulses[i] + curr_balance)));
+  }
+  TapeBand r;
+  r.job0 = (u16)cur.tw->jobs;
+  r.nl[0] = r.nl[1] = 0;
+  r.itheta = 0; r.imid = 0; r.iside = 0;
+  int flags = 0;
+  // folding source and the bands whose collapse masks it brings (bands.c:1408-1428)
+  if (xo - N >= norm_offset && (ps.update_lowband || ps.lowband_offset == 0)) ps.lowband_offset = i;
+  int effective_lowband = -1, fold_start = 0, fold_end = 0;
+  if (ps.lowband_offset != 0 && (spread != CB_SPREAD_AGGRESSIVE || B > 1 || tf_change < 0)) {
+    effective_lowband = cb_imax(0, M * ebands(ps.lowband_offset) - norm_offset - N);
+    fold_start = ps.lowband_offset;
+    CB_NOUNROLL while (M * ebands(--fold_start) > effective_lowband + norm_offset) {}
+    fold_end = ps.lowband_offset - 1;
+    CB_NOUNROLL while (M * ebands(++fold_end) < effective_lowband + norm_offset + N) {}
+  }
+  r.eff_lowband = (i16)effective_lowband;
+  r.fold0 = (u8)fold_start; r.fold1 = (u8)fold_end;
+  if (ps.dual_stereo && i == intensity) {
+    ps.dual_stereo = 0;
+    flags |= CB_TBF_SWITCH;
+  }
+  // The band call is big: it is instantiated at ONE call site (instruction-cache footprint is what bounds the
+  // parse kernel), so the cases below only describe up to two calls and a loop makes them.
+  int mode, ncalls = 2;
+  int cX0 = xo, cX1 = yo;
+  i32 cb0 = 0, cb1 = 0, cg0 = CB_Q15ONE, cg1 = CB_Q15ONE;
+  int rebal = 0, blocked = 0;                                    // joint stereo: what the first call leaves goes to the second
+  i32 rebalance0 = 0;
+  if (ps.dual_stereo) {
+    mode = CB_TB_DUAL;
+    cb0 = cb1 = b / 2;
+  } else if (!stereo) {
+    mode = CB_TB_MONO;
+    ncalls = 1;
+    cb0 = b;
+  } else if (N == 1) {                                           // quant_band_n1 on both channels (bands.c:819-858)
+    mode = CB_TB_N1;
+  } else {
+    // stereo split (compute_theta with stereo = 1, bands.c:1200-1220)
+    Split& sh = w.sp_store;
+    dec_theta(rd, sh, cx.i, cx.intensity, cx.remaining_bits, N, b, B, B, LM, 1);
+    const Split s = sh;
+    const int itheta = s.itheta;
+    r.itheta = (i16)itheta; r.imid = (i16)s.imid; r.iside = (i16)s.iside;
+    if (s.inv) flags |= CB_TBF_INV;
+    if (N == 2) {                                                // bands.c:1222-1262
+      mode = CB_TB_JOINT2;
+      ncalls = 1;
+      int mbits = s.b, sbits = 0;
+      if (itheta != 0 && itheta != 16384) sbits = 1 << CB_BITRES;
+      mbits -= sbits;
+      cx.remaining_bits -= s.qalloc + sbits;
+      if (sbits && rd_bits(rd, 1)) flags |= CB_TBF_N2_NEG;
+      cX0 = itheta > 8192 ? yo : xo;
+      cb0 = mbits;
+    } else {                                                     // bands.c:1263-1318
+      mode = CB_TB_JOINT;
+      const i32 mbits = cb_imax(0, cb_imin(s.b, (s.b - s.delta) / 2));
+      const i32 sbits = s.b - mbits;
+      cx.remaining_bits -= s.qalloc;
+      rebalance0 = cx.remaining_bits;
+      rebal = 1;
+      if (mbits >= sbits) {                                      // mid first
+        flags |= CB_TBF_MID_FIRST;
+        cb0 = mbits; cb1 = sbits; cg1 = s.iside;
+        blocked = itheta == 0;
+      } else {                                                   // side first
+        cX0 = yo; cX1 = xo;
+        cb0 = sbits; cb1 = mbits; cg0 = s.iside;
+        blocked = itheta == 16384;
+      }
+    }
+  }
+  int note0 = 0, note1 = 0;
+  CB_NOUNROLL for (int jn = 0; jn < ncalls; jn++) {
+    i32 jb = jn ? cb1 : cb0;
+    if (jn == 1 && rebal) {
+      const i32 rebalance = cb0 - (rebalance0 - cx.remaining_bits);
+      if (rebalance > 3 << CB_BITRES && !blocked) jb += rebalance - (3 << CB_BITRES);
+    }
+    const int nt = b3_band_parse(w, cx, rd, cur, jn ? cX1 : cX0, N, jb, B, LM, jn ? cg1 : cg0);
+    if (jn) note1 = nt; else note0 = nt;
+  }
+  if (N == 1) flags |= (note0 ? CB_TBF_SIGN0 : 0) | (note1 ? CB_TBF_SIGN1 : 0);
+  else { r.nl[0] = (u8)note0; r.nl[1] = (u8)note1; }
+  r.mode = (u8)mode; r.flags = (u8)flags;
+  cur.tw->t->band[i] = r;
+  ps.balance += w.pulses[i] + tell;
+  ps.update_lowband = b > (N << CB_BITRES);
+}
+
+// ---- quant_band (bands.c:1044-1172), REBUILD -------------------------------------------------------------
+// The call's spectrum from its leaves: the folding source brought to the block layout of the leaves (Haar steps,
+// deinterleave), the leaves without pulses filled from it, the layout undone on the result, the collapse mask and
+// the folding memory for the bands to come.  `note` as b3_band_parse returned it; `sign`: N == 1.
+CB_FN u32 b3_band_rebuild(EntWork& w, BandCtx& cx, B3Cur& cur, int band, int xo, int N, int B, i16* lowband,
+                          i16* lowband_out, i16* lowband_scratch, int fill, int note, int sign) {
+  i16* const X = w.X + xo;
+  if (N == 1) {                                                  // quant_band_n1 (bands.c:819-858), one channel
+    CB_WSYNC();
+    X[0] = sign ? -CB_NORM_SCALING : CB_NORM_SCALING;
+    CB_WSYNC();
+    if (lowband_out) lowband_out[0] = (i16)(X[0] >> 4);
+    return 1;
+  }
   const int N0 = N;
-  i16* const X = REBUILD ? w.X + xo : nullptr;
-  int N_B = N / B, B0 = B;
+  int N_B = N >> cb_ilog2(B), B0 = B;                            // block counts are powers of two
   int time_divide = 0, recombine = 0;
   const int longBlocks = B0 == 1;
   int tf_change = cx.tf_change;
   i16* tmp = (i16*)w.tmp32;
-  if (N == 1) {                                                  // quant_band_n1 (bands.c:819-858), one channel
-    if (!REBUILD) {
-      int sign = 0;
-      if (cx.remaining_bits >= 1 << CB_BITRES) {
-        sign = (int)rd_bits(rd, 1);
-        cx.remaining_bits -= 1 << CB_BITRES;
-      }
-      b3_push_bit(w, cur, sign);
-    } else {
-      const int sign = b3_pop_bit(w, cur);
-      CB_WSYNC();
-      X[0] = sign ? -CB_NORM_SCALING : CB_NORM_SCALING;
-      CB_WSYNC();
-      if (lowband_out) lowband_out[0] = (i16)(X[0] >> 4);
-    }
-    return 1;
-  }
   if (tf_change > 0) recombine = tf_change;
-  if (REBUILD) {
-    if (lowband_scratch && lowband && (recombine || ((N_B & 1) == 0 && tf_change < 0) || B0 > 1)) {
-      CB_WSYNC();
-      CB_LANE_LOOP(j, N) lowband_scratch[j] = lowband[j];
-      CB_WSYNC();
-      lowband = lowband_scratch;
-    }
+  if (lowband_scratch && lowband && (recombine || ((N_B & 1) == 0 && tf_change < 0) || B0 > 1)) {
+    CB_WSYNC();
+    CB_LANE_LOOP(j, N) lowband_scratch[j] = lowband[j];
+    CB_WSYNC();
+    lowband = lowband_scratch;
   }
   CB_NOUNROLL for (int k = 0; k < recombine; k++) {
-    if (REBUILD) {
-      if (lowband) v_haar1(lowband, N >> k, 1 << k);
-      fill = ct_bit_interleave[fill & 0xF] | ct_bit_interleave[fill >> 4] << 2;
-    }
+    if (lowband) v_haar1(lowband, N >> k, 1 << k);
+    fill = ct_bit_interleave[fill & 0xF] | ct_bit_interleave[fill >> 4] << 2;
   }
   B >>= recombine;
   N_B <<= recombine;
   CB_NOUNROLL while ((N_B & 1) == 0 && tf_change < 0) {
-    if (REBUILD) {
-      if (lowband) v_haar1(lowband, N_B, B);
-      fill |= fill << B;
-    }
+    if (lowband) v_haar1(lowband, N_B, B);
+    fill |= fill << B;
     B <<= 1;
     N_B >>= 1;
     time_divide++;
@@ -420,17 +524,9 @@ CB_FN u32 b3_band(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, int xo, int
   }
   B0 = B;
   const int N_B0 = N_B;
-  if (REBUILD && B0 > 1 && lowband) v_deinterleave(lowband, tmp, N_B >> recombine, B0 << recombine, longBlocks);
+  if (B0 > 1 && lowband) v_deinterleave(lowband, tmp, N_B >> recombine, B0 << recombine, longBlocks);
 
-  if (!REBUILD) {                                                // the tree onto the tape: its leaves, then how many
-    TapeW& tw = *cur.tw;
-    const int j0 = tw.jobs;
-    tw.call_empty = 0;
-    b3_partition(w, cx, rd, cur, xo, N, b, B, LM, gain);
-    b3_push(w, cur, (tw.jobs - j0) | (tw.call_empty ? 0x100 : 0));
-    return 0;
-  }
-  u32 cm = b3_leaves_rebuild(w, cx, cur, b3_pop(w, cur), xo, lowband, fill);
+  u32 cm = b3_leaves_rebuild(w, cx, cur, note, xo, lowband, fill);
 
   if (B0 > 1) v_interleave(X, tmp, N_B >> recombine, B0 << recombine, longBlocks);
   N_B = N_B0;
@@ -447,7 +543,7 @@ CB_FN u32 b3_band(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, int xo, int
   }
   B <<= recombine;
   if (lowband_out) {
-    const i16 n = (i16)cb_sqrt(shl32(N0, 22));
+    const i16 n = w.sqrtN[band];                                 // celt_sqrt(SHL32(EXTEND32(N0), 22))
     CB_WSYNC();
     CB_LANE_LOOP(j, N0) lowband_out[j] = (i16)mult16_16_q15(n, X[j]);
     CB_WSYNC();
@@ -456,243 +552,130 @@ CB_FN u32 b3_band(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, int xo, int
   return cm;
 }
 
-// What the two walks carry from band to band.
-struct B3Parse { i32 balance; int dual_stereo; };
-struct B3Rebuild { int dual_stereo, lowband_offset, update_lowband; };
-
-// One band of quant_all_bands, with quant_band_stereo (bands.c:1176-1334) folded in.
-template <bool REBUILD>
-CB_FN void b3_one_band(EntWork& w, RangeDec& rd, B3Cur& cur, BandCtx& cx, B3Parse& ps, B3Rebuild& rs, int i, int start,
-                       int end, int C, int Nfrm, int B, int spread, int intensity, i32 total_bits, int LM, int codedBands) {
+// One band of quant_all_bands (bands.c:1383-1498) with quant_band_stereo (bands.c:1176-1334) folded in, REBUILD,
+// from the band's record.
+CB_FN void b3_one_band_rebuild(EntWork& w, B3Cur& cur, BandCtx& cx, int i, int start, int end, int C, int Nfrm, int B,
+                               int LM) {
+  const TapeBand r = w.bands[i];
   const int M = 1 << LM;
-  const bool stereo = C == 2;
   const int norm_offset = M * ebands(start);
   const int last = (i == end - 1);
+  const int xo = M * ebands(i), yo = Nfrm + xo;                  // the band in X, per channel
+  const int N = M * ebands(i + 1) - xo;
+  i16* const norm = w.norm;
+  i16* const norm2 = w.norm + CB_NORM_STRIDE;
+  i16* const lowband_scratch = last ? nullptr : w.X + M * ebands(CB_NBANDS - 1);
+  i16* const X = w.X + xo;
+  i16* const Y = w.X + yo;                                       // (stereo modes only)
   cx.i = i;
-  const int xo = M * ebands(i), yo = Nfrm + M * ebands(i);     // the band in X, per channel
-  // (the spectrum exists in the REBUILD walk only; the PARSE walk works on offsets)
-  i16* norm = REBUILD ? w.norm : nullptr;
-  i16* norm2 = REBUILD ? w.norm + CB_NORM_STRIDE : nullptr;
-  i16* lowband_scratch = (!REBUILD || last) ? nullptr : w.X + M * ebands(CB_NBANDS - 1);
-  i16* X = REBUILD ? w.X + xo : nullptr;
-  i16* Y = (REBUILD && stereo) ? w.X + yo : nullptr;
-  const int N = M * ebands(i + 1) - M * ebands(i);
-  const int tf_change = w.tf_res[i];
-  cx.tf_change = tf_change;
-  int b = 0;
-  i32 tell = 0;
-  if (!REBUILD) {
-    tell = (i32)rd_tell_frac(rd);
-    if (i != start) ps.balance -= tell;
-    const i32 remaining_bits = total_bits - tell - 1;
-    cx.remaining_bits = remaining_bits;
-    if (i <= codedBands - 1) {
-      const i32 curr_balance = ps.balance / cb_imin(3, codedBands - i);     // celt_sudiv
-      b = cb_imax(0, cb_imin(16383, cb_imin(remaining_bits + 1, w.pulses[i] + curr_balance)));
-    }
-  }
-  // folding source and the collapse masks it brings (REBUILD only)
+  cx.tf_change = w.tf_res[i];
+  cur.jobs = (int)r.job0 - cur.seg_job0;
+  const int mode = r.mode, flags = r.flags;
+  // folding source and the collapse masks it brings
   i16 *lb = nullptr, *lb2 = nullptr, *lout = nullptr, *lout2 = nullptr;
   u32 x_cm = 0, y_cm = 0;
-  if (REBUILD) {
-    if (M * ebands(i) - N >= M * ebands(start) && (rs.update_lowband || rs.lowband_offset == 0)) rs.lowband_offset = i;
-    int effective_lowband = -1;
-    if (rs.lowband_offset != 0 && (spread != CB_SPREAD_AGGRESSIVE || B > 1 || tf_change < 0)) {
-      effective_lowband = cb_imax(0, M * ebands(rs.lowband_offset) - norm_offset - N);
-      int fold_start = rs.lowband_offset;
-      CB_NOUNROLL while (M * ebands(--fold_start) > effective_lowband + norm_offset) {}
-      int fold_end = rs.lowband_offset - 1;
-      CB_NOUNROLL while (M * ebands(++fold_end) < effective_lowband + norm_offset + N) {}
-      int fold_i = fold_start;
-      CB_NOUNROLL do {
-        x_cm |= w.collapse[fold_i * C + 0];
-        y_cm |= w.collapse[fold_i * C + C - 1];
-      } while (++fold_i < fold_end);
-    } else {
-      x_cm = y_cm = (u32)((1 << B) - 1);
+  if (r.eff_lowband >= 0) {
+    CB_NOUNROLL for (int f = r.fold0; f < r.fold1; f++) {
+      x_cm |= w.collapse[f * C + 0];
+      y_cm |= w.collapse[f * C + C - 1];
     }
-    if (effective_lowband != -1) { lb = norm + effective_lowband; lb2 = norm2 + effective_lowband; }
-    if (!last) { lout = norm + M * ebands(i) - norm_offset; lout2 = norm2 + M * ebands(i) - norm_offset; }
-  }
-  int& dual_stereo = REBUILD ? rs.dual_stereo : ps.dual_stereo;
-  if (dual_stereo && i == intensity) {
-    dual_stereo = 0;
-    if (REBUILD) {
-      const int cnt = M * ebands(i) - norm_offset;
-      CB_WSYNC();
-      CB_LANE_LOOP(j, cnt) norm[j] = (i16)(((i32)norm[j] + (i32)norm2[j]) >> 1);
-      CB_WSYNC();
-    }
-  }
-  // The band decoder is big: it is instantiated at ONE call site per walk (instruction-cache footprint is what
-  // bounds this kernel), so the cases below only describe up to two calls -- the channel vector, its bit
-  // budget, gain and folding inputs -- and a loop makes them.
-  int mode;                       // 0 mono, 1 dual stereo, 2 joint stereo N > 2, 3 joint stereo N == 2, 4 done (N == 1)
-  int njobs = 0;
-  int jX0 = xo, jX1 = yo;
-  int jb0 = 0, jb1 = 0, jfill0 = 0, jfill1 = 0;
-  i32 jgain1 = CB_Q15ONE;
-  bool j1_fold = true;            // second call gets lowband / lowband_out / scratch (dual stereo) or none (side)
-  int itheta = 0, inv = 0, imid = 0, iside = 0;
-  int mbits = 0, sbits = 0, mid_first = 1, n2_sign = 1;
-  i32 rebalance0 = 0;
-  u32 cm = 0;
-  if (dual_stereo) {
-    mode = 1;
-    njobs = 2;
-    jb0 = jb1 = b / 2;
-    jfill0 = (int)x_cm; jfill1 = (int)y_cm;
-  } else if (!stereo) {
-    mode = 0;
-    njobs = 1;
-    jb0 = b;
-    jfill0 = (int)(x_cm | y_cm);
-  } else if (N == 1) {                                           // quant_band_n1 on both channels (bands.c:819-858)
-    mode = 4;
-    if (!REBUILD) {
-      CB_NOUNROLL for (int c = 0; c < 2; c++) {
-        int sign = 0;
-        if (cx.remaining_bits >= 1 << CB_BITRES) {
-          sign = (int)rd_bits(rd, 1);
-          cx.remaining_bits -= 1 << CB_BITRES;
-        }
-        b3_push_bit(w, cur, sign);
-      }
-    } else {
-      const int sx = b3_pop_bit(w, cur), sy = b3_pop_bit(w, cur);
-      CB_WSYNC();
-      X[0] = sx ? -CB_NORM_SCALING : CB_NORM_SCALING;
-      Y[0] = sy ? -CB_NORM_SCALING : CB_NORM_SCALING;
-      CB_WSYNC();
-      if (lout) lout[0] = (i16)(X[0] >> 4);
-    }
-    cm = 1;
+    lb = norm + r.eff_lowband;
+    lb2 = norm2 + r.eff_lowband;
   } else {
-    // stereo split (compute_theta with stereo = 1, bands.c:1200-1220)
+    x_cm = y_cm = (u32)((1 << B) - 1);
+  }
+  if (!last) { lout = norm + xo - norm_offset; lout2 = norm2 + xo - norm_offset; }
+  if (flags & CB_TBF_SWITCH) {                                   // dual stereo ends here (bands.c:1430-1437)
+    const int cnt = xo - norm_offset;
+    CB_WSYNC();
+    CB_LANE_LOOP(j, cnt) norm[j] = (i16)(((i32)norm[j] + (i32)norm2[j]) >> 1);
+    CB_WSYNC();
+  }
+  // up to two band calls, in the order the parse walk made them (the leaves are on the tape in that order);
+  // one call site for both
+  const int itheta = r.itheta, imid = r.imid, iside = r.iside;
+  int ncalls = 2;
+  int cX0 = xo, cX1 = yo;
+  int cfill0 = (int)x_cm, cfill1 = (int)y_cm;
+  bool side0 = false, side1 = false;                             // the call is the side of a mid / side pair: no folding
+  bool second0 = false, second1 = true;                          // the call works on the second channel's folding memory
+  if (mode == CB_TB_MONO) {
+    ncalls = 1;
+    cfill0 = (int)(x_cm | y_cm);
+  } else if (mode == CB_TB_JOINT2) {
+    ncalls = 1;
+    cX0 = itheta > 8192 ? yo : xo;
+    cfill0 = (int)(x_cm | y_cm);
+    second0 = false;
+  } else if (mode == CB_TB_N1) {
+    side1 = true;                                                // (only X leaves something in the folding memory)
+  } else if (mode == CB_TB_JOINT) {
     int fill = (int)(x_cm | y_cm);
-    const int orig_fill = fill;
-    if (!REBUILD) {
-      Split& sh = w.sp_store;
-      dec_theta(rd, sh, cx.i, cx.intensity, cx.remaining_bits, N, b, B, B, LM, 1);
-      const Split s = sh;
-      itheta = s.itheta; inv = s.inv; imid = s.imid; iside = s.iside;
-      b3_push(w, cur, itheta);
-      b3_push_bit(w, cur, inv);
-      if (N == 2) {
-        mbits = s.b;
-        sbits = 0;
-        if (itheta != 0 && itheta != 16384) sbits = 1 << CB_BITRES;
-        mbits -= sbits;
-        cx.remaining_bits -= s.qalloc + sbits;
-        int sign = 0;
-        if (sbits) sign = (int)rd_bits(rd, 1);
-        b3_push_bit(w, cur, sign);
-      } else {
-        mbits = cb_imax(0, cb_imin(s.b, (s.b - s.delta) / 2));
-        sbits = s.b - mbits;
-        cx.remaining_bits -= s.qalloc;
-        rebalance0 = cx.remaining_bits;
-        mid_first = mbits >= sbits;
-        b3_push_bit(w, cur, mid_first);
-      }
+    if (itheta == 0) fill &= (1 << B) - 1;
+    else if (itheta == 16384) fill &= ((1 << B) - 1) << B;
+    if (flags & CB_TBF_MID_FIRST) {
+      cfill0 = fill; cfill1 = fill >> B;
+      side1 = true;
     } else {
-      itheta = b3_pop(w, cur);
-      inv = b3_pop_bit(w, cur);
-      if (itheta == 0) {
-        imid = 32767; iside = 0;
-        fill &= (1 << B) - 1;
-      } else if (itheta == 16384) {
-        imid = 0; iside = 32767;
-        fill &= ((1 << B) - 1) << B;
-      } else {
-        imid = bitexact_cos((i16)itheta);
-        iside = bitexact_cos((i16)(16384 - itheta));
-      }
-      if (N == 2) n2_sign = 1 - 2 * b3_pop_bit(w, cur);
-      else mid_first = b3_pop_bit(w, cur);
-    }
-    if (N == 2) {
-      mode = 3;
-      njobs = 1;
-      jX0 = itheta > 8192 ? yo : xo;
-      jb0 = mbits;
-      jfill0 = orig_fill;
-    } else {
-      mode = 2;
-      njobs = 2;
-      j1_fold = false;
-      jgain1 = iside;
-      jX0 = xo; jb0 = mbits; jfill0 = fill;                      // the mid call, always described in slot 0 ...
-      jX1 = yo; jb1 = sbits; jfill1 = fill >> B;                 // ... the side call in slot 1; mid_first picks the order
+      cX0 = yo; cX1 = xo;
+      cfill0 = fill >> B; cfill1 = fill;
+      side0 = true;
+      second0 = false; second1 = false;
     }
   }
   u32 cm0 = 0, cm1 = 0;
-  CB_NOUNROLL for (int jn = 0; jn < njobs; jn++) {
-    const int slot = (mode == 2 && !mid_first) ? 1 - jn : jn;    // which description this call uses
-    i32 jb = slot ? jb1 : jb0;
-    if (!REBUILD && mode == 2 && jn == 1) {
-      const i32 first_bits = mid_first ? mbits : sbits;
-      const i32 rebalance = first_bits - (rebalance0 - cx.remaining_bits);
-      const int blocked = mid_first ? (itheta == 0) : (itheta == 16384);
-      if (rebalance > 3 << CB_BITRES && !blocked) jb += rebalance - (3 << CB_BITRES);
-    }
-    const bool fold = slot == 0 || j1_fold;
-    const u32 r = b3_band<REBUILD>(w, cx, rd, cur, slot ? jX1 : jX0, N, jb, B, fold ? (slot ? lb2 : lb) : nullptr, LM,
-                                   fold ? (slot ? lout2 : lout) : nullptr, slot ? jgain1 : (i32)CB_Q15ONE,
-                                   fold ? lowband_scratch : nullptr, slot ? jfill1 : jfill0);
-    if (slot == 0) cm0 = r; else cm1 = r;
+  CB_NOUNROLL for (int jn = 0; jn < ncalls; jn++) {
+    const bool side = jn ? side1 : side0;
+    const bool second = jn ? second1 : second0;
+    i16* const lo = side ? nullptr : (second ? lb2 : lb);
+    i16* const lo_out = side ? nullptr : (second ? lout2 : lout);
+    const u32 cmr = b3_band_rebuild(w, cx, cur, i, jn ? cX1 : cX0, N, B, lo, lo_out, side ? nullptr : lowband_scratch,
+                                    jn ? cfill1 : cfill0, r.nl[jn], flags & (jn ? CB_TBF_SIGN1 : CB_TBF_SIGN0));
+    if (jn) cm1 = cmr; else cm0 = cmr;
   }
-  if (mode == 0) {
+  if (mode == CB_TB_MONO) {
     x_cm = y_cm = cm0;
-  } else if (mode == 1) {
+  } else if (mode == CB_TB_DUAL) {
     x_cm = cm0;
     y_cm = cm1;
-  } else if (mode == 4) {
-    x_cm = y_cm = cm;
+  } else if (mode == CB_TB_N1) {
+    x_cm = y_cm = 1;
   } else {
-    if (mode == 3) {
-      if (REBUILD) {
-        i16* x2 = itheta > 8192 ? Y : X;
-        i16* y2 = itheta > 8192 ? X : Y;
-        CB_WSYNC();
-        y2[0] = (i16)(-n2_sign * x2[1]);
-        y2[1] = (i16)(n2_sign * x2[0]);
-        const i16 X0 = (i16)mult16_16_q15(imid, X[0]);
-        const i16 X1 = (i16)mult16_16_q15(imid, X[1]);
-        const i16 Y0 = (i16)mult16_16_q15(iside, Y[0]);
-        const i16 Y1 = (i16)mult16_16_q15(iside, Y[1]);
-        CB_WSYNC();
-        X[0] = (i16)sub16(X0, Y0);
-        Y[0] = add16(X0, Y0);
-        X[1] = (i16)sub16(X1, Y1);
-        Y[1] = add16(X1, Y1);
-        CB_WSYNC();
-      }
-      cm = cm0;
+    if (mode == CB_TB_JOINT2) {                                  // bands.c:1248-1261
+      const int n2_sign = (flags & CB_TBF_N2_NEG) ? -1 : 1;
+      i16* x2 = itheta > 8192 ? Y : X;
+      i16* y2 = itheta > 8192 ? X : Y;
+      CB_WSYNC();
+      y2[0] = (i16)(-n2_sign * x2[1]);
+      y2[1] = (i16)(n2_sign * x2[0]);
+      const i16 X0 = (i16)mult16_16_q15(imid, X[0]);
+      const i16 X1 = (i16)mult16_16_q15(imid, X[1]);
+      const i16 Y0 = (i16)mult16_16_q15(iside, Y[0]);
+      const i16 Y1 = (i16)mult16_16_q15(iside, Y[1]);
+      CB_WSYNC();
+      X[0] = (i16)sub16(X0, Y0);
+      Y[0] = add16(X0, Y0);
+      X[1] = (i16)sub16(X1, Y1);
+      Y[1] = add16(X1, Y1);
+      CB_WSYNC();
+      x_cm = y_cm = cm0;
     } else {
-      cm = cm0 | cm1;
-      if (REBUILD) v_stereo_merge(X, Y, imid, N);
+      x_cm = y_cm = cm0 | cm1;
+      v_stereo_merge(X, Y, imid, N);
     }
-    if (REBUILD && inv) {
+    if (flags & CB_TBF_INV) {
       CB_WSYNC();
       CB_LANE_LOOP(j, N) Y[j] = (i16)(-Y[j]);
       CB_WSYNC();
     }
-    x_cm = y_cm = cm;
   }
-  if (!REBUILD) {
-    ps.balance += w.pulses[i] + tell;
-    b3_push_bit(w, cur, b > (N << CB_BITRES));
-  } else {
-    w.collapse[i * C + 0] = (u8)x_cm;
-    w.collapse[i * C + C - 1] = (u8)y_cm;
-    rs.update_lowband = b3_pop_bit(w, cur);
-  }
+  w.collapse[i * C + 0] = (u8)x_cm;
+  w.collapse[i * C + C - 1] = (u8)y_cm;
 }
 
 // quant_all_bands (bands.c:1337-1502), decoder side, PARSE half: every band of the frame onto the tape.
-// A segment is closed when the next band might not fit the rebuild warp's buffers, and before the band whose
-// spectrum slot doubles as scratch for the others (the last band of the mode).
+// A segment is closed when the next band's leaves might not fit the rebuild warp's mask buffer, and before the band
+// whose spectrum slot doubles as scratch for the others (the last band of the mode).
 CB_FN void dec_bands_parse(EntWork& w, RangeDec& rd, TapeW& tw, int start, int end, int C, int Nfrm, int shortBlocks,
                            int spread, int dual_stereo, int intensity, i32 total_bits, i32 balance, int LM,
                            int codedBands) {
@@ -705,63 +688,52 @@ CB_FN void dec_bands_parse(EntWork& w, RangeDec& rd, TapeW& tw, int start, int e
   B3Parse ps;
   ps.balance = balance;
   ps.dual_stereo = dual_stereo;
-  B3Rebuild rs;
-  rs.dual_stereo = dual_stereo;
-  rs.lowband_offset = 0;
-  rs.update_lowband = 1;
+  ps.lowband_offset = 0;
+  ps.update_lowband = 1;
   B3Cur wr;
-  wr.jobs = wr.tape = wr.bits = 0;
+  wr.jobs = wr.seg_job0 = 0;
   wr.tw = &tw;
   wr.seg_jobs = nullptr;
   tw.seg_band0 = start;
   tw.call_empty = 0;
   CB_NOUNROLL for (int i = start; i < end; i++) {
     const int L = b3_band_leaves(M * (ebands(i + 1) - ebands(i)), LM);
-    const bool full = tw.seg_jobs + tw.seg_notes + 2 * L + 3 > CB_B3_BUF || tw.seg_bits + 8 > CB_B3_SEG_BITS;
+    const bool full = tw.seg_jobs + 2 * L > CB_B3_BUF;
     if (i > tw.seg_band0 && (full || i == CB_NBANDS - 1)) b3_close_segment(tw, i);
-    b3_one_band<false>(w, rd, wr, cxp, ps, rs, i, start, end, C, Nfrm, B, spread, intensity, total_bits, LM, codedBands);
+    b3_one_band_parse(w, rd, wr, cxp, ps, i, start, end, C, Nfrm, B, spread, intensity, total_bits, LM, codedBands);
   }
   if (end > tw.seg_band0) b3_close_segment(tw, end);
 }
 
 // PULSES + REBUILD halves, segment by segment.  `seed` = celt_lcg_rand state, carried on to anti_collapse.
-CB_FN void dec_bands_rebuild(EntWork& w, const FrameTape* t, int start, int end, int C, int Nfrm, int B, int spread,
-                             int dual_stereo, int intensity, int LM, u32& seed) {
+CB_FN void dec_bands_rebuild(EntWork& w, const FrameTape* t, int start, int end, int C, int Nfrm, int B, int LM,
+                             u32& seed) {
   BandCtx cxr;
-  cxr.intensity = intensity;
-  cxr.spread = spread;
+  cxr.intensity = 0;
+  cxr.spread = 0;
   cxr.seed = seed;
   cxr.remaining_bits = 0;
-  B3Parse ps;
-  ps.balance = 0;
-  ps.dual_stereo = dual_stereo;
-  B3Rebuild rs;
-  rs.dual_stereo = dual_stereo;
-  rs.lowband_offset = 0;
-  rs.update_lowband = 1;
+  const int M = 1 << LM;
+  CB_WSYNC();
+  {                                                              // the band records, and sqrt(N) of every band
+    const u32* src = (const u32*)t->band;
+    u32* dst = (u32*)w.bands;
+    CB_LANE_LOOP(k, (int)(sizeof(TapeBand) / 4) * CB_NBANDS) dst[k] = src[k];
+    CB_LANE_LOOP(k, CB_NBANDS) w.sqrtN[k] = (i16)cb_sqrt(shl32(M * (ebands(k + 1) - ebands(k)), 22));
+  }
+  CB_WSYNC();
   const int nseg = t->nseg;
-  int job0 = 0, note0 = 0, word0 = 0;
+  int job0 = 0;
   CB_NOUNROLL for (int sgi = 0; sgi < nseg; sgi++) {
     const TapeSeg sg = t->seg[sgi];
-    CB_WSYNC();
-    {
-      const u16* notes = t->notes + note0;
-      const int nn = sg.notes;
-      CB_LANE_LOOP(k, nn) w.b3_buf[CB_B3_BUF - 1 - k] = notes[k];
-      const u32* words = t->bits + word0;
-      const int nw = sg.bitwords;
-      CB_LANE_LOOP(k, nw) w.b3_bits[k] = words[k];
-    }
     b3_run_jobs(w, t->jobs + job0, sg.jobs);
     B3Cur rdc;
-    rdc.jobs = rdc.tape = rdc.bits = 0;
+    rdc.jobs = 0;
+    rdc.seg_job0 = job0;
     rdc.tw = nullptr;
     rdc.seg_jobs = t->jobs + job0;
-    CB_NOUNROLL for (int r = sg.band0; r < sg.band1; r++)
-      b3_one_band<true>(w, w.rd, rdc, cxr, ps, rs, r, start, end, C, Nfrm, B, spread, intensity, 0, LM, 0);
+    CB_NOUNROLL for (int r = sg.band0; r < sg.band1; r++) b3_one_band_rebuild(w, rdc, cxr, r, start, end, C, Nfrm, B, LM);
     job0 += sg.jobs;
-    note0 += sg.notes;
-    word0 += sg.bitwords;
   }
   seed = cxr.seed;
 }

@@ -44,8 +44,7 @@ struct Split { int inv, imid, iside, delta, itheta, qalloc, b; };   // b: update
 // Three-phase band decoder (cb_celt_bands3.h): what one tape segment may hold (the rebuild warp's copy of it)
 #ifndef CB_B3_BUF
 // (sized so that a 20 ms stereo frame of up to ~128 kbit/s has bands 0..19 in one segment)
-#define CB_B3_BUF 224           // 16-bit entries: collapse masks of the segment's jobs from the front, notes from the back
-#define CB_B3_BITWORDS 20       // 640 node bits
+#define CB_B3_BUF 224           // 16-bit entries: the collapse masks of the segment's leaves
 #endif
 
 // One level of the split recursion (quant_partition), kept in shared memory.
@@ -86,12 +85,13 @@ struct alignas(CB_ENTWORK_ALIGN) EntWork {
   PartFrame stack[5];
   Split sp_store;                // result record of dec_theta
 #ifndef CB_THREAD_MODE
-  u16 b3_buf[CB_B3_BUF];         // cb_celt_bands3.h, current tape segment: collapse masks of its jobs from the front,
-                                 //   split angles and other 16-bit notes of the parse walk from the back
-  u32 b3_bits[CB_B3_BITWORDS];   //   a bit or two per node of the walk
+  TapeBand bands[CB_NBANDS];     // cb_celt_bands3.h, REBUILD: the frame's band records (copy of FrameTape::band)
+  u16 b3_buf[CB_B3_BUF];         //   current tape segment: the collapse masks of its leaves
+  i16 sqrtN[CB_NBANDS + 3];      //   sqrt(N) of every band, Q15-ish: the scale of the folding memory (bands.c:1160-1168)
 #else
+  TapeBand bands[1];
   u16 b3_buf[2];
-  u32 b3_bits[2];
+  i16 sqrtN[2];
 #endif
   RangeDec rd;                   // coder registers; in shared memory so the rd_* routines can be real calls
 };
@@ -871,9 +871,7 @@ CB_FN int celt_frame_parse(EntWork& w, CeltDecState* stg, FrameSide* side, Frame
   // ---- the band walk, onto the tape ----
   TapeW tw;
   tw.t = tape;
-  tw.jobs = tw.notes = tw.bitwords = 0;
-  tw.seg_jobs = tw.seg_notes = tw.seg_bits = 0;
-  tw.acc = 0;
+  tw.jobs = tw.seg_jobs = 0;
   tw.nseg = 0;
   tw.seg_band0 = start;
   dec_bands_parse(w, rd, tw, start, end, C, N, shortBlocks, spread_decision, dual_stereo, intensity,
@@ -964,7 +962,7 @@ CB_FN void celt_frame_rebuild(EntWork& w, FrameTape* tape, FrameSide* side) {
   CB_LANE_LOOP(j, CB_NBANDS) { w.pulses[j] = tape->pulses[j]; w.tf_res[j] = tape->tf_res[j]; }
   CB_WSYNC();
   u32 seed = tape->seed;
-  dec_bands_rebuild(w, tape, start, end, C, N, tape->B, tape->spread, tape->dual_stereo, tape->intensity, LM, seed);
+  dec_bands_rebuild(w, tape, start, end, C, N, tape->B, LM, seed);
   if (tape->anti_collapse_on) {
     i16* e = (i16*)w.tmp32;                    // [0,42) bandE, [42,84) oldLogE, [84,126) oldLogE2, before this frame
     CB_WSYNC();

@@ -66,8 +66,6 @@ struct alignas(16) FrameSide {
 // Sizes are the worst case of a 20 ms stereo frame: a band's channel splits into at most 16 leaves (bands of
 // 32+ bins at LM = 3), 8 for 16 bins, 4 for 8 bins: 208 leaves per channel.
 #define CB_TAPE_MAX_JOBS 416
-#define CB_TAPE_MAX_NOTES 448      // per band: the stereo angle and the leaf count of each channel call (far fewer than this)
-#define CB_TAPE_BITWORDS 160       // a few bits per band, plus one word of slack per segment
 #define CB_TAPE_MAX_SEG 24
 #define CB_TAPE_NONE 0             // nothing for the rebuild half
 #define CB_TAPE_FRAME 1            // a decoded frame
@@ -82,9 +80,31 @@ struct TapeJob {                   // a leaf of a band's split tree, in the orde
   u8 sh;                           // where the leaf's collapse bits sit in the band's mask (and in `fill`)
   u8 pad;
 };
-struct TapeSeg {                   // a run of bands whose notes fit the rebuild warp's shared memory
+// What the rebuild half needs to know of one band (quant_all_bands / quant_band_stereo, bands.c:1176-1502) beyond
+// its leaves: everything here is decided by the bitstream alone, so the parse half works it out once.
+#define CB_TB_MONO 0               // one call on X
+#define CB_TB_DUAL 1               // dual stereo: X and Y coded apart
+#define CB_TB_JOINT 2              // mid / side, N > 2
+#define CB_TB_JOINT2 3             // mid / side, N == 2 (bands.c:1222-1262)
+#define CB_TB_N1 4                 // stereo, N == 1: two signs
+#define CB_TBF_INV 1               // side channel inverted
+#define CB_TBF_MID_FIRST 2         // joint stereo: the mid call came first in the walk (else the side call)
+#define CB_TBF_N2_NEG 4            // N == 2: sign of the side
+#define CB_TBF_SWITCH 8            // the band where dual stereo ends: the two folding memories are averaged (bands.c:1430-1437)
+#define CB_TBF_SIGN0 16            // N == 1: sign of the first / second channel
+#define CB_TBF_SIGN1 32
+struct alignas(8) TapeBand {
+  u16 job0;                        // the band's first leaf record (index into FrameTape::jobs)
+  u8 nl[2];                        // leaves of the band's first and second call, in walk order; + 128: one of them
+                                   //   is without pulses
+  i16 eff_lowband;                 // folding source (offset into the folding memory), -1: none
+  u8 fold0, fold1;                 // the bands [fold0, fold1) whose collapse masks the folding source brings
+  u8 mode, flags;                  // CB_TB_*, CB_TBF_*
+  i16 itheta, imid, iside;         // joint stereo: the split angle and its cosines
+};
+struct TapeSeg {                   // a run of bands whose leaf masks fit the rebuild warp's shared memory
   u8 band0, band1;
-  u16 jobs, notes, bitwords;       // counts inside the segment (segments start on a word of bits)
+  u16 jobs;                        // leaf records of the segment (they follow the previous segment's)
 };
 struct alignas(16) FrameTape {
   i32 kind;                        // CB_TAPE_*
@@ -96,8 +116,7 @@ struct alignas(16) FrameTape {
   i16 bandE[2 * CB_NBANDS];        // final log energies of the frame
   i16 prevLogE[2][2 * CB_NBANDS];  // oldLogE / oldLogE2 as they were before this frame (anti_collapse)
   TapeSeg seg[CB_TAPE_MAX_SEG];
-  u32 bits[CB_TAPE_BITWORDS];
-  u16 notes[CB_TAPE_MAX_NOTES];
+  TapeBand band[CB_NBANDS];
   TapeJob jobs[CB_TAPE_MAX_JOBS];
   i16 norm[2 * CB_NORM_STRIDE];    // REBUILD's own scratch: the normalised lower bands kept for folding (bands.c:1380)
 };
