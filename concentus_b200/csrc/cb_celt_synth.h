@@ -317,28 +317,31 @@ CB_FN void v_comb_filter(i32* buf, int off, int n, const i32* hist, int pos, int
 }
 
 // De-emphasis + PCM store + ring update for a finished frame held in buf[0..N) (shared by the
-// synthesis kernel and the concealment kernel).  celt_decoder.c:185-275.
-//  * history ring: the frame overwrites the N oldest samples;
-//  * de-emphasis is a serial one-pole IIR (m = 0.85*(x+m), truncating multiply): one lane;
-//  * SIG2WORD16 + interleaved int16 store (optionally accumulated, hybrid mode) in a lane loop.
-CB_FN void emit_frame(i32* buf, int N, CeltDecState* st, int c, i16* pcm, int accum, int decode_gain) {
-  const int CC = st->channels, downsample = st->downsample;
+// synthesis kernel and the concealment kernel).  celt_decoder.c:185-275.  Three steps:
+//  * emit_ring: the frame overwrites the N oldest samples of the history ring (lane loop);
+//  * emit_deemph: de-emphasis is a serial one-pole IIR (m = 0.85*(x+m), truncating multiply), ONE LANE per
+//    channel.  A warp on its own gives it lane 0; the synthesis kernel hands the channels of a whole CTA to the
+//    lanes of one warp (EmitReq below), so that the 960 serial steps are issued once per CTA, not once per warp;
+//  * emit_pcm: SIG2WORD16 + interleaved int16 store (optionally accumulated, hybrid mode) in a lane loop.
+CB_FN void emit_ring(const i32* buf, int N, CeltDecState* st, int c) {
   i32* hist = st->hist[c];
   const int pos = st->hist_pos[c];
   CB_WSYNC();
   CB_LANE_LOOPU(j, N) hist[(pos + j) & (CB_HIST - 1)] = buf[j];
   CB_WSYNC();
-  CB_IF_LANE0 {
-    i32 m = st->preemph_mem[c];
-    for (int j = 0; j < N; j++) {
-      i32 tmp = add32(buf[j], m);
-      m = mult16_32_q15(27853, tmp);
-      buf[j] = tmp;
-    }
-    st->preemph_mem[c] = m;
-    st->hist_pos[c] = (pos + N) & (CB_HIST - 1);
+  CB_IF_LANE0 st->hist_pos[c] = (pos + N) & (CB_HIST - 1);
+}
+CB_FN void emit_deemph(i32* buf, int N, CeltDecState* st, int c) {     // one lane
+  i32 m = st->preemph_mem[c];
+  for (int j = 0; j < N; j++) {
+    i32 tmp = add32(buf[j], m);
+    m = mult16_32_q15(27853, tmp);
+    buf[j] = tmp;
   }
-  CB_WSYNC();
+  st->preemph_mem[c] = m;
+}
+CB_FN void emit_pcm(const i32* buf, int N, const CeltDecState* st, int c, i16* pcm, int accum, int decode_gain) {
+  const int CC = st->channels, downsample = st->downsample;
   const int Nd = N / downsample;
   if (decode_gain == 0) {
     if (accum) {
@@ -358,11 +361,25 @@ CB_FN void emit_frame(i32* buf, int N, CeltDecState* st, int c, i16* pcm, int ac
   }
   CB_WSYNC();
 }
+CB_FN void emit_frame(i32* buf, int N, CeltDecState* st, int c, i16* pcm, int accum, int decode_gain) {
+  emit_ring(buf, N, st, c);
+  CB_IF_LANE0 emit_deemph(buf, N, st, c);
+  CB_WSYNC();
+  emit_pcm(buf, N, st, c, pcm, accum, decode_gain);
+}
+// A frame whose ring is written and whose de-emphasis + PCM store are still to do (synthesis kernel: the CTA's
+// warps park theirs in shared memory, one warp runs the de-emphasis of all of them, a lane each).
+struct EmitReq {
+  i32* buf;
+  CeltDecState* st;
+  i16* pcm;
+  i32 N, c, accum, decode_gain, valid;
+};
 
 // Synthesis of output channel `c` of one stream for one frame.
 // pcm -> first sample of this frame for this stream (interleaved, CC channels).
 CB_FN void celt_synth_channel(SynWork& w, CeltDecState* st, const FrameSide* side, int c, i16* pcm,
-                               int decode_gain = 0) {
+                               int decode_gain = 0, EmitReq* defer = nullptr) {
   const int LM = side->LM, C = side->C, CC = st->channels;
   const int M = 1 << LM, N = M * 120;
   const int downsample = st->downsample;
@@ -395,5 +412,13 @@ CB_FN void celt_synth_channel(SynWork& w, CeltDecState* st, const FrameSide* sid
   v_comb_filter(w.buf, 0, 120, hist, pos, side->T0, side->T1, side->g0, side->g1, side->tap0, side->tap1, CB_OVERLAP);
   if (LM != 0)
     v_comb_filter(w.buf, 120, N - 120, hist, pos, side->T1, side->T2, side->g1, side->g2, side->tap1, side->tap2, CB_OVERLAP);
-  emit_frame(w.buf, N, st, c, pcm, side->accum, decode_gain);
+  if (defer == nullptr) {
+    emit_frame(w.buf, N, st, c, pcm, side->accum, decode_gain);
+    return;
+  }
+  emit_ring(w.buf, N, st, c);
+  CB_IF_LANE0 {
+    defer->buf = w.buf; defer->st = st; defer->pcm = pcm;
+    defer->N = N; defer->c = c; defer->accum = side->accum; defer->decode_gain = decode_gain; defer->valid = 1;
+  }
 }

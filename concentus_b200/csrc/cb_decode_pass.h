@@ -8,12 +8,12 @@
 
 // Kernel B, one (stream, channel), one pass.  `row` = this stream's PCM row.
 CB_FN void decode_synth_pass(SynWork& w, OpusDecState* st, const StreamPlan* pl, const FrameSide* side,
-                             i16* row, int c, int pass) {
+                             i16* row, int c, int pass, EmitReq* defer = nullptr) {
   const int CC = st->channels;
   const int route = side->route;
   if (route == CB_ROUTE_SILK || route == CB_ROUTE_GENERAL || route == CB_ROUTE_FINISH || route == CB_ROUTE_PLC) return;
   if (side->kind == 1) {
-    celt_synth_channel(w, &st->celt, side, c, row + (size_t)pl->pcm_off[pass] * CC, st->decode_gain);
+    celt_synth_channel(w, &st->celt, side, c, row + (size_t)pl->pcm_off[pass] * CC, st->decode_gain, defer);
   } else if (side->kind == 3 && pass == 0) {
     const int total = pl->total_samples;
     CB_LANE_LOOP(j, total) row[j * CC + c] = 0;

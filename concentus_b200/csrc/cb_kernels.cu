@@ -18,7 +18,8 @@ extern "C" int cbk_sm_count(void);   // SMs of the current device (opus_api.cu)
 
 #define A_WARPS 4           // kernel A, small batches: 4 warps per CTA, 7 CTAs per SM
 #define A_WARPS_SM 28       // rebuild kernel: warps an SM holds
-#define B_WARPS 4
+#define B_WARPS 7           // synthesis kernel: 7 warps per CTA, 4 CTAs per SM (shared memory: 7.9 KB per warp)
+#define B_CTAS_SM 4
 
 // Kernel A2: the REBUILD half of the entropy stage (cb_entropy_pass.h), one warp per stream: tape -> pulse vectors
 // (a lane per leaf) -> folding / recombination / stereo merge -> normalised spectrum for the synthesis kernel.
@@ -38,22 +39,34 @@ celt_rebuild_kernel(FrameSide* sides, FrameTape* tapes, int n) {
   decode_entropy_rebuild(w, &tapes[s], &sides[s]);
 }
 
-__global__ void __launch_bounds__(B_WARPS * 32, 7)
+// Kernel B.  The de-emphasis of a frame is a serial recurrence over its samples (one lane busy for 960 steps), so
+// the warps of a CTA do not each run their own: they park the finished frame (EmitReq), and the lanes of warp 0 run
+// the de-emphasis of all of them side by side; each warp then converts and stores its own PCM.
+__global__ void __launch_bounds__(B_WARPS * 32, B_CTAS_SM)
 celt_synth_kernel(OpusDecState* const* states, const StreamPlan* plans, const FrameSide* sides, i16* pcm,
                   i32 pcm_stride, int n, int pass, int max_ch) {
   extern __shared__ __align__(16) unsigned char smem[];
-  const int warp = threadIdx.x >> 5;
+  EmitReq* reqs = reinterpret_cast<EmitReq*>(smem + (size_t)B_WARPS * sizeof(SynWork));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int gw = blockIdx.x * B_WARPS + warp;
   const int s = max_ch == 2 ? gw >> 1 : gw, c = max_ch == 2 ? gw & 1 : 0;   // a warp per channel the group can have
-  if (s >= n) return;
-  OpusDecState* st = states[s];
-  const int CC = st->channels;
-  if (c >= CC) return;
-  const FrameSide* side = &sides[s];
-  const StreamPlan* pl = &plans[s];
-  SynWork& w = *reinterpret_cast<SynWork*>(smem + (size_t)warp * sizeof(SynWork));
-  i16* row = pcm + (size_t)s * pcm_stride;
-  decode_synth_pass(w, st, pl, side, row, c, pass);
+  if (lane == 0) reqs[warp].valid = 0;
+  __syncwarp();
+  if (s < n) {
+    OpusDecState* st = states[s];
+    if (c < st->channels) {
+      SynWork& w = *reinterpret_cast<SynWork*>(smem + (size_t)warp * sizeof(SynWork));
+      decode_synth_pass(w, st, &plans[s], &sides[s], pcm + (size_t)s * pcm_stride, c, pass, &reqs[warp]);
+    }
+  }
+  __syncthreads();
+  if (warp == 0 && lane < B_WARPS && reqs[lane].valid) {
+    const EmitReq r = reqs[lane];
+    emit_deemph(r.buf, r.N, r.st, r.c);
+  }
+  __syncthreads();
+  const EmitReq r = reqs[warp];
+  if (r.valid) emit_pcm(r.buf, r.N, r.st, r.c, r.pcm, r.accum, r.decode_gain);
 }
 
 // Multistream: one thread per multistream decoder plans its elementary streams.
@@ -156,7 +169,7 @@ extern "C" int cbk_launch_synth(OpusDecState* const* d_states, const StreamPlan*
   if (n <= 0) return 0;
   int rc = ensure_attrs();
   if (rc) return rc;
-  const size_t smemB = sizeof(SynWork) * B_WARPS;
+  const size_t smemB = (sizeof(SynWork) + sizeof(EmitReq)) * B_WARPS;
   if (max_ch != 1) max_ch = 2;
   const int warpsB = n * max_ch;
   celt_synth_kernel<<<(warpsB + B_WARPS - 1) / B_WARPS, B_WARPS * 32, smemB, stream>>>(
