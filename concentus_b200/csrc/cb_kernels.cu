@@ -159,7 +159,7 @@ extern "C" int cbk_launch_entropy(OpusDecState* const* d_states, const u8* d_dat
   if (n <= 0) return 0;
   int rc = ensure_attrs();
   if (rc) return rc;
-  rc = cbk_launch_parse(d_states, d_data, d_plans, d_sides, d_tapes, d_ret, n, pass, max_payload, stream);
+  rc = cbk_launch_parse(d_states, d_data, d_plans, d_sides, d_tapes, d_ret, n, pass, max_payload, 0, stream);
   if (rc) return rc;
   return cbk_launch_rebuild(d_sides, d_tapes, n, stream);
 }

@@ -8,8 +8,10 @@ extern "C" {
 int cbk_launch_entropy(OpusDecState* const* d_states, const u8* d_data, StreamPlan* d_plans, FrameSide* d_sides,
                        FrameTape* d_tapes, i32* d_ret, int n, int pass, int max_payload, cudaStream_t stream);
 int cbk_launch_rebuild(FrameSide* d_sides, FrameTape* d_tapes, int n, cudaStream_t stream);
+// shared_sms: the kernel will run beside the rebuild / synthesis kernels of the call before (run-ahead scheduling)
 int cbk_launch_parse(OpusDecState* const* d_states, const u8* d_data, StreamPlan* d_plans, FrameSide* d_sides,
-                     FrameTape* d_tapes, i32* d_ret, int n, int pass, int max_payload, cudaStream_t stream);
+                     FrameTape* d_tapes, i32* d_ret, int n, int pass, int max_payload, int shared_sms,
+                     cudaStream_t stream);
 int cbk_launch_synth(OpusDecState* const* d_states, const StreamPlan* d_plans, const FrameSide* d_sides,
                      i16* d_pcm, i32 pcm_stride, int n, int pass, int max_ch, cudaStream_t stream);
 // SILK frames of pass `pass` (one thread per stream); streams whose frame is CELT return at once

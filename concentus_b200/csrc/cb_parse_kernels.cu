@@ -62,7 +62,8 @@ static int parse_bytes_per_thread(int max_payload, int spw) {
 }
 
 extern "C" int cbk_launch_parse(OpusDecState* const* d_states, const u8* d_data, StreamPlan* d_plans, FrameSide* d_sides,
-                                FrameTape* d_tapes, i32* d_ret, int n, int pass, int max_payload, cudaStream_t stream) {
+                                FrameTape* d_tapes, i32* d_ret, int n, int pass, int max_payload, int shared_sms,
+                                cudaStream_t stream) {
   if (n <= 0) return 0;
   static int attr_done[64];
   int dev = 0;
@@ -79,8 +80,10 @@ extern "C" int cbk_launch_parse(OpusDecState* const* d_states, const u8* d_data,
   static int spw_env = -1;
   if (spw_env < 0) { const char* e2 = getenv("OPUSB_PARSE_SPW"); spw_env = e2 ? atoi(e2) : 0; }
   // few streams to a warp while that still fits the GPU in one wave (about 16 of these warps per SM: registers),
-  // more for larger batches
-  int spw = P_SPW;
+  // more for larger batches.  A lone parse kernel is a latency chain and is fastest with 2 streams to a warp; when
+  // it shares the SMs with the rebuild / synthesis kernels of the call before (`shared_sms`), issue slots are what
+  // runs out, and 4 streams to a warp -- two thirds of the warp instructions -- measured faster (124 k -> 127 k).
+  int spw = shared_sms ? 2 * P_SPW : P_SPW;
   while (spw < 32 && (n + spw - 1) / spw > cbk_sm_count() * 16) spw <<= 1;
   if (spw_env >= 1 && spw_env <= 32) spw = spw_env;
   const int per_thread = parse_bytes_per_thread(max_payload, spw);

@@ -495,7 +495,14 @@ static int group_enqueue_passes(OpusDecoderGroup* g, DevCtx* c, const CallCtx& c
     }
     if (!rc) {
       ProfScope ps(cc.s_ctl, 1);
-      rc = cbk_launch_parse(g->d_states, d_data, g->d_plans, sides, tapes, d_ret, g->n, p, max_packet_bytes, cc.s_ctl);
+      // does the signal side of the call (or pass) before still have work queued?  Then this parse shares the SMs.
+      int shared_sms = 0;
+      if (cc.ahead && cudaEventQuery(c->ev_synth) == cudaErrorNotReady) {
+        shared_sms = 1;
+        (void)cudaGetLastError();          // "not ready" is an answer, not a fault to report with the launch
+      }
+      rc = cbk_launch_parse(g->d_states, d_data, g->d_plans, sides, tapes, d_ret, g->n, p, max_packet_bytes, shared_sms,
+                            cc.s_ctl);
     }
     if (!rc && cc.ahead) {
       EV_OK(cudaEventRecord(c->ev_parse, cc.s_ctl));
