@@ -117,12 +117,32 @@ CB_FN int celt_encode_frame(EncWork& w, EncScratch& sc, CeltEncState* st, const 
     }
   }
 
-  CB_ENC_PHASE(w);                                            // 3: pre-filter done
   // ---- transient decision, MDCT, band energies ----
   int isTransient = 0, shortBlocks = 0, tf_chan = 0, transient_got_disabled = 0;
-  if (s.complexity >= 1 && !lfe)
+  const bool want_ta = s.complexity >= 1 && !lfe;
+#if CB_DEVICE_BUILD
+  // the detector's recurrences run in the CTA's serial section (cb_enc_state.h: EncSerialReq), its metric here
+  CB_WSYNC();
+  if (want_ta && CB_LANE() == 0) {
+    EncSerialReq& r = *w.sreq;
+    r.in = sc.in[0]; r.out = w.ta_tmp[0]; r.len = N + overlap; r.channels = CC;
+    r.stride_in = CB_MAXN + CB_OVERLAP; r.stride_out = CB_MAXN + CB_OVERLAP;
+    r.kind = CB_ES_TRANSIENT;
+  }
+  CB_ENC_PHASE(w);                                            // 3: pre-filter done, requests posted
+  enc_serial_run(w.sreq - (threadIdx.x >> 5));
+  CB_ENC_PHASE(w);                                            // 3b: transient recurrences done
+  if (want_ta) {
+    i32 mean_c[2], maxE_c[2];
+    for (int c = 0; c < 2; c++) { mean_c[c] = w.sreq->m[c]; maxE_c[c] = w.sreq->m[2 + c]; }
+    isTransient = enc_transient_finish(N + overlap, CC, mean_c, maxE_c, &tf_estimate, &tf_chan, w.ta_tmp[0], CB_MAXN + CB_OVERLAP);
+  }
+#else
+  CB_ENC_PHASE(w);                                            // 3: pre-filter done
+  if (want_ta)
     isTransient = enc_transient_analysis(sc.in[0], CB_MAXN + CB_OVERLAP, N + overlap, CC, &tf_estimate, &tf_chan, w.ta_tmp[0],
                                          CB_MAXN + CB_OVERLAP);
+#endif
   if (LM > 0 && re_tell(enc) + 3 <= total_bits) {
     if (isTransient) shortBlocks = M;
   } else {

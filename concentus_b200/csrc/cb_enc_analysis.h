@@ -251,64 +251,66 @@ CB_GTABLE u8 ct_inv_table[128] = {
     6, 6, 6, 6, 6, 6, 6, 6, 6, 6, 5, 5, 5, 5, 5, 5, 5, 5, 5, 5, 5, 5, 4, 4, 4, 4, 4, 4, 4, 4, 4, 4, 4, 4, 4, 4, 4, 4, 4,
     4, 4, 4, 4, 4, 4, 4, 4, 3, 3, 3, 3, 3, 3, 3, 3, 3, 3, 3, 3, 3, 3, 3, 3, 3, 2};
 
-CB_FN_NOINLINE int enc_transient_analysis(const i32* in, int cstride, int len, int C, i32* tf_estimate, int* tf_chan,
-                                          i16* tmp0, int tstride) {
+// transient_analysis (celt_encoder.c:227-330) in two parts.
+// Part 1, one channel, one thread -- the recurrences: the high-pass filter, the scaling to full range (a maximum
+// over the filtered vector, applied on the fly in the next pass), the forward and the backward smoothing.
+// Leaves the smoothed energy envelope in tmp[0 .. len/2) and returns its mean / maximum terms.
+CB_FN void enc_ta_chain(const i32* x_in, i16* tmp, int len, i32* mean_out, i32* maxE_out) {
+  const int len2 = len / 2;
+  i32 mem0 = 0, mem1 = 0;
+  i32 mx = 0, mn = 0;
+  // len is a multiple of 4 (N + overlap).  Sixteen samples per trip while they last: the loads (global memory) go
+  // out together, then the chain runs -- in the CTA's serial section only two warps are there to hide their latency.
+  int i = 0;
+#define CB_TA_STEP(W)                                                                                      \
+  {                                                                                                        \
+    i32 xs[W];                                                                                             \
+    for (int k = 0; k < W; k++) xs[k] = x_in[i + k];                                                       \
+    for (int k = 0; k < W; k++) {                                                                          \
+      i32 x = xs[k] >> CB_SIG_SHIFT;                                                                       \
+      i32 y = add32(mem0, x);                                                                              \
+      mem0 = sub32(add32(mem1, y), shl32(x, 1));                                                           \
+      mem1 = sub32(x, y >> 1);                                                                             \
+      const i16 v = (i16)(y >> 2);                                                                         \
+      tmp[i + k] = v;                                                                                      \
+      if (i + k >= 12) { mx = max32(mx, v); mn = min32(mn, v); } /* (the first 12 are cleared below) */    \
+    }                                                                                                      \
+  }
+  CB_NOUNROLL for (; i + 16 <= len; i += 16) CB_TA_STEP(16)
+  CB_NOUNROLL for (; i < len; i += 4) CB_TA_STEP(4)
+#undef CB_TA_STEP
+  for (int i = 0; i < 12; i++) tmp[i] = 0;
+  const i32 maxabs = max32(mx, neg32(mn));
+  const int shift = 14 - cb_ilog2(add32(1, maxabs));         // normalise to full range, applied as the values are read
+  i32 mean = 0, maxE = 0;
+  mem0 = 0;
+  CB_NOUNROLL for (int i = 0; i < len2; i++) {
+    i16 a = tmp[2 * i], b = tmp[2 * i + 1];
+    if (shift != 0) { a = shl16(a, shift); b = shl16(b, shift); }
+    i16 x2 = (i16)pshr32(add32(mult16_16(a, a), mult16_16(b, b)), 16);
+    mean = add32(mean, x2);
+    tmp[i] = (i16)add32(mem0, pshr32(sub32(x2, mem0), 4));
+    mem0 = tmp[i];
+  }
+  mem0 = 0;
+  CB_NOUNROLL for (int i = len2 - 1; i >= 0; i--) {
+    tmp[i] = (i16)add32(mem0, pshr32(sub32(tmp[i], mem0), 3));
+    mem0 = tmp[i];
+    maxE = max32(maxE, (i16)mem0);
+  }
+  *mean_out = mean;
+  *maxE_out = maxE;
+}
+// Part 2, lane-parallel: the masking metric of every channel from its envelope.
+CB_FN_NOINLINE int enc_transient_finish(int len, int C, const i32* mean_c, const i32* maxE_c, i32* tf_estimate, int* tf_chan,
+                                        const i16* tmp0, int tstride) {
   i32 mask_metric = 0;
   const int len2 = len / 2;
   CB_WSYNC();
-  CB_CHANNEL_LANES(c, C) {                                   // high-pass IIR: a serial recurrence per channel
-    const i32* x_in = in + c * cstride;
-    i16* tmp = tmp0 + c * tstride;
-    i32 mem0 = 0, mem1 = 0;
-    CB_NOUNROLL for (int i = 0; i < len; i += 4) {         // len is a multiple of 4 (N + overlap)
-      i32 xs[4];
-      for (int k = 0; k < 4; k++) xs[k] = x_in[i + k];
-      for (int k = 0; k < 4; k++) {
-        i32 x = xs[k] >> CB_SIG_SHIFT;
-        i32 y = add32(mem0, x);
-        mem0 = sub32(add32(mem1, y), shl32(x, 1));
-        mem1 = sub32(x, y >> 1);
-        tmp[i + k] = (i16)(y >> 2);
-      }
-    }
-    for (int i = 0; i < 12; i++) tmp[i] = 0;
-  }
-  CB_WSYNC();
-  CB_NOUNROLL for (int c = 0; c < C; c++) {                  // normalise to full range (lane-parallel)
-    i16* tmp = tmp0 + c * tstride;
-    i32 mx = 0, mn = 0;
-    CB_LANE_LOOP(i, len) { i32 v = tmp[i]; mx = max32(mx, v); mn = min32(mn, v); }
-    i32 maxabs = max32(cb_wmax(mx), neg32(cb_wmin(mn)));
-    int shift = 14 - cb_ilog2(add32(1, maxabs));
-    if (shift != 0) {
-      CB_LANE_LOOP(i, len) tmp[i] = shl16(tmp[i], shift);
-    }
-  }
-  CB_WSYNC();
-  i32 mean_c[2] = {0, 0}, maxE_c[2] = {0, 0};
-  CB_CHANNEL_LANES(c, C) {                                   // forward / backward smoothing: serial per channel
-    i16* tmp = tmp0 + c * tstride;
-    i32 mean = 0, maxE = 0, mem0 = 0;
-    CB_NOUNROLL for (int i = 0; i < len2; i++) {
-      i16 x2 = (i16)pshr32(add32(mult16_16(tmp[2 * i], tmp[2 * i]), mult16_16(tmp[2 * i + 1], tmp[2 * i + 1])), 16);
-      mean = add32(mean, x2);
-      tmp[i] = (i16)add32(mem0, pshr32(sub32(x2, mem0), 4));
-      mem0 = tmp[i];
-    }
-    mem0 = 0;
-    CB_NOUNROLL for (int i = len2 - 1; i >= 0; i--) {
-      tmp[i] = (i16)add32(mem0, pshr32(sub32(tmp[i], mem0), 3));
-      mem0 = tmp[i];
-      maxE = max32(maxE, (i16)mem0);
-    }
-    mean_c[c] = mean;
-    maxE_c[c] = maxE;
-  }
-  CB_WSYNC();
   CB_NOUNROLL for (int c = 0; c < C; c++) {
     const i16* tmp = tmp0 + c * tstride;
-    i32 mean = cb_bcast(mean_c[c], c);
-    const i32 maxE = cb_bcast(maxE_c[c], c);
+    i32 mean = mean_c[c];
+    const i32 maxE = maxE_c[c];
     mean = mult16_16(cb_sqrt(mean), cb_sqrt(mult16_16(maxE, len2 >> 1)));
     i32 norm = shl32(len2, 6 + 14) / add32(1, mean >> 1);
     i32 un = 0;
@@ -326,6 +328,72 @@ CB_FN_NOINLINE int enc_transient_analysis(const i32* in, int cstride, int len, i
   *tf_estimate = (i16)cb_sqrt(max32(0, sub32(shl32(mult16_16(113, min32(163, tf_max)), 14), 37312528)));
   return is_transient;
 }
+// Host build: both parts in turn.  (The device posts part 1 as a serial-section request: cb_celt_enc.h.)
+CB_FN int enc_transient_analysis(const i32* in, int cstride, int len, int C, i32* tf_estimate, int* tf_chan,
+                                 i16* tmp0, int tstride) {
+  i32 mean_c[2] = {0, 0}, maxE_c[2] = {0, 0};
+  for (int c = 0; c < C; c++) enc_ta_chain(in + c * cstride, tmp0 + c * tstride, len, &mean_c[c], &maxE_c[c]);
+  return enc_transient_finish(len, C, mean_c, maxE_c, tf_estimate, tf_chan, tmp0, tstride);
+}
+
+// dc_reject (opus_encoder.c:362-384): two cascaded one-pole sections.  One channel, one thread: the recurrence.
+CB_FN void enc_dc_chain(const i16* in, i16* out, i32* mem, int c, int len, int channels, int shift) {
+  i32 m0 = mem[2 * c], m1 = mem[2 * c + 1];
+  const i16* ip = in + c;
+  i16* op = out + c;
+  int i = 0;
+  CB_NOUNROLL for (; i + 16 <= len; i += 16) {            // sixteen samples per trip: loads first, then the chain
+    i32 xs[16];
+    for (int k = 0; k < 16; k++) xs[k] = ip[channels * (i + k)];
+    for (int k = 0; k < 16; k++) {
+      const i32 x = shl32(xs[k], 15);
+      const i32 tmp = sub32(x, m0);
+      m0 = add32(m0, pshr32(tmp, shift));
+      const i32 y = sub32(tmp, m1);
+      m1 = add32(m1, pshr32(y, shift));
+      i32 v = pshr32(y, 15);
+      v = v > 32767 ? 32767 : (v < -32767 ? -32767 : v);
+      op[channels * (i + k)] = (i16)v;
+    }
+  }
+  for (; i < len; i++) {
+    const i32 x = shl32(ip[channels * i], 15);
+    const i32 tmp = sub32(x, m0);
+    m0 = add32(m0, pshr32(tmp, shift));
+    const i32 y = sub32(tmp, m1);
+    m1 = add32(m1, pshr32(y, shift));
+    i32 v = pshr32(y, 15);
+    v = v > 32767 ? 32767 : (v < -32767 ? -32767 : v);
+    op[channels * i] = (i16)v;
+  }
+  mem[2 * c] = m0;
+  mem[2 * c + 1] = m1;
+}
+
+#if CB_DEVICE_BUILD
+// ---- serial sections of the CTA's streams on the lanes of warps 0 and 1 (cb_enc_state.h: EncSerialReq) ----------
+// Called by every warp after a rendezvous (whether it encodes or only makes up rendezvous).
+CB_FN void enc_serial_run(EncSerialReq* table) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp >= 2) return;
+  const int nw = blockDim.x >> 5;
+  const int slot = warp * 16 + (lane >> 1), c = lane & 1;
+  if (slot < nw) {
+    EncSerialReq& r = table[slot];
+    const int kind = r.kind;
+    if (c < r.channels) {
+      if (kind == CB_ES_DC) {
+        enc_dc_chain((const i16*)r.in, (i16*)r.out, r.m, c, r.len, r.channels, r.shift);
+      } else if (kind == CB_ES_TRANSIENT) {
+        enc_ta_chain((const i32*)r.in + c * r.stride_in, (i16*)r.out + c * r.stride_out, r.len, &r.m[c], &r.m[2 + c]);
+      }
+    }
+  }
+  __syncwarp();
+  if (slot < nw && c == 0) table[slot].kind = CB_ES_NONE;
+  __syncwarp();
+}
+#endif
 
 // patch_transient_decision (celt_encoder.c:380-415)
 CB_FN_NOINLINE int enc_patch_transient(const i16* newE, const i16* oldE, int start, int end, int C) {

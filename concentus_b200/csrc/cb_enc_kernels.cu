@@ -21,8 +21,15 @@ opus_encode_kernel(OpusEncState* const* states, EncScratch* scratch, const i16* 
   const int warp = threadIdx.x >> 5;
   const int s = blockIdx.x * (blockDim.x >> 5) + warp;
   EncWork& w = *reinterpret_cast<EncWork*>(smem + (size_t)warp * sizeof(EncWork));
-  if ((threadIdx.x & 31) == 0) w.nsync = 0;
-  __syncwarp();
+  // the CTA's table of serial-section requests sits behind the warps' workspaces
+  EncSerialReq* table = reinterpret_cast<EncSerialReq*>(smem + (size_t)(blockDim.x >> 5) * sizeof(EncWork));
+  if ((threadIdx.x & 31) == 0) {
+    w.nsync = 0;
+    w.sreq = table + warp;
+    table[warp].kind = CB_ES_NONE;
+    table[warp].channels = 0;
+  }
+  __syncthreads();
   if (s < n) {
     const int ret = opus_encode_stream<MULTI>(w, scratch[s], states[s], pcm + (size_t)s * pcm_stride, frame_size,
                                        data + (size_t)s * data_stride, max_data_bytes);
@@ -31,7 +38,11 @@ opus_encode_kernel(OpusEncState* const* states, EncScratch* scratch, const i16* 
   __syncwarp();
   // warps that left early (or have no stream) still owe the CTA their remaining rendezvous
   // (`phases` = CB_ENC_PHASES times the most 20 ms frames any stream of this launch codes for one call)
-  for (int k = w.nsync; k < phases; k++) __syncthreads();
+  // -- and warps 0 and 1 still run the serial sections of the streams that go on (cb_enc_state.h: EncSerialReq)
+  for (int k = w.nsync; k < phases; k++) {
+    __syncthreads();
+    enc_serial_run(table);
+  }
 }
 
 extern "C" int cbk_sm_count(void);   // SMs of the current device (opus_api.cu)
@@ -45,7 +56,7 @@ int cbk_launch_encode(OpusEncState* const* d_states, void* d_scratch, const i16*
                       int frame_size, u8* d_data, i32 data_stride, int max_data_bytes, i32* d_len, int n,
                       int max_subframes, int general, cudaStream_t stream) {
   static bool attr_set[16] = {false};
-  const size_t smem = sizeof(EncWork) * E_WARPS;
+  const size_t smem = (sizeof(EncWork) + sizeof(EncSerialReq)) * E_WARPS;
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev >= 0 && dev < 16 && !attr_set[dev]) {
@@ -63,7 +74,7 @@ int cbk_launch_encode(OpusEncState* const* d_states, void* d_scratch, const i16*
   if (ew > E_WARPS) ew = E_WARPS;
   if (ew < 1) ew = 1;
   const int blocks = (n + ew - 1) / ew;
-  const size_t smem_l = sizeof(EncWork) * ew;
+  const size_t smem_l = (sizeof(EncWork) + sizeof(EncSerialReq)) * ew;
   if (max_subframes > 1 || general)
     opus_encode_kernel<true><<<blocks, ew * 32, smem_l, stream>>>(d_states, (EncScratch*)d_scratch, d_pcm, pcm_stride,
                                                                     frame_size, d_data, data_stride, max_data_bytes, d_len, n,

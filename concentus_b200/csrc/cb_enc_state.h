@@ -164,12 +164,31 @@ struct alignas(16) EncScratch {
 // instructions and instruction-fetch stalls dominated when every warp sat in a different stage.
 // No data crosses warps; the barrier is only pacing.  Every warp must reach CB_ENC_PHASES barriers
 // per frame: a warp that leaves early (error, silence) makes up the remainder in the kernel wrapper.
-#define CB_ENC_PHASES (9 + 2 * CB_NBANDS)   // nine stage boundaries + two per band of the residual loop
+#define CB_ENC_PHASES (11 + 2 * CB_NBANDS)  // eleven stage boundaries + two per band of the residual loop
 #if CB_DEVICE_BUILD
 #define CB_ENC_PHASE(w) do { __syncthreads(); if (CB_LANE() == 0) (w).nsync++; __syncwarp(); } while (0)
 #else
 #define CB_ENC_PHASE(w) ((void)0)
 #endif
+
+// Serial sections.  Two parts of a frame are recurrences over its samples that cannot be reassociated bit-exactly:
+// the input high-pass (dc_reject, opus_encoder.c:362-384) and the transient detector's filter and smoothing passes
+// (celt_encoder.c:227-330).  Run by each warp for itself they keep one lane per channel busy for thousands of dependent
+// steps -- 12 % of the kernel's warp instructions.  Since the CTA's warps are at the same stage anyway (phase
+// rendezvous above), a warp instead posts a request, and after the next rendezvous the lanes of warps 0 and 1 run the
+// chains of all the CTA's streams side by side (lane = stream slot x channel); the rendezvous after that hands the
+// results back.  The warps that run the chains look for requests after EVERY rendezvous they pass, also while they are
+// only making up rendezvous for a stream that ended early (cb_enc_kernels.cu).
+#define CB_ES_NONE 0
+#define CB_ES_DC 1                 // dc_reject
+#define CB_ES_TRANSIENT 2          // transient_analysis: high-pass, forward / backward smoothing
+struct EncSerialReq {
+  const void* in;                  // DC: int16 PCM in (interleaved); transient: i32 signal, `stride_in` per channel
+  void* out;                       // DC: int16 out (interleaved); transient: i16 work vector, `stride_out` per channel
+  i32 kind, len, channels, shift;  // (shift: DC only)
+  i32 stride_in, stride_out;
+  i32 m[4];                        // DC: the filter memories, in and out; transient: out, mean[0..1] then maxE[0..1]
+};
 
 // One level of the encoder's split recursion (quant_partition).
 struct EncPartFrame {
@@ -217,5 +236,6 @@ struct alignas(16) EncWork {
   EncPartFrame stack[5];
   EncSplit sp_store;
   i32 nsync;                     // phase rendezvous points passed so far (CB_ENC_PHASE)
+  EncSerialReq* sreq;            // device: this warp's slot in the CTA's table of serial-section requests
   RangeEnc enc, enc_save0, enc_save1;
 };

@@ -102,49 +102,24 @@ CB_FN void enc_move_down(i16* buf, int shift, int n) {
 #endif
 }
 
-// dc_reject (opus_encoder.c:362-384): two cascaded one-pole sections; one lane per channel.
+// Host build: both channels in turn.  (The device posts a request instead: enc_post_dc below.)
 CB_FN void enc_dc_reject(const i16* in, int cutoff_Hz, i16* out, i32* hp_mem, int len, int channels, int Fs) {
   const int shift = cb_ilog2(Fs / (cutoff_Hz * 3));
-  CB_WSYNC();
+  for (int c = 0; c < channels; c++) enc_dc_chain(in, out, hp_mem, c, len, channels, shift);
+}
+
 #if CB_DEVICE_BUILD
-  const int c = CB_LANE();
-  if (c < channels) {
-#else
-  for (int c = 0; c < channels; c++) {
-#endif
-    i32 m0 = hp_mem[2 * c], m1 = hp_mem[2 * c + 1];
-    const i16* ip = in + c;
-    i16* op = out + c;
-    int i = 0;
-    CB_NOUNROLL for (; i + 4 <= len; i += 4) {              // four samples per trip: loads first, then the chain
-      i32 xs[4];
-      for (int k = 0; k < 4; k++) xs[k] = ip[channels * (i + k)];
-      for (int k = 0; k < 4; k++) {
-        const i32 x = shl32(xs[k], 15);
-        const i32 tmp = sub32(x, m0);
-        m0 = add32(m0, pshr32(tmp, shift));
-        const i32 y = sub32(tmp, m1);
-        m1 = add32(m1, pshr32(y, shift));
-        i32 v = pshr32(y, 15);
-        v = v > 32767 ? 32767 : (v < -32767 ? -32767 : v);
-        op[channels * (i + k)] = (i16)v;
-      }
-    }
-    for (; i < len; i++) {
-      const i32 x = shl32(ip[channels * i], 15);
-      const i32 tmp = sub32(x, m0);
-      m0 = add32(m0, pshr32(tmp, shift));
-      const i32 y = sub32(tmp, m1);
-      m1 = add32(m1, pshr32(y, shift));
-      i32 v = pshr32(y, 15);
-      v = v > 32767 ? 32767 : (v < -32767 ? -32767 : v);
-      op[channels * i] = (i16)v;
-    }
-    hp_mem[2 * c] = m0;
-    hp_mem[2 * c + 1] = m1;
+CB_FN void enc_post_dc(EncWork& w, const i16* in, int cutoff_Hz, i16* out, const i32* hp_mem, int len, int channels, int Fs) {
+  CB_WSYNC();
+  if (CB_LANE() == 0) {
+    EncSerialReq& r = *w.sreq;
+    r.in = in; r.out = out; r.len = len; r.channels = channels; r.shift = cb_ilog2(Fs / (cutoff_Hz * 3));
+    for (int k = 0; k < 4; k++) r.m[k] = hp_mem[k];
+    r.kind = CB_ES_DC;
   }
   CB_WSYNC();
 }
+#endif
 
 // stereo_fade (opus_encoder.c:411-441), in place
 CB_FN void enc_stereo_fade(i16* buf, i32 g1, i32 g2, int frame_size, int Fs) {
@@ -424,14 +399,28 @@ CB_FN int enc_one_frame(EncWork& w, EncScratch& sc, OpusEncState* st, OpusEncSca
     const i32 hp_freq_smth1 = esk_lin2log(60) << 8;
     o.variable_HP_smth2_Q15 = esk_smlawb(o.variable_HP_smth2_Q15, hp_freq_smth1 - o.variable_HP_smth2_Q15, 983);
     const i32 cutoff_Hz = esk_log2lin(o.variable_HP_smth2_Q15 >> 8);
+#if CB_DEVICE_BUILD
+    // the VOIP high-pass (a biquad) stays with the warp; dc_reject goes to the CTA's serial section
+    const bool voip = o.application == CB_APP_VOIP;
+    if (voip) {
+      enc_hp_cutoff(pcm, cutoff_Hz, &pcm_buf[total_buffer * ch], o.hp_mem, frame_size, ch, o.Fs);
+      for (int k = 0; k < 4; k++) o.hp_mem[k] = __shfl_sync(0xffffffffu, o.hp_mem[k], k >> 1);
+    } else {
+      enc_post_dc(w, pcm, 3, &pcm_buf[total_buffer * ch], o.hp_mem, frame_size, ch, o.Fs);
+    }
+    CB_ENC_PHASE(w);                                          // 0: serial-section requests posted
+    enc_serial_run(w.sreq - (threadIdx.x >> 5));
+    CB_ENC_PHASE(w);                                          // 1: input conditioned
+    if (!voip) {
+      for (int k = 0; k < 4; k++) o.hp_mem[k] = w.sreq->m[k];
+    }
+    CB_WSYNC();
+#else
     if (o.application == CB_APP_VOIP) enc_hp_cutoff(pcm, cutoff_Hz, &pcm_buf[total_buffer * ch], o.hp_mem, frame_size, ch, o.Fs);
     else enc_dc_reject(pcm, 3, &pcm_buf[total_buffer * ch], o.hp_mem, frame_size, ch, o.Fs);
-  }
-#if CB_DEVICE_BUILD
-  for (int k = 0; k < 4; k++) o.hp_mem[k] = __shfl_sync(0xffffffffu, o.hp_mem[k], k >> 1);
 #endif
+  }
 
-  CB_ENC_PHASE(w);                                            // 1: input conditioned
   // CELT set-up (opus_encoder.c:1697-1761)
   {
     int endband = 21;
