@@ -362,7 +362,11 @@ CB_FN void v_stereo_merge(i16* X, i16* Y, i32 mid, int N) {
 // anti_collapse (bands.c:241-335)
 CB_FN void v_anti_collapse(EntWork& w, int LM, int C, int Nfrm, int start, int end, const i16* logE,
                            const i16* prev1logE, const i16* prev2logE, u32 seed) {
+  const u32 all_blocks = (1u << (1 << LM)) - 1;
   CB_NOUNROLL for (int i = start; i < end; i++) {
+    // (nothing to do for a band none of whose short blocks collapsed -- the usual case -- and nothing here but the
+    // filled blocks advances the seed)
+    if ((w.collapse[i * C] & all_blocks) == all_blocks && (w.collapse[i * C + C - 1] & all_blocks) == all_blocks) continue;
     int N0 = ebands(i + 1) - ebands(i);
     int depth = (int)((u32)(1 + w.pulses[i]) / (u32)N0) >> LM;
     i32 thresh32 = cb_exp2(-(i32)shl16(depth, 10 - CB_BITRES)) >> 1;
