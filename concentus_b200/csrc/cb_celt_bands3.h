@@ -20,6 +20,18 @@
 // segment.
 #pragma once
 
+// Path counters of the host emulation build (tests/emu, CB_HOST_EMU): the CPU tests assert that the fixtures they
+// compare with the reference really take every branch of the rebuild below.  Nothing in a device build.
+#if defined(CB_HOST_EMU)
+enum { CB_COV_EMPTY_IN_TREE, CB_COV_EMPTY_WHOLE_CALL, CB_COV_MASKED, CB_COV_ZERO, CB_COV_NOISE, CB_COV_FOLD, CB_COV_SEGMENTS3,
+       CB_COV_SWITCH, CB_COV_JOINT2, CB_COV_N1_STEREO, CB_COV_N1_MONO, CB_COV_SIDE_FIRST, CB_COV_DUAL, CB_COV_RECOMBINE,
+       CB_COV_TIME_DIVIDE, CB_COV_SCRATCH, CB_COV_INV, CB_COV_COUNT };
+static long cb_cov[CB_COV_COUNT];
+#define CB_COV(k) (cb_cov[k]++)
+#else
+#define CB_COV(k) ((void)0)
+#endif
+
 // Writer side of the tape (PARSE): cursors in registers, the tape itself in global memory.
 struct TapeW {
   FrameTape* t;
@@ -305,16 +317,20 @@ CB_FN u32 b3_leaves_rebuild(EntWork& w, BandCtx& cx, B3Cur& cur, int note, int x
   CB_NOUNROLL for (int l = 0; l < nl; l++) {
     const TapeJob jb = cur.seg_jobs[j0 + l];
     if (jb.K != 0) continue;
+    if (nl > 1) CB_COV(CB_COV_EMPTY_IN_TREE); else CB_COV(CB_COV_EMPTY_WHOLE_CALL);
+    if (jb.idx) CB_COV(CB_COV_MASKED);
     const int N = jb.N;
     i16* const X = w.X + jb.xoff;
     const u32 cm_mask = (u32)((1ull << jb.B) - 1);
     const u32 lf = jb.idx ? 0u : (((u32)fill >> jb.sh) & cm_mask);
     CB_WSYNC();
     if (!lf) {
+      CB_COV(CB_COV_ZERO);
       CB_LANE_LOOP(j, N) X[j] = 0;
       CB_WSYNC();
       continue;
     }
+    if (lowband == nullptr) CB_COV(CB_COV_NOISE); else CB_COV(CB_COV_FOLD);
     const u32 seed0 = cx.seed;
     if (lowband == nullptr) {                                     // noise
       CB_LANE_LOOP(j, N) X[j] = (i16)((i32)cb_lcg_skip(seed0, (u32)j + 1) >> 20);
@@ -489,6 +505,7 @@ CB_FN u32 b3_band_rebuild(EntWork& w, BandCtx& cx, B3Cur& cur, int band, int xo,
                           i16* lowband_out, i16* lowband_scratch, int fill, int note, int sign) {
   i16* const X = w.X + xo;
   if (N == 1) {                                                  // quant_band_n1 (bands.c:819-858), one channel
+    CB_COV(CB_COV_N1_MONO);
     CB_WSYNC();
     X[0] = sign ? -CB_NORM_SCALING : CB_NORM_SCALING;
     CB_WSYNC();
@@ -503,11 +520,13 @@ CB_FN u32 b3_band_rebuild(EntWork& w, BandCtx& cx, B3Cur& cur, int band, int xo,
   i16* tmp = (i16*)w.tmp32;
   if (tf_change > 0) recombine = tf_change;
   if (lowband_scratch && lowband && (recombine || ((N_B & 1) == 0 && tf_change < 0) || B0 > 1)) {
+    CB_COV(CB_COV_SCRATCH);
     CB_WSYNC();
     CB_LANE_LOOP(j, N) lowband_scratch[j] = lowband[j];
     CB_WSYNC();
     lowband = lowband_scratch;
   }
+  if (recombine) CB_COV(CB_COV_RECOMBINE);
   CB_NOUNROLL for (int k = 0; k < recombine; k++) {
     if (lowband) v_haar1(lowband, N >> k, 1 << k);
     fill = ct_bit_interleave[fill & 0xF] | ct_bit_interleave[fill >> 4] << 2;
@@ -524,6 +543,7 @@ CB_FN u32 b3_band_rebuild(EntWork& w, BandCtx& cx, B3Cur& cur, int band, int xo,
   }
   B0 = B;
   const int N_B0 = N_B;
+  if (time_divide) CB_COV(CB_COV_TIME_DIVIDE);
   if (B0 > 1 && lowband) v_deinterleave(lowband, tmp, N_B >> recombine, B0 << recombine, longBlocks);
 
   u32 cm = b3_leaves_rebuild(w, cx, cur, note, xo, lowband, fill);
@@ -586,6 +606,7 @@ CB_FN void b3_one_band_rebuild(EntWork& w, B3Cur& cur, BandCtx& cx, int i, int s
   }
   if (!last) { lout = norm + xo - norm_offset; lout2 = norm2 + xo - norm_offset; }
   if (flags & CB_TBF_SWITCH) {                                   // dual stereo ends here (bands.c:1430-1437)
+    CB_COV(CB_COV_SWITCH);
     const int cnt = xo - norm_offset;
     CB_WSYNC();
     CB_LANE_LOOP(j, cnt) norm[j] = (i16)(((i32)norm[j] + (i32)norm2[j]) >> 1);
@@ -599,15 +620,18 @@ CB_FN void b3_one_band_rebuild(EntWork& w, B3Cur& cur, BandCtx& cx, int i, int s
   int cfill0 = (int)x_cm, cfill1 = (int)y_cm;
   bool side0 = false, side1 = false;                             // the call is the side of a mid / side pair: no folding
   bool second0 = false, second1 = true;                          // the call works on the second channel's folding memory
+  if (mode == CB_TB_DUAL) CB_COV(CB_COV_DUAL);
   if (mode == CB_TB_MONO) {
     ncalls = 1;
     cfill0 = (int)(x_cm | y_cm);
   } else if (mode == CB_TB_JOINT2) {
+    CB_COV(CB_COV_JOINT2);
     ncalls = 1;
     cX0 = itheta > 8192 ? yo : xo;
     cfill0 = (int)(x_cm | y_cm);
     second0 = false;
   } else if (mode == CB_TB_N1) {
+    CB_COV(CB_COV_N1_STEREO);
     side1 = true;                                                // (only X leaves something in the folding memory)
   } else if (mode == CB_TB_JOINT) {
     int fill = (int)(x_cm | y_cm);
@@ -617,6 +641,7 @@ CB_FN void b3_one_band_rebuild(EntWork& w, B3Cur& cur, BandCtx& cx, int i, int s
       cfill0 = fill; cfill1 = fill >> B;
       side1 = true;
     } else {
+      CB_COV(CB_COV_SIDE_FIRST);
       cX0 = yo; cX1 = xo;
       cfill0 = fill >> B; cfill1 = fill;
       side0 = true;
@@ -664,6 +689,7 @@ CB_FN void b3_one_band_rebuild(EntWork& w, B3Cur& cur, BandCtx& cx, int i, int s
       v_stereo_merge(X, Y, imid, N);
     }
     if (flags & CB_TBF_INV) {
+      CB_COV(CB_COV_INV);
       CB_WSYNC();
       CB_LANE_LOOP(j, N) Y[j] = (i16)(-Y[j]);
       CB_WSYNC();
@@ -723,6 +749,7 @@ CB_FN void dec_bands_rebuild(EntWork& w, const FrameTape* t, int start, int end,
   }
   CB_WSYNC();
   const int nseg = t->nseg;
+  if (nseg >= 3) CB_COV(CB_COV_SEGMENTS3);
   int job0 = 0;
   CB_NOUNROLL for (int sgi = 0; sgi < nseg; sgi++) {
     const TapeSeg sg = t->seg[sgi];

@@ -11,6 +11,12 @@
 
 extern "C" {
 
+// path counters of the band rebuild (cb_celt_bands3.h: CB_COV): copy out and clear
+int emu_cov_read(long* out, int n) {
+  for (int i = 0; i < n && i < CB_COV_COUNT; i++) { out[i] = cb_cov[i]; cb_cov[i] = 0; }
+  return CB_COV_COUNT;
+}
+
 // ---- CELT layer only (payload without TOC) ----
 void* emu_celt_create(int channels, int downsample) {
   CeltDecState* s = (CeltDecState*)malloc(sizeof(CeltDecState));
