@@ -277,26 +277,18 @@ CB_FN void b3_partition(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, int x
         b3_leaf_node(w, cx, rd, cur, f.xo, N, b, B, LM, f.gain, f.sh, f.fz);
         sp--;
       }
-    } else if (f.stage == 1) {                   // mid done, now side
+    } else if (f.stage == 1) {                   // mid done, now side: the node itself becomes its side half
       const i32 rebalance = f.mbits - (f.rebal0 - cx.remaining_bits);
       if (rebalance > 3 << CB_BITRES && f.itheta != 0) f.sbits += rebalance - (3 << CB_BITRES);
-      PartFrame& c = st[sp + 1];
-      c.N = f.N; c.B = f.B; c.LM = f.LM; c.stage = 0;
-      c.xo = f.xo + f.N; c.b = f.sbits; c.gain = (i16)f.gside;
-      c.sh = (u8)(f.sh + f.dsh); c.fz = (u8)(f.fz | (f.itheta == 0));
-      f.stage = 2;
-      sp++;
-    } else if (f.stage == 3) {                   // side done, now mid
+      f.xo = (u16)(f.xo + f.N); f.b = f.sbits; f.gain = (i16)f.gside;
+      f.sh = (u8)(f.sh + f.dsh); f.fz = (u8)(f.fz | (f.itheta == 0));
+      f.stage = 0;
+    } else {                                     // side done, now mid: the node itself becomes its mid half
       const i32 rebalance = f.sbits - (f.rebal0 - cx.remaining_bits);
       if (rebalance > 3 << CB_BITRES && f.itheta != 16384) f.mbits += rebalance - (3 << CB_BITRES);
-      PartFrame& c = st[sp + 1];
-      c.N = f.N; c.B = f.B; c.LM = f.LM; c.stage = 0;
-      c.xo = f.xo; c.b = f.mbits; c.gain = (i16)f.gmid;
-      c.sh = f.sh; c.fz = (u8)(f.fz | (f.itheta == 16384));
-      f.stage = 4;
-      sp++;
-    } else {                                     // both halves done
-      sp--;
+      f.b = f.mbits; f.gain = (i16)f.gmid;
+      f.fz = (u8)(f.fz | (f.itheta == 16384));
+      f.stage = 0;
     }
   }
 }
