@@ -236,8 +236,8 @@ CB_FN void b3_partition(EntWork& w, BandCtx& cx, RangeDec& rd, B3Cur& cur, int x
     PartFrame& f = st[sp];
     if (f.stage == 0) {
       int N = f.N, b = f.b, B = f.B, LM = f.LM;
-      const u8* cache = pulse_cache(cx.i, LM);
-      const int split = LM != -1 && b > cache[cache[0]] + 12 && N > 2;
+      // (bands.c:893: b > cache[cache[0]] + 12, from the derived table)
+      const int split = LM != -1 && N > 2 && b > ct_split_thresh[(LM + 1) * CB_NBANDS + cx.i];
       if (split) {
         const int B0 = B;
         N >>= 1;

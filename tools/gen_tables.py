@@ -111,6 +111,10 @@ def main():
     T["band_of_bin_g"] = ("uint8_t", [max(b for b in range(21) if eb[b] <= j) for j in range(eb[21])])   # band of a 2.5 ms bin
     T["cache_bits50_g"] = (T["cache_bits50"][0], T["cache_bits50"][1] + [0] * 64)   # padded: lanes read 64 entries of a row
     T["band_alloc_g"] = T["band_alloc"]
+    # derived: the budget above which quant_partition splits a band (bands.c:893: b > cache[cache[0]] + 12), per
+    # (LM + 1, band) like cache_index50 -- one read instead of two dependent ones in the parse walk
+    ci, cbits = T["cache_index50"][1], T["cache_bits50"][1]
+    T["split_thresh"] = ("int16_t", [cbits[i + cbits[i]] + 12 if i >= 0 else 32767 for i in ci])
     T["pvq_u_data_g"] = ("uint32_t", data)
     T["pvq_u_row_g"] = ("int16_t", rows)
     assert len(T["eband5ms"][1]) == 22 and len(T["band_alloc"][1]) == 231
@@ -137,7 +141,7 @@ def main():
           " * (normative RFC 6716 data, libopus 1.1.2) for the plain-C oracle. */\n#ifndef ORACLE_TABLES_H\n"
           "#define ORACLE_TABLES_H\n#include <stdint.h>\n"]
     for name, (ty, vals) in T.items():
-        if name.endswith("_g"):
+        if name.endswith("_g") or name == "split_thresh":
             continue
         oc.append("static const %s ot_%s[%d] = {\n%s\n};\n" % (ty, name, len(vals), fmt(vals)))
     oc.append("#endif\n")
