@@ -138,7 +138,11 @@ CB_FN int bits2pulses_lanes(int band, int LM, int bits) {
   if (bits - (lo == 0 ? -1 : (int)cache[lo]) <= (int)cache[hi] - bits) return lo;
   return hi;
 #else
-  return bits2pulses(band, LM, bits);
+  // one thread (the parse kernel, the host build): the answer from the derived table (celt_tables.h:
+  // ct_bits2pulses, every (row, budget) of the bisection above worked out by the generator)
+  if (bits < 0) return bits2pulses(band, LM, bits);
+  const int row = ct_pulse_row[(LM + 1) * CB_NBANDS + band];
+  return ct_bits2pulses[row * 257 + cb_imin(bits, 256)];
 #endif
 }
 CB_FN int pulses2bits(int band, int LM, int pulses) {

@@ -115,6 +115,27 @@ def main():
     # (LM + 1, band) like cache_index50 -- one read instead of two dependent ones in the parse walk
     ci, cbits = T["cache_index50"][1], T["cache_bits50"][1]
     T["split_thresh"] = ("int16_t", [cbits[i + cbits[i]] + 12 if i >= 0 else 32767 for i in ci])
+    # derived: bits2pulses (rate.h:48-70) as a table.  The 6-step bisection over a row of cache_bits50 depends on
+    # (row, bits) only and is constant from bits = 256 on (no entry exceeds 255), so every answer fits in
+    # 23 rows x 257 budgets; pulse_row maps (LM + 1, band) to the row.
+    def bits2pulses(row, bits):
+        cache = cbits[row:]
+        lo, hi = 0, cache[0]
+        bits -= 1
+        for _ in range(6):
+            mid = (lo + hi + 1) >> 1
+            if cache[mid] >= bits:
+                hi = mid
+            else:
+                lo = mid
+        return lo if bits - (-1 if lo == 0 else cache[lo]) <= cache[hi] - bits else hi
+    rows_d = sorted(set(i for i in ci if i >= 0))
+    T["pulse_row"] = ("uint8_t", [rows_d.index(i) if i >= 0 else 255 for i in ci])
+    inv = []
+    for r in rows_d:
+        inv += [bits2pulses(r, b) for b in range(257)]
+        assert all(bits2pulses(r, b) == bits2pulses(r, 256) for b in range(256, 4096))
+    T["bits2pulses"] = ("uint8_t", inv)
     T["pvq_u_data_g"] = ("uint32_t", data)
     T["pvq_u_row_g"] = ("int16_t", rows)
     assert len(T["eband5ms"][1]) == 22 and len(T["band_alloc"][1]) == 231
@@ -141,7 +162,7 @@ def main():
           " * (normative RFC 6716 data, libopus 1.1.2) for the plain-C oracle. */\n#ifndef ORACLE_TABLES_H\n"
           "#define ORACLE_TABLES_H\n#include <stdint.h>\n"]
     for name, (ty, vals) in T.items():
-        if name.endswith("_g") or name == "split_thresh":
+        if name.endswith("_g") or name in ("split_thresh", "pulse_row", "bits2pulses"):
             continue
         oc.append("static const %s ot_%s[%d] = {\n%s\n};\n" % (ty, name, len(vals), fmt(vals)))
     oc.append("#endif\n")
