@@ -122,6 +122,13 @@ CB_FN int bits2pulses(int band, int LM, int bits) {
 // the bisection measured faster).  The reference's 6-step bisection over a non-decreasing row ends at
 // hi = the first entry >= bits (or the last entry when none is) and lo = hi - 1 -- checked exhaustively
 // over every row and every budget.
+// The same answer from the derived table (celt_tables.h: ct_bits2pulses, every (row, budget) of the bisection above
+// worked out by the generator; tests/test_kat.py compares the two exhaustively).
+CB_FN int bits2pulses_tab(int band, int LM, int bits) {
+  if (bits < 0) return bits2pulses(band, LM, bits);
+  const int row = ct_pulse_row[(LM + 1) * CB_NBANDS + band];
+  return ct_bits2pulses[row * 257 + cb_imin(bits, 256)];
+}
 CB_FN int bits2pulses_lanes(int band, int LM, int bits) {
 #if CB_DEVICE_BUILD
   const u8* cache = pulse_cache(band, LM);
@@ -138,11 +145,7 @@ CB_FN int bits2pulses_lanes(int band, int LM, int bits) {
   if (bits - (lo == 0 ? -1 : (int)cache[lo]) <= (int)cache[hi] - bits) return lo;
   return hi;
 #else
-  // one thread (the parse kernel, the host build): the answer from the derived table (celt_tables.h:
-  // ct_bits2pulses, every (row, budget) of the bisection above worked out by the generator)
-  if (bits < 0) return bits2pulses(band, LM, bits);
-  const int row = ct_pulse_row[(LM + 1) * CB_NBANDS + band];
-  return ct_bits2pulses[row * 257 + cb_imin(bits, 256)];
+  return bits2pulses_tab(band, LM, bits);       // one thread (the parse kernel, the host build)
 #endif
 }
 CB_FN int pulses2bits(int band, int LM, int pulses) {

@@ -279,7 +279,7 @@ CB_FN_NOINLINE void enc_theta(EncWork& w, RangeEnc& enc, int band, int intensity
 
 // leaf of quant_partition (bands.c:966-994, encoder side)
 CB_FN void enc_part_leaf(EncWork& w, EncBandCtx& cx, RangeEnc& enc, i16* X, int N, int b, int B, int LM) {
-  int q = bits2pulses(cx.i, LM, b);
+  int q = bits2pulses_tab(cx.i, LM, b);
   int curr_bits = pulses2bits(cx.i, LM, q);
   cx.remaining_bits -= curr_bits;
   CB_NOUNROLL while (cx.remaining_bits < 0 && q > 0) {

@@ -17,6 +17,11 @@ unsigned kat_pvq_v(int n, int k) { return pvq_u(n, k) + pvq_u(n, k + 1); }      
 int kat_cwrsi(int n, int k, unsigned idx, short* y) { return b3_cwrsi(y, n, k, idx); }   // returns yy
 unsigned kat_icwrs(int n, const short* y) { return enc_icwrs(n, y); }
 int kat_get_pulses(int i) { return get_pulses(i); }
+// bits2pulses (rate.h:48-70): the reference's bisection and the table-driven form the scalar builds use
+int kat_bits2pulses_bisect(int band, int LM, int bits) { return bits2pulses(band, LM, bits); }
+int kat_bits2pulses_table(int band, int LM, int bits) { return bits2pulses_lanes(band, LM, bits); }
+int kat_split_thresh(int band, int LM) { return ct_split_thresh[(LM + 1) * CB_NBANDS + band]; }
+int kat_split_thresh_ref(int band, int LM) { const u8* c = pulse_cache(band, LM); return c[c[0]] + 12; }
 
 // ---- mathops.c / mathops.h ----
 unsigned kat_isqrt32(unsigned v) { return cb_isqrt32(v); }

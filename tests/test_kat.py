@@ -130,6 +130,20 @@ def test_log2_exp2_accuracy(kat):
         x += x >> 3
 
 
+def test_derived_rate_tables_equal_the_bisection(kat):
+    """The parse walk reads bits2pulses (rate.h:48-70) and the split threshold (bands.c:893) from tables the
+    generator derives (tools/gen_tables.py); every entry must equal what the reference's own search gives -- all
+    (LM, band) rows of the mode, every budget up to well past the largest cache entry."""
+    for LM in range(0, 4):
+        for band in range(21):
+            assert kat.kat_split_thresh(band, LM) == kat.kat_split_thresh_ref(band, LM)
+            for bits in list(range(0, 420)) + [1000, 8191, 16383]:
+                assert kat.kat_bits2pulses_table(band, LM, bits) == kat.kat_bits2pulses_bisect(band, LM, bits), (LM, band, bits)
+    for band in range(8, 21):                       # LM = -1 rows exist from band 8 on (a split of an LM = 0 band)
+        for bits in range(0, 300):
+            assert kat.kat_bits2pulses_table(band, -1, bits) == kat.kat_bits2pulses_bisect(band, -1, bits)
+
+
 def test_bitexact_cos_checksum(kat):
     """test_unit_mathops.c testbitexactcos :121-147: checksum and monotonic step bounds over 64..16320."""
     chk, last, min_d, max_d = 0, 32767, 32767, 0
