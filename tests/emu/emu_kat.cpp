@@ -20,6 +20,7 @@ int kat_get_pulses(int i) { return get_pulses(i); }
 // bits2pulses (rate.h:48-70): the reference's bisection and the table-driven form the scalar builds use
 int kat_bits2pulses_bisect(int band, int LM, int bits) { return bits2pulses(band, LM, bits); }
 int kat_bits2pulses_table(int band, int LM, int bits) { return bits2pulses_lanes(band, LM, bits); }
+int kat_compute_qn(int N, int b, int offset, int pulse_cap, int stereo) { return compute_qn(N, b, offset, pulse_cap, stereo); }
 int kat_split_thresh(int band, int LM) { return ct_split_thresh[(LM + 1) * CB_NBANDS + band]; }
 int kat_split_thresh_ref(int band, int LM) { const u8* c = pulse_cache(band, LM); return c[c[0]] + 12; }
 

@@ -144,6 +144,31 @@ def test_derived_rate_tables_equal_the_bisection(kat):
             assert kat.kat_bits2pulses_table(band, -1, bits) == kat.kat_bits2pulses_bisect(band, -1, bits)
 
 
+def test_compute_qn(kat):
+    """compute_qn (bands.c:596-616) against a restatement that divides the way the reference does."""
+    exp2_table8 = [16384, 17866, 19483, 21247, 23170, 25267, 27554, 30048]
+
+    def ref_qn(N, b, offset, pulse_cap, stereo):
+        N2 = 2 * N - 1
+        if stereo and N == 2:
+            N2 -= 1
+        num = b + N2 * offset
+        qb = abs(num) // N2 * (1 if num >= 0 else -1)          # C division truncates toward zero
+        qb = min(b - pulse_cap - 32, qb)
+        qb = min(64, qb)
+        if qb < 4:
+            return 1
+        qn = exp2_table8[qb & 7] >> (14 - (qb >> 3))
+        return (qn + 1) >> 1 << 1
+
+    for N in (2, 3, 4, 6, 8, 9, 11, 12, 16, 18, 22, 24, 36, 44, 48, 72, 88, 96, 144, 176):
+        for stereo in (0, 1):
+            for pulse_cap in (0, 8, 20, 33, 48, 64):
+                offset = (pulse_cap >> 1) - (16 if stereo and N == 2 else 4)
+                for b in list(range(0, 600, 7)) + [1000, 5000, 16383, 81600]:
+                    assert kat.kat_compute_qn(N, b, offset, pulse_cap, stereo) == ref_qn(N, b, offset, pulse_cap, stereo)
+
+
 def test_bitexact_cos_checksum(kat):
     """test_unit_mathops.c testbitexactcos :121-147: checksum and monotonic step bounds over 64..16320."""
     chk, last, min_d, max_d = 0, 32767, 32767, 0
