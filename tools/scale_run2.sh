@@ -10,13 +10,13 @@ run() {  # config n
         bench.py --gpus $2 --config $1 --steps 60 --warmup 5 --no-cpu-baseline
   fi 2>> $R/r02_scale.err | tail -1
 }
-for c in 2 5; do
+for c in ${SCALE_CONFIGS:-2 5}; do
   : > $R/r02_scale_$c.json
   for n in 1 2 4 8; do run $c $n >> $R/r02_scale_$c.json; done
 done
 python - <<'PY'
-import json
-for c in ("2", "5"):
+import json, os
+for c in os.environ.get("SCALE_CONFIGS", "2 5").split():
     for l in open("gpurun_out/r02_scale_%s.json" % c):
         try:
             d = json.loads(l)
