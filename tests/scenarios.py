@@ -155,3 +155,25 @@ def silk_fuzz_calls(packets, seed, random_toc=False):
             p = bytes([int(rng.randint(0, 256)) & 0xFC]) + p[1:]       # any configuration, one frame
         out.append(p)
     return out
+
+
+def random_payload_scenario(fs, ch, seed, n=160):
+    """Packets with a CELT-only TOC and RANDOM payload bytes: whatever band layout, stereo mode, split tree, tf /
+    anti-collapse combination the bits happen to spell (things no encoder would emit included).  Golden and
+    corrupted-golden packets stay close to what the encoder produces; these do not.  -> (meta, calls)."""
+    rng = np.random.default_rng(seed)
+    calls = []
+    for k in range(n):
+        stereo = int(rng.integers(0, 2))
+        cfg = int(rng.integers(16, 32))                       # CELT-only NB .. FB, 2.5 .. 20 ms
+        toc = (cfg << 3) | (stereo << 2)
+        size = int(rng.choice([2, 3, 6, 12, 25, 50, 100, 160, 240, 400, 700, 1275]))
+        if int(rng.integers(0, 5)) == 0:
+            body = bytes([int(rng.choice([0, 255]))]) * (size - 1)
+        else:
+            body = rng.integers(0, 256, size - 1, dtype=np.uint8).tobytes()
+        spf = fs // 400 << (cfg & 3)
+        calls.append((bytes([toc]) + body, spf, 0))
+        if k % 23 == 5:
+            calls.append((None, spf, 0))                      # and a loss now and then
+    return {"fs": fs, "channels": ch}, calls

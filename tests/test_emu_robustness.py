@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 
 from conftest import RefDecoder, needs_ref
-from scenarios import fuzz_scenario, loss_scenario
+from scenarios import fuzz_scenario, loss_scenario, random_payload_scenario
 
 LOSS = ["c2_96k_cbr_st", "vbr_128k_st", "f10_64k_st", "f2_5_96k_st", "mono_12k", "low_24k_st",
         "st_to_mono_out", "mono_to_st_out", "st_to_24k_out", "mono_to_16k_out", "nb_20k_mono"]
@@ -130,3 +130,12 @@ def test_emu_max_passes_cap(emu_lib):
     finally:
         emu_lib.emu_opus_destroy(a)
         emu_lib.emu_opus_destroy(b)
+
+
+@needs_ref
+@pytest.mark.parametrize("fs,ch,seed", [(48000, 2, 1), (48000, 1, 2), (24000, 2, 3), (16000, 1, 4)])
+def test_emu_random_celt_payloads(emu_lib, fs, ch, seed):
+    """Random payloads behind a CELT-only TOC (scenarios.random_payload_scenario): the tape the parse half writes and
+    the rebuild half's reading of it must give the reference's PCM and final range for any bit pattern."""
+    meta, calls = random_payload_scenario(fs, ch, seed)
+    _run(emu_lib, meta, calls)

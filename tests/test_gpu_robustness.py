@@ -10,7 +10,7 @@ import pytest
 
 import concentus_b200 as cb
 from conftest import RefDecoder, needs_ref
-from scenarios import fuzz_scenario, loss_scenario
+from scenarios import fuzz_scenario, loss_scenario, random_payload_scenario
 
 pytestmark = pytest.mark.gpu
 
@@ -80,6 +80,17 @@ def test_gpu_multiframe_and_corruption_batch():
     for rep in range(3):
         for name in FUZZ:
             scripts.append(fuzz_scenario(name, seed=len(name) + 3 + 100 * rep))
+    _run_batch(scripts)
+
+
+@needs_ref
+def test_gpu_random_celt_payloads_batch():
+    """48 streams fed random payloads behind CELT-only TOCs (every frame size, mono / stereo packets into mono /
+    stereo decoders at 48 / 24 / 16 kHz): each must follow the reference."""
+    scripts = []
+    for rep in range(12):
+        for fs, ch in ((48000, 2), (48000, 1), (24000, 2), (16000, 1)):
+            scripts.append(random_payload_scenario(fs, ch, seed=1000 + 17 * rep + ch + fs // 8000, n=60))
     _run_batch(scripts)
 
 
